@@ -1,0 +1,261 @@
+"""Voxel worlds: the input side of the hot path.
+
+A *world* is an ordered list of voxel objects (robots first, then everything else, each group
+alphabetical -- the load order ``EvoSim._init_world_items`` imposes, reference
+``evogym/sim.py:52-62``), each described exactly by what the reference hands to
+``Sim.read_robot_from_array`` / ``Sim.read_object_from_array`` (``evogym/sim.py:67-97``):
+
+* ``grid``        -- ``(h, w)`` int array of voxel types, **row 0 is the TOP row**,
+* ``connections`` -- ``(2, k)`` int array of connected voxel index pairs, indices into ``grid.ravel()``,
+* ``x, y``        -- position of the bottom-left voxel in the world grid, in voxels,
+* ``is_robot``    -- object contains at least one actuator voxel.
+
+This module is a fresh, small implementation (numpy only) so the package is self-contained on a
+machine without the reference checkout; duck-typed ``evogym.EvoWorld`` instances are accepted too
+(see :func:`WorldSpec.from_evoworld`).
+"""
+from __future__ import annotations
+
+import json
+import random as _random
+from dataclasses import dataclass, field
+from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+VOXEL_TYPES = {"EMPTY": 0, "RIGID": 1, "SOFT": 2, "H_ACT": 3, "V_ACT": 4, "FIXED": 5}
+VOXEL_SIZE = 0.1
+
+
+def full_connectivity(structure: np.ndarray) -> np.ndarray:
+    """All 4-adjacent non-empty voxel pairs of ``structure`` as a ``(2, k)`` int array.
+
+    Same contract as reference ``evogym/utils.py:257-292`` (right neighbour, then lower neighbour,
+    voxels visited in row-major order)."""
+    s = np.asarray(structure)
+    h, w = s.shape
+    out: List[Tuple[int, int]] = []
+    for r in range(h):
+        for c in range(w):
+            if s[r, c] == 0:
+                continue
+            if c + 1 < w and s[r, c + 1] != 0:
+                out.append((r * w + c, r * w + c + 1))
+            if r + 1 < h and s[r + 1, c] != 0:
+                out.append((r * w + c, (r + 1) * w + c))
+    if not out:
+        return np.zeros((2, 0), dtype=np.int64)
+    return np.asarray(out, dtype=np.int64).T
+
+
+def is_connected(structure: np.ndarray) -> bool:
+    """True when the non-empty voxels form one 4-connected component (``evogym/utils.py:205-238``)."""
+    s = np.asarray(structure)
+    nz = np.argwhere(s != 0)
+    if len(nz) == 0:
+        return False
+    h, w = s.shape
+    seen = np.zeros(s.shape, dtype=bool)
+    stack = [tuple(nz[0])]
+    seen[stack[0]] = True
+    while stack:
+        r, c = stack.pop()
+        for dr, dc in ((-1, 0), (1, 0), (0, -1), (0, 1)):
+            rr, cc = r + dr, c + dc
+            if 0 <= rr < h and 0 <= cc < w and s[rr, cc] != 0 and not seen[rr, cc]:
+                seen[rr, cc] = True
+                stack.append((rr, cc))
+    return bool(seen[s != 0].all())
+
+
+def has_actuator(structure: np.ndarray) -> bool:
+    s = np.asarray(structure)
+    return bool(((s == VOXEL_TYPES["H_ACT"]) | (s == VOXEL_TYPES["V_ACT"])).any())
+
+
+def sample_robot(shape: Tuple[int, int], pd: Optional[Sequence[float]] = None,
+                 rng=_random) -> Tuple[np.ndarray, np.ndarray]:
+    """Random valid (connected, actuated) robot of ``shape`` and its full connectivity.
+
+    Consumes the random stream exactly like reference ``evogym/utils.py:99-152``: one
+    ``rng.uniform(0, 1)`` per voxel, inverse-CDF over the voxel-type distribution (default
+    ``[0.6, .2, .2, .2, .2]`` normalised), whole-robot rejection until connected and actuated --
+    so ``random.seed(i); sample_robot((5, 5))`` reproduces the reference's robot ``i``."""
+    if pd is None:
+        pd = np.ones(5) / 5
+        pd[0] = 0.6
+    pd = np.asarray(pd, dtype=np.float64)
+    cdf_terms = pd / pd.sum()
+    h, w = shape
+    while True:
+        robot = np.zeros((h, w))
+        for r in range(h):
+            for c in range(w):
+                u = rng.uniform(0, 1)
+                acc = 0.0
+                pick = None
+                for t in range(cdf_terms.size):
+                    acc = acc + cdf_terms[t]
+                    if u <= acc:
+                        pick = t
+                        break
+                # the reference returns None (-> nan) when rounding leaves u above the last
+                # partial sum; that cannot produce a valid robot cell, so treat it as EMPTY.
+                robot[r, c] = 0 if pick is None else pick
+        if is_connected(robot) and has_actuator(robot):
+            return robot, full_connectivity(robot)
+
+
+@dataclass
+class ObjectSpec:
+    """One voxel object, in the form the simulator's ``read_*_from_array`` takes."""
+    name: str
+    grid: np.ndarray          # (h, w) ints, row 0 = top
+    connections: np.ndarray   # (2, k) ints into grid.ravel()
+    x: int
+    y: int
+
+    @property
+    def is_robot(self) -> bool:
+        return has_actuator(self.grid)
+
+    @property
+    def size(self) -> Tuple[int, int]:
+        return int(self.grid.shape[1]), int(self.grid.shape[0])  # (w, h)
+
+
+@dataclass
+class WorldSpec:
+    """Ordered voxel world."""
+    width: int = 1
+    height: int = 1
+    objects: Dict[str, ObjectSpec] = field(default_factory=dict)
+
+    # ---- construction -------------------------------------------------------------------
+    @classmethod
+    def from_json(cls, path: str) -> "WorldSpec":
+        """Load a world ``.json`` (format of reference ``evogym/world.py:39-72,367-433``:
+        ``grid_width``, ``grid_height``, ``objects{name: {indices, types, neighbors}}`` with voxel
+        indices counted row-major from the BOTTOM-left of the world grid)."""
+        with open(path, "r") as f:
+            state = json.load(f)
+        return cls.from_parsed_json(state)
+
+    @classmethod
+    def from_parsed_json(cls, state: dict) -> "WorldSpec":
+        gw, gh = int(state["grid_width"]), int(state["grid_height"])
+        world = cls(width=1, height=1)
+        for name, od in state["objects"].items():
+            idx = [int(i) for i in od["indices"]]
+            types = [int(t) for t in od["types"]]
+            if len(idx) != len(types) or len(idx) != len(od["neighbors"]) or not idx:
+                raise ValueError(f"corrupted object {name}")
+            xs = [i % gw for i in idx]
+            ys = [i // gw for i in idx]
+            x0, y0 = min(xs), min(ys)
+            w, h = max(xs) - x0 + 1, max(ys) - y0 + 1
+            grid = np.zeros((h, w), dtype=np.int64)       # row 0 = top
+            local = {}
+            for i, xx, yy, t in zip(idx, xs, ys, types):
+                r, c = (h - 1) - (yy - y0), xx - x0
+                grid[r, c] = t
+                local[i] = r * w + c
+            conn: List[Tuple[int, int]] = []
+            for i in idx:
+                for n in od["neighbors"][str(i)]:
+                    if int(n) not in local:
+                        raise ValueError(f"object {name} has voxels with invalid neighbors")
+                    conn.append((local[i], local[int(n)]))
+            cn = np.asarray(conn, dtype=np.int64).T if conn else np.zeros((2, 0), dtype=np.int64)
+            world.add_object(ObjectSpec(name, grid, cn, x0, y0))
+        world.width = max(world.width, gw)
+        world.height = max(world.height, gh)
+        return world
+
+    @classmethod
+    def from_evoworld(cls, world) -> "WorldSpec":
+        """Convert a duck-typed reference ``EvoWorld`` (``.grid_size``, ``.objects[name].grid`` with
+        row 0 = bottom, ``.neighbors`` keyed by ``Pair``) -- mirrors ``evogym/sim.py:64-97``."""
+        out = cls(width=int(world.grid_size.x), height=int(world.grid_size.y))
+        for name, obj in world.objects.items():
+            gw, gh = int(obj.grid_size.x), int(obj.grid_size.y)
+            conn: List[Tuple[int, int]] = []
+            by_xy = {(int(k.x), int(k.y)): neis for k, neis in obj.neighbors.items()}
+            for y in range(gh):
+                for x in range(gw):
+                    if obj.grid[y][x] == 0:
+                        continue
+                    for nei in by_xy.get((x, y), ()):
+                        conn.append(((gh - 1 - y) * gw + x, (gh - 1 - nei.y) * gw + nei.x))
+            cn = np.asarray(conn, dtype=np.int64).T if conn else np.zeros((2, 0), dtype=np.int64)
+            out.objects[name] = ObjectSpec(name, np.flipud(np.asarray(obj.grid)).astype(np.int64), cn,
+                                           int(obj.pos.x), int(obj.pos.y))
+        return out
+
+    def add_object(self, obj: ObjectSpec) -> None:
+        if obj.name in self.objects:
+            raise ValueError(f"cannot add object with duplicate name: {obj.name}")
+        if obj.x < 0 or obj.y < 0:
+            raise ValueError(f"object {obj.name} position must be non-negative")
+        w, h = obj.size
+        occ = self.occupancy()
+        self.width = max(self.width, obj.x + w)
+        self.height = max(self.height, obj.y + h)
+        for r in range(h):
+            for c in range(w):
+                if obj.grid[r, c] != 0 and (obj.x + c, obj.y + (h - 1 - r)) in occ:
+                    raise ValueError(f"cannot add object {obj.name}: overlaps an existing object")
+        self.objects[obj.name] = obj
+
+    def add_from_array(self, name: str, structure: np.ndarray, x: int, y: int,
+                       connections: Optional[np.ndarray] = None) -> None:
+        """Add an object from a ``(h, w)`` structure with row 0 = TOP (the orientation robots are
+        written in; reference ``evogym/world.py:75-94``)."""
+        grid = np.asarray(structure).astype(np.int64)
+        cn = full_connectivity(grid) if connections is None else np.asarray(connections, dtype=np.int64)
+        if cn.size == 0:
+            cn = np.zeros((2, 0), dtype=np.int64)
+        flat = grid.ravel()
+        for v in cn.ravel():
+            if v < 0 or v >= flat.size or flat[v] == 0:
+                raise ValueError(f"could not load object {name}: connections contain invalid elements")
+        self.add_object(ObjectSpec(name, grid, cn, int(x), int(y)))
+
+    # ---- queries ------------------------------------------------------------------------
+    def occupancy(self) -> set:
+        occ = set()
+        for o in self.objects.values():
+            w, h = o.size
+            for r in range(h):
+                for c in range(w):
+                    if o.grid[r, c] != 0:
+                        occ.add((o.x + c, o.y + (h - 1 - r)))
+        return occ
+
+    def load_order(self) -> List[ObjectSpec]:
+        """Robots first, then the rest, each alphabetical (``evogym/sim.py:52-62``); this fixes the
+        global point/edge numbering."""
+        keyed = sorted(((0 if o.is_robot else 1), name) for name, o in self.objects.items())
+        return [self.objects[name] for _, name in keyed]
+
+    def copy(self) -> "WorldSpec":
+        w = WorldSpec(self.width, self.height)
+        for name, o in self.objects.items():
+            w.objects[name] = ObjectSpec(o.name, o.grid.copy(), o.connections.copy(), o.x, o.y)
+        return w
+
+
+def flat_ground_world(width: int = 100, name: str = "ground") -> WorldSpec:
+    """``width`` x 1 strip of FIXED voxels at the bottom of the world: the terrain of Walker-v0
+    (reference ``evogym/envs/sim_files/Walker-v0.json``: grid 100 x 1, one object ``ground``)."""
+    w = WorldSpec(width=width, height=1)
+    grid = np.full((1, width), VOXEL_TYPES["FIXED"], dtype=np.int64)
+    w.add_from_array(name, grid, 0, 0)
+    return w
+
+
+def walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None, width: int = 100) -> WorldSpec:
+    """Walker-v0: flat fixed ground + ``robot`` placed at voxel (1, 1) (``evogym/envs/walk.py:19-20``)."""
+    w = flat_ground_world(width)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
