@@ -1,0 +1,161 @@
+/* mevo_b200 -- C ABI of the B200-native batched soft-body engine.
+ *
+ * Drop-in boundary for ONE hot path of ModularEvoGym / EvoGym: the substep loop
+ * Sim::step -> Environment::step -> PhysicsEngine::* (reference
+ * evogym/simulator/SimulatorCPP/Sim.cpp:105-115, Environment.cpp:166-205, PhysicsEngine.cpp).
+ * The reference exposes that path through the pybind11 class `Sim`
+ * (SimulatorCPP/PythonBindings.cpp:26-44); each entry point below names the `Sim` / `Environment`
+ * member it replaces.  The pybind11 module `simulator_cpp` shipped in modularevogym_b200/csrc is a
+ * thin C++ layer over exactly these functions, and tests bind them with ctypes.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ or torch types; no exception crosses this boundary.
+ *   - every function returning `int` returns >= 0 on success and MEVO_ERR (-1) on failure;
+ *     mevo_last_error() then describes the failure (thread-local string).
+ *   - one `mevo_batch` owns N independent environments on one GPU and one CUDA stream.  An
+ *     "environment" is what the reference calls one `Sim`.
+ *   - point arrays are (P, 2) row-major doubles x0,y0,x1,y1,... in the reference's global point
+ *     numbering (the memory order of its column-major 2 x P Eigen matrices); engine units (metres,
+ *     voxel = 0.1), i.e. what `Sim::pos_at_time` returns BEFORE `EvoSim` divides by VOXEL_SIZE.
+ *   - the library needs a CUDA device (sm_100a); there is no CPU fallback: creation fails loudly.
+ */
+#ifndef MEVO_B200_H
+#define MEVO_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MEVO_ERR (-1)
+#define MEVO_ABI_VERSION 1
+
+typedef struct mevo_batch mevo_batch;
+
+int mevo_abi_version(void);
+const char* mevo_last_error(void);
+int mevo_device_count(void);                       /* CUDA devices visible; MEVO_ERR if CUDA is unusable */
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+mevo_batch* mevo_batch_create(int device);         /* NULL on failure */
+void mevo_batch_destroy(mevo_batch* b);
+
+/* ---- world construction (host) -------------------------------------------------------------- */
+/* Sim::init(x, y)  (Sim.cpp:26-28): opens a new environment with a world grid of w x h voxels.
+ * Returns the environment id. */
+int mevo_batch_begin_env(mevo_batch* b, int world_w, int world_h);
+
+/* Sim::read_robot_from_array / Sim::read_object_from_array  (Sim.cpp:50-99).
+ *   grid : h x w row-major voxel types (0 empty, 1 rigid, 2 soft, 3 h-act, 4 v-act, 5 fixed), row 0 = TOP
+ *   conn : 2 x k, conn[i] and conn[k + i] are the two voxel indices (into grid) of connection i
+ *   x, y : position of the bottom-left voxel in the world grid, in voxels
+ * Returns 1 when the object was added, 0 when refused like the reference refuses it (message
+ * "Error: ..." on stdout, world unchanged), MEVO_ERR on API misuse. */
+int mevo_batch_add_object(mevo_batch* b, int env, const double* grid, int w, int h, const double* conn,
+                          int k, const char* name, double x, double y, int is_robot);
+
+/* Packs all environments into HBM (struct-of-arrays blobs) and uploads.  Called implicitly by the
+ * first step.  May be called again after adding environments/objects; state is preserved. */
+int mevo_batch_finalize(mevo_batch* b);
+
+/* ---- queries --------------------------------------------------------------------------------- */
+int mevo_batch_num_envs(const mevo_batch* b);
+int mevo_env_num_points(const mevo_batch* b, int env);
+int mevo_env_num_edges(const mevo_batch* b, int env);
+int mevo_env_num_objects(const mevo_batch* b, int env);
+int mevo_env_object_index(const mevo_batch* b, int env, const char* name);      /* MEVO_ERR if unknown */
+/* info[0..7] = is_robot, min_point_index, max_point_index, n_boxels, grid_w, grid_h, n_surface_boxels,
+ * is_static (all-FIXED object pruned from integration) */
+int mevo_env_object_info(const mevo_batch* b, int env, int obj, int* info);
+/* per boxel 18 ints: cell_type, grid_index, TL,TR,BR,BL point ids, top,right,bot,left edge ids, 8 neighbour flags */
+int mevo_env_object_boxels(const mevo_batch* b, int env, int obj, int* out);
+int mevo_env_object_surface_boxels(const mevo_batch* b, int env, int obj, int* out);
+/* Sim::get_actuator_indices (Sim.cpp:161-163): grid indices of the robot's actuators; returns the count */
+int mevo_env_actuator_indices(const mevo_batch* b, int env, const char* robot, int* out, int cap);
+/* topology arrays in global numbering; any pointer may be NULL */
+int mevo_env_get_topology(const mevo_batch* b, int env, double* pos0, double* mass, unsigned char* fixed,
+                          int* edge_a, int* edge_b, double* edge_k, double* edge_l0, unsigned char* edge_on_surface);
+
+/* ---- host-only world builder ----------------------------------------------------------------- */
+/* The same voxel-grid -> points/springs/boxels builder the batch uses (replaces ObjectCreator::
+ * read_object_from_array + SimObject::compute_surface, ObjectCreator.cpp:193-641, SimObject.cpp:235-307),
+ * usable without a GPU: topology checks, design tools, CPU tests of the host logic. */
+typedef struct mevo_world mevo_world;
+mevo_world* mevo_world_create(int world_w, int world_h);
+void mevo_world_destroy(mevo_world* w);
+int mevo_world_add_object(mevo_world* w, const double* grid, int gw, int gh, const double* conn, int k,
+                          const char* name, double x, double y, int is_robot);
+int mevo_world_num_points(const mevo_world* w);
+int mevo_world_num_edges(const mevo_world* w);
+int mevo_world_num_objects(const mevo_world* w);
+int mevo_world_object_info(const mevo_world* w, int obj, int* info);
+int mevo_world_object_boxels(const mevo_world* w, int obj, int* out);
+int mevo_world_object_surface_boxels(const mevo_world* w, int obj, int* out);
+int mevo_world_actuator_indices(const mevo_world* w, const char* robot, int* out, int cap);
+int mevo_world_get_topology(const mevo_world* w, double* pos0, double* mass, unsigned char* fixed,
+                            int* edge_a, int* edge_b, double* edge_k, double* edge_l0, unsigned char* edge_on_surface);
+
+/* ---- actions --------------------------------------------------------------------------------- */
+/* Sim::set_action (Sim.cpp:101-103 -> Environment::set_robot_action -> PhysicsEngine::update_actuator_goals):
+ * action is n x 2 row-major (actuator grid_index, target length ratio).  Only the listed actuators' edges
+ * are updated, exactly like the reference.  Returns 1, or 0 when refused (unknown robot / actuator). */
+int mevo_env_set_action(mevo_batch* b, int env, const char* robot, const double* action, int n);
+/* Batched form: values[env * stride + slot]; slot = actuators of the env's robots in load order, each
+ * robot's actuators in mevo_env_actuator_indices order.  Consumed by the next step with apply_actions = 1. */
+int mevo_batch_action_stride(const mevo_batch* b);            /* max actuators per env (after finalize) */
+int mevo_batch_set_actions(mevo_batch* b, const double* host_values, int stride);
+int mevo_batch_set_actions_device(mevo_batch* b, const double* device_values, int stride);
+
+/* ---- stepping -------------------------------------------------------------------------------- */
+/* Sim::step (Sim.cpp:105-115) for every environment, n_steps times, each 30 substeps of
+ * Environment::step.  An environment whose substep reports "unstable" stops there: its time does not
+ * advance (as in the reference) and its flag is set.  unstable_out (host, n_envs bytes) may be NULL.
+ * Returns the number of unstable environments.  apply_actions: 1 = derive edge goals from the batched
+ * action buffer on the device, 0 = keep the goals as last set by mevo_env_set_action. */
+int mevo_batch_step(mevo_batch* b, int n_steps, int apply_actions, unsigned char* unstable_out);
+/* as above with an explicit substep count (tests step one substep at a time = Environment::step) */
+int mevo_batch_step_substeps(mevo_batch* b, int n_steps, int n_substeps, int apply_actions, unsigned char* unstable_out);
+/* enqueue only; pair with mevo_batch_sync */
+int mevo_batch_step_async(mevo_batch* b, int n_steps, int apply_actions);
+int mevo_batch_sync(mevo_batch* b);
+int mevo_batch_last_launches(const mevo_batch* b);            /* kernels launched by the last step call */
+
+/* ---- state ----------------------------------------------------------------------------------- */
+/* Sim::get_time (Sim.cpp:135-137) */
+long mevo_env_get_time(mevo_batch* b, int env);
+int mevo_env_set_time(mevo_batch* b, int env, long t);
+/* current pos / vel / pos_last / vel_true (Environment.h:28-34); any pointer may be NULL */
+int mevo_env_get_state(mevo_batch* b, int env, double* pos, double* vel, double* pos_last, double* vel_true);
+/* overwrite the state (Sim::revert = pos, vel, pos_last := pos, vel_true := vel; Environment.cpp:247-263) */
+int mevo_env_set_state(mevo_batch* b, int env, const double* pos, const double* vel, const double* pos_last,
+                       const double* vel_true);
+/* length_eq_goal over all edges (Environment.h:41) */
+int mevo_env_get_goal(mevo_batch* b, int env, double* goal);
+int mevo_env_set_goal(mevo_batch* b, int env, const double* goal);
+/* Sim::translate_object (Sim.cpp:148-151) without the snapshot (the caller owns history) */
+int mevo_env_translate_object(mevo_batch* b, int env, const char* name, double dx, double dy);
+
+/* batched reset = Sim::revert(0) for the listed environments (goals are NOT reset, like the reference) */
+int mevo_batch_save_reset_state(mevo_batch* b);
+int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n);    /* env_ids NULL = all */
+/* centre of mass (mean of point positions) of object `obj` in every env: out = n_envs x 2 doubles (host) */
+int mevo_batch_object_com(mevo_batch* b, int obj, double* out);
+
+/* device pointers for zero-copy consumers (valid until the next finalize) */
+double* mevo_batch_actions_device_ptr(mevo_batch* b);
+const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b);
+void* mevo_batch_cuda_stream(mevo_batch* b);
+long long mevo_batch_device_bytes(const mevo_batch* b);
+
+/* ---- test hooks ------------------------------------------------------------------------------ */
+/* record the compacted collision-candidate list of the first substep of subsequent step calls */
+int mevo_batch_enable_candidate_dump(mevo_batch* b, int cap_per_env);
+/* out: cap x 4 ints (object_a, boxel_a, object_b, boxel_b); returns the number of candidates found.
+ * Pairs of two all-fixed objects are never generated (they cannot move anything); pairs inside one
+ * object are listed once (a < b) and applied twice, which is what the reference's ordered descent does. */
+int mevo_env_read_candidates(mevo_batch* b, int env, int* out, int cap);
+int mevo_env_error_flags(mevo_batch* b, int env);             /* bit 0: candidate list overflow */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MEVO_B200_H */

@@ -1,0 +1,397 @@
+"""ctypes binding of ``libmevo_b200.so`` -- exactly the functions ``include/mevo_b200.h`` declares.
+
+The product path: if the shared library is missing this module raises at import time of the first
+handle (``load()``); there is no Python or CPU fallback for the physics.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libmevo_b200.so")
+HEADER_PATH = os.path.join(PKG_DIR, "..", "include", "mevo_b200.h")
+
+_vp, _i, _d, _cp = C.c_void_p, C.c_int, C.c_double, C.c_char_p
+_dp, _ip, _bp = C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_ubyte)
+
+SIGNATURES: Dict[str, tuple] = {
+    "mevo_abi_version": (_i, []),
+    "mevo_last_error": (_cp, []),
+    "mevo_device_count": (_i, []),
+    "mevo_batch_create": (_vp, [_i]),
+    "mevo_batch_destroy": (None, [_vp]),
+    "mevo_batch_begin_env": (_i, [_vp, _i, _i]),
+    "mevo_batch_add_object": (_i, [_vp, _i, _dp, _i, _i, _dp, _i, _cp, _d, _d, _i]),
+    "mevo_batch_finalize": (_i, [_vp]),
+    "mevo_batch_num_envs": (_i, [_vp]),
+    "mevo_env_num_points": (_i, [_vp, _i]),
+    "mevo_env_num_edges": (_i, [_vp, _i]),
+    "mevo_env_num_objects": (_i, [_vp, _i]),
+    "mevo_env_object_index": (_i, [_vp, _i, _cp]),
+    "mevo_env_object_info": (_i, [_vp, _i, _i, _ip]),
+    "mevo_env_object_boxels": (_i, [_vp, _i, _i, _ip]),
+    "mevo_env_object_surface_boxels": (_i, [_vp, _i, _i, _ip]),
+    "mevo_env_actuator_indices": (_i, [_vp, _i, _cp, _ip, _i]),
+    "mevo_env_get_topology": (_i, [_vp, _i, _dp, _dp, _bp, _ip, _ip, _dp, _dp, _bp]),
+    "mevo_world_create": (_vp, [_i, _i]),
+    "mevo_world_destroy": (None, [_vp]),
+    "mevo_world_add_object": (_i, [_vp, _dp, _i, _i, _dp, _i, _cp, _d, _d, _i]),
+    "mevo_world_num_points": (_i, [_vp]),
+    "mevo_world_num_edges": (_i, [_vp]),
+    "mevo_world_num_objects": (_i, [_vp]),
+    "mevo_world_object_info": (_i, [_vp, _i, _ip]),
+    "mevo_world_object_boxels": (_i, [_vp, _i, _ip]),
+    "mevo_world_object_surface_boxels": (_i, [_vp, _i, _ip]),
+    "mevo_world_actuator_indices": (_i, [_vp, _cp, _ip, _i]),
+    "mevo_world_get_topology": (_i, [_vp, _dp, _dp, _bp, _ip, _ip, _dp, _dp, _bp]),
+    "mevo_env_set_action": (_i, [_vp, _i, _cp, _dp, _i]),
+    "mevo_batch_action_stride": (_i, [_vp]),
+    "mevo_batch_set_actions": (_i, [_vp, _dp, _i]),
+    "mevo_batch_set_actions_device": (_i, [_vp, _vp, _i]),
+    "mevo_batch_step": (_i, [_vp, _i, _i, _bp]),
+    "mevo_batch_step_substeps": (_i, [_vp, _i, _i, _i, _bp]),
+    "mevo_batch_step_async": (_i, [_vp, _i, _i]),
+    "mevo_batch_sync": (_i, [_vp]),
+    "mevo_batch_last_launches": (_i, [_vp]),
+    "mevo_env_get_time": (C.c_long, [_vp, _i]),
+    "mevo_env_set_time": (_i, [_vp, _i, C.c_long]),
+    "mevo_env_get_state": (_i, [_vp, _i, _dp, _dp, _dp, _dp]),
+    "mevo_env_set_state": (_i, [_vp, _i, _dp, _dp, _dp, _dp]),
+    "mevo_env_get_goal": (_i, [_vp, _i, _dp]),
+    "mevo_env_set_goal": (_i, [_vp, _i, _dp]),
+    "mevo_env_translate_object": (_i, [_vp, _i, _cp, _d, _d]),
+    "mevo_batch_save_reset_state": (_i, [_vp]),
+    "mevo_batch_reset": (_i, [_vp, _ip, _i]),
+    "mevo_batch_object_com": (_i, [_vp, _i, _dp]),
+    "mevo_batch_actions_device_ptr": (_vp, [_vp]),
+    "mevo_batch_unstable_device_ptr": (_vp, [_vp]),
+    "mevo_batch_cuda_stream": (_vp, [_vp]),
+    "mevo_batch_device_bytes": (C.c_longlong, [_vp]),
+    "mevo_batch_enable_candidate_dump": (_i, [_vp, _i]),
+    "mevo_env_read_candidates": (_i, [_vp, _i, _ip, _i]),
+    "mevo_env_error_flags": (_i, [_vp, _i]),
+}
+
+_lib = None
+
+
+class MevoError(RuntimeError):
+    pass
+
+
+def header_symbols(path: str = HEADER_PATH) -> List[str]:
+    """Function names declared in ``include/mevo_b200.h`` (used by the export test)."""
+    with open(path) as f:
+        text = re.sub(r"/\*.*?\*/", "", f.read(), flags=re.S)
+    return sorted(set(re.findall(r"\b(mevo_[a-z0-9_]+)\s*\(", text)))
+
+
+def load():
+    """Load the C-ABI library (fails loudly if it was not built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MevoError(f"{LIB_PATH} is missing: build it with `python -m modularevogym_b200._build` "
+                            "(needs nvcc). The engine has no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        if L.mevo_abi_version() != 1:
+            raise MevoError("libmevo_b200.so ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+def _dptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _iptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(_ip)
+
+
+def _bptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(_bp)
+
+
+def _check(rc: int) -> int:
+    if rc < 0:
+        raise MevoError(load().mevo_last_error().decode())
+    return rc
+
+
+OBJ_INFO_KEYS = ("is_robot", "min_point", "max_point", "n_boxels", "grid_w", "grid_h", "n_surface", "is_static")
+
+
+class HostWorld:
+    """Host-only world builder handle (no GPU): ``mevo_world_*``."""
+
+    def __init__(self, world=None, world_w: int = 1, world_h: int = 1):
+        self.L = load()
+        if world is not None:
+            world_w, world_h = world.width, world.height
+        self.h = self.L.mevo_world_create(int(world_w), int(world_h))
+        if not self.h:
+            raise MevoError(self.L.mevo_last_error().decode())
+        if world is not None:
+            for o in world.load_order():
+                if not self.add_object(o.grid, o.connections, o.name, o.x, o.y, o.is_robot):
+                    raise ValueError(f"object {o.name} refused")
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                self.L.mevo_world_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def add_object(self, grid, connections, name: str, x: float, y: float, is_robot: bool) -> bool:
+        g = np.ascontiguousarray(grid, dtype=np.float64)
+        cn = np.ascontiguousarray(connections, dtype=np.float64).reshape(2, -1)
+        return bool(_check(self.L.mevo_world_add_object(self.h, _dptr(g), g.shape[1], g.shape[0], _dptr(cn), cn.shape[1],
+                                                        name.encode(), float(x), float(y), int(bool(is_robot)))))
+
+    @property
+    def num_points(self): return self.L.mevo_world_num_points(self.h)
+    @property
+    def num_edges(self): return self.L.mevo_world_num_edges(self.h)
+    @property
+    def num_objects(self): return self.L.mevo_world_num_objects(self.h)
+
+    def object_info(self, obj: int) -> dict:
+        info = np.zeros(8, dtype=np.int32)
+        _check(self.L.mevo_world_object_info(self.h, obj, _iptr(info)))
+        return dict(zip(OBJ_INFO_KEYS, (int(v) for v in info)))
+
+    def object_boxels(self, obj: int) -> np.ndarray:
+        out = np.zeros((self.object_info(obj)["n_boxels"], 18), dtype=np.int32)
+        _check(self.L.mevo_world_object_boxels(self.h, obj, _iptr(out)))
+        return out
+
+    def object_surface_boxels(self, obj: int) -> np.ndarray:
+        out = np.zeros(self.object_info(obj)["n_surface"], dtype=np.int32)
+        _check(self.L.mevo_world_object_surface_boxels(self.h, obj, _iptr(out)))
+        return out
+
+    def actuator_indices(self, robot: str) -> np.ndarray:
+        out = np.zeros(4096, dtype=np.int32)
+        n = _check(self.L.mevo_world_actuator_indices(self.h, robot.encode(), _iptr(out), out.size))
+        return out[:n].copy()
+
+    def topology(self) -> dict:
+        P, E = self.num_points, self.num_edges
+        t = dict(pos0=np.zeros((P, 2)), mass=np.zeros(P), fixed=np.zeros(P, dtype=np.uint8),
+                 a=np.zeros(E, dtype=np.int32), b=np.zeros(E, dtype=np.int32), k=np.zeros(E), l0=np.zeros(E),
+                 on_surface=np.zeros(E, dtype=np.uint8))
+        _check(self.L.mevo_world_get_topology(self.h, _dptr(t["pos0"]), _dptr(t["mass"]), _bptr(t["fixed"]), _iptr(t["a"]),
+                                              _iptr(t["b"]), _dptr(t["k"]), _dptr(t["l0"]), _bptr(t["on_surface"])))
+        return t
+
+
+class Batch:
+    """N environments on one GPU: ``mevo_batch_*`` / ``mevo_env_*``."""
+
+    def __init__(self, device: int = 0):
+        self.L = load()
+        self.h = self.L.mevo_batch_create(int(device))
+        if not self.h:
+            raise MevoError(self.L.mevo_last_error().decode())
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.mevo_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- construction
+    def begin_env(self, world_w: int, world_h: int) -> int:
+        return _check(self.L.mevo_batch_begin_env(self.h, int(world_w), int(world_h)))
+
+    def add_object(self, env: int, grid, connections, name: str, x: float, y: float, is_robot: bool) -> bool:
+        g = np.ascontiguousarray(grid, dtype=np.float64)
+        cn = np.ascontiguousarray(connections, dtype=np.float64).reshape(2, -1)
+        return bool(_check(self.L.mevo_batch_add_object(self.h, env, _dptr(g), g.shape[1], g.shape[0], _dptr(cn), cn.shape[1],
+                                                        name.encode(), float(x), float(y), int(bool(is_robot)))))
+
+    def add_world(self, world) -> int:
+        """Add one environment from a ``WorldSpec`` (objects in the reference's load order)."""
+        env = self.begin_env(world.width, world.height)
+        for o in world.load_order():
+            if not self.add_object(env, o.grid, o.connections, o.name, o.x, o.y, o.is_robot):
+                raise ValueError(f"object {o.name} refused")
+        return env
+
+    def finalize(self) -> None:
+        _check(self.L.mevo_batch_finalize(self.h))
+
+    # -- queries
+    @property
+    def num_envs(self) -> int:
+        return self.L.mevo_batch_num_envs(self.h)
+
+    def num_points(self, env: int) -> int: return _check(self.L.mevo_env_num_points(self.h, env))
+    def num_edges(self, env: int) -> int: return _check(self.L.mevo_env_num_edges(self.h, env))
+    def num_objects(self, env: int) -> int: return _check(self.L.mevo_env_num_objects(self.h, env))
+    def object_index(self, env: int, name: str) -> int: return _check(self.L.mevo_env_object_index(self.h, env, name.encode()))
+
+    def object_info(self, env: int, obj: int) -> dict:
+        info = np.zeros(8, dtype=np.int32)
+        _check(self.L.mevo_env_object_info(self.h, env, obj, _iptr(info)))
+        return dict(zip(OBJ_INFO_KEYS, (int(v) for v in info)))
+
+    def object_boxels(self, env: int, obj: int) -> np.ndarray:
+        out = np.zeros((self.object_info(env, obj)["n_boxels"], 18), dtype=np.int32)
+        _check(self.L.mevo_env_object_boxels(self.h, env, obj, _iptr(out)))
+        return out
+
+    def object_surface_boxels(self, env: int, obj: int) -> np.ndarray:
+        out = np.zeros(self.object_info(env, obj)["n_surface"], dtype=np.int32)
+        _check(self.L.mevo_env_object_surface_boxels(self.h, env, obj, _iptr(out)))
+        return out
+
+    def actuator_indices(self, env: int, robot: str) -> np.ndarray:
+        out = np.zeros(4096, dtype=np.int32)
+        n = _check(self.L.mevo_env_actuator_indices(self.h, env, robot.encode(), _iptr(out), out.size))
+        return out[:n].copy()
+
+    def topology(self, env: int) -> dict:
+        P, E = self.num_points(env), self.num_edges(env)
+        t = dict(pos0=np.zeros((P, 2)), mass=np.zeros(P), fixed=np.zeros(P, dtype=np.uint8),
+                 a=np.zeros(E, dtype=np.int32), b=np.zeros(E, dtype=np.int32), k=np.zeros(E), l0=np.zeros(E),
+                 on_surface=np.zeros(E, dtype=np.uint8))
+        _check(self.L.mevo_env_get_topology(self.h, env, _dptr(t["pos0"]), _dptr(t["mass"]), _bptr(t["fixed"]), _iptr(t["a"]),
+                                            _iptr(t["b"]), _dptr(t["k"]), _dptr(t["l0"]), _bptr(t["on_surface"])))
+        return t
+
+    # -- actions
+    def set_action(self, env: int, robot: str, action) -> bool:
+        a = np.ascontiguousarray(action, dtype=np.float64).reshape(-1, 2)
+        return bool(_check(self.L.mevo_env_set_action(self.h, env, robot.encode(), _dptr(a), a.shape[0])))
+
+    def set_action_values(self, env: int, robot: str, values) -> bool:
+        idx = self.actuator_indices(env, robot)
+        return self.set_action(env, robot, np.stack((idx.astype(np.float64), np.asarray(values, dtype=np.float64).ravel()), axis=1))
+
+    @property
+    def action_stride(self) -> int:
+        return self.L.mevo_batch_action_stride(self.h)
+
+    def set_actions(self, values: np.ndarray) -> None:
+        """values: (n_envs, stride) float64 host array (pinned or pageable)."""
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        assert v.ndim == 2 and v.shape[0] == self.num_envs
+        _check(self.L.mevo_batch_set_actions(self.h, _dptr(v), v.shape[1]))
+
+    def set_actions_ptr(self, host_ptr: int, stride: int) -> None:
+        _check(self.L.mevo_batch_set_actions(self.h, C.cast(host_ptr, _dp), int(stride)))
+
+    def set_actions_device(self, device_ptr: int, stride: int) -> None:
+        _check(self.L.mevo_batch_set_actions_device(self.h, C.c_void_p(device_ptr), int(stride)))
+
+    # -- stepping
+    def step(self, n_steps: int = 1, apply_actions: bool = True, want_flags: bool = True):
+        flags = np.zeros(self.num_envs, dtype=np.uint8) if want_flags else None
+        n = _check(self.L.mevo_batch_step(self.h, int(n_steps), int(apply_actions), _bptr(flags)))
+        return (n, flags) if want_flags else n
+
+    def step_substeps(self, n_steps: int, n_substeps: int, apply_actions: bool = False):
+        flags = np.zeros(self.num_envs, dtype=np.uint8)
+        n = _check(self.L.mevo_batch_step_substeps(self.h, int(n_steps), int(n_substeps), int(apply_actions), _bptr(flags)))
+        return n, flags
+
+    def step_async(self, n_steps: int = 1, apply_actions: bool = True) -> None:
+        _check(self.L.mevo_batch_step_async(self.h, int(n_steps), int(apply_actions)))
+
+    def sync(self) -> None:
+        _check(self.L.mevo_batch_sync(self.h))
+
+    @property
+    def last_launches(self) -> int:
+        return self.L.mevo_batch_last_launches(self.h)
+
+    # -- state
+    def get_time(self, env: int) -> int:
+        return int(self.L.mevo_env_get_time(self.h, env))
+
+    def set_time(self, env: int, t: int) -> None:
+        _check(self.L.mevo_env_set_time(self.h, env, int(t)))
+
+    def get_state(self, env: int) -> Tuple[np.ndarray, np.ndarray, np.ndarray, np.ndarray]:
+        P = self.num_points(env)
+        out = [np.zeros((P, 2)) for _ in range(4)]
+        _check(self.L.mevo_env_get_state(self.h, env, *[_dptr(a) for a in out]))
+        return tuple(out)
+
+    def set_state(self, env: int, pos=None, vel=None, pos_last=None, vel_true=None) -> None:
+        arrs = [None if a is None else np.ascontiguousarray(a, dtype=np.float64) for a in (pos, vel, pos_last, vel_true)]
+        _check(self.L.mevo_env_set_state(self.h, env, *[_dptr(a) for a in arrs]))
+
+    def get_goal(self, env: int) -> np.ndarray:
+        out = np.zeros(self.num_edges(env))
+        _check(self.L.mevo_env_get_goal(self.h, env, _dptr(out)))
+        return out
+
+    def set_goal(self, env: int, goal) -> None:
+        g = np.ascontiguousarray(goal, dtype=np.float64)
+        _check(self.L.mevo_env_set_goal(self.h, env, _dptr(g)))
+
+    def translate_object(self, env: int, name: str, dx: float, dy: float) -> None:
+        _check(self.L.mevo_env_translate_object(self.h, env, name.encode(), float(dx), float(dy)))
+
+    def save_reset_state(self) -> None:
+        _check(self.L.mevo_batch_save_reset_state(self.h))
+
+    def reset(self, env_ids: Optional[Sequence[int]] = None) -> None:
+        if env_ids is None:
+            _check(self.L.mevo_batch_reset(self.h, None, 0))
+        else:
+            ids = np.ascontiguousarray(env_ids, dtype=np.int32)
+            _check(self.L.mevo_batch_reset(self.h, _iptr(ids), ids.size))
+
+    def object_com(self, obj: int, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.zeros((self.num_envs, 2))
+        _check(self.L.mevo_batch_object_com(self.h, int(obj), _dptr(out)))
+        return out
+
+    def object_com_ptr(self, obj: int, host_ptr: int) -> None:
+        _check(self.L.mevo_batch_object_com(self.h, int(obj), C.cast(host_ptr, _dp)))
+
+    @property
+    def actions_device_ptr(self) -> int:
+        return int(self.L.mevo_batch_actions_device_ptr(self.h) or 0)
+
+    @property
+    def cuda_stream(self) -> int:
+        return int(self.L.mevo_batch_cuda_stream(self.h) or 0)
+
+    @property
+    def device_bytes(self) -> int:
+        return int(self.L.mevo_batch_device_bytes(self.h))
+
+    # -- test hooks
+    def enable_candidate_dump(self, cap_per_env: int = 4096) -> None:
+        _check(self.L.mevo_batch_enable_candidate_dump(self.h, int(cap_per_env)))
+        self._cand_cap = int(cap_per_env)
+
+    def read_candidates(self, env: int) -> np.ndarray:
+        cap = getattr(self, "_cand_cap", 4096)
+        out = np.zeros((cap, 4), dtype=np.int32)
+        n = _check(self.L.mevo_env_read_candidates(self.h, env, _iptr(out), cap))
+        return out[:min(n, cap)].copy()
+
+    def error_flags(self, env: int) -> int:
+        return _check(self.L.mevo_env_error_flags(self.h, env))

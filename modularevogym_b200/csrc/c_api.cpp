@@ -1,0 +1,335 @@
+// extern "C" surface of libmevo_b200.so (declared in include/mevo_b200.h).
+// Every entry point catches C++ exceptions and converts them to MEVO_ERR + mevo_last_error().
+#include "../../include/mevo_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <exception>
+#include <stdexcept>
+#include <string>
+
+#include "engine.h"
+
+using mevo::Batch;
+
+struct mevo_batch {
+    Batch impl;
+    explicit mevo_batch(int device) : impl(device) {}
+};
+
+struct mevo_world {
+    mevo::World impl;
+};
+
+namespace {
+thread_local std::string g_err;
+
+template <class F>
+int guard(F&& f) {
+    try {
+        return f();
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+    } catch (...) {
+        g_err = "unknown C++ exception";
+    }
+    return MEVO_ERR;
+}
+
+void fill_object_info(const mevo::World& w, int obj, bool is_static, int* info) {
+    if (obj < 0 || obj >= (int)w.objects.size()) throw std::out_of_range("object index out of range");
+    const mevo::VoxelObject& o = w.objects[obj];
+    info[0] = o.is_robot ? 1 : 0;
+    info[1] = o.min_point; info[2] = o.max_point;
+    info[3] = (int)o.boxels.size();
+    info[4] = o.grid_w; info[5] = o.grid_h;
+    info[6] = (int)o.surface_boxels.size();
+    info[7] = is_static ? 1 : 0;
+}
+
+int fill_object_boxels(const mevo::World& w, int obj, int* out) {
+    if (obj < 0 || obj >= (int)w.objects.size()) throw std::out_of_range("object index out of range");
+    const mevo::VoxelObject& o = w.objects[obj];
+    for (size_t j = 0; j < o.boxels.size(); j++) {
+        const mevo::Boxel& bx = o.boxels[j];
+        int* r = out + 18 * j;
+        r[0] = bx.cell_type; r[1] = bx.grid_index;
+        for (int q = 0; q < 4; q++) { r[2 + q] = bx.pt[q]; r[6 + q] = bx.ed[q]; }
+        for (int q = 0; q < 8; q++) r[10 + q] = bx.nei[q] ? 1 : 0;
+    }
+    return (int)o.boxels.size();
+}
+
+int fill_surface_boxels(const mevo::World& w, int obj, int* out) {
+    if (obj < 0 || obj >= (int)w.objects.size()) throw std::out_of_range("object index out of range");
+    const mevo::VoxelObject& o = w.objects[obj];
+    for (size_t j = 0; j < o.surface_boxels.size(); j++) out[j] = o.surface_boxels[j];
+    return (int)o.surface_boxels.size();
+}
+
+int fill_actuator_indices(const mevo::World& w, const char* robot, int* out, int cap) {
+    int i = w.find_object(robot);
+    if (i < 0 || !w.objects[i].is_robot) throw std::invalid_argument(std::string(robot) + " is not a robot");
+    const auto& idx = w.objects[i].actuator_grid_index;
+    for (size_t j = 0; j < idx.size() && (int)j < cap; j++) out[j] = idx[j];
+    return (int)idx.size();
+}
+
+void fill_topology(const mevo::World& w, double* pos0, double* mass, unsigned char* fixed, int* edge_a, int* edge_b,
+                   double* edge_k, double* edge_l0, unsigned char* edge_on_surface) {
+    const size_t P = w.num_points(), E = w.num_edges();
+    if (pos0) std::memcpy(pos0, w.pos.data(), sizeof(double) * 2 * P);
+    if (mass) std::memcpy(mass, w.mass.data(), sizeof(double) * P);
+    if (fixed) std::memcpy(fixed, w.fixed.data(), P);
+    if (edge_a) std::memcpy(edge_a, w.ea.data(), sizeof(int) * E);
+    if (edge_b) std::memcpy(edge_b, w.eb.data(), sizeof(int) * E);
+    if (edge_k) std::memcpy(edge_k, w.ek.data(), sizeof(double) * E);
+    if (edge_l0) std::memcpy(edge_l0, w.el0.data(), sizeof(double) * E);
+    if (edge_on_surface) std::memcpy(edge_on_surface, w.on_surface.data(), E);
+}
+}  // namespace
+
+extern "C" {
+
+int mevo_abi_version(void) { return MEVO_ABI_VERSION; }
+const char* mevo_last_error(void) { return g_err.c_str(); }
+
+int mevo_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { g_err = std::string("CUDA unusable: ") + cudaGetErrorString(e); return MEVO_ERR; }
+    return n;
+}
+
+mevo_batch* mevo_batch_create(int device) {
+    try {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess || n <= 0)
+            throw std::runtime_error(std::string("mevo_b200 needs a CUDA device (sm_100a); none usable: ") +
+                                     (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                                     " -- there is no CPU fallback");
+        if (device < 0 || device >= n) throw std::runtime_error("device index out of range");
+        return new mevo_batch(device);
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+    } catch (...) {
+        g_err = "unknown C++ exception";
+    }
+    return nullptr;
+}
+
+void mevo_batch_destroy(mevo_batch* b) { delete b; }
+
+int mevo_batch_begin_env(mevo_batch* b, int world_w, int world_h) {
+    return guard([&] { return b->impl.begin_env(world_w, world_h); });
+}
+
+int mevo_batch_add_object(mevo_batch* b, int env, const double* grid, int w, int h, const double* conn, int k,
+                          const char* name, double x, double y, int is_robot) {
+    return guard([&] {
+        if (!grid || w <= 0 || h <= 0 || k < 0 || (k > 0 && !conn) || !name) throw std::invalid_argument("bad add_object arguments");
+        return b->impl.add_object(env, grid, w, h, conn, k, name, x, y, is_robot != 0) ? 1 : 0;
+    });
+}
+
+int mevo_batch_finalize(mevo_batch* b) {
+    return guard([&] { b->impl.finalize(); return 0; });
+}
+
+int mevo_batch_num_envs(const mevo_batch* b) { return b->impl.num_envs(); }
+int mevo_env_num_points(const mevo_batch* b, int env) { return guard([&] { return b->impl.world(env).num_points(); }); }
+int mevo_env_num_edges(const mevo_batch* b, int env) { return guard([&] { return b->impl.world(env).num_edges(); }); }
+int mevo_env_num_objects(const mevo_batch* b, int env) { return guard([&] { return (int)b->impl.world(env).objects.size(); }); }
+
+int mevo_env_object_index(const mevo_batch* b, int env, const char* name) {
+    return guard([&] {
+        int i = b->impl.world(env).find_object(name);
+        if (i < 0) throw std::invalid_argument(std::string("no object named ") + name);
+        return i;
+    });
+}
+
+int mevo_env_object_info(const mevo_batch* b, int env, int obj, int* info) {
+    return guard([&] {
+        const mevo::World& w = b->impl.world(env);
+        if (obj < 0 || obj >= (int)w.objects.size()) throw std::out_of_range("object index out of range");
+        const mevo::VoxelObject& o = w.objects[obj];
+        fill_object_info(w, obj, o.all_fixed && !o.is_robot && !b->impl.env_host(env).obj_force_dynamic[obj], info);
+        return 0;
+    });
+}
+
+int mevo_env_object_boxels(const mevo_batch* b, int env, int obj, int* out) {
+    return guard([&] { return fill_object_boxels(b->impl.world(env), obj, out); });
+}
+
+int mevo_env_object_surface_boxels(const mevo_batch* b, int env, int obj, int* out) {
+    return guard([&] { return fill_surface_boxels(b->impl.world(env), obj, out); });
+}
+
+int mevo_env_actuator_indices(const mevo_batch* b, int env, const char* robot, int* out, int cap) {
+    return guard([&] { return fill_actuator_indices(b->impl.world(env), robot, out, cap); });
+}
+
+int mevo_env_get_topology(const mevo_batch* b, int env, double* pos0, double* mass, unsigned char* fixed, int* edge_a,
+                          int* edge_b, double* edge_k, double* edge_l0, unsigned char* edge_on_surface) {
+    return guard([&] {
+        fill_topology(b->impl.world(env), pos0, mass, fixed, edge_a, edge_b, edge_k, edge_l0, edge_on_surface);
+        return 0;
+    });
+}
+
+/* ---- host-only world builder (no GPU needed) ------------------------------------------------ */
+mevo_world* mevo_world_create(int world_w, int world_h) {
+    try {
+        mevo_world* w = new mevo_world();
+        w->impl.init(world_w, world_h);
+        return w;
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+    }
+    return nullptr;
+}
+
+void mevo_world_destroy(mevo_world* w) { delete w; }
+
+int mevo_world_add_object(mevo_world* w, const double* grid, int gw, int gh, const double* conn, int k, const char* name,
+                          double x, double y, int is_robot) {
+    return guard([&] {
+        if (!grid || gw <= 0 || gh <= 0 || k < 0 || (k > 0 && !conn) || !name) throw std::invalid_argument("bad add_object arguments");
+        return w->impl.add_object(grid, gw, gh, conn, k, name, x, y, is_robot != 0) ? 1 : 0;
+    });
+}
+
+int mevo_world_num_points(const mevo_world* w) { return w->impl.num_points(); }
+int mevo_world_num_edges(const mevo_world* w) { return w->impl.num_edges(); }
+int mevo_world_num_objects(const mevo_world* w) { return (int)w->impl.objects.size(); }
+
+int mevo_world_object_info(const mevo_world* w, int obj, int* info) {
+    return guard([&] {
+        if (obj < 0 || obj >= (int)w->impl.objects.size()) throw std::out_of_range("object index out of range");
+        const mevo::VoxelObject& o = w->impl.objects[obj];
+        fill_object_info(w->impl, obj, o.all_fixed && !o.is_robot, info);
+        return 0;
+    });
+}
+
+int mevo_world_object_boxels(const mevo_world* w, int obj, int* out) {
+    return guard([&] { return fill_object_boxels(w->impl, obj, out); });
+}
+
+int mevo_world_object_surface_boxels(const mevo_world* w, int obj, int* out) {
+    return guard([&] { return fill_surface_boxels(w->impl, obj, out); });
+}
+
+int mevo_world_actuator_indices(const mevo_world* w, const char* robot, int* out, int cap) {
+    return guard([&] { return fill_actuator_indices(w->impl, robot, out, cap); });
+}
+
+int mevo_world_get_topology(const mevo_world* w, double* pos0, double* mass, unsigned char* fixed, int* edge_a, int* edge_b,
+                            double* edge_k, double* edge_l0, unsigned char* edge_on_surface) {
+    return guard([&] {
+        fill_topology(w->impl, pos0, mass, fixed, edge_a, edge_b, edge_k, edge_l0, edge_on_surface);
+        return 0;
+    });
+}
+
+int mevo_env_set_action(mevo_batch* b, int env, const char* robot, const double* action, int n) {
+    return guard([&] { return b->impl.env_set_action(env, robot, action, n) ? 1 : 0; });
+}
+
+int mevo_batch_action_stride(const mevo_batch* b) { return b->impl.act_stride(); }
+
+int mevo_batch_set_actions(mevo_batch* b, const double* host_values, int stride) {
+    return guard([&] { b->impl.set_actions(host_values, stride); return 0; });
+}
+
+int mevo_batch_set_actions_device(mevo_batch* b, const double* device_values, int stride) {
+    return guard([&] { b->impl.set_actions_device(device_values, stride); return 0; });
+}
+
+int mevo_batch_step(mevo_batch* b, int n_steps, int apply_actions, unsigned char* unstable_out) {
+    return guard([&] { return b->impl.step(n_steps, apply_actions != 0, unstable_out, 30); });
+}
+
+int mevo_batch_step_substeps(mevo_batch* b, int n_steps, int n_substeps, int apply_actions, unsigned char* unstable_out) {
+    return guard([&] { return b->impl.step(n_steps, apply_actions != 0, unstable_out, n_substeps); });
+}
+
+int mevo_batch_step_async(mevo_batch* b, int n_steps, int apply_actions) {
+    return guard([&] { b->impl.step_async(n_steps, apply_actions != 0, 30); return 0; });
+}
+
+int mevo_batch_sync(mevo_batch* b) {
+    return guard([&] { b->impl.sync(); return 0; });
+}
+
+int mevo_batch_last_launches(const mevo_batch* b) { return b->impl.last_stats().launches; }
+
+long mevo_env_get_time(mevo_batch* b, int env) {
+    long t = MEVO_ERR;
+    guard([&] { t = b->impl.get_time(env); return 0; });
+    return t;
+}
+
+int mevo_env_set_time(mevo_batch* b, int env, long t) {
+    return guard([&] { b->impl.set_time(env, t); return 0; });
+}
+
+int mevo_env_get_state(mevo_batch* b, int env, double* pos, double* vel, double* pos_last, double* vel_true) {
+    return guard([&] { b->impl.get_state(env, pos, vel, pos_last, vel_true); return 0; });
+}
+
+int mevo_env_set_state(mevo_batch* b, int env, const double* pos, const double* vel, const double* pos_last,
+                       const double* vel_true) {
+    return guard([&] { b->impl.set_state(env, pos, vel, pos_last, vel_true); return 0; });
+}
+
+int mevo_env_get_goal(mevo_batch* b, int env, double* goal) {
+    return guard([&] { b->impl.get_goal(env, goal); return 0; });
+}
+
+int mevo_env_set_goal(mevo_batch* b, int env, const double* goal) {
+    return guard([&] { b->impl.set_goal(env, goal); return 0; });
+}
+
+int mevo_env_translate_object(mevo_batch* b, int env, const char* name, double dx, double dy) {
+    return guard([&] { b->impl.translate_object(env, name, dx, dy); return 0; });
+}
+
+int mevo_batch_save_reset_state(mevo_batch* b) {
+    return guard([&] { b->impl.save_reset_state(); return 0; });
+}
+
+int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n) {
+    return guard([&] {
+        if (!env_ids) b->impl.reset_all();
+        else b->impl.reset_envs(env_ids, n);
+        return 0;
+    });
+}
+
+int mevo_batch_object_com(mevo_batch* b, int obj, double* out) {
+    return guard([&] { b->impl.object_com(obj, out); return 0; });
+}
+
+double* mevo_batch_actions_device_ptr(mevo_batch* b) { return b->impl.actions_device_ptr(); }
+const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b) { return b->impl.unstable_device_ptr(); }
+void* mevo_batch_cuda_stream(mevo_batch* b) { return b->impl.stream(); }
+long long mevo_batch_device_bytes(const mevo_batch* b) { return (long long)b->impl.device_bytes(); }
+
+int mevo_batch_enable_candidate_dump(mevo_batch* b, int cap_per_env) {
+    return guard([&] { b->impl.enable_candidate_dump(cap_per_env); return 0; });
+}
+
+int mevo_env_read_candidates(mevo_batch* b, int env, int* out, int cap) {
+    return guard([&] { return b->impl.read_candidates(env, out, cap); });
+}
+
+int mevo_env_error_flags(mevo_batch* b, int env) {
+    return guard([&] { return b->impl.error_flags(env); });
+}
+
+}  // extern "C"

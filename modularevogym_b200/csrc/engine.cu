@@ -1,0 +1,904 @@
+// Batch: packs worlds into HBM blobs, launches the step kernels, moves state in and out.
+// Compiled with:  nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo --fmad=false
+#include "engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+
+#include "kernels.cuh"
+
+namespace mevo {
+
+#define CUDA_CHECK(expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess)                                                                    \
+            throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " + \
+                                     __FILE__ + ":" + std::to_string(__LINE__) + " (" #expr ")");   \
+    } while (0)
+
+namespace {
+
+constexpr int kNumClasses = 5;
+const int kGroupSizes[kNumClasses] = {32, 64, 128, 256, 512};
+constexpr int kMaxSmemPerBlock = 227 * 1024;
+
+int class_for(int Pd, int Ed) {
+    if (Ed <= 160 && Pd <= 64) return 0;
+    if (Ed <= 400 && Pd <= 160) return 1;
+    if (Ed <= 900 && Pd <= 320) return 2;
+    if (Ed <= 1800 && Pd <= 640) return 3;
+    return 4;
+}
+
+uint64_t fnv1a(const std::vector<uint8_t>& v) {
+    uint64_t h = 1469598103934665603ull;
+    for (uint8_t b : v) { h ^= b; h *= 1099511628211ull; }
+    return h;
+}
+
+struct BlobWriter {
+    std::vector<uint8_t>& buf;
+    explicit BlobWriter(std::vector<uint8_t>& b) : buf(b) {}
+    int begin_section() {
+        while (buf.size() % 16) buf.push_back(0);
+        return (int)buf.size();
+    }
+    template <class T>
+    void put(const T& v) {
+        const uint8_t* p = reinterpret_cast<const uint8_t*>(&v);
+        buf.insert(buf.end(), p, p + sizeof(T));
+    }
+    template <class T>
+    void put_array(const std::vector<T>& v) {
+        const uint8_t* p = reinterpret_cast<const uint8_t*>(v.data());
+        buf.insert(buf.end(), p, p + sizeof(T) * v.size());
+    }
+};
+
+template <int G, int EPC>
+void launch_step(const StepParams& prm, int smem_per_env, cudaStream_t stream) {
+    const int smem = smem_per_env * EPC;
+    static int configured = -1;
+    if (smem > configured) {
+        CUDA_CHECK(cudaFuncSetAttribute(step_kernel<G, EPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = smem;
+    }
+    const int grid = (prm.n_class_envs + EPC - 1) / EPC;
+    step_kernel<G, EPC><<<grid, G * EPC, smem, stream>>>(prm);
+}
+
+__global__ void reset_kernel(double* state, const double* state0, const EnvDesc* envs, const uint8_t* design,
+                             const int* env_ids, int n, int* sim_time, uint8_t* unstable) {
+    // Environment::revert_to_snapshot(0) (Environment.cpp:247-263): pos, vel <- snapshot; pos_last <- pos;
+    // vel_true <- vel; length_eq_goal is NOT touched.
+    const int k = blockIdx.x;
+    if (k >= n) return;
+    const int env = env_ids ? env_ids[k] : k;
+    const EnvDesc ed = envs[env];
+    const int Pd = reinterpret_cast<const DesignHeader*>(design + ed.design_off)->Pd;
+    double2* s = reinterpret_cast<double2*>(state + ed.state_off);
+    const double2* s0 = reinterpret_cast<const double2*>(state0 + ed.state_off);
+    for (int i = threadIdx.x; i < Pd; i += blockDim.x) {
+        const double2 p = s0[i], v = s0[Pd + i];
+        s[i] = p; s[Pd + i] = v; s[2 * Pd + i] = p; s[3 * Pd + i] = v;
+    }
+    if (threadIdx.x == 0) { sim_time[env] = 0; unstable[env] = 0; }
+}
+
+}  // namespace
+
+struct Batch::Impl {
+    std::vector<std::vector<int>> class_envs;     // per class: env ids
+    std::vector<int> class_smem;                  // per class: bytes of shared memory per env
+    std::vector<size_t> class_off;                // per class: offset into d_class_envs_
+    std::vector<EnvDesc> desc;
+    std::vector<std::vector<double>> pos0, vel0;  // reset snapshot (global numbering)
+    int epc32 = 2;
+    int* d_com_ranges = nullptr;
+    double* d_com_out = nullptr;
+    int com_obj = -1;
+    std::vector<uint8_t> unstable_host;
+    std::vector<int> time_host;
+    bool time_dirty = true;
+};
+
+Batch::Batch(int device) : device_(device), impl_(new Impl()) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    cudaStream_t s;
+    CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    stream_ = s;
+    if (const char* e = std::getenv("MEVO_EPC32")) {
+        int v = std::atoi(e);
+        if (v == 1 || v == 2 || v == 4) impl_->epc32 = v;
+    }
+}
+
+Batch::~Batch() {
+    cudaSetDevice(device_);
+    cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
+    cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
+    cudaFree(d_cand_); cudaFree(d_cand_n_);
+    if (impl_) { cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); }
+    if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
+    delete impl_;
+}
+
+int Batch::begin_env(int world_w, int world_h) {
+    envs_.emplace_back();
+    envs_.back().world.init(world_w, world_h);
+    finalized_ = false;
+    return (int)envs_.size() - 1;
+}
+
+bool Batch::add_object(int env, const double* grid, int w, int h, const double* conn, int k,
+                       const std::string& name, double x, double y, bool is_robot) {
+    EnvHost& e = envs_.at(env);
+    if (finalized_) download_all();
+    const int P_before = e.world.num_points(), E_before = e.world.num_edges();
+    if (!e.world.add_object(grid, w, h, conn, k, name, x, y, is_robot)) return false;
+    // extend the host mirror with the new object's rest state (Environment.cpp:44-109)
+    const World& W = e.world;
+    e.pos.insert(e.pos.end(), W.pos.begin() + 2 * P_before, W.pos.end());
+    e.pos_last.insert(e.pos_last.end(), W.pos.begin() + 2 * P_before, W.pos.end());
+    e.vel.resize(2 * W.num_points(), 0.0);
+    e.vel_true.resize(2 * W.num_points(), 0.0);
+    e.goal.insert(e.goal.end(), W.el0.begin() + E_before, W.el0.end());
+    e.obj_force_dynamic.push_back(0);
+    e.host_fresh = true;
+    finalized_ = false;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// packing
+
+void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8_t>& statics) {
+    EnvHost& e = envs_[env_id];
+    const World& W = e.world;
+    const int P = W.num_points(), E = W.num_edges(), n_obj = (int)W.objects.size();
+
+    std::vector<uint8_t> dyn(n_obj, 0);
+    for (int o = 0; o < n_obj; o++)
+        dyn[o] = !(W.objects[o].all_fixed && !W.objects[o].is_robot) || e.obj_force_dynamic[o];
+
+    e.point_local.assign(P, 0);
+    e.edge_local.assign(E, -1);
+    e.dyn_points.clear(); e.dyn_edges.clear();
+    std::vector<int> static_points;
+    for (int o = 0; o < n_obj; o++) {
+        const VoxelObject& ob = W.objects[o];
+        for (int p = ob.min_point; p <= ob.max_point; p++) {
+            if (dyn[o]) { e.point_local[p] = (int)e.dyn_points.size(); e.dyn_points.push_back(p); }
+            else { e.point_local[p] = -(int)static_points.size() - 1; static_points.push_back(p); }
+        }
+        if (dyn[o])
+            for (int k = ob.min_edge; k <= ob.max_edge; k++) { e.edge_local[k] = (int)e.dyn_edges.size(); e.dyn_edges.push_back(k); }
+    }
+    const int Pd = (int)e.dyn_points.size(), Ed = (int)e.dyn_edges.size();
+    if (Pd > 65000 || Ed > 32000) throw std::runtime_error("environment too large for 16-bit local ids");
+
+    auto make_leaf = [&](const VoxelObject& ob, const Boxel& b, bool is_dyn, int obj_slot) {
+        LeafRec r;
+        std::memset(&r, 0, sizeof(r));
+        for (int q = 0; q < 4; q++) {
+            const int lp = e.point_local[b.pt[q]];
+            r.pt[q] = (uint16_t)(is_dyn ? lp : -lp - 1);
+            const int ge = b.ed[q];
+            const int la = e.point_local[W.ea[ge]], lb = e.point_local[W.eb[ge]];
+            r.ea[q] = (uint16_t)(is_dyn ? la : -la - 1);
+            r.eb[q] = (uint16_t)(is_dyn ? lb : -lb - 1);
+            if (W.on_surface[ge]) r.surf_mask |= (uint8_t)(1u << q);
+        }
+        r.obj = (uint8_t)obj_slot;
+        r.gx = (int16_t)(b.grid_index % ob.grid_w);
+        r.gy = (int16_t)(b.grid_index / ob.grid_w);
+        return r;
+    };
+
+    // ---- dynamic design blob
+    design.clear();
+    BlobWriter dw(design);
+    DesignHeader H;
+    std::memset(&H, 0, sizeof(H));
+    design.resize(sizeof(DesignHeader));
+    H.Pd = Pd; H.Ed = Ed;
+
+    std::vector<double> mass(Pd), ek(Ed), el0(Ed);
+    std::vector<uint16_t> ea(Ed), eb(Ed);
+    std::vector<uint8_t> fixed(Pd);
+    for (int i = 0; i < Pd; i++) { mass[i] = W.mass[e.dyn_points[i]]; fixed[i] = W.fixed[e.dyn_points[i]]; }
+    for (int k = 0; k < Ed; k++) {
+        const int g = e.dyn_edges[k];
+        ek[k] = W.ek[g]; el0[k] = W.el0[g];
+        ea[k] = (uint16_t)e.point_local[W.ea[g]];
+        eb[k] = (uint16_t)e.point_local[W.eb[g]];
+    }
+    // action slots: robots in load order, actuators in Robot::init order
+    std::vector<int16_t> eact(2 * (size_t)Ed, -1);
+    e.act_slot_obj.clear(); e.act_slot_boxel.clear();
+    for (int o = 0; o < n_obj; o++) {
+        const VoxelObject& ob = W.objects[o];
+        if (!ob.is_robot) continue;
+        for (int gidx : ob.actuator_grid_index) {
+            const int bi = ob.actuator_grid_to_boxel.at(gidx);
+            const Boxel& b = ob.boxels[bi];
+            const int slot = (int)e.act_slot_obj.size();
+            e.act_slot_obj.push_back(o); e.act_slot_boxel.push_back(bi);
+            // H actuator drives top + bot, V actuator left + right (PhysicsEngine.cpp:47-68); ed = top,right,bot,left
+            const int e0 = b.cell_type == CELL_ACT_H ? b.ed[0] : b.ed[3];
+            const int e1 = b.cell_type == CELL_ACT_H ? b.ed[2] : b.ed[1];
+            for (int ge : {e0, e1}) {
+                const int le = e.edge_local[ge];
+                if (le < 0) continue;
+                if (eact[2 * le] < 0) eact[2 * le] = (int16_t)slot;
+                else if (eact[2 * le + 1] < 0) eact[2 * le + 1] = (int16_t)slot;
+            }
+        }
+    }
+    e.n_act = (int)e.act_slot_obj.size();
+    H.n_act = e.n_act;
+    // per-point gather lists: a-sides by edge id, then b-sides by edge id (PhysicsEngine.cpp:530-531)
+    std::vector<uint16_t> csro(Pd + 1, 0), csre;
+    {
+        std::vector<std::vector<uint16_t>> lists(Pd);
+        for (int k = 0; k < Ed; k++) lists[ea[k]].push_back((uint16_t)(k << 1));
+        for (int k = 0; k < Ed; k++) lists[eb[k]].push_back((uint16_t)((k << 1) | 1));
+        for (int i = 0; i < Pd; i++) {
+            csro[i] = (uint16_t)csre.size();
+            csre.insert(csre.end(), lists[i].begin(), lists[i].end());
+        }
+        csro[Pd] = (uint16_t)csre.size();
+    }
+    // leaves, objects, pair table
+    std::vector<LeafRec> leaves;
+    std::vector<ObjRec> objrecs;
+    std::vector<int> leaf_obj_slot;
+    for (int o = 0; o < n_obj; o++) {
+        if (!dyn[o]) continue;
+        const VoxelObject& ob = W.objects[o];
+        ObjRec r;
+        std::memset(&r, 0, sizeof(r));
+        r.is_robot = ob.is_robot ? 1 : 0;
+        r.n_surface = (uint16_t)ob.surface_boxels.size();
+        r.leaf_start = (uint16_t)leaves.size();
+        const int slot = (int)objrecs.size();
+        for (int bi : ob.surface_boxels) { leaves.push_back(make_leaf(ob, ob.boxels[bi], true, slot)); leaf_obj_slot.push_back(slot); }
+        r.leaf_count = (uint16_t)(leaves.size() - r.leaf_start);
+        objrecs.push_back(r);
+    }
+    if ((int)objrecs.size() > kMaxDynObjects) throw std::runtime_error("too many dynamic objects in one environment (max 8)");
+    if ((int)leaves.size() > kMaxLeaves) throw std::runtime_error("too many surface voxels in one environment (max 4095)");
+    std::vector<uint32_t> pairs;
+    for (size_t a = 0; a < leaves.size(); a++)
+        for (size_t b = a + 1; b < leaves.size(); b++) {
+            uint32_t code = (uint32_t)a | ((uint32_t)b << 12);
+            if (leaf_obj_slot[a] == leaf_obj_slot[b]) {
+                code |= kCodeSameObj;
+                const int dx = std::abs(leaves[a].gx - leaves[b].gx), dy = std::abs(leaves[a].gy - leaves[b].gy);
+                if (objrecs[leaf_obj_slot[a]].is_robot && !(dx <= 1 && dy <= 1)) code |= kCodeCount;   // PhysicsEngine.cpp:856-863
+                code |= (uint32_t)leaf_obj_slot[a] << kCodeObjShift;
+            }
+            pairs.push_back(code);
+        }
+    // rigid-cell visit schedule: reference order = object, boxel, (top,right,bot,left); levels = point-disjoint
+    std::vector<uint16_t> rlev(1, 0), rvis;
+    {
+        std::vector<int> visit_edge, visit_level, last_level(Pd, 0);
+        int n_levels = 0;
+        for (int o = 0; o < n_obj; o++) {
+            if (!dyn[o]) continue;
+            for (const Boxel& b : W.objects[o].boxels) {
+                if (b.cell_type != CELL_RIGID) continue;
+                for (int q = 0; q < 4; q++) {
+                    const int le = e.edge_local[b.ed[q]];
+                    const int lv = std::max(last_level[ea[le]], last_level[eb[le]]) + 1;
+                    last_level[ea[le]] = last_level[eb[le]] = lv;
+                    visit_edge.push_back(le); visit_level.push_back(lv);
+                    n_levels = std::max(n_levels, lv);
+                }
+            }
+        }
+        for (int lv = 1; lv <= n_levels; lv++) {
+            for (size_t v = 0; v < visit_edge.size(); v++)
+                if (visit_level[v] == lv) rvis.push_back((uint16_t)visit_edge[v]);
+            rlev.push_back((uint16_t)rvis.size());
+        }
+        H.n_rlev = n_levels;
+        H.n_rvis = (int)rvis.size();
+    }
+    H.n_leaf = (int)leaves.size();
+    H.n_obj = (int)objrecs.size();
+    H.n_pairs = (int)pairs.size();
+    H.cand_cap = ((std::max(128, 16 * H.n_leaf) + 15) / 16) * 16;
+
+    H.o_mass = dw.begin_section(); dw.put_array(mass);
+    H.o_ek = dw.begin_section(); dw.put_array(ek);
+    H.o_el0 = dw.begin_section(); dw.put_array(el0);
+    H.o_ea = dw.begin_section(); dw.put_array(ea);
+    H.o_eb = dw.begin_section(); dw.put_array(eb);
+    H.o_eact = dw.begin_section(); dw.put_array(eact);
+    H.o_fixed = dw.begin_section(); dw.put_array(fixed);
+    H.o_csro = dw.begin_section(); dw.put_array(csro);
+    H.o_csre = dw.begin_section(); dw.put_array(csre);
+    H.o_leaf = dw.begin_section(); dw.put_array(leaves);
+    H.o_obj = dw.begin_section(); dw.put_array(objrecs);
+    H.o_pairs = dw.begin_section(); dw.put_array(pairs);
+    H.o_rlev = dw.begin_section(); dw.put_array(rlev);
+    H.o_rvis = dw.begin_section(); dw.put_array(rvis);
+    H.total = dw.begin_section();
+    std::memcpy(design.data(), &H, sizeof(H));
+
+    // ---- static blob
+    statics.clear();
+    if (!static_points.empty()) {
+        BlobWriter sw(statics);
+        StaticHeader S;
+        std::memset(&S, 0, sizeof(S));
+        statics.resize(sizeof(StaticHeader));
+        S.Ps = (int)static_points.size();
+        std::vector<double> spos(2 * static_points.size());
+        for (size_t i = 0; i < static_points.size(); i++) {
+            spos[2 * i] = e.pos[2 * static_points[i]];
+            spos[2 * i + 1] = e.pos[2 * static_points[i] + 1];
+        }
+        std::vector<LeafRec> sleaves;
+        std::vector<double> saabb;
+        std::vector<int> cellx, celly;
+        for (int o = 0; o < n_obj; o++) {
+            if (dyn[o]) continue;
+            const VoxelObject& ob = W.objects[o];
+            for (int bi : ob.surface_boxels) {
+                const Boxel& b = ob.boxels[bi];
+                sleaves.push_back(make_leaf(ob, b, false, 0));
+                double minx = 0, miny = 0, maxx = 0, maxy = 0;
+                for (int q = 0; q < 4; q++) {
+                    const double px = e.pos[2 * b.pt[q]], py = e.pos[2 * b.pt[q] + 1];
+                    if (q == 0) { minx = maxx = px; miny = maxy = py; }
+                    else { minx = std::fmin(minx, px); maxx = std::fmax(maxx, px); miny = std::fmin(miny, py); maxy = std::fmax(maxy, py); }
+                }
+                saabb.insert(saabb.end(), {minx, miny, maxx, maxy});
+                // cell of the box centre on the voxel lattice (robust to object translations)
+                cellx.push_back((int)std::floor(0.5 * (minx + maxx) / 0.1));
+                celly.push_back((int)std::floor(0.5 * (miny + maxy) / 0.1));
+            }
+        }
+        if ((int)sleaves.size() > kMaxLeaves) throw std::runtime_error("too many static surface voxels (max 4095)");
+        S.n_leaf = (int)sleaves.size();
+        std::vector<int16_t> grid;
+        if (!sleaves.empty()) {
+            const int x0 = *std::min_element(cellx.begin(), cellx.end()), x1 = *std::max_element(cellx.begin(), cellx.end());
+            const int y0 = *std::min_element(celly.begin(), celly.end()), y1 = *std::max_element(celly.begin(), celly.end());
+            S.gx0 = x0; S.gy0 = y0; S.gw = x1 - x0 + 1; S.gh = y1 - y0 + 1;
+            grid.assign((size_t)S.gw * S.gh, (int16_t)-1);
+            for (size_t l = 0; l < sleaves.size(); l++) {
+                int16_t& slot = grid[(size_t)(celly[l] - y0) * S.gw + (cellx[l] - x0)];
+                if (slot >= 0) throw std::runtime_error("two static voxels share one lattice cell");
+                slot = (int16_t)l;
+            }
+        }
+        S.o_pos = sw.begin_section(); sw.put_array(spos);
+        S.o_leaf = sw.begin_section(); sw.put_array(sleaves);
+        S.o_aabb = sw.begin_section(); sw.put_array(saabb);
+        S.o_grid = sw.begin_section(); sw.put_array(grid);
+        S.total = sw.begin_section();
+        std::memcpy(statics.data(), &S, sizeof(S));
+    }
+}
+
+void Batch::finalize() {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (finalized_) download_all();
+    const int n = num_envs();
+    if (n == 0) throw std::runtime_error("finalize: no environments");
+
+    std::vector<uint8_t> all_design, all_static;
+    std::unordered_map<uint64_t, std::vector<std::pair<size_t, size_t>>> design_index, static_index;  // hash -> (offset, size)
+    impl_->desc.assign(n, EnvDesc());
+    impl_->class_envs.assign(kNumClasses, {});
+    impl_->class_smem.assign(kNumClasses, 0);
+    size_t state_doubles = 0;
+    act_stride_ = 1;
+
+    auto intern = [](std::vector<uint8_t>& pool, std::unordered_map<uint64_t, std::vector<std::pair<size_t, size_t>>>& index,
+                     const std::vector<uint8_t>& blob) -> size_t {
+        const uint64_t h = fnv1a(blob);
+        for (auto& cand : index[h])
+            if (cand.second == blob.size() && std::memcmp(pool.data() + cand.first, blob.data(), blob.size()) == 0) return cand.first;
+        const size_t off = pool.size();
+        pool.insert(pool.end(), blob.begin(), blob.end());
+        index[h].push_back({off, blob.size()});
+        return off;
+    };
+
+    std::vector<uint8_t> design, statics;
+    for (int i = 0; i < n; i++) {
+        EnvHost& e = envs_[i];
+        if (e.world.objects.empty()) throw std::runtime_error("finalize: environment " + std::to_string(i) + " has no objects");
+        pack_env(i, design, statics);
+        const DesignHeader* H = reinterpret_cast<const DesignHeader*>(design.data());
+        EnvDesc& d = impl_->desc[i];
+        d.design_off = intern(all_design, design_index, design);
+        d.static_off = statics.empty() ? ~0ull : intern(all_static, static_index, statics);
+        d.state_off = state_doubles;
+        e.state_off = state_doubles;
+        size_t sd = 8 * (size_t)H->Pd + (size_t)H->Ed;
+        sd = (sd + 1) & ~(size_t)1;
+        state_doubles += sd;
+        act_stride_ = std::max(act_stride_, e.n_act);
+        e.cls = class_for(H->Pd, H->Ed);
+        const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap);
+        if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
+        impl_->class_envs[e.cls].push_back(i);
+        impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
+    }
+    for (int i = 0; i < n; i++) impl_->desc[i].act_off = i * act_stride_;
+
+    // (re)allocate
+    cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
+    cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
+    d_design_ = d_static_ = nullptr; d_state_ = d_state0_ = d_act_ = nullptr;
+    state_doubles_ = state_doubles;
+    CUDA_CHECK(cudaMalloc(&d_design_, all_design.size() + 16));
+    CUDA_CHECK(cudaMalloc(&d_static_, all_static.size() + 16));
+    CUDA_CHECK(cudaMalloc(&d_state_, sizeof(double) * (state_doubles + 2)));
+    CUDA_CHECK(cudaMalloc(&d_state0_, sizeof(double) * (state_doubles + 2)));
+    CUDA_CHECK(cudaMalloc(&d_act_, sizeof(double) * (size_t)n * act_stride_));
+    CUDA_CHECK(cudaMalloc(&d_envdesc_, sizeof(EnvDesc) * n));
+    CUDA_CHECK(cudaMalloc(&d_class_envs_, sizeof(int) * n));
+    CUDA_CHECK(cudaMalloc(&d_unstable_, n));
+    CUDA_CHECK(cudaMalloc(&d_time_, sizeof(int) * n));
+    CUDA_CHECK(cudaMalloc(&d_err_, sizeof(int) * n));
+    device_bytes_ = all_design.size() + all_static.size() + 2 * sizeof(double) * state_doubles +
+                    sizeof(double) * (size_t)n * act_stride_ + sizeof(EnvDesc) * n + 10 * (size_t)n;
+    CUDA_CHECK(cudaMemcpy(d_design_, all_design.data(), all_design.size(), cudaMemcpyHostToDevice));
+    if (!all_static.empty()) CUDA_CHECK(cudaMemcpy(d_static_, all_static.data(), all_static.size(), cudaMemcpyHostToDevice));
+    CUDA_CHECK(cudaMemcpy(d_envdesc_, impl_->desc.data(), sizeof(EnvDesc) * n, cudaMemcpyHostToDevice));
+    {
+        std::vector<int> flat;
+        impl_->class_off.assign(kNumClasses, 0);
+        for (int c = 0; c < kNumClasses; c++) {
+            impl_->class_off[c] = flat.size();
+            flat.insert(flat.end(), impl_->class_envs[c].begin(), impl_->class_envs[c].end());
+        }
+        CUDA_CHECK(cudaMemcpy(d_class_envs_, flat.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    }
+    {
+        std::vector<double> ones((size_t)n * act_stride_, 1.0);   // action 1.0 == rest length
+        CUDA_CHECK(cudaMemcpy(d_act_, ones.data(), sizeof(double) * ones.size(), cudaMemcpyHostToDevice));
+        std::vector<int> times(n);
+        for (int i = 0; i < n; i++) times[i] = (int)envs_[i].sim_time;
+        CUDA_CHECK(cudaMemcpy(d_time_, times.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemset(d_unstable_, 0, n));
+        CUDA_CHECK(cudaMemset(d_err_, 0, sizeof(int) * n));
+    }
+    impl_->unstable_host.assign(n, 0);
+    impl_->time_host.assign(n, 0);
+    impl_->com_obj = -1;
+    if (cand_cap_ > 0) enable_candidate_dump(cand_cap_);
+
+    // state + reset snapshot
+    const bool first = impl_->pos0.empty();
+    if (first) { impl_->pos0.resize(n); impl_->vel0.resize(n); }
+    impl_->pos0.resize(n); impl_->vel0.resize(n);
+    std::vector<double> host_state(state_doubles + 2, 0.0), host_state0(state_doubles + 2, 0.0);
+    for (int i = 0; i < n; i++) {
+        EnvHost& e = envs_[i];
+        if (impl_->pos0[i].size() != e.pos.size()) { impl_->pos0[i] = e.pos; impl_->vel0[i] = e.vel; }
+        const int Pd = (int)e.dyn_points.size(), Ed = (int)e.dyn_edges.size();
+        double* s = host_state.data() + e.state_off;
+        double* s0 = host_state0.data() + e.state_off;
+        for (int k = 0; k < Pd; k++) {
+            const int g = e.dyn_points[k];
+            for (int c = 0; c < 2; c++) {
+                s[2 * k + c] = e.pos[2 * g + c];
+                s[2 * Pd + 2 * k + c] = e.vel[2 * g + c];
+                s[4 * Pd + 2 * k + c] = e.pos_last[2 * g + c];
+                s[6 * Pd + 2 * k + c] = e.vel_true[2 * g + c];
+                s0[2 * k + c] = impl_->pos0[i][2 * g + c];
+                s0[2 * Pd + 2 * k + c] = impl_->vel0[i][2 * g + c];
+            }
+        }
+        for (int k = 0; k < Ed; k++) s[8 * Pd + k] = e.goal[e.dyn_edges[k]];
+        e.host_fresh = true;
+    }
+    CUDA_CHECK(cudaMemcpy(d_state_, host_state.data(), sizeof(double) * (state_doubles + 2), cudaMemcpyHostToDevice));
+    CUDA_CHECK(cudaMemcpy(d_state0_, host_state0.data(), sizeof(double) * (state_doubles + 2), cudaMemcpyHostToDevice));
+    finalized_ = true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// state movement
+
+void Batch::download_state(int env) {
+    EnvHost& e = envs_.at(env);
+    if (!finalized_ || e.host_fresh) return;
+    CUDA_CHECK(cudaSetDevice(device_));
+    const int Pd = (int)e.dyn_points.size(), Ed = (int)e.dyn_edges.size();
+    std::vector<double> s(8 * (size_t)Pd + Ed);
+    CUDA_CHECK(cudaMemcpyAsync(s.data(), d_state_ + e.state_off, sizeof(double) * s.size(), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    int t = 0;
+    CUDA_CHECK(cudaMemcpyAsync(&t, d_time_ + env, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    for (int k = 0; k < Pd; k++) {
+        const int g = e.dyn_points[k];
+        for (int c = 0; c < 2; c++) {
+            e.pos[2 * g + c] = s[2 * k + c];
+            e.vel[2 * g + c] = s[2 * Pd + 2 * k + c];
+            e.pos_last[2 * g + c] = s[4 * Pd + 2 * k + c];
+            e.vel_true[2 * g + c] = s[6 * Pd + 2 * k + c];
+        }
+    }
+    for (int k = 0; k < Ed; k++) e.goal[e.dyn_edges[k]] = s[8 * Pd + k];
+    e.sim_time = t;
+    e.host_fresh = true;
+}
+
+void Batch::download_all() {
+    if (!finalized_) return;
+    CUDA_CHECK(cudaSetDevice(device_));
+    bool any = false;
+    for (auto& e : envs_) any |= !e.host_fresh;
+    if (!any) return;
+    std::vector<double> all(state_doubles_ + 2);
+    std::vector<int> times(num_envs());
+    CUDA_CHECK(cudaMemcpyAsync(all.data(), d_state_, sizeof(double) * state_doubles_, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaMemcpyAsync(times.data(), d_time_, sizeof(int) * num_envs(), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    for (int i = 0; i < num_envs(); i++) {
+        EnvHost& e = envs_[i];
+        if (e.host_fresh) continue;
+        const int Pd = (int)e.dyn_points.size(), Ed = (int)e.dyn_edges.size();
+        const double* s = all.data() + e.state_off;
+        for (int k = 0; k < Pd; k++) {
+            const int g = e.dyn_points[k];
+            for (int c = 0; c < 2; c++) {
+                e.pos[2 * g + c] = s[2 * k + c];
+                e.vel[2 * g + c] = s[2 * Pd + 2 * k + c];
+                e.pos_last[2 * g + c] = s[4 * Pd + 2 * k + c];
+                e.vel_true[2 * g + c] = s[6 * Pd + 2 * k + c];
+            }
+        }
+        for (int k = 0; k < Ed; k++) e.goal[e.dyn_edges[k]] = s[8 * Pd + k];
+        e.sim_time = times[i];
+        e.host_fresh = true;
+    }
+}
+
+void Batch::upload_state(int env) {
+    EnvHost& e = envs_.at(env);
+    CUDA_CHECK(cudaSetDevice(device_));
+    const int Pd = (int)e.dyn_points.size(), Ed = (int)e.dyn_edges.size();
+    std::vector<double> s(8 * (size_t)Pd + Ed);
+    for (int k = 0; k < Pd; k++) {
+        const int g = e.dyn_points[k];
+        for (int c = 0; c < 2; c++) {
+            s[2 * k + c] = e.pos[2 * g + c];
+            s[2 * Pd + 2 * k + c] = e.vel[2 * g + c];
+            s[4 * Pd + 2 * k + c] = e.pos_last[2 * g + c];
+            s[6 * Pd + 2 * k + c] = e.vel_true[2 * g + c];
+        }
+    }
+    for (int k = 0; k < Ed; k++) s[8 * Pd + k] = e.goal[e.dyn_edges[k]];
+    const int t = (int)e.sim_time;
+    CUDA_CHECK(cudaMemcpyAsync(d_state_ + e.state_off, s.data(), sizeof(double) * s.size(), cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaMemcpyAsync(d_time_ + env, &t, sizeof(int), cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    e.host_fresh = true;
+}
+
+void Batch::get_state(int env, double* pos, double* vel, double* pos_last, double* vel_true) {
+    download_state(env);
+    const EnvHost& e = envs_.at(env);
+    const size_t bytes = sizeof(double) * e.pos.size();
+    if (pos) std::memcpy(pos, e.pos.data(), bytes);
+    if (vel) std::memcpy(vel, e.vel.data(), bytes);
+    if (pos_last) std::memcpy(pos_last, e.pos_last.data(), bytes);
+    if (vel_true) std::memcpy(vel_true, e.vel_true.data(), bytes);
+}
+
+void Batch::set_state(int env, const double* pos, const double* vel, const double* pos_last, const double* vel_true) {
+    download_state(env);
+    EnvHost& e = envs_.at(env);
+    // static (all-fixed, pruned) points keep their own values: they cannot move
+    for (size_t g = 0; g < e.pos.size() / 2; g++) {
+        if (finalized_ && e.point_local[g] < 0) continue;
+        for (int c = 0; c < 2; c++) {
+            if (pos) e.pos[2 * g + c] = pos[2 * g + c];
+            if (vel) e.vel[2 * g + c] = vel[2 * g + c];
+            if (pos_last) e.pos_last[2 * g + c] = pos_last[2 * g + c];
+            if (vel_true) e.vel_true[2 * g + c] = vel_true[2 * g + c];
+        }
+    }
+    if (finalized_) upload_state(env);
+}
+
+void Batch::get_goal(int env, double* goal) {
+    download_state(env);
+    const EnvHost& e = envs_.at(env);
+    std::memcpy(goal, e.goal.data(), sizeof(double) * e.goal.size());
+}
+
+void Batch::set_goal(int env, const double* goal) {
+    download_state(env);
+    EnvHost& e = envs_.at(env);
+    std::memcpy(e.goal.data(), goal, sizeof(double) * e.goal.size());
+    if (finalized_) upload_state(env);
+}
+
+long Batch::get_time(int env) {
+    download_state(env);
+    return envs_.at(env).sim_time;
+}
+
+void Batch::set_time(int env, long t) {
+    download_state(env);
+    envs_.at(env).sim_time = t;
+    if (finalized_) upload_state(env);
+}
+
+void Batch::translate_object(int env, const std::string& name, double dx, double dy) {
+    // Environment::translate_object (Environment.cpp:381-392): only points_pos moves; pos_last stays, so the
+    // next substep sees a true-velocity spike -- reproduced by simulating the object from now on.
+    EnvHost& e = envs_.at(env);
+    const int o = e.world.find_object(name);
+    if (o < 0) return;
+    if (finalized_) download_all();
+    const VoxelObject& ob = e.world.objects[o];
+    for (int p = ob.min_point; p <= ob.max_point; p++) { e.pos[2 * p] += dx; e.pos[2 * p + 1] += dy; }
+    const bool was_static = ob.all_fixed && !ob.is_robot && !e.obj_force_dynamic[o];
+    if (was_static) {
+        e.obj_force_dynamic[o] = 1;
+        if (finalized_) { finalized_ = false; finalize(); }
+    } else if (finalized_) {
+        upload_state(env);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// actions
+
+void Batch::set_actions(const double* host_values, int stride) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) throw std::runtime_error("set_actions before finalize");
+    if (stride == act_stride_) {
+        CUDA_CHECK(cudaMemcpyAsync(d_act_, host_values, sizeof(double) * (size_t)num_envs() * stride, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    } else {
+        CUDA_CHECK(cudaMemcpy2DAsync(d_act_, sizeof(double) * act_stride_, host_values, sizeof(double) * stride,
+                                     sizeof(double) * std::min(stride, act_stride_), num_envs(), cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    }
+}
+
+void Batch::set_actions_device(const double* dev_values, int stride) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) throw std::runtime_error("set_actions before finalize");
+    CUDA_CHECK(cudaMemcpy2DAsync(d_act_, sizeof(double) * act_stride_, dev_values, sizeof(double) * stride,
+                                 sizeof(double) * std::min(stride, act_stride_), num_envs(), cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+}
+
+bool Batch::env_set_action(int env, const std::string& robot, const double* action, int n) {
+    // Environment::set_robot_action + PhysicsEngine::update_actuator_goals (Environment.cpp:207-237,
+    // PhysicsEngine.cpp:38-97), evaluated on the host mirror of length_eq_goal, then uploaded.
+    EnvHost& e = envs_.at(env);
+    const int o = e.world.find_object(robot);
+    if (o < 0) { std::printf("Error: No robot named %s.\n", robot.c_str()); return false; }
+    const VoxelObject& ob = e.world.objects[o];
+    if (!ob.is_robot) { std::printf("Error: %s is not robot.\n", robot.c_str()); return false; }
+    std::vector<const Boxel*> acts;
+    for (int i = 0; i < n; i++) {
+        auto it = ob.actuator_grid_to_boxel.find((int)action[2 * i]);
+        if (it == ob.actuator_grid_to_boxel.end()) {
+            // the reference does `throw;` here -> std::terminate (Robot.cpp:28-35); we refuse instead
+            std::printf("Error: Robot action inproperly defined - no actuator found at index.\n");
+            return false;
+        }
+        acts.push_back(&ob.boxels[it->second]);
+    }
+    download_state(env);
+    std::map<int, int> count;
+    auto driven = [](const Boxel* b, int& e0, int& e1) {
+        if (b->cell_type == CELL_ACT_H) { e0 = b->ed[0]; e1 = b->ed[2]; }
+        else { e0 = b->ed[3]; e1 = b->ed[1]; }
+    };
+    for (const Boxel* b : acts) { int e0, e1; driven(b, e0, e1); e.goal[e0] = 0; e.goal[e1] = 0; count[e0] = 0; count[e1] = 0; }
+    for (int i = 0; i < n; i++) {
+        int e0, e1; driven(acts[i], e0, e1);
+        e.goal[e0] += action[2 * i + 1]; e.goal[e1] += action[2 * i + 1];
+        count[e0] += 1; count[e1] += 1;
+    }
+    for (auto& kv : count) e.goal[kv.first] *= e.world.el0[kv.first] / kv.second;
+    if (finalized_) upload_state(env);
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// stepping
+
+void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    StepParams prm;
+    prm.design = d_design_;
+    prm.statics = d_static_;
+    prm.state = d_state_;
+    prm.act = d_act_;
+    prm.envs = reinterpret_cast<const EnvDesc*>(d_envdesc_);
+    prm.n_steps = n_steps;
+    prm.n_substeps = n_substeps;
+    prm.apply_actions = apply_actions ? 1 : 0;
+    prm.unstable = d_unstable_;
+    prm.sim_time = d_time_;
+    prm.err = d_err_;
+    prm.dbg_cand = d_cand_;
+    prm.dbg_cand_n = d_cand_n_;
+    prm.dbg_cand_cap = cand_cap_;
+    cudaStream_t st = (cudaStream_t)stream_;
+    stats_.launches = 0;
+    for (int c = 0; c < kNumClasses; c++) {
+        const int n = (int)impl_->class_envs[c].size();
+        if (n == 0) continue;
+        prm.class_envs = d_class_envs_ + impl_->class_off[c];
+        prm.n_class_envs = n;
+        prm.smem_per_env = impl_->class_smem[c];
+        switch (c) {
+            case 0:
+                if (impl_->epc32 == 4 && 4 * prm.smem_per_env <= kMaxSmemPerBlock) launch_step<32, 4>(prm, prm.smem_per_env, st);
+                else if (impl_->epc32 == 1) launch_step<32, 1>(prm, prm.smem_per_env, st);
+                else launch_step<32, 2>(prm, prm.smem_per_env, st);
+                break;
+            case 1: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
+            case 2: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
+            case 3: launch_step<256, 1>(prm, prm.smem_per_env, st); break;
+            default: launch_step<512, 1>(prm, prm.smem_per_env, st); break;
+        }
+        CUDA_CHECK(cudaGetLastError());
+        stats_.launches++;
+    }
+    for (auto& e : envs_) e.host_fresh = false;
+}
+
+void Batch::sync() {
+    CUDA_CHECK(cudaSetDevice(device_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+int Batch::step(int n_steps, bool apply_actions, uint8_t* unstable_host, int n_substeps) {
+    step_async(n_steps, apply_actions, n_substeps);
+    const int n = num_envs();
+    CUDA_CHECK(cudaMemcpyAsync(impl_->unstable_host.data(), d_unstable_, n, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    int count = 0;
+    for (int i = 0; i < n; i++) count += impl_->unstable_host[i] ? 1 : 0;
+    if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host.data(), n);
+    return count;
+}
+
+// ------------------------------------------------------------------------------------------------
+// reset snapshot
+
+void Batch::save_reset_state() {
+    download_all();
+    for (int i = 0; i < num_envs(); i++) { impl_->pos0[i] = envs_[i].pos; impl_->vel0[i] = envs_[i].vel; }
+    CUDA_CHECK(cudaSetDevice(device_));
+    // pos/vel sections of the device snapshot = current state
+    CUDA_CHECK(cudaMemcpyAsync(d_state0_, d_state_, sizeof(double) * state_doubles_, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+void Batch::reset_envs(const int* env_ids, int n) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (n <= 0) return;
+    int* d_ids = nullptr;
+    CUDA_CHECK(cudaMalloc(&d_ids, sizeof(int) * n));
+    CUDA_CHECK(cudaMemcpyAsync(d_ids, env_ids, sizeof(int) * n, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    reset_kernel<<<n, 64, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, reinterpret_cast<const EnvDesc*>(d_envdesc_), d_design_, d_ids, n,
+                                                       d_time_, d_unstable_);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    CUDA_CHECK(cudaFree(d_ids));
+    for (int i = 0; i < n; i++) envs_.at(env_ids[i]).host_fresh = false;
+}
+
+void Batch::reset_all() {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    reset_kernel<<<num_envs(), 64, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, reinterpret_cast<const EnvDesc*>(d_envdesc_), d_design_,
+                                                                nullptr, num_envs(), d_time_, d_unstable_);
+    CUDA_CHECK(cudaGetLastError());
+    for (auto& e : envs_) e.host_fresh = false;
+}
+
+void Batch::object_com(int obj_index, double* out_host_2n) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    const int n = num_envs();
+    if (impl_->com_obj != obj_index) {
+        std::vector<int> ranges(3 * (size_t)n, 0);
+        for (int i = 0; i < n; i++) {
+            const EnvHost& e = envs_[i];
+            if (obj_index >= (int)e.world.objects.size()) continue;
+            const VoxelObject& ob = e.world.objects[obj_index];
+            const int l0 = e.point_local[ob.min_point];
+            if (l0 < 0) continue;   // static object: not tracked on the device
+            ranges[3 * i] = l0;
+            ranges[3 * i + 1] = ob.max_point - ob.min_point + 1;
+            ranges[3 * i + 2] = (int)e.dyn_points.size();
+        }
+        cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out);
+        CUDA_CHECK(cudaMalloc(&impl_->d_com_ranges, sizeof(int) * ranges.size()));
+        CUDA_CHECK(cudaMalloc(&impl_->d_com_out, sizeof(double) * 2 * n));
+        CUDA_CHECK(cudaMemcpy(impl_->d_com_ranges, ranges.data(), sizeof(int) * ranges.size(), cudaMemcpyHostToDevice));
+        impl_->com_obj = obj_index;
+    }
+    com_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), impl_->d_com_ranges, n,
+                                                                   impl_->d_com_out);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaMemcpyAsync(out_host_2n, impl_->d_com_out, sizeof(double) * 2 * n, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+// ------------------------------------------------------------------------------------------------
+// debug hooks
+
+void Batch::enable_candidate_dump(int cap_per_env) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    cudaFree(d_cand_); cudaFree(d_cand_n_);
+    d_cand_ = nullptr; d_cand_n_ = nullptr;
+    cand_cap_ = cap_per_env;
+    if (cap_per_env <= 0 || num_envs() == 0) return;
+    CUDA_CHECK(cudaMalloc(&d_cand_, sizeof(unsigned int) * (size_t)cap_per_env * num_envs()));
+    CUDA_CHECK(cudaMalloc(&d_cand_n_, sizeof(int) * num_envs()));
+    CUDA_CHECK(cudaMemset(d_cand_n_, 0, sizeof(int) * num_envs()));
+}
+
+void Batch::leaf_info(int env, int dynamic, int leaf, int* obj, int* boxel) const {
+    // leaves are numbered per environment: dynamic leaves over dynamic objects in load order, static leaves
+    // over static objects in load order; inside an object by ascending boxel index
+    const EnvHost& e = envs_.at(env);
+    int k = 0;
+    for (int o = 0; o < (int)e.world.objects.size(); o++) {
+        const VoxelObject& ob = e.world.objects[o];
+        const bool is_dyn = !(ob.all_fixed && !ob.is_robot) || e.obj_force_dynamic[o];
+        if ((is_dyn ? 1 : 0) != (dynamic ? 1 : 0)) continue;
+        if (leaf < k + (int)ob.surface_boxels.size()) { *obj = o; *boxel = ob.surface_boxels[leaf - k]; return; }
+        k += (int)ob.surface_boxels.size();
+    }
+    *obj = -1; *boxel = -1;
+}
+
+int Batch::read_candidates(int env, int* out_pairs, int cap) {
+    if (!d_cand_) return -1;
+    CUDA_CHECK(cudaSetDevice(device_));
+    sync();
+    int n = 0;
+    CUDA_CHECK(cudaMemcpy(&n, d_cand_n_ + env, sizeof(int), cudaMemcpyDeviceToHost));
+    const int m = std::min(n, cand_cap_);
+    std::vector<unsigned int> codes(m);
+    if (m) CUDA_CHECK(cudaMemcpy(codes.data(), d_cand_ + (size_t)env * cand_cap_, sizeof(unsigned int) * m, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < m && i < cap; i++) {
+        const unsigned c = codes[i];
+        int oa, ba, ob, bb;
+        leaf_info(env, 1, (int)(c & kCodeLeafMask), &oa, &ba);
+        leaf_info(env, (c & kCodeStatic) ? 0 : 1, (int)((c >> 12) & kCodeLeafMask), &ob, &bb);
+        out_pairs[4 * i] = oa; out_pairs[4 * i + 1] = ba; out_pairs[4 * i + 2] = ob; out_pairs[4 * i + 3] = bb;
+    }
+    return n;
+}
+
+int Batch::error_flags(int env) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    sync();
+    int v = 0;
+    CUDA_CHECK(cudaMemcpy(&v, d_err_ + env, sizeof(int), cudaMemcpyDeviceToHost));
+    return v;
+}
+
+}  // namespace mevo

@@ -1,0 +1,139 @@
+// Batched soft-body engine: host-side owner of the device buffers (see engine.cu for the kernels).
+//
+// One Batch = N independent environments (each what the reference calls one `Sim`,
+// SimulatorCPP/Sim.h:12-58) resident in HBM on one GPU.  No torch types, no exceptions across the
+// C-ABI (c_api.cpp catches and converts to status codes).
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "topology.h"
+
+namespace mevo {
+
+struct EnvHost {
+    World world;
+    // full-state host mirror in the reference's global numbering
+    std::vector<double> pos, vel, pos_last, vel_true;   // 2P interleaved
+    std::vector<double> goal;                            // E  (length_eq_goal)
+    std::vector<uint8_t> obj_force_dynamic;              // per object: simulate even if all-fixed
+    // packing results
+    std::vector<int> point_local;    // global point -> dynamic local id, or -(static local id)-1
+    std::vector<int> edge_local;     // global edge  -> dynamic local id, or -1
+    std::vector<int> dyn_points;     // dynamic local id -> global point
+    std::vector<int> dyn_edges;      // dynamic local id -> global edge
+    std::vector<int> act_slot_obj;   // action slot -> object index
+    std::vector<int> act_slot_boxel; // action slot -> boxel index in that object
+    int design_id = -1, static_id = -1;
+    size_t state_off = 0;            // doubles into the state buffer
+    int n_act = 0;
+    int cls = 0;                     // size class (index into kGroupSizes)
+    long sim_time = 0;
+    bool host_fresh = true;          // host mirror newer than device?
+};
+
+struct StepStats {
+    int launches = 0;                // kernel launches issued by the last step() call
+};
+
+class Batch {
+public:
+    explicit Batch(int device);
+    ~Batch();
+    Batch(const Batch&) = delete;
+    Batch& operator=(const Batch&) = delete;
+
+    int device() const { return device_; }
+    int num_envs() const { return (int)envs_.size(); }
+    bool finalized() const { return finalized_; }
+
+    int begin_env(int world_w, int world_h);
+    bool add_object(int env, const double* grid, int w, int h, const double* conn, int k,
+                    const std::string& name, double x, double y, bool is_robot);
+    void finalize();   // (re)pack every environment and upload; current state is preserved
+
+    const World& world(int env) const { return envs_.at(env).world; }
+    const EnvHost& env_host(int env) const { return envs_.at(env); }
+    int act_stride() const { return act_stride_; }
+    int num_actuators(int env) const { return envs_.at(env).n_act; }
+
+    // dense actions: values[env * stride + slot]; slot order = robots in load order, actuators in
+    // Robot::init order.  Applied by the next step(apply_actions = true).
+    void set_actions(const double* host_values, int stride);
+    void set_actions_device(const double* dev_values, int stride);
+    double* actions_device_ptr() { return d_act_; }
+    // reference semantics (PhysicsEngine::update_actuator_goals): partial (grid_index, value) list
+    bool env_set_action(int env, const std::string& robot, const double* action_n_by_2, int n);
+
+    // n_steps env-steps of n_substeps substeps each.  Returns the number of environments that
+    // reported "unstable" in the LAST of the n_steps; per-env flags land in unstable_host (may be
+    // null).  An unstable env-step does not advance that env's time (Sim.cpp:105-115).
+    int step(int n_steps, bool apply_actions, uint8_t* unstable_host, int n_substeps = 30);
+    void step_async(int n_steps, bool apply_actions, int n_substeps = 30);   // no host sync
+    void sync();
+    const uint8_t* unstable_device_ptr() const { return d_unstable_; }
+    const int* time_device_ptr() const { return d_time_; }
+
+    // full state access in the reference's numbering, (P,2) row-major
+    void get_state(int env, double* pos, double* vel, double* pos_last, double* vel_true);
+    void set_state(int env, const double* pos, const double* vel, const double* pos_last, const double* vel_true);
+    void get_goal(int env, double* goal);
+    void set_goal(int env, const double* goal);
+    long get_time(int env);
+    void set_time(int env, long t);
+    void translate_object(int env, const std::string& name, double dx, double dy);
+
+    // snapshot 0 of every env (state right after finalize, or after save_reset_state())
+    void save_reset_state();
+    void reset_envs(const int* env_ids, int n);     // Environment::revert_to_snapshot(0) semantics
+    void reset_all();
+
+    // packed robot positions for the learner side: COM (x, y) of object `obj_index` per env
+    void object_com(int obj_index, double* out_host_2n);
+
+    // debug / test hooks: candidate pairs of the first substep of the next step() call
+    void enable_candidate_dump(int cap_per_env);
+    int read_candidates(int env, int* out_pairs /* cap x 4: kind_a, leaf_a, kind_b, leaf_b */, int cap);
+    int error_flags(int env);
+    void leaf_info(int env, int dynamic, int leaf, int* obj, int* boxel) const;
+
+    StepStats last_stats() const { return stats_; }
+    void* stream() const { return stream_; }
+    size_t device_bytes() const { return device_bytes_; }
+
+private:
+    struct Impl;
+    void upload_state(int env);
+    void download_state(int env);
+    void download_all();
+    void pack_env(int env, std::vector<uint8_t>& design_blob, std::vector<uint8_t>& static_blob);
+
+    int device_;
+    bool finalized_ = false;
+    std::vector<EnvHost> envs_;
+    int act_stride_ = 0;
+    StepStats stats_;
+    size_t device_bytes_ = 0;
+
+    // device buffers
+    uint8_t* d_design_ = nullptr;
+    uint8_t* d_static_ = nullptr;
+    double* d_state_ = nullptr;
+    double* d_state0_ = nullptr;
+    double* d_act_ = nullptr;
+    void* d_envdesc_ = nullptr;
+    int* d_class_envs_ = nullptr;
+    uint8_t* d_unstable_ = nullptr;
+    int* d_time_ = nullptr;
+    int* d_err_ = nullptr;
+    unsigned int* d_cand_ = nullptr;
+    int* d_cand_n_ = nullptr;
+    int cand_cap_ = 0;
+    size_t state_doubles_ = 0;
+    void* stream_ = nullptr;
+    Impl* impl_ = nullptr;
+};
+
+}  // namespace mevo

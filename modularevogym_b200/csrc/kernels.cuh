@@ -1,0 +1,668 @@
+// sm_100a kernels of the batched soft-body engine.
+//
+// One GROUP of G threads (G = 32 .. 512, one warp for 5x5 robots) owns one environment for a whole
+// env-step: its dynamic state is staged from HBM into shared memory once, the 30 substeps of
+// Sim::step (reference SimulatorCPP/Sim.cpp:105-115 -> Environment::step, Environment.cpp:166-205)
+// run out of shared memory, and the state is written back once.  No tensor cores: the path is a
+// gather / sqrt / div / scatter chain in FP64, bounded by FP64 issue and latency, not a contraction.
+//
+// Arithmetic contract: every expression keeps the reference's operand order and association, and
+// this translation unit is compiled with --fmad=false, so each product and sum is rounded
+// separately exactly like the reference's x86-64 build (no FMA).  IEEE sqrt / div are the CUDA
+// defaults for double.  Spring forces and constraint corrections are summed per point through a
+// gather list sorted "a-sides by edge id, then b-sides by edge id", which is the order the
+// reference's sequential Eigen indexed-view updates produce (PhysicsEngine.cpp:530-531,670-671),
+// so those sums are bit-identical.  Contact forces are summed in candidate-list order (the
+// reference uses its bounding-box-tree descent order) -> ulp-level differences, see DESIGN.md.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "device_layout.h"
+
+namespace mevo {
+
+struct StepParams {
+    const uint8_t* design;
+    const uint8_t* statics;
+    double* state;
+    const double* act;
+    const EnvDesc* envs;
+    const int* class_envs;
+    int n_class_envs;
+    int smem_per_env;
+    int n_steps;
+    int n_substeps;
+    int apply_actions;
+    uint8_t* unstable;
+    int* sim_time;
+    int* err;
+    unsigned int* dbg_cand;     // optional: candidate codes of the first substep
+    int* dbg_cand_n;
+    int dbg_cand_cap;
+};
+
+// PhysicsEngine.h:17-27
+#define MEVO_VISCOUS_DRAG 0.1
+#define MEVO_GRAVITY 110.0
+#define MEVO_COLLISION_CONST_GROUND (2000000.0 * 7)
+#define MEVO_COLLISION_CONST_OBJ (300000.0 * 7)
+#define MEVO_COLLISION_VEL_DAMPING 140.0
+#define MEVO_COLLISION_BASE_DIST 0.005
+#define MEVO_DYN_FRICTION 0.2
+#define MEVO_FRICTION_CONST (150.0 * 8)
+#define MEVO_DT 0.0001
+#define MEVO_CELL 0.1
+
+template <int G, int EPC>
+__device__ __forceinline__ void group_sync(int grp) {
+    if (EPC == 1) {
+        __syncthreads();
+    } else if (G == 32) {
+        __syncwarp();
+    } else {
+        asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "n"(G) : "memory");
+    }
+}
+
+__device__ __forceinline__ bool aabb_overlap(const double4& a, const double4& b) {
+    // BoundingBox::in, main.h:64-72 (closed intervals, F_ERROR_TOL = 0); (x,y,z,w) = (minx,miny,maxx,maxy)
+    if (a.x > b.z || a.z < b.x) return false;
+    if (a.y > b.w || a.w < b.y) return false;
+    return true;
+}
+
+__device__ __forceinline__ double4 ldg_d4(const double4* p) {
+    const double2 lo = __ldg(reinterpret_cast<const double2*>(p));
+    const double2 hi = __ldg(reinterpret_cast<const double2*>(p) + 1);
+    return make_double4(lo.x, lo.y, hi.x, hi.y);
+}
+
+__device__ __forceinline__ double cross2(double ax, double ay, double bx, double by) {
+    return ax * by - ay * bx;   // Boxel.cpp:37-39
+}
+
+// MatrixBase::normalized (Eigen/src/Core/Dot.h:124-134)
+__device__ __forceinline__ void normalize2(double& x, double& y) {
+    double z = x * x + y * y;
+    if (z > 0) { double s = sqrt(z); x = x / s; y = y / s; }
+}
+
+struct PointSrc {
+    const double2* dyn_pos;     // shared memory
+    const double2* dyn_vt;      // shared memory
+    const double2* st_pos;      // global (read-only)
+    __device__ __forceinline__ double2 pos(int id, bool is_static) const {
+        return is_static ? __ldg(st_pos + id) : dyn_pos[id];
+    }
+    __device__ __forceinline__ double2 vt(int id, bool is_static) const {
+        return is_static ? make_double2(0.0, 0.0) : dyn_vt[id];
+    }
+};
+
+// PhysicsEngine::get_intersecting, PhysicsEngine.cpp:1094-1121
+__device__ __forceinline__ bool segments_intersect(double2 a1, double2 b1, double2 a2, double2 b2) {
+    double d1x = b1.x - a1.x, d1y = b1.y - a1.y;
+    double d2x = b2.x - a2.x, d2y = b2.y - a2.y;
+    double det = -d1x * d2y + d2x * d1y;
+    if (fabs(det) < 0.0001) return false;
+    double x_diff = a2.x - a1.x;
+    double y_diff = a2.y - a1.y;
+    double t = (-d2y * x_diff + d2x * y_diff) / det;
+    double s = (-d1y * x_diff + d1x * y_diff) / det;
+    return (0.0 <= t && t <= 1 && 0.0 <= s && s <= 1);
+}
+
+// PhysicsEngine::dist_point_edge, PhysicsEngine.cpp:1123-1135
+__device__ __forceinline__ double dist_point_segment(double2 p, double2 a, double2 b) {
+    double bx = b.x - a.x, by = b.y - a.y;
+    double base_length = sqrt(bx * bx + by * by);
+    if (base_length < 0.000001) return 1000.0;
+    double sx = p.x - a.x, sy = p.y - a.y;
+    double cross = fabs(bx * sy - sx * by);
+    return cross / base_length;
+}
+
+struct Contact {
+    int p, a, b;                 // point ids (namespace given by the flags)
+    bool p_static, ab_static;
+    double fpx, fpy;             // normal_force + vel_additive1        (added to p)
+    double fax, fay;             // normal_force/2 + vel_additive2/2    (subtracted from a)
+    double fbx, fby;             // normal_force/2 + vel_additive3/2    (subtracted from b)
+    double frx, fry;             // friction_force (added to p; halves subtracted from a and b)
+};
+
+// Boxel::point_in_boxel (Boxel.cpp:41-65) followed by
+// PhysicsEngine::resolve_point_boxel_collisions (PhysicsEngine.cpp:910-1092).
+// corner = index of p in main's TL,TR,BR,BL list.  Returns false when no contact results.
+__device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const LeafRec& mainb, bool main_static,
+                                                    const LeafRec& refb, bool ref_static, int corner, Contact& c) {
+    const int p = mainb.pt[corner];
+    if (main_static == ref_static) {           // shared points only exist inside one object (PhysicsEngine.cpp:895-901)
+        if (p == refb.pt[0] || p == refb.pt[1] || p == refb.pt[2] || p == refb.pt[3]) return false;
+    }
+    const double2 pp = src.pos(p, main_static);
+    const double2 rtl = src.pos(refb.pt[0], ref_static), rtr = src.pos(refb.pt[1], ref_static);
+    const double2 rbr = src.pos(refb.pt[2], ref_static), rbl = src.pos(refb.pt[3], ref_static);
+    {
+        double tlx = rtl.x - pp.x, tly = rtl.y - pp.y;
+        double trx = rtr.x - pp.x, try_ = rtr.y - pp.y;
+        double blx = rbl.x - pp.x, bly = rbl.y - pp.y;
+        double brx = rbr.x - pp.x, bry = rbr.y - pp.y;
+        double a = cross2(tlx, tly, trx, try_);
+        double b = cross2(trx, try_, brx, bry);
+        double cc = cross2(brx, bry, tlx, tly);
+        bool inside = (cc * a >= 0.0 && cc * b >= 0.0);
+        if (!inside) {
+            double d = cross2(tlx, tly, blx, bly);
+            double e = cross2(blx, bly, brx, bry);
+            inside = (cc * d >= 0.0 && cc * e >= 0.0);
+        }
+        if (!inside) return false;
+    }
+    // the two main-boxel sides incident to corner p (PhysicsEngine.cpp:915-938): sides are top,right,bot,left
+    const int s0 = (corner == 0 || corner == 1) ? 0 : 2;      // top for TL/TR, bot for BR/BL
+    const int s1 = (corner == 0 || corner == 3) ? 3 : 1;      // left for TL/BL, right for TR/BR
+    const double2 m0a = src.pos(mainb.ea[s0], main_static), m0b = src.pos(mainb.eb[s0], main_static);
+    const double2 m1a = src.pos(mainb.ea[s1], main_static), m1b = src.pos(mainb.eb[s1], main_static);
+
+    int best = -1;
+    double min_dist = 0.0;
+    double2 best_a = make_double2(0, 0), best_b = make_double2(0, 0);
+#pragma unroll 1
+    for (int s = 0; s < 4; s++) {                                              // :943-960
+        if (!((refb.surf_mask >> s) & 1)) continue;
+        const double2 ra = src.pos(refb.ea[s], ref_static), rb = src.pos(refb.eb[s], ref_static);
+        bool viable = segments_intersect(m0a, m0b, ra, rb);
+        if (!viable) viable = segments_intersect(m1a, m1b, ra, rb);
+        if (!viable) continue;
+        double d = dist_point_segment(pp, ra, rb);
+        if (best < 0 || d < min_dist) { best = s; min_dist = d; best_a = ra; best_b = rb; }   // :1026-1037
+    }
+    if (best < 0) return false;
+
+    c.p = p; c.a = refb.ea[best]; c.b = refb.eb[best];
+    c.p_static = main_static; c.ab_static = ref_static;
+    // Edge::get_normal, Edge.cpp:16-22
+    double sx = best_b.x - best_a.x, sy = best_b.y - best_a.y;
+    double nx = -sy, ny = sx;
+    normalize2(nx, ny);
+    double nfx = nx * MEVO_COLLISION_CONST_OBJ * (MEVO_COLLISION_BASE_DIST + min_dist);     // :1041
+    double nfy = ny * MEVO_COLLISION_CONST_OBJ * (MEVO_COLLISION_BASE_DIST + min_dist);
+    double ux = nx, uy = ny;                                                               // :1044-1045
+    normalize2(ux, uy);
+    const double2 vp = src.vt(c.p, main_static), va = src.vt(c.a, ref_static), vb = src.vt(c.b, ref_static);
+    double dp = ux * vp.x + uy * vp.y;
+    double da = ux * va.x + uy * va.y;
+    double db = ux * vb.x + uy * vb.y;
+    double v1x = ux * (-1.0) * dp * MEVO_COLLISION_VEL_DAMPING, v1y = uy * (-1.0) * dp * MEVO_COLLISION_VEL_DAMPING;
+    double v2x = ux * (1.0) * da * MEVO_COLLISION_VEL_DAMPING, v2y = uy * (1.0) * da * MEVO_COLLISION_VEL_DAMPING;
+    double v3x = ux * (1.0) * db * MEVO_COLLISION_VEL_DAMPING, v3y = uy * (1.0) * db * MEVO_COLLISION_VEL_DAMPING;
+    c.fpx = nfx + v1x;           c.fpy = nfy + v1y;                                         // :1057-1059
+    c.fax = nfx / 2 + v2x / 2;   c.fay = nfy / 2 + v2y / 2;
+    c.fbx = nfx / 2 + v3x / 2;   c.fby = nfy / 2 + v3y / 2;
+    double tx0 = nx, ty0 = ny;                                                             // :1065-1066
+    normalize2(tx0, ty0);
+    double tx = -ty0, ty = tx0;
+    double proj = tx * vp.x + ty * vp.y;
+    double nfm = sqrt(nfx * nfx + nfy * nfy);
+    if (proj < 0) { proj *= -1.0; tx *= -1.0; ty *= -1.0; }
+    double th = tanh(proj / (MEVO_DYN_FRICTION * nfm));
+    c.frx = MEVO_FRICTION_CONST * tx * (-1.0) * MEVO_DYN_FRICTION * nfm * th;               // :1077
+    c.fry = MEVO_FRICTION_CONST * ty * (-1.0) * MEVO_DYN_FRICTION * nfm * th;
+    return true;
+}
+
+// collision_forces += contact, in the reference's statement order (PhysicsEngine.cpp:1057-1082).
+// Forces on static (all-fixed, pruned) points are dropped: they can never move anything.
+__device__ __forceinline__ void apply_contact(double2* cf, const Contact& c, int reps) {
+    for (int r = 0; r < reps; r++) {
+        if (!c.p_static) { double2 v = cf[c.p]; v.x += c.fpx; v.y += c.fpy; cf[c.p] = v; }
+        if (!c.ab_static) {
+            double2 v = cf[c.a]; v.x -= c.fax; v.y -= c.fay; cf[c.a] = v;
+            v = cf[c.b]; v.x -= c.fbx; v.y -= c.fby; cf[c.b] = v;
+        }
+        if (!c.p_static) { double2 v = cf[c.p]; v.x += c.frx; v.y += c.fry; cf[c.p] = v; }
+        if (!c.ab_static) {
+            double2 v = cf[c.a]; v.x -= c.frx / 2; v.y -= c.fry / 2; cf[c.a] = v;
+            v = cf[c.b]; v.x -= c.frx / 2; v.y -= c.fry / 2; cf[c.b] = v;
+        }
+    }
+}
+
+template <int G, int EPC>
+__global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int NW = G / 32;
+    const int grp = threadIdx.x / G;
+    const int t = threadIdx.x % G;
+    const int lane = threadIdx.x & 31;
+    const int warp = t >> 5;
+    const int slot = blockIdx.x * EPC + grp;
+    if (slot >= prm.n_class_envs) return;     // whole group leaves together
+    const int env = prm.class_envs[slot];
+    const EnvDesc ed = prm.envs[env];
+    const uint8_t* db = prm.design + ed.design_off;
+    const DesignHeader H = *reinterpret_cast<const DesignHeader*>(db);
+    const int Pd = H.Pd, Ed = H.Ed, n_leaf = H.n_leaf;
+    const bool has_static = ed.static_off != ~0ull;
+    const uint8_t* sb = has_static ? prm.statics + ed.static_off : nullptr;
+    StaticHeader SH;
+    if (has_static) SH = *reinterpret_cast<const StaticHeader*>(sb);
+    else { SH.Ps = 0; SH.n_leaf = 0; SH.gx0 = SH.gy0 = 0; SH.gw = SH.gh = 0; SH.o_pos = SH.o_leaf = SH.o_aabb = SH.o_grid = 0; }
+    const double2* st_pos = reinterpret_cast<const double2*>(sb + SH.o_pos);
+    const LeafRec* st_leaf = reinterpret_cast<const LeafRec*>(sb + SH.o_leaf);
+    const double4* st_aabb = reinterpret_cast<const double4*>(sb + SH.o_aabb);
+    const int16_t* st_grid = reinterpret_cast<const int16_t*>(sb + SH.o_grid);
+
+    unsigned char* sm = smem_raw + (size_t)grp * prm.smem_per_env;
+    const SmemLayout L = smem_layout(Pd, Ed, n_leaf, H.cand_cap);
+    double2* pos = reinterpret_cast<double2*>(sm + L.o_pos);
+    double2* vel = reinterpret_cast<double2*>(sm + L.o_vel);
+    double2* last = reinterpret_cast<double2*>(sm + L.o_last);
+    double2* vt = reinterpret_cast<double2*>(sm + L.o_vt);
+    double2* cf = reinterpret_cast<double2*>(sm + L.o_cf);
+    double2* spos = reinterpret_cast<double2*>(sm + L.o_spos);
+    double2* svel = reinterpret_cast<double2*>(sm + L.o_svel);
+    double2* accp = reinterpret_cast<double2*>(sm + L.o_accp);
+    double2* accv = reinterpret_cast<double2*>(sm + L.o_accv);
+    double* mass = reinterpret_cast<double*>(sm + L.o_mass);
+    double* ek = reinterpret_cast<double*>(sm + L.o_ek);
+    double* el0 = reinterpret_cast<double*>(sm + L.o_el0);
+    double* leq = reinterpret_cast<double*>(sm + L.o_leq);
+    double* goal = reinterpret_cast<double*>(sm + L.o_goal);
+    double2* ef = reinterpret_cast<double2*>(sm + L.o_ef);
+    double4* aabb = reinterpret_cast<double4*>(sm + L.o_aabb);
+    LeafRec* leaf = reinterpret_cast<LeafRec*>(sm + L.o_leaf);
+    uint16_t* ea = reinterpret_cast<uint16_t*>(sm + L.o_ea);
+    uint16_t* eb = reinterpret_cast<uint16_t*>(sm + L.o_eb);
+    uint16_t* csro = reinterpret_cast<uint16_t*>(sm + L.o_csro);
+    uint16_t* csre = reinterpret_cast<uint16_t*>(sm + L.o_csre);
+    uint8_t* fixedp = reinterpret_cast<uint8_t*>(sm + L.o_fixed);
+    unsigned int* cand = reinterpret_cast<unsigned int*>(sm + L.o_cand);
+    volatile int* misc = reinterpret_cast<volatile int*>(sm + L.o_misc);
+    const int seg_cap = H.cand_cap / NW;
+
+    // ---------------------------------------------------------------- stage in (coalesced, once per step)
+    double* gstate = prm.state + ed.state_off;
+    {
+        const double2* g2 = reinterpret_cast<const double2*>(gstate);
+        for (int i = t; i < Pd; i += G) {
+            pos[i] = g2[i];
+            vel[i] = g2[Pd + i];
+            last[i] = g2[2 * Pd + i];
+            vt[i] = g2[3 * Pd + i];
+            mass[i] = __ldg(reinterpret_cast<const double*>(db + H.o_mass) + i);
+            fixedp[i] = __ldg(db + H.o_fixed + i);
+        }
+        const double* ggoal = gstate + 8 * (size_t)Pd;
+        const int16_t* eact = reinterpret_cast<const int16_t*>(db + H.o_eact);
+        const double* act = prm.act + ed.act_off;
+        for (int e = t; e < Ed; e += G) {
+            ek[e] = __ldg(reinterpret_cast<const double*>(db + H.o_ek) + e);
+            double l0 = __ldg(reinterpret_cast<const double*>(db + H.o_el0) + e);
+            el0[e] = l0;
+            ea[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_ea) + e);
+            eb[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_eb) + e);
+            double g = ggoal[e];
+            if (prm.apply_actions) {
+                // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather:
+                // goal = (sum of the <= 2 actuations driving this edge) * (init_len / count)
+                int a0 = eact[2 * e], a1 = eact[2 * e + 1];
+                if (a0 >= 0) {
+                    double sum = 0.0 + act[a0];
+                    int cnt = 1;
+                    if (a1 >= 0) { sum += act[a1]; cnt = 2; }
+                    g = sum * (l0 / cnt);
+                }
+            }
+            goal[e] = g;
+        }
+        for (int i = t; i < Pd + 1; i += G) csro[i] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_csro) + i);
+        for (int i = t; i < 2 * Ed; i += G) csre[i] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_csre) + i);
+        const uint4* gl = reinterpret_cast<const uint4*>(db + H.o_leaf);
+        uint4* sl = reinterpret_cast<uint4*>(leaf);
+        for (int i = t; i < 2 * n_leaf; i += G) sl[i] = __ldg(gl + i);
+        if (t < kMiscInts) misc[t] = 0;
+    }
+    group_sync<G, EPC>(grp);
+
+    const ObjRec* objs = reinterpret_cast<const ObjRec*>(db + H.o_obj);
+    const unsigned int* pairs = reinterpret_cast<const unsigned int*>(db + H.o_pairs);
+    const uint16_t* rlev = reinterpret_cast<const uint16_t*>(db + H.o_rlev);
+    const uint16_t* rvis = reinterpret_cast<const uint16_t*>(db + H.o_rvis);
+    PointSrc src;
+    src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = st_pos;
+
+    int unstable = 0;
+    int completed_steps = 0;
+    bool overflow = false;
+
+    for (int step = 0; step < prm.n_steps && !unstable; step++) {
+        for (int sub = 0; sub < prm.n_substeps; sub++) {
+            // ======================================================= K2a: leaf AABB refit (a-4)
+            for (int l = t; l < n_leaf; l += G) {
+                const LeafRec r = leaf[l];
+                double2 q = pos[r.pt[0]];
+                double minx = q.x, maxx = q.x, miny = q.y, maxy = q.y;
+#pragma unroll
+                for (int c = 1; c < 4; c++) {
+                    q = pos[r.pt[c]];
+                    minx = fmin(minx, q.x); maxx = fmax(maxx, q.x);
+                    miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
+                }
+                aabb[l] = make_double4(minx, miny, maxx, maxy);
+            }
+            for (int i = t; i < Pd; i += G) cf[i] = make_double2(0.0, 0.0);
+            if (t < 8) misc[16 + t] = 0;
+            group_sync<G, EPC>(grp);
+
+            // ======================================================= K2b: broad phase + compaction (a-4, a-12)
+            int cnt = 0;     // warp-uniform number of candidates in this warp's segment
+            unsigned int* myseg = cand + warp * seg_cap;
+            // (i) dynamic-vs-dynamic leaf pairs from the precomputed pair table (each unordered pair once)
+            for (int base = 0; base < H.n_pairs; base += G) {
+                const int i = base + t;
+                bool hit = false;
+                unsigned int code = 0;
+                if (i < H.n_pairs) {
+                    code = __ldg(pairs + i);
+                    const int a = code & kCodeLeafMask, b = (code >> 12) & kCodeLeafMask;
+                    hit = aabb_overlap(aabb[a], aabb[b]);
+                    if (hit && (code & kCodeCount))                // ordered pairs (a,b) and (b,a) both count (a-12)
+                        atomicAdd((int*)&misc[16 + (code >> kCodeObjShift)], 2);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int at = cnt + __popc(m & ((1u << lane) - 1u));
+                    if (at < seg_cap) myseg[at] = code & (kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj);
+                    else overflow = true;
+                }
+                cnt += __popc(m);
+            }
+            // (ii) dynamic leaves vs the static uniform grid (cell = one voxel); the window is widened
+            //      by one cell each way, then the exact closed-interval test decides
+            if (has_static) {
+                for (int base = 0; base < n_leaf; base += G) {
+                    const int l = base + t;
+                    int cx0 = 0, cy0 = 0, wx = 0, n_cells = 0;
+                    double4 bb = make_double4(0, 0, 0, 0);
+                    if (l < n_leaf) {
+                        bb = aabb[l];
+                        cx0 = max((int)floor(bb.x / MEVO_CELL) - 1 - SH.gx0, 0);
+                        int cx1 = min((int)floor(bb.z / MEVO_CELL) + 1 - SH.gx0, SH.gw - 1);
+                        cy0 = max((int)floor(bb.y / MEVO_CELL) - 1 - SH.gy0, 0);
+                        int cy1 = min((int)floor(bb.w / MEVO_CELL) + 1 - SH.gy0, SH.gh - 1);
+                        wx = cx1 - cx0 + 1;
+                        const int wy = cy1 - cy0 + 1;
+                        n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
+                    }
+                    const int max_cells = __reduce_max_sync(0xffffffffu, n_cells);
+                    for (int it = 0; it < max_cells; it++) {
+                        bool hit = false;
+                        int s = -1;
+                        if (it < n_cells) {
+                            const int cx = cx0 + it % wx, cy = cy0 + it / wx;
+                            s = __ldg(st_grid + cy * SH.gw + cx);
+                            if (s >= 0) hit = aabb_overlap(bb, ldg_d4(st_aabb + s));
+                        }
+                        const unsigned m = __ballot_sync(0xffffffffu, hit);
+                        if (hit) {
+                            const int at = cnt + __popc(m & ((1u << lane) - 1u));
+                            if (at < seg_cap) myseg[at] = (unsigned)l | ((unsigned)s << 12) | kCodeStatic;
+                            else overflow = true;
+                        }
+                        cnt += __popc(m);
+                    }
+                }
+            }
+            if (cnt > seg_cap) cnt = seg_cap;
+            if (lane == 0) misc[warp] = cnt;
+            group_sync<G, EPC>(grp);
+
+            if (prm.dbg_cand && step == 0 && sub == 0) {
+                int off = 0;
+                for (int w = 0; w < NW; w++) {
+                    const int c = misc[w];
+                    for (int i = t; i < c; i += G)
+                        if (off + i < prm.dbg_cand_cap) prm.dbg_cand[(size_t)env * prm.dbg_cand_cap + off + i] = cand[w * seg_cap + i];
+                    off += c;
+                }
+                if (t == 0) prm.dbg_cand_n[env] = off;
+            }
+
+            // ======================================================= K3: narrow phase + contact response (a-5, a-6)
+            for (int w = 0; w < NW; w++) {
+                const int n_items = misc[w] * 8;      // candidate x {a->b, b->a} x 4 corners
+                for (int base = 0; base < n_items; base += G) {
+                    const int i = base + t;
+                    bool has = false;
+                    Contact c;
+                    int reps = 1;
+                    if (i < n_items) {
+                        const unsigned code = cand[w * seg_cap + (i >> 3)];
+                        const int a = code & kCodeLeafMask, b = (code >> 12) & kCodeLeafMask;
+                        const bool b_static = (code & kCodeStatic) != 0;
+                        reps = (code & kCodeSameObj) ? 2 : 1;
+                        const LeafRec la = leaf[a];
+                        LeafRec lb;
+                        if (b_static) {
+                            const uint4* g = reinterpret_cast<const uint4*>(st_leaf + b);
+                            uint4* d = reinterpret_cast<uint4*>(&lb);
+                            d[0] = __ldg(g); d[1] = __ldg(g + 1);
+                        } else {
+                            lb = leaf[b];
+                        }
+                        const int dir = (i >> 2) & 1, corner = i & 3;
+                        if (dir == 0) has = resolve_point_vs_boxel(src, la, false, lb, b_static, corner, c);
+                        else has = resolve_point_vs_boxel(src, lb, b_static, la, false, corner, c);
+                    }
+                    // deterministic, race-free accumulation: warps in order, lanes in order
+                    unsigned m = __ballot_sync(0xffffffffu, has);
+                    if (NW == 1) {
+                        while (m) {
+                            const int l = __ffs(m) - 1;
+                            if (lane == l) apply_contact(cf, c, reps);
+                            m &= m - 1;
+                            __syncwarp();
+                        }
+                    } else {
+                        if (lane == 0) misc[32 + warp] = (int)m;
+                        group_sync<G, EPC>(grp);
+                        for (int w2 = 0; w2 < NW; w2++) {
+                            unsigned m2 = (unsigned)misc[32 + w2];
+                            if (m2 == 0) continue;           // uniform across the group
+                            if (warp == w2) {
+                                while (m2) {
+                                    const int l = __ffs(m2) - 1;
+                                    if (lane == l) apply_contact(cf, c, reps);
+                                    m2 &= m2 - 1;
+                                    __syncwarp();
+                                }
+                            }
+                            group_sync<G, EPC>(grp);
+                        }
+                        group_sync<G, EPC>(grp);             // masks are rewritten in the next round
+                    }
+                }
+            }
+            // K6a: unstable test uses the boxes of the START of this substep (a-12)
+            int sub_unstable = 0;
+            for (int o = 0; o < H.n_obj; o++) {
+                const ObjRec orc = objs[o];
+                if (orc.is_robot && misc[16 + o] > (int)orc.n_surface) sub_unstable = 1;
+            }
+            group_sync<G, EPC>(grp);
+
+            // ======================================================= K4: actuators + RK4 (a-7, a-8, a-9)
+            for (int e = t; e < Ed; e += G) {
+                const double2 pa = pos[ea[e]], pb = pos[eb[e]];
+                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                const double dist = sqrt(dx * dx + dy * dy);
+                const double additive = (goal[e] - dist) * 0.006;
+                leq[e] = dist + additive;
+            }
+            // leq[e] is written and read by the same thread (same striding): no barrier needed
+#pragma unroll 1
+            for (int s = 0; s < 4; s++) {
+                const double2* sp = (s == 0) ? pos : spos;
+                const double2* sv = (s == 0) ? vel : svel;
+                for (int e = t; e < Ed; e += G) {
+                    const double2 pa = sp[ea[e]], pb = sp[eb[e]];
+                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                    const double dist = sqrt(dx * dx + dy * dy);
+                    const double mag = (dist - leq[e]) * ek[e] / dist;
+                    ef[e] = make_double2(dx * mag, dy * mag);
+                }
+                group_sync<G, EPC>(grp);
+                for (int p = t; p < Pd; p += G) {
+                    const double2 v = sv[p];
+                    const double2 x = sp[p];
+                    double Fx = 0.0, Fy = 0.0;
+                    const int j1 = csro[p + 1];
+                    for (int j = csro[p]; j < j1; j++) {
+                        const unsigned ent = csre[j];
+                        const double2 f = ef[ent >> 1];
+                        if (ent & 1u) { Fx += f.x; Fy += f.y; } else { Fx -= f.x; Fy -= f.y; }
+                    }
+                    Fx += v.x * (-MEVO_VISCOUS_DRAG);
+                    Fy += v.y * (-MEVO_VISCOUS_DRAG);
+                    const double m = mass[p];
+                    Fy += m * (-MEVO_GRAVITY);
+                    const double2 c = cf[p];
+                    Fx += c.x; Fy += c.y;
+                    {   // analytic ground plane y = 0 (PhysicsEngine.cpp:566-577)
+                        const bool hit = x.y < 0;
+                        const double normal_force = (hit ? x.y : 0.0) * (-MEVO_COLLISION_CONST_GROUND);
+                        Fy += normal_force;
+                        const double friction_temp = hit ? tanh(v.x * normal_force * MEVO_DYN_FRICTION) : 0.0;
+                        Fx += (-10 * MEVO_DYN_FRICTION) * (normal_force * friction_temp);
+                    }
+                    const double ax = (m == 1.0) ? Fx : Fx / m;    // x / 1.0 == x exactly
+                    const double ay = (m == 1.0) ? Fy : Fy / m;
+                    const double kpx = v.x * MEVO_DT, kpy = v.y * MEVO_DT;
+                    const double kvx = ax * MEVO_DT, kvy = ay * MEVO_DT;
+                    if (s == 0) {
+                        accp[p] = make_double2(kpx, kpy);
+                        accv[p] = make_double2(kvx, kvy);
+                    } else if (s < 3) {
+                        double2 q = accp[p]; q.x = q.x + 2 * kpx; q.y = q.y + 2 * kpy; accp[p] = q;
+                        q = accv[p]; q.x = q.x + 2 * kvx; q.y = q.y + 2 * kvy; accv[p] = q;
+                    }
+                    if (s < 2) {
+                        const double2 x0 = pos[p], v0 = vel[p];
+                        spos[p] = make_double2(x0.x + (kpx * 0.5), x0.y + (kpy * 0.5));
+                        svel[p] = make_double2(v0.x + (kvx * 0.5), v0.y + (kvy * 0.5));
+                    } else if (s == 2) {
+                        const double2 x0 = pos[p], v0 = vel[p];
+                        spos[p] = make_double2(x0.x + kpx, x0.y + kpy);
+                        svel[p] = make_double2(v0.x + kvx, v0.y + kvy);
+                    } else {
+                        double2 qp = accp[p], qv = accv[p];
+                        double dpx = (qp.x + kpx) / 6, dpy = (qp.y + kpy) / 6;
+                        double dvx = (qv.x + kvx) / 6, dvy = (qv.y + kvy) / 6;
+                        if (fixedp[p]) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
+                        double2 x0 = pos[p], v0 = vel[p];
+                        x0.x += dpx; x0.y += dpy; v0.x += dvx; v0.y += dvy;
+                        pos[p] = x0; vel[p] = v0;
+                    }
+                }
+                group_sync<G, EPC>(grp);
+            }
+
+            // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
+            for (int e = t; e < Ed; e += G) {
+                const double2 pa = pos[ea[e]], pb = pos[eb[e]];
+                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                const double dist = sqrt(dx * dx + dy * dy);
+                const double l0 = el0[e];
+                const double over_mag = (dist - l0 * (1 + 0.25)) / (dist * 2);
+                const double under_mag = (dist - l0 * (1 - 0.25)) / (dist * 2);
+                double ox = dx * over_mag, oy = dy * over_mag;
+                double ux = dx * under_mag, uy = dy * under_mag;
+                const double stress = dist / l0;
+                if (!(stress > (1 + 0.25))) { ox = 0.0; oy = 0.0; }
+                if (!(stress < (1 - 0.25))) { ux = 0.0; uy = 0.0; }
+                ef[e] = make_double2((ox + ux) * 0.8, (oy + uy) * 0.8);
+            }
+            group_sync<G, EPC>(grp);
+            for (int p = t; p < Pd; p += G) {
+                if (fixedp[p]) continue;                  // fixed end points receive "0.0" (PhysicsEngine.cpp:670-671)
+                double2 x = pos[p];
+                const int j1 = csro[p + 1];
+                for (int j = csro[p]; j < j1; j++) {
+                    const unsigned ent = csre[j];
+                    const double2 c = ef[ent >> 1];
+                    if (ent & 1u) { x.x += c.x; x.y += c.y; } else { x.x -= c.x; x.y -= c.y; }
+                }
+                pos[p] = x;
+            }
+            group_sync<G, EPC>(grp);
+            // ordered rigid-cell pass, scheduled in point-disjoint levels (PhysicsEngine.cpp:675-710)
+            for (int lv = 0; lv < H.n_rlev; lv++) {
+                const int i1 = __ldg(rlev + lv + 1);
+                for (int i = __ldg(rlev + lv) + t; i < i1; i += G) {
+                    const int e = __ldg(rvis + i);
+                    const int a = ea[e], b = eb[e];
+                    double2 pa = pos[a], pb = pos[b];
+                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                    const double dist = sqrt(dx * dx + dy * dy);
+                    const double l0 = el0[e];
+                    const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
+                    const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
+                    double ox = dx * over_mag, oy = dy * over_mag;
+                    double ux = dx * under_mag, uy = dy * under_mag;
+                    const double stress = dist / l0;
+                    if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
+                    if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
+                    const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
+                    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
+                    pos[a] = pa; pos[b] = pb;
+                }
+                group_sync<G, EPC>(grp);
+            }
+            for (int p = t; p < Pd; p += G) {             // PhysicsEngine::update_true_vel (:602-607)
+                const double2 x = pos[p], l = last[p];
+                vt[p] = make_double2((x.x - l.x) / MEVO_DT, (x.y - l.y) / MEVO_DT);
+                last[p] = x;
+            }
+            group_sync<G, EPC>(grp);
+
+            if (sub_unstable) { unstable = 1; break; }    // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
+        }
+        if (!unstable) completed_steps++;
+    }
+
+    // ---------------------------------------------------------------- stage out
+    {
+        double2* g2 = reinterpret_cast<double2*>(gstate);
+        for (int i = t; i < Pd; i += G) {
+            g2[i] = pos[i];
+            g2[Pd + i] = vel[i];
+            g2[2 * Pd + i] = last[i];
+            g2[3 * Pd + i] = vt[i];
+        }
+        double* ggoal = gstate + 8 * (size_t)Pd;
+        for (int e = t; e < Ed; e += G) ggoal[e] = goal[e];
+        if (overflow) atomicOr(prm.err + env, 1);
+        if (t == 0) {
+            prm.unstable[env] = (uint8_t)unstable;
+            prm.sim_time[env] += completed_steps;
+        }
+    }
+}
+
+// COM of a contiguous dynamic-point range per env (observation side of the path)
+__global__ void com_kernel(const double* state, const EnvDesc* envs, const int* ranges /* n_envs x 3: start, count, Pd */,
+                           int n_envs, double* out) {
+    const int env = blockIdx.x * blockDim.x + threadIdx.x;
+    if (env >= n_envs) return;
+    const int start = ranges[3 * env], count = ranges[3 * env + 1];
+    const double2* pos = reinterpret_cast<const double2*>(state + envs[env].state_off);
+    double sx = 0.0, sy = 0.0;
+    for (int i = 0; i < count; i++) { const double2 q = pos[start + i]; sx += q.x; sy += q.y; }
+    out[2 * env] = count ? sx / count : 0.0;
+    out[2 * env + 1] = count ? sy / count : 0.0;
+}
+
+}  // namespace mevo
