@@ -106,6 +106,43 @@ def sample_robot(shape: Tuple[int, int], pd: Optional[Sequence[float]] = None,
             return robot, full_connectivity(robot)
 
 
+def sample_large_robot(shape: Tuple[int, int], rng=_random, p_empty: float = 0.25) -> Tuple[np.ndarray, np.ndarray]:
+    """Random connected, actuated robot for shapes where whole-robot rejection (``sample_robot``,
+    ``evogym/utils.py:99-152``) practically never terminates (10x10, 20x20: a 43 %-empty random grid
+    is almost never one component).  One ``rng.uniform(0, 1)`` per voxel over
+    ``[p_empty, rest equally]``, then only the largest 4-connected component is kept."""
+    h, w = shape
+    edges = [p_empty + (1.0 - p_empty) * k / 4.0 for k in range(5)]
+    while True:
+        robot = np.zeros((h, w))
+        for r in range(h):
+            for c in range(w):
+                u = rng.uniform(0, 1)
+                robot[r, c] = next((t for t in range(5) if u <= edges[t]), 4)
+        comp = -np.ones((h, w), dtype=np.int64)
+        sizes = []
+        for r0 in range(h):
+            for c0 in range(w):
+                if robot[r0, c0] == 0 or comp[r0, c0] >= 0:
+                    continue
+                cid, n, stack = len(sizes), 0, [(r0, c0)]
+                comp[r0, c0] = cid
+                while stack:
+                    r, c = stack.pop()
+                    n += 1
+                    for dr, dc in ((-1, 0), (1, 0), (0, -1), (0, 1)):
+                        rr, cc = r + dr, c + dc
+                        if 0 <= rr < h and 0 <= cc < w and robot[rr, cc] != 0 and comp[rr, cc] < 0:
+                            comp[rr, cc] = cid
+                            stack.append((rr, cc))
+                sizes.append(n)
+        if not sizes:
+            continue
+        robot[comp != int(np.argmax(sizes))] = 0
+        if has_actuator(robot):
+            return robot, full_connectivity(robot)
+
+
 @dataclass
 class ObjectSpec:
     """One voxel object, in the form the simulator's ``read_*_from_array`` takes."""
@@ -237,6 +274,21 @@ class WorldSpec:
         global point/edge numbering."""
         keyed = sorted(((0 if o.is_robot else 1), name) for name, o in self.objects.items())
         return [self.objects[name] for _, name in keyed]
+
+    def to_dict(self) -> dict:
+        """Plain-JSON form (used by the committed test fixtures)."""
+        return {"width": int(self.width), "height": int(self.height),
+                "objects": [{"name": o.name, "grid": np.asarray(o.grid).astype(int).tolist(),
+                             "connections": np.asarray(o.connections).astype(int).reshape(2, -1).tolist(),
+                             "x": int(o.x), "y": int(o.y)} for o in self.objects.values()]}
+
+    @classmethod
+    def from_dict(cls, d: dict) -> "WorldSpec":
+        w = cls(width=int(d["width"]), height=int(d["height"]))
+        for o in d["objects"]:
+            cn = np.asarray(o["connections"], dtype=np.int64).reshape(2, -1)
+            w.objects[o["name"]] = ObjectSpec(o["name"], np.asarray(o["grid"], dtype=np.int64), cn, int(o["x"]), int(o["y"]))
+        return w
 
     def copy(self) -> "WorldSpec":
         w = WorldSpec(self.width, self.height)

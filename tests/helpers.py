@@ -1,0 +1,82 @@
+"""Shared helpers of the test-suite: fixture loading and candidate-set normalisation."""
+from __future__ import annotations
+
+import glob
+import json
+import os
+from typing import Dict, List, Set, Tuple
+
+import numpy as np
+
+from modularevogym_b200.world import WorldSpec
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def golden_names() -> List[str]:
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+
+
+class Golden:
+    """One committed fixture (layout: tests/golden/make_golden.py::record)."""
+
+    def __init__(self, name: str):
+        self.name = name
+        with np.load(os.path.join(GOLDEN_DIR, name + ".npz")) as z:
+            self.z = {k: z[k] for k in z.files}       # decompress once
+        self.world = WorldSpec.from_dict(json.loads(str(self.z["world_json"])))
+        self.obj_info = self.z["obj_info"]
+        self.n_obj = int(self.obj_info.shape[0])
+        self.P = int(self.z["pos0"].shape[0])
+        self.E = int(self.z["ea"].shape[0])
+        self.n_sub = int(self.z["sub_pos"].shape[0])
+        self.n_steps = int(self.z["step_unstable"].shape[0])
+
+    def __getitem__(self, k):
+        return self.z[k]
+
+    def static_objects(self) -> List[bool]:
+        """objects made of FIXED voxels only that are not robots (never move)"""
+        out = []
+        for o in range(self.n_obj):
+            bx = self.z[f"boxels_{o}"]
+            out.append(bool((bx[:, 0] == 5).all()) and not bool(self.obj_info[o, 0]))
+        return out
+
+    def state_before_substep(self, k: int):
+        """(pos, vel, pos_last, vel_true) the reference had when substep k started"""
+        if k == 0:
+            p, v = self.z["init_pos"], self.z["init_vel"]
+            return p, v, p, v
+        p = self.z["sub_pos"][k - 1]
+        return p, self.z["sub_vel"][k - 1], p, self.z["sub_vt"][k - 1]
+
+    def action_rows(self, step: int) -> np.ndarray:
+        """(A, 2) rows (grid_index, value) as EvoSim.set_action stacks them (evogym/sim.py:141)"""
+        return np.stack((self.z["act_idx"].astype(np.float64), self.z["actions"][step]), axis=1)
+
+
+Pair = Tuple[Tuple[int, int], Tuple[int, int]]
+
+
+def pair_set(cands: np.ndarray, static: List[bool] = None, drop_self: bool = False) -> Set[Pair]:
+    """(n,4) rows (obj_a, boxel_a, obj_b, boxel_b) -> set of unordered pairs.  With ``static`` given,
+    pairs of two static objects are dropped (the engine never generates them: they cannot move
+    anything); ``drop_self`` drops (a, a)."""
+    out: Set[Pair] = set()
+    for oa, ba, ob, bb in np.asarray(cands).reshape(-1, 4).tolist():
+        a, b = (oa, ba), (ob, bb)
+        if drop_self and a == b:
+            continue
+        if static is not None and static[oa] and static[ob]:
+            continue
+        out.add((a, b) if a <= b else (b, a))
+    return out
+
+
+def rel_err(x: np.ndarray, y: np.ndarray) -> float:
+    """max |x - y| / max(1, max |y|): relative to the array's scale, absolute below 1"""
+    x, y = np.asarray(x), np.asarray(y)
+    if x.size == 0:
+        return 0.0
+    return float(np.abs(x - y).max() / max(1.0, float(np.abs(y).max())))
