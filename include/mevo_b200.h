@@ -104,6 +104,9 @@ int mevo_env_set_action(mevo_batch* b, int env, const char* robot, const double*
 int mevo_batch_action_stride(const mevo_batch* b);            /* max actuators per env (after finalize) */
 int mevo_batch_set_actions(mevo_batch* b, const double* host_values, int stride);
 int mevo_batch_set_actions_device(mevo_batch* b, const double* device_values, int stride);
+/* Zero-copy form: subsequent steps read values[env * stride + slot] straight from this DEVICE buffer
+ * (it must stay valid until those steps have run; NULL returns to the internal buffer). */
+int mevo_batch_bind_actions_device(mevo_batch* b, const double* device_values, int stride);
 
 /* ---- stepping -------------------------------------------------------------------------------- */
 /* Sim::step (Sim.cpp:105-115) for every environment, n_steps times, each 30 substeps of
@@ -118,6 +121,11 @@ int mevo_batch_step_substeps(mevo_batch* b, int n_steps, int n_substeps, int app
 int mevo_batch_step_async(mevo_batch* b, int n_steps, int apply_actions);
 int mevo_batch_sync(mevo_batch* b);
 int mevo_batch_last_launches(const mevo_batch* b);            /* kernels launched by the last step call */
+/* on = 1: an environment whose step reports "unstable" is reverted to snapshot 0 (Sim::revert(0),
+ * what the reference's envs do through reset() after the -3 reward, evogym/envs/walk.py:75-78) inside
+ * the step kernel; its flag is still reported for that step.  Default 0 = reference Sim::step behaviour. */
+int mevo_batch_set_auto_reset(mevo_batch* b, int on);
+long long mevo_batch_unstable_events(mevo_batch* b);          /* unstable env-steps since creation */
 
 /* ---- state ----------------------------------------------------------------------------------- */
 /* Sim::get_time (Sim.cpp:135-137) */
@@ -139,6 +147,8 @@ int mevo_batch_save_reset_state(mevo_batch* b);
 int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n);    /* env_ids NULL = all */
 /* centre of mass (mean of point positions) of object `obj` in every env: out = n_envs x 2 doubles (host) */
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out);
+/* same, into a caller-owned DEVICE buffer (n_envs x 2 doubles), enqueued on the batch's stream, no sync */
+int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out);
 
 /* device pointers for zero-copy consumers (valid until the next finalize) */
 double* mevo_batch_actions_device_ptr(mevo_batch* b);

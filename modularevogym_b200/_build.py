@@ -75,7 +75,8 @@ def build_pymodule(force: bool = False, verbose: bool = False) -> str:
 
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_lib(force, verbose)
-    build_pymodule(force, verbose)
+    if os.path.exists(os.path.join(CSRC, "simulator_cpp.cpp")):
+        build_pymodule(force, verbose)
 
 
 if __name__ == "__main__":

@@ -53,6 +53,10 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_action_stride": (_i, [_vp]),
     "mevo_batch_set_actions": (_i, [_vp, _dp, _i]),
     "mevo_batch_set_actions_device": (_i, [_vp, _vp, _i]),
+    "mevo_batch_bind_actions_device": (_i, [_vp, _vp, _i]),
+    "mevo_batch_set_auto_reset": (_i, [_vp, _i]),
+    "mevo_batch_unstable_events": (C.c_longlong, [_vp]),
+    "mevo_batch_object_com_device": (_i, [_vp, _i, _vp]),
     "mevo_batch_step": (_i, [_vp, _i, _i, _bp]),
     "mevo_batch_step_substeps": (_i, [_vp, _i, _i, _i, _bp]),
     "mevo_batch_step_async": (_i, [_vp, _i, _i]),
@@ -300,6 +304,19 @@ class Batch:
 
     def set_actions_device(self, device_ptr: int, stride: int) -> None:
         _check(self.L.mevo_batch_set_actions_device(self.h, C.c_void_p(device_ptr), int(stride)))
+
+    def bind_actions_device(self, device_ptr: int, stride: int) -> None:
+        _check(self.L.mevo_batch_bind_actions_device(self.h, C.c_void_p(device_ptr or None), int(stride)))
+
+    def set_auto_reset(self, on: bool) -> None:
+        _check(self.L.mevo_batch_set_auto_reset(self.h, int(bool(on))))
+
+    @property
+    def unstable_events(self) -> int:
+        return int(self.L.mevo_batch_unstable_events(self.h))
+
+    def object_com_device(self, obj: int, device_ptr: int) -> None:
+        _check(self.L.mevo_batch_object_com_device(self.h, int(obj), C.c_void_p(device_ptr)))
 
     # -- stepping
     def step(self, n_steps: int = 1, apply_actions: bool = True, want_flags: bool = True):

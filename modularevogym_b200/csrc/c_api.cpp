@@ -250,6 +250,20 @@ int mevo_batch_set_actions_device(mevo_batch* b, const double* device_values, in
     return guard([&] { b->impl.set_actions_device(device_values, stride); return 0; });
 }
 
+int mevo_batch_bind_actions_device(mevo_batch* b, const double* device_values, int stride) {
+    return guard([&] { b->impl.bind_actions_device(device_values, stride); return 0; });
+}
+
+int mevo_batch_set_auto_reset(mevo_batch* b, int on) {
+    return guard([&] { b->impl.set_auto_reset(on != 0); return 0; });
+}
+
+long long mevo_batch_unstable_events(mevo_batch* b) {
+    long long v = MEVO_ERR;
+    guard([&] { v = (long long)b->impl.unstable_events(); return 0; });
+    return v;
+}
+
 int mevo_batch_step(mevo_batch* b, int n_steps, int apply_actions, unsigned char* unstable_out) {
     return guard([&] { return b->impl.step(n_steps, apply_actions != 0, unstable_out, 30); });
 }
@@ -313,6 +327,14 @@ int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n) {
 
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out) {
     return guard([&] { b->impl.object_com(obj, out); return 0; });
+}
+
+int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out) {
+    return guard([&] {
+        if (!device_out) throw std::invalid_argument("object_com_device: null output");
+        b->impl.object_com_device(obj, device_out);
+        return 0;
+    });
 }
 
 double* mevo_batch_actions_device_ptr(mevo_batch* b) { return b->impl.actions_device_ptr(); }

@@ -125,7 +125,7 @@ Batch::~Batch() {
     cudaSetDevice(device_);
     cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
     cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
-    cudaFree(d_cand_); cudaFree(d_cand_n_);
+    cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);
     if (impl_) { cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); }
     if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
     delete impl_;
@@ -456,6 +456,8 @@ void Batch::finalize() {
     CUDA_CHECK(cudaMalloc(&d_unstable_, n));
     CUDA_CHECK(cudaMalloc(&d_time_, sizeof(int) * n));
     CUDA_CHECK(cudaMalloc(&d_err_, sizeof(int) * n));
+    if (!d_events_) { CUDA_CHECK(cudaMalloc(&d_events_, sizeof(unsigned long long))); CUDA_CHECK(cudaMemset(d_events_, 0, sizeof(unsigned long long))); }
+    d_act_ext_ = nullptr;
     device_bytes_ = all_design.size() + all_static.size() + 2 * sizeof(double) * state_doubles +
                     sizeof(double) * (size_t)n * act_stride_ + sizeof(EnvDesc) * n + 10 * (size_t)n;
     CUDA_CHECK(cudaMemcpy(d_design_, all_design.data(), all_design.size(), cudaMemcpyHostToDevice));
@@ -683,6 +685,21 @@ void Batch::set_actions_device(const double* dev_values, int stride) {
                                  sizeof(double) * std::min(stride, act_stride_), num_envs(), cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
 }
 
+void Batch::bind_actions_device(const double* dev_values, int stride) {
+    if (dev_values && stride < act_stride_) throw std::runtime_error("bind_actions_device: stride smaller than the batch's action stride");
+    d_act_ext_ = dev_values;
+    act_ext_stride_ = stride;
+}
+
+unsigned long long Batch::unstable_events() {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!d_events_) return 0;
+    sync();
+    unsigned long long v = 0;
+    CUDA_CHECK(cudaMemcpy(&v, d_events_, sizeof(v), cudaMemcpyDeviceToHost));
+    return v;
+}
+
 bool Batch::env_set_action(int env, const std::string& robot, const double* action, int n) {
     // Environment::set_robot_action + PhysicsEngine::update_actuator_goals (Environment.cpp:207-237,
     // PhysicsEngine.cpp:38-97), evaluated on the host mirror of length_eq_goal, then uploaded.
@@ -728,7 +745,11 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.design = d_design_;
     prm.statics = d_static_;
     prm.state = d_state_;
-    prm.act = d_act_;
+    prm.act = d_act_ext_ ? d_act_ext_ : d_act_;
+    prm.act_stride = d_act_ext_ ? act_ext_stride_ : act_stride_;
+    prm.state0 = d_state0_;
+    prm.auto_reset = auto_reset_ ? 1 : 0;
+    prm.unstable_events = d_events_;
     prm.envs = reinterpret_cast<const EnvDesc*>(d_envdesc_);
     prm.n_steps = n_steps;
     prm.n_substeps = n_substeps;
@@ -817,6 +838,12 @@ void Batch::reset_all() {
 }
 
 void Batch::object_com(int obj_index, double* out_host_2n) {
+    object_com_device(obj_index, nullptr);
+    CUDA_CHECK(cudaMemcpyAsync(out_host_2n, impl_->d_com_out, sizeof(double) * 2 * num_envs(), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+void Batch::object_com_device(int obj_index, double* out_device_2n) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     const int n = num_envs();
@@ -839,10 +866,8 @@ void Batch::object_com(int obj_index, double* out_host_2n) {
         impl_->com_obj = obj_index;
     }
     com_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), impl_->d_com_ranges, n,
-                                                                   impl_->d_com_out);
+                                                                   out_device_2n ? out_device_2n : impl_->d_com_out);
     CUDA_CHECK(cudaGetLastError());
-    CUDA_CHECK(cudaMemcpyAsync(out_host_2n, impl_->d_com_out, sizeof(double) * 2 * n, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
-    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -64,6 +64,11 @@ public:
     void set_actions(const double* host_values, int stride);
     void set_actions_device(const double* dev_values, int stride);
     double* actions_device_ptr() { return d_act_; }
+    // zero-copy: subsequent steps read actions straight from this device buffer (nullptr = internal buffer)
+    void bind_actions_device(const double* dev_values, int stride);
+    // unstable environments are reverted to snapshot 0 inside the step kernel (flag still reported)
+    void set_auto_reset(bool on) { auto_reset_ = on; }
+    unsigned long long unstable_events();
     // reference semantics (PhysicsEngine::update_actuator_goals): partial (grid_index, value) list
     bool env_set_action(int env, const std::string& robot, const double* action_n_by_2, int n);
 
@@ -92,6 +97,7 @@ public:
 
     // packed robot positions for the learner side: COM (x, y) of object `obj_index` per env
     void object_com(int obj_index, double* out_host_2n);
+    void object_com_device(int obj_index, double* out_device_2n);   // async on stream()
 
     // debug / test hooks: candidate pairs of the first substep of the next step() call
     void enable_candidate_dump(int cap_per_env);
@@ -128,6 +134,10 @@ private:
     uint8_t* d_unstable_ = nullptr;
     int* d_time_ = nullptr;
     int* d_err_ = nullptr;
+    unsigned long long* d_events_ = nullptr;
+    const double* d_act_ext_ = nullptr;
+    int act_ext_stride_ = 0;
+    bool auto_reset_ = false;
     unsigned int* d_cand_ = nullptr;
     int* d_cand_n_ = nullptr;
     int cand_cap_ = 0;

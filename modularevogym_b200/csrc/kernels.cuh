@@ -26,7 +26,11 @@ struct StepParams {
     const uint8_t* design;
     const uint8_t* statics;
     double* state;
-    const double* act;
+    const double* act;          // dense actions, act[env * act_stride + slot]
+    int act_stride;
+    const double* state0;       // reset snapshot (same layout as state; pos and vel sections used)
+    int auto_reset;             // 1: an environment that reports "unstable" is reverted to snapshot 0 in place
+    unsigned long long* unstable_events;
     const EnvDesc* envs;
     const int* class_envs;
     int n_class_envs;
@@ -297,7 +301,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
         }
         const double* ggoal = gstate + 8 * (size_t)Pd;
         const int16_t* eact = reinterpret_cast<const int16_t*>(db + H.o_eact);
-        const double* act = prm.act + ed.act_off;
+        const double* act = prm.act + (size_t)env * prm.act_stride;
         for (int e = t; e < Ed; e += G) {
             ek[e] = __ldg(reinterpret_cast<const double*>(db + H.o_ek) + e);
             double l0 = __ldg(reinterpret_cast<const double*>(db + H.o_el0) + e);
@@ -636,18 +640,29 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
     // ---------------------------------------------------------------- stage out
     {
         double2* g2 = reinterpret_cast<double2*>(gstate);
-        for (int i = t; i < Pd; i += G) {
-            g2[i] = pos[i];
-            g2[Pd + i] = vel[i];
-            g2[2 * Pd + i] = last[i];
-            g2[3 * Pd + i] = vt[i];
+        if (unstable && prm.auto_reset) {
+            // Sim::revert(0) in place (Environment.cpp:247-263): pos, vel <- snapshot; pos_last = pos; vel_true = vel
+            const double2* s0 = reinterpret_cast<const double2*>(prm.state0 + ed.state_off);
+            for (int i = t; i < Pd; i += G) {
+                const double2 p0 = s0[i], v0 = s0[Pd + i];
+                g2[i] = p0; g2[Pd + i] = v0; g2[2 * Pd + i] = p0; g2[3 * Pd + i] = v0;
+            }
+        } else {
+            for (int i = t; i < Pd; i += G) {
+                g2[i] = pos[i];
+                g2[Pd + i] = vel[i];
+                g2[2 * Pd + i] = last[i];
+                g2[3 * Pd + i] = vt[i];
+            }
         }
         double* ggoal = gstate + 8 * (size_t)Pd;
         for (int e = t; e < Ed; e += G) ggoal[e] = goal[e];
         if (overflow) atomicOr(prm.err + env, 1);
         if (t == 0) {
             prm.unstable[env] = (uint8_t)unstable;
-            prm.sim_time[env] += completed_steps;
+            if (unstable && prm.auto_reset) prm.sim_time[env] = 0;
+            else prm.sim_time[env] += completed_steps;
+            if (unstable) atomicAdd(prm.unstable_events, 1ull);
         }
     }
 }
