@@ -53,11 +53,23 @@ constexpr uint32_t kCodeCount = 1u << 25;     // pair table: robot self pair wit
 constexpr uint32_t kCodeStatic = 1u << 25;    // candidate list: leaf b is a static leaf
 constexpr int kCodeObjShift = 26;
 
+// narrow-phase item code: one corner of leaf `main` against leaf `ref`
+//   bits 0-11 main leaf, 12-23 ref leaf, 24-25 corner (TL,TR,BR,BL), 26 main is static, 27 ref is static,
+//   28 both leaves in one object (every contact counts twice)
+constexpr uint32_t kItemMainStatic = 1u << 26;
+constexpr uint32_t kItemRefStatic = 1u << 27;
+constexpr uint32_t kItemSameObj = 1u << 28;
+constexpr int kItemCornerShift = 24;
+
+// per-edge flags (design blob / shared memory)
+constexpr uint8_t kEdgeRigidCell = 1;         // side of a CELL_RIGID voxel: visited by the ordered rigid pass
+
 struct DesignHeader {        // 128 bytes
     int Pd, Ed, n_leaf, n_obj, n_pairs, n_rlev, n_rvis, n_act;
     int cand_cap, o_mass, o_ek, o_el0, o_ea, o_eb, o_eact, o_fixed;
     int o_csro, o_csre, o_leaf, o_obj, o_pairs, o_rlev, o_rvis, total;
-    int reserved[8];
+    int n_items, o_items, o_eflag;
+    int reserved[5];
 };
 static_assert(sizeof(DesignHeader) == 128, "DesignHeader must be 128 bytes");
 
@@ -81,11 +93,12 @@ MEVO_HD int align16(int x) { return (x + 15) & ~15; }
 struct SmemLayout {
     int o_pos, o_vel, o_last, o_vt, o_cf, o_spos, o_svel, o_accp, o_accv;
     int o_mass, o_ek, o_el0, o_leq, o_goal, o_ef, o_aabb, o_leaf;
-    int o_ea, o_eb, o_csro, o_csre, o_fixed, o_cand, o_misc, total;
+    int o_ea, o_eb, o_csro, o_csre, o_fixed, o_eflag, o_cand, o_surv, o_misc, total;
 };
 
 constexpr int kMiscInts = 64;   // [0..15] per-warp candidate counts, [16..23] self-collision counts,
-                                // [24] unstable, [25] overflow, [32..47] per-warp contact masks
+                                // [24] constraint-violation flag, [32..47] per-warp contact masks,
+                                // [48..63] per-warp survivor counts
 
 MEVO_HD SmemLayout smem_layout(int Pd, int Ed, int n_leaf, int cand_cap) {
     SmemLayout L;
@@ -112,7 +125,9 @@ MEVO_HD SmemLayout smem_layout(int Pd, int Ed, int n_leaf, int cand_cap) {
     L.o_csro = o; o += align16(2 * (Pd + 1));
     L.o_csre = o; o += align16(4 * Ed);
     L.o_fixed = o; o += align16(Pd);
+    L.o_eflag = o; o += align16(Ed);
     L.o_cand = o; o += align16(4 * cand_cap);
+    L.o_surv = o; o += align16(4 * cand_cap);
     L.o_misc = o; o += 4 * kMiscInts;
     L.total = align16(o);
     return L;

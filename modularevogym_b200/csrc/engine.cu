@@ -276,11 +276,34 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     }
     if ((int)objrecs.size() > kMaxDynObjects) throw std::runtime_error("too many dynamic objects in one environment (max 8)");
     if ((int)leaves.size() > kMaxLeaves) throw std::runtime_error("too many surface voxels in one environment (max 4095)");
-    std::vector<uint32_t> pairs;
+    // Leaf pairs inside one object that share a point ALWAYS have overlapping boxes (both boxes contain
+    // the shared point), so they are candidates in every substep: they are not tested; their non-shared
+    // corners are listed once as narrow-phase items.  Every other pair goes to the tested pair table.
+    std::vector<uint32_t> pairs, items;
+    e.always_pairs.clear();
+    auto shares_point = [&](const LeafRec& x, const LeafRec& y) {
+        for (int i = 0; i < 4; i++)
+            for (int j = 0; j < 4; j++)
+                if (x.pt[i] == y.pt[j]) return true;
+        return false;
+    };
     for (size_t a = 0; a < leaves.size(); a++)
         for (size_t b = a + 1; b < leaves.size(); b++) {
+            const bool same = leaf_obj_slot[a] == leaf_obj_slot[b];
+            if (same && shares_point(leaves[a], leaves[b])) {
+                e.always_pairs.push_back((int)a); e.always_pairs.push_back((int)b);
+                for (int dir = 0; dir < 2; dir++) {
+                    const size_t m = dir ? b : a, r = dir ? a : b;
+                    for (int c = 0; c < 4; c++) {
+                        bool shared = false;
+                        for (int j = 0; j < 4; j++) shared |= leaves[m].pt[c] == leaves[r].pt[j];
+                        if (!shared) items.push_back((uint32_t)m | ((uint32_t)r << 12) | ((uint32_t)c << kItemCornerShift) | kItemSameObj);
+                    }
+                }
+                continue;
+            }
             uint32_t code = (uint32_t)a | ((uint32_t)b << 12);
-            if (leaf_obj_slot[a] == leaf_obj_slot[b]) {
+            if (same) {
                 code |= kCodeSameObj;
                 const int dx = std::abs(leaves[a].gx - leaves[b].gx), dy = std::abs(leaves[a].gy - leaves[b].gy);
                 if (objrecs[leaf_obj_slot[a]].is_robot && !(dx <= 1 && dy <= 1)) code |= kCodeCount;   // PhysicsEngine.cpp:856-863
@@ -288,6 +311,14 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
             }
             pairs.push_back(code);
         }
+    // per-edge flags
+    std::vector<uint8_t> eflag(Ed, 0);
+    for (int o = 0; o < n_obj; o++) {
+        if (!dyn[o]) continue;
+        for (const Boxel& b : W.objects[o].boxels)
+            if (b.cell_type == CELL_RIGID)
+                for (int q = 0; q < 4; q++) eflag[e.edge_local[b.ed[q]]] |= kEdgeRigidCell;
+    }
     // rigid-cell visit schedule: reference order = object, boxel, (top,right,bot,left); levels = point-disjoint
     std::vector<uint16_t> rlev(1, 0), rvis;
     {
@@ -317,7 +348,9 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.n_leaf = (int)leaves.size();
     H.n_obj = (int)objrecs.size();
     H.n_pairs = (int)pairs.size();
-    H.cand_cap = ((std::max(128, 16 * H.n_leaf) + 15) / 16) * 16;
+    H.n_items = (int)items.size();
+    // per-warp segments of the candidate / survivor lists must hold at least two 32-wide chunks
+    H.cand_cap = ((std::max(std::max(128, 16 * H.n_leaf), 64 * (kGroupSizes[class_for(Pd, Ed)] / 32)) + 15) / 16) * 16;
 
     H.o_mass = dw.begin_section(); dw.put_array(mass);
     H.o_ek = dw.begin_section(); dw.put_array(ek);
@@ -333,6 +366,8 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.o_pairs = dw.begin_section(); dw.put_array(pairs);
     H.o_rlev = dw.begin_section(); dw.put_array(rlev);
     H.o_rvis = dw.begin_section(); dw.put_array(rvis);
+    H.o_items = dw.begin_section(); dw.put_array(items);
+    H.o_eflag = dw.begin_section(); dw.put_array(eflag);
     H.total = dw.begin_section();
     std::memcpy(design.data(), &H, sizeof(H));
 
@@ -908,14 +943,24 @@ int Batch::read_candidates(int env, int* out_pairs, int cap) {
     const int m = std::min(n, cand_cap_);
     std::vector<unsigned int> codes(m);
     if (m) CUDA_CHECK(cudaMemcpy(codes.data(), d_cand_ + (size_t)env * cand_cap_, sizeof(unsigned int) * m, cudaMemcpyDeviceToHost));
-    for (int i = 0; i < m && i < cap; i++) {
+    int w = 0;
+    for (int i = 0; i < m && w < cap; i++, w++) {
         const unsigned c = codes[i];
         int oa, ba, ob, bb;
         leaf_info(env, 1, (int)(c & kCodeLeafMask), &oa, &ba);
         leaf_info(env, (c & kCodeStatic) ? 0 : 1, (int)((c >> 12) & kCodeLeafMask), &ob, &bb);
-        out_pairs[4 * i] = oa; out_pairs[4 * i + 1] = ba; out_pairs[4 * i + 2] = ob; out_pairs[4 * i + 3] = bb;
+        out_pairs[4 * w] = oa; out_pairs[4 * w + 1] = ba; out_pairs[4 * w + 2] = ob; out_pairs[4 * w + 3] = bb;
     }
-    return n;
+    // pairs of leaves that share a point are candidates in every substep by construction (their boxes both
+    // contain the shared point); the kernel never tests them, so they are appended here
+    const std::vector<int>& ap = envs_.at(env).always_pairs;
+    for (size_t i = 0; i + 1 < ap.size() && w < cap; i += 2, w++) {
+        int oa, ba, ob, bb;
+        leaf_info(env, 1, ap[i], &oa, &ba);
+        leaf_info(env, 1, ap[i + 1], &ob, &bb);
+        out_pairs[4 * w] = oa; out_pairs[4 * w + 1] = ba; out_pairs[4 * w + 2] = ob; out_pairs[4 * w + 3] = bb;
+    }
+    return n + (int)ap.size() / 2;
 }
 
 int Batch::error_flags(int env) {

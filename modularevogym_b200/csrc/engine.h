@@ -24,6 +24,7 @@ struct EnvHost {
     std::vector<int> edge_local;     // global edge  -> dynamic local id, or -1
     std::vector<int> dyn_points;     // dynamic local id -> global point
     std::vector<int> dyn_edges;      // dynamic local id -> global edge
+    std::vector<int> always_pairs;   // dynamic leaf pairs (a, b, a, b, ...) that share a point: candidates in every substep
     std::vector<int> act_slot_obj;   // action slot -> object index
     std::vector<int> act_slot_boxel; // action slot -> boxel index in that object
     int design_id = -1, static_id = -1;

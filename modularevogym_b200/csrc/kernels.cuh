@@ -69,6 +69,19 @@ __device__ __forceinline__ void group_sync(int grp) {
     }
 }
 
+// group-wide OR of a per-thread predicate (uniform result); `slot` is a shared-memory word of the group
+template <int G, int EPC>
+__device__ __forceinline__ bool group_any(int grp, bool pred, volatile int* slot) {
+    if (G == 32) return __any_sync(0xffffffffu, pred) != 0;
+    if ((threadIdx.x % G) == 0) *slot = 0;
+    group_sync<G, EPC>(grp);
+    if (__any_sync(0xffffffffu, pred) && (threadIdx.x & 31) == 0) *slot = 1;
+    group_sync<G, EPC>(grp);
+    const bool r = *slot != 0;
+    group_sync<G, EPC>(grp);
+    return r;
+}
+
 __device__ __forceinline__ bool aabb_overlap(const double4& a, const double4& b) {
     // BoundingBox::in, main.h:64-72 (closed intervals, F_ERROR_TOL = 0); (x,y,z,w) = (minx,miny,maxx,maxy)
     if (a.x > b.z || a.z < b.x) return false;
@@ -80,6 +93,22 @@ __device__ __forceinline__ double4 ldg_d4(const double4* p) {
     const double2 lo = __ldg(reinterpret_cast<const double2*>(p));
     const double2 hi = __ldg(reinterpret_cast<const double2*>(p) + 1);
     return make_double4(lo.x, lo.y, hi.x, hi.y);
+}
+
+// necessary condition of Boxel::point_in_boxel: both triangles lie inside the box of the four corners
+__device__ __forceinline__ bool point_in_box(const double2 p, const double4& b) {
+    return p.x >= b.x && p.x <= b.z && p.y >= b.y && p.y <= b.w;
+}
+
+__device__ __forceinline__ void load_leaf(LeafRec& out, const LeafRec* dyn_leaf, const LeafRec* st_leaf, unsigned id, bool is_static) {
+    uint4* d = reinterpret_cast<uint4*>(&out);
+    if (is_static) {
+        const uint4* g = reinterpret_cast<const uint4*>(st_leaf + id);
+        d[0] = __ldg(g); d[1] = __ldg(g + 1);
+    } else {
+        const uint4* g = reinterpret_cast<const uint4*>(dyn_leaf + id);
+        d[0] = g[0]; d[1] = g[1];
+    }
 }
 
 __device__ __forceinline__ double cross2(double ax, double ay, double bx, double by) {
@@ -141,10 +170,9 @@ struct Contact {
 // corner = index of p in main's TL,TR,BR,BL list.  Returns false when no contact results.
 __device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const LeafRec& mainb, bool main_static,
                                                     const LeafRec& refb, bool ref_static, int corner, Contact& c) {
+    // corners shared with refb (PhysicsEngine.cpp:895-901) never reach this function: the host lists only the
+    // non-shared corners of point-sharing leaf pairs, and no other pair shares a point
     const int p = mainb.pt[corner];
-    if (main_static == ref_static) {           // shared points only exist inside one object (PhysicsEngine.cpp:895-901)
-        if (p == refb.pt[0] || p == refb.pt[1] || p == refb.pt[2] || p == refb.pt[3]) return false;
-    }
     const double2 pp = src.pos(p, main_static);
     const double2 rtl = src.pos(refb.pt[0], ref_static), rtr = src.pos(refb.pt[1], ref_static);
     const double2 rbr = src.pos(refb.pt[2], ref_static), rbl = src.pos(refb.pt[3], ref_static);
@@ -284,6 +312,8 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
     uint16_t* csre = reinterpret_cast<uint16_t*>(sm + L.o_csre);
     uint8_t* fixedp = reinterpret_cast<uint8_t*>(sm + L.o_fixed);
     unsigned int* cand = reinterpret_cast<unsigned int*>(sm + L.o_cand);
+    unsigned int* surv = reinterpret_cast<unsigned int*>(sm + L.o_surv);
+    uint8_t* eflag = reinterpret_cast<uint8_t*>(sm + L.o_eflag);
     volatile int* misc = reinterpret_cast<volatile int*>(sm + L.o_misc);
     const int seg_cap = H.cand_cap / NW;
 
@@ -306,6 +336,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             ek[e] = __ldg(reinterpret_cast<const double*>(db + H.o_ek) + e);
             double l0 = __ldg(reinterpret_cast<const double*>(db + H.o_el0) + e);
             el0[e] = l0;
+            eflag[e] = __ldg(db + H.o_eflag + e);
             ea[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_ea) + e);
             eb[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_eb) + e);
             double g = ggoal[e];
@@ -333,6 +364,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
 
     const ObjRec* objs = reinterpret_cast<const ObjRec*>(db + H.o_obj);
     const unsigned int* pairs = reinterpret_cast<const unsigned int*>(db + H.o_pairs);
+    const unsigned int* items = reinterpret_cast<const unsigned int*>(db + H.o_items);
     const uint16_t* rlev = reinterpret_cast<const uint16_t*>(db + H.o_rlev);
     const uint16_t* rvis = reinterpret_cast<const uint16_t*>(db + H.o_rvis);
     PointSrc src;
@@ -393,10 +425,13 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                     double4 bb = make_double4(0, 0, 0, 0);
                     if (l < n_leaf) {
                         bb = aabb[l];
-                        cx0 = max((int)floor(bb.x / MEVO_CELL) - 1 - SH.gx0, 0);
-                        int cx1 = min((int)floor(bb.z / MEVO_CELL) + 1 - SH.gx0, SH.gw - 1);
-                        cy0 = max((int)floor(bb.y / MEVO_CELL) - 1 - SH.gy0, 0);
-                        int cy1 = min((int)floor(bb.w / MEVO_CELL) + 1 - SH.gy0, SH.gh - 1);
+                        // static leaf in lattice cell c spans [c, c+1] * 0.1 (to ~1e-15): the closed-interval test
+                        // can only succeed for ceil(min*10 - 1) <= c <= floor(max*10); 1e-6 cells of slack, then
+                        // the exact test below decides
+                        cx0 = max((int)ceil(bb.x * 10.0 - 1.000001) - SH.gx0, 0);
+                        int cx1 = min((int)floor(bb.z * 10.0 + 0.000001) - SH.gx0, SH.gw - 1);
+                        cy0 = max((int)ceil(bb.y * 10.0 - 1.000001) - SH.gy0, 0);
+                        int cy1 = min((int)floor(bb.w * 10.0 + 0.000001) - SH.gy0, SH.gh - 1);
                         wx = cx1 - cx0 + 1;
                         const int wy = cy1 - cy0 + 1;
                         n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
@@ -435,61 +470,112 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                 if (t == 0) prm.dbg_cand_n[env] = off;
             }
 
-            // ======================================================= K3: narrow phase + contact response (a-5, a-6)
-            for (int w = 0; w < NW; w++) {
-                const int n_items = misc[w] * 8;      // candidate x {a->b, b->a} x 4 corners
-                for (int base = 0; base < n_items; base += G) {
-                    const int i = base + t;
-                    bool has = false;
-                    Contact c;
-                    int reps = 1;
-                    if (i < n_items) {
-                        const unsigned code = cand[w * seg_cap + (i >> 3)];
-                        const int a = code & kCodeLeafMask, b = (code >> 12) & kCodeLeafMask;
-                        const bool b_static = (code & kCodeStatic) != 0;
-                        reps = (code & kCodeSameObj) ? 2 : 1;
-                        const LeafRec la = leaf[a];
-                        LeafRec lb;
-                        if (b_static) {
-                            const uint4* g = reinterpret_cast<const uint4*>(st_leaf + b);
-                            uint4* d = reinterpret_cast<uint4*>(&lb);
-                            d[0] = __ldg(g); d[1] = __ldg(g + 1);
-                        } else {
-                            lb = leaf[b];
-                        }
+            // ======================================================= K3a: narrow-phase filter
+            // A corner can only lie inside a boxel (Boxel::point_in_boxel) if it lies inside the boxel's
+            // bounding box, so every (corner, boxel) item is first tested against the box (4 compares) and
+            // only the survivors -- real or near penetrations, a handful per substep -- reach the resolver.
+            // Survivors are collected in rounds of at most seg_cap per warp (one round in practice; a collapsed
+            // robot with hundreds of simultaneous penetrations takes several) so the list can never overflow.
+            unsigned int* mysurv = surv + warp * seg_cap;
+            int next_ic = warp;          // next 32-wide chunk of the always-items owned by this warp
+            int next_cc = 0;             // next 32-wide chunk of this warp's own candidate corners
+            __syncwarp();
+            bool more;
+            do {
+            int scnt = 0;
+            while (scnt + 32 <= seg_cap) {
+                bool hit = false;
+                unsigned int code = 0;
+                if (next_ic * 32 < H.n_items) {
+                    // (i) corners of leaf pairs that share a point (always candidates, never tested in K2b)
+                    const int i = next_ic * 32 + lane;
+                    next_ic += NW;
+                    if (i < H.n_items) {
+                        code = __ldg(items + i);
+                        const int p = leaf[code & kCodeLeafMask].pt[(code >> kItemCornerShift) & 3];
+                        hit = point_in_box(pos[p], aabb[(code >> 12) & kCodeLeafMask]);
+                    }
+                } else if (next_cc * 32 < cnt * 8) {
+                    // (ii) the 8 corners of this warp's own candidates (no point is shared by these pairs)
+                    const int i = next_cc * 32 + lane;
+                    next_cc++;
+                    if (i < cnt * 8) {
+                        const unsigned int cc = myseg[i >> 3];
+                        const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
+                        const bool b_static = (cc & kCodeStatic) != 0;
                         const int dir = (i >> 2) & 1, corner = i & 3;
-                        if (dir == 0) has = resolve_point_vs_boxel(src, la, false, lb, b_static, corner, c);
-                        else has = resolve_point_vs_boxel(src, lb, b_static, la, false, corner, c);
-                    }
-                    // deterministic, race-free accumulation: warps in order, lanes in order
-                    unsigned m = __ballot_sync(0xffffffffu, has);
-                    if (NW == 1) {
-                        while (m) {
-                            const int l = __ffs(m) - 1;
-                            if (lane == l) apply_contact(cf, c, reps);
-                            m &= m - 1;
-                            __syncwarp();
+                        const unsigned same = (cc & kCodeSameObj) ? kItemSameObj : 0u;
+                        if (dir == 0) {
+                            code = a | (b << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
+                            const double4 bb = b_static ? ldg_d4(st_aabb + b) : aabb[b];
+                            hit = point_in_box(pos[leaf[a].pt[corner]], bb);
+                        } else {
+                            code = b | (a << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
+                            const double2 pp = b_static ? __ldg(st_pos + __ldg(&st_leaf[b].pt[corner])) : pos[leaf[b].pt[corner]];
+                            hit = point_in_box(pp, aabb[a]);
                         }
-                    } else {
-                        if (lane == 0) misc[32 + warp] = (int)m;
-                        group_sync<G, EPC>(grp);
-                        for (int w2 = 0; w2 < NW; w2++) {
-                            unsigned m2 = (unsigned)misc[32 + w2];
-                            if (m2 == 0) continue;           // uniform across the group
-                            if (warp == w2) {
-                                while (m2) {
-                                    const int l = __ffs(m2) - 1;
-                                    if (lane == l) apply_contact(cf, c, reps);
-                                    m2 &= m2 - 1;
-                                    __syncwarp();
-                                }
+                    }
+                } else {
+                    break;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) mysurv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
+                scnt += __popc(m);
+            }
+            more = (next_ic * 32 < H.n_items) || (next_cc * 32 < cnt * 8);
+            if (lane == 0) misc[48 + warp] = scnt;
+            group_sync<G, EPC>(grp);
+
+            // ======================================================= K3b: resolve + contact response (a-5, a-6)
+            int n_surv = 0;
+#pragma unroll
+            for (int w = 0; w < NW; w++) n_surv += misc[48 + w];
+            for (int base = 0; base < n_surv; base += G) {
+                int i = base + t;
+                bool has = false;
+                Contact c;
+                int reps = 1;
+                if (i < n_surv) {
+                    int w = 0;
+                    while (i >= misc[48 + w]) { i -= misc[48 + w]; w++; }
+                    const unsigned code = surv[w * seg_cap + i];
+                    const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
+                    reps = (code & kItemSameObj) ? 2 : 1;
+                    LeafRec lm, lr;
+                    load_leaf(lm, leaf, st_leaf, code & kCodeLeafMask, m_static);
+                    load_leaf(lr, leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
+                    has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
+                }
+                // deterministic, race-free accumulation: warps in order, lanes in order
+                unsigned m = __ballot_sync(0xffffffffu, has);
+                if (NW == 1) {
+                    while (m) {
+                        const int l = __ffs(m) - 1;
+                        if (lane == l) apply_contact(cf, c, reps);
+                        m &= m - 1;
+                        __syncwarp();
+                    }
+                } else {
+                    if (lane == 0) misc[32 + warp] = (int)m;
+                    group_sync<G, EPC>(grp);
+                    for (int w2 = 0; w2 < NW; w2++) {
+                        unsigned m2 = (unsigned)misc[32 + w2];
+                        if (m2 == 0) continue;           // uniform across the group
+                        if (warp == w2) {
+                            while (m2) {
+                                const int l = __ffs(m2) - 1;
+                                if (lane == l) apply_contact(cf, c, reps);
+                                m2 &= m2 - 1;
+                                __syncwarp();
                             }
-                            group_sync<G, EPC>(grp);
                         }
-                        group_sync<G, EPC>(grp);             // masks are rewritten in the next round
+                        group_sync<G, EPC>(grp);
                     }
+                    group_sync<G, EPC>(grp);             // masks are rewritten in the next round
                 }
             }
+            if (NW == 1) __syncwarp(); else group_sync<G, EPC>(grp);
+            } while (group_any<G, EPC>(grp, more, misc + 25));
             // K6a: unstable test uses the boxes of the START of this substep (a-12)
             int sub_unstable = 0;
             for (int o = 0; o < H.n_obj; o++) {
@@ -575,6 +661,21 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             }
 
             // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
+            // Fast path: the limiters only act beyond +-25 % strain (+-3 % on the sides of rigid voxels).  One
+            // sqrt per edge decides, with a 1e-7 relative guard band so that the decision never depends on the
+            // rounding of dist / L0; inside the band every correction of the reference is exactly zero and the
+            // positions are left untouched, which is what the reference computes.  Otherwise: the exact passes.
+            bool viol = false;
+            for (int e = t; e < Ed; e += G) {
+                const double2 pa = pos[ea[e]], pb = pos[eb[e]];
+                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                const double dist = sqrt(dx * dx + dy * dy);
+                const double l0 = el0[e];
+                const bool rigid = (eflag[e] & kEdgeRigidCell) != 0;
+                const double lo = rigid ? 0.9700001 : 0.7500001, hi = rigid ? 1.0299999 : 1.2499999;
+                if (!(dist > l0 * lo && dist < l0 * hi)) viol = true;
+            }
+            if (group_any<G, EPC>(grp, viol, misc + 24)) {
             for (int e = t; e < Ed; e += G) {
                 const double2 pa = pos[ea[e]], pb = pos[eb[e]];
                 const double dx = pa.x - pb.x, dy = pa.y - pb.y;
@@ -625,6 +726,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                 }
                 group_sync<G, EPC>(grp);
             }
+            }   // exact passes
             for (int p = t; p < Pd; p += G) {             // PhysicsEngine::update_true_vel (:602-607)
                 const double2 x = pos[p], l = last[p];
                 vt[p] = make_double2((x.x - l.x) / MEVO_DT, (x.y - l.y) / MEVO_DT);
