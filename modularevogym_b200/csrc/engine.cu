@@ -101,7 +101,8 @@ struct Batch::Impl {
     std::vector<size_t> class_off;                // per class: offset into d_class_envs_
     std::vector<EnvDesc> desc;
     std::vector<std::vector<double>> pos0, vel0;  // reset snapshot (global numbering)
-    int epc32 = 2;
+    int epc32 = 12;
+    int cta_sync = 1;
     int* d_com_ranges = nullptr;
     double* d_com_out = nullptr;
     int com_obj = -1;
@@ -117,8 +118,9 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     stream_ = s;
     if (const char* e = std::getenv("MEVO_EPC32")) {
         int v = std::atoi(e);
-        if (v == 1 || v == 2 || v == 4) impl_->epc32 = v;
+        if (v == 1 || v == 2 || v == 4 || v == 6 || v == 12) impl_->epc32 = v;
     }
+    if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
 }
 
 Batch::~Batch() {
@@ -789,6 +791,7 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.n_steps = n_steps;
     prm.n_substeps = n_substeps;
     prm.apply_actions = apply_actions ? 1 : 0;
+    prm.cta_sync = impl_->cta_sync;
     prm.unstable = d_unstable_;
     prm.sim_time = d_time_;
     prm.err = d_err_;
@@ -804,11 +807,16 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         prm.n_class_envs = n;
         prm.smem_per_env = impl_->class_smem[c];
         switch (c) {
-            case 0:
-                if (impl_->epc32 == 4 && 4 * prm.smem_per_env <= kMaxSmemPerBlock) launch_step<32, 4>(prm, prm.smem_per_env, st);
-                else if (impl_->epc32 == 1) launch_step<32, 1>(prm, prm.smem_per_env, st);
-                else launch_step<32, 2>(prm, prm.smem_per_env, st);
+            case 0: {
+                // largest environments-per-CTA <= the configured one that fits in shared memory
+                const int want = impl_->epc32, sz = prm.smem_per_env;
+                if (want >= 12 && 12 * sz <= kMaxSmemPerBlock) launch_step<32, 12>(prm, sz, st);
+                else if (want >= 6 && 6 * sz <= kMaxSmemPerBlock) launch_step<32, 6>(prm, sz, st);
+                else if (want >= 4 && 4 * sz <= kMaxSmemPerBlock) launch_step<32, 4>(prm, sz, st);
+                else if (want >= 2 && 2 * sz <= kMaxSmemPerBlock) launch_step<32, 2>(prm, sz, st);
+                else launch_step<32, 1>(prm, sz, st);
                 break;
+            }
             case 1: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
             case 2: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
             case 3: launch_step<256, 1>(prm, prm.smem_per_env, st); break;

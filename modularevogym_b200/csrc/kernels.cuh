@@ -38,6 +38,7 @@ struct StepParams {
     int n_steps;
     int n_substeps;
     int apply_actions;
+    int cta_sync;               // 1: CTA barrier once per substep (multi-environment CTAs)
     uint8_t* unstable;
     int* sim_time;
     int* err;
@@ -270,8 +271,11 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
     const int t = threadIdx.x % G;
     const int lane = threadIdx.x & 31;
     const int warp = t >> 5;
-    const int slot = blockIdx.x * EPC + grp;
-    if (slot >= prm.n_class_envs) return;     // whole group leaves together
+    int slot = blockIdx.x * EPC + grp;
+    // a group beyond the end of the list shadows the last environment (same work, nothing written back) so that
+    // every warp of the CTA reaches the per-substep CTA barrier
+    const bool ghost = slot >= prm.n_class_envs;
+    if (ghost) slot = prm.n_class_envs - 1;
     const int env = prm.class_envs[slot];
     const EnvDesc ed = prm.envs[env];
     const uint8_t* db = prm.design + ed.design_off;
@@ -374,8 +378,12 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
     int completed_steps = 0;
     bool overflow = false;
 
-    for (int step = 0; step < prm.n_steps && !unstable; step++) {
+    for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
+            // Warps of one CTA are kept within one substep of each other: they then run the same code at about
+            // the same time and share its instruction-cache lines (the loop body is far larger than the I-cache).
+            if (EPC > 1 && prm.cta_sync) __syncthreads();
+            if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110); only keeps the barrier
             // ======================================================= K2a: leaf AABB refit (a-4)
             for (int l = t; l < n_leaf; l += G) {
                 const LeafRec r = leaf[l];
@@ -393,6 +401,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             if (t < 8) misc[16 + t] = 0;
             group_sync<G, EPC>(grp);
 
+            if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K2b: broad phase + compaction (a-4, a-12)
             int cnt = 0;     // warp-uniform number of candidates in this warp's segment
             unsigned int* myseg = cand + warp * seg_cap;
@@ -459,7 +468,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             if (lane == 0) misc[warp] = cnt;
             group_sync<G, EPC>(grp);
 
-            if (prm.dbg_cand && step == 0 && sub == 0) {
+            if (prm.dbg_cand && step == 0 && sub == 0 && !ghost) {
                 int off = 0;
                 for (int w = 0; w < NW; w++) {
                     const int c = misc[w];
@@ -470,6 +479,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                 if (t == 0) prm.dbg_cand_n[env] = off;
             }
 
+            if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K3a: narrow-phase filter
             // A corner can only lie inside a boxel (Boxel::point_in_boxel) if it lies inside the boxel's
             // bounding box, so every (corner, boxel) item is first tested against the box (4 compares) and
@@ -584,6 +594,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             }
             group_sync<G, EPC>(grp);
 
+            if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K4: actuators + RK4 (a-7, a-8, a-9)
             for (int e = t; e < Ed; e += G) {
                 const double2 pa = pos[ea[e]], pb = pos[eb[e]];
@@ -595,6 +606,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             // leq[e] is written and read by the same thread (same striding): no barrier needed
 #pragma unroll 1
             for (int s = 0; s < 4; s++) {
+                if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
                 const double2* sp = (s == 0) ? pos : spos;
                 const double2* sv = (s == 0) ? vel : svel;
                 for (int e = t; e < Ed; e += G) {
@@ -660,6 +672,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                 group_sync<G, EPC>(grp);
             }
 
+            if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
             // Fast path: the limiters only act beyond +-25 % strain (+-3 % on the sides of rigid voxels).  One
             // sqrt per edge decides, with a 1e-7 relative guard band so that the decision never depends on the
@@ -734,13 +747,13 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             }
             group_sync<G, EPC>(grp);
 
-            if (sub_unstable) { unstable = 1; break; }    // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
+            if (sub_unstable) unstable = 1;               // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
         }
         if (!unstable) completed_steps++;
     }
 
     // ---------------------------------------------------------------- stage out
-    {
+    if (!ghost) {
         double2* g2 = reinterpret_cast<double2*>(gstate);
         if (unstable && prm.auto_reset) {
             // Sim::revert(0) in place (Environment.cpp:247-263): pos, vel <- snapshot; pos_last = pos; vel_true = vel
