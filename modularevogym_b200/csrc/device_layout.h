@@ -69,7 +69,8 @@ struct DesignHeader {        // 128 bytes
     int cand_cap, o_mass, o_ek, o_el0, o_ea, o_eb, o_eact, o_fixed;
     int o_csro, o_csre, o_leaf, o_obj, o_pairs, o_rlev, o_rvis, total;
     int n_items, o_items, o_eflag;
-    int reserved[5];
+    int max_deg, unit_mass, o_csr8, o_eidx;   // warp kernel: 8-slot gather records, packed edge end points
+    int reserved[1];
 };
 static_assert(sizeof(DesignHeader) == 128, "DesignHeader must be 128 bytes");
 

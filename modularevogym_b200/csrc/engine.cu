@@ -13,6 +13,7 @@
 #include <unordered_map>
 
 #include "kernels.cuh"
+#include "wkernel.cuh"
 
 namespace mevo {
 
@@ -26,16 +27,29 @@ namespace mevo {
 
 namespace {
 
-constexpr int kNumClasses = 5;
-const int kGroupSizes[kNumClasses] = {32, 64, 128, 256, 512};
+// size classes: 0, 1 = warp-per-environment kernel (wkernel.cuh) with compile-time capacities;
+// 2..6 = group-per-environment kernel (kernels.cuh) with 32..512 threads per environment
+constexpr int kNumClasses = 7;
+constexpr int kFirstGroupClass = 2;
+const int kGroupSizes[kNumClasses] = {32, 32, 32, 64, 128, 256, 512};
 constexpr int kMaxSmemPerBlock = 227 * 1024;
+using WarpSmemA = WarpSmem<40, 112, 16>;     // one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...)
+using WarpSmemB = WarpSmem<64, 160, 32>;     // 5x5 robot + a small free object (Pusher-v0, Thrower-v0, Carrier-v0)
 
-int class_for(int Pd, int Ed) {
-    if (Ed <= 160 && Pd <= 64) return 0;
-    if (Ed <= 400 && Pd <= 160) return 1;
-    if (Ed <= 900 && Pd <= 320) return 2;
-    if (Ed <= 1800 && Pd <= 640) return 3;
-    return 4;
+int group_class_for(int Pd, int Ed) {
+    if (Ed <= 160 && Pd <= 64) return 2;
+    if (Ed <= 400 && Pd <= 160) return 3;
+    if (Ed <= 900 && Pd <= 320) return 4;
+    if (Ed <= 1800 && Pd <= 640) return 5;
+    return 6;
+}
+
+int class_for(const DesignHeader& H, bool use_warp_kernel) {
+    if (use_warp_kernel && H.max_deg <= 8 && H.unit_mass && H.n_obj <= 8) {
+        if (H.Pd <= 40 && H.Ed <= 112 && H.n_leaf <= 16) return 0;
+        if (H.Pd <= 64 && H.Ed <= 160 && H.n_leaf <= 32) return 1;
+    }
+    return group_class_for(H.Pd, H.Ed);
 }
 
 uint64_t fnv1a(const std::vector<uint8_t>& v) {
@@ -75,6 +89,19 @@ void launch_step(const StepParams& prm, int smem_per_env, cudaStream_t stream) {
     step_kernel<G, EPC><<<grid, G * EPC, smem, stream>>>(prm);
 }
 
+template <int PCAP, int ECAP, int LCAP, int EPC, int MINB>
+void launch_wstep(const StepParams& prm, cudaStream_t stream) {
+    constexpr int smem = WarpSmem<PCAP, ECAP, LCAP>::kBytes * EPC;
+    static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
+    static bool configured = false;
+    if (!configured) {
+        CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, EPC, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    const int grid = (prm.n_class_envs + EPC - 1) / EPC;
+    wstep_kernel<PCAP, ECAP, LCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
+}
+
 __global__ void reset_kernel(double* state, const double* state0, const EnvDesc* envs, const uint8_t* design,
                              const int* env_ids, int n, int* sim_time, uint8_t* unstable) {
     // Environment::revert_to_snapshot(0) (Environment.cpp:247-263): pos, vel <- snapshot; pos_last <- pos;
@@ -101,6 +128,8 @@ struct Batch::Impl {
     std::vector<size_t> class_off;                // per class: offset into d_class_envs_
     std::vector<EnvDesc> desc;
     std::vector<std::vector<double>> pos0, vel0;  // reset snapshot (global numbering)
+    bool use_warp_kernel = true;
+    int wepc = 0;                                 // warp kernel: environments per CTA override (0 = default)
     int epc32 = 12;
     int cta_sync = 1;
     int* d_com_ranges = nullptr;
@@ -120,6 +149,8 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
         int v = std::atoi(e);
         if (v == 1 || v == 2 || v == 4 || v == 6 || v == 12) impl_->epc32 = v;
     }
+    if (const char* e = std::getenv("MEVO_NO_WKERNEL")) impl_->use_warp_kernel = std::atoi(e) == 0;
+    if (const char* e = std::getenv("MEVO_WEPC")) impl_->wepc = std::atoi(e);
     if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
 }
 
@@ -259,6 +290,18 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
         }
         csro[Pd] = (uint16_t)csre.size();
     }
+    // warp kernel: one 16-byte record per point (8 x u16 entries (edge << 1 | side), same order, 0xffff = empty)
+    // and one u32 per edge (a | b << 8 | flags << 16)
+    std::vector<uint16_t> csr8(8 * (size_t)Pd, 0xffff);
+    int max_deg = 0;
+    for (int i = 0; i < Pd; i++) {
+        const int deg = csro[i + 1] - csro[i];
+        max_deg = std::max(max_deg, deg);
+        for (int j = 0; j < deg && j < 8; j++) csr8[8 * (size_t)i + j] = csre[csro[i] + j];
+    }
+    H.max_deg = max_deg;
+    H.unit_mass = 1;
+    for (int i = 0; i < Pd; i++) if (mass[i] != 1.0) H.unit_mass = 0;
     // leaves, objects, pair table
     std::vector<LeafRec> leaves;
     std::vector<ObjRec> objrecs;
@@ -352,7 +395,7 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.n_pairs = (int)pairs.size();
     H.n_items = (int)items.size();
     // per-warp segments of the candidate / survivor lists must hold at least two 32-wide chunks
-    H.cand_cap = ((std::max(std::max(128, 16 * H.n_leaf), 64 * (kGroupSizes[class_for(Pd, Ed)] / 32)) + 15) / 16) * 16;
+    H.cand_cap = ((std::max(std::max(128, 16 * H.n_leaf), 64 * (kGroupSizes[group_class_for(Pd, Ed)] / 32)) + 15) / 16) * 16;
 
     H.o_mass = dw.begin_section(); dw.put_array(mass);
     H.o_ek = dw.begin_section(); dw.put_array(ek);
@@ -370,6 +413,10 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.o_rvis = dw.begin_section(); dw.put_array(rvis);
     H.o_items = dw.begin_section(); dw.put_array(items);
     H.o_eflag = dw.begin_section(); dw.put_array(eflag);
+    std::vector<uint32_t> eidx(Ed);
+    for (int k = 0; k < Ed; k++) eidx[k] = (uint32_t)(ea[k] & 0xff) | ((uint32_t)(eb[k] & 0xff) << 8) | ((uint32_t)eflag[k] << 16);
+    H.o_csr8 = dw.begin_section(); dw.put_array(csr8);
+    H.o_eidx = dw.begin_section(); dw.put_array(eidx);
     H.total = dw.begin_section();
     std::memcpy(design.data(), &H, sizeof(H));
 
@@ -470,11 +517,13 @@ void Batch::finalize() {
         sd = (sd + 1) & ~(size_t)1;
         state_doubles += sd;
         act_stride_ = std::max(act_stride_, e.n_act);
-        e.cls = class_for(H->Pd, H->Ed);
-        const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap);
-        if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
+        e.cls = class_for(*H, impl_->use_warp_kernel);
+        if (e.cls >= kFirstGroupClass) {
+            const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap);
+            if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
+            impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
+        }
         impl_->class_envs[e.cls].push_back(i);
-        impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
     }
     for (int i = 0; i < n; i++) impl_->desc[i].act_off = i * act_stride_;
 
@@ -807,7 +856,13 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         prm.n_class_envs = n;
         prm.smem_per_env = impl_->class_smem[c];
         switch (c) {
-            case 0: {
+            case 0:
+                if (impl_->wepc == 16) launch_wstep<40, 112, 16, 16, 1>(prm, st);
+                else if (impl_->wepc == 4) launch_wstep<40, 112, 16, 4, 4>(prm, st);
+                else launch_wstep<40, 112, 16, 8, 2>(prm, st);
+                break;
+            case 1: launch_wstep<64, 160, 32, 5, 2>(prm, st); break;
+            case 2: {
                 // largest environments-per-CTA <= the configured one that fits in shared memory
                 const int want = impl_->epc32, sz = prm.smem_per_env;
                 if (want >= 12 && 12 * sz <= kMaxSmemPerBlock) launch_step<32, 12>(prm, sz, st);
@@ -817,9 +872,9 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 else launch_step<32, 1>(prm, sz, st);
                 break;
             }
-            case 1: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
-            case 2: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
-            case 3: launch_step<256, 1>(prm, prm.smem_per_env, st); break;
+            case 3: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
+            case 4: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
+            case 5: launch_step<256, 1>(prm, prm.smem_per_env, st); break;
             default: launch_step<512, 1>(prm, prm.smem_per_env, st); break;
         }
         CUDA_CHECK(cudaGetLastError());

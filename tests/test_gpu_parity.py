@@ -31,6 +31,15 @@ def goldens():
     return [Golden(n) for n in NAMES]
 
 
+@pytest.fixture(params=["warp", "group"])
+def kernel_choice(request, monkeypatch):
+    """Small environments run in the warp-per-environment kernel (wkernel.cuh) by default; MEVO_NO_WKERNEL=1
+    (read when a batch is created) sends them through the group-per-environment kernel (kernels.cuh) like
+    the large ones.  Both must reproduce the reference."""
+    monkeypatch.setenv("MEVO_NO_WKERNEL", "0" if request.param == "warp" else "1")
+    return request.param
+
+
 def make_batch(goldens, cand_dump=0):
     B = capi.Batch(0)
     for g in goldens:
@@ -54,7 +63,7 @@ def test_topology_through_batch(goldens):
     B.close()
 
 
-def test_teacher_forced_substeps_and_candidates(goldens):
+def test_teacher_forced_substeps_and_candidates(goldens, kernel_choice):
     """Environment::step, one substep at a time, from the reference's own state."""
     B = make_batch(goldens, cand_dump=8192)
     n_sub = max(g.n_sub for g in goldens)
@@ -84,13 +93,13 @@ def test_teacher_forced_substeps_and_candidates(goldens):
                 want = pair_set(g[f"cand_{k}"], static, drop_self=True)
                 got = pair_set(B.read_candidates(i), static, drop_self=True)
                 assert got == want, (g.name, k, sorted(got - want)[:4], sorted(want - got)[:4])
-    print(f"\nteacher-forced: {exact}/{total} substeps bit-identical to the reference; worst rel err {worst}")
+    print(f"\n[{kernel_choice}] teacher-forced: {exact}/{total} substeps bit-identical to the reference; worst rel err {worst}")
     no_contact = sum(int((np.abs(g['sub_cf']).sum(axis=(1, 2)) == 0).sum()) for g in goldens)
     assert exact >= no_contact       # without contacts the result is bit-identical
     B.close()
 
 
-def test_free_running_steps(goldens):
+def test_free_running_steps(goldens, kernel_choice):
     """Sim::step for every fixture at once: 30 substeps per launch, actions through the per-env API;
     unstable flag and sim_time semantics (Sim.cpp:105-115)."""
     B = make_batch(goldens)
