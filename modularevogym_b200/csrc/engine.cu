@@ -33,7 +33,7 @@ constexpr int kNumClasses = 7;
 constexpr int kFirstGroupClass = 2;
 const int kGroupSizes[kNumClasses] = {32, 32, 32, 64, 128, 256, 512};
 constexpr int kMaxSmemPerBlock = 227 * 1024;
-using WarpSmemA = WarpSmem<40, 112, 16>;     // one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...)
+using WarpSmemA = WarpSmem<40, 112, 24>;     // one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...)
 using WarpSmemB = WarpSmem<64, 160, 32>;     // 5x5 robot + a small free object (Pusher-v0, Thrower-v0, Carrier-v0)
 
 int group_class_for(int Pd, int Ed) {
@@ -46,7 +46,7 @@ int group_class_for(int Pd, int Ed) {
 
 int class_for(const DesignHeader& H, bool use_warp_kernel) {
     if (use_warp_kernel && H.max_deg <= 8 && H.unit_mass && H.n_obj <= 8) {
-        if (H.Pd <= 40 && H.Ed <= 112 && H.n_leaf <= 16) return 0;
+        if (H.Pd <= 40 && H.Ed <= 112 && H.n_leaf <= 24) return 0;
         if (H.Pd <= 64 && H.Ed <= 160 && H.n_leaf <= 32) return 1;
     }
     return group_class_for(H.Pd, H.Ed);
@@ -857,9 +857,9 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         prm.smem_per_env = impl_->class_smem[c];
         switch (c) {
             case 0:
-                if (impl_->wepc == 16) launch_wstep<40, 112, 16, 16, 1>(prm, st);
-                else if (impl_->wepc == 4) launch_wstep<40, 112, 16, 4, 4>(prm, st);
-                else launch_wstep<40, 112, 16, 8, 2>(prm, st);
+                if (impl_->wepc == 16) launch_wstep<40, 112, 24, 16, 1>(prm, st);
+                else if (impl_->wepc == 4) launch_wstep<40, 112, 24, 4, 4>(prm, st);
+                else launch_wstep<40, 112, 24, 8, 2>(prm, st);
                 break;
             case 1: launch_wstep<64, 160, 32, 5, 2>(prm, st); break;
             case 2: {

@@ -19,7 +19,7 @@ namespace mevo {
 
 template <int PCAP, int ECAP, int LCAP>
 struct WarpSmem {
-    static constexpr int kCandCap = 16 * LCAP;     // tested-pair hits + static hits per substep
+    static constexpr int kCandCap = 64;            // overlapping pairs per round (two 32-wide chunks)
     static constexpr int kSurvCap = 64;            // survivors per round (two 32-wide chunks)
     static constexpr int o_pos = 0;
     static constexpr int o_spos = o_pos + 16 * PCAP;
@@ -210,7 +210,6 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
 
     int unstable = 0;
     int completed_steps = 0;
-    bool overflow = false;
     bool first_substep = true;
 
     for (int step = 0; step < prm.n_steps; step++) {
@@ -235,141 +234,150 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             if (lane < 8) misc[lane] = 0;
             __syncwarp();
 
-            // ======================================================= K2b: broad phase + compaction (a-4, a-12)
-            int cnt = 0;
-            for (int base = 0; base < n_pairs; base += 32) {
-                const int i = base + lane;
-                bool hit = false;
-                unsigned int code = 0;
-                if (i < n_pairs) {
-                    code = __ldg(pairs + i);
-                    hit = aabb_overlap(aabb[code & kCodeLeafMask], aabb[(code >> 12) & kCodeLeafMask]);
-                    if (hit && (code & kCodeCount)) atomicAdd((int*)&misc[code >> kCodeObjShift], 2);   // both ordered pairs (a-12)
-                }
-                const unsigned m = __ballot_sync(0xffffffffu, hit);
-                if (hit) {
-                    const int at = cnt + __popc(m & ((1u << lane) - 1u));
-                    if (at < S::kCandCap) cand[at] = code & (kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj);
-                    else overflow = true;
-                }
-                cnt += __popc(m);
-            }
-            if (has_static) {
-                const int gx0 = SHp->gx0, gy0 = SHp->gy0, gw = SHp->gw, gh = SHp->gh;
-                const int16_t* st_grid = reinterpret_cast<const int16_t*>(sb + SHp->o_grid);
-                int cx0 = 0, cy0 = 0, wx = 0, n_cells = 0;
-                double4 bb = make_double4(0, 0, 0, 0);
-                if (lane < n_leaf) {
-                    bb = aabb[lane];
-                    // static leaf in lattice cell c spans [c, c+1] * 0.1: only ceil(min*10 - 1) <= c <= floor(max*10)
-                    // can pass the closed-interval test; 1e-6 cells of slack, the exact test decides
-                    cx0 = max((int)ceil(bb.x * 10.0 - 1.000001) - gx0, 0);
-                    const int cx1 = min((int)floor(bb.z * 10.0 + 0.000001) - gx0, gw - 1);
-                    cy0 = max((int)ceil(bb.y * 10.0 - 1.000001) - gy0, 0);
-                    const int cy1 = min((int)floor(bb.w * 10.0 + 0.000001) - gy0, gh - 1);
-                    wx = cx1 - cx0 + 1;
-                    const int wy = cy1 - cy0 + 1;
-                    n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
-                }
-                const int max_cells = __reduce_max_sync(0xffffffffu, n_cells);
-                for (int it = 0; it < max_cells; it++) {
-                    bool hit = false;
-                    int s = -1;
-                    if (it < n_cells) {
-                        const int cx = cx0 + it % wx, cy = cy0 + it / wx;
-                        s = __ldg(st_grid + cy * gw + cx);
-                        if (s >= 0) hit = aabb_overlap(bb, ldg_d4(st_aabb + s));
-                    }
-                    const unsigned m = __ballot_sync(0xffffffffu, hit);
-                    if (hit) {
-                        const int at = cnt + __popc(m & ((1u << lane) - 1u));
-                        if (at < S::kCandCap) cand[at] = (unsigned)lane | ((unsigned)s << 12) | kCodeStatic;
-                        else overflow = true;
-                    }
-                    cnt += __popc(m);
-                }
-            }
-            if (cnt > S::kCandCap) cnt = S::kCandCap;
-            __syncwarp();
-            if (prm.dbg_cand && step == 0 && sub == 0 && !ghost) {
-                for (int i = lane; i < cnt; i += 32)
-                    if (i < prm.dbg_cand_cap) prm.dbg_cand[(size_t)env * prm.dbg_cand_cap + i] = cand[i];
-                if (lane == 0) prm.dbg_cand_n[env] = cnt;
-            }
-
-            // ======================================================= K3: narrow phase (a-5, a-6)
-            // box prefilter (necessary condition of Boxel::point_in_boxel) in rounds of <= kSurvCap survivors,
-            // then the out-of-line resolver on the survivors, contacts applied in list order
+            // ======================================================= K2b + K3: broad phase, narrow phase, contacts
+            // Producer: tested leaf pairs (pair table) and terrain cells under each leaf -> overlapping pairs are
+            //           compacted (ballot + popc) into a small candidate buffer.
+            // Consumer: every (corner, boxel) item of the candidates, plus the non-shared corners of leaf pairs
+            //           that share a point (always candidates), passes the box prefilter -- a necessary condition
+            //           of Boxel::point_in_boxel -- into a survivor buffer; survivors go through the out-of-line
+            //           resolver and their contacts are applied in list order.
+            // Both buffers are drained whenever they fill, so no configuration can overflow them.
             {
-                int next_ic = 0, next_cc = 0;
-                bool more;
-                do {
-                    int scnt = 0;
-                    while (scnt + 32 <= S::kSurvCap) {
+                int gx0 = 0, gy0 = 0, gw = 0, gh = 0;
+                const int16_t* st_grid = nullptr;
+                int cx0 = 0, cy0 = 0, wx = 1, n_cells = 0, max_cells = 0;
+                double4 mybb = make_double4(0, 0, 0, 0);
+                if (has_static) {
+                    gx0 = SHp->gx0; gy0 = SHp->gy0; gw = SHp->gw; gh = SHp->gh;
+                    st_grid = reinterpret_cast<const int16_t*>(sb + SHp->o_grid);
+                    if (lane < n_leaf) {
+                        mybb = aabb[lane];
+                        // static leaf in lattice cell c spans [c, c+1] * 0.1: only ceil(min*10 - 1) <= c <= floor(max*10)
+                        // can pass the closed-interval test; 1e-6 cells of slack, the exact test decides
+                        cx0 = max((int)ceil(mybb.x * 10.0 - 1.000001) - gx0, 0);
+                        const int cx1 = min((int)floor(mybb.z * 10.0 + 0.000001) - gx0, gw - 1);
+                        cy0 = max((int)ceil(mybb.y * 10.0 - 1.000001) - gy0, 0);
+                        const int cy1 = min((int)floor(mybb.w * 10.0 + 0.000001) - gy0, gh - 1);
+                        wx = cx1 - cx0 + 1;
+                        const int wy = cy1 - cy0 + 1;
+                        n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
+                        if (n_cells == 0) wx = 1;
+                    }
+                    max_cells = __reduce_max_sync(0xffffffffu, n_cells);
+                }
+                int pair_base = 0, cell_it = 0, next_ic = 0, dbg_off = 0;
+                bool producing = true;
+                while (producing) {
+                    // ---- produce candidates
+                    int cnt = 0;
+                    while (cnt + 32 <= S::kCandCap) {
                         bool hit = false;
                         unsigned int code = 0;
-                        if (next_ic * 32 < n_items) {
-                            // (i) non-shared corners of leaf pairs that share a point (always candidates)
-                            const int i = next_ic * 32 + lane;
-                            next_ic++;
-                            if (i < n_items) {
-                                code = __ldg(items + i);
-                                const int p = leaf[code & kCodeLeafMask].pt[(code >> kItemCornerShift) & 3];
-                                hit = point_in_box(pos[p], aabb[(code >> 12) & kCodeLeafMask]);
+                        if (pair_base < n_pairs) {
+                            const int i = pair_base + lane;
+                            pair_base += 32;
+                            if (i < n_pairs) {
+                                code = __ldg(pairs + i);
+                                hit = aabb_overlap(aabb[code & kCodeLeafMask], aabb[(code >> 12) & kCodeLeafMask]);
+                                if (hit && (code & kCodeCount)) atomicAdd((int*)&misc[code >> kCodeObjShift], 2);   // both ordered pairs (a-12)
+                                code &= kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj;
                             }
-                        } else if (next_cc * 32 < cnt * 8) {
-                            // (ii) the 8 corners of each candidate pair (these pairs share no point)
-                            const int i = next_cc * 32 + lane;
-                            next_cc++;
-                            if (i < cnt * 8) {
-                                const unsigned int cc = cand[i >> 3];
-                                const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
-                                const bool b_static = (cc & kCodeStatic) != 0;
-                                const int dir = (i >> 2) & 1, corner = i & 3;
-                                const unsigned same = (cc & kCodeSameObj) ? kItemSameObj : 0u;
-                                if (dir == 0) {
-                                    code = a | (b << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
-                                    const double4 bb = b_static ? ldg_d4(st_aabb + b) : aabb[b];
-                                    hit = point_in_box(pos[leaf[a].pt[corner]], bb);
-                                } else {
-                                    code = b | (a << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
-                                    const double2 pp = b_static ? __ldg(st_pos + __ldg(&st_leaf[b].pt[corner])) : pos[leaf[b].pt[corner]];
-                                    hit = point_in_box(pp, aabb[a]);
+                        } else if (cell_it < max_cells) {
+                            const int it = cell_it++;
+                            if (it < n_cells) {
+                                const int cx = cx0 + it % wx, cy = cy0 + it / wx;
+                                const int sl = __ldg(st_grid + cy * gw + cx);
+                                if (sl >= 0) {
+                                    hit = aabb_overlap(mybb, ldg_d4(st_aabb + sl));
+                                    code = (unsigned)lane | ((unsigned)sl << 12) | kCodeStatic;
                                 }
                             }
                         } else {
+                            producing = false;
                             break;
                         }
                         const unsigned m = __ballot_sync(0xffffffffu, hit);
-                        if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
-                        scnt += __popc(m);
-                    }
-                    more = (next_ic * 32 < n_items) || (next_cc * 32 < cnt * 8);
-                    __syncwarp();
-                    for (int base = 0; base < scnt; base += 32) {
-                        const int i = base + lane;
-                        bool has = false;
-                        Contact c;
-                        int reps = 1;
-                        if (i < scnt) {
-                            const unsigned code = surv[i];
-                            const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
-                            reps = (code & kItemSameObj) ? 2 : 1;
-                            LeafRec lm, lr;
-                            load_leaf(lm, leaf, st_leaf, code & kCodeLeafMask, m_static);
-                            load_leaf(lr, leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
-                            has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
-                        }
-                        unsigned m = __ballot_sync(0xffffffffu, has);
-                        while (m) {                       // deterministic, race-free: lanes in order
-                            const int l = __ffs(m) - 1;
-                            if (lane == l) apply_contact(cf, c, reps);
-                            m &= m - 1;
-                            __syncwarp();
-                        }
+                        if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
+                        cnt += __popc(m);
                     }
                     __syncwarp();
-                } while (more);
+                    if (prm.dbg_cand && step == 0 && sub == 0 && !ghost) {
+                        for (int i = lane; i < cnt; i += 32)
+                            if (dbg_off + i < prm.dbg_cand_cap) prm.dbg_cand[(size_t)env * prm.dbg_cand_cap + dbg_off + i] = cand[i];
+                        dbg_off += cnt;
+                        if (lane == 0) prm.dbg_cand_n[env] = dbg_off;
+                    }
+                    // ---- consume: prefilter into survivors, resolve, apply
+                    int next_cc = 0;
+                    bool more = true;
+                    while (more) {
+                        int scnt = 0;
+                        while (scnt + 32 <= S::kSurvCap) {
+                            bool hit = false;
+                            unsigned int code = 0;
+                            if (next_ic * 32 < n_items) {
+                                // non-shared corners of leaf pairs that share a point
+                                const int i = next_ic * 32 + lane;
+                                next_ic++;
+                                if (i < n_items) {
+                                    code = __ldg(items + i);
+                                    const int p = leaf[code & kCodeLeafMask].pt[(code >> kItemCornerShift) & 3];
+                                    hit = point_in_box(pos[p], aabb[(code >> 12) & kCodeLeafMask]);
+                                }
+                            } else if (next_cc * 32 < cnt * 8) {
+                                // the 8 corners of each candidate pair (these pairs share no point)
+                                const int i = next_cc * 32 + lane;
+                                next_cc++;
+                                if (i < cnt * 8) {
+                                    const unsigned int cc = cand[i >> 3];
+                                    const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
+                                    const bool b_static = (cc & kCodeStatic) != 0;
+                                    const int dir = (i >> 2) & 1, corner = i & 3;
+                                    const unsigned same = (cc & kCodeSameObj) ? kItemSameObj : 0u;
+                                    if (dir == 0) {
+                                        code = a | (b << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
+                                        const double4 bb = b_static ? ldg_d4(st_aabb + b) : aabb[b];
+                                        hit = point_in_box(pos[leaf[a].pt[corner]], bb);
+                                    } else {
+                                        code = b | (a << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
+                                        const double2 pp = b_static ? __ldg(st_pos + __ldg(&st_leaf[b].pt[corner])) : pos[leaf[b].pt[corner]];
+                                        hit = point_in_box(pp, aabb[a]);
+                                    }
+                                }
+                            } else {
+                                more = false;
+                                break;
+                            }
+                            const unsigned m = __ballot_sync(0xffffffffu, hit);
+                            if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
+                            scnt += __popc(m);
+                        }
+                        __syncwarp();
+                        for (int base = 0; base < scnt; base += 32) {
+                            const int i = base + lane;
+                            bool has = false;
+                            Contact c;
+                            int reps = 1;
+                            if (i < scnt) {
+                                const unsigned code = surv[i];
+                                const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
+                                reps = (code & kItemSameObj) ? 2 : 1;
+                                LeafRec lm, lr;
+                                load_leaf(lm, leaf, st_leaf, code & kCodeLeafMask, m_static);
+                                load_leaf(lr, leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
+                                has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
+                            }
+                            unsigned m = __ballot_sync(0xffffffffu, has);
+                            while (m) {                   // deterministic, race-free: lanes in order
+                                const int l = __ffs(m) - 1;
+                                if (lane == l) apply_contact(cf, c, reps);
+                                m &= m - 1;
+                                __syncwarp();
+                            }
+                        }
+                        __syncwarp();
+                    }
+                }
             }
             // K6a: unstable test uses the boxes of the START of this substep (a-12)
             int sub_unstable = 0;
@@ -525,7 +533,6 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         }
         double* ggoal = gstate + 8 * (size_t)Pd;
         for (int e = lane; e < Ed; e += 32) ggoal[e] = l0g[e].y;
-        if (overflow) atomicOr(prm.err + env, 1);
         if (lane == 0) {
             prm.unstable[env] = (uint8_t)unstable;
             if (unstable && prm.auto_reset) prm.sim_time[env] = 0;
