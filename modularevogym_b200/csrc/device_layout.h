@@ -69,10 +69,21 @@ struct DesignHeader {        // 128 bytes
     int cand_cap, o_mass, o_ek, o_el0, o_ea, o_eb, o_eact, o_fixed;
     int o_csro, o_csre, o_leaf, o_obj, o_pairs, o_rlev, o_rvis, total;
     int n_items, o_items, o_eflag;
-    int max_deg, unit_mass, o_csr8, o_eidx;   // warp kernel: 8-slot gather records, packed edge end points
-    int reserved[1];
+    // warp kernel (wkernel.cuh): compact copies that fit its shared-memory layout
+    int max_deg, unit_mass, o_csr8, o_eidx;   // 8-slot gather records; a | b << 8 | type << 16 | rigid-cell << 20
+    int n_types, o_etab;                      // distinct (spring constant, init_length_eq) pairs, double2 each
+    int o_pairs16, o_items16, o_rord8;        // 16-bit pair / item codes, rigid-cell visits (u8 edge ids) in reference order
+    int warp_ok;                              // every compact encoding above is valid for this design
+    int reserved[3];
 };
-static_assert(sizeof(DesignHeader) == 128, "DesignHeader must be 128 bytes");
+static_assert(sizeof(DesignHeader) == 160, "DesignHeader must be 160 bytes");
+
+// 16-bit codes of the warp kernel (<= 32 leaves): pair = a | b << 5 | same-object << 10 | count << 11 | object << 12
+//                                                 item = main | ref << 5 | corner << 10 | same-object << 12
+constexpr uint32_t kPair16Same = 1u << 10, kPair16Count = 1u << 11;
+constexpr int kPair16ObjShift = 12;
+constexpr uint32_t kItem16Same = 1u << 12;
+constexpr int kEidxTypeShift = 16, kEidxRigidBit = 20;
 
 struct StaticHeader {        // 64 bytes
     int Ps, n_leaf, gx0, gy0, gw, gh, o_pos, o_leaf;

@@ -33,8 +33,9 @@ constexpr int kNumClasses = 7;
 constexpr int kFirstGroupClass = 2;
 const int kGroupSizes[kNumClasses] = {32, 32, 32, 64, 128, 256, 512};
 constexpr int kMaxSmemPerBlock = 227 * 1024;
-using WarpSmemA = WarpSmem<40, 112, 24>;     // one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...)
-using WarpSmemB = WarpSmem<64, 160, 32>;     // 5x5 robot + a small free object (Pusher-v0, Thrower-v0, Carrier-v0)
+// warp-kernel capacities: points, edges, leaves, tested pairs, always-items, rigid-cell visits
+#define MEVO_WCAPS_A 40, 112, 24, 192, 256, 112     /* one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...) */
+#define MEVO_WCAPS_B 64, 160, 32, 512, 640, 128     /* 5x5 robot + a small free object (Pusher-v0, Thrower-v0, Carrier-v0) */
 
 int group_class_for(int Pd, int Ed) {
     if (Ed <= 160 && Pd <= 64) return 2;
@@ -45,9 +46,11 @@ int group_class_for(int Pd, int Ed) {
 }
 
 int class_for(const DesignHeader& H, bool use_warp_kernel) {
-    if (use_warp_kernel && H.max_deg <= 8 && H.unit_mass && H.n_obj <= 8) {
-        if (H.Pd <= 40 && H.Ed <= 112 && H.n_leaf <= 24) return 0;
-        if (H.Pd <= 64 && H.Ed <= 160 && H.n_leaf <= 32) return 1;
+    if (use_warp_kernel && H.warp_ok && H.max_deg <= 8 && H.unit_mass && H.n_obj <= 8 && H.n_types <= 16) {
+        const int caps[2][6] = {{MEVO_WCAPS_A}, {MEVO_WCAPS_B}};
+        for (int c = 0; c < 2; c++)
+            if (H.Pd <= caps[c][0] && H.Ed <= caps[c][1] && H.n_leaf <= caps[c][2] && H.n_pairs <= caps[c][3] &&
+                H.n_items <= caps[c][4] && H.n_rvis <= caps[c][5]) return c;
     }
     return group_class_for(H.Pd, H.Ed);
 }
@@ -89,17 +92,18 @@ void launch_step(const StepParams& prm, int smem_per_env, cudaStream_t stream) {
     step_kernel<G, EPC><<<grid, G * EPC, smem, stream>>>(prm);
 }
 
-template <int PCAP, int ECAP, int LCAP, int EPC, int MINB>
+template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 void launch_wstep(const StepParams& prm, cudaStream_t stream) {
-    constexpr int smem = WarpSmem<PCAP, ECAP, LCAP>::kBytes * EPC;
+    constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
     static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
     static bool configured = false;
     if (!configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, EPC, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
     const int grid = (prm.n_class_envs + EPC - 1) / EPC;
-    wstep_kernel<PCAP, ECAP, LCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
+    wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
 }
 
 __global__ void reset_kernel(double* state, const double* state0, const EnvDesc* envs, const uint8_t* design,
@@ -366,6 +370,7 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     }
     // rigid-cell visit schedule: reference order = object, boxel, (top,right,bot,left); levels = point-disjoint
     std::vector<uint16_t> rlev(1, 0), rvis;
+    std::vector<int> visit_order;      // dynamic-local edge id of every rigid-cell visit, reference order
     {
         std::vector<int> visit_edge, visit_level, last_level(Pd, 0);
         int n_levels = 0;
@@ -389,6 +394,7 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
         }
         H.n_rlev = n_levels;
         H.n_rvis = (int)rvis.size();
+        visit_order = visit_edge;
     }
     H.n_leaf = (int)leaves.size();
     H.n_obj = (int)objrecs.size();
@@ -413,10 +419,41 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.o_rvis = dw.begin_section(); dw.put_array(rvis);
     H.o_items = dw.begin_section(); dw.put_array(items);
     H.o_eflag = dw.begin_section(); dw.put_array(eflag);
+    // compact encodings for the warp kernel
+    bool warp_ok = Pd <= 255 && Ed <= 32767 && leaves.size() <= 32 && objrecs.size() <= 8 && visit_order.size() <= 255 * 4;
+    std::vector<double> etab;                       // (ek, el0) pairs
     std::vector<uint32_t> eidx(Ed);
-    for (int k = 0; k < Ed; k++) eidx[k] = (uint32_t)(ea[k] & 0xff) | ((uint32_t)(eb[k] & 0xff) << 8) | ((uint32_t)eflag[k] << 16);
+    for (int k = 0; k < Ed; k++) {
+        int type = -1;
+        for (size_t q = 0; q + 1 < etab.size(); q += 2)
+            if (etab[q] == ek[k] && etab[q + 1] == el0[k]) { type = (int)q / 2; break; }
+        if (type < 0) { type = (int)etab.size() / 2; etab.push_back(ek[k]); etab.push_back(el0[k]); }
+        if (type > 15) { warp_ok = false; type = 15; }
+        eidx[k] = (uint32_t)(ea[k] & 0xff) | ((uint32_t)(eb[k] & 0xff) << 8) | ((uint32_t)type << kEidxTypeShift) |
+                  ((uint32_t)(eflag[k] & kEdgeRigidCell ? 1 : 0) << kEidxRigidBit);
+    }
+    H.n_types = (int)etab.size() / 2;
+    std::vector<uint16_t> pairs16, items16;
+    std::vector<uint8_t> rord8;
+    if (warp_ok) {
+        for (uint32_t c : pairs) {
+            uint32_t v = (c & 31u) | (((c >> 12) & 31u) << 5);
+            if (c & kCodeSameObj) v |= kPair16Same;
+            if (c & kCodeCount) v |= kPair16Count | ((c >> kCodeObjShift) << kPair16ObjShift);
+            pairs16.push_back((uint16_t)v);
+        }
+        for (uint32_t c : items)
+            items16.push_back((uint16_t)((c & 31u) | (((c >> 12) & 31u) << 5) | (((c >> kItemCornerShift) & 3u) << 10) | kItem16Same));
+        for (int le : visit_order) rord8.push_back((uint8_t)le);
+        if (Ed > 255 && !visit_order.empty()) warp_ok = false;
+    }
+    H.warp_ok = warp_ok ? 1 : 0;
     H.o_csr8 = dw.begin_section(); dw.put_array(csr8);
     H.o_eidx = dw.begin_section(); dw.put_array(eidx);
+    H.o_etab = dw.begin_section(); dw.put_array(etab);
+    H.o_pairs16 = dw.begin_section(); dw.put_array(pairs16);
+    H.o_items16 = dw.begin_section(); dw.put_array(items16);
+    H.o_rord8 = dw.begin_section(); dw.put_array(rord8);
     H.total = dw.begin_section();
     std::memcpy(design.data(), &H, sizeof(H));
 
@@ -857,11 +894,11 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         prm.smem_per_env = impl_->class_smem[c];
         switch (c) {
             case 0:
-                if (impl_->wepc == 16) launch_wstep<40, 112, 24, 16, 1>(prm, st);
-                else if (impl_->wepc == 4) launch_wstep<40, 112, 24, 4, 4>(prm, st);
-                else launch_wstep<40, 112, 24, 8, 2>(prm, st);
+                if (impl_->wepc == 16) launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, st);
+                else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, st);
+                else launch_wstep<MEVO_WCAPS_A, 8, 2>(prm, st);
                 break;
-            case 1: launch_wstep<64, 160, 32, 5, 2>(prm, st); break;
+            case 1: launch_wstep<MEVO_WCAPS_B, 4, 2>(prm, st); break;
             case 2: {
                 // largest environments-per-CTA <= the configured one that fits in shared memory
                 const int want = impl_->epc32, sz = prm.smem_per_env;

@@ -1,15 +1,18 @@
-// Warp-per-environment step kernel for small robots (<= 64 dynamic points, <= ECAP dynamic edges,
-// <= 32 surface leaves): the Walker-v0 / Pusher-v0 / Thrower-v0 5x5 configurations.
+// Warp-per-environment step kernel for small worlds (one 5x5-class robot, optionally a small free object):
+// the Walker-v0 / Pusher-v0 / Thrower-v0 configurations of BASELINE.json.
 //
-// Same arithmetic as step_kernel (kernels.cuh) -- the two are interchangeable bit for bit -- but laid out
-// for the instruction front end, which is what bounds this path on B200 (ncu: `no_inst` and fixed-latency
-// `wait` stalls dominate; FP64 pipe < 15 %, DRAM ~ 0):
-//   * compile-time shared-memory layout (template capacities) -> no pointer registers, one base per warp,
+// Same arithmetic as step_kernel (kernels.cuh) -- the two agree bit for bit and tests run both -- but laid out
+// for what bounds this path on B200: instruction issue and fixed-latency dependency stalls (ncu: FP64 pipe
+// < 20 %, DRAM ~ 0, the loop body larger than the instruction cache).  Hence
+//   * everything a substep touches lives in shared memory in compact form (16-bit pair / item codes, 16-byte
+//     gather records, an edge-type table instead of per-edge constants): no global load inside the loop,
+//   * compile-time layout (template capacities): one base register per warp, constant offsets,
+//   * every spring force is stored with both signs, so the per-point gather is 8 x (LDS.128 + 2 DADD),
 //   * the spring pass handles two edges per lane at a time (two independent sqrt / div chains in flight),
-//   * per-point gather lists are one 16-byte record (8 x u16) instead of a CSR walk,
-//   * rarely taken paths (contact resolver, tanh of the analytic ground, exact strain limiters) are
-//     out-of-line so the hot loop body stays small,
-//   * every warp of a CTA owns one environment; a CTA barrier per substep keeps the warps in the same code
+//   * strain limiters: squared-length band test (no sqrt); the ordered rigid-cell pass jumps from one violating
+//     visit to the next instead of walking all visits,
+//   * rarely taken paths (contact resolver, analytic-ground tanh, exact Jacobi limiter) are out of line,
+//   * one environment per warp, several per CTA; a CTA barrier every substep keeps the warps in the same code
 //     region so they share instruction-cache lines.
 #pragma once
 
@@ -17,11 +20,12 @@
 
 namespace mevo {
 
-template <int PCAP, int ECAP, int LCAP>
+template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP>
 struct WarpSmem {
     static constexpr int kCandCap = 64;            // overlapping pairs per round (two 32-wide chunks)
-    static constexpr int kSurvCap = 64;            // survivors per round (two 32-wide chunks)
-    static constexpr int o_pos = 0;
+    static constexpr int kSurvCap = 64;            // prefilter survivors per round
+    static constexpr int kZero = 2 * ECAP;         // index of the all-zero entry of ef2
+    static constexpr int o_pos = 0;                // double2 per point ...
     static constexpr int o_spos = o_pos + 16 * PCAP;
     static constexpr int o_vel = o_spos + 16 * PCAP;
     static constexpr int o_svel = o_vel + 16 * PCAP;
@@ -29,35 +33,38 @@ struct WarpSmem {
     static constexpr int o_cf = o_vt + 16 * PCAP;
     static constexpr int o_accp = o_cf + 16 * PCAP;
     static constexpr int o_accv = o_accp + 16 * PCAP;
-    static constexpr int o_csr = o_accv + 16 * PCAP;          // uint4 per point: 8 x (edge << 1 | side)
-    static constexpr int o_ef = o_csr + 16 * PCAP;            // double2 per edge, [ECAP] = (0, 0)
-    static constexpr int o_ekl = o_ef + 16 * (ECAP + 1);      // double2 per edge: (spring constant, length_eq)
-    static constexpr int o_l0g = o_ekl + 16 * ECAP;           // double2 per edge: (init_length_eq, length_eq_goal)
-    static constexpr int o_aabb = o_l0g + 16 * ECAP;
-    static constexpr int o_leaf = o_aabb + 32 * LCAP;
-    static constexpr int o_eidx = o_leaf + 32 * LCAP;         // u32 per edge: a | b << 8 | flags << 16
-    static constexpr int o_cand = o_eidx + 4 * ECAP;
+    static constexpr int o_csr = o_accv + 16 * PCAP;           // uint4 per point: 8 x u16 index into ef2 (edge << 1 | side)
+    static constexpr int o_ef2 = o_csr + 16 * PCAP;            // double2 x 2 per edge: [2e] = -f (a side), [2e+1] = +f (b side)
+    static constexpr int o_leq = o_ef2 + 16 * (2 * ECAP + 1);  // double per edge: length_eq
+    static constexpr int o_goal = o_leq + 8 * ECAP;            // double per edge: length_eq_goal
+    static constexpr int o_etab = o_goal + 8 * ECAP;           // double2 x 16: (spring constant, init_length_eq) per edge type
+    static constexpr int o_aabb = o_etab + 16 * 16;            // double4 per leaf
+    static constexpr int o_eidx = o_aabb + 32 * LCAP;          // u32 per edge: a | b << 8 | type << 16 | rigid-cell << 20
+    static constexpr int o_lpt = o_eidx + 4 * ECAP;            // u32 per leaf: the 4 corner point ids (TL,TR,BR,BL), u8 each
+    static constexpr int o_cand = o_lpt + 4 * LCAP;
     static constexpr int o_surv = o_cand + 4 * kCandCap;
-    static constexpr int o_misc = o_surv + 4 * kSurvCap;      // [0..7] self-collision counts per object
-    static constexpr int kBytes = (o_misc + 4 * 8 + 15) & ~15;
+    static constexpr int o_pairs = o_surv + 4 * kSurvCap;      // u16 pair codes
+    static constexpr int o_items = o_pairs + 2 * PAIRCAP;      // u16 item codes
+    static constexpr int o_rord = o_items + 2 * ITEMCAP;       // u8 edge id per rigid-cell visit, reference order
+    static constexpr int o_misc = (o_rord + VISCAP + 3) & ~3;  // int[8] self-collision counts, int[8] n_surface (robots) or INT_MAX
+    static constexpr int kBytes = (o_misc + 4 * 16 + 15) & ~15;
 };
 
 // tanh of the analytic ground plane's friction term (PhysicsEngine.cpp:573-577); out of line: a robot standing
 // on voxel terrain never gets below y = 0
 __device__ __noinline__ double ground_friction_tanh(double x) { return tanh(x); }
 
-// exact strain limiters of PhysicsEngine::resolve_edge_constraints (PhysicsEngine.cpp:608-713) for one warp;
-// out of line: runs only in substeps where some edge left the +-25 % / +-3 % band
-__device__ __noinline__ void warp_exact_constraints(double2* pos, double2* ef, const double2* l0g, const uint32_t* eidx,
-                                                    const uint4* csr, int Pd, int Ed, unsigned fixmask, int ecap,
-                                                    const uint16_t* rlev, const uint16_t* rvis, int n_rlev) {
+// Jacobi half of PhysicsEngine::resolve_edge_constraints (PhysicsEngine.cpp:613-671) for one warp; out of line:
+// runs only in substeps where some edge left the +-25 % band
+__device__ __noinline__ void warp_jacobi_limiter(double2* pos, double2* ef2, const uint32_t* eidx, const double2* etab,
+                                                 const uint4* csr, int Pd, int Ed, unsigned fixmask, int zero_idx) {
     const int lane = threadIdx.x & 31;
     for (int e = lane; e < Ed; e += 32) {
         const uint32_t ix = eidx[e];
         const double2 pa = pos[ix & 0xff], pb = pos[(ix >> 8) & 0xff];
         const double dx = pa.x - pb.x, dy = pa.y - pb.y;
         const double dist = sqrt(dx * dx + dy * dy);
-        const double l0 = l0g[e].x;
+        const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
         const double over_mag = (dist - l0 * (1 + 0.25)) / (dist * 2);
         const double under_mag = (dist - l0 * (1 - 0.25)) / (dist * 2);
         double ox = dx * over_mag, oy = dy * over_mag;
@@ -65,7 +72,9 @@ __device__ __noinline__ void warp_exact_constraints(double2* pos, double2* ef, c
         const double stress = dist / l0;
         if (!(stress > (1 + 0.25))) { ox = 0.0; oy = 0.0; }
         if (!(stress < (1 - 0.25))) { ux = 0.0; uy = 0.0; }
-        ef[e] = make_double2((ox + ux) * 0.8, (oy + uy) * 0.8);
+        const double cx = (ox + ux) * 0.8, cy = (oy + uy) * 0.8;
+        ef2[2 * e] = make_double2(-cx, -cy);
+        ef2[2 * e + 1] = make_double2(cx, cy);
     }
     __syncwarp();
     for (int p = lane, k = 0; p < Pd; p += 32, k++) {
@@ -76,55 +85,47 @@ __device__ __noinline__ void warp_exact_constraints(double2* pos, double2* ef, c
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const unsigned ent = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-            if (ent == 0xffffu) continue;
-            const double2 c = ef[ent >> 1];
-            if (ent & 1u) { x.x += c.x; x.y += c.y; } else { x.x -= c.x; x.y -= c.y; }
+            const double2 c = ef2[min(ent, (unsigned)zero_idx)];
+            x.x += c.x; x.y += c.y;
         }
         pos[p] = x;
     }
     __syncwarp();
-    // ordered rigid-cell pass, scheduled in point-disjoint levels (PhysicsEngine.cpp:675-710)
-    for (int lv = 0; lv < n_rlev; lv++) {
-        const int i1 = __ldg(rlev + lv + 1);
-        for (int i = __ldg(rlev + lv) + lane; i < i1; i += 32) {
-            const int e = __ldg(rvis + i);
-            const uint32_t ix = eidx[e];
-            const int a = ix & 0xff, b = (ix >> 8) & 0xff;
-            double2 pa = pos[a], pb = pos[b];
-            const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-            const double d2 = dx * dx + dy * dy;
-            const double l0 = l0g[e].x;
-            // cheap exact skip: inside the +-3 % band (guarded) every term of the reference is zero
-            const double l2 = l0 * l0;
-            if (d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999) continue;
-            const double dist = sqrt(d2);
-            const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
-            const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
-            double ox = dx * over_mag, oy = dy * over_mag;
-            double ux = dx * under_mag, uy = dy * under_mag;
-            const double stress = dist / l0;
-            if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
-            if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
-            const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
-            pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
-            pos[a] = pa; pos[b] = pb;
-        }
-        __syncwarp();
-    }
+}
+
+// The exact +-3 % limiter of one rigid-cell visit (PhysicsEngine.cpp:675-710); out of line, one lane.
+__device__ __noinline__ void rigid_visit_exact(double2* pos, int a, int b, double l0) {
+    double2 pa = pos[a], pb = pos[b];
+    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+    const double dist = sqrt(dx * dx + dy * dy);
+    const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
+    const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
+    double ox = dx * over_mag, oy = dy * over_mag;
+    double ux = dx * under_mag, uy = dy * under_mag;
+    const double stress = dist / l0;
+    if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
+    if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
+    const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
+    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
+    pos[a] = pa; pos[b] = pb;
 }
 
 // spring force of one edge for stage positions sp (PhysicsEngine.cpp:498-528)
-__device__ __forceinline__ double2 spring_force(const double2* sp, uint32_t ix, double2 kl) {
+__device__ __forceinline__ double2 spring_force(const double2* sp, uint32_t ix, double k, double leq) {
     const double2 pa = sp[ix & 0xff], pb = sp[(ix >> 8) & 0xff];
     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
     const double dist = sqrt(dx * dx + dy * dy);
-    const double mag = (dist - kl.y) * kl.x / dist;
+    const double mag = (dist - leq) * k / dist;
     return make_double2(dx * mag, dy * mag);
 }
 
-template <int PCAP, int ECAP, int LCAP, int EPC, int MINB>
+__device__ __forceinline__ double flip_sign(double x) {       // -x on the integer pipe (exact)
+    return __hiloint2double(__double2hiint(x) ^ 0x80000000, __double2loint(x));
+}
+
+template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams prm) {
-    using S = WarpSmem<PCAP, ECAP, LCAP>;
+    using S = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int grp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -136,13 +137,14 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     const uint8_t* db = prm.design + ed.design_off;
     const DesignHeader* Hp = reinterpret_cast<const DesignHeader*>(db);
     const int Pd = Hp->Pd, Ed = Hp->Ed, n_leaf = Hp->n_leaf;
-    const int n_pairs = Hp->n_pairs, n_items = Hp->n_items, n_obj = Hp->n_obj;
+    const int n_pairs = Hp->n_pairs, n_items = Hp->n_items, n_vis = Hp->n_rvis;
     const bool has_static = ed.static_off != ~0ull;
     const uint8_t* sb = prm.statics + (has_static ? ed.static_off : 0);
     const StaticHeader* SHp = reinterpret_cast<const StaticHeader*>(sb);
     const double2* st_pos = reinterpret_cast<const double2*>(sb + (has_static ? SHp->o_pos : 0));
     const LeafRec* st_leaf = reinterpret_cast<const LeafRec*>(sb + (has_static ? SHp->o_leaf : 0));
     const double4* st_aabb = reinterpret_cast<const double4*>(sb + (has_static ? SHp->o_aabb : 0));
+    const LeafRec* g_leaf = reinterpret_cast<const LeafRec*>(db + Hp->o_leaf);     // full records: resolver only
 
     unsigned char* sm = smem_raw + grp * S::kBytes;
     double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
@@ -154,14 +156,18 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     double2* accp = reinterpret_cast<double2*>(sm + S::o_accp);
     double2* accv = reinterpret_cast<double2*>(sm + S::o_accv);
     uint4* csr = reinterpret_cast<uint4*>(sm + S::o_csr);
-    double2* ef = reinterpret_cast<double2*>(sm + S::o_ef);
-    double2* ekl = reinterpret_cast<double2*>(sm + S::o_ekl);
-    double2* l0g = reinterpret_cast<double2*>(sm + S::o_l0g);
+    double2* ef2 = reinterpret_cast<double2*>(sm + S::o_ef2);
+    double* leq = reinterpret_cast<double*>(sm + S::o_leq);
+    double* goal = reinterpret_cast<double*>(sm + S::o_goal);
+    double2* etab = reinterpret_cast<double2*>(sm + S::o_etab);
     double4* aabb = reinterpret_cast<double4*>(sm + S::o_aabb);
-    LeafRec* leaf = reinterpret_cast<LeafRec*>(sm + S::o_leaf);
     uint32_t* eidx = reinterpret_cast<uint32_t*>(sm + S::o_eidx);
+    uint32_t* lpt = reinterpret_cast<uint32_t*>(sm + S::o_lpt);
     unsigned int* cand = reinterpret_cast<unsigned int*>(sm + S::o_cand);
     unsigned int* surv = reinterpret_cast<unsigned int*>(sm + S::o_surv);
+    uint16_t* pairs = reinterpret_cast<uint16_t*>(sm + S::o_pairs);
+    uint16_t* items = reinterpret_cast<uint16_t*>(sm + S::o_items);
+    uint8_t* rord = reinterpret_cast<uint8_t*>(sm + S::o_rord);
     volatile int* misc = reinterpret_cast<volatile int*>(sm + S::o_misc);
 
     // ---------------------------------------------------------------- stage in (once per launch)
@@ -180,31 +186,41 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         const int16_t* eact = reinterpret_cast<const int16_t*>(db + Hp->o_eact);
         const double* act = prm.act + (size_t)env * prm.act_stride;
         for (int e = lane; e < Ed; e += 32) {
-            const double l0 = __ldg(reinterpret_cast<const double*>(db + Hp->o_el0) + e);
             double g = ggoal[e];
             if (prm.apply_actions) {
                 // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather
                 const int a0 = eact[2 * e], a1 = eact[2 * e + 1];
                 if (a0 >= 0) {
+                    const double l0 = __ldg(reinterpret_cast<const double*>(db + Hp->o_el0) + e);
                     double sum = 0.0 + act[a0];
                     int cnt = 1;
                     if (a1 >= 0) { sum += act[a1]; cnt = 2; }
                     g = sum * (l0 / cnt);
                 }
             }
-            l0g[e] = make_double2(l0, g);
-            ekl[e] = make_double2(__ldg(reinterpret_cast<const double*>(db + Hp->o_ek) + e), 0.0);
+            goal[e] = g;
             eidx[e] = __ldg(reinterpret_cast<const uint32_t*>(db + Hp->o_eidx) + e);
         }
-        if (lane == 0) ef[ECAP] = make_double2(0.0, 0.0);
-        const uint4* gl = reinterpret_cast<const uint4*>(db + Hp->o_leaf);
-        uint4* sl = reinterpret_cast<uint4*>(leaf);
-        for (int i = lane; i < 2 * n_leaf; i += 32) sl[i] = __ldg(gl + i);
+        if (lane < Hp->n_types) etab[lane] = __ldg(reinterpret_cast<const double2*>(db + Hp->o_etab) + lane);
+        if (lane == 0) ef2[S::kZero] = make_double2(0.0, 0.0);
+        if (lane < n_leaf) {
+            const LeafRec r = g_leaf[lane];
+            lpt[lane] = (uint32_t)r.pt[0] | ((uint32_t)r.pt[1] << 8) | ((uint32_t)r.pt[2] << 16) | ((uint32_t)r.pt[3] << 24);
+        }
+        for (int i = lane; i < n_pairs; i += 32) pairs[i] = __ldg(reinterpret_cast<const uint16_t*>(db + Hp->o_pairs16) + i);
+        for (int i = lane; i < n_items; i += 32) items[i] = __ldg(reinterpret_cast<const uint16_t*>(db + Hp->o_items16) + i);
+        for (int i = lane; i < n_vis; i += 32) rord[i] = __ldg(db + Hp->o_rord8 + i);
+        if (lane < 8) {
+            int ns = 0x7fffffff;                        // never "unstable" unless a robot (PhysicsEngine.cpp:819-834)
+            if (lane < Hp->n_obj) {
+                const ObjRec orc = reinterpret_cast<const ObjRec*>(db + Hp->o_obj)[lane];
+                if (orc.is_robot) ns = orc.n_surface;
+            }
+            misc[8 + lane] = ns;
+        }
     }
     __syncwarp();
 
-    const unsigned int* pairs = reinterpret_cast<const unsigned int*>(db + Hp->o_pairs);
-    const unsigned int* items = reinterpret_cast<const unsigned int*>(db + Hp->o_items);
     PointSrc src;
     src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = st_pos;
 
@@ -214,17 +230,18 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
 
     for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
-            if (EPC > 1) __syncthreads();                 // keeps the CTA's warps in the same code region (I-cache)
+            // keeps the CTA's warps in the same code region: they share instruction-cache lines
+            if (EPC > 1 && prm.cta_sync > 0 && (sub % prm.cta_sync) == 0) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
 
             // ======================================================= K2a: leaf boxes (a-4), zero collision_forces
             if (lane < n_leaf) {
-                const LeafRec r = leaf[lane];
-                double2 q = pos[r.pt[0]];
+                const uint32_t lp = lpt[lane];
+                double2 q = pos[lp & 0xff];
                 double minx = q.x, maxx = q.x, miny = q.y, maxy = q.y;
 #pragma unroll
                 for (int c = 1; c < 4; c++) {
-                    q = pos[r.pt[c]];
+                    q = pos[(lp >> (8 * c)) & 0xff];
                     minx = fmin(minx, q.x); maxx = fmax(maxx, q.x);
                     miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
                 }
@@ -268,7 +285,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                 int pair_base = 0, cell_it = 0, next_ic = 0, dbg_off = 0;
                 bool producing = true;
                 while (producing) {
-                    // ---- produce candidates
+                    // ---- produce candidates (32-bit codes of kernels.cuh)
                     int cnt = 0;
                     while (cnt + 32 <= S::kCandCap) {
                         bool hit = false;
@@ -277,10 +294,11 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                             const int i = pair_base + lane;
                             pair_base += 32;
                             if (i < n_pairs) {
-                                code = __ldg(pairs + i);
-                                hit = aabb_overlap(aabb[code & kCodeLeafMask], aabb[(code >> 12) & kCodeLeafMask]);
-                                if (hit && (code & kCodeCount)) atomicAdd((int*)&misc[code >> kCodeObjShift], 2);   // both ordered pairs (a-12)
-                                code &= kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj;
+                                const unsigned pc = pairs[i];
+                                const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
+                                hit = aabb_overlap(aabb[a], aabb[b]);
+                                if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
+                                code = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
                             }
                         } else if (cell_it < max_cells) {
                             const int it = cell_it++;
@@ -320,9 +338,10 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                                 const int i = next_ic * 32 + lane;
                                 next_ic++;
                                 if (i < n_items) {
-                                    code = __ldg(items + i);
-                                    const int p = leaf[code & kCodeLeafMask].pt[(code >> kItemCornerShift) & 3];
-                                    hit = point_in_box(pos[p], aabb[(code >> 12) & kCodeLeafMask]);
+                                    const unsigned ic = items[i];
+                                    const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
+                                    code = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
+                                    hit = point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
                                 }
                             } else if (next_cc * 32 < cnt * 8) {
                                 // the 8 corners of each candidate pair (these pairs share no point)
@@ -337,10 +356,11 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                                     if (dir == 0) {
                                         code = a | (b << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
                                         const double4 bb = b_static ? ldg_d4(st_aabb + b) : aabb[b];
-                                        hit = point_in_box(pos[leaf[a].pt[corner]], bb);
+                                        hit = point_in_box(pos[(lpt[a] >> (8 * corner)) & 0xff], bb);
                                     } else {
                                         code = b | (a << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
-                                        const double2 pp = b_static ? __ldg(st_pos + __ldg(&st_leaf[b].pt[corner])) : pos[leaf[b].pt[corner]];
+                                        const double2 pp = b_static ? __ldg(st_pos + __ldg(&st_leaf[b].pt[corner]))
+                                                                    : pos[(lpt[b] >> (8 * corner)) & 0xff];
                                         hit = point_in_box(pp, aabb[a]);
                                     }
                                 }
@@ -363,8 +383,8 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                                 const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
                                 reps = (code & kItemSameObj) ? 2 : 1;
                                 LeafRec lm, lr;
-                                load_leaf(lm, leaf, st_leaf, code & kCodeLeafMask, m_static);
-                                load_leaf(lr, leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
+                                load_leaf(lm, g_leaf, st_leaf, code & kCodeLeafMask, m_static);
+                                load_leaf(lr, g_leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
                                 has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
                             }
                             unsigned m = __ballot_sync(0xffffffffu, has);
@@ -380,14 +400,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                 }
             }
             // K6a: unstable test uses the boxes of the START of this substep (a-12)
-            int sub_unstable = 0;
-            {
-                const ObjRec* objs = reinterpret_cast<const ObjRec*>(db + Hp->o_obj);
-                for (int o = 0; o < n_obj; o++) {
-                    const ObjRec orc = objs[o];
-                    if (orc.is_robot && misc[o] > (int)orc.n_surface) sub_unstable = 1;
-                }
-            }
+            const int sub_unstable = __any_sync(0xffffffffu, lane < 8 && misc[lane] > misc[8 + lane]);
 
             // ======================================================= K4: actuators + RK4 (a-7, a-8, a-9)
             // two edges per lane per trip: e and e + 32 (the second clamped and its stores predicated)
@@ -402,10 +415,10 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                 const double dx1 = a1.x - b1.x, dy1 = a1.y - b1.y;
                 const double d0 = sqrt(dx0 * dx0 + dy0 * dy0);
                 const double d1 = sqrt(dx1 * dx1 + dy1 * dy1);
-                const double add0 = (l0g[e0].y - d0) * 0.006;
-                const double add1 = (l0g[e1c].y - d1) * 0.006;
-                ekl[e0].y = d0 + add0;
-                if (v1) ekl[e1].y = d1 + add1;
+                const double add0 = (goal[e0] - d0) * 0.006;
+                const double add1 = (goal[e1c] - d1) * 0.006;
+                leq[e0] = d0 + add0;
+                if (v1) leq[e1] = d1 + add1;
             }
             // length_eq[e] is written and read by the same lane: no barrier needed
 #pragma unroll 1
@@ -416,10 +429,15 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                     const int e1 = e0 + 32;
                     const bool v1 = e1 < Ed;
                     const int e1c = v1 ? e1 : e0;
-                    const double2 f0 = spring_force(sp, eidx[e0], ekl[e0]);
-                    const double2 f1 = spring_force(sp, eidx[e1c], ekl[e1c]);
-                    ef[e0] = f0;
-                    if (v1) ef[e1] = f1;
+                    const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
+                    const double2 f0 = spring_force(sp, i0, etab[(i0 >> kEidxTypeShift) & 15].x, leq[e0]);
+                    const double2 f1 = spring_force(sp, i1, etab[(i1 >> kEidxTypeShift) & 15].x, leq[e1c]);
+                    ef2[2 * e0] = make_double2(flip_sign(f0.x), flip_sign(f0.y));
+                    ef2[2 * e0 + 1] = f0;
+                    if (v1) {
+                        ef2[2 * e1] = make_double2(flip_sign(f1.x), flip_sign(f1.y));
+                        ef2[2 * e1 + 1] = f1;
+                    }
                 }
                 __syncwarp();
                 for (int p = lane, k = 0; p < Pd; p += 32, k++) {
@@ -427,14 +445,15 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                     const double2 x = sp[p];
                     double Fx = 0.0, Fy = 0.0;
                     {
+                        // F -= f over the a sides in edge order, then F += f over the b sides (PhysicsEngine.cpp:530-531):
+                        // the record lists them in that order, the sign is in the stored value, empty slots read zero
                         const uint4 rec = csr[p];
                         const unsigned w[4] = {rec.x, rec.y, rec.z, rec.w};
                         double2 f[8];
 #pragma unroll
                         for (int j = 0; j < 8; j++) {
                             const unsigned ent = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-                            f[j] = ef[min(ent >> 1, (unsigned)ECAP)];          // empty slot -> the zero entry
-                            if (!(ent & 1u)) { f[j].x = -f[j].x; f[j].y = -f[j].y; }
+                            f[j] = ef2[min(ent, (unsigned)S::kZero)];
                         }
 #pragma unroll
                         for (int j = 0; j < 8; j++) { Fx += f[j].x; Fy += f[j].y; }
@@ -478,25 +497,53 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             }
 
             // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
-            // strain-band fast path on squared lengths (no sqrt): inside the guarded band every correction of the
-            // reference is exactly zero; otherwise the exact, ordered passes run out of line
+            // Band test on squared lengths (no sqrt), guarded by 1e-7 so the decision never depends on the rounding
+            // of dist / L0: inside the band every correction of the reference is exactly zero.
             {
-                bool viol = false;
+                bool jviol = false, rviol = false;
                 for (int e = lane; e < Ed; e += 32) {
                     const uint32_t ix = eidx[e];
                     const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
                     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
                     const double d2 = dx * dx + dy * dy;
-                    const double l0 = l0g[e].x;
+                    const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
                     const double l2 = l0 * l0;
-                    const bool rigid = (ix & (kEdgeRigidCell << 16)) != 0;
-                    const double lo = rigid ? 0.9409001 : 0.5625001, hi = rigid ? 1.0608999 : 1.5624999;
-                    if (!(d2 > l2 * lo && d2 < l2 * hi)) viol = true;
+                    if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) jviol = true;
+                    if (((ix >> kEidxRigidBit) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) rviol = true;
                 }
-                if (__any_sync(0xffffffffu, viol))
-                    warp_exact_constraints(spos, ef, l0g, eidx, csr, Pd, Ed, fixmask, ECAP,
-                                           reinterpret_cast<const uint16_t*>(db + Hp->o_rlev),
-                                           reinterpret_cast<const uint16_t*>(db + Hp->o_rvis), Hp->n_rlev);
+                const bool anyj = __any_sync(0xffffffffu, jviol);
+                if (anyj) warp_jacobi_limiter(spos, ef2, eidx, etab, csr, Pd, Ed, fixmask, S::kZero);
+                if (n_vis > 0 && (anyj || __any_sync(0xffffffffu, rviol))) {
+                    // ordered rigid-cell pass (PhysicsEngine.cpp:675-710): a visit inside the +-3 % band changes
+                    // nothing, so jump from one violating visit to the next; each is applied exactly by one lane
+                    // and the visits after it are re-tested against the updated positions
+                    int start = 0;
+                    while (start < n_vis) {
+                        int first = -1;
+                        for (int c = start & ~31; c < n_vis; c += 32) {
+                            const int i = c + lane;
+                            bool v = false;
+                            if (i >= start && i < n_vis) {
+                                const uint32_t ix = eidx[rord[i]];
+                                const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
+                                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                                const double d2 = dx * dx + dy * dy;
+                                const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
+                                const double l2 = l0 * l0;
+                                v = !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999);
+                            }
+                            const unsigned m = __ballot_sync(0xffffffffu, v);
+                            if (m) { first = c + __ffs(m) - 1; break; }
+                        }
+                        if (first < 0) break;
+                        if (lane == (first & 31)) {
+                            const uint32_t ix = eidx[rord[first]];
+                            rigid_visit_exact(spos, ix & 0xff, (ix >> 8) & 0xff, etab[(ix >> kEidxTypeShift) & 15].y);
+                        }
+                        __syncwarp();
+                        start = first + 1;
+                    }
+                }
             }
             for (int p = lane; p < Pd; p += 32) {        // PhysicsEngine::update_true_vel (:602-607)
                 const double2 x = spos[p];
@@ -532,7 +579,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             }
         }
         double* ggoal = gstate + 8 * (size_t)Pd;
-        for (int e = lane; e < Ed; e += 32) ggoal[e] = l0g[e].y;
+        for (int e = lane; e < Ed; e += 32) ggoal[e] = goal[e];
         if (lane == 0) {
             prm.unstable[env] = (uint8_t)unstable;
             if (unstable && prm.auto_reset) prm.sim_time[env] = 0;
