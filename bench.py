@@ -306,9 +306,9 @@ def main_ours(args) -> None:
     launches += 1
     B.sync()
     if world > 1:
-        gathered = torch.empty((world * n, 2), dtype=torch.float64, device=dev)
-        with torch.cuda.stream(stream):
-            dist.all_gather_into_tensor(gathered, com_dev)
+        from modularevogym_b200.sharding import gather_env_rows
+        gathered = gather_env_rows(com_dev, world * n)       # (world * n, 2) on every rank
+        assert gathered.shape[0] == world * n
     barrier()
     t_wall = time.perf_counter() - t_wall
     clock_info = clocks.stop() if clocks else None

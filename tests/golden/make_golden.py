@@ -124,7 +124,7 @@ def record(name: str, world: WorldSpec, seed: int, perturb=None, n_sub=N_SUB, n_
     sub_unstable (n_sub,)           return value of each Environment::step
     cand_<k> (n,4)                  leaf-leaf candidates (obj_a,boxel_a,obj_b,boxel_b) for the positions
                                     BEFORE substep k, reference descent order; k in cand_at
-    step_pos, step_vel (n_steps+1,P,2), step_unstable, step_time (n_steps,)   the Sim::step run
+    step_pos, step_vel (n_steps+1,P,2), step_unstable, step_time, step_orient (n_steps,)   the Sim::step run
     """
     rng = np.random.default_rng(99 + seed)
     out = {"world_json": np.array(json.dumps(world.to_dict()))}
@@ -177,6 +177,7 @@ def record(name: str, world: WorldSpec, seed: int, perturb=None, n_sub=N_SUB, n_
     step_vel = np.zeros((n_steps + 1, P, 2))
     step_unstable = np.zeros(n_steps, dtype=np.uint8)
     step_time = np.zeros(n_steps, dtype=np.int32)
+    step_orient = np.zeros(n_steps)          # Sim::object_orientation_at_time(get_time(), "robot") after each step
     step_pos[0], step_vel[0] = pos, vel
     for s in range(n_steps):
         ref2.set_action_values("robot", actions[s])
@@ -184,7 +185,8 @@ def record(name: str, world: WorldSpec, seed: int, perturb=None, n_sub=N_SUB, n_
         step_time[s] = ref2.get_time()
         p, v, _, _ = ref2.get_state()
         step_pos[s + 1], step_vel[s + 1] = p, v
-    out.update(step_pos=step_pos, step_vel=step_vel, step_unstable=step_unstable, step_time=step_time)
+        step_orient[s] = ref2.object_orientation_at_time(ref2.get_time(), "robot")
+    out.update(step_pos=step_pos, step_vel=step_vel, step_unstable=step_unstable, step_time=step_time, step_orient=step_orient)
     n_contacts = int((np.abs(sub["cf"]).sum(axis=(1, 2)) > 0).sum())
     print(f"{name:24s} P={P:4d} E={E:5d} objs={ref.num_objects} A={len(act_idx):3d} "
           f"substeps-with-contact={n_contacts:3d}/{n_sub} unstable(sub)={int(sub_unstable.sum())} "
