@@ -132,6 +132,7 @@ struct Batch::Impl {
     std::vector<size_t> class_off;                // per class: offset into d_class_envs_
     std::vector<EnvDesc> desc;
     std::vector<std::vector<double>> pos0, vel0;  // reset snapshot (global numbering)
+    std::vector<int> env_cost;                    // per env: estimated work of one substep
     bool use_warp_kernel = true;
     int wepc = 0;                                 // warp kernel: environments per CTA override (0 = default)
     int epc32 = 12;
@@ -525,6 +526,7 @@ void Batch::finalize() {
     impl_->desc.assign(n, EnvDesc());
     impl_->class_envs.assign(kNumClasses, {});
     impl_->class_smem.assign(kNumClasses, 0);
+    impl_->env_cost.clear();
     size_t state_doubles = 0;
     act_stride_ = 1;
 
@@ -561,7 +563,14 @@ void Batch::finalize() {
             impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
         }
         impl_->class_envs[e.cls].push_back(i);
+        // work estimate of one substep (spring passes, point passes, corner items): environments of similar cost
+        // are placed in the same CTA so that the per-substep CTA barrier waits as little as possible
+        impl_->env_cost.push_back(1000 * ((H->Pd + 31) / 32) + 700 * ((H->Ed + 63) / 64) + 40 * ((H->n_items + 31) / 32) +
+                                  40 * ((H->n_pairs + 31) / 32) + 20 * H->n_rvis);
     }
+    for (int c = 0; c < kFirstGroupClass; c++)
+        std::stable_sort(impl_->class_envs[c].begin(), impl_->class_envs[c].end(),
+                         [&](int a, int b) { return impl_->env_cost[a] > impl_->env_cost[b]; });
     for (int i = 0; i < n; i++) impl_->desc[i].act_off = i * act_stride_;
 
     // (re)allocate

@@ -47,8 +47,23 @@ struct WarpSmem {
     static constexpr int o_items = o_pairs + 2 * PAIRCAP;      // u16 item codes
     static constexpr int o_rord = o_items + 2 * ITEMCAP;       // u8 edge id per rigid-cell visit, reference order
     static constexpr int o_misc = (o_rord + VISCAP + 3) & ~3;  // int[8] self-collision counts, int[8] n_surface (robots) or INT_MAX
-    static constexpr int kBytes = (o_misc + 4 * 16 + 15) & ~15;
+    static constexpr int o_hdr = (o_misc + 4 * 16 + 7) & ~7;   // WarpHdr: per-environment scalars and pointers
+    static constexpr int kBytes = (o_hdr + 96 + 15) & ~15;
 };
+
+// Per-environment scalars the phases need, kept in shared memory instead of registers (the phases are separate
+// out-of-line functions so that each gets the whole register budget; broadcast LDS is cheap).
+struct WarpHdr {                                   // 96 bytes
+    int Pd, Ed, n_leaf, n_pairs, n_items, n_vis;
+    int gx0, gy0, gw, gh;                          // terrain grid (gw = 0: no static terrain)
+    const int16_t* st_grid;
+    const double4* st_aabb;
+    const double2* st_pos;
+    const LeafRec* st_leaf;
+    const LeafRec* g_leaf;                         // full dynamic leaf records (resolver only)
+    const double2* g_last;                         // pos_last in HBM: read in the first substep of a launch only
+};
+static_assert(sizeof(WarpHdr) == 88, "WarpHdr layout");
 
 // tanh of the analytic ground plane's friction term (PhysicsEngine.cpp:573-577); out of line: a robot standing
 // on voxel terrain never gets below y = 0
@@ -123,6 +138,391 @@ __device__ __forceinline__ double flip_sign(double x) {       // -x on the integ
     return __hiloint2double(__double2hiint(x) ^ 0x80000000, __double2loint(x));
 }
 
+
+// =================================================================================== phase 1: collisions
+// K2a leaf boxes, K2b broad phase, K3 narrow phase + contact response, K6 unstable count (SURVEY 8a-4,5,6,12).
+// Returns 1 when PhysicsEngine::is_any_robot_self_colliding would (boxes of the START of the substep).
+//
+// Producer: tested leaf pairs (pair table) and terrain cells under each leaf -> overlapping pairs are compacted
+//           (ballot + popc) into a small candidate buffer.
+// Consumer: every (corner, boxel) item of the candidates, plus the non-shared corners of leaf pairs that share a
+//           point (always candidates), passes the box prefilter -- a necessary condition of
+//           Boxel::point_in_boxel -- into a survivor buffer; survivors go through the out-of-line resolver and
+//           their contacts are applied in list order.
+// Both buffers are drained whenever they fill, so no configuration can overflow them.
+template <class S>
+__device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_row, int* dbg_n, int dbg_cap) {
+    const int lane = threadIdx.x & 31;
+    const WarpHdr* H = reinterpret_cast<const WarpHdr*>(sm + S::o_hdr);
+    double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
+    double2* vt = reinterpret_cast<double2*>(sm + S::o_vt);
+    double2* cf = reinterpret_cast<double2*>(sm + S::o_cf);
+    double4* aabb = reinterpret_cast<double4*>(sm + S::o_aabb);
+    const uint32_t* lpt = reinterpret_cast<const uint32_t*>(sm + S::o_lpt);
+    unsigned int* cand = reinterpret_cast<unsigned int*>(sm + S::o_cand);
+    unsigned int* surv = reinterpret_cast<unsigned int*>(sm + S::o_surv);
+    const uint16_t* pairs = reinterpret_cast<const uint16_t*>(sm + S::o_pairs);
+    const uint16_t* items = reinterpret_cast<const uint16_t*>(sm + S::o_items);
+    volatile int* misc = reinterpret_cast<volatile int*>(sm + S::o_misc);
+    const int Pd = H->Pd, n_leaf = H->n_leaf, n_pairs = H->n_pairs, n_items = H->n_items;
+
+    // ---- K2a: leaf boxes (a-4), zero collision_forces
+    if (lane < n_leaf) {
+        const uint32_t lp = lpt[lane];
+        double2 q = pos[lp & 0xff];
+        double minx = q.x, maxx = q.x, miny = q.y, maxy = q.y;
+#pragma unroll
+        for (int c = 1; c < 4; c++) {
+            q = pos[(lp >> (8 * c)) & 0xff];
+            minx = fmin(minx, q.x); maxx = fmax(maxx, q.x);
+            miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
+        }
+        aabb[lane] = make_double4(minx, miny, maxx, maxy);
+    }
+    for (int i = lane; i < Pd; i += 32) cf[i] = make_double2(0.0, 0.0);
+    if (lane < 8) misc[lane] = 0;
+    __syncwarp();
+
+    // ---- terrain window of this lane's leaf
+    const int gw = H->gw;
+    const int16_t* st_grid = H->st_grid;
+    const double4* st_aabb = H->st_aabb;
+    int cx0 = 0, cy0 = 0, wx = 1, n_cells = 0, max_cells = 0;
+    double4 mybb = make_double4(0, 0, 0, 0);
+    if (gw > 0) {
+        if (lane < n_leaf) {
+            mybb = aabb[lane];
+            // static leaf in lattice cell c spans [c, c+1] * 0.1: only ceil(min*10 - 1) <= c <= floor(max*10) can
+            // pass the closed-interval test; 1e-6 cells of slack, the exact test decides
+            cx0 = max((int)ceil(mybb.x * 10.0 - 1.000001) - H->gx0, 0);
+            const int cx1 = min((int)floor(mybb.z * 10.0 + 0.000001) - H->gx0, gw - 1);
+            cy0 = max((int)ceil(mybb.y * 10.0 - 1.000001) - H->gy0, 0);
+            const int cy1 = min((int)floor(mybb.w * 10.0 + 0.000001) - H->gy0, H->gh - 1);
+            wx = cx1 - cx0 + 1;
+            const int wy = cy1 - cy0 + 1;
+            n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
+            if (n_cells == 0) wx = 1;
+        }
+        max_cells = __reduce_max_sync(0xffffffffu, n_cells);
+    }
+
+    int pair_base = 0, cell_it = 0, next_ic = 0, dbg_off = 0;
+    bool producing = true;
+    while (producing) {
+        // ---- produce candidates (32-bit codes of kernels.cuh)
+        int cnt = 0;
+        while (cnt + 32 <= S::kCandCap) {
+            bool hit = false;
+            unsigned int code = 0;
+            if (pair_base < n_pairs) {
+                const int i = pair_base + lane;
+                pair_base += 32;
+                if (i < n_pairs) {
+                    const unsigned pc = pairs[i];
+                    const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
+                    hit = aabb_overlap(aabb[a], aabb[b]);
+                    if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
+                    code = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
+                }
+            } else if (cell_it < max_cells) {
+                const int it = cell_it++;
+                if (it < n_cells) {
+                    const int cx = cx0 + it % wx, cy = cy0 + it / wx;
+                    const int sl = __ldg(st_grid + cy * gw + cx);
+                    if (sl >= 0) {
+                        hit = aabb_overlap(mybb, ldg_d4(st_aabb + sl));
+                        code = (unsigned)lane | ((unsigned)sl << 12) | kCodeStatic;
+                    }
+                }
+            } else {
+                producing = false;
+                break;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
+            cnt += __popc(m);
+        }
+        __syncwarp();
+        if (dbg_row) {
+            for (int i = lane; i < cnt; i += 32)
+                if (dbg_off + i < dbg_cap) dbg_row[dbg_off + i] = cand[i];
+            dbg_off += cnt;
+            if (lane == 0) *dbg_n = dbg_off;
+        }
+        // ---- consume: prefilter into survivors, resolve, apply
+        int next_cc = 0;
+        bool more = true;
+        while (more) {
+            int scnt = 0;
+            while (scnt + 32 <= S::kSurvCap) {
+                bool hit = false;
+                unsigned int code = 0;
+                if (next_ic * 32 < n_items) {
+                    // non-shared corners of leaf pairs that share a point
+                    const int i = next_ic * 32 + lane;
+                    next_ic++;
+                    if (i < n_items) {
+                        const unsigned ic = items[i];
+                        const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
+                        code = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
+                        hit = point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
+                    }
+                } else if (next_cc * 32 < cnt * 8) {
+                    // the 8 corners of each candidate pair (these pairs share no point)
+                    const int i = next_cc * 32 + lane;
+                    next_cc++;
+                    if (i < cnt * 8) {
+                        const unsigned int cc = cand[i >> 3];
+                        const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
+                        const bool b_static = (cc & kCodeStatic) != 0;
+                        const int dir = (i >> 2) & 1, corner = i & 3;
+                        const unsigned same = (cc & kCodeSameObj) ? kItemSameObj : 0u;
+                        if (dir == 0) {
+                            code = a | (b << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
+                            const double4 bb = b_static ? ldg_d4(st_aabb + b) : aabb[b];
+                            hit = point_in_box(pos[(lpt[a] >> (8 * corner)) & 0xff], bb);
+                        } else {
+                            code = b | (a << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
+                            const double2 pp = b_static ? __ldg(H->st_pos + __ldg(&H->st_leaf[b].pt[corner]))
+                                                        : pos[(lpt[b] >> (8 * corner)) & 0xff];
+                            hit = point_in_box(pp, aabb[a]);
+                        }
+                    }
+                } else {
+                    more = false;
+                    break;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
+                scnt += __popc(m);
+            }
+            __syncwarp();
+            if (scnt > 0) {
+                PointSrc src;
+                src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = H->st_pos;
+                for (int base = 0; base < scnt; base += 32) {
+                    const int i = base + lane;
+                    bool has = false;
+                    Contact c;
+                    int reps = 1;
+                    if (i < scnt) {
+                        const unsigned code = surv[i];
+                        const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
+                        reps = (code & kItemSameObj) ? 2 : 1;
+                        LeafRec lm, lr;
+                        load_leaf(lm, H->g_leaf, H->st_leaf, code & kCodeLeafMask, m_static);
+                        load_leaf(lr, H->g_leaf, H->st_leaf, (code >> 12) & kCodeLeafMask, r_static);
+                        has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
+                    }
+                    unsigned m = __ballot_sync(0xffffffffu, has);
+                    while (m) {                           // deterministic, race-free: lanes in order
+                        const int l = __ffs(m) - 1;
+                        if (lane == l) apply_contact(cf, c, reps);
+                        m &= m - 1;
+                        __syncwarp();
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    // K6a: unstable test uses the boxes of the START of this substep (a-12)
+    return __any_sync(0xffffffffu, lane < 8 && misc[lane] > misc[8 + lane]);
+}
+
+// =================================================================================== phase 2: actuators + RK4
+// PhysicsEngine::update_actuators + step_rk4 + get_pos_vel_slope (SURVEY 8a-7,8,9).  On return spos holds the new
+// positions (pos still holds the substep's start positions = pos_last) and vel the new velocities.
+template <class S>
+__device__ __noinline__ void warp_rk4(unsigned char* sm, unsigned fixmask) {
+    const int lane = threadIdx.x & 31;
+    const WarpHdr* H = reinterpret_cast<const WarpHdr*>(sm + S::o_hdr);
+    double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
+    double2* spos = reinterpret_cast<double2*>(sm + S::o_spos);
+    double2* vel = reinterpret_cast<double2*>(sm + S::o_vel);
+    double2* svel = reinterpret_cast<double2*>(sm + S::o_svel);
+    const double2* cf = reinterpret_cast<const double2*>(sm + S::o_cf);
+    double2* accp = reinterpret_cast<double2*>(sm + S::o_accp);
+    double2* accv = reinterpret_cast<double2*>(sm + S::o_accv);
+    const uint4* csr = reinterpret_cast<const uint4*>(sm + S::o_csr);
+    double2* ef2 = reinterpret_cast<double2*>(sm + S::o_ef2);
+    double* leq = reinterpret_cast<double*>(sm + S::o_leq);
+    const double* goal = reinterpret_cast<const double*>(sm + S::o_goal);
+    const double2* etab = reinterpret_cast<const double2*>(sm + S::o_etab);
+    const uint32_t* eidx = reinterpret_cast<const uint32_t*>(sm + S::o_eidx);
+    const int Pd = H->Pd, Ed = H->Ed;
+
+    // length_eq: two edges per lane per trip, e and e + 32 (the second clamped, its store predicated)
+    for (int e0 = lane; e0 < Ed; e0 += 64) {
+        const int e1 = e0 + 32;
+        const bool v1 = e1 < Ed;
+        const int e1c = v1 ? e1 : e0;
+        const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
+        const double2 a0 = pos[i0 & 0xff], b0 = pos[(i0 >> 8) & 0xff];
+        const double2 a1 = pos[i1 & 0xff], b1 = pos[(i1 >> 8) & 0xff];
+        const double dx0 = a0.x - b0.x, dy0 = a0.y - b0.y;
+        const double dx1 = a1.x - b1.x, dy1 = a1.y - b1.y;
+        const double d0 = sqrt(dx0 * dx0 + dy0 * dy0);
+        const double d1 = sqrt(dx1 * dx1 + dy1 * dy1);
+        const double add0 = (goal[e0] - d0) * 0.006;
+        const double add1 = (goal[e1c] - d1) * 0.006;
+        leq[e0] = d0 + add0;
+        if (v1) leq[e1] = d1 + add1;
+    }
+    // length_eq[e] is written and read by the same lane: no barrier needed
+#pragma unroll 1
+    for (int s = 0; s < 4; s++) {
+        const double2* sp = (s == 0) ? pos : spos;
+        const double2* sv = (s == 0) ? vel : svel;
+        for (int e0 = lane; e0 < Ed; e0 += 64) {
+            const int e1 = e0 + 32;
+            const bool v1 = e1 < Ed;
+            const int e1c = v1 ? e1 : e0;
+            const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
+            const double2 f0 = spring_force(sp, i0, etab[(i0 >> kEidxTypeShift) & 15].x, leq[e0]);
+            const double2 f1 = spring_force(sp, i1, etab[(i1 >> kEidxTypeShift) & 15].x, leq[e1c]);
+            ef2[2 * e0] = make_double2(flip_sign(f0.x), flip_sign(f0.y));
+            ef2[2 * e0 + 1] = f0;
+            if (v1) {
+                ef2[2 * e1] = make_double2(flip_sign(f1.x), flip_sign(f1.y));
+                ef2[2 * e1 + 1] = f1;
+            }
+        }
+        __syncwarp();
+        for (int p = lane, k = 0; p < Pd; p += 32, k++) {
+            const double2 v = sv[p];
+            double Fx = 0.0, Fy = 0.0;
+            {
+                // F -= f over the a sides in edge order, then F += f over the b sides (PhysicsEngine.cpp:530-531): the
+                // record lists them in that order, the sign is in the stored value, empty slots read zero
+                const uint4 rec = csr[p];
+                const unsigned w[4] = {rec.x, rec.y, rec.z, rec.w};
+#pragma unroll
+                for (int half = 0; half < 2; half++) {
+                    double2 f[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int q = 4 * half + j;
+                        const unsigned ent = (w[q >> 1] >> ((q & 1) * 16)) & 0xffffu;
+                        f[j] = ef2[min(ent, (unsigned)S::kZero)];
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; j++) { Fx += f[j].x; Fy += f[j].y; }
+                }
+            }
+            Fx += v.x * (-MEVO_VISCOUS_DRAG);
+            Fy += v.y * (-MEVO_VISCOUS_DRAG);
+            Fy += 1.0 * (-MEVO_GRAVITY);                    // every point mass is 1.0 (host-checked), F / m == F
+            const double2 c = cf[p];
+            Fx += c.x; Fy += c.y;
+            const double y = sp[p].y;
+            if (y < 0) {                                    // analytic ground plane y = 0 (PhysicsEngine.cpp:566-577)
+                const double normal_force = y * (-MEVO_COLLISION_CONST_GROUND);
+                Fy += normal_force;
+                const double friction_temp = ground_friction_tanh(v.x * normal_force * MEVO_DYN_FRICTION);
+                Fx += (-10 * MEVO_DYN_FRICTION) * (normal_force * friction_temp);
+            }
+            const double kpx = v.x * MEVO_DT, kpy = v.y * MEVO_DT;
+            const double kvx = Fx * MEVO_DT, kvy = Fy * MEVO_DT;
+            const double2 x0 = pos[p], v0 = vel[p];
+            if (s == 0) {
+                accp[p] = make_double2(kpx, kpy);
+                accv[p] = make_double2(kvx, kvy);
+                spos[p] = make_double2(x0.x + (kpx * 0.5), x0.y + (kpy * 0.5));
+                svel[p] = make_double2(v0.x + (kvx * 0.5), v0.y + (kvy * 0.5));
+            } else if (s < 3) {
+                double2 q = accp[p]; q.x = q.x + 2 * kpx; q.y = q.y + 2 * kpy; accp[p] = q;
+                q = accv[p]; q.x = q.x + 2 * kvx; q.y = q.y + 2 * kvy; accv[p] = q;
+                const double h = (s == 1) ? 0.5 : 1.0;      // x * 1.0 == x exactly
+                spos[p] = make_double2(x0.x + (kpx * h), x0.y + (kpy * h));
+                svel[p] = make_double2(v0.x + (kvx * h), v0.y + (kvy * h));
+            } else {
+                const double2 qp = accp[p], qv = accv[p];
+                double dpx = (qp.x + kpx) / 6, dpy = (qp.y + kpy) / 6;
+                double dvx = (qv.x + kvx) / 6, dvy = (qv.y + kvy) / 6;
+                if ((fixmask >> k) & 1u) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
+                // the new position goes to spos: pos keeps the substep's start position (= pos_last)
+                spos[p] = make_double2(x0.x + dpx, x0.y + dpy);
+                vel[p] = make_double2(v0.x + dvx, v0.y + dvy);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// =================================================================================== phase 3: limiters + true velocity
+// PhysicsEngine::resolve_edge_constraints + update_true_vel (SURVEY 8a-10,11) on the new positions in spos.
+// Band test on squared lengths (no sqrt), guarded by 1e-7 so the decision never depends on the rounding of
+// dist / L0: inside the band every correction of the reference is exactly zero.
+template <class S>
+__device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask, bool first_substep) {
+    const int lane = threadIdx.x & 31;
+    const WarpHdr* H = reinterpret_cast<const WarpHdr*>(sm + S::o_hdr);
+    double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
+    double2* spos = reinterpret_cast<double2*>(sm + S::o_spos);
+    double2* vt = reinterpret_cast<double2*>(sm + S::o_vt);
+    const uint4* csr = reinterpret_cast<const uint4*>(sm + S::o_csr);
+    double2* ef2 = reinterpret_cast<double2*>(sm + S::o_ef2);
+    const double2* etab = reinterpret_cast<const double2*>(sm + S::o_etab);
+    const uint32_t* eidx = reinterpret_cast<const uint32_t*>(sm + S::o_eidx);
+    const uint8_t* rord = reinterpret_cast<const uint8_t*>(sm + S::o_rord);
+    const int Pd = H->Pd, Ed = H->Ed, n_vis = H->n_vis;
+
+    bool jviol = false, rviol = false;
+    for (int e = lane; e < Ed; e += 32) {
+        const uint32_t ix = eidx[e];
+        const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
+        const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+        const double d2 = dx * dx + dy * dy;
+        const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
+        const double l2 = l0 * l0;
+        if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) jviol = true;
+        if (((ix >> kEidxRigidBit) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) rviol = true;
+    }
+    const bool anyj = __any_sync(0xffffffffu, jviol);
+    if (anyj) warp_jacobi_limiter(spos, ef2, eidx, etab, csr, Pd, Ed, fixmask, S::kZero);
+    if (n_vis > 0 && (anyj || __any_sync(0xffffffffu, rviol))) {
+        // ordered rigid-cell pass (PhysicsEngine.cpp:675-710): a visit inside the +-3 % band changes nothing, so
+        // jump from one violating visit to the next; each is applied exactly by one lane and the visits after it
+        // are re-tested against the updated positions
+        int start = 0;
+        while (start < n_vis) {
+            int first = -1;
+            for (int c = start & ~31; c < n_vis; c += 32) {
+                const int i = c + lane;
+                bool v = false;
+                if (i >= start && i < n_vis) {
+                    const uint32_t ix = eidx[rord[i]];
+                    const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
+                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                    const double d2 = dx * dx + dy * dy;
+                    const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
+                    const double l2 = l0 * l0;
+                    v = !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, v);
+                if (m) { first = c + __ffs(m) - 1; break; }
+            }
+            if (first < 0) break;
+            if (lane == (first & 31)) {
+                const uint32_t ix = eidx[rord[first]];
+                rigid_visit_exact(spos, ix & 0xff, (ix >> 8) & 0xff, etab[(ix >> kEidxTypeShift) & 15].y);
+            }
+            __syncwarp();
+            start = first + 1;
+        }
+    }
+    for (int p = lane; p < Pd; p += 32) {                // PhysicsEngine::update_true_vel (:602-607)
+        const double2 x = spos[p];
+        // pos_last == pos at the start of every substep except possibly the first of a launch
+        const double2 l = first_substep ? H->g_last[p] : pos[p];
+        vt[p] = make_double2((x.x - l.x) / MEVO_DT, (x.y - l.y) / MEVO_DT);
+        pos[p] = x;
+    }
+    __syncwarp();
+}
+
+// =================================================================================== the kernel
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams prm) {
     using S = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>;
@@ -133,55 +533,51 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     const bool ghost = slot >= prm.n_class_envs;      // shadows the last environment, writes nothing back
     if (ghost) slot = prm.n_class_envs - 1;
     const int env = prm.class_envs[slot];
-    const EnvDesc ed = prm.envs[env];
-    const uint8_t* db = prm.design + ed.design_off;
-    const DesignHeader* Hp = reinterpret_cast<const DesignHeader*>(db);
-    const int Pd = Hp->Pd, Ed = Hp->Ed, n_leaf = Hp->n_leaf;
-    const int n_pairs = Hp->n_pairs, n_items = Hp->n_items, n_vis = Hp->n_rvis;
-    const bool has_static = ed.static_off != ~0ull;
-    const uint8_t* sb = prm.statics + (has_static ? ed.static_off : 0);
-    const StaticHeader* SHp = reinterpret_cast<const StaticHeader*>(sb);
-    const double2* st_pos = reinterpret_cast<const double2*>(sb + (has_static ? SHp->o_pos : 0));
-    const LeafRec* st_leaf = reinterpret_cast<const LeafRec*>(sb + (has_static ? SHp->o_leaf : 0));
-    const double4* st_aabb = reinterpret_cast<const double4*>(sb + (has_static ? SHp->o_aabb : 0));
-    const LeafRec* g_leaf = reinterpret_cast<const LeafRec*>(db + Hp->o_leaf);     // full records: resolver only
-
     unsigned char* sm = smem_raw + grp * S::kBytes;
-    double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
-    double2* spos = reinterpret_cast<double2*>(sm + S::o_spos);
-    double2* vel = reinterpret_cast<double2*>(sm + S::o_vel);
-    double2* svel = reinterpret_cast<double2*>(sm + S::o_svel);
-    double2* vt = reinterpret_cast<double2*>(sm + S::o_vt);
-    double2* cf = reinterpret_cast<double2*>(sm + S::o_cf);
-    double2* accp = reinterpret_cast<double2*>(sm + S::o_accp);
-    double2* accv = reinterpret_cast<double2*>(sm + S::o_accv);
-    uint4* csr = reinterpret_cast<uint4*>(sm + S::o_csr);
-    double2* ef2 = reinterpret_cast<double2*>(sm + S::o_ef2);
-    double* leq = reinterpret_cast<double*>(sm + S::o_leq);
-    double* goal = reinterpret_cast<double*>(sm + S::o_goal);
-    double2* etab = reinterpret_cast<double2*>(sm + S::o_etab);
-    double4* aabb = reinterpret_cast<double4*>(sm + S::o_aabb);
-    uint32_t* eidx = reinterpret_cast<uint32_t*>(sm + S::o_eidx);
-    uint32_t* lpt = reinterpret_cast<uint32_t*>(sm + S::o_lpt);
-    unsigned int* cand = reinterpret_cast<unsigned int*>(sm + S::o_cand);
-    unsigned int* surv = reinterpret_cast<unsigned int*>(sm + S::o_surv);
-    uint16_t* pairs = reinterpret_cast<uint16_t*>(sm + S::o_pairs);
-    uint16_t* items = reinterpret_cast<uint16_t*>(sm + S::o_items);
-    uint8_t* rord = reinterpret_cast<uint8_t*>(sm + S::o_rord);
-    volatile int* misc = reinterpret_cast<volatile int*>(sm + S::o_misc);
+    double* gstate;
+    unsigned fixmask = 0;                               // bit k: point lane + 32 k is fixed
 
     // ---------------------------------------------------------------- stage in (once per launch)
-    double* gstate = prm.state + ed.state_off;
-    const double2* g2 = reinterpret_cast<const double2*>(gstate);
-    unsigned fixmask = 0;                               // bit k: point lane + 32 k is fixed
-    for (int i = lane, k = 0; i < Pd; i += 32, k++) {
-        pos[i] = g2[i];
-        vel[i] = g2[Pd + i];
-        vt[i] = g2[3 * Pd + i];
-        csr[i] = __ldg(reinterpret_cast<const uint4*>(db + Hp->o_csr8) + i);
-        if (__ldg(db + Hp->o_fixed + i)) fixmask |= 1u << k;
-    }
     {
+        const EnvDesc ed = prm.envs[env];
+        const uint8_t* db = prm.design + ed.design_off;
+        const DesignHeader* Hp = reinterpret_cast<const DesignHeader*>(db);
+        const int Pd = Hp->Pd, Ed = Hp->Ed, n_leaf = Hp->n_leaf;
+        const int n_pairs = Hp->n_pairs, n_items = Hp->n_items, n_vis = Hp->n_rvis;
+        gstate = prm.state + ed.state_off;
+        const double2* g2 = reinterpret_cast<const double2*>(gstate);
+        const LeafRec* g_leaf = reinterpret_cast<const LeafRec*>(db + Hp->o_leaf);
+        if (lane == 0) {
+            WarpHdr* H = reinterpret_cast<WarpHdr*>(sm + S::o_hdr);
+            H->Pd = Pd; H->Ed = Ed; H->n_leaf = n_leaf; H->n_pairs = n_pairs; H->n_items = n_items; H->n_vis = n_vis;
+            H->g_leaf = g_leaf;
+            H->g_last = g2 + 2 * Pd;
+            if (ed.static_off != ~0ull) {
+                const uint8_t* sb = prm.statics + ed.static_off;
+                const StaticHeader* SHp = reinterpret_cast<const StaticHeader*>(sb);
+                H->gx0 = SHp->gx0; H->gy0 = SHp->gy0; H->gw = SHp->gw; H->gh = SHp->gh;
+                H->st_grid = reinterpret_cast<const int16_t*>(sb + SHp->o_grid);
+                H->st_aabb = reinterpret_cast<const double4*>(sb + SHp->o_aabb);
+                H->st_pos = reinterpret_cast<const double2*>(sb + SHp->o_pos);
+                H->st_leaf = reinterpret_cast<const LeafRec*>(sb + SHp->o_leaf);
+            } else {
+                H->gx0 = H->gy0 = H->gw = H->gh = 0;
+                H->st_grid = nullptr; H->st_aabb = nullptr; H->st_pos = nullptr; H->st_leaf = nullptr;
+            }
+        }
+        double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
+        double2* vel = reinterpret_cast<double2*>(sm + S::o_vel);
+        double2* vt = reinterpret_cast<double2*>(sm + S::o_vt);
+        uint4* csr = reinterpret_cast<uint4*>(sm + S::o_csr);
+        for (int i = lane, k = 0; i < Pd; i += 32, k++) {
+            pos[i] = g2[i];
+            vel[i] = g2[Pd + i];
+            vt[i] = g2[3 * Pd + i];
+            csr[i] = __ldg(reinterpret_cast<const uint4*>(db + Hp->o_csr8) + i);
+            if (__ldg(db + Hp->o_fixed + i)) fixmask |= 1u << k;
+        }
+        double* goal = reinterpret_cast<double*>(sm + S::o_goal);
+        uint32_t* eidx = reinterpret_cast<uint32_t*>(sm + S::o_eidx);
         const double* ggoal = gstate + 8 * (size_t)Pd;
         const int16_t* eact = reinterpret_cast<const int16_t*>(db + Hp->o_eact);
         const double* act = prm.act + (size_t)env * prm.act_stride;
@@ -201,15 +597,21 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             goal[e] = g;
             eidx[e] = __ldg(reinterpret_cast<const uint32_t*>(db + Hp->o_eidx) + e);
         }
+        double2* etab = reinterpret_cast<double2*>(sm + S::o_etab);
         if (lane < Hp->n_types) etab[lane] = __ldg(reinterpret_cast<const double2*>(db + Hp->o_etab) + lane);
-        if (lane == 0) ef2[S::kZero] = make_double2(0.0, 0.0);
+        if (lane == 0) reinterpret_cast<double2*>(sm + S::o_ef2)[S::kZero] = make_double2(0.0, 0.0);
+        uint32_t* lpt = reinterpret_cast<uint32_t*>(sm + S::o_lpt);
         if (lane < n_leaf) {
             const LeafRec r = g_leaf[lane];
             lpt[lane] = (uint32_t)r.pt[0] | ((uint32_t)r.pt[1] << 8) | ((uint32_t)r.pt[2] << 16) | ((uint32_t)r.pt[3] << 24);
         }
+        uint16_t* pairs = reinterpret_cast<uint16_t*>(sm + S::o_pairs);
+        uint16_t* items = reinterpret_cast<uint16_t*>(sm + S::o_items);
+        uint8_t* rord = reinterpret_cast<uint8_t*>(sm + S::o_rord);
         for (int i = lane; i < n_pairs; i += 32) pairs[i] = __ldg(reinterpret_cast<const uint16_t*>(db + Hp->o_pairs16) + i);
         for (int i = lane; i < n_items; i += 32) items[i] = __ldg(reinterpret_cast<const uint16_t*>(db + Hp->o_items16) + i);
         for (int i = lane; i < n_vis; i += 32) rord[i] = __ldg(db + Hp->o_rord8 + i);
+        volatile int* misc = reinterpret_cast<volatile int*>(sm + S::o_misc);
         if (lane < 8) {
             int ns = 0x7fffffff;                        // never "unstable" unless a robot (PhysicsEngine.cpp:819-834)
             if (lane < Hp->n_obj) {
@@ -221,339 +623,22 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     }
     __syncwarp();
 
-    PointSrc src;
-    src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = st_pos;
-
     int unstable = 0;
     int completed_steps = 0;
     bool first_substep = true;
+    const bool dbg = prm.dbg_cand != nullptr && !ghost;
 
     for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
             // keeps the CTA's warps in the same code region: they share instruction-cache lines
-            if (EPC > 1 && prm.cta_sync > 0 && (sub % prm.cta_sync) == 0) __syncthreads();
+            if (EPC > 1 && prm.cta_sync) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
-
-            // ======================================================= K2a: leaf boxes (a-4), zero collision_forces
-            if (lane < n_leaf) {
-                const uint32_t lp = lpt[lane];
-                double2 q = pos[lp & 0xff];
-                double minx = q.x, maxx = q.x, miny = q.y, maxy = q.y;
-#pragma unroll
-                for (int c = 1; c < 4; c++) {
-                    q = pos[(lp >> (8 * c)) & 0xff];
-                    minx = fmin(minx, q.x); maxx = fmax(maxx, q.x);
-                    miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
-                }
-                aabb[lane] = make_double4(minx, miny, maxx, maxy);
-            }
-            for (int i = lane; i < Pd; i += 32) cf[i] = make_double2(0.0, 0.0);
-            if (lane < 8) misc[lane] = 0;
-            __syncwarp();
-
-            // ======================================================= K2b + K3: broad phase, narrow phase, contacts
-            // Producer: tested leaf pairs (pair table) and terrain cells under each leaf -> overlapping pairs are
-            //           compacted (ballot + popc) into a small candidate buffer.
-            // Consumer: every (corner, boxel) item of the candidates, plus the non-shared corners of leaf pairs
-            //           that share a point (always candidates), passes the box prefilter -- a necessary condition
-            //           of Boxel::point_in_boxel -- into a survivor buffer; survivors go through the out-of-line
-            //           resolver and their contacts are applied in list order.
-            // Both buffers are drained whenever they fill, so no configuration can overflow them.
-            {
-                int gx0 = 0, gy0 = 0, gw = 0, gh = 0;
-                const int16_t* st_grid = nullptr;
-                int cx0 = 0, cy0 = 0, wx = 1, n_cells = 0, max_cells = 0;
-                double4 mybb = make_double4(0, 0, 0, 0);
-                if (has_static) {
-                    gx0 = SHp->gx0; gy0 = SHp->gy0; gw = SHp->gw; gh = SHp->gh;
-                    st_grid = reinterpret_cast<const int16_t*>(sb + SHp->o_grid);
-                    if (lane < n_leaf) {
-                        mybb = aabb[lane];
-                        // static leaf in lattice cell c spans [c, c+1] * 0.1: only ceil(min*10 - 1) <= c <= floor(max*10)
-                        // can pass the closed-interval test; 1e-6 cells of slack, the exact test decides
-                        cx0 = max((int)ceil(mybb.x * 10.0 - 1.000001) - gx0, 0);
-                        const int cx1 = min((int)floor(mybb.z * 10.0 + 0.000001) - gx0, gw - 1);
-                        cy0 = max((int)ceil(mybb.y * 10.0 - 1.000001) - gy0, 0);
-                        const int cy1 = min((int)floor(mybb.w * 10.0 + 0.000001) - gy0, gh - 1);
-                        wx = cx1 - cx0 + 1;
-                        const int wy = cy1 - cy0 + 1;
-                        n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
-                        if (n_cells == 0) wx = 1;
-                    }
-                    max_cells = __reduce_max_sync(0xffffffffu, n_cells);
-                }
-                int pair_base = 0, cell_it = 0, next_ic = 0, dbg_off = 0;
-                bool producing = true;
-                while (producing) {
-                    // ---- produce candidates (32-bit codes of kernels.cuh)
-                    int cnt = 0;
-                    while (cnt + 32 <= S::kCandCap) {
-                        bool hit = false;
-                        unsigned int code = 0;
-                        if (pair_base < n_pairs) {
-                            const int i = pair_base + lane;
-                            pair_base += 32;
-                            if (i < n_pairs) {
-                                const unsigned pc = pairs[i];
-                                const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
-                                hit = aabb_overlap(aabb[a], aabb[b]);
-                                if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
-                                code = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
-                            }
-                        } else if (cell_it < max_cells) {
-                            const int it = cell_it++;
-                            if (it < n_cells) {
-                                const int cx = cx0 + it % wx, cy = cy0 + it / wx;
-                                const int sl = __ldg(st_grid + cy * gw + cx);
-                                if (sl >= 0) {
-                                    hit = aabb_overlap(mybb, ldg_d4(st_aabb + sl));
-                                    code = (unsigned)lane | ((unsigned)sl << 12) | kCodeStatic;
-                                }
-                            }
-                        } else {
-                            producing = false;
-                            break;
-                        }
-                        const unsigned m = __ballot_sync(0xffffffffu, hit);
-                        if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
-                        cnt += __popc(m);
-                    }
-                    __syncwarp();
-                    if (prm.dbg_cand && step == 0 && sub == 0 && !ghost) {
-                        for (int i = lane; i < cnt; i += 32)
-                            if (dbg_off + i < prm.dbg_cand_cap) prm.dbg_cand[(size_t)env * prm.dbg_cand_cap + dbg_off + i] = cand[i];
-                        dbg_off += cnt;
-                        if (lane == 0) prm.dbg_cand_n[env] = dbg_off;
-                    }
-                    // ---- consume: prefilter into survivors, resolve, apply
-                    int next_cc = 0;
-                    bool more = true;
-                    while (more) {
-                        int scnt = 0;
-                        while (scnt + 32 <= S::kSurvCap) {
-                            bool hit = false;
-                            unsigned int code = 0;
-                            if (next_ic * 32 < n_items) {
-                                // non-shared corners of leaf pairs that share a point
-                                const int i = next_ic * 32 + lane;
-                                next_ic++;
-                                if (i < n_items) {
-                                    const unsigned ic = items[i];
-                                    const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
-                                    code = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
-                                    hit = point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
-                                }
-                            } else if (next_cc * 32 < cnt * 8) {
-                                // the 8 corners of each candidate pair (these pairs share no point)
-                                const int i = next_cc * 32 + lane;
-                                next_cc++;
-                                if (i < cnt * 8) {
-                                    const unsigned int cc = cand[i >> 3];
-                                    const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
-                                    const bool b_static = (cc & kCodeStatic) != 0;
-                                    const int dir = (i >> 2) & 1, corner = i & 3;
-                                    const unsigned same = (cc & kCodeSameObj) ? kItemSameObj : 0u;
-                                    if (dir == 0) {
-                                        code = a | (b << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
-                                        const double4 bb = b_static ? ldg_d4(st_aabb + b) : aabb[b];
-                                        hit = point_in_box(pos[(lpt[a] >> (8 * corner)) & 0xff], bb);
-                                    } else {
-                                        code = b | (a << 12) | ((unsigned)corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
-                                        const double2 pp = b_static ? __ldg(st_pos + __ldg(&st_leaf[b].pt[corner]))
-                                                                    : pos[(lpt[b] >> (8 * corner)) & 0xff];
-                                        hit = point_in_box(pp, aabb[a]);
-                                    }
-                                }
-                            } else {
-                                more = false;
-                                break;
-                            }
-                            const unsigned m = __ballot_sync(0xffffffffu, hit);
-                            if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
-                            scnt += __popc(m);
-                        }
-                        __syncwarp();
-                        for (int base = 0; base < scnt; base += 32) {
-                            const int i = base + lane;
-                            bool has = false;
-                            Contact c;
-                            int reps = 1;
-                            if (i < scnt) {
-                                const unsigned code = surv[i];
-                                const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
-                                reps = (code & kItemSameObj) ? 2 : 1;
-                                LeafRec lm, lr;
-                                load_leaf(lm, g_leaf, st_leaf, code & kCodeLeafMask, m_static);
-                                load_leaf(lr, g_leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
-                                has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
-                            }
-                            unsigned m = __ballot_sync(0xffffffffu, has);
-                            while (m) {                   // deterministic, race-free: lanes in order
-                                const int l = __ffs(m) - 1;
-                                if (lane == l) apply_contact(cf, c, reps);
-                                m &= m - 1;
-                                __syncwarp();
-                            }
-                        }
-                        __syncwarp();
-                    }
-                }
-            }
-            // K6a: unstable test uses the boxes of the START of this substep (a-12)
-            const int sub_unstable = __any_sync(0xffffffffu, lane < 8 && misc[lane] > misc[8 + lane]);
-
-            // ======================================================= K4: actuators + RK4 (a-7, a-8, a-9)
-            // two edges per lane per trip: e and e + 32 (the second clamped and its stores predicated)
-            for (int e0 = lane; e0 < Ed; e0 += 64) {
-                const int e1 = e0 + 32;
-                const bool v1 = e1 < Ed;
-                const int e1c = v1 ? e1 : e0;
-                const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
-                const double2 a0 = pos[i0 & 0xff], b0 = pos[(i0 >> 8) & 0xff];
-                const double2 a1 = pos[i1 & 0xff], b1 = pos[(i1 >> 8) & 0xff];
-                const double dx0 = a0.x - b0.x, dy0 = a0.y - b0.y;
-                const double dx1 = a1.x - b1.x, dy1 = a1.y - b1.y;
-                const double d0 = sqrt(dx0 * dx0 + dy0 * dy0);
-                const double d1 = sqrt(dx1 * dx1 + dy1 * dy1);
-                const double add0 = (goal[e0] - d0) * 0.006;
-                const double add1 = (goal[e1c] - d1) * 0.006;
-                leq[e0] = d0 + add0;
-                if (v1) leq[e1] = d1 + add1;
-            }
-            // length_eq[e] is written and read by the same lane: no barrier needed
-#pragma unroll 1
-            for (int s = 0; s < 4; s++) {
-                const double2* sp = (s == 0) ? pos : spos;
-                const double2* sv = (s == 0) ? vel : svel;
-                for (int e0 = lane; e0 < Ed; e0 += 64) {
-                    const int e1 = e0 + 32;
-                    const bool v1 = e1 < Ed;
-                    const int e1c = v1 ? e1 : e0;
-                    const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
-                    const double2 f0 = spring_force(sp, i0, etab[(i0 >> kEidxTypeShift) & 15].x, leq[e0]);
-                    const double2 f1 = spring_force(sp, i1, etab[(i1 >> kEidxTypeShift) & 15].x, leq[e1c]);
-                    ef2[2 * e0] = make_double2(flip_sign(f0.x), flip_sign(f0.y));
-                    ef2[2 * e0 + 1] = f0;
-                    if (v1) {
-                        ef2[2 * e1] = make_double2(flip_sign(f1.x), flip_sign(f1.y));
-                        ef2[2 * e1 + 1] = f1;
-                    }
-                }
-                __syncwarp();
-                for (int p = lane, k = 0; p < Pd; p += 32, k++) {
-                    const double2 v = sv[p];
-                    const double2 x = sp[p];
-                    double Fx = 0.0, Fy = 0.0;
-                    {
-                        // F -= f over the a sides in edge order, then F += f over the b sides (PhysicsEngine.cpp:530-531):
-                        // the record lists them in that order, the sign is in the stored value, empty slots read zero
-                        const uint4 rec = csr[p];
-                        const unsigned w[4] = {rec.x, rec.y, rec.z, rec.w};
-                        double2 f[8];
-#pragma unroll
-                        for (int j = 0; j < 8; j++) {
-                            const unsigned ent = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-                            f[j] = ef2[min(ent, (unsigned)S::kZero)];
-                        }
-#pragma unroll
-                        for (int j = 0; j < 8; j++) { Fx += f[j].x; Fy += f[j].y; }
-                    }
-                    Fx += v.x * (-MEVO_VISCOUS_DRAG);
-                    Fy += v.y * (-MEVO_VISCOUS_DRAG);
-                    Fy += 1.0 * (-MEVO_GRAVITY);            // every point mass is 1.0 (host-checked), F / m == F
-                    const double2 c = cf[p];
-                    Fx += c.x; Fy += c.y;
-                    if (x.y < 0) {                          // analytic ground plane y = 0 (PhysicsEngine.cpp:566-577)
-                        const double normal_force = x.y * (-MEVO_COLLISION_CONST_GROUND);
-                        Fy += normal_force;
-                        const double friction_temp = ground_friction_tanh(v.x * normal_force * MEVO_DYN_FRICTION);
-                        Fx += (-10 * MEVO_DYN_FRICTION) * (normal_force * friction_temp);
-                    }
-                    const double kpx = v.x * MEVO_DT, kpy = v.y * MEVO_DT;
-                    const double kvx = Fx * MEVO_DT, kvy = Fy * MEVO_DT;
-                    const double2 x0 = pos[p], v0 = vel[p];
-                    if (s == 0) {
-                        accp[p] = make_double2(kpx, kpy);
-                        accv[p] = make_double2(kvx, kvy);
-                        spos[p] = make_double2(x0.x + (kpx * 0.5), x0.y + (kpy * 0.5));
-                        svel[p] = make_double2(v0.x + (kvx * 0.5), v0.y + (kvy * 0.5));
-                    } else if (s < 3) {
-                        double2 q = accp[p]; q.x = q.x + 2 * kpx; q.y = q.y + 2 * kpy; accp[p] = q;
-                        q = accv[p]; q.x = q.x + 2 * kvx; q.y = q.y + 2 * kvy; accv[p] = q;
-                        const double h = (s == 1) ? 0.5 : 1.0;      // x * 1.0 == x exactly
-                        spos[p] = make_double2(x0.x + (kpx * h), x0.y + (kpy * h));
-                        svel[p] = make_double2(v0.x + (kvx * h), v0.y + (kvy * h));
-                    } else {
-                        const double2 qp = accp[p], qv = accv[p];
-                        double dpx = (qp.x + kpx) / 6, dpy = (qp.y + kpy) / 6;
-                        double dvx = (qv.x + kvx) / 6, dvy = (qv.y + kvy) / 6;
-                        if ((fixmask >> k) & 1u) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
-                        // the new position goes to spos: pos keeps the substep's start position (= pos_last)
-                        spos[p] = make_double2(x0.x + dpx, x0.y + dpy);
-                        vel[p] = make_double2(v0.x + dvx, v0.y + dvy);
-                    }
-                }
-                __syncwarp();
-            }
-
-            // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
-            // Band test on squared lengths (no sqrt), guarded by 1e-7 so the decision never depends on the rounding
-            // of dist / L0: inside the band every correction of the reference is exactly zero.
-            {
-                bool jviol = false, rviol = false;
-                for (int e = lane; e < Ed; e += 32) {
-                    const uint32_t ix = eidx[e];
-                    const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
-                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                    const double d2 = dx * dx + dy * dy;
-                    const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
-                    const double l2 = l0 * l0;
-                    if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) jviol = true;
-                    if (((ix >> kEidxRigidBit) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) rviol = true;
-                }
-                const bool anyj = __any_sync(0xffffffffu, jviol);
-                if (anyj) warp_jacobi_limiter(spos, ef2, eidx, etab, csr, Pd, Ed, fixmask, S::kZero);
-                if (n_vis > 0 && (anyj || __any_sync(0xffffffffu, rviol))) {
-                    // ordered rigid-cell pass (PhysicsEngine.cpp:675-710): a visit inside the +-3 % band changes
-                    // nothing, so jump from one violating visit to the next; each is applied exactly by one lane
-                    // and the visits after it are re-tested against the updated positions
-                    int start = 0;
-                    while (start < n_vis) {
-                        int first = -1;
-                        for (int c = start & ~31; c < n_vis; c += 32) {
-                            const int i = c + lane;
-                            bool v = false;
-                            if (i >= start && i < n_vis) {
-                                const uint32_t ix = eidx[rord[i]];
-                                const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
-                                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                                const double d2 = dx * dx + dy * dy;
-                                const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
-                                const double l2 = l0 * l0;
-                                v = !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999);
-                            }
-                            const unsigned m = __ballot_sync(0xffffffffu, v);
-                            if (m) { first = c + __ffs(m) - 1; break; }
-                        }
-                        if (first < 0) break;
-                        if (lane == (first & 31)) {
-                            const uint32_t ix = eidx[rord[first]];
-                            rigid_visit_exact(spos, ix & 0xff, (ix >> 8) & 0xff, etab[(ix >> kEidxTypeShift) & 15].y);
-                        }
-                        __syncwarp();
-                        start = first + 1;
-                    }
-                }
-            }
-            for (int p = lane; p < Pd; p += 32) {        // PhysicsEngine::update_true_vel (:602-607)
-                const double2 x = spos[p];
-                // pos_last == pos at the start of every substep except possibly the first of a launch
-                const double2 l = first_substep ? g2[2 * Pd + p] : pos[p];
-                vt[p] = make_double2((x.x - l.x) / MEVO_DT, (x.y - l.y) / MEVO_DT);
-                pos[p] = x;
-            }
+            const bool dump = dbg && step == 0 && sub == 0;
+            const int sub_unstable = warp_collide<S>(sm, dump ? prm.dbg_cand + (size_t)env * prm.dbg_cand_cap : nullptr,
+                                                     dump ? prm.dbg_cand_n + env : nullptr, prm.dbg_cand_cap);
+            warp_rk4<S>(sm, fixmask);
+            warp_constrain<S>(sm, fixmask, first_substep);
             first_substep = false;
-            __syncwarp();
             if (sub_unstable) unstable = 1;               // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
         }
         if (!unstable) completed_steps++;
@@ -561,15 +646,20 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
 
     // ---------------------------------------------------------------- stage out
     if (!ghost) {
+        const WarpHdr* H = reinterpret_cast<const WarpHdr*>(sm + S::o_hdr);
+        const int Pd = H->Pd, Ed = H->Ed;
         double2* o2 = reinterpret_cast<double2*>(gstate);
         if (unstable && prm.auto_reset) {
             // Sim::revert(0) in place (Environment.cpp:247-263)
-            const double2* s0 = reinterpret_cast<const double2*>(prm.state0 + ed.state_off);
+            const double2* s0 = reinterpret_cast<const double2*>(prm.state0 + (gstate - prm.state));
             for (int i = lane; i < Pd; i += 32) {
                 const double2 p0 = s0[i], v0 = s0[Pd + i];
                 o2[i] = p0; o2[Pd + i] = v0; o2[2 * Pd + i] = p0; o2[3 * Pd + i] = v0;
             }
         } else if (!first_substep) {
+            const double2* pos = reinterpret_cast<const double2*>(sm + S::o_pos);
+            const double2* vel = reinterpret_cast<const double2*>(sm + S::o_vel);
+            const double2* vt = reinterpret_cast<const double2*>(sm + S::o_vt);
             for (int i = lane; i < Pd; i += 32) {
                 const double2 x = pos[i];
                 o2[i] = x;
@@ -578,6 +668,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
                 o2[3 * Pd + i] = vt[i];
             }
         }
+        const double* goal = reinterpret_cast<const double*>(sm + S::o_goal);
         double* ggoal = gstate + 8 * (size_t)Pd;
         for (int e = lane; e < Ed; e += 32) ggoal[e] = goal[e];
         if (lane == 0) {
