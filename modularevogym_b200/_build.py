@@ -27,7 +27,7 @@ NVCC_FLAGS = [
 ]
 
 LIB_SOURCES = ["engine.cu", "c_api.cpp", "topology.cpp"]
-LIB_HEADERS = ["engine.h", "kernels.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
+LIB_HEADERS = ["engine.h", "kernels.cuh", "wkernel.cuh", "fkernel.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
 
 
 def _nvcc() -> str:
@@ -47,7 +47,8 @@ def _stale(target: str, deps: List[str]) -> bool:
 def build_lib(force: bool = False, verbose: bool = False) -> str:
     deps = [os.path.join(CSRC, s) for s in LIB_SOURCES + LIB_HEADERS]
     if force or _stale(LIB_PATH, deps):
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH] + \
+        extra = os.environ.get("MEVO_NVCC_EXTRA", "").split()          # development only (e.g. -DMEVO_PROF)
+        cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH] + \
               [os.path.join(CSRC, s) for s in LIB_SOURCES]
         if verbose:
             print(" ".join(cmd))

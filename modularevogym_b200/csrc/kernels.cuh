@@ -42,6 +42,7 @@ struct StepParams {
     uint8_t* unstable;
     int* sim_time;
     int* err;
+    unsigned int* env_cycles;   // per env: SM cycles its own work took in the last launch (scheduling hint)
     unsigned int* dbg_cand;     // optional: candidate codes of the first substep
     int* dbg_cand_n;
     int dbg_cand_cap;

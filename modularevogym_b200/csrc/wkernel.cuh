@@ -627,12 +627,14 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     int completed_steps = 0;
     bool first_substep = true;
     const bool dbg = prm.dbg_cand != nullptr && !ghost;
+    unsigned int work_cycles = 0;
 
     for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
             // keeps the CTA's warps in the same code region: they share instruction-cache lines
             if (EPC > 1 && prm.cta_sync) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
+            const unsigned int c0 = (unsigned int)clock64();
             const bool dump = dbg && step == 0 && sub == 0;
             const int sub_unstable = warp_collide<S>(sm, dump ? prm.dbg_cand + (size_t)env * prm.dbg_cand_cap : nullptr,
                                                      dump ? prm.dbg_cand_n + env : nullptr, prm.dbg_cand_cap);
@@ -640,6 +642,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             warp_constrain<S>(sm, fixmask, first_substep);
             first_substep = false;
             if (sub_unstable) unstable = 1;               // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
+            work_cycles += (unsigned int)clock64() - c0;
         }
         if (!unstable) completed_steps++;
     }
@@ -673,6 +676,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         for (int e = lane; e < Ed; e += 32) ggoal[e] = goal[e];
         if (lane == 0) {
             prm.unstable[env] = (uint8_t)unstable;
+            prm.env_cycles[env] = work_cycles;
             if (unstable && prm.auto_reset) prm.sim_time[env] = 0;
             else prm.sim_time[env] += completed_steps;
             if (unstable) atomicAdd(prm.unstable_events, 1ull);
