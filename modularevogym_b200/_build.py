@@ -27,7 +27,7 @@ NVCC_FLAGS = [
 ]
 
 LIB_SOURCES = ["engine.cu", "c_api.cpp", "topology.cpp"]
-LIB_HEADERS = ["engine.h", "kernels.cuh", "wkernel.cuh", "fkernel.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
+LIB_HEADERS = ["engine.h", "kernels.cuh", "wkernel.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
 
 
 def _nvcc() -> str:

@@ -74,8 +74,7 @@ struct DesignHeader {        // 128 bytes
     int n_types, o_etab;                      // distinct (spring constant, init_length_eq) pairs, double2 each
     int o_pairs16, o_items16, o_rord8;        // 16-bit pair / item codes, rigid-cell visits (u8 edge ids) in reference order
     int warp_ok;                              // every compact encoding above is valid for this design
-    int max_adeg, max_bdeg;                   // most edges one point is the a end / the b end of (flat kernel: <= 5 each)
-    int reserved[1];
+    int reserved[3];
 };
 static_assert(sizeof(DesignHeader) == 160, "DesignHeader must be 160 bytes");
 

@@ -14,7 +14,6 @@
 
 #include "kernels.cuh"
 #include "wkernel.cuh"
-#include "fkernel.cuh"
 
 namespace mevo {
 
@@ -46,16 +45,12 @@ int group_class_for(int Pd, int Ed) {
     return 6;
 }
 
-int class_for(const DesignHeader& H, bool use_warp_kernel, bool flat) {
+int class_for(const DesignHeader& H, bool use_warp_kernel) {
     if (use_warp_kernel && H.warp_ok && H.max_deg <= 8 && H.unit_mass && H.n_obj <= 8 && H.n_types <= 16) {
         const int caps[2][6] = {{MEVO_WCAPS_A}, {MEVO_WCAPS_B}};
         for (int c = 0; c < 2; c++)
             if (H.Pd <= caps[c][0] && H.Ed <= caps[c][1] && H.n_leaf <= caps[c][2] && H.n_pairs <= caps[c][3] &&
-                H.n_items <= caps[c][4] && H.n_rvis <= caps[c][5]) {
-                // class 0 runs the flat kernel, whose gather record holds <= 5 a sides and <= 5 b sides
-                if (c == 0 && flat && (H.max_adeg > 5 || H.max_bdeg > 5)) continue;
-                return c;
-            }
+                H.n_items <= caps[c][4] && H.n_rvis <= caps[c][5]) return c;
     }
     return group_class_for(H.Pd, H.Ed);
 }
@@ -97,8 +92,16 @@ void launch_step(const StepParams& prm, int smem_per_env, cudaStream_t stream) {
     step_kernel<G, EPC><<<grid, G * EPC, smem, stream>>>(prm);
 }
 
+// environments per CTA that make the launch a whole number of equally full waves (slots = CTAs resident at once)
+int balanced_envs_per_cta(int n_envs, int epc, int slots) {
+    const int ctas = (n_envs + epc - 1) / epc;
+    const int waves = (ctas + slots - 1) / slots;
+    const int per = (n_envs + waves * slots - 1) / (waves * slots);
+    return std::max(1, std::min(epc, per));
+}
+
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
-void launch_wstep(const StepParams& prm, cudaStream_t stream) {
+void launch_wstep(StepParams prm, int n_sm, bool balance, cudaStream_t stream) {
     constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
     static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
     static bool configured = false;
@@ -107,29 +110,9 @@ void launch_wstep(const StepParams& prm, cudaStream_t stream) {
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    const int grid = (prm.n_class_envs + EPC - 1) / EPC;
+    prm.envs_per_cta = balance ? balanced_envs_per_cta(prm.n_class_envs, EPC, n_sm * MINB) : EPC;
+    const int grid = (prm.n_class_envs + prm.envs_per_cta - 1) / prm.envs_per_cta;
     wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
-}
-
-// capacities of one flat CTA: threads, points, edges, leaves, pair codes, item codes, rigid visits, environments
-#define MEVO_FCAPS_256 256, 256, 768, 192, 1536, 2048, 896, 8
-#define MEVO_FCAPS_320 320, 320, 960, 200, 1600, 2048, 960, 10
-#define MEVO_FCAPS_512 512, 512, 1536, 384, 3072, 4096, 1792, 16
-
-struct FlatCaps { int nt, p, e, l, pr, it, v, ne; };
-
-template <int NT, int PMAX, int EMAX, int LMAX, int PRMAX, int ITMAX, int VMAX, int NEMAX, int MINB>
-void launch_fstep(const StepParams& prm, const CtaDesc* ctas, int n_ctas, cudaStream_t stream) {
-    constexpr int smem = FlatSmem<NT, PMAX, EMAX, LMAX, PRMAX, ITMAX, VMAX, NEMAX>::kBytes;
-    static_assert(smem <= kMaxSmemPerBlock, "flat kernel CTA does not fit in shared memory");
-    static_assert(PMAX <= 1024 && 2 * EMAX < 0xffff && NEMAX * 16 <= 2048, "flat index widths");
-    static bool configured = false;
-    if (!configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(fstep_kernel<NT, PMAX, EMAX, LMAX, PRMAX, ITMAX, VMAX, NEMAX, MINB>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
-    fstep_kernel<NT, PMAX, EMAX, LMAX, PRMAX, ITMAX, VMAX, NEMAX, MINB><<<n_ctas, NT, smem, stream>>>(prm, ctas);
 }
 
 __global__ void reset_kernel(double* state, const double* state0, const EnvDesc* envs, const uint8_t* design,
@@ -159,18 +142,12 @@ struct Batch::Impl {
     std::vector<EnvDesc> desc;
     std::vector<std::vector<double>> pos0, vel0;  // reset snapshot (global numbering)
     std::vector<int> env_cost;                    // per env: estimated work of one substep
-    struct Dims { int p, e, l, pr, it, v; };
-    std::vector<Dims> dims;                       // per env: sizes that count against a flat CTA's capacity
-    int flat = 0;                                 // 1: class 0 runs the experimental flat CTA kernel (fkernel.cuh) instead of the warp kernel
-    int flat_nt = 256;                            // threads of a flat CTA (256 or 512)
-    int flat_ne = 0;                              // environments per flat CTA (0 = the variant's capacity)
-    std::vector<CtaDesc> ctas;
-    CtaDesc* d_ctas = nullptr;
-    unsigned int* d_env_cycles = nullptr;
     bool use_warp_kernel = true;
     int wepc = 0;                                 // warp kernel: environments per CTA override (0 = default)
     int epc32 = 12;
     int cta_sync = 1;
+    int balance = 1;                              // warp kernel: environments per CTA chosen for equally full waves
+    int n_sm = 148;
     int* d_com_ranges = nullptr;
     double* d_com_out = nullptr;
     int com_obj = -1;
@@ -191,52 +168,16 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     if (const char* e = std::getenv("MEVO_NO_WKERNEL")) impl_->use_warp_kernel = std::atoi(e) == 0;
     if (const char* e = std::getenv("MEVO_WEPC")) impl_->wepc = std::atoi(e);
     if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
-    if (const char* e = std::getenv("MEVO_FLAT")) impl_->flat = std::atoi(e);
-    if (const char* e = std::getenv("MEVO_FLAT_NT")) {
-        const int v = std::atoi(e);
-        impl_->flat_nt = (v == 512 || v == 320) ? v : 256;
-    }
-    if (const char* e = std::getenv("MEVO_FLAT_NE")) impl_->flat_ne = std::atoi(e);
+    if (const char* e = std::getenv("MEVO_BALANCE")) impl_->balance = std::atoi(e);
+    CUDA_CHECK(cudaDeviceGetAttribute(&impl_->n_sm, cudaDevAttrMultiProcessorCount, device_));
 }
 
 Batch::~Batch() {
     cudaSetDevice(device_);
-#ifdef MEVO_PROF
-    if (impl_ && impl_->d_env_cycles && num_envs() > 8) {
-        std::vector<unsigned int> c(num_envs());
-        cudaMemcpy(c.data(), impl_->d_env_cycles, sizeof(unsigned int) * c.size(), cudaMemcpyDeviceToHost);
-        std::vector<unsigned int> srt(c);
-        std::sort(srt.begin(), srt.end());
-        double sum = 0;
-        for (unsigned int v : srt) sum += v;
-        const size_t m = srt.size();
-        std::fprintf(stderr, "[prof] env work cycles of the last launch: mean %.0f p10 %u p50 %u p90 %u p99 %u max %u\n", sum / m,
-                     srt[m / 10], srt[m / 2], srt[m * 9 / 10], srt[m * 99 / 100], srt[m - 1]);
-        // how uneven are the CTAs of the warp kernel (8 consecutive entries of the class list)?
-        const auto& list = impl_->class_envs[0];
-        double sum_max = 0, sum_mean = 0;
-        for (size_t i = 0; i + 8 <= list.size(); i += 8) {
-            unsigned int mx = 0; double mean = 0;
-            for (int j = 0; j < 8; j++) { mx = std::max(mx, c[list[i + j]]); mean += c[list[i + j]] / 8.0; }
-            sum_max += mx; sum_mean += mean;
-        }
-        if (sum_mean > 0) std::fprintf(stderr, "[prof] per CTA of 8: sum of max / sum of mean = %.3f\n", sum_max / sum_mean);
-    }
-    {
-        unsigned long long h[16];
-        if (cudaMemcpyFromSymbol(h, g_fprof, sizeof(h)) == cudaSuccess && h[4]) {
-            const double n = (double)h[4];
-            std::fprintf(stderr, "[prof] warp-substeps %.0f: collide %.0f wait %.0f rk4 %.0f constrain %.0f cycles avg; max collide %llu max constrain %llu\n",
-                         n, h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[11], h[12]);
-            std::fprintf(stderr, "[prof] rigid loops %llu (%.3f per warp-substep), jacobi with them %llu, visits avg %.2f max %llu, cycles avg %.0f\n",
-                         h[9], h[9] / n, h[10], h[9] ? (double)h[5] / h[9] : 0.0, h[6], h[9] ? (double)h[8] / h[9] : 0.0);
-        }
-    }
-#endif
     cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
     cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
     cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);
-    if (impl_) { cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); cudaFree(impl_->d_ctas); cudaFree(impl_->d_env_cycles); }
+    if (impl_) { cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); }
     if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
     delete impl_;
 }
@@ -377,12 +318,6 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
         for (int j = 0; j < deg && j < 8; j++) csr8[8 * (size_t)i + j] = csre[csro[i] + j];
     }
     H.max_deg = max_deg;
-    {
-        std::vector<int> na(Pd, 0), nb(Pd, 0);
-        for (int k = 0; k < Ed; k++) { na[ea[k]]++; nb[eb[k]]++; }
-        H.max_adeg = Pd ? *std::max_element(na.begin(), na.end()) : 0;
-        H.max_bdeg = Pd ? *std::max_element(nb.begin(), nb.end()) : 0;
-    }
     H.unit_mass = 1;
     for (int i = 0; i < Pd; i++) if (mass[i] != 1.0) H.unit_mass = 0;
     // leaves, objects, pair table
@@ -605,7 +540,6 @@ void Batch::finalize() {
     impl_->class_envs.assign(kNumClasses, {});
     impl_->class_smem.assign(kNumClasses, 0);
     impl_->env_cost.clear();
-    impl_->dims.clear();
     size_t state_doubles = 0;
     act_stride_ = 1;
 
@@ -635,14 +569,13 @@ void Batch::finalize() {
         sd = (sd + 1) & ~(size_t)1;
         state_doubles += sd;
         act_stride_ = std::max(act_stride_, e.n_act);
-        e.cls = class_for(*H, impl_->use_warp_kernel, impl_->flat != 0);
+        e.cls = class_for(*H, impl_->use_warp_kernel);
         if (e.cls >= kFirstGroupClass) {
             const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap);
             if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
             impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
         }
         impl_->class_envs[e.cls].push_back(i);
-        impl_->dims.push_back({H->Pd, H->Ed, H->n_leaf, H->n_pairs, H->n_items, H->n_rvis});
         // work estimate of one substep (spring passes, point passes, corner items): environments of similar cost
         // are placed in the same CTA so that the per-substep CTA barrier waits as little as possible
         impl_->env_cost.push_back(1000 * ((H->Pd + 31) / 32) + 700 * ((H->Ed + 63) / 64) + 40 * ((H->n_items + 31) / 32) +
@@ -652,8 +585,6 @@ void Batch::finalize() {
         std::stable_sort(impl_->class_envs[c].begin(), impl_->class_envs[c].end(),
                          [&](int a, int b) { return impl_->env_cost[a] > impl_->env_cost[b]; });
     for (int i = 0; i < n; i++) impl_->desc[i].act_off = i * act_stride_;
-    impl_->ctas.clear();
-    if (impl_->flat && impl_->use_warp_kernel && !impl_->class_envs[0].empty()) pack_flat_ctas();
 
     // (re)allocate
     cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
@@ -685,15 +616,6 @@ void Batch::finalize() {
             flat.insert(flat.end(), impl_->class_envs[c].begin(), impl_->class_envs[c].end());
         }
         CUDA_CHECK(cudaMemcpy(d_class_envs_, flat.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
-        cudaFree(impl_->d_env_cycles);
-        CUDA_CHECK(cudaMalloc(&impl_->d_env_cycles, sizeof(unsigned int) * n));
-        CUDA_CHECK(cudaMemset(impl_->d_env_cycles, 0, sizeof(unsigned int) * n));
-        cudaFree(impl_->d_ctas);
-        impl_->d_ctas = nullptr;
-        if (!impl_->ctas.empty()) {
-            CUDA_CHECK(cudaMalloc(&impl_->d_ctas, sizeof(CtaDesc) * impl_->ctas.size()));
-            CUDA_CHECK(cudaMemcpy(impl_->d_ctas, impl_->ctas.data(), sizeof(CtaDesc) * impl_->ctas.size(), cudaMemcpyHostToDevice));
-        }
     }
     {
         std::vector<double> ones((size_t)n * act_stride_, 1.0);   // action 1.0 == rest length
@@ -959,47 +881,6 @@ bool Batch::env_set_action(int env, const std::string& robot, const double* acti
 }
 
 // ------------------------------------------------------------------------------------------------
-// flat CTAs (fkernel.cuh): which class-0 environments share a CTA
-
-void Batch::pack_flat_ctas() {
-    // The environments of one CTA are integrated as one flat system, so what matters is that the totals of every
-    // CTA fit its capacity and are about equal: sort by size and deal the environments out boustrophedon (CTA 0..M-1,
-    // then M-1..0, ...), with M grown until every CTA fits.
-    const FlatCaps caps = impl_->flat_nt == 512 ? FlatCaps{MEVO_FCAPS_512} : impl_->flat_nt == 320 ? FlatCaps{MEVO_FCAPS_320} : FlatCaps{MEVO_FCAPS_256};
-    std::vector<int>& list = impl_->class_envs[0];
-    const auto& D = impl_->dims;
-    std::stable_sort(list.begin(), list.end(), [&](int a, int b) {
-        return D[a].p != D[b].p ? D[a].p > D[b].p : D[a].e > D[b].e;
-    });
-    const int n = (int)list.size();
-    int ne = caps.ne;
-    if (impl_->flat_ne > 0 && impl_->flat_ne < ne) ne = impl_->flat_ne;
-    std::vector<std::vector<int>> bins;
-    for (int M = (n + ne - 1) / ne;; M++) {
-        bins.assign(M, {});
-        for (int i = 0; i < n; i++) {
-            const int r = i / M, j = i % M;
-            bins[(r & 1) ? M - 1 - j : j].push_back(list[i]);
-        }
-        bool ok = true;
-        for (const auto& b : bins) {
-            Impl::Dims t{0, 0, 0, 0, 0, 0};
-            for (int env : b) { t.p += D[env].p; t.e += D[env].e; t.l += D[env].l; t.pr += D[env].pr; t.it += D[env].it; t.v += D[env].v; }
-            if ((int)b.size() > ne || t.p > caps.p || t.e > caps.e || t.l > caps.l || t.pr > caps.pr || t.it > caps.it || t.v > caps.v) { ok = false; break; }
-        }
-        if (ok) break;
-        if (M >= n) throw std::runtime_error("flat CTA packing: an environment exceeds the CTA capacity");
-    }
-    list.clear();
-    impl_->ctas.clear();
-    for (const auto& b : bins) {
-        if (b.empty()) continue;
-        impl_->ctas.push_back(CtaDesc{(int)list.size(), (int)b.size()});
-        list.insert(list.end(), b.begin(), b.end());
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
 // stepping
 
 void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
@@ -1022,7 +903,6 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.unstable = d_unstable_;
     prm.sim_time = d_time_;
     prm.err = d_err_;
-    prm.env_cycles = impl_->d_env_cycles;
     prm.dbg_cand = d_cand_;
     prm.dbg_cand_n = d_cand_n_;
     prm.dbg_cand_cap = cand_cap_;
@@ -1036,17 +916,12 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         prm.smem_per_env = impl_->class_smem[c];
         switch (c) {
             case 0:
-                if (!impl_->ctas.empty()) {
-                    const int m = (int)impl_->ctas.size();
-                    if (impl_->flat_nt == 512) launch_fstep<MEVO_FCAPS_512, 1>(prm, impl_->d_ctas, m, st);
-                    else if (impl_->flat_nt == 320) launch_fstep<MEVO_FCAPS_320, 2>(prm, impl_->d_ctas, m, st);
-                    else launch_fstep<MEVO_FCAPS_256, 3>(prm, impl_->d_ctas, m, st);
-                }
-                else if (impl_->wepc == 16) launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, st);
-                else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, st);
-                else launch_wstep<MEVO_WCAPS_A, 8, 2>(prm, st);
+                // default: one 16-warp CTA per SM (all warps of an SM in the same code region)
+                if (impl_->wepc == 8) launch_wstep<MEVO_WCAPS_A, 8, 2>(prm, impl_->n_sm, impl_->balance != 0, st);
+                else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, impl_->n_sm, impl_->balance != 0, st);
+                else launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, impl_->n_sm, impl_->balance != 0, st);
                 break;
-            case 1: launch_wstep<MEVO_WCAPS_B, 4, 2>(prm, st); break;
+            case 1: launch_wstep<MEVO_WCAPS_B, 4, 2>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: {
                 // largest environments-per-CTA <= the configured one that fits in shared memory
                 const int want = impl_->epc32, sz = prm.smem_per_env;

@@ -115,7 +115,6 @@ private:
     void upload_state(int env);
     void download_state(int env);
     void download_all();
-    void pack_flat_ctas();
     void pack_env(int env, std::vector<uint8_t>& design_blob, std::vector<uint8_t>& static_blob);
 
     int device_;

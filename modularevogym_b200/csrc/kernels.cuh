@@ -39,10 +39,10 @@ struct StepParams {
     int n_substeps;
     int apply_actions;
     int cta_sync;               // 1: CTA barrier once per substep (multi-environment CTAs)
+    int envs_per_cta;           // warp kernel: environments one CTA takes (<= its warp count)
     uint8_t* unstable;
     int* sim_time;
     int* err;
-    unsigned int* env_cycles;   // per env: SM cycles its own work took in the last launch (scheduling hint)
     unsigned int* dbg_cand;     // optional: candidate codes of the first substep
     int* dbg_cand_n;
     int dbg_cand_cap;

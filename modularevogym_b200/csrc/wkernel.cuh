@@ -125,12 +125,18 @@ __device__ __noinline__ void rigid_visit_exact(double2* pos, int a, int b, doubl
     pos[a] = pa; pos[b] = pb;
 }
 
-// spring force of one edge for stage positions sp (PhysicsEngine.cpp:498-528)
-__device__ __forceinline__ double2 spring_force(const double2* sp, uint32_t ix, double k, double leq) {
+// Spring force of one edge for stage positions sp (PhysicsEngine.cpp:498-528).  q is the edge's length_eq; in the
+// first stage of a substep it comes in as length_eq_goal and leaves as the relaxed length_eq
+// (PhysicsEngine::update_actuators: the stage's distance is the substep's start distance).
+__device__ __forceinline__ double2 spring_force(const double2* sp, uint32_t ix, double k, double& q, bool first_stage) {
     const double2 pa = sp[ix & 0xff], pb = sp[(ix >> 8) & 0xff];
     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
     const double dist = sqrt(dx * dx + dy * dy);
-    const double mag = (dist - leq) * k / dist;
+    if (first_stage) {
+        const double add = (q - dist) * 0.006;
+        q = dist + add;
+    }
+    const double mag = (dist - q) * k / dist;
     return make_double2(dx * mag, dy * mag);
 }
 
@@ -352,40 +358,40 @@ __device__ __noinline__ void warp_rk4(unsigned char* sm, unsigned fixmask) {
     const uint32_t* eidx = reinterpret_cast<const uint32_t*>(sm + S::o_eidx);
     const int Pd = H->Pd, Ed = H->Ed;
 
-    // length_eq: two edges per lane per trip, e and e + 32 (the second clamped, its store predicated)
-    for (int e0 = lane; e0 < Ed; e0 += 64) {
-        const int e1 = e0 + 32;
-        const bool v1 = e1 < Ed;
-        const int e1c = v1 ? e1 : e0;
-        const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
-        const double2 a0 = pos[i0 & 0xff], b0 = pos[(i0 >> 8) & 0xff];
-        const double2 a1 = pos[i1 & 0xff], b1 = pos[(i1 >> 8) & 0xff];
-        const double dx0 = a0.x - b0.x, dy0 = a0.y - b0.y;
-        const double dx1 = a1.x - b1.x, dy1 = a1.y - b1.y;
-        const double d0 = sqrt(dx0 * dx0 + dy0 * dy0);
-        const double d1 = sqrt(dx1 * dx1 + dy1 * dy1);
-        const double add0 = (goal[e0] - d0) * 0.006;
-        const double add1 = (goal[e1c] - d1) * 0.006;
-        leq[e0] = d0 + add0;
-        if (v1) leq[e1] = d1 + add1;
-    }
-    // length_eq[e] is written and read by the same lane: no barrier needed
 #pragma unroll 1
     for (int s = 0; s < 4; s++) {
         const double2* sp = (s == 0) ? pos : spos;
         const double2* sv = (s == 0) ? vel : svel;
-        for (int e0 = lane; e0 < Ed; e0 += 64) {
-            const int e1 = e0 + 32;
-            const bool v1 = e1 < Ed;
-            const int e1c = v1 ? e1 : e0;
-            const uint32_t i0 = eidx[e0], i1 = eidx[e1c];
-            const double2 f0 = spring_force(sp, i0, etab[(i0 >> kEidxTypeShift) & 15].x, leq[e0]);
-            const double2 f1 = spring_force(sp, i1, etab[(i1 >> kEidxTypeShift) & 15].x, leq[e1c]);
-            ef2[2 * e0] = make_double2(flip_sign(f0.x), flip_sign(f0.y));
-            ef2[2 * e0 + 1] = f0;
+        // Spring pass: three edges per lane in flight (e, e + 32, e + 64: three independent sqrt / div chains); lanes
+        // past the end recompute a valid edge and store nothing.  Stage 0 also does PhysicsEngine::update_actuators:
+        // its distance is the one length_eq is relaxed from (same positions, same expression).
+        for (int base = 0; base < Ed; base += 96) {
+            const int e0 = base + lane, e1 = e0 + 32, e2 = e0 + 64;
+            const bool v0 = e0 < Ed, v1 = e1 < Ed, v2 = e2 < Ed;
+            const int c0 = v0 ? e0 : base, c1 = v1 ? e1 : c0, c2 = v2 ? e2 : c0;
+            const uint32_t i0 = eidx[c0], i1 = eidx[c1], i2 = eidx[c2];
+            double q0, q1, q2;                          // stage 0: length_eq_goal; later stages: length_eq
+            if (s == 0) { q0 = goal[c0]; q1 = goal[c1]; q2 = goal[c2]; }
+            else { q0 = leq[c0]; q1 = leq[c1]; q2 = leq[c2]; }
+            const double2 f0 = spring_force(sp, i0, etab[(i0 >> kEidxTypeShift) & 15].x, q0, s == 0);
+            const double2 f1 = spring_force(sp, i1, etab[(i1 >> kEidxTypeShift) & 15].x, q1, s == 0);
+            const double2 f2 = spring_force(sp, i2, etab[(i2 >> kEidxTypeShift) & 15].x, q2, s == 0);
+            if (v0) {
+                ef2[2 * e0] = make_double2(flip_sign(f0.x), flip_sign(f0.y));
+                ef2[2 * e0 + 1] = f0;
+            }
             if (v1) {
                 ef2[2 * e1] = make_double2(flip_sign(f1.x), flip_sign(f1.y));
                 ef2[2 * e1 + 1] = f1;
+            }
+            if (v2) {
+                ef2[2 * e2] = make_double2(flip_sign(f2.x), flip_sign(f2.y));
+                ef2[2 * e2 + 1] = f2;
+            }
+            if (s == 0) {
+                if (v0) leq[e0] = q0;
+                if (v1) leq[e1] = q1;
+                if (v2) leq[e2] = q2;
             }
         }
         __syncwarp();
@@ -529,9 +535,15 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int grp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    int slot = blockIdx.x * EPC + grp;
-    const bool ghost = slot >= prm.n_class_envs;      // shadows the last environment, writes nothing back
-    if (ghost) slot = prm.n_class_envs - 1;
+    // A CTA takes prm.envs_per_cta (<= EPC) consecutive entries of the class list; the host picks that number so that
+    // the launch is a whole number of equally full waves.  Spare warps only keep the barrier count.
+    const int slot = blockIdx.x * prm.envs_per_cta + grp;
+    if (grp >= prm.envs_per_cta || slot >= prm.n_class_envs) {
+        if (EPC > 1 && prm.cta_sync)
+            for (int i = prm.n_steps * prm.n_substeps; i > 0; i--) __syncthreads();
+        return;
+    }
+    constexpr bool ghost = false;
     const int env = prm.class_envs[slot];
     unsigned char* sm = smem_raw + grp * S::kBytes;
     double* gstate;
@@ -627,14 +639,12 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     int completed_steps = 0;
     bool first_substep = true;
     const bool dbg = prm.dbg_cand != nullptr && !ghost;
-    unsigned int work_cycles = 0;
 
     for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
             // keeps the CTA's warps in the same code region: they share instruction-cache lines
             if (EPC > 1 && prm.cta_sync) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
-            const unsigned int c0 = (unsigned int)clock64();
             const bool dump = dbg && step == 0 && sub == 0;
             const int sub_unstable = warp_collide<S>(sm, dump ? prm.dbg_cand + (size_t)env * prm.dbg_cand_cap : nullptr,
                                                      dump ? prm.dbg_cand_n + env : nullptr, prm.dbg_cand_cap);
@@ -642,7 +652,6 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             warp_constrain<S>(sm, fixmask, first_substep);
             first_substep = false;
             if (sub_unstable) unstable = 1;               // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
-            work_cycles += (unsigned int)clock64() - c0;
         }
         if (!unstable) completed_steps++;
     }
@@ -676,7 +685,6 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         for (int e = lane; e < Ed; e += 32) ggoal[e] = goal[e];
         if (lane == 0) {
             prm.unstable[env] = (uint8_t)unstable;
-            prm.env_cycles[env] = work_cycles;
             if (unstable && prm.auto_reset) prm.sim_time[env] = 0;
             else prm.sim_time[env] += completed_steps;
             if (unstable) atomicAdd(prm.unstable_events, 1ull);

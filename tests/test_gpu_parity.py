@@ -31,13 +31,12 @@ def goldens():
     return [Golden(n) for n in NAMES]
 
 
-@pytest.fixture(params=["flat", "warp", "group"])
+@pytest.fixture(params=["warp", "group"])
 def kernel_choice(request, monkeypatch):
-    """Small environments run in the flat CTA kernel (fkernel.cuh) by default; MEVO_FLAT=0 (read when a batch is
-    created) sends them through the warp-per-environment kernel (wkernel.cuh), MEVO_NO_WKERNEL=1 through the
-    group-per-environment kernel (kernels.cuh) like the large ones.  All three must reproduce the reference."""
-    monkeypatch.setenv("MEVO_FLAT", "1" if request.param == "flat" else "0")
-    monkeypatch.setenv("MEVO_NO_WKERNEL", "1" if request.param == "group" else "0")
+    """Small environments run in the warp-per-environment kernel (wkernel.cuh) by default; MEVO_NO_WKERNEL=1
+    (read when a batch is created) sends them through the group-per-environment kernel (kernels.cuh) like
+    the large ones.  Both must reproduce the reference."""
+    monkeypatch.setenv("MEVO_NO_WKERNEL", "0" if request.param == "warp" else "1")
     return request.param
 
 
