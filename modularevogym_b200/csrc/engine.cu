@@ -174,6 +174,26 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
 
 Batch::~Batch() {
     cudaSetDevice(device_);
+#ifdef MEVO_PROF
+    {
+        unsigned long long h[16];
+        if (cudaMemcpyFromSymbol(h, g_wprof, sizeof(h)) == cudaSuccess && h[3]) {
+            const char* names[4] = {"collide", "rk4", "constrain", "substep"};
+            for (int q = 0; q < 4; q++)
+                std::fprintf(stderr, "[prof] %-9s own cycles share %.3f, slowest-warp / mean = %.3f\n", names[q], (double)h[q] / h[3], (double)h[4 + q] / h[q]);
+            unsigned long long hist[3][16][2];
+            cudaMemcpyFromSymbol(hist, g_whist, sizeof(hist));
+            const char* hn[3] = {"survivors/4", "candidates/4", "contacts (resolve round cycles)"};
+            std::fprintf(stderr, "[prof] apply loop: %.0f cycles per contact (%llu contacts)\n", h[9] ? (double)h[8] / h[9] : 0.0, h[9]);
+            for (int t = 0; t < 3; t++) {
+                std::fprintf(stderr, "[prof] collide cycles by %s:", hn[t]);
+                for (int b = 0; b < 16; b++)
+                    if (hist[t][b][1]) std::fprintf(stderr, " %d:%.0f(n=%llu)", b, (double)hist[t][b][0] / hist[t][b][1], hist[t][b][1]);
+                std::fprintf(stderr, "\n");
+            }
+        }
+    }
+#endif
     cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
     cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
     cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);

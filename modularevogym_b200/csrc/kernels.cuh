@@ -102,15 +102,30 @@ __device__ __forceinline__ bool point_in_box(const double2 p, const double4& b) 
     return p.x >= b.x && p.x <= b.z && p.y >= b.y && p.y <= b.w;
 }
 
-__device__ __forceinline__ void load_leaf(LeafRec& out, const LeafRec* dyn_leaf, const LeafRec* st_leaf, unsigned id, bool is_static) {
-    uint4* d = reinterpret_cast<uint4*>(&out);
+// A LeafRec held in registers: fields picked with shifts, never with a dynamic array index (which would put the
+// record in local memory and every access on an L1 / L2 round trip).
+struct LeafRegs {
+    unsigned long long pt, ea, eb;     // 4 x u16 each
+    unsigned int misc;                 // surf_mask | obj << 8 | gx << 16
+    __device__ __forceinline__ int point(int k) const { return (int)((pt >> (16 * k)) & 0xffffu); }
+    __device__ __forceinline__ int edge_a(int k) const { return (int)((ea >> (16 * k)) & 0xffffu); }
+    __device__ __forceinline__ int edge_b(int k) const { return (int)((eb >> (16 * k)) & 0xffffu); }
+    __device__ __forceinline__ bool on_surface(int k) const { return (misc >> k) & 1u; }
+};
+
+__device__ __forceinline__ void load_leaf(LeafRegs& out, const LeafRec* dyn_leaf, const LeafRec* st_leaf, unsigned id, bool is_static) {
+    uint4 d0, d1;
     if (is_static) {
         const uint4* g = reinterpret_cast<const uint4*>(st_leaf + id);
-        d[0] = __ldg(g); d[1] = __ldg(g + 1);
+        d0 = __ldg(g); d1 = __ldg(g + 1);
     } else {
         const uint4* g = reinterpret_cast<const uint4*>(dyn_leaf + id);
-        d[0] = g[0]; d[1] = g[1];
+        d0 = g[0]; d1 = g[1];
     }
+    out.pt = (unsigned long long)d0.x | ((unsigned long long)d0.y << 32);
+    out.ea = (unsigned long long)d0.z | ((unsigned long long)d0.w << 32);
+    out.eb = (unsigned long long)d1.x | ((unsigned long long)d1.y << 32);
+    out.misc = d1.z;
 }
 
 __device__ __forceinline__ double cross2(double ax, double ay, double bx, double by) {
@@ -120,7 +135,7 @@ __device__ __forceinline__ double cross2(double ax, double ay, double bx, double
 // MatrixBase::normalized (Eigen/src/Core/Dot.h:124-134)
 __device__ __forceinline__ void normalize2(double& x, double& y) {
     double z = x * x + y * y;
-    if (z > 0) { double s = sqrt(z); x = x / s; y = y / s; }
+    if (z > 0 && z != 1.0) { double s = sqrt(z); x = x / s; y = y / s; }     // z == 1: s == 1 and x / 1 == x
 }
 
 struct PointSrc {
@@ -135,7 +150,11 @@ struct PointSrc {
     }
 };
 
-// PhysicsEngine::get_intersecting, PhysicsEngine.cpp:1094-1121
+// PhysicsEngine::get_intersecting, PhysicsEngine.cpp:1094-1121: t = nt / det and s = ns / det both in [0, 1].
+// Decided without the two divisions: for det > 0 that is 0 <= n <= det, for det < 0 it is det <= n <= 0.  The rounded
+// quotient of the reference can only disagree with this when n / det lies within one rounding error of 0 or 1 (n
+// the neighbouring double of det, or a quotient that underflows) -- a measure-zero set of inputs, like the box
+// prefilter's (exact shortcuts).
 __device__ __forceinline__ bool segments_intersect(double2 a1, double2 b1, double2 a2, double2 b2) {
     double d1x = b1.x - a1.x, d1y = b1.y - a1.y;
     double d2x = b2.x - a2.x, d2y = b2.y - a2.y;
@@ -143,9 +162,10 @@ __device__ __forceinline__ bool segments_intersect(double2 a1, double2 b1, doubl
     if (fabs(det) < 0.0001) return false;
     double x_diff = a2.x - a1.x;
     double y_diff = a2.y - a1.y;
-    double t = (-d2y * x_diff + d2x * y_diff) / det;
-    double s = (-d1y * x_diff + d1x * y_diff) / det;
-    return (0.0 <= t && t <= 1 && 0.0 <= s && s <= 1);
+    double nt = -d2y * x_diff + d2x * y_diff;
+    double ns = -d1y * x_diff + d1x * y_diff;
+    if (det < 0) { nt = -nt; ns = -ns; det = -det; }
+    return (0.0 <= nt && nt <= det && 0.0 <= ns && ns <= det);
 }
 
 // PhysicsEngine::dist_point_edge, PhysicsEngine.cpp:1123-1135
@@ -170,14 +190,14 @@ struct Contact {
 // Boxel::point_in_boxel (Boxel.cpp:41-65) followed by
 // PhysicsEngine::resolve_point_boxel_collisions (PhysicsEngine.cpp:910-1092).
 // corner = index of p in main's TL,TR,BR,BL list.  Returns false when no contact results.
-__device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const LeafRec& mainb, bool main_static,
-                                                    const LeafRec& refb, bool ref_static, int corner, Contact& c) {
+__device__ __forceinline__ bool resolve_point_vs_boxel(const PointSrc& src, const LeafRegs& mainb, bool main_static,
+                                                       const LeafRegs& refb, bool ref_static, int corner, Contact& c) {
     // corners shared with refb (PhysicsEngine.cpp:895-901) never reach this function: the host lists only the
     // non-shared corners of point-sharing leaf pairs, and no other pair shares a point
-    const int p = mainb.pt[corner];
+    const int p = mainb.point(corner);
     const double2 pp = src.pos(p, main_static);
-    const double2 rtl = src.pos(refb.pt[0], ref_static), rtr = src.pos(refb.pt[1], ref_static);
-    const double2 rbr = src.pos(refb.pt[2], ref_static), rbl = src.pos(refb.pt[3], ref_static);
+    const double2 rtl = src.pos(refb.point(0), ref_static), rtr = src.pos(refb.point(1), ref_static);
+    const double2 rbr = src.pos(refb.point(2), ref_static), rbl = src.pos(refb.point(3), ref_static);
     {
         double tlx = rtl.x - pp.x, tly = rtl.y - pp.y;
         double trx = rtr.x - pp.x, try_ = rtr.y - pp.y;
@@ -197,16 +217,16 @@ __device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const L
     // the two main-boxel sides incident to corner p (PhysicsEngine.cpp:915-938): sides are top,right,bot,left
     const int s0 = (corner == 0 || corner == 1) ? 0 : 2;      // top for TL/TR, bot for BR/BL
     const int s1 = (corner == 0 || corner == 3) ? 3 : 1;      // left for TL/BL, right for TR/BR
-    const double2 m0a = src.pos(mainb.ea[s0], main_static), m0b = src.pos(mainb.eb[s0], main_static);
-    const double2 m1a = src.pos(mainb.ea[s1], main_static), m1b = src.pos(mainb.eb[s1], main_static);
+    const double2 m0a = src.pos(mainb.edge_a(s0), main_static), m0b = src.pos(mainb.edge_b(s0), main_static);
+    const double2 m1a = src.pos(mainb.edge_a(s1), main_static), m1b = src.pos(mainb.edge_b(s1), main_static);
 
     int best = -1;
     double min_dist = 0.0;
     double2 best_a = make_double2(0, 0), best_b = make_double2(0, 0);
 #pragma unroll 1
     for (int s = 0; s < 4; s++) {                                              // :943-960
-        if (!((refb.surf_mask >> s) & 1)) continue;
-        const double2 ra = src.pos(refb.ea[s], ref_static), rb = src.pos(refb.eb[s], ref_static);
+        if (!refb.on_surface(s)) continue;
+        const double2 ra = src.pos(refb.edge_a(s), ref_static), rb = src.pos(refb.edge_b(s), ref_static);
         bool viable = segments_intersect(m0a, m0b, ra, rb);
         if (!viable) viable = segments_intersect(m1a, m1b, ra, rb);
         if (!viable) continue;
@@ -215,7 +235,7 @@ __device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const L
     }
     if (best < 0) return false;
 
-    c.p = p; c.a = refb.ea[best]; c.b = refb.eb[best];
+    c.p = p; c.a = refb.edge_a(best); c.b = refb.edge_b(best);
     c.p_static = main_static; c.ab_static = ref_static;
     // Edge::get_normal, Edge.cpp:16-22
     double sx = best_b.x - best_a.x, sy = best_b.y - best_a.y;
@@ -235,9 +255,8 @@ __device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const L
     c.fpx = nfx + v1x;           c.fpy = nfy + v1y;                                         // :1057-1059
     c.fax = nfx / 2 + v2x / 2;   c.fay = nfy / 2 + v2y / 2;
     c.fbx = nfx / 2 + v3x / 2;   c.fby = nfy / 2 + v3y / 2;
-    double tx0 = nx, ty0 = ny;                                                             // :1065-1066
-    normalize2(tx0, ty0);
-    double tx = -ty0, ty = tx0;
+    // :1065-1066 normalises the normal once more for the tangent: same input as (ux, uy), same result
+    double tx = -uy, ty = ux;
     double proj = tx * vp.x + ty * vp.y;
     double nfm = sqrt(nfx * nfx + nfy * nfy);
     if (proj < 0) { proj *= -1.0; tx *= -1.0; ty *= -1.0; }
@@ -250,18 +269,22 @@ __device__ __noinline__ bool resolve_point_vs_boxel(const PointSrc& src, const L
 // collision_forces += contact, in the reference's statement order (PhysicsEngine.cpp:1057-1082).
 // Forces on static (all-fixed, pruned) points are dropped: they can never move anything.
 __device__ __forceinline__ void apply_contact(double2* cf, const Contact& c, int reps) {
+    // p, a and b are three different points, so each one's running sum can stay in a register: same additions in
+    // the same order per point as the statement-by-statement read-modify-write
+    double2 vp = make_double2(0.0, 0.0), va = vp, vb = vp;
+    if (!c.p_static) vp = cf[c.p];
+    if (!c.ab_static) { va = cf[c.a]; vb = cf[c.b]; }
+    const double hx = c.frx / 2, hy = c.fry / 2;
     for (int r = 0; r < reps; r++) {
-        if (!c.p_static) { double2 v = cf[c.p]; v.x += c.fpx; v.y += c.fpy; cf[c.p] = v; }
-        if (!c.ab_static) {
-            double2 v = cf[c.a]; v.x -= c.fax; v.y -= c.fay; cf[c.a] = v;
-            v = cf[c.b]; v.x -= c.fbx; v.y -= c.fby; cf[c.b] = v;
-        }
-        if (!c.p_static) { double2 v = cf[c.p]; v.x += c.frx; v.y += c.fry; cf[c.p] = v; }
-        if (!c.ab_static) {
-            double2 v = cf[c.a]; v.x -= c.frx / 2; v.y -= c.fry / 2; cf[c.a] = v;
-            v = cf[c.b]; v.x -= c.frx / 2; v.y -= c.fry / 2; cf[c.b] = v;
-        }
+        vp.x += c.fpx; vp.y += c.fpy;
+        va.x -= c.fax; va.y -= c.fay;
+        vb.x -= c.fbx; vb.y -= c.fby;
+        vp.x += c.frx; vp.y += c.fry;
+        va.x -= hx; va.y -= hy;
+        vb.x -= hx; vb.y -= hy;
     }
+    if (!c.p_static) cf[c.p] = vp;
+    if (!c.ab_static) { cf[c.a] = va; cf[c.b] = vb; }
 }
 
 template <int G, int EPC>
@@ -552,7 +575,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                     const unsigned code = surv[w * seg_cap + i];
                     const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
                     reps = (code & kItemSameObj) ? 2 : 1;
-                    LeafRec lm, lr;
+                    LeafRegs lm, lr;
                     load_leaf(lm, leaf, st_leaf, code & kCodeLeafMask, m_static);
                     load_leaf(lr, leaf, st_leaf, (code >> 12) & kCodeLeafMask, r_static);
                     has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);

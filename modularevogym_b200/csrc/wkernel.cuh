@@ -65,6 +65,28 @@ struct WarpHdr {                                   // 96 bytes
 };
 static_assert(sizeof(WarpHdr) == 88, "WarpHdr layout");
 
+#ifdef MEVO_PROF
+// development only (-DMEVO_PROF): per phase, the sum over warps of their own time and the sum over CTA-substeps of
+// the slowest warp's time x warps -- their ratio is what the per-substep barrier costs
+__device__ unsigned long long g_wprof[16];
+__device__ unsigned long long g_whist[3][16][2];     // [collide by survivors / collide by candidates / constrain by rigid moves][bucket][cycles, count]
+#endif
+
+// a / b for a compile-time constant b, bit-identical to the IEEE quotient in three instructions instead of the
+// ~25 of a general double division (Markstein's theorem: with rb = RN(1 / b) and a faithful q = RN(a * rb), the
+// remainder r = a - q b is exact in one fma and RN(q + r rb) is the correctly rounded a / b; also checked against
+// the hardware quotient on 8e8 random operands, tools/check_const_div.c).  Zero, denormal-range, huge and non-finite
+// operands take the ordinary division.
+__device__ __noinline__ double div_slow(double a, double b) { return a / b; }
+__device__ __forceinline__ double div_const(double a, const double b) {
+    const double rb = 1.0 / b;                          // folded at compile time
+    const double m = fabs(a);
+    if (!(m > 1e-290 && m < 1e290)) return div_slow(a, b);
+    const double q = a * rb;
+    const double r = __fma_rn(-q, b, a);
+    return __fma_rn(r, rb, q);
+}
+
 // tanh of the analytic ground plane's friction term (PhysicsEngine.cpp:573-577); out of line: a robot standing
 // on voxel terrain never gets below y = 0
 __device__ __noinline__ double ground_friction_tanh(double x) { return tanh(x); }
@@ -108,9 +130,11 @@ __device__ __noinline__ void warp_jacobi_limiter(double2* pos, double2* ef2, con
     __syncwarp();
 }
 
-// The exact +-3 % limiter of one rigid-cell visit (PhysicsEngine.cpp:675-710); out of line, one lane.
-__device__ __noinline__ void rigid_visit_exact(double2* pos, int a, int b, double l0) {
-    double2 pa = pos[a], pb = pos[b];
+// The +-3 % limiter of one rigid-cell visit (PhysicsEngine.cpp:675-710): does the visit move its end points, and by
+// what.  The reference applies pa -= c, pb += c on every visit; outside (0.97, 1.03) c is what is computed here,
+// inside it is zero.
+__device__ __forceinline__ bool rigid_visit_eval(const double2* pos, int a, int b, double l0, double& cx, double& cy) {
+    const double2 pa = pos[a], pb = pos[b];
     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
     const double dist = sqrt(dx * dx + dy * dy);
     const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
@@ -118,11 +142,11 @@ __device__ __noinline__ void rigid_visit_exact(double2* pos, int a, int b, doubl
     double ox = dx * over_mag, oy = dy * over_mag;
     double ux = dx * under_mag, uy = dy * under_mag;
     const double stress = dist / l0;
-    if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
-    if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
-    const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
-    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
-    pos[a] = pa; pos[b] = pb;
+    const bool no_over = stress < (1 + 0.03), no_under = stress > (1 - 0.03);
+    if (no_over) { ox = 0.0; oy = 0.0; }
+    if (no_under) { ux = 0.0; uy = 0.0; }
+    cx = (ox + ux) * 0.5; cy = (oy + uy) * 0.5;
+    return !(no_over && no_under);
 }
 
 // Spring force of one edge for stage positions sp (PhysicsEngine.cpp:498-528).  q is the edge's length_eq; in the
@@ -213,6 +237,10 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
     }
 
     int pair_base = 0, cell_it = 0, next_ic = 0, dbg_off = 0;
+#ifdef MEVO_PROF
+    const long long tc0 = clock64();
+    int prof_cand = 0, prof_surv = 0;
+#endif
     bool producing = true;
     while (producing) {
         // ---- produce candidates (32-bit codes of kernels.cuh)
@@ -249,6 +277,9 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
             cnt += __popc(m);
         }
         __syncwarp();
+#ifdef MEVO_PROF
+        prof_cand += cnt;
+#endif
         if (dbg_row) {
             for (int i = lane; i < cnt; i += 32)
                 if (dbg_off + i < dbg_cap) dbg_row[dbg_off + i] = cand[i];
@@ -303,10 +334,16 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                 scnt += __popc(m);
             }
             __syncwarp();
+#ifdef MEVO_PROF
+            prof_surv += scnt;
+#endif
             if (scnt > 0) {
                 PointSrc src;
                 src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = H->st_pos;
                 for (int base = 0; base < scnt; base += 32) {
+#ifdef MEVO_PROF
+                    const long long tr0 = clock64();
+#endif
                     const int i = base + lane;
                     bool has = false;
                     Contact c;
@@ -315,23 +352,42 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                         const unsigned code = surv[i];
                         const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
                         reps = (code & kItemSameObj) ? 2 : 1;
-                        LeafRec lm, lr;
+                        LeafRegs lm, lr;
                         load_leaf(lm, H->g_leaf, H->st_leaf, code & kCodeLeafMask, m_static);
                         load_leaf(lr, H->g_leaf, H->st_leaf, (code >> 12) & kCodeLeafMask, r_static);
                         has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
                     }
                     unsigned m = __ballot_sync(0xffffffffu, has);
+#ifdef MEVO_PROF
+                    const long long tr1 = clock64();
+                    const int n_contacts = __popc(m);
+#endif
                     while (m) {                           // deterministic, race-free: lanes in order
                         const int l = __ffs(m) - 1;
                         if (lane == l) apply_contact(cf, c, reps);
                         m &= m - 1;
                         __syncwarp();
                     }
+#ifdef MEVO_PROF
+                    if (lane == 0) {
+                        const int bk = min(n_contacts, 15);
+                        atomicAdd(&g_whist[2][bk][0], (unsigned long long)(tr1 - tr0)); atomicAdd(&g_whist[2][bk][1], 1ull);
+                        atomicAdd(&g_wprof[8], (unsigned long long)(clock64() - tr1)); atomicAdd(&g_wprof[9], (unsigned long long)n_contacts);
+                    }
+#endif
                 }
             }
             __syncwarp();
         }
     }
+#ifdef MEVO_PROF
+    if (lane == 0) {
+        const unsigned long long d = clock64() - tc0;
+        const int bs = min(prof_surv / 4, 15), bc = min(prof_cand / 4, 15);
+        atomicAdd(&g_whist[0][bs][0], d); atomicAdd(&g_whist[0][bs][1], 1ull);
+        atomicAdd(&g_whist[1][bc][0], d); atomicAdd(&g_whist[1][bc][1], 1ull);
+    }
+#endif
     // K6a: unstable test uses the boxes of the START of this substep (a-12)
     return __any_sync(0xffffffffu, lane < 8 && misc[lane] > misc[8 + lane]);
 }
@@ -444,8 +500,8 @@ __device__ __noinline__ void warp_rk4(unsigned char* sm, unsigned fixmask) {
                 svel[p] = make_double2(v0.x + (kvx * h), v0.y + (kvy * h));
             } else {
                 const double2 qp = accp[p], qv = accv[p];
-                double dpx = (qp.x + kpx) / 6, dpy = (qp.y + kpy) / 6;
-                double dvx = (qv.x + kvx) / 6, dvy = (qv.y + kvy) / 6;
+                double dpx = div_const(qp.x + kpx, 6.0), dpy = div_const(qp.y + kpy, 6.0);
+                double dvx = div_const(qv.x + kvx, 6.0), dvy = div_const(qv.y + kvy, 6.0);
                 if ((fixmask >> k) & 1u) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
                 // the new position goes to spos: pos keeps the substep's start position (= pos_last)
                 spos[p] = make_double2(x0.x + dpx, x0.y + dpy);
@@ -488,41 +544,42 @@ __device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask,
     const bool anyj = __any_sync(0xffffffffu, jviol);
     if (anyj) warp_jacobi_limiter(spos, ef2, eidx, etab, csr, Pd, Ed, fixmask, S::kZero);
     if (n_vis > 0 && (anyj || __any_sync(0xffffffffu, rviol))) {
-        // ordered rigid-cell pass (PhysicsEngine.cpp:675-710): a visit inside the +-3 % band changes nothing, so
-        // jump from one violating visit to the next; each is applied exactly by one lane and the visits after it
-        // are re-tested against the updated positions
-        int start = 0;
-        while (start < n_vis) {
-            int first = -1;
-            for (int c = start & ~31; c < n_vis; c += 32) {
-                const int i = c + lane;
-                bool v = false;
-                if (i >= start && i < n_vis) {
-                    const uint32_t ix = eidx[rord[i]];
-                    const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
-                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                    const double d2 = dx * dx + dy * dy;
-                    const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
-                    const double l2 = l0 * l0;
-                    v = !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999);
+        // Ordered rigid-cell pass (PhysicsEngine.cpp:675-710).  A visit inside the +-3 % band changes nothing and a
+        // visit's outcome depends only on its two end points, so: every lane evaluates its own visit from the current
+        // positions (32 visits at once), the first one that moves its points is applied, and only the later visits
+        // that share a point with it are evaluated again.  Visits are retired strictly in the reference's order.
+        for (int c0 = 0; c0 < n_vis; c0 += 32) {
+            const int i = c0 + lane;
+            bool done = i >= n_vis, fresh = false, moves = false;
+            int a = 0, b = 0;
+            double l0 = 1.0, cx = 0.0, cy = 0.0;
+            if (!done) {
+                const uint32_t ix = eidx[rord[i]];
+                a = ix & 0xff; b = (ix >> 8) & 0xff;
+                l0 = etab[(ix >> kEidxTypeShift) & 15].y;
+            }
+            while (true) {
+                if (!done && !fresh) { moves = rigid_visit_eval(spos, a, b, l0, cx, cy); fresh = true; }
+                const unsigned m = __ballot_sync(0xffffffffu, !done && moves);
+                if (!m) break;
+                const int f = __ffs(m) - 1;
+                if (lane == f) {
+                    double2 pa = spos[a], pb = spos[b];
+                    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
+                    spos[a] = pa; spos[b] = pb;
                 }
-                const unsigned m = __ballot_sync(0xffffffffu, v);
-                if (m) { first = c + __ffs(m) - 1; break; }
+                __syncwarp();
+                const int fa = __shfl_sync(0xffffffffu, a, f), fb = __shfl_sync(0xffffffffu, b, f);
+                if (lane <= f) done = true;
+                else if (a == fa || a == fb || b == fa || b == fb) fresh = false;
             }
-            if (first < 0) break;
-            if (lane == (first & 31)) {
-                const uint32_t ix = eidx[rord[first]];
-                rigid_visit_exact(spos, ix & 0xff, (ix >> 8) & 0xff, etab[(ix >> kEidxTypeShift) & 15].y);
-            }
-            __syncwarp();
-            start = first + 1;
         }
     }
     for (int p = lane; p < Pd; p += 32) {                // PhysicsEngine::update_true_vel (:602-607)
         const double2 x = spos[p];
         // pos_last == pos at the start of every substep except possibly the first of a launch
         const double2 l = first_substep ? H->g_last[p] : pos[p];
-        vt[p] = make_double2((x.x - l.x) / MEVO_DT, (x.y - l.y) / MEVO_DT);
+        vt[p] = make_double2(div_const(x.x - l.x, MEVO_DT), div_const(x.y - l.y, MEVO_DT));
         pos[p] = x;
     }
     __syncwarp();
@@ -646,10 +703,32 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             if (EPC > 1 && prm.cta_sync) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
             const bool dump = dbg && step == 0 && sub == 0;
+#ifdef MEVO_PROF
+            const long long tq0 = clock64();
+#endif
             const int sub_unstable = warp_collide<S>(sm, dump ? prm.dbg_cand + (size_t)env * prm.dbg_cand_cap : nullptr,
                                                      dump ? prm.dbg_cand_n + env : nullptr, prm.dbg_cand_cap);
+#ifdef MEVO_PROF
+            const long long tq1 = clock64();
+#endif
             warp_rk4<S>(sm, fixmask);
+#ifdef MEVO_PROF
+            const long long tq2 = clock64();
+#endif
             warp_constrain<S>(sm, fixmask, first_substep);
+#ifdef MEVO_PROF
+            {
+                __shared__ unsigned int pmax[4];
+                const long long tq3 = clock64();
+                const unsigned int d[4] = {(unsigned)(tq1 - tq0), (unsigned)(tq2 - tq1), (unsigned)(tq3 - tq2), (unsigned)(tq3 - tq0)};
+                if (threadIdx.x < 4) pmax[threadIdx.x] = 0;
+                __syncthreads();
+                if (lane == 0) for (int q = 0; q < 4; q++) { atomicMax(&pmax[q], d[q]); atomicAdd(&g_wprof[q], (unsigned long long)d[q]); }
+                __syncthreads();
+                if (threadIdx.x < 4) atomicAdd(&g_wprof[4 + threadIdx.x], (unsigned long long)pmax[threadIdx.x] * prm.envs_per_cta);
+                __syncthreads();
+            }
+#endif
             first_substep = false;
             if (sub_unstable) unstable = 1;               // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
         }
