@@ -229,6 +229,11 @@ def main_reference(args) -> None:
     print(json.dumps(line), flush=True)
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one step launch of 4096 envs, from the ncu --set full capture
+# summarised in profiles/r01f_wstep_kernel_raw.csv (25.21 MB read + 0.27 MB written): the state stays on chip
+NCU_DRAM_BYTES_PER_LAUNCH = 25_481_984
+
+
 def algorithmic_bytes_per_step(P: int, E: int) -> int:
     """every array the reference touches once in and once out per substep --
     105 B per point (pos, vel, pos_last read+written, mass, fixed) + 32 B per edge (a, b, goal, L0, k),
@@ -372,7 +377,7 @@ def main_ours(args) -> None:
                     "ms_per_step": e2e_ms / K},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "mevo::step_kernel<32,*>", "peak_source": peak_src,
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if n == 4096 else None, "kernel": "mevo::wstep_kernel<40,112,24,192,256,112,16,1>", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes},
             "cpu_baseline": cpu,
             "clocks": clock_info,

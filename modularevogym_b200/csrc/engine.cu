@@ -183,10 +183,9 @@ Batch::~Batch() {
                 std::fprintf(stderr, "[prof] %-9s own cycles share %.3f, slowest-warp / mean = %.3f\n", names[q], (double)h[q] / h[3], (double)h[4 + q] / h[q]);
             unsigned long long hist[3][16][2];
             cudaMemcpyFromSymbol(hist, g_whist, sizeof(hist));
-            const char* hn[3] = {"survivors/4", "candidates/4", "contacts (resolve round cycles)"};
-            std::fprintf(stderr, "[prof] apply loop: %.0f cycles per contact (%llu contacts)\n", h[9] ? (double)h[8] / h[9] : 0.0, h[9]);
+            const char* hn[3] = {"survivors/4", "candidates/4", "constrain: rigid moves (+8: Jacobi ran)"};
             for (int t = 0; t < 3; t++) {
-                std::fprintf(stderr, "[prof] collide cycles by %s:", hn[t]);
+                std::fprintf(stderr, "[prof] %s cycles by %s:", t < 2 ? "collide" : "limiter", hn[t]);
                 for (int b = 0; b < 16; b++)
                     if (hist[t][b][1]) std::fprintf(stderr, " %d:%.0f(n=%llu)", b, (double)hist[t][b][0] / hist[t][b][1], hist[t][b][1]);
                 std::fprintf(stderr, "\n");

@@ -92,11 +92,21 @@ __device__ __forceinline__ double div_const(double a, const double b) {
 __device__ __noinline__ double ground_friction_tanh(double x) { return tanh(x); }
 
 // Jacobi half of PhysicsEngine::resolve_edge_constraints (PhysicsEngine.cpp:613-671) for one warp; out of line:
-// runs only in substeps where some edge left the +-25 % band
+// runs only in substeps where some edge left the +-25 % band.  `list` holds the n_list edges outside the (guarded)
+// band: every other edge's correction is exactly zero, so only those are evaluated (sqrt + three divisions each).
+// list == nullptr: all edges.
 __device__ __noinline__ void warp_jacobi_limiter(double2* pos, double2* ef2, const uint32_t* eidx, const double2* etab,
-                                                 const uint4* csr, int Pd, int Ed, unsigned fixmask, int zero_idx) {
+                                                 const uint4* csr, int Pd, int Ed, unsigned fixmask, int zero_idx,
+                                                 const unsigned int* list, int n_list) {
     const int lane = threadIdx.x & 31;
-    for (int e = lane; e < Ed; e += 32) {
+    if (list) {
+        for (int i = lane; i < 2 * Ed; i += 32) ef2[i] = make_double2(0.0, 0.0);
+        __syncwarp();
+    } else {
+        n_list = Ed;
+    }
+    for (int i = lane; i < n_list; i += 32) {
+        const int e = list ? (int)list[i] : i;
         const uint32_t ix = eidx[e];
         const double2 pa = pos[ix & 0xff], pb = pos[(ix >> 8) & 0xff];
         const double dx = pa.x - pb.x, dy = pa.y - pb.y;
@@ -341,9 +351,6 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                 PointSrc src;
                 src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = H->st_pos;
                 for (int base = 0; base < scnt; base += 32) {
-#ifdef MEVO_PROF
-                    const long long tr0 = clock64();
-#endif
                     const int i = base + lane;
                     bool has = false;
                     Contact c;
@@ -358,23 +365,12 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                         has = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
                     }
                     unsigned m = __ballot_sync(0xffffffffu, has);
-#ifdef MEVO_PROF
-                    const long long tr1 = clock64();
-                    const int n_contacts = __popc(m);
-#endif
                     while (m) {                           // deterministic, race-free: lanes in order
                         const int l = __ffs(m) - 1;
                         if (lane == l) apply_contact(cf, c, reps);
                         m &= m - 1;
                         __syncwarp();
                     }
-#ifdef MEVO_PROF
-                    if (lane == 0) {
-                        const int bk = min(n_contacts, 15);
-                        atomicAdd(&g_whist[2][bk][0], (unsigned long long)(tr1 - tr0)); atomicAdd(&g_whist[2][bk][1], 1ull);
-                        atomicAdd(&g_wprof[8], (unsigned long long)(clock64() - tr1)); atomicAdd(&g_wprof[9], (unsigned long long)n_contacts);
-                    }
-#endif
                 }
             }
             __syncwarp();
@@ -530,19 +526,46 @@ __device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask,
     const uint8_t* rord = reinterpret_cast<const uint8_t*>(sm + S::o_rord);
     const int Pd = H->Pd, Ed = H->Ed, n_vis = H->n_vis;
 
-    bool jviol = false, rviol = false;
-    for (int e = lane; e < Ed; e += 32) {
-        const uint32_t ix = eidx[e];
-        const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
-        const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-        const double d2 = dx * dx + dy * dy;
-        const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
-        const double l2 = l0 * l0;
-        if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) jviol = true;
-        if (((ix >> kEidxRigidBit) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) rviol = true;
+#ifdef MEVO_PROF
+    const long long tk0 = clock64();
+    int prof_moves = 0;
+#endif
+    // edges outside the +-25 % band are listed (candidate + survivor buffers are free in this phase)
+    unsigned int* jlist = reinterpret_cast<unsigned int*>(sm + S::o_cand);
+    constexpr int kJCap = S::kCandCap + S::kSurvCap;
+    static_assert(S::o_surv == S::o_cand + 4 * S::kCandCap, "the two buffers are contiguous");
+    int nj = 0;
+    bool rviol = false;
+    for (int e0 = 0; e0 < Ed; e0 += 128) {                // four edges per lane in flight, then their ballots
+        bool jv[4];
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            const int e = e0 + 32 * t + lane;
+            const bool valid = e < Ed;
+            const uint32_t ix = eidx[valid ? e : e0];
+            const double2 pa = spos[ix & 0xff], pb = spos[(ix >> 8) & 0xff];
+            const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+            const double d2 = dx * dx + dy * dy;
+            const double l0 = etab[(ix >> kEidxTypeShift) & 15].y;
+            const double l2 = l0 * l0;
+            jv[t] = valid && !(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999);
+            if (valid && ((ix >> kEidxRigidBit) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) rviol = true;
+        }
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            const unsigned m = __ballot_sync(0xffffffffu, jv[t]);
+            if (m) {
+                const int at = nj + __popc(m & ((1u << lane) - 1u));
+                if (jv[t] && at < kJCap) jlist[at] = (unsigned int)(e0 + 32 * t + lane);
+                nj += __popc(m);
+            }
+        }
     }
-    const bool anyj = __any_sync(0xffffffffu, jviol);
-    if (anyj) warp_jacobi_limiter(spos, ef2, eidx, etab, csr, Pd, Ed, fixmask, S::kZero);
+    const bool anyj = nj > 0;
+    if (anyj) {
+        __syncwarp();
+        warp_jacobi_limiter(spos, ef2, eidx, etab, csr, Pd, Ed, fixmask, S::kZero, nj <= kJCap ? jlist : nullptr, nj);
+    }
     if (n_vis > 0 && (anyj || __any_sync(0xffffffffu, rviol))) {
         // Ordered rigid-cell pass (PhysicsEngine.cpp:675-710).  A visit inside the +-3 % band changes nothing and a
         // visit's outcome depends only on its two end points, so: every lane evaluates its own visit from the current
@@ -563,6 +586,9 @@ __device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask,
                 const unsigned m = __ballot_sync(0xffffffffu, !done && moves);
                 if (!m) break;
                 const int f = __ffs(m) - 1;
+#ifdef MEVO_PROF
+                prof_moves++;
+#endif
                 if (lane == f) {
                     double2 pa = spos[a], pb = spos[b];
                     pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
@@ -575,6 +601,12 @@ __device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask,
             }
         }
     }
+#ifdef MEVO_PROF
+    if (lane == 0) {
+        const int bk = (anyj ? 8 : 0) + min(prof_moves, 7);
+        atomicAdd(&g_whist[2][bk][0], (unsigned long long)(clock64() - tk0)); atomicAdd(&g_whist[2][bk][1], 1ull);
+    }
+#endif
     for (int p = lane; p < Pd; p += 32) {                // PhysicsEngine::update_true_vel (:602-607)
         const double2 x = spos[p];
         // pos_last == pos at the start of every substep except possibly the first of a launch
