@@ -86,9 +86,8 @@ __device__ __forceinline__ bool group_any(int grp, bool pred, volatile int* slot
 
 __device__ __forceinline__ bool aabb_overlap(const double4& a, const double4& b) {
     // BoundingBox::in, main.h:64-72 (closed intervals, F_ERROR_TOL = 0); (x,y,z,w) = (minx,miny,maxx,maxy)
-    if (a.x > b.z || a.z < b.x) return false;
-    if (a.y > b.w || a.w < b.y) return false;
-    return true;
+    // (no short-circuit: one predicate chain instead of four branches; a NaN compares false as before)
+    return !(a.x > b.z) & !(a.z < b.x) & !(a.y > b.w) & !(a.w < b.y);
 }
 
 __device__ __forceinline__ double4 ldg_d4(const double4* p) {
@@ -99,7 +98,7 @@ __device__ __forceinline__ double4 ldg_d4(const double4* p) {
 
 // necessary condition of Boxel::point_in_boxel: both triangles lie inside the box of the four corners
 __device__ __forceinline__ bool point_in_box(const double2 p, const double4& b) {
-    return p.x >= b.x && p.x <= b.z && p.y >= b.y && p.y <= b.w;
+    return (p.x >= b.x) & (p.x <= b.z) & (p.y >= b.y) & (p.y <= b.w);
 }
 
 // A LeafRec held in registers: fields picked with shifts, never with a dynamic array index (which would put the

@@ -259,15 +259,13 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
             bool hit = false;
             unsigned int code = 0;
             if (pair_base < n_pairs) {
-                const int i = pair_base + lane;
+                const int i = pair_base + lane;          // lanes past the end repeat a valid pair: no branch
+                const unsigned pc = pairs[i < n_pairs ? i : pair_base];
                 pair_base += 32;
-                if (i < n_pairs) {
-                    const unsigned pc = pairs[i];
-                    const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
-                    hit = aabb_overlap(aabb[a], aabb[b]);
-                    if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
-                    code = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
-                }
+                const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
+                hit = (i < n_pairs) & aabb_overlap(aabb[a], aabb[b]);
+                if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
+                code = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
             } else if (cell_it < max_cells) {
                 const int it = cell_it++;
                 if (it < n_cells) {
@@ -307,13 +305,11 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                 if (next_ic * 32 < n_items) {
                     // non-shared corners of leaf pairs that share a point
                     const int i = next_ic * 32 + lane;
+                    const unsigned ic = items[i < n_items ? i : next_ic * 32];
                     next_ic++;
-                    if (i < n_items) {
-                        const unsigned ic = items[i];
-                        const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
-                        code = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
-                        hit = point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
-                    }
+                    const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
+                    code = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
+                    hit = (i < n_items) & point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
                 } else if (next_cc * 32 < cnt * 8) {
                     // the 8 corners of each candidate pair (these pairs share no point)
                     const int i = next_cc * 32 + lane;
