@@ -253,21 +253,41 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
 #endif
     bool producing = true;
     while (producing) {
-        // ---- produce candidates (32-bit codes of kernels.cuh)
+        // ---- produce candidates (32-bit codes of kernels.cuh): tested leaf pairs first, then terrain cells
         int cnt = 0;
-        while (cnt + 32 <= S::kCandCap) {
-            bool hit = false;
-            unsigned int code = 0;
-            if (pair_base < n_pairs) {
-                const int i = pair_base + lane;          // lanes past the end repeat a valid pair: no branch
-                const unsigned pc = pairs[i < n_pairs ? i : pair_base];
-                pair_base += 32;
-                const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
-                hit = (i < n_pairs) & aabb_overlap(aabb[a], aabb[b]);
-                if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
-                code = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
-            } else if (cell_it < max_cells) {
+        while (pair_base < n_pairs && cnt + 64 <= S::kCandCap) {      // two pairs per lane in flight
+            const int i0 = pair_base + lane, i1 = i0 + 32;
+            const unsigned pc0 = pairs[i0 < n_pairs ? i0 : pair_base], pc1 = pairs[i1 < n_pairs ? i1 : pair_base];
+            pair_base += 64;
+            const unsigned a0 = pc0 & 31u, b0 = (pc0 >> 5) & 31u, a1 = pc1 & 31u, b1 = (pc1 >> 5) & 31u;
+            const bool hit0 = (i0 < n_pairs) & aabb_overlap(aabb[a0], aabb[b0]);
+            const bool hit1 = (i1 < n_pairs) & aabb_overlap(aabb[a1], aabb[b1]);
+            const unsigned m0 = __ballot_sync(0xffffffffu, hit0), m1 = __ballot_sync(0xffffffffu, hit1);
+            if (m0 | m1) {
+                if (hit0 && (pc0 & kPair16Count)) atomicAdd((int*)&misc[pc0 >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
+                if (hit1 && (pc1 & kPair16Count)) atomicAdd((int*)&misc[pc1 >> kPair16ObjShift], 2);
+                if (hit0) cand[cnt + __popc(m0 & ((1u << lane) - 1u))] = a0 | (b0 << 12) | ((pc0 & kPair16Same) ? kCodeSameObj : 0u);
+                cnt += __popc(m0);
+                if (hit1) cand[cnt + __popc(m1 & ((1u << lane) - 1u))] = a1 | (b1 << 12) | ((pc1 & kPair16Same) ? kCodeSameObj : 0u);
+                cnt += __popc(m1);
+            }
+        }
+        while (pair_base < n_pairs && cnt + 32 <= S::kCandCap) {
+            const int i = pair_base + lane;              // lanes past the end repeat a valid pair: no branch
+            const unsigned pc = pairs[i < n_pairs ? i : pair_base];
+            pair_base += 32;
+            const unsigned a = pc & 31u, b = (pc >> 5) & 31u;
+            const bool hit = (i < n_pairs) & aabb_overlap(aabb[a], aabb[b]);
+            if (hit && (pc & kPair16Count)) atomicAdd((int*)&misc[pc >> kPair16ObjShift], 2);   // both ordered pairs (a-12)
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = a | (b << 12) | ((pc & kPair16Same) ? kCodeSameObj : 0u);
+            cnt += __popc(m);
+        }
+        if (pair_base >= n_pairs) {
+            while (cell_it < max_cells && cnt + 32 <= S::kCandCap) {
                 const int it = cell_it++;
+                bool hit = false;
+                unsigned int code = 0;
                 if (it < n_cells) {
                     const int cx = cx0 + it % wx, cy = cy0 + it / wx;
                     const int sl = __ldg(st_grid + cy * gw + cx);
@@ -276,13 +296,11 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                         code = (unsigned)lane | ((unsigned)sl << 12) | kCodeStatic;
                     }
                 }
-            } else {
-                producing = false;
-                break;
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
+                cnt += __popc(m);
             }
-            const unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
-            cnt += __popc(m);
+            if (cell_it >= max_cells) producing = false;
         }
         __syncwarp();
 #ifdef MEVO_PROF
@@ -299,21 +317,40 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
         bool more = true;
         while (more) {
             int scnt = 0;
-            while (scnt + 32 <= S::kSurvCap) {
-                bool hit = false;
-                unsigned int code = 0;
-                if (next_ic * 32 < n_items) {
-                    // non-shared corners of leaf pairs that share a point
-                    const int i = next_ic * 32 + lane;
-                    const unsigned ic = items[i < n_items ? i : next_ic * 32];
-                    next_ic++;
-                    const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
-                    code = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
-                    hit = (i < n_items) & point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
-                } else if (next_cc * 32 < cnt * 8) {
-                    // the 8 corners of each candidate pair (these pairs share no point)
+            // non-shared corners of leaf pairs that share a point (always candidates) first ...
+            while (next_ic * 32 < n_items && scnt + 64 <= S::kSurvCap) {      // two items per lane in flight
+                const int i0 = next_ic * 32 + lane, i1 = i0 + 32;
+                const unsigned ic0 = items[i0 < n_items ? i0 : next_ic * 32], ic1 = items[i1 < n_items ? i1 : next_ic * 32];
+                next_ic += 2;
+                const unsigned mn0 = ic0 & 31u, rf0 = (ic0 >> 5) & 31u, cr0 = (ic0 >> 10) & 3u;
+                const unsigned mn1 = ic1 & 31u, rf1 = (ic1 >> 5) & 31u, cr1 = (ic1 >> 10) & 3u;
+                const bool hit0 = (i0 < n_items) & point_in_box(pos[(lpt[mn0] >> (8 * cr0)) & 0xff], aabb[rf0]);
+                const bool hit1 = (i1 < n_items) & point_in_box(pos[(lpt[mn1] >> (8 * cr1)) & 0xff], aabb[rf1]);
+                const unsigned m0 = __ballot_sync(0xffffffffu, hit0), m1 = __ballot_sync(0xffffffffu, hit1);
+                if (m0 | m1) {
+                    if (hit0) surv[scnt + __popc(m0 & ((1u << lane) - 1u))] = mn0 | (rf0 << 12) | (cr0 << kItemCornerShift) | kItemSameObj;
+                    scnt += __popc(m0);
+                    if (hit1) surv[scnt + __popc(m1 & ((1u << lane) - 1u))] = mn1 | (rf1 << 12) | (cr1 << kItemCornerShift) | kItemSameObj;
+                    scnt += __popc(m1);
+                }
+            }
+            while (next_ic * 32 < n_items && scnt + 32 <= S::kSurvCap) {
+                const int i = next_ic * 32 + lane;
+                const unsigned ic = items[i < n_items ? i : next_ic * 32];
+                next_ic++;
+                const unsigned mn = ic & 31u, rf = (ic >> 5) & 31u, corner = (ic >> 10) & 3u;
+                const bool hit = (i < n_items) & point_in_box(pos[(lpt[mn] >> (8 * corner)) & 0xff], aabb[rf]);
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = mn | (rf << 12) | (corner << kItemCornerShift) | kItemSameObj;
+                scnt += __popc(m);
+            }
+            // ... then the 8 corners of each candidate pair (these pairs share no point)
+            if (next_ic * 32 >= n_items) {
+                while (next_cc * 32 < cnt * 8 && scnt + 32 <= S::kSurvCap) {
                     const int i = next_cc * 32 + lane;
                     next_cc++;
+                    bool hit = false;
+                    unsigned int code = 0;
                     if (i < cnt * 8) {
                         const unsigned int cc = cand[i >> 3];
                         const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
@@ -331,13 +368,11 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
                             hit = point_in_box(pp, aabb[a]);
                         }
                     }
-                } else {
-                    more = false;
-                    break;
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
+                    scnt += __popc(m);
                 }
-                const unsigned m = __ballot_sync(0xffffffffu, hit);
-                if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
-                scnt += __popc(m);
+                if (next_cc * 32 >= cnt * 8) more = false;
             }
             __syncwarp();
 #ifdef MEVO_PROF
