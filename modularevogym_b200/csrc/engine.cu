@@ -940,7 +940,7 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, impl_->n_sm, impl_->balance != 0, st);
                 else launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, impl_->n_sm, impl_->balance != 0, st);
                 break;
-            case 1: launch_wstep<MEVO_WCAPS_B, 4, 2>(prm, impl_->n_sm, impl_->balance != 0, st); break;
+            case 1: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: {
                 // largest environments-per-CTA <= the configured one that fits in shared memory
                 const int want = impl_->epc32, sz = prm.smem_per_env;

@@ -71,6 +71,21 @@ __device__ __forceinline__ void group_sync(int grp) {
     }
 }
 
+// a / b for a compile-time constant b, bit-identical to the IEEE quotient in three instructions instead of the
+// ~25 of a general double division (Markstein's theorem: with rb = RN(1 / b) and a faithful q = RN(a * rb), the
+// remainder r = a - q b is exact in one fma and RN(q + r rb) is the correctly rounded a / b; also checked against
+// the hardware quotient on 8e8 random operands, tools/check_const_div.c).  Zero, denormal-range, huge and non-finite
+// operands take the ordinary division.
+__device__ __noinline__ double div_slow(double a, double b) { return a / b; }
+__device__ __forceinline__ double div_const(double a, const double b) {
+    const double rb = 1.0 / b;                          // folded at compile time
+    const double m = fabs(a);
+    if (!(m > 1e-290 && m < 1e290)) return div_slow(a, b);
+    const double q = a * rb;
+    const double r = __fma_rn(-q, b, a);
+    return __fma_rn(r, rb, q);
+}
+
 // group-wide OR of a per-thread predicate (uniform result); `slot` is a shared-memory word of the group
 template <int G, int EPC>
 __device__ __forceinline__ bool group_any(int grp, bool pred, volatile int* slot) {
@@ -80,6 +95,20 @@ __device__ __forceinline__ bool group_any(int grp, bool pred, volatile int* slot
     if (__any_sync(0xffffffffu, pred) && (threadIdx.x & 31) == 0) *slot = 1;
     group_sync<G, EPC>(grp);
     const bool r = *slot != 0;
+    group_sync<G, EPC>(grp);
+    return r;
+}
+
+// group-wide OR of a per-thread bit mask (uniform result)
+template <int G, int EPC>
+__device__ __forceinline__ int group_or(int grp, int bits, volatile int* slot) {
+    if (G == 32) return __reduce_or_sync(0xffffffffu, (unsigned)bits);
+    if ((threadIdx.x % G) == 0) *slot = 0;
+    group_sync<G, EPC>(grp);
+    const unsigned w = __reduce_or_sync(0xffffffffu, (unsigned)bits);
+    if (w && (threadIdx.x & 31) == 0) atomicOr((int*)slot, (int)w);
+    group_sync<G, EPC>(grp);
+    const int r = *slot;
     group_sync<G, EPC>(grp);
     return r;
 }
@@ -619,14 +648,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
 
             if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K4: actuators + RK4 (a-7, a-8, a-9)
-            for (int e = t; e < Ed; e += G) {
-                const double2 pa = pos[ea[e]], pb = pos[eb[e]];
-                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                const double dist = sqrt(dx * dx + dy * dy);
-                const double additive = (goal[e] - dist) * 0.006;
-                leq[e] = dist + additive;
-            }
-            // leq[e] is written and read by the same thread (same striding): no barrier needed
+            // (PhysicsEngine::update_actuators is done inside the first stage's edge pass: same positions, same distance)
 #pragma unroll 1
             for (int s = 0; s < 4; s++) {
                 if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
@@ -636,7 +658,15 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                     const double2 pa = sp[ea[e]], pb = sp[eb[e]];
                     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
                     const double dist = sqrt(dx * dx + dy * dy);
-                    const double mag = (dist - leq[e]) * ek[e] / dist;
+                    double q;
+                    if (s == 0) {
+                        const double additive = (goal[e] - dist) * 0.006;
+                        q = dist + additive;
+                        leq[e] = q;                       // written and read by the same thread (same striding)
+                    } else {
+                        q = leq[e];
+                    }
+                    const double mag = (dist - q) * ek[e] / dist;
                     ef[e] = make_double2(dx * mag, dy * mag);
                 }
                 group_sync<G, EPC>(grp);
@@ -684,8 +714,8 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                         svel[p] = make_double2(v0.x + kvx, v0.y + kvy);
                     } else {
                         double2 qp = accp[p], qv = accv[p];
-                        double dpx = (qp.x + kpx) / 6, dpy = (qp.y + kpy) / 6;
-                        double dvx = (qv.x + kvx) / 6, dvy = (qv.y + kvy) / 6;
+                        double dpx = div_const(qp.x + kpx, 6.0), dpy = div_const(qp.y + kpy, 6.0);
+                        double dvx = div_const(qv.x + kvx, 6.0), dvy = div_const(qv.y + kvy, 6.0);
                         if (fixedp[p]) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
                         double2 x0 = pos[p], v0 = vel[p];
                         x0.x += dpx; x0.y += dpy; v0.x += dvx; v0.y += dvy;
@@ -697,34 +727,42 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
 
             if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
-            // Fast path: the limiters only act beyond +-25 % strain (+-3 % on the sides of rigid voxels).  One
-            // sqrt per edge decides, with a 1e-7 relative guard band so that the decision never depends on the
+            // Fast path: the limiters only act beyond +-25 % strain (+-3 % on the sides of rigid voxels).  Squared
+            // lengths decide (no sqrt), with a 1e-7 relative guard band so that the decision never depends on the
             // rounding of dist / L0; inside the band every correction of the reference is exactly zero and the
             // positions are left untouched, which is what the reference computes.  Otherwise: the exact passes.
-            bool viol = false;
+            int viol = 0;
             for (int e = t; e < Ed; e += G) {
                 const double2 pa = pos[ea[e]], pb = pos[eb[e]];
                 const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                const double dist = sqrt(dx * dx + dy * dy);
+                const double d2 = dx * dx + dy * dy;
                 const double l0 = el0[e];
-                const bool rigid = (eflag[e] & kEdgeRigidCell) != 0;
-                const double lo = rigid ? 0.9700001 : 0.7500001, hi = rigid ? 1.0299999 : 1.2499999;
-                if (!(dist > l0 * lo && dist < l0 * hi)) viol = true;
+                const double l2 = l0 * l0;
+                if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) viol |= 1;
+                if ((eflag[e] & kEdgeRigidCell) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) viol |= 2;
             }
-            if (group_any<G, EPC>(grp, viol, misc + 24)) {
+            viol = group_or<G, EPC>(grp, viol, misc + 24);
+            if (viol) {
+            if (viol & 1) {
             for (int e = t; e < Ed; e += G) {
                 const double2 pa = pos[ea[e]], pb = pos[eb[e]];
                 const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                const double dist = sqrt(dx * dx + dy * dy);
+                const double d2 = dx * dx + dy * dy;
                 const double l0 = el0[e];
-                const double over_mag = (dist - l0 * (1 + 0.25)) / (dist * 2);
-                const double under_mag = (dist - l0 * (1 - 0.25)) / (dist * 2);
-                double ox = dx * over_mag, oy = dy * over_mag;
-                double ux = dx * under_mag, uy = dy * under_mag;
-                const double stress = dist / l0;
-                if (!(stress > (1 + 0.25))) { ox = 0.0; oy = 0.0; }
-                if (!(stress < (1 - 0.25))) { ux = 0.0; uy = 0.0; }
-                ef[e] = make_double2((ox + ux) * 0.8, (oy + uy) * 0.8);
+                const double l2 = l0 * l0;
+                double2 c = make_double2(0.0, 0.0);       // inside the guarded band the correction is exactly zero
+                if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) {
+                    const double dist = sqrt(d2);
+                    const double over_mag = (dist - l0 * (1 + 0.25)) / (dist * 2);
+                    const double under_mag = (dist - l0 * (1 - 0.25)) / (dist * 2);
+                    double ox = dx * over_mag, oy = dy * over_mag;
+                    double ux = dx * under_mag, uy = dy * under_mag;
+                    const double stress = dist / l0;
+                    if (!(stress > (1 + 0.25))) { ox = 0.0; oy = 0.0; }
+                    if (!(stress < (1 - 0.25))) { ux = 0.0; uy = 0.0; }
+                    c = make_double2((ox + ux) * 0.8, (oy + uy) * 0.8);
+                }
+                ef[e] = c;
             }
             group_sync<G, EPC>(grp);
             for (int p = t; p < Pd; p += G) {
@@ -739,6 +777,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                 pos[p] = x;
             }
             group_sync<G, EPC>(grp);
+            }   // Jacobi pass
             // ordered rigid-cell pass, scheduled in point-disjoint levels (PhysicsEngine.cpp:675-710)
             for (int lv = 0; lv < H.n_rlev; lv++) {
                 const int i1 = __ldg(rlev + lv + 1);
@@ -747,8 +786,11 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
                     const int a = ea[e], b = eb[e];
                     double2 pa = pos[a], pb = pos[b];
                     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                    const double dist = sqrt(dx * dx + dy * dy);
+                    const double d2 = dx * dx + dy * dy;
                     const double l0 = el0[e];
+                    const double l2 = l0 * l0;
+                    if (d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999) continue;     // inside the guarded band: a no-op
+                    const double dist = sqrt(d2);
                     const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
                     const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
                     double ox = dx * over_mag, oy = dy * over_mag;
@@ -765,7 +807,7 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             }   // exact passes
             for (int p = t; p < Pd; p += G) {             // PhysicsEngine::update_true_vel (:602-607)
                 const double2 x = pos[p], l = last[p];
-                vt[p] = make_double2((x.x - l.x) / MEVO_DT, (x.y - l.y) / MEVO_DT);
+                vt[p] = make_double2(div_const(x.x - l.x, MEVO_DT), div_const(x.y - l.y, MEVO_DT));
                 last[p] = x;
             }
             group_sync<G, EPC>(grp);

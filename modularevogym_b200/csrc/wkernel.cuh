@@ -72,21 +72,6 @@ __device__ unsigned long long g_wprof[16];
 __device__ unsigned long long g_whist[3][16][2];     // [collide by survivors / collide by candidates / constrain by rigid moves][bucket][cycles, count]
 #endif
 
-// a / b for a compile-time constant b, bit-identical to the IEEE quotient in three instructions instead of the
-// ~25 of a general double division (Markstein's theorem: with rb = RN(1 / b) and a faithful q = RN(a * rb), the
-// remainder r = a - q b is exact in one fma and RN(q + r rb) is the correctly rounded a / b; also checked against
-// the hardware quotient on 8e8 random operands, tools/check_const_div.c).  Zero, denormal-range, huge and non-finite
-// operands take the ordinary division.
-__device__ __noinline__ double div_slow(double a, double b) { return a / b; }
-__device__ __forceinline__ double div_const(double a, const double b) {
-    const double rb = 1.0 / b;                          // folded at compile time
-    const double m = fabs(a);
-    if (!(m > 1e-290 && m < 1e290)) return div_slow(a, b);
-    const double q = a * rb;
-    const double r = __fma_rn(-q, b, a);
-    return __fma_rn(r, rb, q);
-}
-
 // tanh of the analytic ground plane's friction term (PhysicsEngine.cpp:573-577); out of line: a robot standing
 // on voxel terrain never gets below y = 0
 __device__ __noinline__ double ground_friction_tanh(double x) { return tanh(x); }
