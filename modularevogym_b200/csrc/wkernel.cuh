@@ -2,18 +2,24 @@
 // the Walker-v0 / Pusher-v0 / Thrower-v0 configurations of BASELINE.json.
 //
 // Same arithmetic as step_kernel (kernels.cuh) -- the two agree bit for bit and tests run both -- but laid out
-// for what bounds this path on B200: instruction issue and fixed-latency dependency stalls (ncu: FP64 pipe
-// < 20 %, DRAM ~ 0, the loop body larger than the instruction cache).  Hence
+// for what bounds this path on B200 (ncu: DRAM ~ 0, FP64 pipe < 20 %, issue slots < 40 %): each environment is one
+// long dependent chain (FP64 sqrt / div sequences, shared-memory round trips, ballots), shared memory allows 16 of
+// them per SM, the substep body is larger than the instruction cache, and with the barrier that keeps the warps in
+// step a substep lasts as long as its slowest warp.  Hence
 //   * everything a substep touches lives in shared memory in compact form (16-bit pair / item codes, 16-byte
 //     gather records, an edge-type table instead of per-edge constants): no global load inside the loop,
 //   * compile-time layout (template capacities): one base register per warp, constant offsets,
 //   * every spring force is stored with both signs, so the per-point gather is 8 x (LDS.128 + 2 DADD),
-//   * the spring pass handles two edges per lane at a time (two independent sqrt / div chains in flight),
-//   * strain limiters: squared-length band test (no sqrt); the ordered rigid-cell pass jumps from one violating
-//     visit to the next instead of walking all visits,
-//   * rarely taken paths (contact resolver, analytic-ground tanh, exact Jacobi limiter) are out of line,
-//   * one environment per warp, several per CTA; a CTA barrier every substep keeps the warps in the same code
-//     region so they share instruction-cache lines.
+//   * independent work per lane is kept in flight: three edges in the spring pass (length_eq is relaxed inside
+//     the first stage's pass), two pairs / items in the collision trips; box tests are branch-free,
+//   * strain limiters: squared-length band test (no sqrt); the Jacobi limiter evaluates only the edges outside the
+//     band; the ordered rigid-cell pass evaluates 32 visits at once and re-evaluates only what the applied visit
+//     touched,
+//   * the contact resolver keeps its leaf records in registers, decides segment crossings without dividing, and
+//     accumulates a contact's forces in registers,
+//   * division by a compile-time constant is three instructions and bit-identical (div_const, kernels.cuh),
+//   * one environment per warp, 16 warps = one CTA per SM; a CTA barrier every substep keeps them in the same code
+//     region so they share instruction-cache lines; the host sizes CTAs for equally full waves.
 #pragma once
 
 #include "kernels.cuh"
