@@ -149,6 +149,12 @@ int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n);    /* env_ids NU
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out);
 /* same, into a caller-owned DEVICE buffer (n_envs x 2 doubles), enqueued on the batch's stream, no sync */
 int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out);
+/* Walker-v0 observation of object `obj` in every env (evogym/envs/walk.py:58-61 = get_vel_com_obs + get_relative_pos_obs,
+ * evogym/envs/base.py:214-240), simulator units: row = [mean vel x, mean vel y, x_i - com_x (i < n), y_i - com_y
+ * (i < n), zeros up to `stride`].  width = 2 + 2 * (largest point count of `obj` over the envs). */
+int mevo_batch_object_obs_width(mevo_batch* b, int obj);
+int mevo_batch_object_obs(mevo_batch* b, int obj, double* out, int stride);                 /* host, n_envs x stride */
+int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int stride);   /* device, on the stream, no sync */
 
 /* device pointers for zero-copy consumers (valid until the next finalize) */
 double* mevo_batch_actions_device_ptr(mevo_batch* b);

@@ -72,6 +72,9 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_save_reset_state": (_i, [_vp]),
     "mevo_batch_reset": (_i, [_vp, _ip, _i]),
     "mevo_batch_object_com": (_i, [_vp, _i, _dp]),
+    "mevo_batch_object_obs_width": (_i, [_vp, _i]),
+    "mevo_batch_object_obs": (_i, [_vp, _i, _dp, _i]),
+    "mevo_batch_object_obs_device": (_i, [_vp, _i, _vp, _i]),
     "mevo_batch_actions_device_ptr": (_vp, [_vp]),
     "mevo_batch_unstable_device_ptr": (_vp, [_vp]),
     "mevo_batch_cuda_stream": (_vp, [_vp]),
@@ -383,6 +386,19 @@ class Batch:
             out = np.zeros((self.num_envs, 2))
         _check(self.L.mevo_batch_object_com(self.h, int(obj), _dptr(out)))
         return out
+
+    def object_obs(self, obj: int, stride: int = 0) -> np.ndarray:
+        """(n_envs, stride) Walker-style observation rows of object `obj` (evogym/envs/walk.py:58-61)."""
+        w = int(self.L.mevo_batch_object_obs_width(self.h, int(obj)))
+        if w < 0:
+            raise MevoError(self.L.mevo_last_error().decode())
+        stride = max(int(stride), w)
+        out = np.zeros((self.num_envs, stride))
+        _check(self.L.mevo_batch_object_obs(self.h, int(obj), _dptr(out), stride))
+        return out
+
+    def object_obs_device(self, obj: int, device_ptr: int, stride: int) -> None:
+        _check(self.L.mevo_batch_object_obs_device(self.h, int(obj), C.c_void_p(device_ptr), int(stride)))
 
     def object_com_ptr(self, obj: int, host_ptr: int) -> None:
         _check(self.L.mevo_batch_object_com(self.h, int(obj), C.cast(host_ptr, _dp)))

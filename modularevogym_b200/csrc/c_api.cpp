@@ -337,6 +337,28 @@ int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out) {
     });
 }
 
+int mevo_batch_object_obs_width(mevo_batch* b, int obj) {
+    int w = -1;
+    const int rc = guard([&] { w = b->impl.object_obs_width(obj); return 0; });
+    return rc ? -1 : w;
+}
+
+int mevo_batch_object_obs(mevo_batch* b, int obj, double* out, int stride) {
+    return guard([&] {
+        if (!out || stride < 2) throw std::invalid_argument("object_obs: null output or stride < 2");
+        b->impl.object_obs(obj, out, stride);
+        return 0;
+    });
+}
+
+int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int stride) {
+    return guard([&] {
+        if (!device_out || stride < 2) throw std::invalid_argument("object_obs_device: null output or stride < 2");
+        b->impl.object_obs_device(obj, device_out, stride);
+        return 0;
+    });
+}
+
 double* mevo_batch_actions_device_ptr(mevo_batch* b) { return b->impl.actions_device_ptr(); }
 const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b) { return b->impl.unstable_device_ptr(); }
 void* mevo_batch_cuda_stream(mevo_batch* b) { return b->impl.stream(); }

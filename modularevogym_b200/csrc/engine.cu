@@ -1020,31 +1020,68 @@ void Batch::object_com(int obj_index, double* out_host_2n) {
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
 }
 
+void Batch::bind_object_ranges(int obj_index) {
+    const int n = num_envs();
+    if (impl_->com_obj == obj_index) return;
+    std::vector<int> ranges(3 * (size_t)n, 0);
+    for (int i = 0; i < n; i++) {
+        const EnvHost& e = envs_[i];
+        ranges[3 * i + 2] = (int)e.dyn_points.size();
+        if (obj_index >= (int)e.world.objects.size()) continue;
+        const VoxelObject& ob = e.world.objects[obj_index];
+        const int l0 = e.point_local[ob.min_point];
+        if (l0 < 0) continue;   // static object: not tracked on the device
+        ranges[3 * i] = l0;
+        ranges[3 * i + 1] = ob.max_point - ob.min_point + 1;
+    }
+    cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out);
+    CUDA_CHECK(cudaMalloc(&impl_->d_com_ranges, sizeof(int) * ranges.size()));
+    CUDA_CHECK(cudaMalloc(&impl_->d_com_out, sizeof(double) * 2 * n));
+    CUDA_CHECK(cudaMemcpy(impl_->d_com_ranges, ranges.data(), sizeof(int) * ranges.size(), cudaMemcpyHostToDevice));
+    impl_->com_obj = obj_index;
+}
+
 void Batch::object_com_device(int obj_index, double* out_device_2n) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     const int n = num_envs();
-    if (impl_->com_obj != obj_index) {
-        std::vector<int> ranges(3 * (size_t)n, 0);
-        for (int i = 0; i < n; i++) {
-            const EnvHost& e = envs_[i];
-            if (obj_index >= (int)e.world.objects.size()) continue;
-            const VoxelObject& ob = e.world.objects[obj_index];
-            const int l0 = e.point_local[ob.min_point];
-            if (l0 < 0) continue;   // static object: not tracked on the device
-            ranges[3 * i] = l0;
-            ranges[3 * i + 1] = ob.max_point - ob.min_point + 1;
-            ranges[3 * i + 2] = (int)e.dyn_points.size();
-        }
-        cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out);
-        CUDA_CHECK(cudaMalloc(&impl_->d_com_ranges, sizeof(int) * ranges.size()));
-        CUDA_CHECK(cudaMalloc(&impl_->d_com_out, sizeof(double) * 2 * n));
-        CUDA_CHECK(cudaMemcpy(impl_->d_com_ranges, ranges.data(), sizeof(int) * ranges.size(), cudaMemcpyHostToDevice));
-        impl_->com_obj = obj_index;
-    }
+    bind_object_ranges(obj_index);
     com_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), impl_->d_com_ranges, n,
                                                                    out_device_2n ? out_device_2n : impl_->d_com_out);
     CUDA_CHECK(cudaGetLastError());
+}
+
+int Batch::object_obs_width(int obj_index) const {
+    int w = 2;
+    for (const EnvHost& e : envs_) {
+        if (obj_index >= (int)e.world.objects.size()) continue;
+        const VoxelObject& ob = e.world.objects[obj_index];
+        w = std::max(w, 2 + 2 * (ob.max_point - ob.min_point + 1));
+    }
+    return w;
+}
+
+void Batch::object_obs_device(int obj_index, double* out_device, int stride) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    const int n = num_envs();
+    bind_object_ranges(obj_index);
+    obs_kernel<<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), impl_->d_com_ranges, n,
+                                                              out_device, stride);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void Batch::object_obs(int obj_index, double* out_host, int stride) {
+    const size_t bytes = sizeof(double) * (size_t)stride * num_envs();
+    double* d = nullptr;
+    CUDA_CHECK(cudaSetDevice(device_));
+    CUDA_CHECK(cudaMalloc(&d, bytes));
+    try {
+        object_obs_device(obj_index, d, stride);
+        CUDA_CHECK(cudaMemcpyAsync(out_host, d, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    } catch (...) { cudaFree(d); throw; }
+    cudaFree(d);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -99,6 +99,10 @@ public:
     // packed robot positions for the learner side: COM (x, y) of object `obj_index` per env
     void object_com(int obj_index, double* out_host_2n);
     void object_com_device(int obj_index, double* out_device_2n);   // async on stream()
+    // Walker-style observation rows [vel com (2), relative x (n), relative y (n), zero padding] (evogym/envs/walk.py:58-61)
+    int object_obs_width(int obj_index) const;                       // 2 + 2 * (largest point count of the object)
+    void object_obs_device(int obj_index, double* out_device, int stride);   // async on stream()
+    void object_obs(int obj_index, double* out_host, int stride);
 
     // debug / test hooks: candidate pairs of the first substep of the next step() call
     void enable_candidate_dump(int cap_per_env);
@@ -115,6 +119,7 @@ private:
     void upload_state(int env);
     void download_state(int env);
     void download_all();
+    void bind_object_ranges(int obj_index);
     void pack_env(int env, std::vector<uint8_t>& design_blob, std::vector<uint8_t>& static_blob);
 
     int device_;

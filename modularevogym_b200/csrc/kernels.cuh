@@ -860,4 +860,36 @@ __global__ void com_kernel(const double* state, const EnvDesc* envs, const int* 
     out[2 * env + 1] = count ? sy / count : 0.0;
 }
 
+// Walker-style observation of one object per env (evogym/envs/walk.py:58-61 = get_vel_com_obs + get_relative_pos_obs,
+// evogym/envs/base.py:214-240): row = [mean vel x, mean vel y, x_i - com_x (i < n), y_i - com_y (i < n), 0 ...].
+// One warp per environment.
+__global__ void obs_kernel(const double* state, const EnvDesc* envs, const int* ranges /* n_envs x 3: start, count, Pd */,
+                           int n_envs, double* out, int stride) {
+    const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= n_envs) return;
+    const int start = ranges[3 * env], count = ranges[3 * env + 1], Pd = ranges[3 * env + 2];
+    const double2* pos = reinterpret_cast<const double2*>(state + envs[env].state_off);
+    const double2* vel = pos + Pd;
+    double sx = 0.0, sy = 0.0, vx = 0.0, vy = 0.0;
+    for (int i = lane; i < count; i += 32) {
+        const double2 q = pos[start + i], v = vel[start + i];
+        sx += q.x; sy += q.y; vx += v.x; vy += v.y;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sx += __shfl_xor_sync(0xffffffffu, sx, o); sy += __shfl_xor_sync(0xffffffffu, sy, o);
+        vx += __shfl_xor_sync(0xffffffffu, vx, o); vy += __shfl_xor_sync(0xffffffffu, vy, o);
+    }
+    double* row = out + (size_t)env * stride;
+    const double cx = count ? sx / count : 0.0, cy = count ? sy / count : 0.0;
+    if (lane == 0 && stride >= 2) { row[0] = count ? vx / count : 0.0; row[1] = count ? vy / count : 0.0; }
+    for (int i = lane; i < count; i += 32) {
+        const double2 q = pos[start + i];
+        if (2 + i < stride) row[2 + i] = q.x - cx;
+        if (2 + count + i < stride) row[2 + count + i] = q.y - cy;
+    }
+    for (int i = 2 + 2 * count + lane; i < stride; i += 32) row[i] = 0.0;
+}
+
 }  // namespace mevo

@@ -341,6 +341,17 @@ public:
         return a;
     }
     void object_com_device(int obj, std::uintptr_t ptr) { chk(mevo_batch_object_com_device(b_, obj, reinterpret_cast<double*>(ptr))); }
+    // (n_envs, width) rows [vel com, relative x, relative y, zeros]: what Walker-v0 observes (evogym/envs/walk.py:58-61)
+    py::array_t<double> object_obs(int obj) {
+        const int w = mevo_batch_object_obs_width(b_, obj);
+        if (w < 0) throw std::runtime_error(mevo_last_error());
+        py::array_t<double> a({(py::ssize_t)mevo_batch_num_envs(b_), (py::ssize_t)w});
+        chk(mevo_batch_object_obs(b_, obj, a.mutable_data(), w));
+        return a;
+    }
+    void object_obs_device(int obj, std::uintptr_t ptr, int stride) {
+        chk(mevo_batch_object_obs_device(b_, obj, reinterpret_cast<double*>(ptr), stride));
+    }
     std::uintptr_t cuda_stream() { return reinterpret_cast<std::uintptr_t>(mevo_batch_cuda_stream(b_)); }
     long long unstable_events() { return mevo_batch_unstable_events(b_); }
 
@@ -420,6 +431,8 @@ PYBIND11_MODULE(simulator_cpp, m) {
         .def("vel", &BatchSim::vel)
         .def("object_com", &BatchSim::object_com)
         .def("object_com_device", &BatchSim::object_com_device)
+        .def("object_obs", &BatchSim::object_obs)
+        .def("object_obs_device", &BatchSim::object_obs_device)
         .def_property_readonly("cuda_stream", &BatchSim::cuda_stream)
         .def_property_readonly("unstable_events", &BatchSim::unstable_events);
 }

@@ -6,7 +6,7 @@ import random
 import numpy as np
 import pytest
 
-from helpers import rel_err
+from helpers import Golden, rel_err
 from modularevogym_b200 import capi
 from modularevogym_b200.world import sample_robot, walker_world
 from oracle.oracle import OracleSim
@@ -135,3 +135,32 @@ def test_full_size_properties():
             o.step()
         a, b = o.topo.objects[0].min_point, o.topo.objects[0].max_point + 1
         assert rel_err(com1[k], o.get_state()[0][a:b].mean(axis=0)) <= 1e-8
+
+
+def test_walker_observation_rows():
+    """On-device Walker-v0 observation (evogym/envs/walk.py:58-61: get_vel_com_obs + get_relative_pos_obs,
+    evogym/envs/base.py:214-240) against the same numpy expressions on the downloaded state."""
+    gs = [Golden(n) for n in ("walker_s0", "walker_s1", "walker_dense", "pusher_s3")]
+    B = capi.Batch(0)
+    for g in gs:
+        B.add_world(g.world)
+    B.finalize()
+    rng = np.random.default_rng(5)
+    B.set_actions(np.clip(rng.uniform(-1, 1, (len(gs), B.action_stride)) + 1.0, 0.6, 1.6))
+    B.step(2)
+    obs = B.object_obs(0)
+    width = obs.shape[1]
+    for i, g in enumerate(gs):
+        a, b = int(g.obj_info[0, 1]), int(g.obj_info[0, 2])
+        pos, vel = B.get_state(i)[:2]
+        p = pos[a:b + 1].T                      # (2, n) like Sim::object_pos_at_time
+        v = vel[a:b + 1].T
+        want = np.concatenate((np.mean(v, axis=1), (p - np.array([np.mean(p, axis=1)]).T).flatten()))
+        assert width >= want.size
+        assert np.max(np.abs(obs[i, :want.size] - want)) <= 1e-12
+        assert not obs[i, want.size:].any()
+    com = B.object_com(0)
+    for i, g in enumerate(gs):
+        a, b = int(g.obj_info[0, 1]), int(g.obj_info[0, 2])
+        assert np.max(np.abs(com[i] - B.get_state(i)[0][a:b + 1].mean(axis=0))) <= 1e-12
+    B.close()
