@@ -458,24 +458,34 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             int cnt = 0;     // warp-uniform number of candidates in this warp's segment
             unsigned int* myseg = cand + warp * seg_cap;
             // (i) dynamic-vs-dynamic leaf pairs from the precomputed pair table (each unordered pair once)
-            for (int base = 0; base < H.n_pairs; base += G) {
-                const int i = base + t;
-                bool hit = false;
-                unsigned int code = 0;
-                if (i < H.n_pairs) {
-                    code = __ldg(pairs + i);
-                    const int a = code & kCodeLeafMask, b = (code >> 12) & kCodeLeafMask;
-                    hit = aabb_overlap(aabb[a], aabb[b]);
-                    if (hit && (code & kCodeCount))                // ordered pairs (a,b) and (b,a) both count (a-12)
-                        atomicAdd((int*)&misc[16 + (code >> kCodeObjShift)], 2);
+            //     four pairs per thread in flight: the table is read from L2
+            for (int base = 0; base < H.n_pairs; base += 4 * G) {
+                unsigned int code[4];
+                bool hit[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int i = base + u * G + t;
+                    code[u] = __ldg(pairs + (i < H.n_pairs ? i : base));
                 }
-                const unsigned m = __ballot_sync(0xffffffffu, hit);
-                if (hit) {
-                    const int at = cnt + __popc(m & ((1u << lane) - 1u));
-                    if (at < seg_cap) myseg[at] = code & (kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj);
-                    else overflow = true;
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int i = base + u * G + t;
+                    const int a = code[u] & kCodeLeafMask, b = (code[u] >> 12) & kCodeLeafMask;
+                    hit[u] = (i < H.n_pairs) & aabb_overlap(aabb[a], aabb[b]);
+                    if (hit[u] && (code[u] & kCodeCount))          // ordered pairs (a,b) and (b,a) both count (a-12)
+                        atomicAdd((int*)&misc[16 + (code[u] >> kCodeObjShift)], 2);
                 }
-                cnt += __popc(m);
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (base + u * G >= H.n_pairs) break;
+                    const unsigned m = __ballot_sync(0xffffffffu, hit[u]);
+                    if (hit[u]) {
+                        const int at = cnt + __popc(m & ((1u << lane) - 1u));
+                        if (at < seg_cap) myseg[at] = code[u] & (kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj);
+                        else overflow = true;
+                    }
+                    cnt += __popc(m);
+                }
             }
             // (ii) dynamic leaves vs the static uniform grid (cell = one voxel); the window is widened
             //      by one cell each way, then the exact closed-interval test decides
