@@ -149,18 +149,28 @@ class CpuPool:
 # clocks during the timed region (B200_PROFILING.md)
 
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi clocks and throttle reasons, sampled every 20 ms from before the warm-up; stop() keeps the samples
+    whose timestamps fall inside the timed region [mark_start(), mark_end()] (all samples under load if the region
+    was shorter than the sampling period)."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index: int):
         self.path = tempfile.mktemp(prefix="mevo_clocks_", suffix=".csv")
         self.proc = None
+        self.t0 = self.t1 = None
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
+
+    def mark_start(self) -> None:
+        self.t0 = time.time()
+
+    def mark_end(self) -> None:
+        self.t1 = time.time()
 
     def stop(self) -> dict:
         if self.proc is None:
@@ -171,25 +181,30 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         self.f.close()
-        sm, mx, reasons = [], [], set()
+        import datetime
+        rows = []
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         for line in open(self.path):
             c = [x.strip() for x in line.split(",")]
             if len(c) < 9:
                 continue
             try:
-                sm.append(float(c[1])); mx.append(float(c[2]))
+                ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(c[1]), float(c[2]), [n for n, v in zip(names, c[5:9]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for n, v in zip(names, c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
         try:
             os.unlink(self.path)
         except OSError:
             pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        inside = [r for r in rows if self.t0 is not None and self.t1 is not None and self.t0 <= r[0] <= self.t1]
+        window = "timed region"
+        if not inside:
+            inside, window = [r for r in rows if self.t0 is None or r[0] >= self.t0 - 1.0], "warm-up + timed region (timed region shorter than the sampling period)"
+        reasons = sorted({n for r in inside for n in r[3]})
+        return {"sm_mhz": float(np.median([r[1] for r in inside])) if inside else None,
+                "sm_max_mhz": max(r[2] for r in inside) if inside else None,
+                "samples": len(inside), "window": window, "reasons": reasons}
 
 
 def dist_env():
@@ -292,13 +307,15 @@ def main_ours(args) -> None:
         B.bind_actions_device(acts_dev[s].data_ptr(), stride)
         B.step_async(1, True)
 
+    clocks = ClockSampler(local) if rank == 0 else None
     for s in range(W):
         resident_step(s)
     barrier()
     ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    clocks = ClockSampler(local) if rank == 0 else None
     launches = 0
+    if clocks:
+        clocks.mark_start()
     t_wall = time.perf_counter()
     for s in range(K):
         flush_l2()                                           # between timed iterations, outside the events
@@ -316,6 +333,8 @@ def main_ours(args) -> None:
         assert gathered.shape[0] == world * n
     barrier()
     t_wall = time.perf_counter() - t_wall
+    if clocks:
+        clocks.mark_end()
     clock_info = clocks.stop() if clocks else None
     dev_ms = sum(a.elapsed_time(b) for a, b in zip(ev0, ev1))
     events_before = B.unstable_events
@@ -395,7 +414,7 @@ def main() -> None:
         return
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--envs", type=int, default=4096, help="environments per GPU")
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")

@@ -123,7 +123,7 @@ __device__ __noinline__ void warp_jacobi_limiter(double2* pos, double2* ef2, con
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const unsigned ent = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-            const double2 c = ef2[min(ent, (unsigned)zero_idx)];
+            const double2 c = ef2[ent];
             x.x += c.x; x.y += c.y;
         }
         pos[p] = x;
@@ -484,7 +484,7 @@ __device__ __noinline__ void warp_rk4(unsigned char* sm, unsigned fixmask) {
                     for (int j = 0; j < 4; j++) {
                         const int q = 4 * half + j;
                         const unsigned ent = (w[q >> 1] >> ((q & 1) * 16)) & 0xffffu;
-                        f[j] = ef2[min(ent, (unsigned)S::kZero)];
+                        f[j] = ef2[ent];
                     }
 #pragma unroll
                     for (int j = 0; j < 4; j++) { Fx += f[j].x; Fy += f[j].y; }
@@ -696,7 +696,17 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             pos[i] = g2[i];
             vel[i] = g2[Pd + i];
             vt[i] = g2[3 * Pd + i];
-            csr[i] = __ldg(reinterpret_cast<const uint4*>(db + Hp->o_csr8) + i);
+            {
+                // empty gather slots (0xffff) point at the all-zero entry of ef2 from here on
+                uint4 rec = __ldg(reinterpret_cast<const uint4*>(db + Hp->o_csr8) + i);
+                unsigned* w = reinterpret_cast<unsigned*>(&rec);
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    if ((w[q] & 0xffffu) == 0xffffu) w[q] = (w[q] & 0xffff0000u) | (unsigned)S::kZero;
+                    if ((w[q] >> 16) == 0xffffu) w[q] = (w[q] & 0xffffu) | ((unsigned)S::kZero << 16);
+                }
+                csr[i] = rec;
+            }
             if (__ldg(db + Hp->o_fixed + i)) fixmask |= 1u << k;
         }
         double* goal = reinterpret_cast<double*>(sm + S::o_goal);
