@@ -156,6 +156,46 @@ int mevo_batch_object_obs_width(mevo_batch* b, int obj);
 int mevo_batch_object_obs(mevo_batch* b, int obj, double* out, int stride);                 /* host, n_envs x stride */
 int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int stride);   /* device, on the stream, no sync */
 
+/* ---- task layer: the gym environments either side of Sim::step, batched on the device ----------------- */
+/* What evogym/envs/walk.py:35-84 (WalkingFlat, Walker-v0), evogym/envs/manipulate.py:346-398 (PushSmallRect,
+ * Pusher-v0) and manipulate.py:535-600 (ThrowSmallRect, Thrower-v0) compute around `EvoGymBase.step`:
+ * policy action + 1 clipped to [0.6, 1.6] (base.py:384-391, 40-45), reward, done, the flat observation, and
+ * ModularEvoGym's per-voxel observation (base.py:427-506, 746-753); plus what the vec-env worker does when an
+ * environment is done (reset, return the reset observation) and gym's TimeLimit.  Values are in the units the
+ * reference's environments see.  All *_device entry points enqueue on the batch's stream and do not sync. */
+#define MEVO_TASK_WALKER 0
+#define MEVO_TASK_PUSHER 1
+#define MEVO_TASK_THROWER 2
+#define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
+#define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
+#define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */
+/* package: NULL for MEVO_TASK_WALKER.  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
+int mevo_batch_task_configure(mevo_batch* b, int task, const char* robot, const char* package, int max_episode_steps);
+/* dims[0..4] = flat observation width, modular observation width (9 x voxels), "other" observation width,
+ * largest voxel count of a robot grid, action stride */
+int mevo_batch_task_dims(mevo_batch* b, int* dims);
+/* per environment, host: obs_index_array (voxels x 4: TL, TR, BL, BR point index, -1 = empty voxel; base.py:427-466),
+ * act_mask (base.py:536-545), obs_mask (base.py:547-557); any pointer may be NULL; returns voxel_corner_size */
+int mevo_batch_task_env_tables(mevo_batch* b, int env, int* index_array, int* act_mask, int* obs_mask, int cap_voxels);
+/* transform_to_modular_obs on a bare h x w voxel grid (row 0 = top), host only, no GPU needed; out: h*w*4 ints */
+int mevo_modular_corner_index(const int* body, int h, int w, int* out);
+/* policy outputs -> action buffer of the next step.  per_voxel = 0: actions[env * stride + slot] (flat mode);
+ * per_voxel = 1: one value per voxel of the robot grid, actuator voxels picked in row-major order (walk.py:41-42) */
+int mevo_batch_task_apply_policy(mevo_batch* b, const double* host_actions, int stride, int per_voxel);
+int mevo_batch_task_apply_policy_device(mevo_batch* b, const void* device_actions, int stride, int per_voxel, int is_f32);
+/* after mevo_batch_step*: reward (n_envs), done bytes (n_envs), observations (n_envs x stride, zero padded); any
+ * output may be NULL.  reset_done = 1: environments that are done are reverted to snapshot 0 first and their
+ * observation is the reset observation (vec-env semantics). */
+int mevo_batch_task_outputs(mevo_batch* b, double* reward, unsigned char* done, double* flat, int flat_stride, double* modular,
+                            int modular_stride, double* other, int other_stride, int reset_done);
+int mevo_batch_task_outputs_device(mevo_batch* b, void* reward, unsigned char* done, void* flat, int flat_stride, void* modular,
+                                   int modular_stride, void* other, int other_stride, int is_f32, int reset_done);
+/* env.reset() of every environment (EvoGymBase.reset, base.py:47-51): state <- snapshot 0, observation returned */
+int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* modular, int modular_stride, double* other,
+                          int other_stride);
+int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
+                                 int other_stride, int is_f32);
+
 /* device pointers for zero-copy consumers (valid until the next finalize) */
 double* mevo_batch_actions_device_ptr(mevo_batch* b);
 const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b);

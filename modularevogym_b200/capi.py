@@ -75,6 +75,16 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_object_obs_width": (_i, [_vp, _i]),
     "mevo_batch_object_obs": (_i, [_vp, _i, _dp, _i]),
     "mevo_batch_object_obs_device": (_i, [_vp, _i, _vp, _i]),
+    "mevo_batch_task_configure": (_i, [_vp, _i, _cp, _cp, _i]),
+    "mevo_batch_task_dims": (_i, [_vp, _ip]),
+    "mevo_batch_task_env_tables": (_i, [_vp, _i, _ip, _ip, _ip, _i]),
+    "mevo_modular_corner_index": (_i, [_ip, _i, _i, _ip]),
+    "mevo_batch_task_apply_policy": (_i, [_vp, _dp, _i, _i]),
+    "mevo_batch_task_apply_policy_device": (_i, [_vp, _vp, _i, _i, _i]),
+    "mevo_batch_task_outputs": (_i, [_vp, _dp, _bp, _dp, _i, _dp, _i, _dp, _i, _i]),
+    "mevo_batch_task_outputs_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i]),
+    "mevo_batch_task_reset": (_i, [_vp, _dp, _i, _dp, _i, _dp, _i]),
+    "mevo_batch_task_reset_device": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i]),
     "mevo_batch_actions_device_ptr": (_vp, [_vp]),
     "mevo_batch_unstable_device_ptr": (_vp, [_vp]),
     "mevo_batch_cuda_stream": (_vp, [_vp]),
@@ -83,6 +93,9 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_env_read_candidates": (_i, [_vp, _i, _ip, _i]),
     "mevo_env_error_flags": (_i, [_vp, _i]),
 }
+
+MEVO_TASK_WALKER, MEVO_TASK_PUSHER, MEVO_TASK_THROWER = 0, 1, 2
+MEVO_DONE, MEVO_DONE_TRUNCATED, MEVO_DONE_UNSTABLE = 1, 2, 4      # done byte bits (include/mevo_b200.h)
 
 _lib = None
 
@@ -400,6 +413,57 @@ class Batch:
     def object_obs_device(self, obj: int, device_ptr: int, stride: int) -> None:
         _check(self.L.mevo_batch_object_obs_device(self.h, int(obj), C.c_void_p(device_ptr), int(stride)))
 
+    # -- task layer (gym environments either side of Sim::step; include/mevo_b200.h "task layer")
+    def task_configure(self, task: int, robot: str = "robot", package: Optional[str] = None, max_episode_steps: int = 0) -> None:
+        _check(self.L.mevo_batch_task_configure(self.h, int(task), robot.encode(), package.encode() if package else None,
+                                                int(max_episode_steps)))
+
+    def task_dims(self) -> dict:
+        d = np.zeros(5, dtype=np.int32)
+        _check(self.L.mevo_batch_task_dims(self.h, _iptr(d)))
+        return dict(zip(("flat", "modular", "other", "max_voxels", "action_stride"), (int(v) for v in d)))
+
+    def task_env_tables(self, env: int) -> dict:
+        nv = self.task_dims()["max_voxels"]
+        idx, am, om = np.full((nv, 4), -1, dtype=np.int32), np.zeros(nv, dtype=np.int32), np.zeros(nv, dtype=np.int32)
+        corner = _check(self.L.mevo_batch_task_env_tables(self.h, int(env), _iptr(idx), _iptr(am), _iptr(om), nv))
+        return {"obs_index_array": idx, "act_mask": am, "obs_mask": om, "voxel_corner_size": corner}
+
+    def task_apply_policy(self, actions: np.ndarray, per_voxel: bool = False) -> None:
+        a = np.ascontiguousarray(actions, dtype=np.float64)
+        _check(self.L.mevo_batch_task_apply_policy(self.h, _dptr(a), a.shape[1], int(per_voxel)))
+
+    def task_apply_policy_device(self, device_ptr: int, stride: int, per_voxel: bool, is_f32: bool) -> None:
+        _check(self.L.mevo_batch_task_apply_policy_device(self.h, C.c_void_p(device_ptr), int(stride), int(per_voxel), int(is_f32)))
+
+    def _task_bufs(self):
+        d, n = self.task_dims(), self.num_envs
+        return np.zeros((n, d["flat"])), np.zeros((n, d["modular"])), np.zeros((n, d["other"]))
+
+    def task_outputs(self, reset_done: bool = True) -> dict:
+        flat, mod, oth = self._task_bufs()
+        rew, done = np.zeros(self.num_envs), np.zeros(self.num_envs, dtype=np.uint8)
+        _check(self.L.mevo_batch_task_outputs(self.h, _dptr(rew), _bptr(done), _dptr(flat), flat.shape[1], _dptr(mod), mod.shape[1],
+                                              _dptr(oth), oth.shape[1], int(reset_done)))
+        return {"reward": rew, "done": done, "flat": flat, "modular": mod, "other": oth}
+
+    def task_outputs_device(self, reward_ptr: int, done_ptr: int, flat_ptr: int, flat_stride: int, modular_ptr: int, modular_stride: int,
+                            other_ptr: int, other_stride: int, is_f32: bool, reset_done: bool = True) -> None:
+        vp = lambda p: C.c_void_p(p) if p else None
+        _check(self.L.mevo_batch_task_outputs_device(self.h, vp(reward_ptr), vp(done_ptr), vp(flat_ptr), int(flat_stride), vp(modular_ptr),
+                                                     int(modular_stride), vp(other_ptr), int(other_stride), int(is_f32), int(reset_done)))
+
+    def task_reset(self) -> dict:
+        flat, mod, oth = self._task_bufs()
+        _check(self.L.mevo_batch_task_reset(self.h, _dptr(flat), flat.shape[1], _dptr(mod), mod.shape[1], _dptr(oth), oth.shape[1]))
+        return {"flat": flat, "modular": mod, "other": oth}
+
+    def task_reset_device(self, flat_ptr: int, flat_stride: int, modular_ptr: int, modular_stride: int, other_ptr: int, other_stride: int,
+                          is_f32: bool) -> None:
+        vp = lambda p: C.c_void_p(p) if p else None
+        _check(self.L.mevo_batch_task_reset_device(self.h, vp(flat_ptr), int(flat_stride), vp(modular_ptr), int(modular_stride),
+                                                   vp(other_ptr), int(other_stride), int(is_f32)))
+
     def object_com_ptr(self, obj: int, host_ptr: int) -> None:
         _check(self.L.mevo_batch_object_com(self.h, int(obj), C.cast(host_ptr, _dp)))
 
@@ -428,3 +492,12 @@ class Batch:
 
     def error_flags(self, env: int) -> int:
         return _check(self.L.mevo_env_error_flags(self.h, env))
+
+
+def modular_corner_index(body: np.ndarray) -> Tuple[np.ndarray, int]:
+    """``transform_to_modular_obs`` (reference ``evogym/envs/base.py:427-466``) through the library's host code: returns
+    ``(index_array (h*w, 4) [TL, TR, BL, BR], voxel_corner_size)``.  Needs no GPU."""
+    g = np.ascontiguousarray(body, dtype=np.int32)
+    out = np.zeros((g.size, 4), dtype=np.int32)
+    loc = _check(load().mevo_modular_corner_index(_iptr(g), g.shape[0], g.shape[1], _iptr(out)))
+    return out, loc

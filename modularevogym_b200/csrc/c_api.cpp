@@ -359,6 +359,87 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
     });
 }
 
+// ---- task layer ---------------------------------------------------------------------------------
+
+int mevo_batch_task_configure(mevo_batch* b, int task, const char* robot, const char* package, int max_episode_steps) {
+    return guard([&] {
+        if (!robot) throw std::invalid_argument("task_configure: robot name is null");
+        b->impl.task_configure(task, robot, package ? package : "", max_episode_steps);
+        return 0;
+    });
+}
+
+int mevo_batch_task_dims(mevo_batch* b, int* dims) {
+    return guard([&] {
+        if (!dims) throw std::invalid_argument("task_dims: null output");
+        b->impl.task_dims(dims);
+        return 0;
+    });
+}
+
+int mevo_batch_task_env_tables(mevo_batch* b, int env, int* index_array, int* act_mask, int* obs_mask, int cap_voxels) {
+    return guard([&] { return b->impl.task_env_tables(env, index_array, act_mask, obs_mask, cap_voxels); });
+}
+
+int mevo_modular_corner_index(const int* body, int h, int w, int* out) {
+    return guard([&] {
+        if (!body || !out || h <= 0 || w <= 0) throw std::invalid_argument("modular_corner_index: bad arguments");
+        std::vector<int> grid(body, body + (size_t)h * w), idx;
+        const int loc = mevo::modular_corner_index(grid, h, w, idx);
+        std::copy(idx.begin(), idx.end(), out);
+        return loc;
+    });
+}
+
+int mevo_batch_task_apply_policy(mevo_batch* b, const double* host_actions, int stride, int per_voxel) {
+    return guard([&] {
+        if (!host_actions) throw std::invalid_argument("task_apply_policy: null actions");
+        b->impl.task_apply_policy(host_actions, stride, per_voxel != 0);
+        return 0;
+    });
+}
+
+int mevo_batch_task_apply_policy_device(mevo_batch* b, const void* device_actions, int stride, int per_voxel, int is_f32) {
+    return guard([&] {
+        if (!device_actions) throw std::invalid_argument("task_apply_policy_device: null actions");
+        b->impl.task_apply_policy_device(device_actions, stride, per_voxel != 0, is_f32 != 0);
+        return 0;
+    });
+}
+
+int mevo_batch_task_outputs(mevo_batch* b, double* reward, unsigned char* done, double* flat, int flat_stride, double* modular,
+                            int modular_stride, double* other, int other_stride, int reset_done) {
+    return guard([&] {
+        b->impl.task_outputs(reward, done, flat, flat_stride, modular, modular_stride, other, other_stride, reset_done != 0);
+        return 0;
+    });
+}
+
+int mevo_batch_task_outputs_device(mevo_batch* b, void* reward, unsigned char* done, void* flat, int flat_stride, void* modular,
+                                   int modular_stride, void* other, int other_stride, int is_f32, int reset_done) {
+    return guard([&] {
+        b->impl.task_outputs_device(reward, done, flat, flat_stride, modular, modular_stride, other, other_stride, is_f32 != 0,
+                                    reset_done != 0);
+        return 0;
+    });
+}
+
+int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* modular, int modular_stride, double* other,
+                          int other_stride) {
+    return guard([&] {
+        b->impl.task_reset(flat, flat_stride, modular, modular_stride, other, other_stride);
+        return 0;
+    });
+}
+
+int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
+                                 int other_stride, int is_f32) {
+    return guard([&] {
+        b->impl.task_reset_device(flat, flat_stride, modular, modular_stride, other, other_stride, is_f32 != 0);
+        return 0;
+    });
+}
+
 double* mevo_batch_actions_device_ptr(mevo_batch* b) { return b->impl.actions_device_ptr(); }
 const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b) { return b->impl.unstable_device_ptr(); }
 void* mevo_batch_cuda_stream(mevo_batch* b) { return b->impl.stream(); }

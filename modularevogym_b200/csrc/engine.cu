@@ -178,6 +178,7 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
 
 Batch::~Batch() {
     cudaSetDevice(device_);
+    task_free();
 #ifdef MEVO_PROF
     {
         unsigned long long h[16];
@@ -682,6 +683,7 @@ void Batch::finalize() {
     CUDA_CHECK(cudaMemcpy(d_state_, host_state.data(), sizeof(double) * (state_doubles + 2), cudaMemcpyHostToDevice));
     CUDA_CHECK(cudaMemcpy(d_state0_, host_state0.data(), sizeof(double) * (state_doubles + 2), cudaMemcpyHostToDevice));
     finalized_ = true;
+    finalize_epoch_++;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -104,6 +104,24 @@ public:
     void object_obs_device(int obj_index, double* out_device, int stride);   // async on stream()
     void object_obs(int obj_index, double* out_host, int stride);
 
+    // ---- task layer (task.cu): what the reference's gym envs compute either side of Sim::step, on the device.
+    // task: 0 Walker-v0 (walk.py WalkingFlat), 1 Pusher-v0 (manipulate.py PushSmallRect), 2 Thrower-v0 (ThrowSmallRect)
+    void task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps);
+    void task_dims(int* dims /* flat width, modular width, other width, max voxels, action stride */);
+    // per env host tables: obs_index_array (n_vox x 4: TL,TR,BL,BR), act_mask, obs_mask; returns voxel_corner_size
+    int task_env_tables(int env, int* index_array, int* act_mask, int* obs_mask, int cap_voxels);
+    // policy output (one value per actuator slot, or per voxel in modular mode) -> +1, clip [0.6, 1.6] -> action buffer
+    void task_apply_policy_device(const void* actions, int stride, bool per_voxel, bool is_f32);
+    void task_apply_policy(const double* host_actions, int stride, bool per_voxel);
+    // after step(): reward, done flags (bit 0 done, bit 1 truncated by the step limit, bit 2 unstable), observations of the
+    // resulting state; reset_done: environments that are done are reverted to snapshot 0 first (vec-env semantics)
+    void task_outputs_device(void* reward, unsigned char* done, void* flat, int flat_stride, void* modular, int modular_stride,
+                             void* other, int other_stride, bool is_f32, bool reset_done);
+    void task_outputs(double* reward, unsigned char* done, double* flat, int flat_stride, double* modular, int modular_stride,
+                      double* other, int other_stride, bool reset_done);
+    void task_reset_device(void* flat, int flat_stride, void* modular, int modular_stride, void* other, int other_stride, bool is_f32);
+    void task_reset(double* flat, int flat_stride, double* modular, int modular_stride, double* other, int other_stride);
+
     // debug / test hooks: candidate pairs of the first substep of the next step() call
     void enable_candidate_dump(int cap_per_env);
     int read_candidates(int env, int* out_pairs /* cap x 4: kind_a, leaf_a, kind_b, leaf_b */, int cap);
@@ -116,6 +134,9 @@ public:
 
 private:
     struct Impl;
+    struct Task;
+    void task_build();
+    void task_free();
     void upload_state(int env);
     void download_state(int env);
     void download_all();
@@ -150,6 +171,11 @@ private:
     size_t state_doubles_ = 0;
     void* stream_ = nullptr;
     Impl* impl_ = nullptr;
+    Task* task_ = nullptr;
+    int finalize_epoch_ = 0;
 };
+
+// transform_to_modular_obs (evogym/envs/base.py:427-466), host only: corner indices per cell (h*w*4: TL,TR,BL,BR), returns loc_idx
+int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector<int>& out);
 
 }  // namespace mevo

@@ -1,0 +1,497 @@
+// Task layer: what the reference's gym environments compute either side of Sim::step, batched on the device
+// (SURVEY 8f-1 / 8f-2).  One warp per environment, one launch per env-step, no host round trip:
+//
+//   policy_actions_kernel   BenchmarkBase.step (evogym/envs/base.py:384-391: action + 1) -> EvoGymBase.step
+//                           (base.py:40-45: clip to [0.6, 1.6]); in modular mode the action is one value per
+//                           voxel and the actuator voxels are picked in row-major order (walk.py:41-42
+//                           `action[~act_mask]`).
+//   task_outputs_kernel     reward / done / observation of
+//                             WalkingFlat    evogym/envs/walk.py:35-84        (Walker-v0)
+//                             PushSmallRect  evogym/envs/manipulate.py:346-398 (Pusher-v0)
+//                             ThrowSmallRect manipulate.py:535-600             (Thrower-v0)
+//                           flat observation (walk.py:58-61, manipulate.py:22-36) and ModularEvoGym's per-voxel
+//                           observation (base.py:427-506 transform_to_modular_obs / modular_ob_wrapper_padding,
+//                           base.py:746-753 get_modular_obs); then what the vec-env worker does on `done`
+//                           (examples/modular_envs/wrappers/subproc_vec_env.py: reset and return the reset
+//                           observation) and gym's TimeLimit.
+//
+// Unit convention of the reference, kept operation for operation: EvoSim getters divide engine metres by
+// VOXEL_SIZE = 0.1 (evogym/sim.py:188-231), BenchmarkBase multiplies by 0.1 again (base.py:393-421).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "device_layout.h"
+#include "engine.h"
+
+namespace mevo {
+
+#define CUDA_CHECK(expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess)                                                                    \
+            throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " + \
+                                     __FILE__ + ":" + std::to_string(__LINE__) + " (" #expr ")");   \
+    } while (0)
+
+namespace {
+
+constexpr double kVoxel = 0.1;          // EvoSim.VOXEL_SIZE, BenchmarkBase.VOXEL_SIZE
+
+struct TaskEnvRec {                      // 32 bytes per environment
+    int r_start, r_count;                // robot: first dynamic-local point, point count
+    int p_start, p_count;                // package (count 0: task has none)
+    int Pd;                              // dynamic points of the env (state section length)
+    int vox_off, n_vox;                  // rows of the modular table
+    int n_act;
+};
+
+struct TaskParams {
+    const double* state;
+    double* state_rw;
+    const double* state0;
+    const EnvDesc* envs;
+    const TaskEnvRec* tenv;
+    const short4* vox_idx;               // per modular row: TL, TR, BL, BR point index inside the robot, -1 = empty voxel
+    const unsigned char* vox_mat;        // per modular row: voxel type
+    double* prev;                        // per env: robot com x, y, package com x, y at the last observation
+    int* episode_len;
+    unsigned char* unstable;             // flags of the last step launch (cleared for environments reset here)
+    int* sim_time;
+    void* reward; unsigned char* done;
+    void* flat; int flat_stride;
+    void* modular; int modular_stride;
+    void* other; int other_stride;
+    int n_envs, task, max_episode_steps, reset_done, other_width;
+};
+
+struct ObjMeans { double ax, ay, bx, by, cx, cy, dx, dy; };
+
+// means over one object's points of: a = (x / 0.1) * 0.1 (BenchmarkBase.object_pos_at_time), b = x / 0.1
+// (EvoSim.object_pos_at_time), c = v / 0.1, d = (v / 0.1) * 0.1.
+__device__ __forceinline__ ObjMeans object_means(const double2* pos, const double2* vel, int start, int count, int lane) {
+    ObjMeans m = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = lane; i < count; i += 32) {
+        const double2 q = pos[start + i], v = vel[start + i];
+        const double qx = q.x / kVoxel, qy = q.y / kVoxel, vx = v.x / kVoxel, vy = v.y / kVoxel;
+        m.ax += qx * kVoxel; m.ay += qy * kVoxel; m.bx += qx; m.by += qy;
+        m.cx += vx; m.cy += vy; m.dx += vx * kVoxel; m.dy += vy * kVoxel;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m.ax += __shfl_xor_sync(0xffffffffu, m.ax, o); m.ay += __shfl_xor_sync(0xffffffffu, m.ay, o);
+        m.bx += __shfl_xor_sync(0xffffffffu, m.bx, o); m.by += __shfl_xor_sync(0xffffffffu, m.by, o);
+        m.cx += __shfl_xor_sync(0xffffffffu, m.cx, o); m.cy += __shfl_xor_sync(0xffffffffu, m.cy, o);
+        m.dx += __shfl_xor_sync(0xffffffffu, m.dx, o); m.dy += __shfl_xor_sync(0xffffffffu, m.dy, o);
+    }
+    if (count > 0) {
+        const double n = (double)count;
+        m.ax /= n; m.ay /= n; m.bx /= n; m.by /= n; m.cx /= n; m.cy /= n; m.dx /= n; m.dy /= n;
+    }
+    return m;
+}
+
+template <typename OutT>
+__global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
+    const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= p.n_envs) return;
+    const TaskEnvRec te = p.tenv[env];
+    const size_t soff = p.envs[env].state_off;
+    double2* pos = reinterpret_cast<double2*>(p.state_rw + soff);
+    double2* vel = pos + te.Pd;
+
+    const bool unstable = p.unstable[env] != 0;
+    const double ri_x = p.prev[4 * env], pi_x = p.prev[4 * env + 2], pi_y = p.prev[4 * env + 3];
+    ObjMeans R = object_means(pos, vel, te.r_start, te.r_count, lane);
+    ObjMeans P = object_means(pos, vel, te.p_start, te.p_count, lane);
+    // Sim::step that reports "unstable" saves no snapshot and does not advance time (Sim.cpp:105-115): the
+    // environment then reads the same snapshot before and after the step.
+    const double rf_x = unstable ? ri_x : R.ax;
+    const double pf_x = unstable ? pi_x : P.ax, pf_y = unstable ? pi_y : P.ay;
+
+    double reward;
+    bool done = unstable;
+    if (p.task == 0) {                                   // walk.py:70-84
+        reward = rf_x - ri_x;
+    } else if (p.task == 1) {                            // manipulate.py:38-58
+        reward = (pf_x - pi_x) * 0.75;
+        reward += (rf_x - ri_x) * 0.5;
+        reward += fabs(ri_x - pi_x) - fabs(rf_x - pf_x);
+        if (pf_y < 0.0 * kVoxel) reward += 10 * (pf_y - pi_y);
+    } else {                                             // manipulate.py:545-562
+        double motion_penalty = (ri_x - rf_x) * 0.25;
+        if (rf_x < 0) motion_penalty *= -1;
+        reward = pf_x - pi_x + motion_penalty;
+    }
+    if (unstable) reward -= 3.0;
+    if (p.task != 2 && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
+    int flags = (done ? 1 : 0) | (unstable ? 4 : 0);
+    int ep = p.episode_len[env] + 1;
+    if (p.max_episode_steps > 0 && ep >= p.max_episode_steps) {   // gym TimeLimit: truncated = not already done
+        if (!done) flags |= 2;
+        flags |= 1;
+    }
+    if ((flags & 1) && p.reset_done) {
+        // Environment::revert_to_snapshot(0) (Environment.cpp:247-263): pos, vel <- snapshot 0; pos_last <- pos;
+        // vel_true <- vel; length_eq_goal untouched.
+        const double2* s0 = reinterpret_cast<const double2*>(p.state0 + soff);
+        for (int i = lane; i < te.Pd; i += 32) {
+            const double2 q = s0[i], v = s0[te.Pd + i];
+            pos[i] = q; vel[i] = v; pos[2 * te.Pd + i] = q; pos[3 * te.Pd + i] = v;
+        }
+        __syncwarp();
+        if (lane == 0) { p.sim_time[env] = 0; p.unstable[env] = 0; }
+        ep = 0;
+        R = object_means(pos, vel, te.r_start, te.r_count, lane);
+        P = object_means(pos, vel, te.p_start, te.p_count, lane);
+    }
+    if (lane == 0) {
+        p.episode_len[env] = ep;
+        p.prev[4 * env] = R.ax; p.prev[4 * env + 1] = R.ay; p.prev[4 * env + 2] = P.ax; p.prev[4 * env + 3] = P.ay;
+        if (p.reward) reinterpret_cast<OutT*>(p.reward)[env] = (OutT)reward;
+        if (p.done) p.done[env] = (unsigned char)flags;
+    }
+
+    // ---- observations of the (possibly reset) state
+    double oth[6];
+    if (p.task == 0) {                                   // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+        oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;
+    } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
+        oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
+    }
+    const int ow = p.other_width;
+    if (p.other) {
+        OutT* row = reinterpret_cast<OutT*>(p.other) + (size_t)env * p.other_stride;
+        if (lane < p.other_stride) row[lane] = lane < ow ? (OutT)oth[lane < 6 ? lane : 0] : (OutT)0;
+        for (int i = 32 + lane; i < p.other_stride; i += 32) row[i] = (OutT)0;
+    }
+    if (p.flat) {                                        // walk.py:58-61 / manipulate.py:363-367
+        OutT* row = reinterpret_cast<OutT*>(p.flat) + (size_t)env * p.flat_stride;
+        if (lane < ow && lane < p.flat_stride) row[lane] = (OutT)oth[lane < 6 ? lane : 0];
+        const int n = te.r_count;
+        for (int i = lane; i < n; i += 32) {             // get_relative_pos_obs (base.py:228-240 * VOXEL_SIZE)
+            const double2 q = pos[te.r_start + i];
+            if (ow + i < p.flat_stride) row[ow + i] = (OutT)((q.x / kVoxel - R.bx) * kVoxel);
+            if (ow + n + i < p.flat_stride) row[ow + n + i] = (OutT)((q.y / kVoxel - R.by) * kVoxel);
+        }
+        for (int i = ow + 2 * n + lane; i < p.flat_stride; i += 32) row[i] = (OutT)0;
+    }
+    if (p.modular) {                                     // base.py:480-506: 9 values per voxel, non-empty voxels first
+        OutT* row = reinterpret_cast<OutT*>(p.modular) + (size_t)env * p.modular_stride;
+        const int total = 9 * te.n_vox;
+        for (int i = lane; i < p.modular_stride; i += 32) {
+            double v = 0.0;
+            if (i < total) {
+                const int j = i / 9, c = i - 9 * j;
+                const short4 id = p.vox_idx[te.vox_off + j];
+                if (c == 8) {
+                    v = (double)p.vox_mat[te.vox_off + j];
+                } else if (id.x >= 0) {
+                    const int k = c & 3;
+                    const int pt = k == 0 ? id.x : k == 1 ? id.y : k == 2 ? id.z : id.w;
+                    const double2 q = pos[te.r_start + pt];
+                    v = c < 4 ? (q.x / kVoxel - R.bx) * kVoxel : (q.y / kVoxel - R.by) * kVoxel;
+                }
+            }
+            row[i] = (OutT)v;
+        }
+    }
+}
+
+template <typename InT>
+__global__ void policy_actions_kernel(const InT* a, int in_stride, int per_voxel, const TaskEnvRec* tenv, const short* act_vox,
+                                      double* act, int act_stride, int n_envs) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_envs * act_stride) return;
+    const int env = idx / act_stride, slot = idx - env * act_stride;
+    double out = 1.0;
+    if (slot < tenv[env].n_act) {
+        const int col = per_voxel ? act_vox[idx] : slot;
+        // the reference adds 1 and clips in the policy's dtype (numpy keeps float32 under python scalars)
+        InT v = a[(size_t)env * in_stride + col] + (InT)1;
+        v = v < (InT)0.6 ? (InT)0.6 : v;
+        v = v > (InT)1.6 ? (InT)1.6 : v;
+        out = (double)v;
+    }
+    act[idx] = out;
+}
+
+}  // namespace
+
+struct Batch::Task {
+    int task = -1;
+    std::string robot, package;
+    int max_episode_steps = 0;
+    int epoch = -1;                          // finalize epoch the tables were built for
+    int flat_width = 0, modular_width = 0, other_width = 0, max_vox = 0;
+    std::vector<TaskEnvRec> rec;
+    std::vector<short4> vox_idx;
+    std::vector<unsigned char> vox_mat;
+    std::vector<short> act_vox;
+    std::vector<std::vector<int>> index_array;   // per env: n_vox x 4 in grid order (transform_to_modular_obs)
+    std::vector<std::vector<int>> act_mask, obs_mask;
+    std::vector<int> corner_size;
+    TaskEnvRec* d_rec = nullptr;
+    short4* d_vox_idx = nullptr;
+    unsigned char* d_vox_mat = nullptr;
+    short* d_act_vox = nullptr;
+    double* d_prev = nullptr;
+    int* d_episode = nullptr;
+    void* d_scratch = nullptr;               // host-facing outputs staged here
+    size_t scratch_bytes = 0;
+    void free_device() {
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_episode);
+        cudaFree(d_scratch);
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_episode = nullptr;
+        d_scratch = nullptr; scratch_bytes = 0;
+    }
+};
+
+void Batch::task_free() {
+    if (!task_) return;
+    task_->free_device();
+    delete task_;
+    task_ = nullptr;
+}
+
+// transform_to_modular_obs (evogym/envs/base.py:427-466) on a voxel grid, row 0 = top: for each cell the indices
+// (into the object's point list) of its TL, TR, BL, BR corners, -1 for empty cells; returns loc_idx.
+int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector<int>& out) {
+    out.assign((size_t)h * w * 4, -1);
+    auto at = [&](int y, int x, int r, int c) -> int& { return out[((size_t)(y * w + x) * 2 + r) * 2 + c]; };
+    int loc = 0;
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            if (body[y * w + x] == 0) continue;
+            const bool up = y - 1 >= 0 && body[(y - 1) * w + x] != 0;
+            const bool left = x - 1 >= 0 && body[y * w + x - 1] != 0;
+            const bool right = x + 1 < w && body[y * w + x + 1] != 0;
+            const bool up_right = x + 1 < w && y - 1 >= 0 && body[(y - 1) * w + x + 1] != 0;
+            if (up) { at(y, x, 0, 0) = at(y - 1, x, 1, 0); at(y, x, 0, 1) = at(y - 1, x, 1, 1); }
+            if (left) { at(y, x, 0, 0) = at(y, x - 1, 0, 1); at(y, x, 1, 0) = at(y, x - 1, 1, 1); }
+            if (!(up || left)) at(y, x, 0, 0) = loc++;
+            if (!up) {
+                if (right && up_right) at(y, x, 0, 1) = at(y - 1, x + 1, 1, 0);
+                else at(y, x, 0, 1) = loc++;
+            }
+            if (!left) at(y, x, 1, 0) = loc++;
+            at(y, x, 1, 1) = loc++;
+        }
+    return loc;
+}
+
+void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
+    if (task < 0 || task > 2) throw std::runtime_error("task_configure: unknown task id");
+    if (task != 0 && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
+    if (!task_) task_ = new Task();
+    task_->task = task;
+    task_->robot = robot;
+    task_->package = task == 0 ? std::string() : package;
+    task_->max_episode_steps = max_episode_steps;
+    task_->epoch = -1;
+}
+
+void Batch::task_build() {
+    if (!task_ || task_->task < 0) throw std::runtime_error("task layer used before mevo_batch_task_configure");
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (task_->epoch == finalize_epoch_) return;
+    Task& T = *task_;
+    const int n = num_envs();
+    T.free_device();
+    T.rec.assign(n, TaskEnvRec());
+    T.vox_idx.clear(); T.vox_mat.clear();
+    T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
+    T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
+    T.other_width = T.task == 0 ? 2 : 6;
+    T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
+    for (int e = 0; e < n; e++) {
+        const EnvHost& E = envs_[e];
+        const int ro = E.world.find_object(T.robot);
+        if (ro < 0) throw std::runtime_error("task: environment " + std::to_string(e) + " has no object named " + T.robot);
+        const VoxelObject& rb = E.world.objects[ro];
+        TaskEnvRec& r = T.rec[e];
+        r.Pd = (int)E.dyn_points.size();
+        r.r_start = E.point_local[rb.min_point];
+        r.r_count = rb.max_point - rb.min_point + 1;
+        if (r.r_start < 0) throw std::runtime_error("task: the robot is a static object");
+        if (!T.package.empty()) {
+            const int po = E.world.find_object(T.package);
+            if (po < 0) throw std::runtime_error("task: environment " + std::to_string(e) + " has no object named " + T.package);
+            const VoxelObject& pk = E.world.objects[po];
+            r.p_start = E.point_local[pk.min_point];
+            r.p_count = pk.max_point - pk.min_point + 1;
+            if (r.p_start < 0) throw std::runtime_error("task: the package is a static object");
+        }
+        // voxel grid of the robot, row 0 = top
+        const int w = rb.grid_w, h = rb.grid_h;
+        std::vector<int> body((size_t)w * h, 0);
+        for (const Boxel& b : rb.boxels) body[b.grid_index] = b.cell_type;
+        std::vector<int> corner;
+        T.corner_size[e] = modular_corner_index(body, h, w, corner);
+        T.index_array[e] = corner;
+        if (T.corner_size[e] > r.r_count)
+            throw std::runtime_error("task: modular corner numbering exceeds the robot's point count (env " + std::to_string(e) + ")");
+        r.vox_off = (int)T.vox_idx.size();
+        r.n_vox = w * h;
+        // modular_ob_wrapper_padding (base.py:480-506): non-empty voxels in grid order, then the empty ones
+        for (int pass = 0; pass < 2; pass++)
+            for (int v = 0; v < w * h; v++) {
+                if ((body[v] != 0) != (pass == 0)) continue;
+                short4 id;
+                id.x = (short)corner[4 * v]; id.y = (short)corner[4 * v + 1]; id.z = (short)corner[4 * v + 2]; id.w = (short)corner[4 * v + 3];
+                T.vox_idx.push_back(id);
+                T.vox_mat.push_back((unsigned char)body[v]);
+            }
+        // get_act_mask (base.py:536-545): 0 on actuator voxels; get_obs_mask (:547-557): 0 per non-empty voxel, then 1 per empty
+        T.act_mask[e].resize(w * h);
+        int k = 0, n_full = 0;
+        for (int v = 0; v < w * h; v++) {
+            const bool act = body[v] == CELL_ACT_H || body[v] == CELL_ACT_V;
+            T.act_mask[e][v] = act ? 0 : 1;
+            if (act && k < act_stride_) T.act_vox[(size_t)e * act_stride_ + k++] = (short)v;
+            n_full += body[v] != 0;
+        }
+        T.obs_mask[e].assign(w * h, 1);
+        std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
+        r.n_act = std::min(k, E.n_act);
+        T.flat_width = std::max(T.flat_width, T.other_width + 2 * r.r_count);
+        T.modular_width = std::max(T.modular_width, 9 * w * h);
+        T.max_vox = std::max(T.max_vox, w * h);
+    }
+    auto up = [&](auto*& d, const auto& v) {
+        using Elem = typename std::remove_reference<decltype(v)>::type::value_type;
+        CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&d), sizeof(Elem) * std::max<size_t>(1, v.size())));
+        if (!v.empty()) CUDA_CHECK(cudaMemcpy(d, v.data(), sizeof(Elem) * v.size(), cudaMemcpyHostToDevice));
+    };
+    up(T.d_rec, T.rec); up(T.d_vox_idx, T.vox_idx); up(T.d_vox_mat, T.vox_mat); up(T.d_act_vox, T.act_vox);
+    CUDA_CHECK(cudaMalloc(&T.d_prev, sizeof(double) * 4 * n));
+    CUDA_CHECK(cudaMalloc(&T.d_episode, sizeof(int) * n));
+    CUDA_CHECK(cudaMemset(T.d_prev, 0, sizeof(double) * 4 * n));
+    CUDA_CHECK(cudaMemset(T.d_episode, 0, sizeof(int) * n));
+    T.epoch = finalize_epoch_;
+}
+
+void Batch::task_dims(int* dims) {
+    task_build();
+    dims[0] = task_->flat_width; dims[1] = task_->modular_width; dims[2] = task_->other_width; dims[3] = task_->max_vox;
+    dims[4] = act_stride_;
+}
+
+int Batch::task_env_tables(int env, int* index_array, int* act_mask, int* obs_mask, int cap_voxels) {
+    task_build();
+    const Task& T = *task_;
+    const int nv = T.rec.at(env).n_vox;
+    if (cap_voxels < nv) throw std::runtime_error("task_env_tables: buffers too small");
+    if (index_array) std::copy(T.index_array[env].begin(), T.index_array[env].end(), index_array);
+    if (act_mask) std::copy(T.act_mask[env].begin(), T.act_mask[env].end(), act_mask);
+    if (obs_mask) std::copy(T.obs_mask[env].begin(), T.obs_mask[env].end(), obs_mask);
+    return T.corner_size[env];
+}
+
+void Batch::task_apply_policy_device(const void* actions, int stride, bool per_voxel, bool is_f32) {
+    task_build();
+    const int n = num_envs();
+    if (stride < (per_voxel ? task_->max_vox : act_stride_)) throw std::runtime_error("task_apply_policy: stride too small");
+    d_act_ext_ = nullptr;                    // the step reads the internal action buffer
+    const int total = n * act_stride_;
+    if (total == 0) return;
+    const int grid = (total + 255) / 256;
+    if (is_f32)
+        policy_actions_kernel<float><<<grid, 256, 0, (cudaStream_t)stream_>>>(static_cast<const float*>(actions), stride, per_voxel ? 1 : 0,
+                                                                             task_->d_rec, task_->d_act_vox, d_act_, act_stride_, n);
+    else
+        policy_actions_kernel<double><<<grid, 256, 0, (cudaStream_t)stream_>>>(static_cast<const double*>(actions), stride, per_voxel ? 1 : 0,
+                                                                              task_->d_rec, task_->d_act_vox, d_act_, act_stride_, n);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void Batch::task_apply_policy(const double* host_actions, int stride, bool per_voxel) {
+    task_build();
+    const size_t bytes = sizeof(double) * (size_t)stride * num_envs();
+    double* d = nullptr;
+    CUDA_CHECK(cudaMalloc(&d, bytes));
+    try {
+        CUDA_CHECK(cudaMemcpyAsync(d, host_actions, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        task_apply_policy_device(d, stride, per_voxel, false);
+        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    } catch (...) { cudaFree(d); throw; }
+    cudaFree(d);
+}
+
+void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, int flat_stride, void* modular, int modular_stride,
+                                void* other, int other_stride, bool is_f32, bool reset_done) {
+    task_build();
+    Task& T = *task_;
+    TaskParams p;
+    p.state = d_state_; p.state_rw = d_state_; p.state0 = d_state0_;
+    p.envs = reinterpret_cast<const EnvDesc*>(d_envdesc_);
+    p.tenv = T.d_rec; p.vox_idx = T.d_vox_idx; p.vox_mat = T.d_vox_mat;
+    p.prev = T.d_prev; p.episode_len = T.d_episode; p.unstable = d_unstable_; p.sim_time = d_time_;
+    p.reward = reward; p.done = done;
+    p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
+    p.other = other; p.other_stride = other_stride;
+    p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
+    p.other_width = T.other_width;
+    const int grid = (p.n_envs + 3) / 4;
+    if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
+    else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
+    CUDA_CHECK(cudaGetLastError());
+    if (reset_done) for (auto& e : envs_) e.host_fresh = false;
+}
+
+void Batch::task_outputs(double* reward, unsigned char* done, double* flat, int flat_stride, double* modular, int modular_stride,
+                         double* other, int other_stride, bool reset_done) {
+    task_build();
+    Task& T = *task_;
+    const size_t n = num_envs();
+    const size_t b_rew = sizeof(double) * n, b_flat = flat ? sizeof(double) * n * flat_stride : 0,
+                 b_mod = modular ? sizeof(double) * n * modular_stride : 0, b_oth = other ? sizeof(double) * n * other_stride : 0;
+    const size_t need = b_rew + b_flat + b_mod + b_oth + n;
+    if (need > T.scratch_bytes) {
+        cudaFree(T.d_scratch); T.d_scratch = nullptr; T.scratch_bytes = 0;
+        CUDA_CHECK(cudaMalloc(&T.d_scratch, need));
+        T.scratch_bytes = need;
+    }
+    char* base = static_cast<char*>(T.d_scratch);
+    double* d_rew = reinterpret_cast<double*>(base);
+    double* d_flat = reinterpret_cast<double*>(base + b_rew);
+    double* d_mod = reinterpret_cast<double*>(base + b_rew + b_flat);
+    double* d_oth = reinterpret_cast<double*>(base + b_rew + b_flat + b_mod);
+    unsigned char* d_done = reinterpret_cast<unsigned char*>(base + b_rew + b_flat + b_mod + b_oth);
+    task_outputs_device(d_rew, d_done, flat ? d_flat : nullptr, flat_stride, modular ? d_mod : nullptr, modular_stride,
+                        other ? d_oth : nullptr, other_stride, false, reset_done);
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (reward) CUDA_CHECK(cudaMemcpyAsync(reward, d_rew, b_rew, cudaMemcpyDeviceToHost, s));
+    if (done) CUDA_CHECK(cudaMemcpyAsync(done, d_done, n, cudaMemcpyDeviceToHost, s));
+    if (flat) CUDA_CHECK(cudaMemcpyAsync(flat, d_flat, b_flat, cudaMemcpyDeviceToHost, s));
+    if (modular) CUDA_CHECK(cudaMemcpyAsync(modular, d_mod, b_mod, cudaMemcpyDeviceToHost, s));
+    if (other) CUDA_CHECK(cudaMemcpyAsync(other, d_oth, b_oth, cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+// env.reset() of every environment (EvoGymBase.reset, base.py:47-51 -> Sim::revert(0)): state <- snapshot 0, episode
+// counters cleared, the "previous" centres of mass refreshed; observations via task_outputs(reset_done = false)
+// would add a step to the counters, so the reset observation is produced here.
+void Batch::task_reset_device(void* flat, int flat_stride, void* modular, int modular_stride, void* other, int other_stride, bool is_f32) {
+    task_build();
+    reset_all();
+    Task& T = *task_;
+    CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));   // -1: the outputs pass counts one
+    task_outputs_device(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, is_f32, false);
+}
+
+void Batch::task_reset(double* flat, int flat_stride, double* modular, int modular_stride, double* other, int other_stride) {
+    task_build();
+    reset_all();
+    Task& T = *task_;
+    CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));
+    task_outputs(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, false);
+}
+
+}  // namespace mevo

@@ -1,0 +1,145 @@
+"""Batched vector environment: the front the PPO loop talks to, on the device.
+
+Host-side mirror of what the reference assembles per rollout worker out of processes and pipes
+(``examples/transformer_ppo/envs.py:29-77`` ``make_env`` / ``make_vec_envs``: ``gym.make(env_id, body=..., mode='modular')``
+-> ``TimeLimit`` -> ``SubprocVecEnv`` (``examples/modular_envs/wrappers/subproc_vec_env.py``: reset on done, return the reset
+observation) -> ``VecPyTorch`` (``envs.py:126-159``: numpy -> float32 torch tensors on the device, reward ``(n, 1)``)),
+for the three environments the benchmark configurations name (Walker-v0, Pusher-v0, Thrower-v0).
+
+One env-step of all environments = three launches on one CUDA stream and no host round trip:
+policy output -> actuator targets (``policy_actions_kernel``), 30 substeps (``wstep_kernel`` / ``step_kernel``),
+reward / done / observation + reset of finished environments (``task_outputs_kernel``).  PyTorch is used for the
+output tensors only; all compute is in ``libmevo_b200.so`` through the C ABI (``include/mevo_b200.h``, "task layer").
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import capi
+from .world import WorldSpec, full_connectivity, pusher_world, thrower_world, walker_world
+
+# env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
+# (evogym/envs/__init__.py:16-20,125-129,149-153))
+TASKS = {
+    "Walker-v0": (0, walker_world, None, 500),
+    "Pusher-v0": (1, pusher_world, "package", 500),
+    "Thrower-v0": (2, thrower_world, "package", 300),
+}
+
+
+class BatchedEvoGymEnv:
+    """``n`` environments of one task, one robot body each, resident on one GPU.
+
+    ``mode='modular'`` (ModularEvoGym, ``evogym/envs/base.py:746-753``): observations are a dict ``modular`` (n, 9 * voxels),
+    ``other`` (n, 2 | 6), ``act_mask`` / ``obs_mask`` (n, voxels), ``stage`` (n, 1); actions are one value per voxel.
+    ``mode=None`` (EvoGym): the flat observation (n, width) and one action value per actuator.
+    ``worlds`` overrides the built-in terrain (a ``WorldSpec`` per environment that already contains the robot)."""
+
+    def __init__(self, env_id: str, bodies: Sequence[np.ndarray], connections: Optional[Sequence[Optional[np.ndarray]]] = None,
+                 device: int = 0, mode: Optional[str] = "modular", max_episode_steps: Optional[int] = None,
+                 worlds: Optional[Sequence[WorldSpec]] = None, out_dtype: str = "float32"):
+        import torch
+
+        if env_id not in TASKS:
+            raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
+        task, builder, package, limit = TASKS[env_id]
+        self.env_id, self.mode, self.device_index = env_id, mode, device
+        self.num_envs = len(bodies)
+        self.bodies = [np.asarray(b) for b in bodies]
+        self.torch = torch
+        self.device = torch.device("cuda", device)
+        self.dtype = {"float32": torch.float32, "float64": torch.float64}[out_dtype]
+        self.B = capi.Batch(device)
+        for i, body in enumerate(self.bodies):
+            if worlds is not None:
+                self.B.add_world(worlds[i])
+            else:
+                cn = connections[i] if connections is not None and connections[i] is not None else full_connectivity(body)
+                self.B.add_world(builder(body, cn))
+        self.B.finalize()
+        self.B.set_auto_reset(False)            # the task kernel resets (it needs the flag and the pre-step centres of mass)
+        self.B.task_configure(task, "robot", package, limit if max_episode_steps is None else max_episode_steps)
+        self.dims = self.B.task_dims()
+        n, d = self.num_envs, self.dims
+        dev, dt = self.device, self.dtype
+        self._flat = torch.zeros((n, d["flat"]), device=dev, dtype=dt)
+        self._modular = torch.zeros((n, d["modular"]), device=dev, dtype=dt)
+        self._other = torch.zeros((n, d["other"]), device=dev, dtype=dt)
+        self._reward = torch.zeros((n, 1), device=dev, dtype=dt)
+        self._done = torch.zeros((n,), device=dev, dtype=torch.uint8)
+        am = np.ones((n, d["max_voxels"]), dtype=np.int64)
+        om = np.ones((n, d["max_voxels"]), dtype=np.int64)
+        for i in range(n):
+            t = self.B.task_env_tables(i)
+            nv = self.bodies[i].size
+            am[i, :nv], om[i, :nv] = t["act_mask"][:nv], t["obs_mask"][:nv]
+        self.act_mask = torch.from_numpy(am).to(dev)
+        self.obs_mask = torch.from_numpy(om).to(dev)
+        self._stage = torch.ones((n, 1), device=dev, dtype=dt)
+        self._stream = torch.cuda.ExternalStream(self.B.cuda_stream, device=dev)
+        self.action_width = d["max_voxels"] if mode == "modular" else d["action_stride"]
+
+    # -- helpers
+    def _obs(self):
+        if self.mode == "modular":
+            return {"modular": self._modular, "other": self._other, "act_mask": self.act_mask, "obs_mask": self.obs_mask,
+                    "stage": self._stage}
+        return self._flat
+
+    def _ptrs(self) -> Tuple[int, int, int, int, int, int]:
+        if self.mode == "modular":
+            return 0, 0, self._modular.data_ptr(), self._modular.shape[1], self._other.data_ptr(), self._other.shape[1]
+        return self._flat.data_ptr(), self._flat.shape[1], 0, 0, 0, 0
+
+    # -- VecEnv surface
+    def reset(self):
+        """``venv.reset()``: every environment to snapshot 0; returns the observation (tensors owned by the env, overwritten
+        by the next ``step``)."""
+        f, fs, m, ms, o, os_ = self._ptrs()
+        self.B.task_reset_device(f, fs, m, ms, o, os_, self.dtype == self.torch.float32)
+        self._wait()
+        return self._obs()
+
+    def step(self, actions):
+        """``actions``: (n, voxels) in modular mode, (n, actuators) otherwise -- raw policy outputs (the environment adds 1 and
+        clips to [0.6, 1.6] like ``BenchmarkBase.step``); a CUDA tensor (float32 / float64) or anything ``torch.as_tensor`` takes.
+        Returns ``obs, reward (n, 1), done (n,) bool, infos`` with ``infos = {'truncated': ..., 'unstable': ...}`` tensors."""
+        torch = self.torch
+        a = torch.as_tensor(actions)
+        if a.dtype not in (torch.float32, torch.float64):
+            a = a.to(torch.float32)
+        a = a.to(self.device).contiguous()
+        if a.shape != (self.num_envs, self.action_width):
+            raise ValueError(f"actions must have shape {(self.num_envs, self.action_width)}, got {tuple(a.shape)}")
+        cur = torch.cuda.current_stream(self.device)
+        self._stream.wait_stream(cur)           # the engine's stream sees the policy's output
+        self.B.task_apply_policy_device(a.data_ptr(), a.shape[1], self.mode == "modular", a.dtype == torch.float32)
+        self.B.step_async(1, apply_actions=True)
+        f, fs, m, ms, o, os_ = self._ptrs()
+        self.B.task_outputs_device(self._reward.data_ptr(), self._done.data_ptr(), f, fs, m, ms, o, os_,
+                                   self.dtype == torch.float32, reset_done=True)
+        a.record_stream(self._stream)
+        self._wait()
+        done = (self._done & 1).bool()
+        infos = {"truncated": (self._done & 2).bool(), "unstable": (self._done & 4).bool()}
+        return self._obs(), self._reward, done, infos
+
+    def _wait(self):
+        self.torch.cuda.current_stream(self.device).wait_stream(self._stream)
+
+    def close(self):
+        self.B.close()
+
+
+def make_vec_envs(env_name: str, robot_structures: Sequence, device: int = 0, mode: Optional[str] = "modular",
+                  max_episode_steps: Optional[int] = None) -> BatchedEvoGymEnv:
+    """Signature after ``examples/transformer_ppo/envs.py:52-77``: ``robot_structures[i]`` is either ``(body, connections)`` or
+    an object with ``.body`` / ``.connections`` (the reference's ``Structure``)."""
+    bodies, conns = [], []
+    for s in robot_structures:
+        body, cn = (s.body, s.connections) if hasattr(s, "body") else s
+        bodies.append(np.asarray(body))
+        conns.append(None if cn is None else np.asarray(cn))
+    return BatchedEvoGymEnv(env_name, bodies, conns, device=device, mode=mode, max_episode_steps=max_episode_steps)

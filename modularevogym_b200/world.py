@@ -311,3 +311,34 @@ def walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None, wi
     w = flat_ground_world(width)
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
+
+
+def _package() -> np.ndarray:
+    """the 3 x 2 SOFT block named ``package`` of Pusher-v0 / Thrower-v0 (``evogym/envs/sim_files/Pusher-v0.json``)"""
+    return np.full((2, 3), VOXEL_TYPES["SOFT"], dtype=np.int64)
+
+
+def pusher_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Pusher-v0 (``evogym/envs/sim_files/Pusher-v0.json`` + ``evogym/envs/manipulate.py:323-324``): 100 x 1 fixed
+    ground, the package at voxel (8, 1), the robot at (1, 1)."""
+    w = flat_ground_world(100)
+    w.add_from_array("package", _package(), 8, 1)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
+THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
+
+
+def thrower_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Thrower-v0 (``evogym/envs/sim_files/Thrower-v0.json`` + ``evogym/envs/manipulate.py:524-525``): 70 x 10 fixed
+    terrain (ground row + posts of rising height), the package at voxel (3, 7), the robot at (1, 1)."""
+    w = WorldSpec(width=70, height=10)
+    grid = np.zeros((10, 70), dtype=np.int64)
+    grid[9, :] = VOXEL_TYPES["FIXED"]
+    for col, hgt in THROWER_POSTS.items():
+        grid[9 - hgt:9, col] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("package", _package(), 3, 7)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w

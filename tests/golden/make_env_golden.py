@@ -1,0 +1,218 @@
+"""Generates tests/golden/env_*.npz: rollouts of the reference's OWN gym environments (Python, unmodified,
+imported from /root/reference) over the reference's OWN engine (oracle/_ref, compiled from the unmodified C++
+sources), for the task layer either side of the hot path:
+
+    evogym/envs/walk.py:13-103        WalkingFlat      (Walker-v0)
+    evogym/envs/manipulate.py:318-417 PushSmallRect    (Pusher-v0)
+    evogym/envs/manipulate.py:519-628 ThrowSmallRect   (Thrower-v0)
+
+each in the reference's flat-observation mode and in ModularEvoGym's "modular" mode
+(evogym/envs/base.py:427-506,746-753).  Run HERE only (needs /root/reference); the fixtures travel.
+
+What is stubbed, and why it does not touch the numbers:
+  * `gym` is not installed: a 30-line stand-in provides Env / spaces.Box / spaces.Dict / register; the envs use
+    them for space declarations only.
+  * numpy 2.x has no `np.float`: aliased to `float` (it was an alias of `float`).
+  * `evogym.simulator_cpp` (the pybind11 module) is replaced by a class with the same methods that forwards every
+    call to the compiled reference `Sim` through oracle/ref.py -- the C++ that runs is the reference's.
+  * `Viewer` / `Camera` (OpenGL) are inert.
+"""
+from __future__ import annotations
+
+import json
+import os
+import random
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+sys.path.insert(0, ROOT)
+
+
+def install_stubs():
+    if not hasattr(np, "float"):
+        np.float = float          # noqa: NPY001  (the alias numpy removed)
+    from oracle.ref import RefSim
+
+    # ---- gym
+    gym = types.ModuleType("gym")
+
+    class Env:
+        pass
+
+    class Box:
+        def __init__(self, low, high, shape=None, dtype=np.float32):
+            self.low, self.high, self.dtype = low, high, dtype
+            self.shape = tuple(shape) if shape is not None else np.asarray(low).shape
+
+    class Dict_:
+        def __init__(self, spaces):
+            self.spaces = spaces
+
+        def __getitem__(self, k):
+            return self.spaces[k]
+
+    spaces = types.ModuleType("gym.spaces")
+    spaces.Box, spaces.Dict = Box, Dict_
+    gym.Env, gym.spaces = Env, spaces
+    gym.error = types.ModuleType("gym.error")
+    gym.utils = types.ModuleType("gym.utils")
+    gym.utils.seeding = types.ModuleType("gym.utils.seeding")
+    gym.envs = types.ModuleType("gym.envs")
+    gym.envs.registration = types.ModuleType("gym.envs.registration")
+    gym.envs.registration.register = lambda **kw: None
+    for name, mod in (("gym", gym), ("gym.spaces", spaces), ("gym.error", gym.error), ("gym.utils", gym.utils),
+                      ("gym.utils.seeding", gym.utils.seeding), ("gym.envs", gym.envs),
+                      ("gym.envs.registration", gym.envs.registration)):
+        sys.modules[name] = mod
+
+    # ---- evogym.simulator_cpp over the compiled reference
+    class Sim:
+        def __init__(self):
+            self._r = None
+
+        @staticmethod
+        def get_version():
+            pass
+
+        def init(self, w, h):
+            self._r = RefSim(world_w=int(w), world_h=int(h))
+            self._range = {}
+
+        def _add(self, grid, conn, name, x, y, robot):
+            ok = self._r.add_object(np.asarray(grid, dtype=np.float64), np.asarray(conn, dtype=np.float64), name, x, y, robot)
+            if ok:
+                info = self._r.object_info(self._r.num_objects - 1)
+                self._range[name] = (info["min_point"], info["max_point"])
+            return ok
+
+        def read_robot_from_array(self, grid, conn, name, x, y):
+            return self._add(grid, conn, name, x, y, True)
+
+        def read_object_from_array(self, grid, conn, name, x, y):
+            return self._add(grid, conn, name, x, y, False)
+
+        def step(self):
+            return self._r.step()
+
+        def set_action(self, name, action):
+            self._r.set_action(name, action)
+
+        def revert(self, t):
+            self._r.revert(t)
+
+        def get_time(self):
+            return self._r.get_time()
+
+        def pos_at_time(self, t):
+            return np.asfortranarray(self._r.pos_at_time(t).T)
+
+        def vel_at_time(self, t):
+            return np.asfortranarray(self._r.pos_at_time(t, vel=True).T)
+
+        def object_pos_at_time(self, t, name):
+            a, b = self._range[name]
+            return self.pos_at_time(t)[:, a:b + 1]
+
+        def object_vel_at_time(self, t, name):
+            a, b = self._range[name]
+            return self.vel_at_time(t)[:, a:b + 1]
+
+        def object_orientation_at_time(self, t, name):
+            return self._r.object_orientation_at_time(t, name)
+
+        def translate_object(self, x, y, name):
+            self._r.translate_object(x, y, name)
+
+        def get_indices_of_actuators(self, name):
+            return self._r.actuator_indices(name).reshape(1, -1)
+
+    class Viewer:
+        def __init__(self, sim): pass
+        def init(self): pass
+        def render(self, *a, **k): pass
+        def show_debug_window(self): pass
+        def hide_debug_window(self): pass
+        def get_debug_window_pos(self): return (0, 0)
+
+    class Camera:
+        def __init__(self, b): pass
+        def set_pos(self, x, y): pass
+        def set_size(self, x, y): pass
+        def set_resolution(self, x, y): pass
+        def get_resolution_width(self): return 0
+        def get_resolution_height(self): return 0
+        def get_image(self): return None
+
+    mod = types.ModuleType("evogym.simulator_cpp")
+    mod.Sim, mod.Viewer, mod.Camera = Sim, Viewer, Camera
+    sys.modules["evogym.simulator_cpp"] = mod      # before `import evogym`: evogym/sim.py:14 imports it
+    sys.path.insert(0, REF)
+
+
+def main():
+    import warnings
+    warnings.filterwarnings("ignore")
+    install_stubs()
+
+    from evogym.envs.walk import WalkingFlat
+    from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
+    from evogym import sample_robot
+
+    tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0")}
+    n_steps = 12
+    for task, (cls, env_id) in tasks.items():
+        for seed in (0, 1, 2):
+            random.seed(100 + seed)
+            np.random.seed(100 + seed)
+            body, conn = sample_robot((5, 5))
+            rng = np.random.default_rng(500 + seed)
+            out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": env_id}
+            # ---- flat mode
+            env = cls(body, conn, mode=None, env_id=env_id)
+            n_act = env.get_actuator_indices("robot").size
+            acts = rng.uniform(-1.0, 1.0, size=(n_steps, n_act))       # policy outputs; BenchmarkBase.step adds 1, base clips
+            obs0 = env.reset()
+            flat_obs, rew, done = [np.asarray(obs0, dtype=np.float64)], [], []
+            pre = {k: [] for k in ("pos", "vel", "pos_last", "vel_true", "goal")}
+            for t in range(n_steps):
+                # engine state the step starts from (teacher forcing in the GPU test)
+                st = env._sim._r.get_state()
+                for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
+                    pre[k].append(v.copy())
+                pre["goal"].append(env._sim._r.edges()["goal"].copy())
+                o, r, d, _ = env.step(acts[t].copy())
+                flat_obs.append(np.asarray(o, dtype=np.float64)); rew.append(float(r)); done.append(bool(d))
+            from modularevogym_b200.world import WorldSpec
+            out["world_json"] = json.dumps(WorldSpec.from_evoworld(env.world).to_dict())
+            out.update({"pre_" + k: np.stack(v) for k, v in pre.items()})
+            out.update(actions=acts, flat_obs=np.stack(flat_obs), reward=np.asarray(rew), done=np.asarray(done),
+                       actuator_indices=env.get_actuator_indices("robot").astype(np.int32))
+            # ---- modular mode, same policy outputs scattered over the voxel grid
+            envm = cls(body, conn, mode="modular", env_id=env_id)
+            act_mask = envm.act_mask.astype(bool)
+            m0 = envm.reset()
+            mod_obs, other_obs, mrew, mdone = [np.asarray(m0["modular"], dtype=np.float64)], [np.asarray(m0["other"], dtype=np.float64)], [], []
+            vox_acts = np.zeros((n_steps, body.size))
+            for t in range(n_steps):
+                vox_acts[t, ~act_mask] = acts[t]
+                o, r, d, _ = envm.step(vox_acts[t].copy())
+                mod_obs.append(np.asarray(o["modular"], dtype=np.float64)); other_obs.append(np.asarray(o["other"], dtype=np.float64))
+                mrew.append(float(r)); mdone.append(bool(d))
+            out.update(voxel_actions=vox_acts, modular_obs=np.stack(mod_obs), other_obs=np.stack(other_obs),
+                       modular_reward=np.asarray(mrew), modular_done=np.asarray(mdone),
+                       act_mask=envm.act_mask.astype(np.int32), obs_mask=np.asarray(envm.obs_mask).astype(np.int32),
+                       obs_index_array=np.asarray(envm.obs_index_array, dtype=np.int32),
+                       voxel_corner_size=np.int32(envm.voxel_corner_size))
+            path = os.path.join(HERE, f"env_{task}_s{seed}.npz")
+            np.savez_compressed(path, **out)
+            print(path, "reward sum", float(np.sum(rew)), "modular width", out["modular_obs"].shape[1],
+                  "flat == modular rewards:", np.array_equal(out["reward"], out["modular_reward"]))
+
+
+if __name__ == "__main__":
+    main()

@@ -14,7 +14,30 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def golden_names() -> List[str]:
-    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+    """engine fixtures (make_golden.py); the env_* files are the task-layer fixtures (make_env_golden.py)"""
+    names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+    return [n for n in names if not n.startswith("env_")]
+
+
+def env_golden_names() -> List[str]:
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "env_*.npz")))
+
+
+class EnvGolden:
+    """One rollout of a reference gym environment (layout: tests/golden/make_env_golden.py)."""
+
+    def __init__(self, name: str):
+        self.name = name
+        with np.load(os.path.join(GOLDEN_DIR, name + ".npz")) as z:
+            self.z = {k: z[k] for k in z.files}
+        self.world = WorldSpec.from_dict(json.loads(str(self.z["world_json"])))
+        self.env_id = str(self.z["env_id"])
+        self.task = {"Walker-v0": 0, "Pusher-v0": 1, "Thrower-v0": 2}[self.env_id]
+        self.package = None if self.task == 0 else "package"
+        self.n_steps = int(self.z["reward"].shape[0])
+
+    def __getitem__(self, k):
+        return self.z[k]
 
 
 class Golden:

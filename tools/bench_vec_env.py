@@ -1,0 +1,54 @@
+#!/usr/bin/env python
+"""Throughput of the batched vec-env front (modularevogym_b200/vec_env.py): policy output (float32, on the device) ->
+actuator targets -> 30 substeps -> reward / done / modular observation (float32) + reset of finished environments, three
+launches per env-step on one stream, no host round trip.  CUDA events on the engine's stream.
+
+    python tools/bench_vec_env.py [env_id:n_envs ...]
+"""
+import json
+import os
+import random
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    from modularevogym_b200.vec_env import BatchedEvoGymEnv
+    from modularevogym_b200.world import sample_robot
+    specs = sys.argv[1:] or ["Walker-v0:4096", "Pusher-v0:4096", "Thrower-v0:4096"]
+    for spec in specs:
+        env_id, n = spec.split(":")
+        n = int(n)
+        bodies, conns = [], []
+        for i in range(n):
+            random.seed(i)
+            b, c = sample_robot((5, 5))
+            bodies.append(b); conns.append(c)
+        env = BatchedEvoGymEnv(env_id, bodies, conns, device=0, mode="modular")
+        env.reset()
+        K, W = 100, 5
+        g = torch.Generator(device="cuda").manual_seed(0)
+        acts = torch.rand((K + W, n, env.action_width), device="cuda", generator=g) * 2 - 1
+        stream = env._stream
+        n_done = 0
+        for s in range(W):
+            env.step(acts[s])
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for s in range(K):
+            _, _, done, _ = env.step(acts[W + s])
+            n_done = n_done + done.sum()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        print(json.dumps({"front": "BatchedEvoGymEnv modular f32", "env_id": env_id, "envs": n, "ms_per_step": ms,
+                          "env_steps_per_s": n / (ms * 1e-3), "launches_per_step": 3, "episodes_finished": int(n_done)}), flush=True)
+        env.close()
+
+
+if __name__ == "__main__":
+    main()
