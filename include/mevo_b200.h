@@ -149,6 +149,11 @@ int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n);    /* env_ids NU
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out);
 /* same, into a caller-owned DEVICE buffer (n_envs x 2 doubles), enqueued on the batch's stream, no sync */
 int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out);
+/* Sim::object_orientation_at_time (Environment.cpp:317-380) of object `obj` in every env, current state against
+ * snapshot 0 (what get_ort_obs feeds the BridgeWalker / ObstacleTraverser / Climber-v2 observations, evogym/envs/base.py:
+ * 258-267): out = n_envs doubles, radians in [0, 2 pi) */
+int mevo_batch_object_orientation(mevo_batch* b, int obj, double* out);
+int mevo_batch_object_orientation_device(mevo_batch* b, int obj, double* device_out);     /* device, on the stream, no sync */
 /* Walker-v0 observation of object `obj` in every env (evogym/envs/walk.py:58-61 = get_vel_com_obs + get_relative_pos_obs,
  * evogym/envs/base.py:214-240), simulator units: row = [mean vel x, mean vel y, x_i - com_x (i < n), y_i - com_y
  * (i < n), zeros up to `stride`].  width = 2 + 2 * (largest point count of `obj` over the envs). */

@@ -72,6 +72,8 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_save_reset_state": (_i, [_vp]),
     "mevo_batch_reset": (_i, [_vp, _ip, _i]),
     "mevo_batch_object_com": (_i, [_vp, _i, _dp]),
+    "mevo_batch_object_orientation": (_i, [_vp, _i, _dp]),
+    "mevo_batch_object_orientation_device": (_i, [_vp, _i, _vp]),
     "mevo_batch_object_obs_width": (_i, [_vp, _i]),
     "mevo_batch_object_obs": (_i, [_vp, _i, _dp, _i]),
     "mevo_batch_object_obs_device": (_i, [_vp, _i, _vp, _i]),
@@ -398,6 +400,11 @@ class Batch:
         if out is None:
             out = np.zeros((self.num_envs, 2))
         _check(self.L.mevo_batch_object_com(self.h, int(obj), _dptr(out)))
+        return out
+
+    def object_orientation(self, obj: int) -> np.ndarray:
+        out = np.zeros(self.num_envs)
+        _check(self.L.mevo_batch_object_orientation(self.h, int(obj), _dptr(out)))
         return out
 
     def object_obs(self, obj: int, stride: int = 0) -> np.ndarray:

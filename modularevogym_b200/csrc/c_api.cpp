@@ -351,6 +351,22 @@ int mevo_batch_object_obs(mevo_batch* b, int obj, double* out, int stride) {
     });
 }
 
+int mevo_batch_object_orientation(mevo_batch* b, int obj, double* out) {
+    return guard([&] {
+        if (!out) throw std::invalid_argument("object_orientation: null output");
+        b->impl.object_orientation(obj, out);
+        return 0;
+    });
+}
+
+int mevo_batch_object_orientation_device(mevo_batch* b, int obj, double* device_out) {
+    return guard([&] {
+        if (!device_out) throw std::invalid_argument("object_orientation_device: null output");
+        b->impl.object_orientation_device(obj, device_out);
+        return 0;
+    });
+}
+
 int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int stride) {
     return guard([&] {
         if (!device_out || stride < 2) throw std::invalid_argument("object_obs_device: null output or stride < 2");

@@ -1057,6 +1057,22 @@ void Batch::object_com_device(int obj_index, double* out_device_2n) {
     CUDA_CHECK(cudaGetLastError());
 }
 
+void Batch::object_orientation_device(int obj_index, double* out_device_n) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    const int n = num_envs();
+    bind_object_ranges(obj_index);
+    orientation_kernel<<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, reinterpret_cast<const EnvDesc*>(d_envdesc_),
+                                                                      impl_->d_com_ranges, n, out_device_n ? out_device_n : impl_->d_com_out);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void Batch::object_orientation(int obj_index, double* out_host_n) {
+    object_orientation_device(obj_index, nullptr);
+    CUDA_CHECK(cudaMemcpyAsync(out_host_n, impl_->d_com_out, sizeof(double) * num_envs(), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
 int Batch::object_obs_width(int obj_index) const {
     int w = 2;
     for (const EnvHost& e : envs_) {

@@ -99,6 +99,9 @@ public:
     // packed robot positions for the learner side: COM (x, y) of object `obj_index` per env
     void object_com(int obj_index, double* out_host_2n);
     void object_com_device(int obj_index, double* out_device_2n);   // async on stream()
+    // Environment::object_orientation_at_time of object `obj_index` per env: current state against snapshot 0
+    void object_orientation(int obj_index, double* out_host_n);
+    void object_orientation_device(int obj_index, double* out_device_n);   // async on stream()
     // Walker-style observation rows [vel com (2), relative x (n), relative y (n), zero padding] (evogym/envs/walk.py:58-61)
     int object_obs_width(int obj_index) const;                       // 2 + 2 * (largest point count of the object)
     void object_obs_device(int obj_index, double* out_device, int stride);   // async on stream()

@@ -902,4 +902,48 @@ __global__ void obs_kernel(const double* state, const EnvDesc* envs, const int* 
     for (int i = 2 + 2 * count + lane; i < stride; i += 32) row[i] = 0.0;
 }
 
+// Environment::object_orientation_at_time (Environment.cpp:317-380) of one object per env, current state against
+// snapshot 0: magnitude-weighted mean angle between the centred point vectors, reflected to [0, 2 pi) by the sign of the
+// summed cross product (the reference's pi is the literal 3.1415926).  One warp per environment.
+__global__ void orientation_kernel(const double* state, const double* state0, const EnvDesc* envs,
+                                   const int* ranges /* n_envs x 3: start, count, Pd */, int n_envs, double* out) {
+    const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= n_envs) return;
+    const int start = ranges[3 * env], count = ranges[3 * env + 1];
+    const double2* pn = reinterpret_cast<const double2*>(state + envs[env].state_off) + start;
+    const double2* po = reinterpret_cast<const double2*>(state0 + envs[env].state_off) + start;
+    double cnx = 0.0, cny = 0.0, cox = 0.0, coy = 0.0;
+    for (int i = lane; i < count; i += 32) { const double2 a = pn[i], b = po[i]; cnx += a.x; cny += a.y; cox += b.x; coy += b.y; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cnx += __shfl_xor_sync(0xffffffffu, cnx, o); cny += __shfl_xor_sync(0xffffffffu, cny, o);
+        cox += __shfl_xor_sync(0xffffffffu, cox, o); coy += __shfl_xor_sync(0xffffffffu, coy, o);
+    }
+    if (count == 0) { if (lane == 0) out[env] = 0.0; return; }
+    cnx /= count; cny /= count; cox /= count; coy /= count;
+    double weighted = 0.0, weights = 0.0, cross = 0.0;
+    for (int i = lane; i < count; i += 32) {
+        double ax = pn[i].x - cnx, ay = pn[i].y - cny, bx = po[i].x - cox, by = po[i].y - coy;
+        const double ma = sqrt(ax * ax + ay * ay), mb = sqrt(bx * bx + by * by);
+        if (ma > 0.0) { ax /= ma; ay /= ma; }           // Eigen normalized(): left as is when the norm is 0
+        if (mb > 0.0) { bx /= mb; by /= mb; }
+        double c = ax * bx + ay * by;
+        if (ma * mb < 0.0000001) c = 0.99999;
+        if (c > 1.0) c = 0.99999;
+        if (c < -1.0) c = -0.99999;
+        weighted += acos(c) * mb;
+        weights += mb;
+        cross += ax * by - ay * bx;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        weighted += __shfl_xor_sync(0xffffffffu, weighted, o); weights += __shfl_xor_sync(0xffffffffu, weights, o);
+        cross += __shfl_xor_sync(0xffffffffu, cross, o);
+    }
+    double angle = weighted / weights;
+    if (cross > 0.0) angle = 2 * 3.1415926 - angle;
+    if (lane == 0) out[env] = angle;
+}
+
 }  // namespace mevo

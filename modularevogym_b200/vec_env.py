@@ -120,7 +120,6 @@ class BatchedEvoGymEnv:
         f, fs, m, ms, o, os_ = self._ptrs()
         self.B.task_outputs_device(self._reward.data_ptr(), self._done.data_ptr(), f, fs, m, ms, o, os_,
                                    self.dtype == torch.float32, reset_done=True)
-        a.record_stream(self._stream)
         self._wait()
         done = (self._done & 1).bool()
         infos = {"truncated": (self._done & 2).bool(), "unstable": (self._done & 4).bool()}
@@ -130,6 +129,7 @@ class BatchedEvoGymEnv:
         self.torch.cuda.current_stream(self.device).wait_stream(self._stream)
 
     def close(self):
+        self.torch.cuda.synchronize(self.device)
         self.B.close()
 
 

@@ -114,13 +114,15 @@ def install_stubs():
         def vel_at_time(self, t):
             return np.asfortranarray(self._r.pos_at_time(t, vel=True).T)
 
+        # NB: explicit Sim.* calls -- EvoSim overrides pos_at_time (divides by VOXEL_SIZE) and a C++ member of the real
+        # pybind11 class never dispatches to a Python override
         def object_pos_at_time(self, t, name):
             a, b = self._range[name]
-            return self.pos_at_time(t)[:, a:b + 1]
+            return Sim.pos_at_time(self, t)[:, a:b + 1]
 
         def object_vel_at_time(self, t, name):
             a, b = self._range[name]
-            return self.vel_at_time(t)[:, a:b + 1]
+            return Sim.vel_at_time(self, t)[:, a:b + 1]
 
         def object_orientation_at_time(self, t, name):
             return self._r.object_orientation_at_time(t, name)

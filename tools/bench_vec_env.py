@@ -34,6 +34,7 @@ def main():
         acts = torch.rand((K + W, n, env.action_width), device="cuda", generator=g) * 2 - 1
         stream = env._stream
         n_done = 0
+        print("built", env_id, n, file=sys.stderr, flush=True)
         for s in range(W):
             env.step(acts[s])
         torch.cuda.synchronize()
@@ -48,6 +49,7 @@ def main():
         print(json.dumps({"front": "BatchedEvoGymEnv modular f32", "env_id": env_id, "envs": n, "ms_per_step": ms,
                           "env_steps_per_s": n / (ms * 1e-3), "launches_per_step": 3, "episodes_finished": int(n_done)}), flush=True)
         env.close()
+        print("closed", env_id, file=sys.stderr, flush=True)
 
 
 if __name__ == "__main__":
