@@ -352,11 +352,80 @@ public:
     void object_obs_device(int obj, std::uintptr_t ptr, int stride) {
         chk(mevo_batch_object_obs_device(b_, obj, reinterpret_cast<double*>(ptr), stride));
     }
+    py::array_t<double> object_orientation(int obj) {           // (n_envs,) Sim::object_orientation_at_time, now vs snapshot 0
+        py::array_t<double> a(num_envs());
+        chk(mevo_batch_object_orientation(b_, obj, a.mutable_data()));
+        return a;
+    }
+    void object_orientation_device(int obj, std::uintptr_t ptr) { chk(mevo_batch_object_orientation_device(b_, obj, reinterpret_cast<double*>(ptr))); }
+
+    // ---- task layer (include/mevo_b200.h "task layer"): the gym environments either side of Sim::step
+    void task_configure(int task, const std::string& robot, py::object package, int max_episode_steps) {
+        const std::string pk = package.is_none() ? std::string() : py::cast<std::string>(package);
+        chk(mevo_batch_task_configure(b_, task, robot.c_str(), pk.empty() ? nullptr : pk.c_str(), max_episode_steps));
+    }
+    py::dict task_dims() {
+        int d[5];
+        chk(mevo_batch_task_dims(b_, d));
+        py::dict out;
+        out["flat"] = d[0]; out["modular"] = d[1]; out["other"] = d[2]; out["max_voxels"] = d[3]; out["action_stride"] = d[4];
+        return out;
+    }
+    py::dict task_env_tables(int env) {
+        int d[5];
+        chk(mevo_batch_task_dims(b_, d));
+        py::array_t<int> idx({d[3], 4}), am(d[3]), om(d[3]);
+        std::fill(idx.mutable_data(), idx.mutable_data() + idx.size(), -1);
+        std::fill(am.mutable_data(), am.mutable_data() + am.size(), 1);
+        std::fill(om.mutable_data(), om.mutable_data() + om.size(), 1);
+        const int corners = chk(mevo_batch_task_env_tables(b_, env, idx.mutable_data(), am.mutable_data(), om.mutable_data(), d[3]));
+        py::dict out;
+        out["obs_index_array"] = idx; out["act_mask"] = am; out["obs_mask"] = om; out["voxel_corner_size"] = corners;
+        return out;
+    }
+    void task_apply_policy(darray actions, bool per_voxel) {
+        if (actions.ndim() != 2 || actions.shape(0) != num_envs()) throw std::invalid_argument("actions must be (n_envs, width)");
+        chk(mevo_batch_task_apply_policy(b_, actions.data(), (int)actions.shape(1), per_voxel ? 1 : 0));
+    }
+    void task_apply_policy_device(std::uintptr_t ptr, int stride, bool per_voxel, bool is_f32) {
+        chk(mevo_batch_task_apply_policy_device(b_, reinterpret_cast<const void*>(ptr), stride, per_voxel ? 1 : 0, is_f32 ? 1 : 0));
+    }
+    py::dict task_outputs(bool reset_done) { return task_io(true, reset_done); }
+    py::dict task_reset() { return task_io(false, false); }
+    void task_outputs_device(std::uintptr_t reward, std::uintptr_t done, std::uintptr_t flat, int flat_stride, std::uintptr_t modular,
+                             int modular_stride, std::uintptr_t other, int other_stride, bool is_f32, bool reset_done) {
+        chk(mevo_batch_task_outputs_device(b_, reinterpret_cast<void*>(reward), reinterpret_cast<unsigned char*>(done),
+                                           reinterpret_cast<void*>(flat), flat_stride, reinterpret_cast<void*>(modular), modular_stride,
+                                           reinterpret_cast<void*>(other), other_stride, is_f32 ? 1 : 0, reset_done ? 1 : 0));
+    }
+    void task_reset_device(std::uintptr_t flat, int flat_stride, std::uintptr_t modular, int modular_stride, std::uintptr_t other,
+                           int other_stride, bool is_f32) {
+        chk(mevo_batch_task_reset_device(b_, reinterpret_cast<void*>(flat), flat_stride, reinterpret_cast<void*>(modular), modular_stride,
+                                         reinterpret_cast<void*>(other), other_stride, is_f32 ? 1 : 0));
+    }
     std::uintptr_t cuda_stream() { return reinterpret_cast<std::uintptr_t>(mevo_batch_cuda_stream(b_)); }
     long long unstable_events() { return mevo_batch_unstable_events(b_); }
 
 private:
     static int chk(int rc) { if (rc < 0) fail(); return rc; }
+    py::dict task_io(bool step_outputs, bool reset_done) {
+        int d[5];
+        chk(mevo_batch_task_dims(b_, d));
+        const py::ssize_t n = num_envs();
+        py::array_t<double> flat({n, (py::ssize_t)d[0]}), modular({n, (py::ssize_t)d[1]}), other({n, (py::ssize_t)d[2]});
+        py::dict out;
+        if (step_outputs) {
+            py::array_t<double> reward(n);
+            py::array_t<unsigned char> done(n);
+            chk(mevo_batch_task_outputs(b_, reward.mutable_data(), done.mutable_data(), flat.mutable_data(), d[0], modular.mutable_data(), d[1],
+                                        other.mutable_data(), d[2], reset_done ? 1 : 0));
+            out["reward"] = reward; out["done"] = done;
+        } else {
+            chk(mevo_batch_task_reset(b_, flat.mutable_data(), d[0], modular.mutable_data(), d[1], other.mutable_data(), d[2]));
+        }
+        out["flat"] = flat; out["modular"] = modular; out["other"] = other;
+        return out;
+    }
     py::array_t<double> state(int env, int which) {
         const int P = chk(mevo_env_num_points(b_, env));
         std::vector<double> buf(2 * (size_t)P);
@@ -433,6 +502,18 @@ PYBIND11_MODULE(simulator_cpp, m) {
         .def("object_com_device", &BatchSim::object_com_device)
         .def("object_obs", &BatchSim::object_obs)
         .def("object_obs_device", &BatchSim::object_obs_device)
+        .def("object_orientation", &BatchSim::object_orientation)
+        .def("object_orientation_device", &BatchSim::object_orientation_device)
+        .def("task_configure", &BatchSim::task_configure, py::arg("task"), py::arg("robot") = "robot", py::arg("package") = py::none(),
+             py::arg("max_episode_steps") = 0)
+        .def("task_dims", &BatchSim::task_dims)
+        .def("task_env_tables", &BatchSim::task_env_tables)
+        .def("task_apply_policy", &BatchSim::task_apply_policy, py::arg("actions"), py::arg("per_voxel") = false)
+        .def("task_apply_policy_device", &BatchSim::task_apply_policy_device)
+        .def("task_outputs", &BatchSim::task_outputs, py::arg("reset_done") = true)
+        .def("task_outputs_device", &BatchSim::task_outputs_device)
+        .def("task_reset", &BatchSim::task_reset)
+        .def("task_reset_device", &BatchSim::task_reset_device)
         .def_property_readonly("cuda_stream", &BatchSim::cuda_stream)
         .def_property_readonly("unstable_events", &BatchSim::unstable_events);
 }

@@ -10,8 +10,8 @@ each in the reference's flat-observation mode and in ModularEvoGym's "modular" m
 (evogym/envs/base.py:427-506,746-753).  Run HERE only (needs /root/reference); the fixtures travel.
 
 What is stubbed, and why it does not touch the numbers:
-  * `gym` is not installed: a 30-line stand-in provides Env / spaces.Box / spaces.Dict / register; the envs use
-    them for space declarations only.
+  * `gym` is not installed: modularevogym_b200/gym_shim.py provides Env / spaces.Box / spaces.Dict / register; the
+    envs use them for space declarations only.
   * numpy 2.x has no `np.float`: aliased to `float` (it was an alias of `float`).
   * `evogym.simulator_cpp` (the pybind11 module) is replaced by a class with the same methods that forwards every
     call to the compiled reference `Sim` through oracle/ref.py -- the C++ that runs is the reference's.
@@ -34,41 +34,7 @@ sys.path.insert(0, ROOT)
 
 
 def install_stubs():
-    if not hasattr(np, "float"):
-        np.float = float          # noqa: NPY001  (the alias numpy removed)
     from oracle.ref import RefSim
-
-    # ---- gym
-    gym = types.ModuleType("gym")
-
-    class Env:
-        pass
-
-    class Box:
-        def __init__(self, low, high, shape=None, dtype=np.float32):
-            self.low, self.high, self.dtype = low, high, dtype
-            self.shape = tuple(shape) if shape is not None else np.asarray(low).shape
-
-    class Dict_:
-        def __init__(self, spaces):
-            self.spaces = spaces
-
-        def __getitem__(self, k):
-            return self.spaces[k]
-
-    spaces = types.ModuleType("gym.spaces")
-    spaces.Box, spaces.Dict = Box, Dict_
-    gym.Env, gym.spaces = Env, spaces
-    gym.error = types.ModuleType("gym.error")
-    gym.utils = types.ModuleType("gym.utils")
-    gym.utils.seeding = types.ModuleType("gym.utils.seeding")
-    gym.envs = types.ModuleType("gym.envs")
-    gym.envs.registration = types.ModuleType("gym.envs.registration")
-    gym.envs.registration.register = lambda **kw: None
-    for name, mod in (("gym", gym), ("gym.spaces", spaces), ("gym.error", gym.error), ("gym.utils", gym.utils),
-                      ("gym.utils.seeding", gym.utils.seeding), ("gym.envs", gym.envs),
-                      ("gym.envs.registration", gym.envs.registration)):
-        sys.modules[name] = mod
 
     # ---- evogym.simulator_cpp over the compiled reference
     class Sim:
@@ -152,7 +118,10 @@ def install_stubs():
 
     mod = types.ModuleType("evogym.simulator_cpp")
     mod.Sim, mod.Viewer, mod.Camera = Sim, Viewer, Camera
-    sys.modules["evogym.simulator_cpp"] = mod      # before `import evogym`: evogym/sim.py:14 imports it
+    # np.float alias, minimal gym, and `evogym.simulator_cpp` = the compiled REFERENCE engine (not this repo's):
+    # registered before `import evogym` because evogym/sim.py:14 imports it
+    from modularevogym_b200 import gym_shim
+    gym_shim.install(simulator_module=mod)
     sys.path.insert(0, REF)
 
 

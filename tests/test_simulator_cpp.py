@@ -113,3 +113,29 @@ def test_batchsim():
     for i, g in enumerate(gs):
         a, b = int(g.obj_info[0, 1]), int(g.obj_info[0, 2])
         assert rel_err(com[i], B.pos(i)[:, a:b + 1].mean(axis=1)) <= 1e-12
+
+
+@pytest.mark.gpu
+def test_batchsim_task_layer():
+    """BatchSim exposes the task layer of the C ABI: one Thrower-v0 step against the reference environment's fixture"""
+    from helpers import EnvGolden
+    from modularevogym_b200 import simulator_cpp as m
+    g = EnvGolden("env_thrower_s0")
+    B = m.BatchSim(0)
+    e = B.begin_env(g.world.width, g.world.height)
+    for o in g.world.load_order():
+        assert B.add_object(e, o.grid.astype(np.float64), o.connections.astype(np.float64), o.name, o.x, o.y, o.is_robot)
+    B.finalize()
+    B.task_configure(2, "robot", "package", 300)
+    d = B.task_dims()
+    assert d["modular"] == 225 and d["other"] == 6 and d["flat"] == g["flat_obs"].shape[1]
+    t = B.task_env_tables(0)
+    assert np.array_equal(t["obs_index_array"], g["obs_index_array"]) and t["voxel_corner_size"] == int(g["voxel_corner_size"])
+    r = B.task_reset()
+    assert rel_err(r["modular"][0], g["modular_obs"][0]) <= 1e-12 and rel_err(r["flat"][0], g["flat_obs"][0]) <= 1e-12
+    B.task_apply_policy(g["voxel_actions"][0][None, :], True)
+    assert not B.step(1).any()
+    o = B.task_outputs(True)
+    assert abs(o["reward"][0] - g["reward"][0]) <= 1e-9 and o["done"][0] == 0
+    assert rel_err(o["modular"][0], g["modular_obs"][1]) <= 1e-9 and rel_err(o["other"][0], g["other_obs"][1]) <= 1e-9
+    assert B.object_orientation(0).shape == (1,)
