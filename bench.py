@@ -40,8 +40,18 @@ WORKLOAD = ("Walker-v0 (100x1 FIXED ground) + random 5x5 robot per env, robot i 
             "random.seed(i); actions U(-1,1)+1 clipped to [0.6,1.6] per actuator per step")
 
 
+HETERO_METRIC = "batched env-steps/sec (heterogeneous modular robots, sizes 5x5..20x20, Walker-v0 ground)"
+HETERO_WORKLOAD = ("BASELINE.json configs[4] per GPU: Walker-v0 ground + robot i of side s_i ~ U{5..20} (default_rng(i)), "
+                   "sample_robot((s,s)) for s <= 6 else sample_large_robot((s,s)) under random.seed(i); same action law")
+ACTIVE_WORKLOAD = "walker5x5"
+
+
 def workload_robot(i: int):
     random.seed(i)
+    if ACTIVE_WORKLOAD == "hetero":
+        from modularevogym_b200.world import sample_large_robot
+        s = int(np.random.default_rng(i).integers(5, 21))
+        return sample_robot((s, s)) if s <= 6 else sample_large_robot((s, s))
     return sample_robot((5, 5))
 
 
@@ -269,6 +279,7 @@ def main_ours(args) -> None:
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     n, K, W = args.envs, args.steps, args.warmup
+    hetero = args.workload == "hetero"
 
     # ---- build this rank's shard of the workload (host, untimed)
     t_build = time.perf_counter()
@@ -374,7 +385,7 @@ def main_ours(args) -> None:
         alg_bytes = algorithmic_bytes_per_step(P_sum, E_sum)              # per launch: this rank's n envs, one env-step
         achieved = alg_bytes / (dev_ms * 1e-3 / K) / 1e9
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and not hetero:          # the CPU arm times the headline workload only
             pool = CpuPool(1)
             pool.sample(5)
             spe = 40
@@ -384,10 +395,10 @@ def main_ours(args) -> None:
             cpu = {"value": 0.5 * (r1["value"] + r2["value"]), "unit": UNIT, "cores": pool.cores, "kind": pool.kind,
                    "sample": pool.describe(spe) + "; mean of 2 samples"}
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "metric": HETERO_METRIC if hetero else METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "envs_per_gpu": n, "substeps_per_step": SUBSTEPS,
+            "config": {"workload": HETERO_WORKLOAD if hetero else WORKLOAD, "envs_per_gpu": n, "substeps_per_step": SUBSTEPS,
                        "points_per_env": P_sum / n, "edges_per_env": E_sum / n, "parallelism": f"env-sharded x{world}, no collective on the step path",
                        "l2": "256 MB buffer written between timed iterations (outside the events)",
                        "timing": "CUDA events on the engine's stream around each step, summed; max over ranks",
@@ -396,7 +407,9 @@ def main_ours(args) -> None:
                     "ms_per_step": e2e_ms / K},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if n == 4096 else None, "kernel": "mevo::wstep_kernel<40,112,24,192,256,112,16,1>", "peak_source": peak_src,
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if n == 4096 and not hetero else None,
+                         "kernel": "mevo::step_kernel<G> per size class + mevo::wstep_kernel" if hetero else "mevo::wstep_kernel<40,112,24,192,256,112,16,1>",
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes},
             "cpu_baseline": cpu,
             "clocks": clock_info,
@@ -419,7 +432,11 @@ def main() -> None:
     ap.add_argument("--envs", type=int, default=4096, help="environments per GPU")
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", choices=("walker5x5", "hetero"), default="walker5x5",
+                    help="walker5x5 = the headline (BASELINE.json configs[1]); hetero = configs[4]'s robot mix (our arm only)")
     args = ap.parse_args()
+    global ACTIVE_WORKLOAD
+    ACTIVE_WORKLOAD = args.workload
     if args.impl == "reference":
         main_reference(args)
     else:

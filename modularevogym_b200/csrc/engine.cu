@@ -152,6 +152,12 @@ struct Batch::Impl {
     int cta_sync = 1;
     int balance = 1;                              // warp kernel: environments per CTA chosen for equally full waves
     int n_sm = 148;
+    // heterogeneous batches: the size classes of one step run concurrently, each on its own stream, forked from and joined
+    // to the batch's stream with events (largest environments first: they set the length of the step)
+    cudaStream_t class_stream[kNumClasses] = {};
+    cudaEvent_t class_done[kNumClasses] = {};
+    cudaEvent_t fork = nullptr;
+    int concurrent_classes = 1;
     int* d_com_ranges = nullptr;
     double* d_com_out = nullptr;
     int com_obj = -1;
@@ -173,6 +179,7 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     if (const char* e = std::getenv("MEVO_WEPC")) impl_->wepc = std::atoi(e);
     if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
     if (const char* e = std::getenv("MEVO_BALANCE")) impl_->balance = std::atoi(e);
+    if (const char* e = std::getenv("MEVO_CONCURRENT_CLASSES")) impl_->concurrent_classes = std::atoi(e);
     CUDA_CHECK(cudaDeviceGetAttribute(&impl_->n_sm, cudaDevAttrMultiProcessorCount, device_));
 }
 
@@ -201,7 +208,14 @@ Batch::~Batch() {
     cudaFree(d_design_); cudaFree(d_static_); cudaFree(d_state_); cudaFree(d_state0_); cudaFree(d_act_);
     cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
     cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);
-    if (impl_) { cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); }
+    if (impl_) {
+        cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out);
+        for (int c = 0; c < kNumClasses; c++) {
+            if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
+            if (impl_->class_done[c]) cudaEventDestroy(impl_->class_done[c]);
+        }
+        if (impl_->fork) cudaEventDestroy(impl_->fork);
+    }
     if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
     delete impl_;
 }
@@ -931,11 +945,27 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.dbg_cand = d_cand_;
     prm.dbg_cand_n = d_cand_n_;
     prm.dbg_cand_cap = cand_cap_;
-    cudaStream_t st = (cudaStream_t)stream_;
+    cudaStream_t main_st = (cudaStream_t)stream_;
     stats_.launches = 0;
-    for (int c = 0; c < kNumClasses; c++) {
+    int n_used = 0;
+    for (int c = 0; c < kNumClasses; c++) n_used += impl_->class_envs[c].empty() ? 0 : 1;
+    const bool fork = n_used > 1 && impl_->concurrent_classes != 0;
+    if (fork) {
+        if (!impl_->fork) CUDA_CHECK(cudaEventCreateWithFlags(&impl_->fork, cudaEventDisableTiming));
+        CUDA_CHECK(cudaEventRecord(impl_->fork, main_st));
+    }
+    for (int c = kNumClasses - 1; c >= 0; c--) {
         const int n = (int)impl_->class_envs[c].size();
         if (n == 0) continue;
+        cudaStream_t st = main_st;
+        if (fork) {
+            if (!impl_->class_stream[c]) {
+                CUDA_CHECK(cudaStreamCreateWithFlags(&impl_->class_stream[c], cudaStreamNonBlocking));
+                CUDA_CHECK(cudaEventCreateWithFlags(&impl_->class_done[c], cudaEventDisableTiming));
+            }
+            st = impl_->class_stream[c];
+            CUDA_CHECK(cudaStreamWaitEvent(st, impl_->fork, 0));
+        }
         prm.class_envs = d_class_envs_ + impl_->class_off[c];
         prm.n_class_envs = n;
         prm.smem_per_env = impl_->class_smem[c];
@@ -964,6 +994,10 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         }
         CUDA_CHECK(cudaGetLastError());
         stats_.launches++;
+        if (fork) {
+            CUDA_CHECK(cudaEventRecord(impl_->class_done[c], st));
+            CUDA_CHECK(cudaStreamWaitEvent(main_st, impl_->class_done[c], 0));
+        }
     }
     for (auto& e : envs_) e.host_fresh = false;
 }

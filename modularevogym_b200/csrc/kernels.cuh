@@ -788,29 +788,36 @@ __global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
             }
             group_sync<G, EPC>(grp);
             }   // Jacobi pass
-            // ordered rigid-cell pass, scheduled in point-disjoint levels (PhysicsEngine.cpp:675-710)
-            for (int lv = 0; lv < H.n_rlev; lv++) {
-                const int i1 = __ldg(rlev + lv + 1);
-                for (int i = __ldg(rlev + lv) + t; i < i1; i += G) {
-                    const int e = __ldg(rvis + i);
-                    const int a = ea[e], b = eb[e];
-                    double2 pa = pos[a], pb = pos[b];
-                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                    const double d2 = dx * dx + dy * dy;
-                    const double l0 = el0[e];
-                    const double l2 = l0 * l0;
-                    if (d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999) continue;     // inside the guarded band: a no-op
-                    const double dist = sqrt(d2);
-                    const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
-                    const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
-                    double ox = dx * over_mag, oy = dy * over_mag;
-                    double ux = dx * under_mag, uy = dy * under_mag;
-                    const double stress = dist / l0;
-                    if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
-                    if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
-                    const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
-                    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
-                    pos[a] = pa; pos[b] = pb;
+            // ordered rigid-cell pass (PhysicsEngine.cpp:675-710), scheduled in point-disjoint levels that keep the reference's
+            // order between visits sharing a point.  Levels are narrow (a dozen visits), so the group's first warp walks them
+            // alone with warp-level synchronisation; the other warps wait at one barrier instead of one per level.
+            if (viol & 2) {
+                if (warp == 0) {
+                    for (int lv = 0; lv < H.n_rlev; lv++) {
+                        const int i1 = __ldg(rlev + lv + 1);
+                        for (int i = __ldg(rlev + lv) + lane; i < i1; i += 32) {
+                            const int e = __ldg(rvis + i);
+                            const int a = ea[e], b = eb[e];
+                            double2 pa = pos[a], pb = pos[b];
+                            const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                            const double d2 = dx * dx + dy * dy;
+                            const double l0 = el0[e];
+                            const double l2 = l0 * l0;
+                            if (d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999) continue;     // inside the guarded band: a no-op
+                            const double dist = sqrt(d2);
+                            const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
+                            const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
+                            double ox = dx * over_mag, oy = dy * over_mag;
+                            double ux = dx * under_mag, uy = dy * under_mag;
+                            const double stress = dist / l0;
+                            if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
+                            if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
+                            const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
+                            pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
+                            pos[a] = pa; pos[b] = pb;
+                        }
+                        __syncwarp();
+                    }
                 }
                 group_sync<G, EPC>(grp);
             }

@@ -39,15 +39,36 @@ def main():
             env.step(acts[s])
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        import time
         e0.record(stream)
+        t_host = time.perf_counter()
         for s in range(K):
             _, _, done, _ = env.step(acts[W + s])
             n_done = n_done + done.sum()
+        t_host = (time.perf_counter() - t_host) / K * 1e3      # host time to enqueue one env-step (no sync inside)
         e1.record(stream)
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / K
+        # per-launch breakdown of one env-step (events between the three launches, on the engine's stream)
+        B, parts = env.B, [0.0, 0.0, 0.0]
+        f, fs, m, msd, o, os_ = env._ptrs()
+        for s in range(20):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            a = acts[W + s]
+            ev[0].record(stream)
+            B.task_apply_policy_device(a.data_ptr(), a.shape[1], True, True)
+            ev[1].record(stream)
+            B.step_async(1, apply_actions=True)
+            ev[2].record(stream)
+            B.task_outputs_device(env._reward.data_ptr(), env._done.data_ptr(), f, fs, m, msd, o, os_, True, reset_done=True)
+            ev[3].record(stream)
+            torch.cuda.synchronize()
+            for k in range(3):
+                parts[k] += ev[k].elapsed_time(ev[k + 1]) / 20
         print(json.dumps({"front": "BatchedEvoGymEnv modular f32", "env_id": env_id, "envs": n, "ms_per_step": ms,
-                          "env_steps_per_s": n / (ms * 1e-3), "launches_per_step": 3, "episodes_finished": int(n_done)}), flush=True)
+                          "env_steps_per_s": n / (ms * 1e-3), "launches_per_step": 3, "episodes_finished": int(n_done),
+                          "host_enqueue_ms_per_step": t_host,
+                          "ms_policy_actions_kernel": parts[0], "ms_step_kernel": parts[1], "ms_task_outputs_kernel": parts[2]}), flush=True)
         env.close()
         print("closed", env_id, file=sys.stderr, flush=True)
 
