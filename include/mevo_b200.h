@@ -154,6 +154,14 @@ int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out);
  * 258-267): out = n_envs doubles, radians in [0, 2 pi) */
 int mevo_batch_object_orientation(mevo_batch* b, int obj, double* out);
 int mevo_batch_object_orientation_device(mevo_batch* b, int obj, double* device_out);     /* device, on the stream, no sync */
+/* get_floor_obs (ceil = 0) / get_ceil_obs (ceil = 1) of object `obj` in every env (evogym/envs/base.py:269-372, times
+ * VOXEL_SIZE as BenchmarkBase returns them, base.py:411-415): 2 * sight_dist + 1 distances to the terrain below / above the
+ * object's centre of mass, clipped to [0, sight_range].  terrain_csv: comma-separated names of the terrain objects (static or
+ * simulated).  out = n_envs x stride, zero padded. */
+int mevo_batch_sight_obs(mevo_batch* b, int obj, const char* terrain_csv, int sight_dist, double sight_range, int ceil, double* out,
+                         int stride);
+int mevo_batch_sight_obs_device(mevo_batch* b, int obj, const char* terrain_csv, int sight_dist, double sight_range, int ceil,
+                                void* device_out, int stride, int is_f32);             /* device, on the stream, no sync */
 /* Walker-v0 observation of object `obj` in every env (evogym/envs/walk.py:58-61 = get_vel_com_obs + get_relative_pos_obs,
  * evogym/envs/base.py:214-240), simulator units: row = [mean vel x, mean vel y, x_i - com_x (i < n), y_i - com_y
  * (i < n), zeros up to `stride`].  width = 2 + 2 * (largest point count of `obj` over the envs). */

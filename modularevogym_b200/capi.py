@@ -74,6 +74,8 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_object_com": (_i, [_vp, _i, _dp]),
     "mevo_batch_object_orientation": (_i, [_vp, _i, _dp]),
     "mevo_batch_object_orientation_device": (_i, [_vp, _i, _vp]),
+    "mevo_batch_sight_obs": (_i, [_vp, _i, _cp, _i, _d, _i, _dp, _i]),
+    "mevo_batch_sight_obs_device": (_i, [_vp, _i, _cp, _i, _d, _i, _vp, _i, _i]),
     "mevo_batch_object_obs_width": (_i, [_vp, _i]),
     "mevo_batch_object_obs": (_i, [_vp, _i, _dp, _i]),
     "mevo_batch_object_obs_device": (_i, [_vp, _i, _vp, _i]),
@@ -405,6 +407,13 @@ class Batch:
     def object_orientation(self, obj: int) -> np.ndarray:
         out = np.zeros(self.num_envs)
         _check(self.L.mevo_batch_object_orientation(self.h, int(obj), _dptr(out)))
+        return out
+
+    def sight_obs(self, obj: int, terrain: Sequence[str], sight_dist: int, sight_range: float = 5.0, ceil: bool = False) -> np.ndarray:
+        """``get_floor_obs`` / ``get_ceil_obs`` (reference ``evogym/envs/base.py:269-372``) of object ``obj`` in every env"""
+        out = np.zeros((self.num_envs, 2 * sight_dist + 1))
+        _check(self.L.mevo_batch_sight_obs(self.h, int(obj), ",".join(terrain).encode(), int(sight_dist), float(sight_range), int(ceil),
+                                           _dptr(out), out.shape[1]))
         return out
 
     def object_obs(self, obj: int, stride: int = 0) -> np.ndarray:

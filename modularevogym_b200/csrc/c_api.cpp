@@ -367,6 +367,34 @@ int mevo_batch_object_orientation_device(mevo_batch* b, int obj, double* device_
     });
 }
 
+static std::vector<std::string> split_names(const char* csv) {
+    std::vector<std::string> out;
+    std::string cur;
+    for (const char* c = csv ? csv : ""; ; c++) {
+        if (*c == ',' || *c == 0) { if (!cur.empty()) out.push_back(cur); cur.clear(); if (*c == 0) break; }
+        else cur.push_back(*c);
+    }
+    return out;
+}
+
+int mevo_batch_sight_obs(mevo_batch* b, int obj, const char* terrain_csv, int sight_dist, double sight_range, int ceil, double* out,
+                         int stride) {
+    return guard([&] {
+        if (!out) throw std::invalid_argument("sight_obs: null output");
+        b->impl.sight_obs(obj, split_names(terrain_csv), sight_dist, sight_range, ceil != 0, out, stride);
+        return 0;
+    });
+}
+
+int mevo_batch_sight_obs_device(mevo_batch* b, int obj, const char* terrain_csv, int sight_dist, double sight_range, int ceil,
+                                void* device_out, int stride, int is_f32) {
+    return guard([&] {
+        if (!device_out) throw std::invalid_argument("sight_obs_device: null output");
+        b->impl.sight_obs_device(obj, split_names(terrain_csv), sight_dist, sight_range, ceil != 0, device_out, stride, is_f32 != 0);
+        return 0;
+    });
+}
+
 int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int stride) {
     return guard([&] {
         if (!device_out || stride < 2) throw std::invalid_argument("object_obs_device: null output or stride < 2");

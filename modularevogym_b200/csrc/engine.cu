@@ -186,6 +186,7 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
 Batch::~Batch() {
     cudaSetDevice(device_);
     task_free();
+    sight_free();
 #ifdef MEVO_PROF
     {
         unsigned long long h[16];
@@ -698,6 +699,7 @@ void Batch::finalize() {
     CUDA_CHECK(cudaMemcpy(d_state0_, host_state0.data(), sizeof(double) * (state_doubles + 2), cudaMemcpyHostToDevice));
     finalized_ = true;
     finalize_epoch_++;
+    impl_->com_obj = -1;              // per-object point ranges are rebuilt on the next use
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -125,6 +125,12 @@ public:
     void task_reset_device(void* flat, int flat_stride, void* modular, int modular_stride, void* other, int other_stride, bool is_f32);
     void task_reset(double* flat, int flat_stride, double* modular, int modular_stride, double* other, int other_stride);
 
+    // get_floor_obs / get_ceil_obs (evogym/envs/base.py:269-372) of object `obj_index` against the named terrain objects
+    void sight_obs_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
+                          void* out, int stride, bool is_f32);                       // async on stream()
+    void sight_obs(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
+                   double* out_host, int stride);
+
     // debug / test hooks: candidate pairs of the first substep of the next step() call
     void enable_candidate_dump(int cap_per_env);
     int read_candidates(int env, int* out_pairs /* cap x 4: kind_a, leaf_a, kind_b, leaf_b */, int cap);
@@ -138,8 +144,10 @@ public:
 private:
     struct Impl;
     struct Task;
+    struct Sight;
     void task_build();
     void task_free();
+    void sight_free();
     void upload_state(int env);
     void download_state(int env);
     void download_all();
@@ -175,6 +183,7 @@ private:
     void* stream_ = nullptr;
     Impl* impl_ = nullptr;
     Task* task_ = nullptr;
+    Sight* sight_ = nullptr;
     int finalize_epoch_ = 0;
 };
 

@@ -920,13 +920,23 @@ __global__ void orientation_kernel(const double* state, const double* state0, co
     const int start = ranges[3 * env], count = ranges[3 * env + 1];
     const double2* pn = reinterpret_cast<const double2*>(state + envs[env].state_off) + start;
     const double2* po = reinterpret_cast<const double2*>(state0 + envs[env].state_off) + start;
+    // The centroids are summed by one lane in the order of the reference's `rowwise().sum()` (Eigen 3.3.90 packetwise redux,
+    // Eigen/src/Core/PartialReduxEvaluator.h:107-129: column 0, then columns four at a time as (c1 + c2) + (c3 + c4), then
+    // the rest one by one): another order moves a centroid by an ulp, which can carry a normalised dot product across 1.0
+    // and with it flip the reference's clamp to 0.99999 -- a 1e-3 change of the angle near zero rotation.
     double cnx = 0.0, cny = 0.0, cox = 0.0, coy = 0.0;
-    for (int i = lane; i < count; i += 32) { const double2 a = pn[i], b = po[i]; cnx += a.x; cny += a.y; cox += b.x; coy += b.y; }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        cnx += __shfl_xor_sync(0xffffffffu, cnx, o); cny += __shfl_xor_sync(0xffffffffu, cny, o);
-        cox += __shfl_xor_sync(0xffffffffu, cox, o); coy += __shfl_xor_sync(0xffffffffu, coy, o);
+    if (lane == 0 && count > 0) {
+        cnx = pn[0].x; cny = pn[0].y; cox = po[0].x; coy = po[0].y;
+        int i = 1;
+        const int size4 = (count - 1) & ~3;
+        for (; i < size4; i += 4) {
+            cnx += (pn[i].x + pn[i + 1].x) + (pn[i + 2].x + pn[i + 3].x); cny += (pn[i].y + pn[i + 1].y) + (pn[i + 2].y + pn[i + 3].y);
+            cox += (po[i].x + po[i + 1].x) + (po[i + 2].x + po[i + 3].x); coy += (po[i].y + po[i + 1].y) + (po[i + 2].y + po[i + 3].y);
+        }
+        for (; i < count; i++) { cnx += pn[i].x; cny += pn[i].y; cox += po[i].x; coy += po[i].y; }
     }
+    cnx = __shfl_sync(0xffffffffu, cnx, 0); cny = __shfl_sync(0xffffffffu, cny, 0);
+    cox = __shfl_sync(0xffffffffu, cox, 0); coy = __shfl_sync(0xffffffffu, coy, 0);
     if (count == 0) { if (lane == 0) out[env] = 0.0; return; }
     cnx /= count; cny /= count; cox /= count; coy /= count;
     double weighted = 0.0, weights = 0.0, cross = 0.0;

@@ -134,9 +134,18 @@ public:
         if (now == history_.end() || then == history_.end() || !range(name, c0, c1)) return 0;
         const int n = c1 - c0 + 1;
         const std::vector<double>&pn = now->second.pos, &po = then->second.pos;
-        double cnx = 0, cny = 0, cox = 0, coy = 0;
-        for (int j = c0; j <= c1; j++) { cnx += pn[2 * j]; cny += pn[2 * j + 1]; cox += po[2 * j]; coy += po[2 * j + 1]; }
-        cnx /= n; cny /= n; cox /= n; coy /= n;
+        // centroid in the order of the reference's rowwise().sum() (Eigen packetwise redux: column 0, then four columns at a
+        // time as (c1 + c2) + (c3 + c4), then one by one) -- see orientation_kernel in kernels.cuh for why the order matters
+        auto rowsum = [&](const std::vector<double>& p, int comp) {
+            double acc = p[2 * c0 + comp];
+            int i = 1;
+            const int size4 = (n - 1) & ~3;
+            auto at = [&](int k) { return p[2 * (c0 + k) + comp]; };
+            for (; i < size4; i += 4) acc += (at(i) + at(i + 1)) + (at(i + 2) + at(i + 3));
+            for (; i < n; i++) acc += at(i);
+            return acc;
+        };
+        const double cnx = rowsum(pn, 0) / n, cny = rowsum(pn, 1) / n, cox = rowsum(po, 0) / n, coy = rowsum(po, 1) / n;
         double weighted = 0, weights = 0, cross = 0;
         for (int j = c0; j <= c1; j++) {
             double ax = pn[2 * j] - cnx, ay = pn[2 * j + 1] - cny, bx = po[2 * j] - cox, by = po[2 * j + 1] - coy;

@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -201,6 +202,64 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
             row[i] = (OutT)v;
         }
     }
+}
+
+struct SightEnvRec {                     // 48 bytes per environment
+    int o_start, o_count;                // observed object: dynamic-local point range
+    int Pd;
+    int st_off, st_count;                // static terrain points (double2 units into the shared table)
+    int n_dyn;
+    int dyn_start[3], dyn_count[3];      // terrain objects that are simulated (mixed / moved terrain): ranges in the state
+};
+
+// get_floor_obs / get_ceil_obs (evogym/envs/base.py:269-372, scaled by VOXEL_SIZE in BenchmarkBase, base.py:411-415): for
+// each of the 2 * sight_dist + 1 voxel columns around the object's centre of mass, the distance to the highest terrain
+// point below it (floor) or the lowest above it (ceil), clipped to [0, sight_range].  One warp per environment; the
+// comparisons are the reference's expressions in the reference's (voxel) units.
+template <typename OutT>
+__global__ void __launch_bounds__(128) sight_kernel(const double* state, const EnvDesc* envs, const SightEnvRec* rec, const double2* st_pts,
+                                                    int n_envs, int sight_dist, double sight_range, int ceil, OutT* out, int stride) {
+    const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= n_envs) return;
+    const SightEnvRec r = rec[env];
+    const double2* pos = reinterpret_cast<const double2*>(state + envs[env].state_off);
+    double cx = 0.0, cy = 0.0;
+    for (int i = lane; i < r.o_count; i += 32) { const double2 q = pos[r.o_start + i]; cx += q.x / kVoxel; cy += q.y / kVoxel; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { cx += __shfl_xor_sync(0xffffffffu, cx, o); cy += __shfl_xor_sync(0xffffffffu, cy, o); }
+    if (r.o_count > 0) { cx /= r.o_count; cy /= r.o_count; }
+    const double x_lo = cx - (sight_dist + 0.5), x_hi = cx + (sight_dist + 0.5);
+    const int n_cols = 2 * sight_dist + 1;
+    OutT* row = out + (size_t)env * stride;
+    for (int c = 0; c < n_cols && c < stride; c++) {
+        const int i = c - sight_dist;
+        const double c_lo = cx + (i - 0.5), c_hi = cx + (i + 0.5);
+        double best = 0.0;
+        bool any = false;
+        auto visit = [&](double2 q) {
+            const double x = q.x / kVoxel, y = q.y / kVoxel;
+            if (!(x > x_lo) || !(x < x_hi)) return;
+            if (ceil ? !(y > cy) : !(y < cy)) return;
+            if (!(x > c_lo) || !(x < c_hi)) return;
+            if (!any) { best = y; any = true; }
+            else best = ceil ? fmin(best, y) : fmax(best, y);
+        };
+        for (int k = lane; k < r.st_count; k += 32) visit(st_pts[r.st_off + k]);
+        for (int s = 0; s < r.n_dyn; s++)
+            for (int k = lane; k < r.dyn_count[s]; k += 32) visit(pos[r.dyn_start[s] + k]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const bool oa = __shfl_xor_sync(0xffffffffu, any ? 1 : 0, o) != 0;
+            if (oa) { best = any ? (ceil ? fmin(best, ob) : fmax(best, ob)) : ob; any = true; }
+        }
+        double elev = any ? best : (ceil ? (0.0 + sight_range) + cy : (0.0 - sight_range) + cy);
+        elev = ceil ? elev - cy : cy - elev;
+        elev = fmin(fmax(elev, 0.0), sight_range);
+        if (lane == 0) row[c] = (OutT)(elev * kVoxel);
+    }
+    for (int c = n_cols + lane; c < stride; c += 32) row[c] = (OutT)0;
 }
 
 template <typename InT>
@@ -492,6 +551,101 @@ void Batch::task_reset(double* flat, int flat_stride, double* modular, int modul
     Task& T = *task_;
     CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));
     task_outputs(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, false);
+}
+
+// ---- terrain sight observations -----------------------------------------------------------------
+
+struct Batch::Sight {
+    std::string key;                     // object index + terrain names the tables were built for
+    int epoch = -1;
+    SightEnvRec* d_rec = nullptr;
+    double2* d_pts = nullptr;
+    void free_device() { cudaFree(d_rec); cudaFree(d_pts); d_rec = nullptr; d_pts = nullptr; }
+};
+
+void Batch::sight_free() {
+    if (!sight_) return;
+    sight_->free_device();
+    delete sight_;
+    sight_ = nullptr;
+}
+
+void Batch::sight_obs_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
+                             void* out, int stride, bool is_f32) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (sight_dist < 0 || sight_dist > 1000) throw std::runtime_error("sight_obs: bad sight_dist");
+    if (stride < 2 * sight_dist + 1) throw std::runtime_error("sight_obs: stride smaller than 2 * sight_dist + 1");
+    std::string key = std::to_string(obj_index);
+    for (const std::string& t : terrain) key += "|" + t;
+    if (!sight_) sight_ = new Sight();
+    Sight& S = *sight_;
+    const int n = num_envs();
+    if (S.key != key || S.epoch != finalize_epoch_) {
+        S.free_device();
+        std::vector<SightEnvRec> rec(n);
+        std::vector<double2> pts;
+        std::vector<std::pair<std::vector<double>, int>> seen;      // static terrain point lists already stored -> offset
+        for (int e = 0; e < n; e++) {
+            const EnvHost& E = envs_[e];
+            SightEnvRec& r = rec[e];
+            std::memset(&r, 0, sizeof(r));
+            r.Pd = (int)E.dyn_points.size();
+            if (obj_index < 0 || obj_index >= (int)E.world.objects.size()) throw std::runtime_error("sight_obs: no such object");
+            const VoxelObject& ob = E.world.objects[obj_index];
+            r.o_start = E.point_local[ob.min_point];
+            r.o_count = ob.max_point - ob.min_point + 1;
+            if (r.o_start < 0) throw std::runtime_error("sight_obs: the observed object is static");
+            std::vector<double> stat;
+            for (const std::string& t : terrain) {
+                const int ti = E.world.find_object(t);
+                if (ti < 0) continue;                              // the reference would raise on an unknown name; envs never pass one
+                const VoxelObject& tb = E.world.objects[ti];
+                const int l0 = E.point_local[tb.min_point];
+                if (l0 >= 0) {
+                    if (r.n_dyn >= 3) throw std::runtime_error("sight_obs: more than 3 simulated terrain objects");
+                    r.dyn_start[r.n_dyn] = l0; r.dyn_count[r.n_dyn] = tb.max_point - tb.min_point + 1; r.n_dyn++;
+                } else {
+                    for (int p = tb.min_point; p <= tb.max_point; p++) { stat.push_back(E.pos[2 * p]); stat.push_back(E.pos[2 * p + 1]); }
+                }
+            }
+            int off = -1;
+            for (const auto& sv : seen) if (sv.first == stat) { off = sv.second; break; }
+            if (off < 0) {
+                off = (int)pts.size();
+                for (size_t k = 0; k + 1 < stat.size(); k += 2) pts.push_back(make_double2(stat[k], stat[k + 1]));
+                seen.emplace_back(stat, off);
+            }
+            r.st_off = off; r.st_count = (int)stat.size() / 2;
+        }
+        CUDA_CHECK(cudaMalloc(&S.d_rec, sizeof(SightEnvRec) * n));
+        CUDA_CHECK(cudaMemcpy(S.d_rec, rec.data(), sizeof(SightEnvRec) * n, cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMalloc(&S.d_pts, sizeof(double2) * std::max<size_t>(1, pts.size())));
+        if (!pts.empty()) CUDA_CHECK(cudaMemcpy(S.d_pts, pts.data(), sizeof(double2) * pts.size(), cudaMemcpyHostToDevice));
+        S.key = key; S.epoch = finalize_epoch_;
+    }
+    const int grid = (n + 3) / 4;
+    if (is_f32)
+        sight_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
+                                                                    sight_dist, sight_range, ceil ? 1 : 0, static_cast<float*>(out), stride);
+    else
+        sight_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
+                                                                     sight_dist, sight_range, ceil ? 1 : 0, static_cast<double*>(out), stride);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void Batch::sight_obs(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil, double* out_host,
+                      int stride) {
+    const size_t bytes = sizeof(double) * (size_t)stride * num_envs();
+    double* d = nullptr;
+    CUDA_CHECK(cudaSetDevice(device_));
+    CUDA_CHECK(cudaMalloc(&d, bytes));
+    try {
+        sight_obs_device(obj_index, terrain, sight_dist, sight_range, ceil, d, stride, false);
+        CUDA_CHECK(cudaMemcpyAsync(out_host, d, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    } catch (...) { cudaFree(d); throw; }
+    cudaFree(d);
 }
 
 }  // namespace mevo

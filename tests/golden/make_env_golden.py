@@ -184,6 +184,43 @@ def main():
             print(path, "reward sum", float(np.sum(rew)), "modular width", out["modular_obs"].shape[1],
                   "flat == modular rewards:", np.array_equal(out["reward"], out["modular_reward"]))
 
+    # ---- terrain sight + orientation observations (base.py:258-372): ObstacleTraverser-v1 (floor, "ground"), CaveCrawler-v0
+    # (floor + ceil, "terrain"), Climber-v2 (ceil, "pipe"); flat mode, the envs' own sight_dist
+    from evogym.envs.traverse import WalkingBumpy2
+    from evogym.envs.walk import Duck
+    from evogym.envs.climb import Climb2
+    from modularevogym_b200.world import WorldSpec
+    for tag, cls, env_id, terrain in (("obstacle", WalkingBumpy2, "ObstacleTraverser-v1", "ground"), ("cave", Duck, "CaveCrawler-v0", "terrain"),
+                                      ("climber2", Climb2, "Climber-v2", "pipe")):
+        random.seed(200)
+        np.random.seed(200)
+        body, conn = sample_robot((5, 5))
+        env = cls(body, conn, mode=None, env_id=env_id)
+        rng = np.random.default_rng(900)
+        n_act = env.get_actuator_indices("robot").size
+        acts = rng.uniform(-1.0, 1.0, size=(n_steps, n_act))
+        env.reset()
+        rec = {k: [] for k in ("pos", "vel", "pos_last", "vel_true", "floor", "ceil", "orient", "vel_com")}
+
+        def snap():
+            st = env._sim._r.get_state()
+            for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
+                rec[k].append(v.copy())
+            rec["floor"].append(np.asarray(env.get_floor_obs("robot", [terrain], env.sight_dist), dtype=np.float64))
+            rec["ceil"].append(np.asarray(env.get_ceil_obs("robot", [terrain], env.sight_dist), dtype=np.float64))
+            rec["orient"].append(float(env.object_orientation_at_time(env.get_time(), "robot")))
+            rec["vel_com"].append(np.asarray(env.get_vel_com_obs("robot"), dtype=np.float64))
+        snap()
+        for t in range(n_steps):
+            env.step(acts[t].copy())
+            snap()
+        out = {"world_json": json.dumps(WorldSpec.from_evoworld(env.world).to_dict()), "env_id": env_id, "terrain": terrain,
+               "sight_dist": np.int32(env.sight_dist), "body": body.astype(np.int32)}
+        out.update({k: np.stack(v) if k != "orient" else np.asarray(v) for k, v in rec.items()})
+        path = os.path.join(HERE, f"sight_{tag}.npz")
+        np.savez_compressed(path, **out)
+        print(path, "floor[0]", out["floor"][0], "ceil[0]", out["ceil"][0])
+
 
 if __name__ == "__main__":
     main()
