@@ -255,8 +255,8 @@ def main_reference(args) -> None:
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one step launch of 4096 envs, from the ncu --set full capture
-# summarised in profiles/r01f_wstep_kernel_raw.csv (25.21 MB read + 0.27 MB written): the state stays on chip
-NCU_DRAM_BYTES_PER_LAUNCH = 25_481_984
+# summarised in profiles/r01h_wstep_kernel_raw.csv (25.50 MB read + 0.39 MB written): the state stays on chip
+NCU_DRAM_BYTES_PER_LAUNCH = 25_889_792
 
 
 def algorithmic_bytes_per_step(P: int, E: int) -> int:
