@@ -209,6 +209,18 @@ int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* 
 int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
                                  int other_stride, int is_f32);
 
+/* ---- CUDA graphs --------------------------------------------------------------------------------------- */
+/* Everything the *_device / *_async entry points enqueue on the batch's stream between capture_begin and capture_end
+ * (policy actions, the step launches of all size classes, task outputs, observations) is recorded into one CUDA graph
+ * instead of being executed; mevo_batch_graph_launch replays it with a single driver call.  Device pointers passed to the
+ * captured calls are baked into the graph (use persistent buffers); every captured entry point must have been called once
+ * before the capture (first calls configure kernels and build tables); mevo_batch_finalize invalidates all graphs.
+ * capture_end returns the graph id. */
+int mevo_batch_capture_begin(mevo_batch* b);
+int mevo_batch_capture_end(mevo_batch* b);
+int mevo_batch_graph_launch(mevo_batch* b, int graph);
+int mevo_batch_graph_destroy(mevo_batch* b, int graph);
+
 /* device pointers for zero-copy consumers (valid until the next finalize) */
 double* mevo_batch_actions_device_ptr(mevo_batch* b);
 const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b);

@@ -89,6 +89,10 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_task_outputs_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i]),
     "mevo_batch_task_reset": (_i, [_vp, _dp, _i, _dp, _i, _dp, _i]),
     "mevo_batch_task_reset_device": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i]),
+    "mevo_batch_capture_begin": (_i, [_vp]),
+    "mevo_batch_capture_end": (_i, [_vp]),
+    "mevo_batch_graph_launch": (_i, [_vp, _i]),
+    "mevo_batch_graph_destroy": (_i, [_vp, _i]),
     "mevo_batch_actions_device_ptr": (_vp, [_vp]),
     "mevo_batch_unstable_device_ptr": (_vp, [_vp]),
     "mevo_batch_cuda_stream": (_vp, [_vp]),
@@ -479,6 +483,19 @@ class Batch:
         vp = lambda p: C.c_void_p(p) if p else None
         _check(self.L.mevo_batch_task_reset_device(self.h, vp(flat_ptr), int(flat_stride), vp(modular_ptr), int(modular_stride),
                                                    vp(other_ptr), int(other_stride), int(is_f32)))
+
+    # -- CUDA graphs (include/mevo_b200.h "CUDA graphs")
+    def capture_begin(self) -> None:
+        _check(self.L.mevo_batch_capture_begin(self.h))
+
+    def capture_end(self) -> int:
+        return _check(self.L.mevo_batch_capture_end(self.h))
+
+    def graph_launch(self, graph: int) -> None:
+        _check(self.L.mevo_batch_graph_launch(self.h, int(graph)))
+
+    def graph_destroy(self, graph: int) -> None:
+        _check(self.L.mevo_batch_graph_destroy(self.h, int(graph)))
 
     def object_com_ptr(self, obj: int, host_ptr: int) -> None:
         _check(self.L.mevo_batch_object_com(self.h, int(obj), C.cast(host_ptr, _dp)))

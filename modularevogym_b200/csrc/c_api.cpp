@@ -484,6 +484,11 @@ int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, voi
     });
 }
 
+int mevo_batch_capture_begin(mevo_batch* b) { return guard([&] { b->impl.capture_begin(); return 0; }); }
+int mevo_batch_capture_end(mevo_batch* b) { return guard([&] { return b->impl.capture_end(); }); }
+int mevo_batch_graph_launch(mevo_batch* b, int graph) { return guard([&] { b->impl.graph_launch(graph); return 0; }); }
+int mevo_batch_graph_destroy(mevo_batch* b, int graph) { return guard([&] { b->impl.graph_destroy(graph); return 0; }); }
+
 double* mevo_batch_actions_device_ptr(mevo_batch* b) { return b->impl.actions_device_ptr(); }
 const unsigned char* mevo_batch_unstable_device_ptr(mevo_batch* b) { return b->impl.unstable_device_ptr(); }
 void* mevo_batch_cuda_stream(mevo_batch* b) { return b->impl.stream(); }

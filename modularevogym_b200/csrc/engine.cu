@@ -3,6 +3,9 @@
 #include "engine.h"
 
 #include <algorithm>
+#include <atomic>
+#include <exception>
+#include <thread>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -187,6 +190,7 @@ Batch::~Batch() {
     cudaSetDevice(device_);
     task_free();
     sight_free();
+    for (void* g : graphs_) if (g) cudaGraphExecDestroy((cudaGraphExec_t)g);
 #ifdef MEVO_PROF
     {
         unsigned long long h[16];
@@ -569,6 +573,7 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
 
 void Batch::finalize() {
     CUDA_CHECK(cudaSetDevice(device_));
+    for (void*& g : graphs_) if (g) { cudaGraphExecDestroy((cudaGraphExec_t)g); g = nullptr; }   // captured pointers go stale
     if (finalized_) download_all();
     const int n = num_envs();
     if (n == 0) throw std::runtime_error("finalize: no environments");
@@ -593,11 +598,37 @@ void Batch::finalize() {
         return off;
     };
 
-    std::vector<uint8_t> design, statics;
+    // Packing one environment (pair tables, gather lists, static grid) touches only that environment: done on all host
+    // cores, a chunk at a time; interning, offsets and class lists follow sequentially in environment order.  This is the
+    // rebuild path of design loops (`env.update(body, connections)`, evogym/envs/walk.py:105-120), where thousands of robots
+    // change between episodes.
+    constexpr int kChunk = 2048;
+    const int n_threads = (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    std::vector<std::vector<uint8_t>> chunk_design(std::min(n, kChunk)), chunk_static(std::min(n, kChunk));
     for (int i = 0; i < n; i++) {
         EnvHost& e = envs_[i];
-        if (e.world.objects.empty()) throw std::runtime_error("finalize: environment " + std::to_string(i) + " has no objects");
-        pack_env(i, design, statics);
+        if (i % kChunk == 0) {
+            const int base = i, m = std::min(kChunk, n - base);
+            for (int k = 0; k < m; k++)
+                if (envs_[base + k].world.objects.empty())
+                    throw std::runtime_error("finalize: environment " + std::to_string(base + k) + " has no objects");
+            std::atomic<int> next(0);
+            std::vector<std::exception_ptr> errors(n_threads);
+            auto worker = [&](int tid) {
+                try {
+                    for (int k = next.fetch_add(1); k < m; k = next.fetch_add(1)) pack_env(base + k, chunk_design[k], chunk_static[k]);
+                } catch (...) { errors[tid] = std::current_exception(); }
+            };
+            if (n_threads == 1 || m < 8) worker(0);
+            else {
+                std::vector<std::thread> pool;
+                for (int t = 0; t < n_threads; t++) pool.emplace_back(worker, t);
+                for (auto& th : pool) th.join();
+            }
+            for (auto& ep : errors) if (ep) std::rethrow_exception(ep);
+        }
+        const std::vector<uint8_t>& design = chunk_design[i % kChunk];
+        const std::vector<uint8_t>& statics = chunk_static[i % kChunk];
         const DesignHeader* H = reinterpret_cast<const DesignHeader*>(design.data());
         EnvDesc& d = impl_->desc[i];
         d.design_off = intern(all_design, design_index, design);
@@ -1018,6 +1049,44 @@ int Batch::step(int n_steps, bool apply_actions, uint8_t* unstable_host, int n_s
     for (int i = 0; i < n; i++) count += impl_->unstable_host[i] ? 1 : 0;
     if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host.data(), n);
     return count;
+}
+
+// ------------------------------------------------------------------------------------------------
+// CUDA graphs
+
+void Batch::capture_begin() {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (capturing_) throw std::runtime_error("capture_begin: a capture is already open");
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamBeginCapture((cudaStream_t)stream_, cudaStreamCaptureModeThreadLocal));
+    capturing_ = true;
+}
+
+int Batch::capture_end() {
+    if (!capturing_) throw std::runtime_error("capture_end without capture_begin");
+    capturing_ = false;
+    cudaGraph_t graph = nullptr;
+    CUDA_CHECK(cudaStreamEndCapture((cudaStream_t)stream_, &graph));
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    CUDA_CHECK(e);
+    graphs_.push_back(exec);
+    return (int)graphs_.size() - 1;
+}
+
+void Batch::graph_launch(int id) {
+    if (id < 0 || id >= (int)graphs_.size() || !graphs_[id]) throw std::runtime_error("graph_launch: no such graph");
+    CUDA_CHECK(cudaGraphLaunch((cudaGraphExec_t)graphs_[id], (cudaStream_t)stream_));
+    for (auto& e : envs_) e.host_fresh = false;
+    impl_->time_dirty = true;
+}
+
+void Batch::graph_destroy(int id) {
+    if (id < 0 || id >= (int)graphs_.size() || !graphs_[id]) return;
+    cudaGraphExecDestroy((cudaGraphExec_t)graphs_[id]);
+    graphs_[id] = nullptr;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -131,6 +131,15 @@ public:
     void sight_obs(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
                    double* out_host, int stride);
 
+    // ---- CUDA graphs: everything enqueued on the batch's stream between capture_begin() and capture_end() (policy actions, the
+    // step launches of all size classes with their fork/join, task outputs, observations ...) becomes one graph; graph_launch
+    // replays it with one driver call.  The device pointers passed to the captured calls are baked in: use persistent buffers.
+    // Every captured entry point must have run once before (first calls configure kernels and allocate tables).
+    void capture_begin();
+    int capture_end();                 // returns a graph id
+    void graph_launch(int id);
+    void graph_destroy(int id);
+
     // debug / test hooks: candidate pairs of the first substep of the next step() call
     void enable_candidate_dump(int cap_per_env);
     int read_candidates(int env, int* out_pairs /* cap x 4: kind_a, leaf_a, kind_b, leaf_b */, int cap);
@@ -182,6 +191,8 @@ private:
     size_t state_doubles_ = 0;
     void* stream_ = nullptr;
     Impl* impl_ = nullptr;
+    std::vector<void*> graphs_;        // cudaGraphExec_t, index = graph id (nullptr after destroy)
+    bool capturing_ = false;
     Task* task_ = nullptr;
     Sight* sight_ = nullptr;
     int finalize_epoch_ = 0;

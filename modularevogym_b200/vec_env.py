@@ -39,7 +39,7 @@ class BatchedEvoGymEnv:
 
     def __init__(self, env_id: str, bodies: Sequence[np.ndarray], connections: Optional[Sequence[Optional[np.ndarray]]] = None,
                  device: int = 0, mode: Optional[str] = "modular", max_episode_steps: Optional[int] = None,
-                 worlds: Optional[Sequence[WorldSpec]] = None, out_dtype: str = "float32"):
+                 worlds: Optional[Sequence[WorldSpec]] = None, out_dtype: str = "float32", use_graph: bool = True):
         import torch
 
         if env_id not in TASKS:
@@ -80,6 +80,13 @@ class BatchedEvoGymEnv:
         self._stage = torch.ones((n, 1), device=dev, dtype=dt)
         self._stream = torch.cuda.ExternalStream(self.B.cuda_stream, device=dev)
         self.action_width = d["max_voxels"] if mode == "modular" else d["action_stride"]
+        # the three launches of one env-step (+ the fork/join of the size classes) as one CUDA graph: captured after the first
+        # eager step, replayed afterwards; the policy output is copied into a persistent buffer the graph reads
+        self.use_graph = use_graph
+        self._graph = None
+        self._graph_dtype = None
+        self._actions = None
+        self._eager_steps = 0
 
     # -- helpers
     def _obs(self):
@@ -114,16 +121,42 @@ class BatchedEvoGymEnv:
         if a.shape != (self.num_envs, self.action_width):
             raise ValueError(f"actions must have shape {(self.num_envs, self.action_width)}, got {tuple(a.shape)}")
         cur = torch.cuda.current_stream(self.device)
-        self._stream.wait_stream(cur)           # the engine's stream sees the policy's output
-        self.B.task_apply_policy_device(a.data_ptr(), a.shape[1], self.mode == "modular", a.dtype == torch.float32)
-        self.B.step_async(1, apply_actions=True)
-        f, fs, m, ms, o, os_ = self._ptrs()
-        self.B.task_outputs_device(self._reward.data_ptr(), self._done.data_ptr(), f, fs, m, ms, o, os_,
-                                   self.dtype == torch.float32, reset_done=True)
+        if self.use_graph and self._graph is not None and a.dtype == self._graph_dtype:
+            self._actions.copy_(a)
+            self._stream.wait_stream(cur)
+            self.B.graph_launch(self._graph)
+        else:
+            if self.use_graph and self._eager_steps >= 1 and self._graph is None:
+                self._capture(a)
+                self._actions.copy_(a)
+                self._stream.wait_stream(cur)
+                self.B.graph_launch(self._graph)
+            else:
+                self._stream.wait_stream(cur)       # the engine's stream sees the policy's output
+                self._enqueue_step(a.data_ptr(), a.shape[1], a.dtype == torch.float32)
+                self._eager_steps += 1
         self._wait()
         done = (self._done & 1).bool()
         infos = {"truncated": (self._done & 2).bool(), "unstable": (self._done & 4).bool()}
         return self._obs(), self._reward, done, infos
+
+    def _enqueue_step(self, act_ptr: int, act_stride: int, act_f32: bool) -> None:
+        self.B.task_apply_policy_device(act_ptr, act_stride, self.mode == "modular", act_f32)
+        self.B.step_async(1, apply_actions=True)
+        f, fs, m, ms, o, os_ = self._ptrs()
+        self.B.task_outputs_device(self._reward.data_ptr(), self._done.data_ptr(), f, fs, m, ms, o, os_,
+                                   self.dtype == self.torch.float32, reset_done=True)
+
+    def _capture(self, like) -> None:
+        torch = self.torch
+        self._actions = torch.zeros((self.num_envs, self.action_width), device=self.device, dtype=like.dtype)
+        self._graph_dtype = like.dtype
+        torch.cuda.synchronize(self.device)
+        self.B.capture_begin()
+        try:
+            self._enqueue_step(self._actions.data_ptr(), self.action_width, like.dtype == torch.float32)
+        finally:
+            self._graph = self.B.capture_end()
 
     def _wait(self):
         self.torch.cuda.current_stream(self.device).wait_stream(self._stream)
