@@ -209,6 +209,22 @@ int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* 
 int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
                                  int other_stride, int is_f32);
 
+/* ---- headless rasteriser ------------------------------------------------------------------------------- */
+/* Interface::render (SimulatorCPP/Interface.cpp:55-135: background, voxel grid lines, one quad per voxel coloured by cell
+ * type / actuation, surface edges) of one environment's current state, rasterised by a CUDA kernel into an RGB8 image of
+ * res_h x res_w x 3 bytes, row 0 = top -- the buffer Camera::get_image hands to EvoViewer.render('img')
+ * (evogym/viewer.py:239-250).  Camera: centre (cam_x, cam_y) and full view size (cam_w, cam_h) in engine units (metres), as
+ * Camera::set_pos / set_size receive them.  The reference's OpenGL path itself is unavailable on this box. */
+#define MEVO_RENDER_HIDE_BACKGROUND 1
+#define MEVO_RENDER_HIDE_GRID 2
+#define MEVO_RENDER_HIDE_EDGES 4
+#define MEVO_RENDER_HIDE_BOXELS 8
+#define MEVO_RENDER_DONT_CLEAR 16
+int mevo_env_render(mevo_batch* b, int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h, int flags,
+                    unsigned char* out);
+int mevo_env_render_device(mevo_batch* b, int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h,
+                           int flags, unsigned char* device_out);
+
 /* ---- CUDA graphs --------------------------------------------------------------------------------------- */
 /* Everything the *_device / *_async entry points enqueue on the batch's stream between capture_begin and capture_end
  * (policy actions, the step launches of all size classes, task outputs, observations) is recorded into one CUDA graph

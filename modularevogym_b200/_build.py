@@ -26,7 +26,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC", "-diag-suppress", "177",
 ]
 
-LIB_SOURCES = ["engine.cu", "task.cu", "c_api.cpp", "topology.cpp"]
+LIB_SOURCES = ["engine.cu", "task.cu", "render.cu", "c_api.cpp", "topology.cpp"]
 LIB_HEADERS = ["engine.h", "kernels.cuh", "wkernel.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
 
 

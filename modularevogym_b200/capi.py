@@ -89,6 +89,8 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_task_outputs_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i]),
     "mevo_batch_task_reset": (_i, [_vp, _dp, _i, _dp, _i, _dp, _i]),
     "mevo_batch_task_reset_device": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i]),
+    "mevo_env_render": (_i, [_vp, _i, _d, _d, _d, _d, _i, _i, _i, _bp]),
+    "mevo_env_render_device": (_i, [_vp, _i, _d, _d, _d, _d, _i, _i, _i, _vp]),
     "mevo_batch_capture_begin": (_i, [_vp]),
     "mevo_batch_capture_end": (_i, [_vp]),
     "mevo_batch_graph_launch": (_i, [_vp, _i]),
@@ -483,6 +485,17 @@ class Batch:
         vp = lambda p: C.c_void_p(p) if p else None
         _check(self.L.mevo_batch_task_reset_device(self.h, vp(flat_ptr), int(flat_stride), vp(modular_ptr), int(modular_stride),
                                                    vp(other_ptr), int(other_stride), int(is_f32)))
+
+    def render(self, env: int, cam_pos, cam_size, resolution, hide_background=False, hide_grid=False, hide_edges=False,
+               hide_boxels=False) -> np.ndarray:
+        """``Viewer.render(img_camera)`` + ``Camera.get_image()``: (h, w, 3) uint8, row 0 = top.  ``cam_pos`` / ``cam_size`` in
+        engine units (metres), ``resolution`` = (w, h)."""
+        w, h = int(resolution[0]), int(resolution[1])
+        img = np.zeros((h, w, 3), dtype=np.uint8)
+        flags = (1 if hide_background else 0) | (2 if hide_grid else 0) | (4 if hide_edges else 0) | (8 if hide_boxels else 0)
+        _check(self.L.mevo_env_render(self.h, int(env), float(cam_pos[0]), float(cam_pos[1]), float(cam_size[0]), float(cam_size[1]),
+                                      w, h, flags, _bptr(img)))
+        return img
 
     # -- CUDA graphs (include/mevo_b200.h "CUDA graphs")
     def capture_begin(self) -> None:

@@ -484,6 +484,24 @@ int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, voi
     });
 }
 
+int mevo_env_render(mevo_batch* b, int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h, int flags,
+                    unsigned char* out) {
+    return guard([&] {
+        if (!out) throw std::invalid_argument("render: null output");
+        b->impl.render(env, cam_x, cam_y, cam_w, cam_h, res_w, res_h, flags, out);
+        return 0;
+    });
+}
+
+int mevo_env_render_device(mevo_batch* b, int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h, int flags,
+                           unsigned char* device_out) {
+    return guard([&] {
+        if (!device_out) throw std::invalid_argument("render_device: null output");
+        b->impl.render_device(env, cam_x, cam_y, cam_w, cam_h, res_w, res_h, flags, device_out);
+        return 0;
+    });
+}
+
 int mevo_batch_capture_begin(mevo_batch* b) { return guard([&] { b->impl.capture_begin(); return 0; }); }
 int mevo_batch_capture_end(mevo_batch* b) { return guard([&] { return b->impl.capture_end(); }); }
 int mevo_batch_graph_launch(mevo_batch* b, int graph) { return guard([&] { b->impl.graph_launch(graph); return 0; }); }

@@ -131,6 +131,12 @@ public:
     void sight_obs(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
                    double* out_host, int stride);
 
+    // headless rasteriser (render.cu): Interface::render of one environment into an RGB8 image (res_h x res_w x 3, row 0 = top).
+    // flags: 1 hide_background, 2 hide_grid, 4 hide_edges, 8 hide_boxels, 16 dont_clear
+    void render_device(int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h, int flags,
+                       unsigned char* out_device);
+    void render(int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h, int flags, unsigned char* out_host);
+
     // ---- CUDA graphs: everything enqueued on the batch's stream between capture_begin() and capture_end() (policy actions, the
     // step launches of all size classes with their fork/join, task outputs, observations ...) becomes one graph; graph_launch
     // replays it with one driver call.  The device pointers passed to the captured calls are baked in: use persistent buffers.

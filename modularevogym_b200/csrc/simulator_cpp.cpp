@@ -62,6 +62,9 @@ public:
     Sim(const Sim&) = delete;
     Sim& operator=(const Sim&) = delete;
 
+    mevo_batch* batch_handle() const { return batch_; }
+    int env_index() const { return env_; }
+
     static void get_version() { std::cout << "Using Evolution Gym Simulator v2.2.5 (mevo_b200 CUDA engine)" << "\n"; }
 
     void init(int x, int y) {                                  // Sim::init, Sim.cpp:26-28
@@ -269,29 +272,51 @@ private:
 // ------------------------------------------------------------------------------------------------
 // Viewer / Camera: the reference draws through OpenGL (SimulatorCPP/Interface.cpp, Camera.cpp).  There is no
 // graphics stack on the B200 boxes, so the classes exist (evogym/viewer.py imports them) and say so when used.
+// Camera / Viewer: the reference renders with OpenGL (Camera.cpp, Interface.cpp), which is unavailable on this box.  An image
+// camera (`Camera(True)`, evogym/viewer.py:393-410) is rendered headlessly by the engine's CUDA rasteriser (csrc/render.cu)
+// into the buffer get_image hands out; a screen camera (`Camera(False)`) has no window to draw to and renders nothing.
 class Camera {
 public:
-    explicit Camera(bool) {}
+    explicit Camera(bool is_renderable) : renderable_(is_renderable) {}
     void set_pos(double x, double y) { px_ = x; py_ = y; }
     void set_size(double x, double y) { sx_ = x; sy_ = y; }
-    void set_resolution(double x, double y) { rw_ = (int)x; rh_ = (int)y; }
+    void set_resolution(double x, double y) {
+        rw_ = (int)x; rh_ = (int)y;
+        if (renderable_) image_.assign((size_t)std::max(0, rw_) * std::max(0, rh_) * 3, 0);
+    }
     int get_resolution_width() const { return rw_; }
     int get_resolution_height() const { return rh_; }
-    py::bytes get_image() const { throw std::runtime_error("Camera.get_image: OpenGL rendering is unavailable on this box (headless CUDA engine)"); }
-private:
-    double px_ = 0, py_ = 0, sx_ = 0, sy_ = 0;
+    py::memoryview get_image() {                                 // like the reference: a view of 3 * w * h bytes, row 0 = top
+        if (!renderable_) throw std::runtime_error("Camera.get_image: this camera renders to a window, which is unavailable on this box");
+        return py::memoryview::from_memory(image_.data(), (py::ssize_t)image_.size());
+    }
+    bool renderable_;
+    double px_ = 0, py_ = 0, sx_ = 1, sy_ = 1;
     int rw_ = 0, rh_ = 0;
+    std::vector<unsigned char> image_;
 };
 
 class Viewer {
 public:
-    explicit Viewer(Sim*) {}
-    void init() { throw std::runtime_error("Viewer.init: OpenGL rendering is unavailable on this box (headless CUDA engine)"); }
-    void render(Camera&, bool, bool, bool, bool, bool) { throw std::runtime_error("Viewer.render: OpenGL rendering is unavailable on this box"); }
+    explicit Viewer(Sim* sim) : sim_(sim) {}
+    void init() {}                                               // the reference opens the GLFW context here
+    void render(Camera& cam, bool hide_background, bool hide_grid, bool hide_edges, bool hide_boxels, bool dont_clear);
     void show_debug_window() {}
     void hide_debug_window() {}
     std::vector<int> get_debug_window_pos() { return {0, 0}; }
+private:
+    Sim* sim_;
 };
+
+void Viewer::render(Camera& cam, bool hide_background, bool hide_grid, bool hide_edges, bool hide_boxels, bool dont_clear) {
+    if (!cam.renderable_) return;                                // screen camera: no window on this box
+    if (!sim_ || !sim_->batch_handle() || sim_->env_index() < 0) throw std::runtime_error("Viewer.render: the Sim has no world yet");
+    if (cam.image_.empty()) throw std::runtime_error("Viewer.render: set the camera's resolution first");
+    const int flags = (hide_background ? 1 : 0) | (hide_grid ? 2 : 0) | (hide_edges ? 4 : 0) | (hide_boxels ? 8 : 0) | (dont_clear ? 16 : 0);
+    if (mevo_env_render(sim_->batch_handle(), sim_->env_index(), cam.px_, cam.py_, cam.sx_, cam.sy_, cam.rw_, cam.rh_, flags,
+                        cam.image_.data()) < 0)
+        fail();
+}
 
 // ------------------------------------------------------------------------------------------------
 // BatchSim: N independent environments on one GPU (what SubprocVecEnv + N reference Sims provide, in one process).
