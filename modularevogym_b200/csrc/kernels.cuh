@@ -316,7 +316,7 @@ __device__ __forceinline__ void apply_contact(double2* cf, const Contact& c, int
 }
 
 template <int G, int EPC>
-__global__ void __launch_bounds__(G* EPC) step_kernel(const StepParams prm) {
+__global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G * EPC) : 1)) step_kernel(const StepParams prm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NW = G / 32;
     const int grp = threadIdx.x / G;
