@@ -30,32 +30,34 @@ namespace mevo {
 
 namespace {
 
-// size classes: 0, 1 = warp-per-environment kernel (wkernel.cuh) with compile-time capacities;
-// 2..6 = group-per-environment kernel (kernels.cuh) with 32..512 threads per environment
-constexpr int kNumClasses = 7;
-constexpr int kFirstGroupClass = 2;
-const int kGroupSizes[kNumClasses] = {32, 32, 32, 64, 128, 256, 512};
+// size classes: 0, 1, 2 = warp-per-environment kernel (wkernel.cuh) with compile-time capacities;
+// 3..7 = group-per-environment kernel (kernels.cuh) with 32..512 threads per environment
+constexpr int kNumClasses = 8;
+constexpr int kFirstGroupClass = 3;
+constexpr int kLastClass = kNumClasses - 1;
+const int kGroupSizes[kNumClasses] = {32, 32, 32, 32, 64, 128, 256, 512};
 constexpr int kMaxSmemPerBlock = 227 * 1024;
 // warp-kernel capacities: points, edges, leaves, tested pairs, always-items, rigid-cell visits
 #define MEVO_WCAPS_A 40, 112, 24, 192, 256, 112     /* one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...) */
-#define MEVO_WCAPS_B 64, 160, 32, 512, 640, 128     /* 5x5 robot + a small free object (Pusher-v0, Thrower-v0, Carrier-v0) */
+#define MEVO_WCAPS_C 52, 144, 28, 320, 288, 64      /* 5x5 robot + the 3x2 package (Pusher-v0, Thrower-v0): 18.6 KB, 12 per SM */
+#define MEVO_WCAPS_B 64, 160, 32, 512, 640, 128     /* 5x5 robot + a larger free object (Carrier, Catcher, beams): 22.5 KB, 10 per SM */
 
 int group_class_for(int Pd, int Ed) {
     // threads per environment (32 / 128 / 256 / 512): the loops of a substep are short dependent chains and the
     // broad phase waits on L2, so more trips in parallel win over fewer barriers (measured on 10x10, 20x20 robots
     // and all-dynamic terrain: 1.06x - 1.33x over one class smaller); MEVO_GROUP_SHIFT (development) moves the classes
     static const int shift = [] { const char* e = std::getenv("MEVO_GROUP_SHIFT"); return e ? std::atoi(e) : 0; }();
-    int c = 6;
-    if (Ed <= 160 && Pd <= 64) c = 2;
-    else if (Ed <= 400 && Pd <= 160) c = 4;
-    else if (Ed <= 900 && Pd <= 320) c = 5;
-    return shift ? std::min(6, std::max(2, c + shift)) : c;
+    int c = kLastClass;
+    if (Ed <= 160 && Pd <= 64) c = kFirstGroupClass;
+    else if (Ed <= 400 && Pd <= 160) c = kFirstGroupClass + 2;
+    else if (Ed <= 900 && Pd <= 320) c = kFirstGroupClass + 3;
+    return shift ? std::min(kLastClass, std::max(kFirstGroupClass, c + shift)) : c;
 }
 
 int class_for(const DesignHeader& H, bool use_warp_kernel) {
     if (use_warp_kernel && H.warp_ok && H.max_deg <= 8 && H.unit_mass && H.n_obj <= 8 && H.n_types <= 16) {
-        const int caps[2][6] = {{MEVO_WCAPS_A}, {MEVO_WCAPS_B}};
-        for (int c = 0; c < 2; c++)
+        const int caps[3][6] = {{MEVO_WCAPS_A}, {MEVO_WCAPS_C}, {MEVO_WCAPS_B}};
+        for (int c = 0; c < 3; c++)
             if (H.Pd <= caps[c][0] && H.Ed <= caps[c][1] && H.n_leaf <= caps[c][2] && H.n_pairs <= caps[c][3] &&
                 H.n_items <= caps[c][4] && H.n_rvis <= caps[c][5]) return c;
     }
@@ -161,6 +163,7 @@ struct Batch::Impl {
     cudaEvent_t class_done[kNumClasses] = {};
     cudaEvent_t fork = nullptr;
     int concurrent_classes = 1;
+    int class_max[kNumClasses][6] = {};
     int* d_com_ranges = nullptr;
     double* d_com_out = nullptr;
     int com_obj = -1;
@@ -582,6 +585,7 @@ void Batch::finalize() {
     std::unordered_map<uint64_t, std::vector<std::pair<size_t, size_t>>> design_index, static_index;  // hash -> (offset, size)
     impl_->desc.assign(n, EnvDesc());
     impl_->class_envs.assign(kNumClasses, {});
+    std::memset(impl_->class_max, 0, sizeof(impl_->class_max));
     impl_->class_smem.assign(kNumClasses, 0);
     impl_->env_cost.clear();
     size_t state_doubles = 0;
@@ -640,6 +644,11 @@ void Batch::finalize() {
         state_doubles += sd;
         act_stride_ = std::max(act_stride_, e.n_act);
         e.cls = class_for(*H, impl_->use_warp_kernel);
+        {   // development aid (MEVO_DUMP_CLASSES=1): largest table sizes per size class, printed at the end of finalize
+            int* m = impl_->class_max[e.cls];
+            const int v[6] = {H->Pd, H->Ed, H->n_leaf, H->n_pairs, H->n_items, H->n_rvis};
+            for (int q = 0; q < 6; q++) m[q] = std::max(m[q], v[q]);
+        }
         if (e.cls >= kFirstGroupClass) {
             const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap);
             if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
@@ -651,6 +660,13 @@ void Batch::finalize() {
         impl_->env_cost.push_back(1000 * ((H->Pd + 31) / 32) + 700 * ((H->Ed + 63) / 64) + 40 * ((H->n_items + 31) / 32) +
                                   40 * ((H->n_pairs + 31) / 32) + 20 * H->n_rvis);
     }
+    if (const char* e = std::getenv("MEVO_DUMP_CLASSES"))
+        if (std::atoi(e))
+            for (int c = 0; c < kNumClasses; c++)
+                if (!impl_->class_envs[c].empty())
+                    std::fprintf(stderr, "[mevo] class %d: %zu envs, max points %d edges %d leaves %d pairs %d items %d visits %d\n", c,
+                                 impl_->class_envs[c].size(), impl_->class_max[c][0], impl_->class_max[c][1], impl_->class_max[c][2],
+                                 impl_->class_max[c][3], impl_->class_max[c][4], impl_->class_max[c][5]);
     for (int c = 0; c < kFirstGroupClass; c++)
         std::stable_sort(impl_->class_envs[c].begin(), impl_->class_envs[c].end(),
                          [&](int a, int b) { return impl_->env_cost[a] > impl_->env_cost[b]; });
@@ -1009,8 +1025,9 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, impl_->n_sm, impl_->balance != 0, st);
                 else launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, impl_->n_sm, impl_->balance != 0, st);
                 break;
-            case 1: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            case 2: {
+            case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
+            case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
+            case 3: {
                 // largest environments-per-CTA <= the configured one that fits in shared memory
                 const int want = impl_->epc32, sz = prm.smem_per_env;
                 if (want >= 12 && 12 * sz <= kMaxSmemPerBlock) launch_step<32, 12>(prm, sz, st);
@@ -1020,9 +1037,9 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 else launch_step<32, 1>(prm, sz, st);
                 break;
             }
-            case 3: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
-            case 4: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
-            case 5: launch_step<256, 1>(prm, prm.smem_per_env, st); break;
+            case 4: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
+            case 5: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
+            case 6: launch_step<256, 1>(prm, prm.smem_per_env, st); break;
             default: launch_step<512, 1>(prm, prm.smem_per_env, st); break;
         }
         CUDA_CHECK(cudaGetLastError());
