@@ -179,10 +179,14 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_WALKER 0
 #define MEVO_TASK_PUSHER 1
 #define MEVO_TASK_THROWER 2
+#define MEVO_TASK_CLIMBER 3             /* Climb0, evogym/envs/climb.py:38-112 (Climber-v0): reward = rise of the centre of mass */
+#define MEVO_TASK_OBSTACLE_TRAVERSER 4  /* WalkingBumpy2, evogym/envs/traverse.py:350-426 (ObstacleTraverser-v1): "other" observation =
+                                           [vel com 2, orientation 1, get_floor_obs("robot", ["ground"], 5) 11]; the flat observation
+                                           of this task holds [vel com, relative positions] only */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */
-/* package: NULL for MEVO_TASK_WALKER.  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
+/* package: used by MEVO_TASK_PUSHER / MEVO_TASK_THROWER only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
 int mevo_batch_task_configure(mevo_batch* b, int task, const char* robot, const char* package, int max_episode_steps);
 /* dims[0..4] = flat observation width, modular observation width (9 x voxels), "other" observation width,
  * largest voxel count of a robot grid, action stride */

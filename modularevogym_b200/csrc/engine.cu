@@ -1179,14 +1179,24 @@ void Batch::object_com_device(int obj_index, double* out_device_2n) {
     CUDA_CHECK(cudaGetLastError());
 }
 
-void Batch::object_orientation_device(int obj_index, double* out_device_n) {
+void Batch::object_orientation_strided_device(int obj_index, void* out, int row_stride, bool is_f32) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     const int n = num_envs();
     bind_object_ranges(obj_index);
-    orientation_kernel<<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, reinterpret_cast<const EnvDesc*>(d_envdesc_),
-                                                                      impl_->d_com_ranges, n, out_device_n ? out_device_n : impl_->d_com_out);
+    const EnvDesc* ed = reinterpret_cast<const EnvDesc*>(d_envdesc_);
+    if (is_f32)
+        orientation_kernel<float><<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, ed, impl_->d_com_ranges, n,
+                                                                                 static_cast<float*>(out), row_stride);
+    else
+        orientation_kernel<double><<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, ed, impl_->d_com_ranges, n,
+                                                                                  static_cast<double*>(out), row_stride);
     CUDA_CHECK(cudaGetLastError());
+}
+
+void Batch::object_orientation_device(int obj_index, double* out_device_n) {
+    bind_object_ranges(obj_index);                 // allocates d_com_out
+    object_orientation_strided_device(obj_index, out_device_n ? out_device_n : impl_->d_com_out, 1, false);
 }
 
 void Batch::object_orientation(int obj_index, double* out_host_n) {

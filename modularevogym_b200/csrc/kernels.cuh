@@ -912,8 +912,9 @@ __global__ void obs_kernel(const double* state, const EnvDesc* envs, const int* 
 // Environment::object_orientation_at_time (Environment.cpp:317-380) of one object per env, current state against
 // snapshot 0: magnitude-weighted mean angle between the centred point vectors, reflected to [0, 2 pi) by the sign of the
 // summed cross product (the reference's pi is the literal 3.1415926).  One warp per environment.
+template <typename OutT>
 __global__ void orientation_kernel(const double* state, const double* state0, const EnvDesc* envs,
-                                   const int* ranges /* n_envs x 3: start, count, Pd */, int n_envs, double* out) {
+                                   const int* ranges /* n_envs x 3: start, count, Pd */, int n_envs, OutT* out, int out_stride) {
     const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (env >= n_envs) return;
@@ -937,7 +938,7 @@ __global__ void orientation_kernel(const double* state, const double* state0, co
     }
     cnx = __shfl_sync(0xffffffffu, cnx, 0); cny = __shfl_sync(0xffffffffu, cny, 0);
     cox = __shfl_sync(0xffffffffu, cox, 0); coy = __shfl_sync(0xffffffffu, coy, 0);
-    if (count == 0) { if (lane == 0) out[env] = 0.0; return; }
+    if (count == 0) { if (lane == 0) out[(size_t)env * out_stride] = (OutT)0; return; }
     cnx /= count; cny /= count; cox /= count; coy /= count;
     double weighted = 0.0, weights = 0.0, cross = 0.0;
     for (int i = lane; i < count; i += 32) {
@@ -960,7 +961,7 @@ __global__ void orientation_kernel(const double* state, const double* state0, co
     }
     double angle = weighted / weights;
     if (cross > 0.0) angle = 2 * 3.1415926 - angle;
-    if (lane == 0) out[env] = angle;
+    if (lane == 0) out[(size_t)env * out_stride] = (OutT)angle;
 }
 
 }  // namespace mevo

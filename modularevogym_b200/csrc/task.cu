@@ -107,18 +107,20 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     double2* vel = pos + te.Pd;
 
     const bool unstable = p.unstable[env] != 0;
-    const double ri_x = p.prev[4 * env], pi_x = p.prev[4 * env + 2], pi_y = p.prev[4 * env + 3];
+    const double ri_x = p.prev[4 * env], ri_y = p.prev[4 * env + 1], pi_x = p.prev[4 * env + 2], pi_y = p.prev[4 * env + 3];
     ObjMeans R = object_means(pos, vel, te.r_start, te.r_count, lane);
     ObjMeans P = object_means(pos, vel, te.p_start, te.p_count, lane);
     // Sim::step that reports "unstable" saves no snapshot and does not advance time (Sim.cpp:105-115): the
     // environment then reads the same snapshot before and after the step.
-    const double rf_x = unstable ? ri_x : R.ax;
+    const double rf_x = unstable ? ri_x : R.ax, rf_y = unstable ? ri_y : R.ay;
     const double pf_x = unstable ? pi_x : P.ax, pf_y = unstable ? pi_y : P.ay;
 
     double reward;
     bool done = unstable;
-    if (p.task == 0) {                                   // walk.py:70-84
+    if (p.task == 0 || p.task == 4) {                    // walk.py:70-84; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
+    } else if (p.task == 3) {                            // climb.py:96-99
+        reward = rf_y - ri_y;
     } else if (p.task == 1) {                            // manipulate.py:38-58
         reward = (pf_x - pi_x) * 0.75;
         reward += (rf_x - ri_x) * 0.5;
@@ -130,7 +132,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         reward = pf_x - pi_x + motion_penalty;
     }
     if (unstable) reward -= 3.0;
-    if (p.task != 2 && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
+    if ((p.task == 0 || p.task == 1) && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
+    if (p.task == 3 && rf_y > 86 * kVoxel) { done = true; reward += 1.0; }        // climb.py:107-109
+    if (p.task == 4 && rf_x > 59 * kVoxel) { done = true; reward += 2.0; }        // traverse.py:420-423
     int flags = (done ? 1 : 0) | (unstable ? 4 : 0);
     int ep = p.episode_len[env] + 1;
     if (p.max_episode_steps > 0 && ep >= p.max_episode_steps) {   // gym TimeLimit: truncated = not already done
@@ -160,8 +164,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     // ---- observations of the (possibly reset) state
     double oth[6];
-    if (p.task == 0) {                                   // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
-        oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;
+    oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
+    if (p.task == 0 || p.task >= 3) {                    // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+        oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
         oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
     }
@@ -218,7 +223,8 @@ struct SightEnvRec {                     // 48 bytes per environment
 // comparisons are the reference's expressions in the reference's (voxel) units.
 template <typename OutT>
 __global__ void __launch_bounds__(128) sight_kernel(const double* state, const EnvDesc* envs, const SightEnvRec* rec, const double2* st_pts,
-                                                    int n_envs, int sight_dist, double sight_range, int ceil, OutT* out, int stride) {
+                                                    int n_envs, int sight_dist, double sight_range, int ceil, OutT* out, int stride,
+                                                    int row_stride) {
     const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (env >= n_envs) return;
@@ -231,7 +237,7 @@ __global__ void __launch_bounds__(128) sight_kernel(const double* state, const E
     if (r.o_count > 0) { cx /= r.o_count; cy /= r.o_count; }
     const double x_lo = cx - (sight_dist + 0.5), x_hi = cx + (sight_dist + 0.5);
     const int n_cols = 2 * sight_dist + 1;
-    OutT* row = out + (size_t)env * stride;
+    OutT* row = out + (size_t)env * row_stride;
     for (int c = 0; c < n_cols && c < stride; c++) {
         const int i = c - sight_dist;
         const double c_lo = cx + (i - 0.5), c_hi = cx + (i + 0.5);
@@ -288,6 +294,7 @@ struct Batch::Task {
     int max_episode_steps = 0;
     int epoch = -1;                          // finalize epoch the tables were built for
     int flat_width = 0, modular_width = 0, other_width = 0, max_vox = 0;
+    int robot_obj = -1;
     std::vector<TaskEnvRec> rec;
     std::vector<short4> vox_idx;
     std::vector<unsigned char> vox_mat;
@@ -345,12 +352,12 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 2) throw std::runtime_error("task_configure: unknown task id");
-    if (task != 0 && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
+    if (task < 0 || task > 4) throw std::runtime_error("task_configure: unknown task id");
+    if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
     task_->robot = robot;
-    task_->package = task == 0 ? std::string() : package;
+    task_->package = (task == 1 || task == 2) ? package : std::string();
     task_->max_episode_steps = max_episode_steps;
     task_->epoch = -1;
 }
@@ -367,13 +374,16 @@ void Batch::task_build() {
     T.vox_idx.clear(); T.vox_mat.clear();
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
-    T.other_width = T.task == 0 ? 2 : 6;
+    T.other_width = (T.task == 1 || T.task == 2) ? 6 : T.task == 4 ? 14 : 2;       // task 4: vel com 2 + orientation 1 + floor sight 11
+    T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
         const EnvHost& E = envs_[e];
         const int ro = E.world.find_object(T.robot);
         if (ro < 0) throw std::runtime_error("task: environment " + std::to_string(e) + " has no object named " + T.robot);
         const VoxelObject& rb = E.world.objects[ro];
+        if (T.robot_obj < 0) T.robot_obj = ro;
+        else if (T.robot_obj != ro) throw std::runtime_error("task: the robot must be the same object index in every environment");
         TaskEnvRec& r = T.rec[e];
         r.Pd = (int)E.dyn_points.size();
         r.r_start = E.point_local[rb.min_point];
@@ -419,7 +429,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, T.other_width + 2 * r.r_count);
+        T.flat_width = std::max(T.flat_width, (T.task == 4 ? 2 : T.other_width) + 2 * r.r_count);
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -496,11 +506,18 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    p.other_width = T.other_width;
+    p.other_width = T.task == 4 ? 2 : T.other_width;     // task 4: the kernel writes the velocity, the rest is filled below
     const int grid = (p.n_envs + 3) / 4;
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     CUDA_CHECK(cudaGetLastError());
+    if (T.task == 4 && other) {
+        // ObstacleTraverser-v1 (get_other_obs, base.py:706-714): [vel com, orientation, get_floor_obs("robot", ["ground"], 5)]
+        if (other_stride < 14) throw std::runtime_error("task_outputs: the 'other' observation of this task is 14 wide");
+        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+        object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
+        sight_obs_strided_device(T.robot_obj, {"ground"}, 5, 5.0, false, static_cast<char*>(other) + 3 * el, 11, other_stride, is_f32);
+    }
     if (reset_done) for (auto& e : envs_) e.host_fresh = false;
 }
 
@@ -572,6 +589,11 @@ void Batch::sight_free() {
 
 void Batch::sight_obs_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
                              void* out, int stride, bool is_f32) {
+    sight_obs_strided_device(obj_index, terrain, sight_dist, sight_range, ceil, out, stride, stride, is_f32);
+}
+
+void Batch::sight_obs_strided_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
+                                     void* out, int stride, int row_stride, bool is_f32) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     if (sight_dist < 0 || sight_dist > 1000) throw std::runtime_error("sight_obs: bad sight_dist");
@@ -627,10 +649,10 @@ void Batch::sight_obs_device(int obj_index, const std::vector<std::string>& terr
     const int grid = (n + 3) / 4;
     if (is_f32)
         sight_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
-                                                                    sight_dist, sight_range, ceil ? 1 : 0, static_cast<float*>(out), stride);
+                                                                    sight_dist, sight_range, ceil ? 1 : 0, static_cast<float*>(out), stride, row_stride);
     else
         sight_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
-                                                                     sight_dist, sight_range, ceil ? 1 : 0, static_cast<double*>(out), stride);
+                                                                     sight_dist, sight_range, ceil ? 1 : 0, static_cast<double*>(out), stride, row_stride);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -4,7 +4,7 @@ Host-side mirror of what the reference assembles per rollout worker out of proce
 (``examples/transformer_ppo/envs.py:29-77`` ``make_env`` / ``make_vec_envs``: ``gym.make(env_id, body=..., mode='modular')``
 -> ``TimeLimit`` -> ``SubprocVecEnv`` (``examples/modular_envs/wrappers/subproc_vec_env.py``: reset on done, return the reset
 observation) -> ``VecPyTorch`` (``envs.py:126-159``: numpy -> float32 torch tensors on the device, reward ``(n, 1)``)),
-for the three environments the benchmark configurations name (Walker-v0, Pusher-v0, Thrower-v0).
+for the environments the benchmark configurations name (Walker-v0, Pusher-v0, Thrower-v0, Climber-v0, ObstacleTraverser-v1).
 
 One env-step of all environments = three launches on one CUDA stream and no host round trip:
 policy output -> actuator targets (``policy_actions_kernel``), 30 substeps (``wstep_kernel`` / ``step_kernel``),
@@ -18,7 +18,8 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import WorldSpec, full_connectivity, pusher_world, thrower_world, walker_world
+from .world import (WorldSpec, climber_world, full_connectivity, obstacle_traverser_world, pusher_world, thrower_world,
+                    walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
 # (evogym/envs/__init__.py:16-20,125-129,149-153))
@@ -26,6 +27,8 @@ TASKS = {
     "Walker-v0": (0, walker_world, None, 500),
     "Pusher-v0": (1, pusher_world, "package", 500),
     "Thrower-v0": (2, thrower_world, "package", 300),
+    "Climber-v0": (3, climber_world, None, 400),                              # evogym/envs/climb.py:38-112, __init__.py:187-191
+    "ObstacleTraverser-v1": (4, obstacle_traverser_world, None, 1000),        # evogym/envs/traverse.py:350-426, __init__.py:76-80
 }
 
 
@@ -45,6 +48,9 @@ class BatchedEvoGymEnv:
         if env_id not in TASKS:
             raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
         task, builder, package, limit = TASKS[env_id]
+        if task == 4 and mode != "modular":
+            raise ValueError("ObstacleTraverser-v1 is available in modular mode only (its flat observation interleaves orientation "
+                             "and sight values with a per-robot number of positions)")
         self.env_id, self.mode, self.device_index = env_id, mode, device
         self.num_envs = len(bodies)
         self.bodies = [np.asarray(b) for b in bodies]

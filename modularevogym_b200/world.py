@@ -342,3 +342,32 @@ def thrower_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -
     w.add_from_array("package", _package(), 3, 7)
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
+
+
+def climber_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Climber-v0 (``evogym/envs/sim_files/Climber-v0.json`` + ``evogym/envs/climb.py:45-46``): a 7 x 90 fixed ``pipe`` (closed
+    at both ends, walls one voxel thick), the robot at voxel (1, 1)."""
+    w = WorldSpec(width=7, height=90)
+    grid = np.zeros((90, 7), dtype=np.int64)
+    grid[:, 0] = grid[:, 6] = VOXEL_TYPES["FIXED"]
+    grid[0, :] = grid[89, :] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("pipe", grid, 0, 0)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
+# column heights (voxels of FIXED ground from the bottom) of evogym/envs/sim_files/ObstacleTraverser-v1.json, 60 x 10
+OBSTACLE_TRAVERSER_V1_HEIGHTS = (3, 3, 4, 3, 4, 3, 3, 3, 2, 3, 2, 2, 3, 3, 2, 2, 1, 3, 4, 3, 2, 3, 3, 4, 3, 2, 3, 2, 3, 3, 2, 3, 4, 4, 2, 3, 4,
+                                 3, 4, 4, 4, 2, 3, 4, 5, 4, 3, 4, 3, 4, 3, 2, 2, 3, 4, 3, 2, 3, 10, 10)
+
+
+def obstacle_traverser_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """ObstacleTraverser-v1 (``evogym/envs/sim_files/ObstacleTraverser-v1.json`` + ``evogym/envs/traverse.py:355-356``): 60 x 10
+    bumpy fixed ``ground``, the robot at voxel (2, 4)."""
+    w = WorldSpec(width=60, height=10)
+    grid = np.zeros((10, 60), dtype=np.int64)
+    for c, hgt in enumerate(OBSTACLE_TRAVERSER_V1_HEIGHTS):
+        grid[10 - hgt:, c] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("robot", robot, 2, 4, connections)
+    return w

@@ -132,12 +132,15 @@ def main():
 
     from evogym.envs.walk import WalkingFlat
     from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
+    from evogym.envs.climb import Climb0
+    from evogym.envs.traverse import WalkingBumpy2
     from evogym import sample_robot
 
-    tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0")}
+    tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
+             "climber": (Climb0, "Climber-v0"), "obstacle": (WalkingBumpy2, "ObstacleTraverser-v1")}
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
-        for seed in (0, 1, 2):
+        for seed in ((0, 1, 2) if task in ("walker", "pusher", "thrower") else (0,)):
             random.seed(100 + seed)
             np.random.seed(100 + seed)
             body, conn = sample_robot((5, 5))

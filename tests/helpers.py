@@ -32,8 +32,8 @@ class EnvGolden:
             self.z = {k: z[k] for k in z.files}
         self.world = WorldSpec.from_dict(json.loads(str(self.z["world_json"])))
         self.env_id = str(self.z["env_id"])
-        self.task = {"Walker-v0": 0, "Pusher-v0": 1, "Thrower-v0": 2}[self.env_id]
-        self.package = None if self.task == 0 else "package"
+        self.task = {"Walker-v0": 0, "Pusher-v0": 1, "Thrower-v0": 2, "Climber-v0": 3, "ObstacleTraverser-v1": 4}[self.env_id]
+        self.package = "package" if self.task in (1, 2) else None
         self.n_steps = int(self.z["reward"].shape[0])
 
     def __getitem__(self, k):
