@@ -43,6 +43,8 @@ class BatchedEvoGymEnv:
     def __init__(self, env_id: str, bodies: Sequence[np.ndarray], connections: Optional[Sequence[Optional[np.ndarray]]] = None,
                  device: int = 0, mode: Optional[str] = "modular", max_episode_steps: Optional[int] = None,
                  worlds: Optional[Sequence[WorldSpec]] = None, out_dtype: str = "float32", use_graph: bool = True):
+        self._ctor = dict(env_id=env_id, device=device, mode=mode, max_episode_steps=max_episode_steps, out_dtype=out_dtype,
+                          use_graph=use_graph)
         import torch
 
         if env_id not in TASKS:
@@ -170,6 +172,14 @@ class BatchedEvoGymEnv:
     def close(self):
         self.torch.cuda.synchronize(self.device)
         self.B.close()
+
+    def update(self, bodies: Sequence[np.ndarray], connections: Optional[Sequence[Optional[np.ndarray]]] = None):
+        """Design loops (``env.update(body, connections)``, ``evogym/envs/walk.py:105-120``, called once per episode by the NCA /
+        CuCo examples): new robot bodies for every environment.  Like the reference, which builds a new world and a new ``EvoSim``,
+        the batch is rebuilt (worlds are packed on all host cores) and the reset observation of the new robots is returned."""
+        self.close()
+        self.__init__(bodies=bodies, connections=connections, **self._ctor)
+        return self.reset()
 
 
 def make_vec_envs(env_name: str, robot_structures: Sequence, device: int = 0, mode: Optional[str] = "modular",
