@@ -353,14 +353,15 @@ def main_ours(args) -> None:
 
     # ---- (2) end-to-end arm: pinned host actions in, host rewards + flags out, every step, through the C ABI
     com_host = torch.zeros((n, 2), dtype=torch.float64).pin_memory()
+    flags_host = torch.zeros((n,), dtype=torch.uint8).pin_memory()
     e2e_s = 0.0
     for s in range(W + K):
         flush_l2()
         B.sync()
         t0 = time.perf_counter()
-        B.set_actions_ptr(acts_host[s].data_ptr(), stride)   # H2D
-        B.step(1, True, want_flags=True)                     # kernel + D2H of the unstable flags
-        B.object_com_ptr(0, com_host.data_ptr())             # D2H of the per-env reward signal
+        B.set_actions_ptr(acts_host[s].data_ptr(), stride)   # H2D (pinned source, on the engine's stream)
+        B.step_async(1, True)                                # kernel
+        B.fetch_step_results_ptr(flags_host.data_ptr(), 0, com_host.data_ptr())   # D2H of flags + per-env reward signal, one sync
         dt = time.perf_counter() - t0
         if s >= W:
             e2e_s += dt

@@ -147,6 +147,10 @@ int mevo_batch_save_reset_state(mevo_batch* b);
 int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n);    /* env_ids NULL = all */
 /* centre of mass (mean of point positions) of object `obj` in every env: out = n_envs x 2 doubles (host) */
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out);
+/* What a rollout loop reads after mevo_batch_step_async, in one host round trip: the unstable flags of that step (n_envs bytes)
+ * and the centre of mass of object `obj` (n_envs x 2 doubles); either pointer may be NULL.  Returns the number of unstable
+ * environments. */
+int mevo_batch_fetch_step_results(mevo_batch* b, unsigned char* unstable_out, int obj, double* com_out);
 /* same, into a caller-owned DEVICE buffer (n_envs x 2 doubles), enqueued on the batch's stream, no sync */
 int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out);
 /* Sim::object_orientation_at_time (Environment.cpp:317-380) of object `obj` in every env, current state against

@@ -57,6 +57,7 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_set_auto_reset": (_i, [_vp, _i]),
     "mevo_batch_unstable_events": (C.c_longlong, [_vp]),
     "mevo_batch_object_com_device": (_i, [_vp, _i, _vp]),
+    "mevo_batch_fetch_step_results": (_i, [_vp, _vp, _i, _vp]),
     "mevo_batch_step": (_i, [_vp, _i, _i, _bp]),
     "mevo_batch_step_substeps": (_i, [_vp, _i, _i, _i, _bp]),
     "mevo_batch_step_async": (_i, [_vp, _i, _i]),
@@ -324,6 +325,11 @@ class Batch:
         v = np.ascontiguousarray(values, dtype=np.float64)
         assert v.ndim == 2 and v.shape[0] == self.num_envs
         _check(self.L.mevo_batch_set_actions(self.h, _dptr(v), v.shape[1]))
+
+    def fetch_step_results_ptr(self, flags_host_ptr: int, obj: int, com_host_ptr: int) -> int:
+        """flags of the last step + COM of ``obj`` into caller-owned (pinned) host buffers, one synchronisation"""
+        return _check(self.L.mevo_batch_fetch_step_results(self.h, C.c_void_p(flags_host_ptr) if flags_host_ptr else None, int(obj),
+                                                           C.c_void_p(com_host_ptr) if com_host_ptr else None))
 
     def set_actions_ptr(self, host_ptr: int, stride: int) -> None:
         _check(self.L.mevo_batch_set_actions(self.h, C.cast(host_ptr, _dp), int(stride)))

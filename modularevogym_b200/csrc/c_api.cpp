@@ -329,6 +329,10 @@ int mevo_batch_object_com(mevo_batch* b, int obj, double* out) {
     return guard([&] { b->impl.object_com(obj, out); return 0; });
 }
 
+int mevo_batch_fetch_step_results(mevo_batch* b, unsigned char* unstable_out, int obj, double* com_out) {
+    return guard([&] { return b->impl.fetch_step_results(unstable_out, obj, com_out); });
+}
+
 int mevo_batch_object_com_device(mevo_batch* b, int obj, double* device_out) {
     return guard([&] {
         if (!device_out) throw std::invalid_argument("object_com_device: null output");

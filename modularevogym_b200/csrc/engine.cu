@@ -1148,6 +1148,26 @@ void Batch::object_com(int obj_index, double* out_host_2n) {
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
 }
 
+// One host round trip for what a rollout loop reads after a step: the unstable flags of the last step launch and the centre of
+// mass of object `obj_index` in every environment (either output may be null).  Enqueues the COM kernel and both copies on the
+// batch's stream and waits once.
+int Batch::fetch_step_results(uint8_t* unstable_host, int obj_index, double* com_host_2n) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    const int n = num_envs();
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (com_host_2n) {
+        object_com_device(obj_index, nullptr);
+        CUDA_CHECK(cudaMemcpyAsync(com_host_2n, impl_->d_com_out, sizeof(double) * 2 * n, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_CHECK(cudaMemcpyAsync(impl_->unstable_host.data(), d_unstable_, n, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    int count = 0;
+    for (int i = 0; i < n; i++) count += impl_->unstable_host[i] ? 1 : 0;
+    if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host.data(), n);
+    return count;
+}
+
 void Batch::bind_object_ranges(int obj_index) {
     const int n = num_envs();
     if (impl_->com_obj == obj_index) return;

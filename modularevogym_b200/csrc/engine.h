@@ -99,6 +99,8 @@ public:
     // packed robot positions for the learner side: COM (x, y) of object `obj_index` per env
     void object_com(int obj_index, double* out_host_2n);
     void object_com_device(int obj_index, double* out_device_2n);   // async on stream()
+    // flags of the last step + COM of `obj_index`, one synchronisation; returns the number of unstable environments
+    int fetch_step_results(uint8_t* unstable_host, int obj_index, double* com_host_2n);
     // Environment::object_orientation_at_time of object `obj_index` per env: current state against snapshot 0
     void object_orientation(int obj_index, double* out_host_n);
     void object_orientation_device(int obj_index, double* out_device_n);   // async on stream()
