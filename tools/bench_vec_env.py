@@ -18,7 +18,7 @@ def main():
     import torch
     from modularevogym_b200.vec_env import BatchedEvoGymEnv
     from modularevogym_b200.world import sample_robot
-    specs = sys.argv[1:] or ["Walker-v0:4096", "Pusher-v0:4096", "Thrower-v0:4096"]
+    specs = sys.argv[1:] or ["Walker-v0:4096", "Pusher-v0:4096", "Thrower-v0:4096", "Climber-v0:4096", "ObstacleTraverser-v1:4096"]
     for spec in specs:
         env_id, n = spec.split(":")
         n = int(n)
