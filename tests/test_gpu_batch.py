@@ -164,3 +164,21 @@ def test_walker_observation_rows():
         a, b = int(g.obj_info[0, 1]), int(g.obj_info[0, 2])
         assert np.max(np.abs(com[i] - B.get_state(i)[0][a:b + 1].mean(axis=0))) <= 1e-12
     B.close()
+
+
+def test_fetch_step_results_equals_separate_reads():
+    """flags + centre of mass of a step in one round trip (mevo_batch_fetch_step_results) = step flags + object_com"""
+    worlds = [walker(s) for s in range(300, 306)]
+    A, B = capi.Batch(0), capi.Batch(0)
+    for w in worlds:
+        A.add_world(w); B.add_world(w)
+    A.finalize(); B.finalize()
+    acts = clipped_actions(np.random.default_rng(11), (len(worlds), A.action_stride))
+    A.set_actions(acts); B.set_actions(acts)
+    _, flags_a = A.step(1, apply_actions=True)
+    com_a = A.object_com(0)
+    B.step_async(1, apply_actions=True)
+    flags_b, com_b = np.zeros(len(worlds), dtype=np.uint8), np.zeros((len(worlds), 2))
+    n_unstable = B.fetch_step_results_ptr(flags_b.ctypes.data, 0, com_b.ctypes.data)
+    assert n_unstable == int(flags_a.sum()) and np.array_equal(flags_a, flags_b) and np.array_equal(com_a, com_b)
+    A.close(); B.close()
