@@ -112,9 +112,16 @@ constexpr int kMiscInts = 64;   // [0..15] per-warp candidate counts, [16..23] s
                                 // [24] constraint-violation flag, [32..47] per-warp contact masks,
                                 // [48..63] per-warp survivor counts
 
-MEVO_HD SmemLayout smem_layout(int Pd, int Ed, int n_leaf, int cand_cap) {
+// Group sizes whose read-only tables (mass, fixed flags, spring constants, rest lengths, end points, gather lists, edge flags:
+// 9 B per point + 25 B per edge) are read from the design blob through L1 instead of being copied to shared memory: for the
+// 256-thread class that is the difference between one and two CTAs per SM.
+constexpr int kGlobalTablesGroup = 256;
+MEVO_HD bool tables_in_global(int group_size) { return group_size == kGlobalTablesGroup; }
+
+MEVO_HD SmemLayout smem_layout(int Pd, int Ed, int n_leaf, int cand_cap, bool global_tables = false) {
     SmemLayout L;
     int o = 0;
+    const int tp = global_tables ? 0 : Pd, te = global_tables ? 0 : Ed;      // table sizes in shared memory
     L.o_pos = o;  o += 16 * Pd;
     L.o_vel = o;  o += 16 * Pd;
     L.o_last = o; o += 16 * Pd;
@@ -124,20 +131,20 @@ MEVO_HD SmemLayout smem_layout(int Pd, int Ed, int n_leaf, int cand_cap) {
     L.o_svel = o; o += 16 * Pd;
     L.o_accp = o; o += 16 * Pd;
     L.o_accv = o; o += 16 * Pd;
-    L.o_mass = o; o += align16(8 * Pd);
-    L.o_ek = o;   o += align16(8 * Ed);
-    L.o_el0 = o;  o += align16(8 * Ed);
+    L.o_mass = o; o += align16(8 * tp);
+    L.o_ek = o;   o += align16(8 * te);
+    L.o_el0 = o;  o += align16(8 * te);
     L.o_leq = o;  o += align16(8 * Ed);
     L.o_goal = o; o += align16(8 * Ed);
     L.o_ef = o;   o += 16 * Ed;
     L.o_aabb = o; o += 32 * n_leaf;
     L.o_leaf = o; o += 32 * n_leaf;
-    L.o_ea = o;   o += align16(2 * Ed);
-    L.o_eb = o;   o += align16(2 * Ed);
-    L.o_csro = o; o += align16(2 * (Pd + 1));
-    L.o_csre = o; o += align16(4 * Ed);
-    L.o_fixed = o; o += align16(Pd);
-    L.o_eflag = o; o += align16(Ed);
+    L.o_ea = o;   o += align16(2 * te);
+    L.o_eb = o;   o += align16(2 * te);
+    L.o_csro = o; o += global_tables ? 0 : align16(2 * (Pd + 1));
+    L.o_csre = o; o += align16(4 * te);
+    L.o_fixed = o; o += align16(tp);
+    L.o_eflag = o; o += align16(te);
     L.o_cand = o; o += align16(4 * cand_cap);
     L.o_surv = o; o += align16(4 * cand_cap);
     L.o_misc = o; o += 4 * kMiscInts;

@@ -46,7 +46,8 @@ int group_class_for(int Pd, int Ed) {
     // threads per environment (32 / 128 / 256 / 512): the loops of a substep are short dependent chains and the
     // broad phase waits on L2, so more trips in parallel win over fewer barriers (measured on 10x10, 20x20 robots
     // and all-dynamic terrain: 1.06x - 1.33x over one class smaller); MEVO_GROUP_SHIFT (development) moves the classes
-    static const int shift = [] { const char* e = std::getenv("MEVO_GROUP_SHIFT"); return e ? std::atoi(e) : 0; }();
+    const char* shift_env = std::getenv("MEVO_GROUP_SHIFT");       // read at every finalize: the tests move fixtures across classes
+    const int shift = shift_env ? std::atoi(shift_env) : 0;
     int c = kLastClass;
     if (Ed <= 160 && Pd <= 64) c = kFirstGroupClass;
     else if (Ed <= 400 && Pd <= 160) c = kFirstGroupClass + 2;
@@ -650,7 +651,7 @@ void Batch::finalize() {
             for (int q = 0; q < 6; q++) m[q] = std::max(m[q], v[q]);
         }
         if (e.cls >= kFirstGroupClass) {
-            const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap);
+            const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap, tables_in_global(kGroupSizes[e.cls]));
             if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
             impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
         }

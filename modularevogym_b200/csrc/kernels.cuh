@@ -344,7 +344,8 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
     const int16_t* st_grid = reinterpret_cast<const int16_t*>(sb + SH.o_grid);
 
     unsigned char* sm = smem_raw + (size_t)grp * prm.smem_per_env;
-    const SmemLayout L = smem_layout(Pd, Ed, n_leaf, H.cand_cap);
+    constexpr bool GT = (G == kGlobalTablesGroup);        // read-only tables stay in the design blob (L1-cached loads)
+    const SmemLayout L = smem_layout(Pd, Ed, n_leaf, H.cand_cap, GT);
     double2* pos = reinterpret_cast<double2*>(sm + L.o_pos);
     double2* vel = reinterpret_cast<double2*>(sm + L.o_vel);
     double2* last = reinterpret_cast<double2*>(sm + L.o_last);
@@ -354,22 +355,22 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
     double2* svel = reinterpret_cast<double2*>(sm + L.o_svel);
     double2* accp = reinterpret_cast<double2*>(sm + L.o_accp);
     double2* accv = reinterpret_cast<double2*>(sm + L.o_accv);
-    double* mass = reinterpret_cast<double*>(sm + L.o_mass);
-    double* ek = reinterpret_cast<double*>(sm + L.o_ek);
-    double* el0 = reinterpret_cast<double*>(sm + L.o_el0);
+    const double* mass = GT ? reinterpret_cast<const double*>(db + H.o_mass) : reinterpret_cast<const double*>(sm + L.o_mass);
+    const double* ek = GT ? reinterpret_cast<const double*>(db + H.o_ek) : reinterpret_cast<const double*>(sm + L.o_ek);
+    const double* el0 = GT ? reinterpret_cast<const double*>(db + H.o_el0) : reinterpret_cast<const double*>(sm + L.o_el0);
     double* leq = reinterpret_cast<double*>(sm + L.o_leq);
     double* goal = reinterpret_cast<double*>(sm + L.o_goal);
     double2* ef = reinterpret_cast<double2*>(sm + L.o_ef);
     double4* aabb = reinterpret_cast<double4*>(sm + L.o_aabb);
     LeafRec* leaf = reinterpret_cast<LeafRec*>(sm + L.o_leaf);
-    uint16_t* ea = reinterpret_cast<uint16_t*>(sm + L.o_ea);
-    uint16_t* eb = reinterpret_cast<uint16_t*>(sm + L.o_eb);
-    uint16_t* csro = reinterpret_cast<uint16_t*>(sm + L.o_csro);
-    uint16_t* csre = reinterpret_cast<uint16_t*>(sm + L.o_csre);
-    uint8_t* fixedp = reinterpret_cast<uint8_t*>(sm + L.o_fixed);
+    const uint16_t* ea = GT ? reinterpret_cast<const uint16_t*>(db + H.o_ea) : reinterpret_cast<const uint16_t*>(sm + L.o_ea);
+    const uint16_t* eb = GT ? reinterpret_cast<const uint16_t*>(db + H.o_eb) : reinterpret_cast<const uint16_t*>(sm + L.o_eb);
+    const uint16_t* csro = GT ? reinterpret_cast<const uint16_t*>(db + H.o_csro) : reinterpret_cast<const uint16_t*>(sm + L.o_csro);
+    const uint16_t* csre = GT ? reinterpret_cast<const uint16_t*>(db + H.o_csre) : reinterpret_cast<const uint16_t*>(sm + L.o_csre);
+    const uint8_t* fixedp = GT ? (db + H.o_fixed) : reinterpret_cast<const uint8_t*>(sm + L.o_fixed);
     unsigned int* cand = reinterpret_cast<unsigned int*>(sm + L.o_cand);
     unsigned int* surv = reinterpret_cast<unsigned int*>(sm + L.o_surv);
-    uint8_t* eflag = reinterpret_cast<uint8_t*>(sm + L.o_eflag);
+    const uint8_t* eflag = GT ? (db + H.o_eflag) : reinterpret_cast<const uint8_t*>(sm + L.o_eflag);
     volatile int* misc = reinterpret_cast<volatile int*>(sm + L.o_misc);
     const int seg_cap = H.cand_cap / NW;
 
@@ -382,19 +383,23 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
             vel[i] = g2[Pd + i];
             last[i] = g2[2 * Pd + i];
             vt[i] = g2[3 * Pd + i];
-            mass[i] = __ldg(reinterpret_cast<const double*>(db + H.o_mass) + i);
-            fixedp[i] = __ldg(db + H.o_fixed + i);
+            if (!GT) {
+                const_cast<double*>(mass)[i] = __ldg(reinterpret_cast<const double*>(db + H.o_mass) + i);
+                const_cast<uint8_t*>(fixedp)[i] = __ldg(db + H.o_fixed + i);
+            }
         }
         const double* ggoal = gstate + 8 * (size_t)Pd;
         const int16_t* eact = reinterpret_cast<const int16_t*>(db + H.o_eact);
         const double* act = prm.act + (size_t)env * prm.act_stride;
         for (int e = t; e < Ed; e += G) {
-            ek[e] = __ldg(reinterpret_cast<const double*>(db + H.o_ek) + e);
-            double l0 = __ldg(reinterpret_cast<const double*>(db + H.o_el0) + e);
-            el0[e] = l0;
-            eflag[e] = __ldg(db + H.o_eflag + e);
-            ea[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_ea) + e);
-            eb[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_eb) + e);
+            const double l0 = __ldg(reinterpret_cast<const double*>(db + H.o_el0) + e);
+            if (!GT) {
+                const_cast<double*>(ek)[e] = __ldg(reinterpret_cast<const double*>(db + H.o_ek) + e);
+                const_cast<double*>(el0)[e] = l0;
+                const_cast<uint8_t*>(eflag)[e] = __ldg(db + H.o_eflag + e);
+                const_cast<uint16_t*>(ea)[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_ea) + e);
+                const_cast<uint16_t*>(eb)[e] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_eb) + e);
+            }
             double g = ggoal[e];
             if (prm.apply_actions) {
                 // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather:
@@ -409,8 +414,10 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
             }
             goal[e] = g;
         }
-        for (int i = t; i < Pd + 1; i += G) csro[i] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_csro) + i);
-        for (int i = t; i < 2 * Ed; i += G) csre[i] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_csre) + i);
+        if (!GT) {
+            for (int i = t; i < Pd + 1; i += G) const_cast<uint16_t*>(csro)[i] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_csro) + i);
+            for (int i = t; i < 2 * Ed; i += G) const_cast<uint16_t*>(csre)[i] = __ldg(reinterpret_cast<const uint16_t*>(db + H.o_csre) + i);
+        }
         const uint4* gl = reinterpret_cast<const uint4*>(db + H.o_leaf);
         uint4* sl = reinterpret_cast<uint4*>(leaf);
         for (int i = t; i < 2 * n_leaf; i += G) sl[i] = __ldg(gl + i);

@@ -31,12 +31,15 @@ def goldens():
     return [Golden(n) for n in NAMES]
 
 
-@pytest.fixture(params=["warp", "group"])
+@pytest.fixture(params=["warp", "group", "group+1", "group-1"])
 def kernel_choice(request, monkeypatch):
     """Small environments run in the warp-per-environment kernel (wkernel.cuh) by default; MEVO_NO_WKERNEL=1
     (read when a batch is created) sends them through the group-per-environment kernel (kernels.cuh) like
     the large ones.  Both must reproduce the reference."""
     monkeypatch.setenv("MEVO_NO_WKERNEL", "0" if request.param == "warp" else "1")
+    # group+1 / group-1: every fixture one size class up / down (MEVO_GROUP_SHIFT), so that each group size -- including the
+    # 256-thread class that reads its tables from global memory -- sees 5x5, 10x10 and 20x20 worlds
+    monkeypatch.setenv("MEVO_GROUP_SHIFT", {"group+1": "1", "group-1": "-1"}.get(request.param, "0"))
     return request.param
 
 
