@@ -165,6 +165,8 @@ struct Batch::Impl {
     cudaEvent_t fork = nullptr;
     int concurrent_classes = 1;
     int class_max[kNumClasses][6] = {};
+    int* d_ids = nullptr;                         // reset_envs: environment ids on the device
+    int ids_cap = 0;
     int* d_com_ranges = nullptr;
     double* d_com_out = nullptr;
     int com_obj = -1;
@@ -218,7 +220,7 @@ Batch::~Batch() {
     cudaFree(d_envdesc_); cudaFree(d_class_envs_); cudaFree(d_unstable_); cudaFree(d_time_); cudaFree(d_err_);
     cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);
     if (impl_) {
-        cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out);
+        cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); cudaFree(impl_->d_ids);
         for (int c = 0; c < kNumClasses; c++) {
             if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
             if (impl_->class_done[c]) cudaEventDestroy(impl_->class_done[c]);
@@ -1098,7 +1100,6 @@ void Batch::graph_launch(int id) {
     if (id < 0 || id >= (int)graphs_.size() || !graphs_[id]) throw std::runtime_error("graph_launch: no such graph");
     CUDA_CHECK(cudaGraphLaunch((cudaGraphExec_t)graphs_[id], (cudaStream_t)stream_));
     for (auto& e : envs_) e.host_fresh = false;
-    impl_->time_dirty = true;
 }
 
 void Batch::graph_destroy(int id) {
@@ -1123,15 +1124,19 @@ void Batch::reset_envs(const int* env_ids, int n) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     if (n <= 0) return;
-    int* d_ids = nullptr;
-    CUDA_CHECK(cudaMalloc(&d_ids, sizeof(int) * n));
-    CUDA_CHECK(cudaMemcpyAsync(d_ids, env_ids, sizeof(int) * n, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
-    reset_kernel<<<n, 64, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, reinterpret_cast<const EnvDesc*>(d_envdesc_), d_design_, d_ids, n,
+    for (int i = 0; i < n; i++)
+        if (env_ids[i] < 0 || env_ids[i] >= num_envs()) throw std::runtime_error("reset: environment id out of range");
+    if (n > impl_->ids_cap) {                       // id list on the device, grown on demand and kept
+        cudaFree(impl_->d_ids); impl_->d_ids = nullptr; impl_->ids_cap = 0;
+        CUDA_CHECK(cudaMalloc(&impl_->d_ids, sizeof(int) * n));
+        impl_->ids_cap = n;
+    }
+    CUDA_CHECK(cudaMemcpyAsync(impl_->d_ids, env_ids, sizeof(int) * n, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    reset_kernel<<<n, 64, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, reinterpret_cast<const EnvDesc*>(d_envdesc_), d_design_, impl_->d_ids, n,
                                                        d_time_, d_unstable_);
     CUDA_CHECK(cudaGetLastError());
-    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
-    CUDA_CHECK(cudaFree(d_ids));
-    for (int i = 0; i < n; i++) envs_.at(env_ids[i]).host_fresh = false;
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));       // env_ids is the caller's (pageable) memory
+    for (int i = 0; i < n; i++) envs_[env_ids[i]].host_fresh = false;
 }
 
 void Batch::reset_all() {

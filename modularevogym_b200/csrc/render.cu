@@ -74,7 +74,6 @@ constexpr int kChunk = 128;
 __global__ void __launch_bounds__(kTile* kTile) render_kernel(RenderParams p) {
     __shared__ Prim sp[kChunk];
     __shared__ int keep[kChunk];
-    __shared__ int n_keep;
     const int c = blockIdx.x * kTile + threadIdx.x, r = blockIdx.y * kTile + threadIdx.y;
     const int tid = threadIdx.y * kTile + threadIdx.x;
     const float px = c + 0.5f, py = r + 0.5f;
@@ -92,7 +91,6 @@ __global__ void __launch_bounds__(kTile* kTile) render_kernel(RenderParams p) {
     }
     for (int base = 0; base < p.n_prims; base += kChunk) {
         const int m = min(kChunk, p.n_prims - base);
-        if (tid == 0) n_keep = 0;
         __syncthreads();
         if (tid < m) {
             const Prim q = p.prims[base + tid];
