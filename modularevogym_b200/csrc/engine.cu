@@ -199,6 +199,19 @@ Batch::~Batch() {
     for (void* g : graphs_) if (g) cudaGraphExecDestroy((cudaGraphExec_t)g);
 #ifdef MEVO_PROF
     {
+        unsigned long long gp[8];
+        if (cudaMemcpyFromSymbol(gp, g_gprof, sizeof(gp)) == cudaSuccess) {
+            unsigned long long tot = 0;
+            for (int q = 0; q < 7; q++) tot += gp[q];
+            if (tot) {
+                const char* names[7] = {"K2a boxes", "K2b broad", "K3a filter", "K3b resolve", "K4 rk4", "K5 limiters", "stage io"};
+                std::fprintf(stderr, "[prof] group kernel, share of group-cycles:");
+                for (int q = 0; q < 7; q++) std::fprintf(stderr, " %s %.3f", names[q], (double)gp[q] / tot);
+                std::fprintf(stderr, "\n");
+            }
+        }
+    }
+    {
         unsigned long long h[16];
         if (cudaMemcpyFromSymbol(h, g_wprof, sizeof(h)) == cudaSuccess && h[3]) {
             const char* names[4] = {"collide", "rk4", "constrain", "substep"};

@@ -315,6 +315,22 @@ __device__ __forceinline__ void apply_contact(double2* cf, const Contact& c, int
     if (!c.ab_static) { cf[c.a] = va; cf[c.b] = vb; }
 }
 
+#ifdef MEVO_PROF
+// development only (-DMEVO_PROF): cycles of the group kernel by phase, taken by the first thread of every group
+// [0] K2a boxes, [1] K2b broad phase, [2] K3a filter, [3] K3b resolve + contacts, [4] K4 RK4, [5] K5 limiters, [6] stage in / out
+__device__ unsigned long long g_gprof[8];
+#define MEVO_GPROF(k)                                                                      \
+    do {                                                                                   \
+        if (t == 0) {                                                                      \
+            const long long _n = clock64();                                                \
+            atomicAdd(&g_gprof[gp_phase], (unsigned long long)(_n - gp_t));                \
+            gp_t = _n; gp_phase = (k);                                                     \
+        }                                                                                  \
+    } while (0)
+#else
+#define MEVO_GPROF(k)
+#endif
+
 template <int G, int EPC>
 __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G * EPC) : 1)) step_kernel(const StepParams prm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -437,6 +453,10 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
     int completed_steps = 0;
     bool overflow = false;
 
+#ifdef MEVO_PROF
+    long long gp_t = clock64();
+    int gp_phase = 6;
+#endif
     for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
             // Warps of one CTA are kept within one substep of each other: they then run the same code at about
@@ -444,6 +464,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
             if (EPC > 1 && prm.cta_sync) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110); only keeps the barrier
             // ======================================================= K2a: leaf AABB refit (a-4)
+            MEVO_GPROF(0);
             for (int l = t; l < n_leaf; l += G) {
                 const LeafRec r = leaf[l];
                 double2 q = pos[r.pt[0]];
@@ -462,6 +483,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
 
             if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K2b: broad phase + compaction (a-4, a-12)
+            MEVO_GPROF(1);
             int cnt = 0;     // warp-uniform number of candidates in this warp's segment
             unsigned int* myseg = cand + warp * seg_cap;
             // (i) dynamic-vs-dynamic leaf pairs from the precomputed pair table (each unordered pair once)
@@ -550,6 +572,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
 
             if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K3a: narrow-phase filter
+            MEVO_GPROF(2);
             // A corner can only lie inside a boxel (Boxel::point_in_boxel) if it lies inside the boxel's
             // bounding box, so every (corner, boxel) item is first tested against the box (4 compares) and
             // only the survivors -- real or near penetrations, a handful per substep -- reach the resolver.
@@ -606,6 +629,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
             group_sync<G, EPC>(grp);
 
             // ======================================================= K3b: resolve + contact response (a-5, a-6)
+            MEVO_GPROF(3);
             int n_surv = 0;
 #pragma unroll
             for (int w = 0; w < NW; w++) n_surv += misc[48 + w];
@@ -665,6 +689,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
 
             if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K4: actuators + RK4 (a-7, a-8, a-9)
+            MEVO_GPROF(4);
             // (PhysicsEngine::update_actuators is done inside the first stage's edge pass: same positions, same distance)
 #pragma unroll 1
             for (int s = 0; s < 4; s++) {
@@ -744,6 +769,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
 
             if (EPC > 1 && prm.cta_sync > 1) __syncthreads();
             // ======================================================= K5: edge constraints + true velocity (a-10, a-11)
+            MEVO_GPROF(5);
             // Fast path: the limiters only act beyond +-25 % strain (+-3 % on the sides of rigid voxels).  Squared
             // lengths decide (no sqrt), with a 1e-7 relative guard band so that the decision never depends on the
             // rounding of dist / L0; inside the band every correction of the reference is exactly zero and the
@@ -841,6 +867,7 @@ __global__ void __launch_bounds__(G* EPC, ((G >= 64 && G * EPC < 512) ? 512 / (G
         if (!unstable) completed_steps++;
     }
 
+    MEVO_GPROF(6);
     // ---------------------------------------------------------------- stage out
     if (!ghost) {
         double2* g2 = reinterpret_cast<double2*>(gstate);
