@@ -258,7 +258,12 @@ int mevo_batch_enable_candidate_dump(mevo_batch* b, int cap_per_env);
  * Pairs of two all-fixed objects are never generated (they cannot move anything); pairs inside one
  * object are listed once (a < b) and applied twice, which is what the reference's ordered descent does. */
 int mevo_env_read_candidates(mevo_batch* b, int env, int* out, int cap);
-int mevo_env_error_flags(mevo_batch* b, int env);             /* bit 0: candidate list overflow */
+/* record collision_forces (PhysicsEngine.cpp:715-751: the contact response accumulated by resolve_collisions) of the first
+ * substep of subsequent step calls; read as (P, 2) doubles in global numbering.  Points of pruned all-FIXED objects read 0:
+ * the engine does not accumulate forces on points that can never move. */
+int mevo_batch_enable_force_dump(mevo_batch* b);
+int mevo_env_read_collision_forces(mevo_batch* b, int env, double* out);
+int mevo_env_error_flags(mevo_batch* b, int env);             /* always 0 since the candidate buffers are drained in rounds; kept for ABI stability */
 
 #ifdef __cplusplus
 }

@@ -102,6 +102,8 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_device_bytes": (C.c_longlong, [_vp]),
     "mevo_batch_enable_candidate_dump": (_i, [_vp, _i]),
     "mevo_env_read_candidates": (_i, [_vp, _i, _ip, _i]),
+    "mevo_batch_enable_force_dump": (_i, [_vp]),
+    "mevo_env_read_collision_forces": (_i, [_vp, _i, _dp]),
     "mevo_env_error_flags": (_i, [_vp, _i]),
 }
 
@@ -541,6 +543,15 @@ class Batch:
         out = np.zeros((cap, 4), dtype=np.int32)
         n = _check(self.L.mevo_env_read_candidates(self.h, env, _iptr(out), cap))
         return out[:min(n, cap)].copy()
+
+    def enable_force_dump(self) -> None:
+        _check(self.L.mevo_batch_enable_force_dump(self.h))
+
+    def read_collision_forces(self, env: int) -> np.ndarray:
+        """(P, 2) ``collision_forces`` of the first substep of the last step call (0 on pruned all-FIXED objects)"""
+        out = np.zeros((self.num_points(env), 2))
+        _check(self.L.mevo_env_read_collision_forces(self.h, env, _dptr(out)))
+        return out
 
     def error_flags(self, env: int) -> int:
         return _check(self.L.mevo_env_error_flags(self.h, env))

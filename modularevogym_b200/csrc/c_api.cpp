@@ -524,6 +524,14 @@ int mevo_env_read_candidates(mevo_batch* b, int env, int* out, int cap) {
     return guard([&] { return b->impl.read_candidates(env, out, cap); });
 }
 
+int mevo_batch_enable_force_dump(mevo_batch* b) {
+    return guard([&] { b->impl.enable_force_dump(); return 0; });
+}
+
+int mevo_env_read_collision_forces(mevo_batch* b, int env, double* out) {
+    return guard([&] { b->impl.read_collision_forces(env, out); return 0; });
+}
+
 int mevo_env_error_flags(mevo_batch* b, int env) {
     return guard([&] { return b->impl.error_flags(env); });
 }

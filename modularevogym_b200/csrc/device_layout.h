@@ -61,20 +61,23 @@ constexpr uint32_t kItemRefStatic = 1u << 27;
 constexpr uint32_t kItemSameObj = 1u << 28;
 constexpr int kItemCornerShift = 24;
 
-// per-edge flags (design blob / shared memory)
-constexpr uint8_t kEdgeRigidCell = 1;         // side of a CELL_RIGID voxel: visited by the ordered rigid pass
-
-struct DesignHeader {        // 128 bytes
+struct DesignHeader {        // 160 bytes
     int Pd, Ed, n_leaf, n_obj, n_pairs, n_rlev, n_rvis, n_act;
-    int cand_cap, o_mass, o_ek, o_el0, o_ea, o_eb, o_eact, o_fixed;
-    int o_csro, o_csre, o_leaf, o_obj, o_pairs, o_rlev, o_rvis, total;
-    int n_items, o_items, o_eflag;
-    // warp kernel (wkernel.cuh): compact copies that fit its shared-memory layout
-    int max_deg, unit_mass, o_csr8, o_eidx;   // 8-slot gather records; a | b << 8 | type << 16 | rigid-cell << 20
+    int cand_cap;                             // group kernel: candidate / survivor buffer entries (64 per warp, drained in rounds)
+    int list_cap;                             // group kernel: neighbour-list entries in the environment's scratch block
+    int o_el0, o_eact, o_fixed, o_leaf, o_obj, o_pairs;
+    int o_rlev, o_rvis, n_items, o_items, total;
+    // compact tables shared by both kernels
+    int max_deg, unit_mass, o_csr8;           // 8-slot gather records (edge << 1 | side, u16 each, 0xffff = empty)
     int n_types, o_etab;                      // distinct (spring constant, init_length_eq) pairs, double2 each
+    // warp kernel (wkernel.cuh): encodings that fit its shared-memory layout
+    int o_eidx;                               // u32 per edge: a | b << 8 | type << 16 | rigid-cell << 20
     int o_pairs16, o_items16, o_rord8;        // 16-bit pair / item codes, rigid-cell visits (u8 edge ids) in reference order
     int warp_ok;                              // every compact encoding above is valid for this design
-    int reserved[3];
+    // group kernel (gkernel.cuh)
+    int o_eidx10;                             // u32 per edge: a | b << 10 | type << 20 | rigid-cell << 26
+    int o_lpt16;                              // 8 bytes per leaf: TL, TR, BR, BL point ids, u16 each
+    int reserved[7];
 };
 static_assert(sizeof(DesignHeader) == 160, "DesignHeader must be 160 bytes");
 
@@ -96,60 +99,9 @@ struct EnvDesc {             // 32 bytes
     unsigned long long static_off;   // bytes into the static buffer, ~0ull = no static geometry
     unsigned long long state_off;    // doubles into the state buffer
     int act_off;                     // doubles into the action buffer
-    int pad;
+    int scratch_off16;               // 16-byte units into the scratch buffer (group kernel: neighbour list)
 };
 
 MEVO_HD int align16(int x) { return (x + 15) & ~15; }
-
-// shared-memory carve-up of one environment (byte offsets from the group's base)
-struct SmemLayout {
-    int o_pos, o_vel, o_last, o_vt, o_cf, o_spos, o_svel, o_accp, o_accv;
-    int o_mass, o_ek, o_el0, o_leq, o_goal, o_ef, o_aabb, o_leaf;
-    int o_ea, o_eb, o_csro, o_csre, o_fixed, o_eflag, o_cand, o_surv, o_misc, total;
-};
-
-constexpr int kMiscInts = 64;   // [0..15] per-warp candidate counts, [16..23] self-collision counts,
-                                // [24] constraint-violation flag, [32..47] per-warp contact masks,
-                                // [48..63] per-warp survivor counts
-
-// Group sizes whose read-only tables (mass, fixed flags, spring constants, rest lengths, end points, gather lists, edge flags:
-// 9 B per point + 25 B per edge) are read from the design blob through L1 instead of being copied to shared memory: for the
-// 256-thread class that is the difference between one and two CTAs per SM.
-constexpr int kGlobalTablesGroup = 256;
-MEVO_HD bool tables_in_global(int group_size) { return group_size == kGlobalTablesGroup; }
-
-MEVO_HD SmemLayout smem_layout(int Pd, int Ed, int n_leaf, int cand_cap, bool global_tables = false) {
-    SmemLayout L;
-    int o = 0;
-    const int tp = global_tables ? 0 : Pd, te = global_tables ? 0 : Ed;      // table sizes in shared memory
-    L.o_pos = o;  o += 16 * Pd;
-    L.o_vel = o;  o += 16 * Pd;
-    L.o_last = o; o += 16 * Pd;
-    L.o_vt = o;   o += 16 * Pd;
-    L.o_cf = o;   o += 16 * Pd;
-    L.o_spos = o; o += 16 * Pd;
-    L.o_svel = o; o += 16 * Pd;
-    L.o_accp = o; o += 16 * Pd;
-    L.o_accv = o; o += 16 * Pd;
-    L.o_mass = o; o += align16(8 * tp);
-    L.o_ek = o;   o += align16(8 * te);
-    L.o_el0 = o;  o += align16(8 * te);
-    L.o_leq = o;  o += align16(8 * Ed);
-    L.o_goal = o; o += align16(8 * Ed);
-    L.o_ef = o;   o += 16 * Ed;
-    L.o_aabb = o; o += 32 * n_leaf;
-    L.o_leaf = o; o += 32 * n_leaf;
-    L.o_ea = o;   o += align16(2 * te);
-    L.o_eb = o;   o += align16(2 * te);
-    L.o_csro = o; o += global_tables ? 0 : align16(2 * (Pd + 1));
-    L.o_csre = o; o += align16(4 * te);
-    L.o_fixed = o; o += align16(tp);
-    L.o_eflag = o; o += align16(te);
-    L.o_cand = o; o += align16(4 * cand_cap);
-    L.o_surv = o; o += align16(4 * cand_cap);
-    L.o_misc = o; o += 4 * kMiscInts;
-    L.total = align16(o);
-    return L;
-}
 
 }  // namespace mevo

@@ -17,6 +17,7 @@
 
 #include "kernels.cuh"
 #include "wkernel.cuh"
+#include "gkernel.cuh"
 
 namespace mevo {
 
@@ -31,28 +32,31 @@ namespace mevo {
 namespace {
 
 // size classes: 0, 1, 2 = warp-per-environment kernel (wkernel.cuh) with compile-time capacities;
-// 3..7 = group-per-environment kernel (kernels.cuh) with 32..512 threads per environment
-constexpr int kNumClasses = 8;
+// 3..6 = CTA-per-environment kernel (gkernel.cuh) with 64 / 128 / 256 / 512 threads per environment
+constexpr int kNumClasses = 7;
 constexpr int kFirstGroupClass = 3;
 constexpr int kLastClass = kNumClasses - 1;
-const int kGroupSizes[kNumClasses] = {32, 32, 32, 32, 64, 128, 256, 512};
+const int kGroupSizes[kNumClasses] = {32, 32, 32, 64, 128, 256, 512};
 constexpr int kMaxSmemPerBlock = 227 * 1024;
+constexpr int kGroupMaxPoints = 1024, kGroupMaxTypes = 64;      // 10-bit point ids, 6-bit edge types in the packed edge word
 // warp-kernel capacities: points, edges, leaves, tested pairs, always-items, rigid-cell visits
 #define MEVO_WCAPS_A 40, 112, 24, 192, 256, 112     /* one 5x5 robot on static terrain (Walker-v0, Climber-v0, ...) */
 #define MEVO_WCAPS_C 52, 144, 28, 320, 288, 64      /* 5x5 robot + the 3x2 package (Pusher-v0, Thrower-v0): 18.6 KB, 12 per SM */
 #define MEVO_WCAPS_B 64, 160, 32, 512, 640, 128     /* 5x5 robot + a larger free object (Carrier, Catcher, beams): 22.5 KB, 10 per SM */
 
 int group_class_for(int Pd, int Ed) {
-    // threads per environment (32 / 128 / 256 / 512): the loops of a substep are short dependent chains and the
-    // broad phase waits on L2, so more trips in parallel win over fewer barriers (measured on 10x10, 20x20 robots
-    // and all-dynamic terrain: 1.06x - 1.33x over one class smaller); MEVO_GROUP_SHIFT (development) moves the classes
+    // threads per environment: one point per thread and ~3 edges per thread in flight (7x7 -> 64, 10x10 -> 128, 14x14 -> 256,
+    // 20x20 -> 512); MEVO_GROUP_SHIFT (development, tests) moves every environment up or down one class -- a class whose
+    // largest environment has more points than threads runs the two-points-per-thread build of the kernel
     const char* shift_env = std::getenv("MEVO_GROUP_SHIFT");       // read at every finalize: the tests move fixtures across classes
     const int shift = shift_env ? std::atoi(shift_env) : 0;
     int c = kLastClass;
-    if (Ed <= 160 && Pd <= 64) c = kFirstGroupClass;
-    else if (Ed <= 400 && Pd <= 160) c = kFirstGroupClass + 2;
-    else if (Ed <= 900 && Pd <= 320) c = kFirstGroupClass + 3;
-    return shift ? std::min(kLastClass, std::max(kFirstGroupClass, c + shift)) : c;
+    if (Ed <= 192 && Pd <= 64) c = kFirstGroupClass;
+    else if (Ed <= 448 && Pd <= 128) c = kFirstGroupClass + 1;
+    else if (Ed <= 832 && Pd <= 256) c = kFirstGroupClass + 2;
+    c = shift ? std::min(kLastClass, std::max(kFirstGroupClass, c + shift)) : c;
+    while (c < kLastClass && Pd > 2 * kGroupSizes[c]) c++;          // at most two points per thread
+    return c;
 }
 
 int class_for(const DesignHeader& H, bool use_warp_kernel) {
@@ -90,18 +94,6 @@ struct BlobWriter {
     }
 };
 
-template <int G, int EPC>
-void launch_step(const StepParams& prm, int smem_per_env, cudaStream_t stream) {
-    const int smem = smem_per_env * EPC;
-    static int configured = -1;
-    if (smem > configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(step_kernel<G, EPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = smem;
-    }
-    const int grid = (prm.n_class_envs + EPC - 1) / EPC;
-    step_kernel<G, EPC><<<grid, G * EPC, smem, stream>>>(prm);
-}
-
 // environments per CTA that make the launch a whole number of equally full waves (slots = CTAs resident at once)
 int balanced_envs_per_cta(int n_envs, int epc, int slots) {
     const int ctas = (n_envs + epc - 1) / epc;
@@ -110,19 +102,52 @@ int balanced_envs_per_cta(int n_envs, int epc, int slots) {
     return std::max(1, std::min(epc, per));
 }
 
+// Kernel attributes are per device: every Batch::finalize sets the dynamic shared-memory limit of the kernels its classes
+// use on its own device (several batches on several GPUs of one process each configure their own context).
+template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
+void configure_wstep() {
+    constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
+    static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
+    CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+}
+
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 void launch_wstep(StepParams prm, int n_sm, bool balance, cudaStream_t stream) {
     constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
-    static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
-    static bool configured = false;
-    if (!configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
     prm.envs_per_cta = balance ? balanced_envs_per_cta(prm.n_class_envs, EPC, n_sm * MINB) : EPC;
     const int grid = (prm.n_class_envs + prm.envs_per_cta - 1) / prm.envs_per_cta;
     wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
+}
+
+// group kernel builds: (threads, CTAs per SM the register budget is set for, points per thread)
+enum class GAction { Configure, Launch };
+template <int G, int MINB, int PPT>
+void gstep_do(GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
+    if (what == GAction::Configure)
+        CUDA_CHECK(cudaFuncSetAttribute(gstep_kernel<G, MINB, PPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    else
+        gstep_kernel<G, MINB, PPT><<<prm->n_class_envs, G, smem, stream>>>(*prm);
+}
+
+void gstep_dispatch(int cls, int ppt, int variant, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
+    const int g = kGroupSizes[cls];
+    if (ppt == 2) {
+        if (g == 64) gstep_do<64, 8, 2>(what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 4, 2>(what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 2, 2>(what, prm, smem, stream);
+        else gstep_do<512, 1, 2>(what, prm, smem, stream);
+    } else if (variant == 0) {
+        if (g == 64) gstep_do<64, 8, 1>(what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 4, 1>(what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 2, 1>(what, prm, smem, stream);
+        else gstep_do<512, 1, 1>(what, prm, smem, stream);
+    } else {
+        if (g == 64) gstep_do<64, 16, 1>(what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 6, 1>(what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 3, 1>(what, prm, smem, stream);
+        else gstep_do<512, 2, 1>(what, prm, smem, stream);
+    }
 }
 
 __global__ void reset_kernel(double* state, const double* state0, const EnvDesc* envs, const uint8_t* design,
@@ -154,7 +179,10 @@ struct Batch::Impl {
     std::vector<int> env_cost;                    // per env: estimated work of one substep
     bool use_warp_kernel = true;
     int wepc = 0;                                 // warp kernel: environments per CTA override (0 = default)
-    int epc32 = 12;
+    int class_ppt[kNumClasses] = {};              // group kernel: points per thread of the class's build (1 or 2)
+    int gvariant[kNumClasses] = {};               // group kernel: which register-budget build (gstep_dispatch) the class runs
+    unsigned int* d_scratch = nullptr;            // group kernel: neighbour lists
+    double* d_cf = nullptr;                       // test hook: collision_forces of the first substep
     int cta_sync = 1;
     int balance = 1;                              // warp kernel: environments per CTA chosen for equally full waves
     int n_sm = 148;
@@ -180,10 +208,10 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     cudaStream_t s;
     CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     stream_ = s;
-    if (const char* e = std::getenv("MEVO_EPC32")) {
-        int v = std::atoi(e);
-        if (v == 1 || v == 2 || v == 4 || v == 6 || v == 12) impl_->epc32 = v;
-    }
+    // development: MEVO_GVARIANT = one digit per group class (64, 128, 256, 512 threads), 0 / 1 = the two register budgets
+    for (int c = kFirstGroupClass; c < kNumClasses; c++) impl_->gvariant[c] = 1;
+    if (const char* e = std::getenv("MEVO_GVARIANT"))
+        for (int c = kFirstGroupClass; c < kNumClasses && e[c - kFirstGroupClass]; c++) impl_->gvariant[c] = e[c - kFirstGroupClass] == '1';
     if (const char* e = std::getenv("MEVO_NO_WKERNEL")) impl_->use_warp_kernel = std::atoi(e) == 0;
     if (const char* e = std::getenv("MEVO_WEPC")) impl_->wepc = std::atoi(e);
     if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
@@ -200,15 +228,11 @@ Batch::~Batch() {
 #ifdef MEVO_PROF
     {
         unsigned long long gp[8];
-        if (cudaMemcpyFromSymbol(gp, g_gprof, sizeof(gp)) == cudaSuccess) {
-            unsigned long long tot = 0;
-            for (int q = 0; q < 7; q++) tot += gp[q];
-            if (tot) {
-                const char* names[7] = {"K2a boxes", "K2b broad", "K3a filter", "K3b resolve", "K4 rk4", "K5 limiters", "stage io"};
-                std::fprintf(stderr, "[prof] group kernel, share of group-cycles:");
-                for (int q = 0; q < 7; q++) std::fprintf(stderr, " %s %.3f", names[q], (double)gp[q] / tot);
-                std::fprintf(stderr, "\n");
-            }
+        if (cudaMemcpyFromSymbol(gp, g_g2prof, sizeof(gp)) == cudaSuccess) {
+            const unsigned long long tot = gp[0] + gp[1] + gp[2];
+            if (tot)
+                std::fprintf(stderr, "[prof] group kernel, share of CTA cycles: collide %.3f rk4 %.3f constrain %.3f\n",
+                             (double)gp[0] / tot, (double)gp[1] / tot, (double)gp[2] / tot);
         }
     }
     {
@@ -234,6 +258,7 @@ Batch::~Batch() {
     cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);
     if (impl_) {
         cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); cudaFree(impl_->d_ids);
+        cudaFree(impl_->d_scratch); cudaFree(impl_->d_cf);
         for (int c = 0; c < kNumClasses; c++) {
             if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
             if (impl_->class_done[c]) cudaEventDestroy(impl_->class_done[c]);
@@ -296,7 +321,8 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
             for (int k = ob.min_edge; k <= ob.max_edge; k++) { e.edge_local[k] = (int)e.dyn_edges.size(); e.dyn_edges.push_back(k); }
     }
     const int Pd = (int)e.dyn_points.size(), Ed = (int)e.dyn_edges.size();
-    if (Pd > 65000 || Ed > 32000) throw std::runtime_error("environment too large for 16-bit local ids");
+    if (Pd > kGroupMaxPoints || Ed > 32000)
+        throw std::runtime_error("environment too large: more than 1024 simulated points (or 32000 springs) in one environment");
 
     auto make_leaf = [&](const VoxelObject& ob, const Boxel& b, bool is_dyn, int obj_slot) {
         LeafRec r;
@@ -382,6 +408,10 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.max_deg = max_deg;
     H.unit_mass = 1;
     for (int i = 0; i < Pd; i++) if (mass[i] != 1.0) H.unit_mass = 0;
+    // both kernels rely on what the reference's world builder guarantees (ObjectCreator.h:36-47: mass 1.0; a lattice point
+    // touches at most 4 sides + 4 diagonals)
+    if (!H.unit_mass) throw std::runtime_error("point masses other than 1.0 are not supported");
+    if (max_deg > 8) throw std::runtime_error("a point with more than 8 incident springs is not supported");
     // leaves, objects, pair table
     std::vector<LeafRec> leaves;
     std::vector<ObjRec> objrecs;
@@ -436,13 +466,13 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
             }
             pairs.push_back(code);
         }
-    // per-edge flags
+    // per-edge flag: side of a CELL_RIGID voxel (visited by the ordered rigid-cell pass)
     std::vector<uint8_t> eflag(Ed, 0);
     for (int o = 0; o < n_obj; o++) {
         if (!dyn[o]) continue;
         for (const Boxel& b : W.objects[o].boxels)
             if (b.cell_type == CELL_RIGID)
-                for (int q = 0; q < 4; q++) eflag[e.edge_local[b.ed[q]]] |= kEdgeRigidCell;
+                for (int q = 0; q < 4; q++) eflag[e.edge_local[b.ed[q]]] = 1;
     }
     // rigid-cell visit schedule: reference order = object, boxel, (top,right,bot,left); levels = point-disjoint
     std::vector<uint16_t> rlev(1, 0), rvis;
@@ -476,40 +506,44 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.n_obj = (int)objrecs.size();
     H.n_pairs = (int)pairs.size();
     H.n_items = (int)items.size();
-    // per-warp segments of the candidate / survivor lists must hold at least two 32-wide chunks
-    H.cand_cap = ((std::max(std::max(128, 16 * H.n_leaf), 64 * (kGroupSizes[group_class_for(Pd, Ed)] / 32)) + 15) / 16) * 16;
+    // group kernel: 64 candidates / survivors per warp and round (both buffers are drained in rounds); the neighbour list holds
+    // the whole pair table when that is small, else room for ~24 near neighbours per leaf (an overflowing warp falls back to
+    // scanning its share of the table)
+    const int n_warps = kGroupSizes[group_class_for(Pd, Ed)] / 32;
+    H.cand_cap = 64 * n_warps;
+    {
+        const int want = std::min(H.n_pairs, std::max(2048, 24 * H.n_leaf));
+        const int per_warp = ((want + n_warps - 1) / n_warps + 63) & ~63;
+        H.list_cap = H.n_pairs ? per_warp * n_warps : 0;
+    }
 
-    H.o_mass = dw.begin_section(); dw.put_array(mass);
-    H.o_ek = dw.begin_section(); dw.put_array(ek);
     H.o_el0 = dw.begin_section(); dw.put_array(el0);
-    H.o_ea = dw.begin_section(); dw.put_array(ea);
-    H.o_eb = dw.begin_section(); dw.put_array(eb);
     H.o_eact = dw.begin_section(); dw.put_array(eact);
     H.o_fixed = dw.begin_section(); dw.put_array(fixed);
-    H.o_csro = dw.begin_section(); dw.put_array(csro);
-    H.o_csre = dw.begin_section(); dw.put_array(csre);
     H.o_leaf = dw.begin_section(); dw.put_array(leaves);
     H.o_obj = dw.begin_section(); dw.put_array(objrecs);
     H.o_pairs = dw.begin_section(); dw.put_array(pairs);
     H.o_rlev = dw.begin_section(); dw.put_array(rlev);
     H.o_rvis = dw.begin_section(); dw.put_array(rvis);
     H.o_items = dw.begin_section(); dw.put_array(items);
-    H.o_eflag = dw.begin_section(); dw.put_array(eflag);
-    // compact encodings for the warp kernel
+    // compact encodings: distinct (spring constant, init_length_eq) pairs + one packed word per edge
     bool warp_ok = Pd <= 255 && Ed <= 32767 && leaves.size() <= 32 && objrecs.size() <= 8 && visit_order.size() <= 255 * 4;
     std::vector<double> etab;                       // (ek, el0) pairs
-    std::vector<uint32_t> eidx(Ed);
+    std::vector<uint32_t> eidx(Ed), eidx10(Ed);
     for (int k = 0; k < Ed; k++) {
         int type = -1;
         for (size_t q = 0; q + 1 < etab.size(); q += 2)
             if (etab[q] == ek[k] && etab[q + 1] == el0[k]) { type = (int)q / 2; break; }
         if (type < 0) { type = (int)etab.size() / 2; etab.push_back(ek[k]); etab.push_back(el0[k]); }
-        if (type > 15) { warp_ok = false; type = 15; }
-        eidx[k] = (uint32_t)(ea[k] & 0xff) | ((uint32_t)(eb[k] & 0xff) << 8) | ((uint32_t)type << kEidxTypeShift) |
-                  ((uint32_t)(eflag[k] & kEdgeRigidCell ? 1 : 0) << kEidxRigidBit);
+        if (type > 15) warp_ok = false;
+        eidx[k] = (uint32_t)(ea[k] & 0xff) | ((uint32_t)(eb[k] & 0xff) << 8) | ((uint32_t)(type & 15) << kEidxTypeShift) |
+                  ((uint32_t)eflag[k] << kEidxRigidBit);
+        eidx10[k] = (uint32_t)(ea[k] & 0x3ff) | ((uint32_t)(eb[k] & 0x3ff) << kEidxBShift) | ((uint32_t)(type & 63) << kEidxTypeShift10) |
+                    ((uint32_t)eflag[k] << kEidxRigidBit10);
     }
     H.n_types = (int)etab.size() / 2;
-    std::vector<uint16_t> pairs16, items16;
+    if (H.n_types > kGroupMaxTypes) throw std::runtime_error("more than 64 distinct (spring constant, rest length) pairs in one environment");
+    std::vector<uint16_t> pairs16, items16, lpt16;
     std::vector<uint8_t> rord8;
     if (warp_ok) {
         for (uint32_t c : pairs) {
@@ -523,6 +557,8 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
         for (int le : visit_order) rord8.push_back((uint8_t)le);
         if (Ed > 255 && !visit_order.empty()) warp_ok = false;
     }
+    for (const LeafRec& lr : leaves)
+        for (int q = 0; q < 4; q++) lpt16.push_back(lr.pt[q]);
     H.warp_ok = warp_ok ? 1 : 0;
     H.o_csr8 = dw.begin_section(); dw.put_array(csr8);
     H.o_eidx = dw.begin_section(); dw.put_array(eidx);
@@ -530,6 +566,8 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.o_pairs16 = dw.begin_section(); dw.put_array(pairs16);
     H.o_items16 = dw.begin_section(); dw.put_array(items16);
     H.o_rord8 = dw.begin_section(); dw.put_array(rord8);
+    H.o_eidx10 = dw.begin_section(); dw.put_array(eidx10);
+    H.o_lpt16 = dw.begin_section(); dw.put_array(lpt16);
     H.total = dw.begin_section();
     std::memcpy(design.data(), &H, sizeof(H));
 
@@ -604,7 +642,8 @@ void Batch::finalize() {
     std::memset(impl_->class_max, 0, sizeof(impl_->class_max));
     impl_->class_smem.assign(kNumClasses, 0);
     impl_->env_cost.clear();
-    size_t state_doubles = 0;
+    size_t state_doubles = 0, scratch_bytes = 0;
+    std::memset(impl_->class_ppt, 0, sizeof(impl_->class_ppt));
     act_stride_ = 1;
 
     auto intern = [](std::vector<uint8_t>& pool, std::unordered_map<uint64_t, std::vector<std::pair<size_t, size_t>>>& index,
@@ -666,9 +705,13 @@ void Batch::finalize() {
             for (int q = 0; q < 6; q++) m[q] = std::max(m[q], v[q]);
         }
         if (e.cls >= kFirstGroupClass) {
-            const SmemLayout L = smem_layout(H->Pd, H->Ed, H->n_leaf, H->cand_cap, tables_in_global(kGroupSizes[e.cls]));
+            const GLayout L = g_layout(H->Pd, H->Ed, H->n_leaf, H->n_types, H->cand_cap);
             if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
             impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
+            impl_->class_ppt[e.cls] = std::max(impl_->class_ppt[e.cls], (H->Pd + kGroupSizes[e.cls] - 1) / kGroupSizes[e.cls]);
+            d.scratch_off16 = (int)(scratch_bytes / 16);
+            scratch_bytes += ((size_t)H->list_cap * 4 + 15) & ~(size_t)15;
+            if (scratch_bytes / 16 > 0x7fffffffull) throw std::runtime_error("neighbour-list scratch exceeds 32 GB");
         }
         impl_->class_envs[e.cls].push_back(i);
         // work estimate of one substep (spring passes, point passes, corner items): environments of similar cost
@@ -703,9 +746,23 @@ void Batch::finalize() {
     CUDA_CHECK(cudaMalloc(&d_unstable_, n));
     CUDA_CHECK(cudaMalloc(&d_time_, sizeof(int) * n));
     CUDA_CHECK(cudaMalloc(&d_err_, sizeof(int) * n));
+    cudaFree(impl_->d_scratch); impl_->d_scratch = nullptr;
+    cudaFree(impl_->d_cf); impl_->d_cf = nullptr;
+    CUDA_CHECK(cudaMalloc(&impl_->d_scratch, scratch_bytes + 16));
+    // dynamic shared-memory limits of the kernels this batch launches, on this batch's device
+    for (int c = 0; c < kNumClasses; c++) {
+        if (impl_->class_envs[c].empty()) continue;
+        if (c == 0) {
+            if (impl_->wepc == 8) configure_wstep<MEVO_WCAPS_A, 8, 2>();
+            else if (impl_->wepc == 4) configure_wstep<MEVO_WCAPS_A, 4, 4>();
+            else configure_wstep<MEVO_WCAPS_A, 16, 1>();
+        } else if (c == 1) configure_wstep<MEVO_WCAPS_C, 12, 1>();
+        else if (c == 2) configure_wstep<MEVO_WCAPS_B, 10, 1>();
+        else gstep_dispatch(c, impl_->class_ppt[c], impl_->gvariant[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
+    }
     if (!d_events_) { CUDA_CHECK(cudaMalloc(&d_events_, sizeof(unsigned long long))); CUDA_CHECK(cudaMemset(d_events_, 0, sizeof(unsigned long long))); }
     d_act_ext_ = nullptr;
-    device_bytes_ = all_design.size() + all_static.size() + 2 * sizeof(double) * state_doubles +
+    device_bytes_ = all_design.size() + all_static.size() + scratch_bytes + 2 * sizeof(double) * state_doubles +
                     sizeof(double) * (size_t)n * act_stride_ + sizeof(EnvDesc) * n + 10 * (size_t)n;
     CUDA_CHECK(cudaMemcpy(d_design_, all_design.data(), all_design.size(), cudaMemcpyHostToDevice));
     if (!all_static.empty()) CUDA_CHECK(cudaMemcpy(d_static_, all_static.data(), all_static.size(), cudaMemcpyHostToDevice));
@@ -732,6 +789,7 @@ void Batch::finalize() {
     impl_->time_host.assign(n, 0);
     impl_->com_obj = -1;
     if (cand_cap_ > 0) enable_candidate_dump(cand_cap_);
+    if (force_dump_) enable_force_dump();
 
     // state + reset snapshot
     const bool first = impl_->pos0.empty();
@@ -1010,6 +1068,8 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.dbg_cand = d_cand_;
     prm.dbg_cand_n = d_cand_n_;
     prm.dbg_cand_cap = cand_cap_;
+    prm.dbg_cf = impl_->d_cf;
+    prm.scratch = impl_->d_scratch;
     cudaStream_t main_st = (cudaStream_t)stream_;
     stats_.launches = 0;
     int n_used = 0;
@@ -1033,7 +1093,6 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         }
         prm.class_envs = d_class_envs_ + impl_->class_off[c];
         prm.n_class_envs = n;
-        prm.smem_per_env = impl_->class_smem[c];
         switch (c) {
             case 0:
                 // default: one 16-warp CTA per SM (all warps of an SM in the same code region)
@@ -1043,20 +1102,7 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 break;
             case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            case 3: {
-                // largest environments-per-CTA <= the configured one that fits in shared memory
-                const int want = impl_->epc32, sz = prm.smem_per_env;
-                if (want >= 12 && 12 * sz <= kMaxSmemPerBlock) launch_step<32, 12>(prm, sz, st);
-                else if (want >= 6 && 6 * sz <= kMaxSmemPerBlock) launch_step<32, 6>(prm, sz, st);
-                else if (want >= 4 && 4 * sz <= kMaxSmemPerBlock) launch_step<32, 4>(prm, sz, st);
-                else if (want >= 2 && 2 * sz <= kMaxSmemPerBlock) launch_step<32, 2>(prm, sz, st);
-                else launch_step<32, 1>(prm, sz, st);
-                break;
-            }
-            case 4: launch_step<64, 1>(prm, prm.smem_per_env, st); break;
-            case 5: launch_step<128, 1>(prm, prm.smem_per_env, st); break;
-            case 6: launch_step<256, 1>(prm, prm.smem_per_env, st); break;
-            default: launch_step<512, 1>(prm, prm.smem_per_env, st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c], impl_->gvariant[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
         }
         CUDA_CHECK(cudaGetLastError());
         stats_.launches++;
@@ -1289,6 +1335,32 @@ void Batch::enable_candidate_dump(int cap_per_env) {
     CUDA_CHECK(cudaMalloc(&d_cand_, sizeof(unsigned int) * (size_t)cap_per_env * num_envs()));
     CUDA_CHECK(cudaMalloc(&d_cand_n_, sizeof(int) * num_envs()));
     CUDA_CHECK(cudaMemset(d_cand_n_, 0, sizeof(int) * num_envs()));
+}
+
+void Batch::enable_force_dump() {
+    CUDA_CHECK(cudaSetDevice(device_));
+    force_dump_ = true;
+    if (!d_state_) return;                          // not finalized yet: finalize() allocates it
+    cudaFree(impl_->d_cf); impl_->d_cf = nullptr;
+    CUDA_CHECK(cudaMalloc(&impl_->d_cf, sizeof(double) * (state_doubles_ + 2)));
+    CUDA_CHECK(cudaMemset(impl_->d_cf, 0, sizeof(double) * (state_doubles_ + 2)));
+}
+
+void Batch::read_collision_forces(int env, double* out) {
+    // collision_forces (PhysicsEngine.cpp:715-751) after the collision phase of the first substep of the last step call, global
+    // numbering; points of pruned all-FIXED objects read 0 (the engine never accumulates forces on points that cannot move)
+    if (!impl_->d_cf) throw std::runtime_error("read_collision_forces: enable_force_dump() first");
+    CUDA_CHECK(cudaSetDevice(device_));
+    sync();
+    const EnvHost& e = envs_.at(env);
+    const int Pd = (int)e.dyn_points.size();
+    std::vector<double> cfv(2 * (size_t)Pd);
+    if (Pd) CUDA_CHECK(cudaMemcpy(cfv.data(), impl_->d_cf + e.state_off, sizeof(double) * cfv.size(), cudaMemcpyDeviceToHost));
+    std::fill(out, out + e.pos.size(), 0.0);
+    for (int k = 0; k < Pd; k++) {
+        out[2 * e.dyn_points[k]] = cfv[2 * k];
+        out[2 * e.dyn_points[k] + 1] = cfv[2 * k + 1];
+    }
 }
 
 void Batch::leaf_info(int env, int dynamic, int leaf, int* obj, int* boxel) const {

@@ -156,6 +156,9 @@ public:
     void enable_candidate_dump(int cap_per_env);
     int read_candidates(int env, int* out_pairs /* cap x 4: kind_a, leaf_a, kind_b, leaf_b */, int cap);
     int error_flags(int env);
+    // collision_forces of the first substep of subsequent step calls (PhysicsEngine.cpp:715-751), (P, 2) in global numbering
+    void enable_force_dump();
+    void read_collision_forces(int env, double* out_2P);
     void leaf_info(int env, int dynamic, int leaf, int* obj, int* boxel) const;
 
     StepStats last_stats() const { return stats_; }
@@ -208,6 +211,7 @@ private:
     Task* task_ = nullptr;
     Sight* sight_ = nullptr;
     int finalize_epoch_ = 0;
+    bool force_dump_ = false;
 };
 
 // transform_to_modular_obs (evogym/envs/base.py:427-466), host only: corner indices per cell (h*w*4: TL,TR,BL,BR), returns loc_idx

@@ -1,0 +1,855 @@
+// Group-per-environment step kernel for everything larger than the warp kernel's capacity classes: 7x7 ... 20x20 robots,
+// simulated (non-FIXED) terrain, several free objects -- BASELINE.json configs[3] and configs[4].
+//
+// One CTA of G = 64 ... 512 threads owns one environment for a whole launch (n_steps x 30 substeps of
+// Sim::step, reference SimulatorCPP/Sim.cpp:105-115 -> Environment::step, Environment.cpp:166-205).  Same arithmetic,
+// statement for statement, as wstep_kernel (wkernel.cuh); the exactness contract is in kernels.cuh / DESIGN.md.
+//
+// What bounds this path on B200 (ncu, profiles/r01h_step512_*): not HBM (the state is on chip) and not the FP64 pipe
+// (11 % busy) but a long chain of short dependent phases separated by CTA barriers, run by too few warps to hide their
+// latency.  The layout below is built around that:
+//   * shared memory holds only what is gathered across threads (positions, stage positions, velocities, contact forces,
+//     true velocities, per-edge forces, length_eq, boxes) plus compact tables (one u32 per edge, one 16-byte gather
+//     record per point, 8 bytes per leaf): a 20x20 robot needs ~100 KB instead of 187 KB, so TWO environments are
+//     resident per SM and one's serial phases (ordered rigid-cell pass, contact rounds) overlap the other's parallel ones;
+//     RK4 accumulators and stage velocities live in registers of the thread that owns the point, length_eq_goal stays in
+//     the state block in HBM (read once per substep, written once per launch);
+//   * broad phase by temporal coherence: the all-pairs leaf table (23 k pairs on a 20x20 robot) is scanned once per
+//     launch -- and again only when points have moved more than half the margin since -- into a per-warp neighbour list
+//     of the pairs whose boxes are within kListMargin of each other; every substep tests only the listed pairs exactly.
+//     The candidate SET is still exactly "all leaf pairs whose boxes overlap" (the list is a superset by construction, the
+//     displacement bound is checked every substep), which is what the reference's tree descent produces;
+//   * candidate and survivor buffers are drained in rounds: no configuration can overflow them;
+//   * contacts are applied by all threads at once, in rounds: a contact is applied when it is the lowest-numbered
+//     unapplied contact on each of its points, so every point still receives its contacts in list order (deterministic,
+//     same sums as a serial walk) without one barrier per warp;
+//   * U edges per thread in flight in the spring / limiter passes (independent sqrt / div chains);
+//   * CTA-wide flags travel on barriers that exist anyway (cta_or: three rotating slots, one barrier per use): a
+//     contact-free substep of a robot inside its strain limits takes 12 barriers.
+#pragma once
+
+#include "kernels.cuh"
+
+namespace mevo {
+
+constexpr double kListMargin = 0.03;     // neighbour-list margin [m]; a voxel is 0.1
+constexpr double kListSlack = 1e-6;      // >> rounding of the box arithmetic (positions are O(10), ulp ~ 1e-15)
+constexpr int kGMiscInts = 96;
+// misc words: [0..7] self-collision counts per object (a-12), [8..10] rotating slots of cta_or, [12..13] largest point
+// displacement of a substep (high word of the double, by substep parity), [16..31] per-warp neighbour-list lengths
+// (-1: list overflowed, this warp scans its table range), [32..63] per-warp survivor counts (two round parities),
+// [64] candidate-dump cursor
+constexpr int kGmSelf = 0, kGmOr = 8, kGmDisp = 12, kGmList = 16, kGmSurv = 32, kGmDump = 64;
+
+constexpr int kEidxBShift = 10, kEidxTypeShift10 = 20, kEidxRigidBit10 = 26;
+
+struct GHdr {                                 // first 256 bytes of the CTA's shared memory
+    int Pd, Ed, n_leaf, n_pairs, n_items, n_rlev, n_obj, seg_cap;
+    int lseg_cap, gx0, gy0, gw, gh, env, pad1, pad2;
+    int o_pos, o_spos, o_vel, o_cf, o_vt, o_ef, o_leq, o_aabb;
+    int o_csr, o_etab, o_eidx, o_lpt, o_claim, o_cand, o_surv, o_misc;
+    const int16_t* st_grid;
+    const double4* st_aabb;
+    const double2* st_pos;
+    const LeafRec* st_leaf;
+    const LeafRec* g_leaf;                    // full dynamic leaf records (resolver only)
+    const double2* g_last;                    // pos_last in HBM: read in the first substep of a launch only
+    const unsigned int* pairs;
+    const unsigned int* items;
+    const uint16_t* rlev;
+    const uint16_t* rvis;
+    const ObjRec* objs;
+    const double* ggoal;                      // length_eq_goal of this environment (state block)
+    unsigned int* list;                       // neighbour list scratch of this environment
+    double* gstate;                           // state block of this environment
+    const double* gstate0;                    // its reset snapshot
+};
+static_assert(sizeof(GHdr) <= 256, "GHdr must fit its 256-byte slot");
+
+struct GLayout {
+    int o_pos, o_spos, o_vel, o_cf, o_vt, o_ef, o_leq, o_aabb, o_csr, o_etab, o_eidx, o_lpt, o_claim, o_cand, o_surv, o_misc, total;
+};
+
+MEVO_HD GLayout g_layout(int Pd, int Ed, int n_leaf, int n_types, int cand_cap) {
+    GLayout L;
+    int o = 256;
+    L.o_pos = o;   o += 16 * Pd;
+    L.o_spos = o;  o += 16 * Pd;
+    L.o_vel = o;   o += 16 * Pd;
+    L.o_cf = o;    o += 16 * Pd;
+    L.o_vt = o;    o += 16 * Pd;
+    L.o_ef = o;    o += 16 * (Ed + 1);              // [Ed] stays zero: empty gather slots point at it
+    L.o_leq = o;   o += align16(8 * Ed);
+    L.o_aabb = o;  o += 32 * n_leaf;
+    L.o_csr = o;   o += 16 * Pd;
+    L.o_etab = o;  o += 16 * n_types;
+    L.o_eidx = o;  o += align16(4 * Ed);
+    L.o_lpt = o;   o += align16(8 * n_leaf);
+    L.o_claim = o; o += align16(4 * Pd);
+    L.o_cand = o;  o += align16(4 * cand_cap);
+    L.o_surv = o;  o += align16(4 * cand_cap);
+    L.o_misc = o;  o += 4 * kGMiscInts;
+    L.total = align16(o);
+    return L;
+}
+
+extern __shared__ __align__(16) unsigned char gsm_raw[];
+
+// CTA-wide OR of a per-thread bit mask on ONE barrier.  Three slots rotate with the (uniform) call counter r: call r
+// ORs into slot r % 3 and clears slot (r + 1) % 3, which was last read after the barrier of call r - 2 -- and every thread
+// has passed the barrier of call r - 1 since.  Whatever else the caller published to shared memory before the call is
+// visible after it.
+__device__ __forceinline__ int cta_or(volatile int* slots, int bits, int& r) {
+    const int s = r % 3;
+    const unsigned w = __reduce_or_sync(0xffffffffu, (unsigned)bits);
+    if ((threadIdx.x & 31) == 0 && w) atomicOr((int*)&slots[s], (int)w);
+    if (threadIdx.x == 0) slots[(s + 1) % 3] = 0;
+    __syncthreads();
+    r++;
+    return slots[s];
+}
+
+// BoundingBox::in (main.h:64-72) with box a grown by m on every side
+__device__ __forceinline__ bool aabb_overlap_margin(const double4& a, const double4& b, double m) {
+    return !(a.x - m > b.z) & !(a.z + m < b.x) & !(a.y - m > b.w) & !(a.w + m < b.y);
+}
+
+__device__ __forceinline__ double2 spring_force10(const double2* sp, uint32_t ix, double k, double& q, bool first_stage) {
+    const double2 pa = sp[ix & 0x3ff], pb = sp[(ix >> kEidxBShift) & 0x3ff];
+    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+    const double dist = sqrt(dx * dx + dy * dy);
+    if (first_stage) {                                  // PhysicsEngine::update_actuators (PhysicsEngine.cpp:99-119)
+        const double add = (q - dist) * 0.006;
+        q = dist + add;
+    }
+    const double mag = (dist - q) * k / dist;           // PhysicsEngine.cpp:498-528
+    return make_double2(dx * mag, dy * mag);
+}
+
+__device__ __forceinline__ double flip_if(double x, unsigned neg) {      // neg ? -x : x, on the integer pipe (exact)
+    return __hiloint2double(__double2hiint(x) ^ (int)(neg << 31), __double2loint(x));
+}
+
+#ifdef MEVO_PROF
+__device__ unsigned long long g_g2prof[8];      // [0] collide [1] rk4 [2] constrain, cycles of thread 0 of every CTA
+#endif
+
+// =================================================================================== phase 1: collisions
+// K2a leaf boxes, neighbour list upkeep, K2b broad phase, K3 narrow phase + contact response, K6 unstable count
+// (SURVEY 8a-4,5,6,12).  Returns (r << 1) | unstable, unstable as PhysicsEngine::is_any_robot_self_colliding
+// (boxes of the START of the substep).
+// (MINB is part of every phase's signature only so that each build of the kernel gets its own copy, compiled to its own
+// register budget: ptxas compiles a shared out-of-line function once, to the tightest budget of its callers.)
+template <int G, int MINB>
+__device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row, int* dbg_n, int dbg_cap, double2* dbg_cf) {
+    constexpr int NW = G / 32;
+    unsigned char* sm = gsm_raw;
+    const GHdr* H = reinterpret_cast<const GHdr*>(sm);
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const double2* pos = reinterpret_cast<const double2*>(sm + H->o_pos);
+    const double2* vt = reinterpret_cast<const double2*>(sm + H->o_vt);
+    double2* cf = reinterpret_cast<double2*>(sm + H->o_cf);
+    double4* aabb = reinterpret_cast<double4*>(sm + H->o_aabb);
+    const uint2* lpt = reinterpret_cast<const uint2*>(sm + H->o_lpt);
+    int* claim = reinterpret_cast<int*>(sm + H->o_claim);
+    volatile int* misc = reinterpret_cast<volatile int*>(sm + H->o_misc);
+    const int Pd = H->Pd, n_leaf = H->n_leaf, n_pairs = H->n_pairs, n_items = H->n_items, seg_cap = H->seg_cap;
+    unsigned int* cand = reinterpret_cast<unsigned int*>(sm + H->o_cand) + warp * seg_cap;
+    unsigned int* surv_all = reinterpret_cast<unsigned int*>(sm + H->o_surv);
+    unsigned int* surv = surv_all + warp * seg_cap;
+
+    // ---- K2a: leaf boxes (a-4), zero collision_forces
+    for (int l = t; l < n_leaf; l += G) {
+        const uint2 lp = lpt[l];
+        double2 q = pos[lp.x & 0xffffu];
+        double minx = q.x, maxx = q.x, miny = q.y, maxy = q.y;
+        q = pos[lp.x >> 16];
+        minx = fmin(minx, q.x); maxx = fmax(maxx, q.x); miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
+        q = pos[lp.y & 0xffffu];
+        minx = fmin(minx, q.x); maxx = fmax(maxx, q.x); miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
+        q = pos[lp.y >> 16];
+        minx = fmin(minx, q.x); maxx = fmax(maxx, q.x); miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
+        aabb[l] = make_double4(minx, miny, maxx, maxy);
+    }
+    for (int i = t; i < Pd; i += G) cf[i] = make_double2(0.0, 0.0);
+    if (t < 8) misc[kGmSelf + t] = 0;
+    __syncthreads();
+
+    // ---- neighbour list of this warp's range of the pair table (see the header comment)
+    const int R = ((n_pairs + NW * 32 - 1) / (NW * 32)) * 32;
+    const int p0 = min(n_pairs, warp * R), p1 = min(n_pairs, p0 + R);
+    const unsigned int* pairs = H->pairs;
+    unsigned int* lseg = H->list + (size_t)warp * H->lseg_cap;
+    if (rebuild) {
+        int lcnt = 0;
+        bool ok = true;
+        for (int base = p0; base < p1; base += 64) {                     // two pairs per lane in flight
+            const int i0 = base + lane, i1 = i0 + 32;
+            const unsigned c0 = __ldg(pairs + (i0 < p1 ? i0 : base)), c1 = __ldg(pairs + (i1 < p1 ? i1 : base));
+            const bool h0 = (i0 < p1) & aabb_overlap_margin(aabb[c0 & kCodeLeafMask], aabb[(c0 >> 12) & kCodeLeafMask], kListMargin);
+            const bool h1 = (i1 < p1) & aabb_overlap_margin(aabb[c1 & kCodeLeafMask], aabb[(c1 >> 12) & kCodeLeafMask], kListMargin);
+            const unsigned m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+            if (m0 | m1) {
+                const int n0 = __popc(m0), at0 = lcnt + __popc(m0 & ((1u << lane) - 1u)), at1 = lcnt + n0 + __popc(m1 & ((1u << lane) - 1u));
+                if (lcnt + n0 + __popc(m1) <= H->lseg_cap) {
+                    if (h0) lseg[at0] = c0;
+                    if (h1) lseg[at1] = c1;
+                    lcnt += n0 + __popc(m1);
+                } else {
+                    ok = false;
+                }
+            }
+        }
+        if (lane == 0) misc[kGmList + warp] = ok ? lcnt : -1;
+        __syncwarp();                                                    // list entries are read by other lanes of this warp
+    }
+    const int lcnt = misc[kGmList + warp];
+    const unsigned int* psrc = lcnt >= 0 ? lseg : pairs + p0;             // overflowed list: the table range itself, every substep
+    const int pn = lcnt >= 0 ? lcnt : p1 - p0;
+
+    // ---- K2b + K3 in rounds: produce candidates into this warp's segment, filter their corners into survivors, resolve
+    const int gw = H->gw;
+    int pi = 0;                                   // cursor in psrc
+    int sc = warp, sit = 0, max_cells = -1;       // terrain: leaf chunk (leaves sc * 32 + lane), cell iteration
+    int cx0 = 0, cy0 = 0, wx = 1, n_cells = 0;
+    double4 mybb = make_double4(0, 0, 0, 0);
+    int next_ic = warp;                           // always-candidate items: next 32-wide chunk of this warp
+    int rc = 0;                                   // survivor round counter (uniform)
+    int flags;
+    do {
+        int cnt = 0;
+        while (pi < pn && cnt + 64 <= seg_cap) {                          // two pairs per lane in flight
+            const int i0 = pi + lane, i1 = i0 + 32;
+            const unsigned c0 = psrc[i0 < pn ? i0 : pi], c1 = psrc[i1 < pn ? i1 : pi];
+            pi += 64;
+            const unsigned a0 = c0 & kCodeLeafMask, b0 = (c0 >> 12) & kCodeLeafMask, a1 = c1 & kCodeLeafMask, b1 = (c1 >> 12) & kCodeLeafMask;
+            const bool h0 = (i0 < pn) & aabb_overlap(aabb[a0], aabb[b0]);
+            const bool h1 = (i1 < pn) & aabb_overlap(aabb[a1], aabb[b1]);
+            const unsigned m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+            if (m0 | m1) {
+                // ordered pairs (a,b) and (b,a) both count (a-12, PhysicsEngine.cpp:842-889)
+                if (h0 && (c0 & kCodeCount)) atomicAdd((int*)&misc[kGmSelf + (c0 >> kCodeObjShift)], 2);
+                if (h1 && (c1 & kCodeCount)) atomicAdd((int*)&misc[kGmSelf + (c1 >> kCodeObjShift)], 2);
+                if (h0) cand[cnt + __popc(m0 & ((1u << lane) - 1u))] = c0 & (kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj);
+                cnt += __popc(m0);
+                if (h1) cand[cnt + __popc(m1 & ((1u << lane) - 1u))] = c1 & (kCodeLeafMask | (kCodeLeafMask << 12) | kCodeSameObj);
+                cnt += __popc(m1);
+            }
+        }
+        if (pi >= pn && gw > 0) {
+            // dynamic leaves vs the static voxel grid (cell = one voxel): window widened by 1e-6 cells, exact test decides
+            while (sc * 32 < n_leaf) {
+                if (max_cells < 0) {
+                    const int l = sc * 32 + lane;
+                    n_cells = 0; wx = 1;
+                    if (l < n_leaf) {
+                        mybb = aabb[l];
+                        cx0 = max((int)ceil(mybb.x * 10.0 - 1.000001) - H->gx0, 0);
+                        const int cx1 = min((int)floor(mybb.z * 10.0 + 0.000001) - H->gx0, gw - 1);
+                        cy0 = max((int)ceil(mybb.y * 10.0 - 1.000001) - H->gy0, 0);
+                        const int cy1 = min((int)floor(mybb.w * 10.0 + 0.000001) - H->gy0, H->gh - 1);
+                        wx = cx1 - cx0 + 1;
+                        const int wy = cy1 - cy0 + 1;
+                        n_cells = (wx > 0 && wy > 0) ? wx * wy : 0;
+                        if (n_cells == 0) wx = 1;
+                    }
+                    max_cells = __reduce_max_sync(0xffffffffu, n_cells);
+                    sit = 0;
+                }
+                while (sit < max_cells && cnt + 32 <= seg_cap) {
+                    const int it = sit++;
+                    bool hit = false;
+                    unsigned int code = 0;
+                    if (it < n_cells) {
+                        const int cx = cx0 + it % wx, cy = cy0 + it / wx;
+                        const int sl = __ldg(H->st_grid + cy * gw + cx);
+                        if (sl >= 0) {
+                            hit = aabb_overlap(mybb, ldg_d4(H->st_aabb + sl));
+                            code = (unsigned)(sc * 32 + lane) | ((unsigned)sl << 12) | kCodeStatic;
+                        }
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
+                    cnt += __popc(m);
+                }
+                if (sit < max_cells) break;                               // segment full: next round
+                sc += NW; max_cells = -1;
+            }
+        }
+        const bool prod_done = pi >= pn && (gw <= 0 || sc * 32 >= n_leaf);
+        __syncwarp();
+        if (dbg_row) {                                                    // test hook: candidate SET of this substep
+            int off = 0;
+            if (lane == 0) off = atomicAdd((int*)&misc[kGmDump], cnt);
+            off = __shfl_sync(0xffffffffu, off, 0);
+            for (int i = lane; i < cnt; i += 32)
+                if (off + i < dbg_cap) dbg_row[off + i] = cand[i];
+        }
+        // ---- consume: box prefilter of every (corner, boxel) item -- a necessary condition of Boxel::point_in_boxel --
+        //      into this warp's survivor segment, in rounds
+        int next_cc = 0;
+        do {
+            int scnt = 0;
+            // non-shared corners of leaf pairs that share a point (always candidates), two chunks in flight
+            while (next_ic * 32 < n_items && scnt + 64 <= seg_cap) {
+                const int i0 = next_ic * 32 + lane, i1 = i0 + NW * 32;
+                next_ic += 2 * NW;
+                const unsigned ic0 = __ldg(H->items + (i0 < n_items ? i0 : 0)), ic1 = __ldg(H->items + (i1 < n_items ? i1 : 0));
+                const unsigned cr0 = (ic0 >> kItemCornerShift) & 3u, cr1 = (ic1 >> kItemCornerShift) & 3u;
+                const uint2 l0 = lpt[ic0 & kCodeLeafMask], l1 = lpt[ic1 & kCodeLeafMask];
+                const unsigned q0 = ((cr0 & 2u) ? l0.y : l0.x) >> ((cr0 & 1u) * 16) & 0xffffu;
+                const unsigned q1 = ((cr1 & 2u) ? l1.y : l1.x) >> ((cr1 & 1u) * 16) & 0xffffu;
+                const bool h0 = (i0 < n_items) & point_in_box(pos[q0], aabb[(ic0 >> 12) & kCodeLeafMask]);
+                const bool h1 = (i1 < n_items) & point_in_box(pos[q1], aabb[(ic1 >> 12) & kCodeLeafMask]);
+                const unsigned m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+                if (m0 | m1) {
+                    if (h0) surv[scnt + __popc(m0 & ((1u << lane) - 1u))] = ic0;
+                    scnt += __popc(m0);
+                    if (h1) surv[scnt + __popc(m1 & ((1u << lane) - 1u))] = ic1;
+                    scnt += __popc(m1);
+                }
+            }
+            const bool items_done = next_ic * 32 >= n_items;
+            if (items_done) {
+                // ... then the 8 corners of each candidate pair of this round (these pairs share no point)
+                while (next_cc * 32 < cnt * 8 && scnt + 32 <= seg_cap) {
+                    const int i = next_cc * 32 + lane;
+                    next_cc++;
+                    bool hit = false;
+                    unsigned int code = 0;
+                    if (i < cnt * 8) {
+                        const unsigned int cc = cand[i >> 3];
+                        const unsigned a = cc & kCodeLeafMask, b = (cc >> 12) & kCodeLeafMask;
+                        const bool b_static = (cc & kCodeStatic) != 0;
+                        const unsigned dir = (i >> 2) & 1, corner = i & 3;
+                        const unsigned same = (cc & kCodeSameObj) ? kItemSameObj : 0u;
+                        if (dir == 0) {
+                            code = a | (b << 12) | (corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
+                            const double4 bb = b_static ? ldg_d4(H->st_aabb + b) : aabb[b];
+                            const uint2 la = lpt[a];
+                            hit = point_in_box(pos[((corner & 2u) ? la.y : la.x) >> ((corner & 1u) * 16) & 0xffffu], bb);
+                        } else {
+                            code = b | (a << 12) | (corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
+                            double2 pp;
+                            if (b_static) {
+                                pp = __ldg(H->st_pos + __ldg(&H->st_leaf[b].pt[corner]));
+                            } else {
+                                const uint2 lb = lpt[b];
+                                pp = pos[((corner & 2u) ? lb.y : lb.x) >> ((corner & 1u) * 16) & 0xffffu];
+                            }
+                            hit = point_in_box(pp, aabb[a]);
+                        }
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (hit) surv[scnt + __popc(m & ((1u << lane) - 1u))] = code;
+                    scnt += __popc(m);
+                }
+            }
+            const bool cons_done = items_done && next_cc * 32 >= cnt * 8;
+            volatile int* scount = misc + kGmSurv + (rc & 1) * 16;         // two parities: a fast warp may start the next round
+            if (lane == 0) scount[warp] = scnt;
+            flags = cta_or(misc + kGmOr, (cons_done ? 0 : 1) | (prod_done ? 0 : 2), r);
+            rc++;
+            int n_surv = 0;
+#pragma unroll
+            for (int w = 0; w < NW; w++) n_surv += scount[w];
+            if (n_surv > 0) {
+                // ---- K3b: resolve survivors, apply their contacts (a-5, a-6)
+                PointSrc src;
+                src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = H->st_pos;
+                for (int base = 0; base < n_surv; base += G) {
+                    const int gi = base + t;
+                    bool pending = false;
+                    Contact c;
+                    int reps = 1;
+                    if (gi < n_surv) {
+                        int i = gi, w = 0;
+                        while (i >= scount[w]) { i -= scount[w]; w++; }
+                        const unsigned code = surv_all[w * seg_cap + i];
+                        const bool m_static = (code & kItemMainStatic) != 0, r_static = (code & kItemRefStatic) != 0;
+                        reps = (code & kItemSameObj) ? 2 : 1;
+                        LeafRegs lm, lr;
+                        load_leaf(lm, H->g_leaf, H->st_leaf, code & kCodeLeafMask, m_static);
+                        load_leaf(lr, H->g_leaf, H->st_leaf, (code >> 12) & kCodeLeafMask, r_static);
+                        pending = resolve_point_vs_boxel(src, lm, m_static, lr, r_static, (code >> kItemCornerShift) & 3, c);
+                    }
+                    // Contacts are applied in rounds: the lowest-numbered unapplied contact on each of its points goes
+                    // first, so every point receives its contacts in list order -- the sums of a serial walk of the list.
+                    while (cta_or(misc + kGmOr, pending ? 1 : 0, r)) {
+                        if (pending) {
+                            if (!c.p_static) atomicMin(&claim[c.p], gi);
+                            if (!c.ab_static) { atomicMin(&claim[c.a], gi); atomicMin(&claim[c.b], gi); }
+                        }
+                        __syncthreads();
+                        if (pending) {
+                            const bool mine = (c.p_static || claim[c.p] == gi) && (c.ab_static || (claim[c.a] == gi && claim[c.b] == gi));
+                            if (mine) {
+                                apply_contact(cf, c, reps);
+                                if (!c.p_static) claim[c.p] = 0x7fffffff;
+                                if (!c.ab_static) { claim[c.a] = 0x7fffffff; claim[c.b] = 0x7fffffff; }
+                                pending = false;
+                            }
+                        }
+                    }
+                }
+            }
+        } while (flags & 1);
+    } while (flags & 2);
+
+    if (dbg_row && t == 0) { *dbg_n = misc[kGmDump]; misc[kGmDump] = 0; }
+    if (dbg_cf)
+        for (int i = t; i < Pd; i += G) dbg_cf[i] = cf[i];
+    // K6a: unstable test uses the boxes of the START of this substep (a-12)
+    int sub_unstable = 0;
+    for (int o = 0; o < H->n_obj; o++) {
+        const ObjRec orc = H->objs[o];
+        if (orc.is_robot && misc[kGmSelf + o] > (int)orc.n_surface) sub_unstable = 1;
+    }
+    return (r << 1) | sub_unstable;
+}
+
+// =================================================================================== phase 2: actuators + RK4
+// PhysicsEngine::update_actuators + step_rk4 + get_pos_vel_slope (SURVEY 8a-7,8,9).  On return spos holds the new
+// positions (pos still holds the substep's start positions = pos_last) and vel the new velocities.
+template <int G, int MINB, int PPT>
+__device__ __noinline__ void g_rk4(unsigned fixmask) {
+    constexpr int U = (G == 128) ? 4 : 3;            // edges per thread in flight: independent sqrt / div chains
+    unsigned char* sm = gsm_raw;
+    const GHdr* H = reinterpret_cast<const GHdr*>(sm);
+    const int t = threadIdx.x;
+    const double2* pos = reinterpret_cast<const double2*>(sm + H->o_pos);
+    double2* spos = reinterpret_cast<double2*>(sm + H->o_spos);
+    double2* vel = reinterpret_cast<double2*>(sm + H->o_vel);
+    const double2* cf = reinterpret_cast<const double2*>(sm + H->o_cf);
+    double2* ef = reinterpret_cast<double2*>(sm + H->o_ef);
+    double* leq = reinterpret_cast<double*>(sm + H->o_leq);
+    const uint4* csr = reinterpret_cast<const uint4*>(sm + H->o_csr);
+    const double2* etab = reinterpret_cast<const double2*>(sm + H->o_etab);
+    const uint32_t* eidx = reinterpret_cast<const uint32_t*>(sm + H->o_eidx);
+    const double* ggoal = H->ggoal;
+    const int Pd = H->Pd, Ed = H->Ed;
+    double2 sv[PPT], ap[PPT], av[PPT];               // stage velocity and RK4 accumulators of this thread's points
+#pragma unroll
+    for (int k = 0; k < PPT; k++) { sv[k] = make_double2(0, 0); ap[k] = sv[k]; av[k] = sv[k]; }
+
+#pragma unroll 1
+    for (int s = 0; s < 4; s++) {
+        const double2* sp = (s == 0) ? pos : spos;
+        for (int base = 0; base < Ed; base += U * G) {
+            int e[U];
+            uint32_t ix[U];
+            double q[U];
+            double2 f[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                e[u] = base + u * G + t;
+                const int c = e[u] < Ed ? e[u] : Ed - 1;            // threads past the end recompute a valid edge, store nothing
+                ix[u] = eidx[c];
+                q[u] = (s == 0) ? ggoal[c] : leq[c];                 // stage 0: length_eq_goal in, relaxed length_eq out
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) f[u] = spring_force10(sp, ix[u], etab[(ix[u] >> kEidxTypeShift10) & 63].x, q[u], s == 0);
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (e[u] < Ed) {
+                    ef[e[u]] = f[u];
+                    if (s == 0) leq[e[u]] = q[u];
+                }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int p = t + k * G;
+            if (p < Pd) {
+                const double2 v = (s == 0) ? vel[p] : sv[k];
+                double Fx = 0.0, Fy = 0.0;
+                {
+                    // F -= f over the a sides in edge order, then F += f over the b sides (PhysicsEngine.cpp:530-531): the
+                    // record lists (edge << 1 | side) in that order; empty slots point at the all-zero entry ef[Ed]
+                    const uint4 rec = csr[p];
+                    const unsigned w[4] = {rec.x, rec.y, rec.z, rec.w};
+#pragma unroll
+                    for (int half = 0; half < 2; half++) {
+                        double2 g[4];
+                        unsigned sg[4];
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const int qd = 4 * half + j;
+                            const unsigned ent = (w[qd >> 1] >> ((qd & 1) * 16)) & 0xffffu;
+                            g[j] = ef[ent >> 1];
+                            sg[j] = (ent & 1u) ^ 1u;                    // a side: subtract
+                        }
+#pragma unroll
+                        for (int j = 0; j < 4; j++) { Fx += flip_if(g[j].x, sg[j]); Fy += flip_if(g[j].y, sg[j]); }
+                    }
+                }
+                Fx += v.x * (-MEVO_VISCOUS_DRAG);
+                Fy += v.y * (-MEVO_VISCOUS_DRAG);
+                Fy += 1.0 * (-MEVO_GRAVITY);                            // every point mass is 1.0 (host-checked), F / m == F
+                const double2 c = cf[p];
+                Fx += c.x; Fy += c.y;
+                const double y = sp[p].y;
+                if (y < 0) {                                            // analytic ground plane y = 0 (PhysicsEngine.cpp:566-577)
+                    const double normal_force = y * (-MEVO_COLLISION_CONST_GROUND);
+                    Fy += normal_force;
+                    const double friction_temp = tanh(v.x * normal_force * MEVO_DYN_FRICTION);
+                    Fx += (-10 * MEVO_DYN_FRICTION) * (normal_force * friction_temp);
+                }
+                const double kpx = v.x * MEVO_DT, kpy = v.y * MEVO_DT;
+                const double kvx = Fx * MEVO_DT, kvy = Fy * MEVO_DT;
+                const double2 x0 = pos[p], v0 = vel[p];
+                if (s == 0) {
+                    ap[k] = make_double2(kpx, kpy);
+                    av[k] = make_double2(kvx, kvy);
+                    spos[p] = make_double2(x0.x + (kpx * 0.5), x0.y + (kpy * 0.5));
+                    sv[k] = make_double2(v0.x + (kvx * 0.5), v0.y + (kvy * 0.5));
+                } else if (s < 3) {
+                    ap[k].x = ap[k].x + 2 * kpx; ap[k].y = ap[k].y + 2 * kpy;
+                    av[k].x = av[k].x + 2 * kvx; av[k].y = av[k].y + 2 * kvy;
+                    const double h = (s == 1) ? 0.5 : 1.0;              // x * 1.0 == x exactly
+                    spos[p] = make_double2(x0.x + (kpx * h), x0.y + (kpy * h));
+                    sv[k] = make_double2(v0.x + (kvx * h), v0.y + (kvy * h));
+                } else {
+                    double dpx = div_const(ap[k].x + kpx, 6.0), dpy = div_const(ap[k].y + kpy, 6.0);
+                    double dvx = div_const(av[k].x + kvx, 6.0), dvy = div_const(av[k].y + kvy, 6.0);
+                    if ((fixmask >> k) & 1u) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
+                    // the new position goes to spos: pos keeps the substep's start position (= pos_last)
+                    spos[p] = make_double2(x0.x + dpx, x0.y + dpy);
+                    vel[p] = make_double2(v0.x + dvx, v0.y + dvy);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// =================================================================================== phase 3: limiters + true velocity
+// PhysicsEngine::resolve_edge_constraints + update_true_vel (SURVEY 8a-10,11) on the new positions in spos.  Band test on
+// squared lengths (no sqrt), guarded by 1e-7 so the decision never depends on the rounding of dist / L0: inside the band
+// every correction of the reference is exactly zero.  Returns r.
+template <int G, int MINB, int PPT>
+__device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int r, int ss) {
+    constexpr int U = (G == 128) ? 4 : 3;
+    unsigned char* sm = gsm_raw;
+    const GHdr* H = reinterpret_cast<const GHdr*>(sm);
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    double2* pos = reinterpret_cast<double2*>(sm + H->o_pos);
+    double2* spos = reinterpret_cast<double2*>(sm + H->o_spos);
+    double2* vt = reinterpret_cast<double2*>(sm + H->o_vt);
+    double2* ef = reinterpret_cast<double2*>(sm + H->o_ef);
+    const uint4* csr = reinterpret_cast<const uint4*>(sm + H->o_csr);
+    const double2* etab = reinterpret_cast<const double2*>(sm + H->o_etab);
+    const uint32_t* eidx = reinterpret_cast<const uint32_t*>(sm + H->o_eidx);
+    volatile int* misc = reinterpret_cast<volatile int*>(sm + H->o_misc);
+    const int Pd = H->Pd, Ed = H->Ed;
+
+    int viol = 0;
+    for (int base = 0; base < Ed; base += U * G) {
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int e = base + u * G + t;
+            const bool valid = e < Ed;
+            const uint32_t ix = eidx[valid ? e : Ed - 1];
+            const double2 pa = spos[ix & 0x3ff], pb = spos[(ix >> kEidxBShift) & 0x3ff];
+            const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+            const double d2 = dx * dx + dy * dy;
+            const double l0 = etab[(ix >> kEidxTypeShift10) & 63].y;
+            const double l2 = l0 * l0;
+            if (valid && !(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) viol |= 1;
+            if (valid && ((ix >> kEidxRigidBit10) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) viol |= 2;
+        }
+    }
+    viol = cta_or(misc + kGmOr, viol, r);
+    if (viol & 1) {
+        // Jacobi half (PhysicsEngine.cpp:613-671): corrections from the pre-correction positions, summed per point in edge order
+        for (int e = t; e < Ed; e += G) {
+            const uint32_t ix = eidx[e];
+            const double2 pa = spos[ix & 0x3ff], pb = spos[(ix >> kEidxBShift) & 0x3ff];
+            const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+            const double d2 = dx * dx + dy * dy;
+            const double l0 = etab[(ix >> kEidxTypeShift10) & 63].y;
+            const double l2 = l0 * l0;
+            double2 c = make_double2(0.0, 0.0);               // inside the guarded band the correction is exactly zero
+            if (!(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) {
+                const double dist = sqrt(d2);
+                const double over_mag = (dist - l0 * (1 + 0.25)) / (dist * 2);
+                const double under_mag = (dist - l0 * (1 - 0.25)) / (dist * 2);
+                double ox = dx * over_mag, oy = dy * over_mag;
+                double ux = dx * under_mag, uy = dy * under_mag;
+                const double stress = dist / l0;
+                if (!(stress > (1 + 0.25))) { ox = 0.0; oy = 0.0; }
+                if (!(stress < (1 - 0.25))) { ux = 0.0; uy = 0.0; }
+                c = make_double2((ox + ux) * 0.8, (oy + uy) * 0.8);
+            }
+            ef[e] = c;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int p = t + k * G;
+            if (p < Pd && !((fixmask >> k) & 1u)) {           // fixed end points receive "0.0" (PhysicsEngine.cpp:670-671)
+                double2 x = spos[p];
+                const uint4 rec = csr[p];
+                const unsigned w[4] = {rec.x, rec.y, rec.z, rec.w};
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const unsigned ent = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+                    const double2 c = ef[ent >> 1];
+                    const unsigned neg = (ent & 1u) ^ 1u;
+                    x.x += flip_if(c.x, neg); x.y += flip_if(c.y, neg);
+                }
+                spos[p] = x;
+            }
+        }
+        __syncthreads();
+    }
+    if (viol & 2) {
+        // ordered rigid-cell pass (PhysicsEngine.cpp:675-710), scheduled in point-disjoint levels that keep the reference's
+        // order between visits sharing a point; the first warp walks the (narrow) levels with warp-level synchronisation
+        if (warp == 0) {
+            const uint16_t* rlev = H->rlev;
+            const uint16_t* rvis = H->rvis;
+            const int n_rlev = H->n_rlev;
+            for (int lv = 0; lv < n_rlev; lv++) {
+                const int i1 = __ldg(rlev + lv + 1);
+                for (int i = __ldg(rlev + lv) + lane; i < i1; i += 32) {
+                    const uint32_t ix = eidx[__ldg(rvis + i)];
+                    const int a = ix & 0x3ff, b = (ix >> kEidxBShift) & 0x3ff;
+                    double2 pa = spos[a], pb = spos[b];
+                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                    const double d2 = dx * dx + dy * dy;
+                    const double l0 = etab[(ix >> kEidxTypeShift10) & 63].y;
+                    const double l2 = l0 * l0;
+                    if (d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999) continue;     // inside the guarded band: a no-op
+                    const double dist = sqrt(d2);
+                    const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
+                    const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
+                    double ox = dx * over_mag, oy = dy * over_mag;
+                    double ux = dx * under_mag, uy = dy * under_mag;
+                    const double stress = dist / l0;
+                    if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
+                    if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
+                    const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
+                    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
+                    spos[a] = pa; spos[b] = pb;
+                }
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+    }
+    // PhysicsEngine::update_true_vel (:602-607) + largest displacement of this substep (neighbour-list validity)
+    unsigned dmax = 0;
+    if (t == 0) misc[kGmDisp + ((ss + 1) & 1)] = 0;
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        const int p = t + k * G;
+        if (p < Pd) {
+            const double2 x = spos[p], x0 = pos[p];
+            // pos_last == pos at the start of every substep except possibly the first of a launch
+            const double2 l = first_substep ? H->g_last[p] : x0;
+            vt[p] = make_double2(div_const(x.x - l.x, MEVO_DT), div_const(x.y - l.y, MEVO_DT));
+            pos[p] = x;
+            // upper bound of max(|dx|, |dy|) as the high word of the double, + 1 (NaN / inf stay huge: the list is rebuilt)
+            const double d = fmax(fabs(x.x - x0.x), fabs(x.y - x0.y));
+            const unsigned hi = (d == d) ? (unsigned)__double2hiint(d) + 1u : 0x7ff00000u;
+            dmax = max(dmax, hi);
+        }
+    }
+    dmax = __reduce_max_sync(0xffffffffu, dmax);
+    if (lane == 0 && dmax) atomicMax((int*)&misc[kGmDisp + (ss & 1)], (int)dmax);
+    __syncthreads();
+    return r;
+}
+
+// =================================================================================== the kernel
+template <int G, int MINB, int PPT>
+__global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
+    static_assert(G % 32 == 0 && G >= 64 && G <= 512, "group size");
+    unsigned char* sm = gsm_raw;
+    const int t = threadIdx.x;
+    const int env = prm.class_envs[blockIdx.x];
+    const EnvDesc ed = prm.envs[env];
+    const uint8_t* db = prm.design + ed.design_off;
+    const DesignHeader* DH = reinterpret_cast<const DesignHeader*>(db);
+    const int Pd = DH->Pd, Ed = DH->Ed, n_leaf = DH->n_leaf;
+    double* gstate = prm.state + ed.state_off;
+    const GLayout L = g_layout(Pd, Ed, n_leaf, DH->n_types, DH->cand_cap);
+    unsigned fixmask = 0;                               // bit k: point t + k * G is fixed
+
+    // ---------------------------------------------------------------- stage in (once per launch)
+    {
+        if (t == 0) {
+            GHdr* H = reinterpret_cast<GHdr*>(sm);
+            H->Pd = Pd; H->Ed = Ed; H->n_leaf = n_leaf; H->n_pairs = DH->n_pairs; H->n_items = DH->n_items;
+            H->n_rlev = DH->n_rlev; H->n_obj = DH->n_obj;
+            H->seg_cap = DH->cand_cap / (G / 32);
+            H->lseg_cap = DH->list_cap / (G / 32);
+            H->o_pos = L.o_pos; H->o_spos = L.o_spos; H->o_vel = L.o_vel; H->o_cf = L.o_cf; H->o_vt = L.o_vt; H->o_ef = L.o_ef;
+            H->o_leq = L.o_leq; H->o_aabb = L.o_aabb; H->o_csr = L.o_csr; H->o_etab = L.o_etab; H->o_eidx = L.o_eidx;
+            H->o_lpt = L.o_lpt; H->o_claim = L.o_claim; H->o_cand = L.o_cand; H->o_surv = L.o_surv; H->o_misc = L.o_misc;
+            if (ed.static_off != ~0ull) {
+                const uint8_t* sb = prm.statics + ed.static_off;
+                const StaticHeader* SHp = reinterpret_cast<const StaticHeader*>(sb);
+                H->gx0 = SHp->gx0; H->gy0 = SHp->gy0; H->gw = SHp->gw; H->gh = SHp->gh;
+                H->st_grid = reinterpret_cast<const int16_t*>(sb + SHp->o_grid);
+                H->st_aabb = reinterpret_cast<const double4*>(sb + SHp->o_aabb);
+                H->st_pos = reinterpret_cast<const double2*>(sb + SHp->o_pos);
+                H->st_leaf = reinterpret_cast<const LeafRec*>(sb + SHp->o_leaf);
+            } else {
+                H->gx0 = H->gy0 = H->gw = H->gh = 0;
+                H->st_grid = nullptr; H->st_aabb = nullptr; H->st_pos = nullptr; H->st_leaf = nullptr;
+            }
+            H->g_leaf = reinterpret_cast<const LeafRec*>(db + DH->o_leaf);
+            H->g_last = reinterpret_cast<const double2*>(gstate) + 2 * Pd;
+            H->pairs = reinterpret_cast<const unsigned int*>(db + DH->o_pairs);
+            H->items = reinterpret_cast<const unsigned int*>(db + DH->o_items);
+            H->rlev = reinterpret_cast<const uint16_t*>(db + DH->o_rlev);
+            H->rvis = reinterpret_cast<const uint16_t*>(db + DH->o_rvis);
+            H->objs = reinterpret_cast<const ObjRec*>(db + DH->o_obj);
+            H->ggoal = gstate + 8 * (size_t)Pd;
+            H->list = prm.scratch + (size_t)ed.scratch_off16 * 4;
+            H->gstate = gstate;
+            H->gstate0 = prm.state0 + ed.state_off;
+            H->env = env;
+        }
+        const double2* g2 = reinterpret_cast<const double2*>(gstate);
+        double2* pos = reinterpret_cast<double2*>(sm + L.o_pos);
+        double2* vel = reinterpret_cast<double2*>(sm + L.o_vel);
+        double2* vt = reinterpret_cast<double2*>(sm + L.o_vt);
+        uint4* csr = reinterpret_cast<uint4*>(sm + L.o_csr);
+        int* claim = reinterpret_cast<int*>(sm + L.o_claim);
+        const unsigned zero_ent = (unsigned)Ed << 1;
+        for (int i = t; i < Pd; i += G) {
+            pos[i] = g2[i];
+            vel[i] = g2[Pd + i];
+            vt[i] = g2[3 * Pd + i];
+            claim[i] = 0x7fffffff;
+            uint4 rec = __ldg(reinterpret_cast<const uint4*>(db + DH->o_csr8) + i);
+            unsigned* w = reinterpret_cast<unsigned*>(&rec);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {                   // empty gather slots (0xffff) point at the all-zero entry ef[Ed]
+                if ((w[q] & 0xffffu) == 0xffffu) w[q] = (w[q] & 0xffff0000u) | zero_ent;
+                if ((w[q] >> 16) == 0xffffu) w[q] = (w[q] & 0xffffu) | (zero_ent << 16);
+            }
+            csr[i] = rec;
+        }
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+            if (t + k * G < Pd && __ldg(db + DH->o_fixed + t + k * G)) fixmask |= 1u << k;
+        uint32_t* eidx = reinterpret_cast<uint32_t*>(sm + L.o_eidx);
+        double* ggoal = gstate + 8 * (size_t)Pd;
+        const int16_t* eact = reinterpret_cast<const int16_t*>(db + DH->o_eact);
+        const double* act = prm.act + (size_t)env * prm.act_stride;
+        for (int e = t; e < Ed; e += G) {
+            eidx[e] = __ldg(reinterpret_cast<const uint32_t*>(db + DH->o_eidx10) + e);
+            if (prm.apply_actions) {
+                // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather, written to the
+                // state block in place: goal = (sum of the <= 2 actuations driving this edge) * (init_len / count).  The
+                // spring pass reads ggoal[e] with the same thread (e % G), so program order is all the ordering it needs.
+                const int a0 = eact[2 * e], a1 = eact[2 * e + 1];
+                if (a0 >= 0) {
+                    const double l0 = __ldg(reinterpret_cast<const double*>(db + DH->o_el0) + e);
+                    double sum = 0.0 + act[a0];
+                    int cnt = 1;
+                    if (a1 >= 0) { sum += act[a1]; cnt = 2; }
+                    ggoal[e] = sum * (l0 / cnt);
+                }
+            }
+        }
+        double2* etab = reinterpret_cast<double2*>(sm + L.o_etab);
+        for (int i = t; i < DH->n_types; i += G) etab[i] = __ldg(reinterpret_cast<const double2*>(db + DH->o_etab) + i);
+        if (t == 0) reinterpret_cast<double2*>(sm + L.o_ef)[Ed] = make_double2(0.0, 0.0);
+        uint2* lpt = reinterpret_cast<uint2*>(sm + L.o_lpt);
+        for (int l = t; l < n_leaf; l += G) lpt[l] = __ldg(reinterpret_cast<const uint2*>(db + DH->o_lpt16) + l);
+        volatile int* misc = reinterpret_cast<volatile int*>(sm + L.o_misc);
+        for (int i = t; i < kGMiscInts; i += G) misc[i] = 0;
+    }
+    __syncthreads();
+
+    int unstable = 0, completed_steps = 0, first_substep = 1;
+    int r = 0, ss = 0;                                  // cta_or call counter, executed-substep counter (uniform)
+    double D = 0.0;                                     // bound of the displacement of any point since the list was built
+    // (everything else the phases need is in the shared-memory header: the loop below keeps a dozen registers live across
+    // the out-of-line calls)
+#ifdef MEVO_PROF
+    long long pt0 = clock64();
+    unsigned long long pacc[3] = {0, 0, 0};
+#endif
+
+    for (int step = 0; step < prm.n_steps; step++) {
+        for (int sub = 0; sub < prm.n_substeps; sub++) {
+            if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
+            const bool dump = step == 0 && sub == 0;
+            const int rebuild = first_substep || !(2.0 * D <= kListMargin - kListSlack);
+            unsigned int* dbg_row = nullptr;
+            int* dbg_n = nullptr;
+            double2* dbg_cf = nullptr;
+            if (dump && (prm.dbg_cand || prm.dbg_cf)) {
+                const GHdr* H = reinterpret_cast<const GHdr*>(sm);
+                if (prm.dbg_cand) { dbg_row = prm.dbg_cand + (size_t)H->env * prm.dbg_cand_cap; dbg_n = prm.dbg_cand_n + H->env; }
+                if (prm.dbg_cf) dbg_cf = reinterpret_cast<double2*>(prm.dbg_cf + (H->gstate - prm.state));
+            }
+            const int cr = g_collide<G, MINB>(rebuild, r, dbg_row, dbg_n, prm.dbg_cand_cap, dbg_cf);
+            r = cr >> 1;
+            if (rebuild) D = 0.0;
+#ifdef MEVO_PROF
+            { const long long n = clock64(); pacc[0] += n - pt0; pt0 = n; }
+#endif
+            g_rk4<G, MINB, PPT>(fixmask);
+#ifdef MEVO_PROF
+            { const long long n = clock64(); pacc[1] += n - pt0; pt0 = n; }
+#endif
+            r = g_constrain<G, MINB, PPT>(fixmask, first_substep, r, ss);
+#ifdef MEVO_PROF
+            { const long long n = clock64(); pacc[2] += n - pt0; pt0 = n; }
+#endif
+            {
+                const GHdr* H = reinterpret_cast<const GHdr*>(sm);
+                const volatile int* misc = reinterpret_cast<const volatile int*>(sm + H->o_misc);
+                D += __hiloint2double(misc[kGmDisp + (ss & 1)], 0);
+            }
+            ss++;
+            first_substep = 0;
+            if (cr & 1) unstable = 1;                     // Sim::step aborts the remaining substeps (Sim.cpp:107-110)
+        }
+        if (!unstable) completed_steps++;
+    }
+#ifdef MEVO_PROF
+    if (threadIdx.x == 0) for (int q = 0; q < 3; q++) atomicAdd(&g_g2prof[q], pacc[q]);
+#endif
+
+    // ---------------------------------------------------------------- stage out (goals were written at stage in)
+    {
+        const GHdr* H = reinterpret_cast<const GHdr*>(sm);
+        const int tt = threadIdx.x, n_pts = H->Pd, e_id = H->env;
+        double2* o2 = reinterpret_cast<double2*>(H->gstate);
+        if (unstable && prm.auto_reset) {
+            // Sim::revert(0) in place (Environment.cpp:247-263): pos, vel <- snapshot; pos_last = pos; vel_true = vel
+            const double2* s0 = reinterpret_cast<const double2*>(H->gstate0);
+            for (int i = tt; i < n_pts; i += G) {
+                const double2 p0 = s0[i], v0 = s0[n_pts + i];
+                o2[i] = p0; o2[n_pts + i] = v0; o2[2 * n_pts + i] = p0; o2[3 * n_pts + i] = v0;
+            }
+        } else if (!first_substep) {
+            const double2* pos = reinterpret_cast<const double2*>(sm + H->o_pos);
+            const double2* vel = reinterpret_cast<const double2*>(sm + H->o_vel);
+            const double2* vt = reinterpret_cast<const double2*>(sm + H->o_vt);
+            for (int i = tt; i < n_pts; i += G) {
+                const double2 x = pos[i];
+                o2[i] = x;
+                o2[n_pts + i] = vel[i];
+                o2[2 * n_pts + i] = x;                     // pos_last = pos after update_true_vel
+                o2[3 * n_pts + i] = vt[i];
+            }
+        }
+        if (tt == 0) {
+            prm.unstable[e_id] = (uint8_t)unstable;
+            if (unstable && prm.auto_reset) prm.sim_time[e_id] = 0;
+            else prm.sim_time[e_id] += completed_steps;
+            if (unstable) atomicAdd(prm.unstable_events, 1ull);
+        }
+    }
+}
+
+}  // namespace mevo

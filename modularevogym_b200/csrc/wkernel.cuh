@@ -182,7 +182,7 @@ __device__ __forceinline__ double flip_sign(double x) {       // -x on the integ
 //           their contacts are applied in list order.
 // Both buffers are drained whenever they fill, so no configuration can overflow them.
 template <class S>
-__device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_row, int* dbg_n, int dbg_cap) {
+__device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_row, int* dbg_n, int dbg_cap, double2* dbg_cf) {
     const int lane = threadIdx.x & 31;
     const WarpHdr* H = reinterpret_cast<const WarpHdr*>(sm + S::o_hdr);
     double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
@@ -406,6 +406,8 @@ __device__ __noinline__ int warp_collide(unsigned char* sm, unsigned int* dbg_ro
         atomicAdd(&g_whist[1][bc][0], d); atomicAdd(&g_whist[1][bc][1], 1ull);
     }
 #endif
+    if (dbg_cf)                                        // test hook: collision_forces of this substep
+        for (int i = lane; i < Pd; i += 32) dbg_cf[i] = cf[i];
     // K6a: unstable test uses the boxes of the START of this substep (a-12)
     return __any_sync(0xffffffffu, lane < 8 && misc[lane] > misc[8 + lane]);
 }
@@ -654,7 +656,6 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
             for (int i = prm.n_steps * prm.n_substeps; i > 0; i--) __syncthreads();
         return;
     }
-    constexpr bool ghost = false;
     const int env = prm.class_envs[slot];
     unsigned char* sm = smem_raw + grp * S::kBytes;
     double* gstate;
@@ -759,7 +760,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     int unstable = 0;
     int completed_steps = 0;
     bool first_substep = true;
-    const bool dbg = prm.dbg_cand != nullptr && !ghost;
+    const bool dbg = prm.dbg_cand != nullptr || prm.dbg_cf != nullptr;
 
     for (int step = 0; step < prm.n_steps; step++) {
         for (int sub = 0; sub < prm.n_substeps; sub++) {
@@ -770,8 +771,9 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
 #ifdef MEVO_PROF
             const long long tq0 = clock64();
 #endif
-            const int sub_unstable = warp_collide<S>(sm, dump ? prm.dbg_cand + (size_t)env * prm.dbg_cand_cap : nullptr,
-                                                     dump ? prm.dbg_cand_n + env : nullptr, prm.dbg_cand_cap);
+            const int sub_unstable = warp_collide<S>(sm, (dump && prm.dbg_cand) ? prm.dbg_cand + (size_t)env * prm.dbg_cand_cap : nullptr,
+                                                     (dump && prm.dbg_cand) ? prm.dbg_cand_n + env : nullptr, prm.dbg_cand_cap,
+                                                     (dump && prm.dbg_cf) ? reinterpret_cast<double2*>(prm.dbg_cf + (gstate - prm.state)) : nullptr);
 #ifdef MEVO_PROF
             const long long tq1 = clock64();
 #endif
@@ -800,7 +802,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     }
 
     // ---------------------------------------------------------------- stage out
-    if (!ghost) {
+    {
         const WarpHdr* H = reinterpret_cast<const WarpHdr*>(sm + S::o_hdr);
         const int Pd = H->Pd, Ed = H->Ed;
         double2* o2 = reinterpret_cast<double2*>(gstate);

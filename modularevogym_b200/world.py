@@ -346,10 +346,13 @@ def thrower_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -
 
 def climber_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
     """Climber-v0 (``evogym/envs/sim_files/Climber-v0.json`` + ``evogym/envs/climb.py:45-46``): a 7 x 90 fixed ``pipe`` (closed
-    at both ends, walls one voxel thick), the robot at voxel (1, 1)."""
-    w = WorldSpec(width=7, height=90)
-    grid = np.zeros((90, 7), dtype=np.int64)
-    grid[:, 0] = grid[:, 6] = VOXEL_TYPES["FIXED"]
+    at both ends, walls one voxel thick), the robot at voxel (1, 1).  The reference's pipe is 5 voxels wide inside; for a wider
+    robot (BASELINE configs[3] names Climber with 10x10 / 20x20 morphologies, which cannot exist in that pipe) the pipe is
+    widened to the robot's width + 2 -- a synthetic Climber-style world, same wall contact on both sides."""
+    width = max(7, int(np.asarray(robot).shape[1]) + 2)
+    w = WorldSpec(width=width, height=90)
+    grid = np.zeros((90, width), dtype=np.int64)
+    grid[:, 0] = grid[:, width - 1] = VOXEL_TYPES["FIXED"]
     grid[0, :] = grid[89, :] = VOXEL_TYPES["FIXED"]
     w.add_from_array("pipe", grid, 0, 0)
     w.add_from_array("robot", robot, 1, 1, connections)

@@ -23,6 +23,7 @@ NAMES = golden_names()
 TF_POS_TOL = 1e-14
 TF_VEL_TOL = 1e-11
 TF_VT_TOL = 1e-9          # vel_true = dpos / 1e-4 amplifies position ulps by 1e4
+TF_CF_TOL = 1e-11         # collision_forces, relative to max(1, |cf| max): O(1e4) forces summed in candidate-list order
 FREE_POS_TOL = 1e-7       # 60 free-running substeps through stiff contacts
 
 
@@ -49,6 +50,7 @@ def make_batch(goldens, cand_dump=0):
         B.add_world(g.world)
     if cand_dump:
         B.enable_candidate_dump(cand_dump)
+        B.enable_force_dump()
     B.finalize()
     return B
 
@@ -70,8 +72,15 @@ def test_teacher_forced_substeps_and_candidates(goldens, kernel_choice):
     """Environment::step, one substep at a time, from the reference's own state."""
     B = make_batch(goldens, cand_dump=8192)
     n_sub = max(g.n_sub for g in goldens)
-    worst = {"pos": 0.0, "vel": 0.0, "vt": 0.0}
+    worst = {"pos": 0.0, "vel": 0.0, "vt": 0.0, "cf": 0.0}
     exact = total = 0
+    dyn = []
+    for i, g in enumerate(goldens):
+        m = np.ones(g.P, dtype=bool)
+        for o, st in enumerate(g.static_objects()):
+            if st:
+                m[g.obj_info[o, 1]:g.obj_info[o, 2] + 1] = False
+        dyn.append(m)
     for k in range(n_sub):
         live = [i for i, g in enumerate(goldens) if k < g.n_sub]
         for i in live:
@@ -88,7 +97,10 @@ def test_teacher_forced_substeps_and_candidates(goldens, kernel_choice):
             e = (rel_err(pos, g["sub_pos"][k]), rel_err(vel, g["sub_vel"][k]), rel_err(vt, g["sub_vt"][k]))
             assert e[0] <= TF_POS_TOL and e[1] <= TF_VEL_TOL and e[2] <= TF_VT_TOL, (g.name, k, e)
             assert np.array_equal(last, pos), (g.name, k)
-            worst = {"pos": max(worst["pos"], e[0]), "vel": max(worst["vel"], e[1]), "vt": max(worst["vt"], e[2])}
+            # PhysicsEngine::resolve_collisions' own output (a-6), on the points the engine simulates
+            ecf = rel_err(B.read_collision_forces(i)[dyn[i]], g["sub_cf"][k][dyn[i]])
+            assert ecf <= TF_CF_TOL, (g.name, k, ecf)
+            worst = {"pos": max(worst["pos"], e[0]), "vel": max(worst["vel"], e[1]), "vt": max(worst["vt"], e[2]), "cf": max(worst["cf"], ecf)}
             total += 1
             exact += int(np.array_equal(pos, g["sub_pos"][k]) and np.array_equal(vel, g["sub_vel"][k]))
             if k in g["cand_at"].tolist():
