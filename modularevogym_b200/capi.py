@@ -13,7 +13,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import numpy as np
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libmevo_b200.so")
+LIB_PATH = os.environ.get("MEVO_LIB") or os.path.join(PKG_DIR, "libmevo_b200.so")     # MEVO_LIB: development builds (e.g. -DMEVO_PROF)
 HEADER_PATH = os.path.join(PKG_DIR, "..", "include", "mevo_b200.h")
 
 _vp, _i, _d, _cp = C.c_void_p, C.c_int, C.c_double, C.c_char_p

@@ -77,7 +77,8 @@ struct DesignHeader {        // 160 bytes
     // group kernel (gkernel.cuh)
     int o_eidx10;                             // u32 per edge: a | b << 10 | type << 20 | rigid-cell << 26
     int o_lpt16;                              // 8 bytes per leaf: TL, TR, BR, BL point ids, u16 each
-    int reserved[7];
+    int ilist_cap;                            // neighbour-list entries for the always-candidate items (follows the pair list)
+    int reserved[6];
 };
 static_assert(sizeof(DesignHeader) == 160, "DesignHeader must be 160 bytes");
 

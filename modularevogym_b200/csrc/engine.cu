@@ -45,17 +45,20 @@ constexpr int kGroupMaxPoints = 1024, kGroupMaxTypes = 64;      // 10-bit point 
 #define MEVO_WCAPS_B 64, 160, 32, 512, 640, 128     /* 5x5 robot + a larger free object (Carrier, Catcher, beams): 22.5 KB, 10 per SM */
 
 int group_class_for(int Pd, int Ed) {
-    // threads per environment: one point per thread and ~3 edges per thread in flight (7x7 -> 64, 10x10 -> 128, 14x14 -> 256,
-    // 20x20 -> 512); MEVO_GROUP_SHIFT (development, tests) moves every environment up or down one class -- a class whose
-    // largest environment has more points than threads runs the two-points-per-thread build of the kernel
+    // threads per environment.  MEVO_GCLASS = "p64,p128,p256" (development): largest point count that runs with 64 / 128 / 256
+    // threads; MEVO_GROUP_SHIFT (development, tests) moves every environment up or down one class.  A class whose largest
+    // environment has more points than threads runs a 2- or 4-points-per-thread build of the kernel.
+    int lim[3] = {128, 256, 512};          // measured on B200: few threads per environment, many environments per SM
+    if (const char* g = std::getenv("MEVO_GCLASS")) std::sscanf(g, "%d,%d,%d", &lim[0], &lim[1], &lim[2]);
     const char* shift_env = std::getenv("MEVO_GROUP_SHIFT");       // read at every finalize: the tests move fixtures across classes
     const int shift = shift_env ? std::atoi(shift_env) : 0;
+    (void)Ed;
     int c = kLastClass;
-    if (Ed <= 192 && Pd <= 64) c = kFirstGroupClass;
-    else if (Ed <= 448 && Pd <= 128) c = kFirstGroupClass + 1;
-    else if (Ed <= 832 && Pd <= 256) c = kFirstGroupClass + 2;
+    if (Pd <= lim[0]) c = kFirstGroupClass;
+    else if (Pd <= lim[1]) c = kFirstGroupClass + 1;
+    else if (Pd <= lim[2]) c = kFirstGroupClass + 2;
     c = shift ? std::min(kLastClass, std::max(kFirstGroupClass, c + shift)) : c;
-    while (c < kLastClass && Pd > 2 * kGroupSizes[c]) c++;          // at most two points per thread
+    while (c < kLastClass && Pd > 4 * kGroupSizes[c]) c++;          // at most four points per thread
     return c;
 }
 
@@ -132,21 +135,22 @@ void gstep_do(GAction what, const StepParams* prm, int smem, cudaStream_t stream
 
 void gstep_dispatch(int cls, int ppt, int variant, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
     const int g = kGroupSizes[cls];
-    if (ppt == 2) {
+    if (ppt > 2) {
+        if (g == 64) gstep_do<64, 8, 4>(what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 4, 4>(what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 2, 4>(what, prm, smem, stream);
+        else gstep_do<512, 1, 4>(what, prm, smem, stream);
+    } else if (ppt == 2) {
         if (g == 64) gstep_do<64, 8, 2>(what, prm, smem, stream);
         else if (g == 128) gstep_do<128, 4, 2>(what, prm, smem, stream);
+        else if (g == 256 && variant == 1) gstep_do<256, 3, 2>(what, prm, smem, stream);
         else if (g == 256) gstep_do<256, 2, 2>(what, prm, smem, stream);
         else gstep_do<512, 1, 2>(what, prm, smem, stream);
-    } else if (variant == 0) {
+    } else {
         if (g == 64) gstep_do<64, 8, 1>(what, prm, smem, stream);
         else if (g == 128) gstep_do<128, 4, 1>(what, prm, smem, stream);
         else if (g == 256) gstep_do<256, 2, 1>(what, prm, smem, stream);
         else gstep_do<512, 1, 1>(what, prm, smem, stream);
-    } else {
-        if (g == 64) gstep_do<64, 16, 1>(what, prm, smem, stream);
-        else if (g == 128) gstep_do<128, 6, 1>(what, prm, smem, stream);
-        else if (g == 256) gstep_do<256, 3, 1>(what, prm, smem, stream);
-        else gstep_do<512, 2, 1>(what, prm, smem, stream);
     }
 }
 
@@ -209,7 +213,7 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     stream_ = s;
     // development: MEVO_GVARIANT = one digit per group class (64, 128, 256, 512 threads), 0 / 1 = the two register budgets
-    for (int c = kFirstGroupClass; c < kNumClasses; c++) impl_->gvariant[c] = 1;
+    for (int c = kFirstGroupClass; c < kNumClasses; c++) impl_->gvariant[c] = 0;
     if (const char* e = std::getenv("MEVO_GVARIANT"))
         for (int c = kFirstGroupClass; c < kNumClasses && e[c - kFirstGroupClass]; c++) impl_->gvariant[c] = e[c - kFirstGroupClass] == '1';
     if (const char* e = std::getenv("MEVO_NO_WKERNEL")) impl_->use_warp_kernel = std::atoi(e) == 0;
@@ -229,10 +233,14 @@ Batch::~Batch() {
     {
         unsigned long long gp[8];
         if (cudaMemcpyFromSymbol(gp, g_g2prof, sizeof(gp)) == cudaSuccess) {
-            const unsigned long long tot = gp[0] + gp[1] + gp[2];
-            if (tot)
-                std::fprintf(stderr, "[prof] group kernel, share of CTA cycles: collide %.3f rk4 %.3f constrain %.3f\n",
-                             (double)gp[0] / tot, (double)gp[1] / tot, (double)gp[2] / tot);
+            unsigned long long tot = 0;
+            for (int q = 0; q < 8; q++) tot += gp[q];
+            if (tot) {
+                const char* names[8] = {"boxes+list", "broad+filter", "resolve+contacts", "rk4", "band test", "jacobi", "rigid pass", "true vel"};
+                std::fprintf(stderr, "[prof] group kernel, share of CTA cycles:");
+                for (int q = 0; q < 8; q++) std::fprintf(stderr, " %s %.3f", names[q], (double)gp[q] / tot);
+                std::fprintf(stderr, "\n");
+            }
         }
     }
     {
@@ -506,15 +514,19 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.n_obj = (int)objrecs.size();
     H.n_pairs = (int)pairs.size();
     H.n_items = (int)items.size();
-    // group kernel: 64 candidates / survivors per warp and round (both buffers are drained in rounds); the neighbour list holds
+    // group kernel: 128 candidates / survivors per warp and round (both buffers are drained in rounds, 64 at a time, so a
+    // round keeps going after its first hits); the neighbour list holds
     // the whole pair table when that is small, else room for ~24 near neighbours per leaf (an overflowing warp falls back to
     // scanning its share of the table)
     const int n_warps = kGroupSizes[group_class_for(Pd, Ed)] / 32;
-    H.cand_cap = 64 * n_warps;
+    H.cand_cap = 128 * n_warps;
     {
         const int want = std::min(H.n_pairs, std::max(2048, 24 * H.n_leaf));
         const int per_warp = ((want + n_warps - 1) / n_warps + 63) & ~63;
         H.list_cap = H.n_pairs ? per_warp * n_warps : 0;
+        // items: a warp lists at most its own 32-wide chunks of the item table (chunks warp, warp + n_warps, ...)
+        const int chunks = (H.n_items + 31) / 32;
+        H.ilist_cap = ((chunks + n_warps - 1) / n_warps) * 32 * n_warps;
     }
 
     H.o_el0 = dw.begin_section(); dw.put_array(el0);
@@ -705,12 +717,13 @@ void Batch::finalize() {
             for (int q = 0; q < 6; q++) m[q] = std::max(m[q], v[q]);
         }
         if (e.cls >= kFirstGroupClass) {
-            const GLayout L = g_layout(H->Pd, H->Ed, H->n_leaf, H->n_types, H->cand_cap);
+            const GLayout L = g_layout(H->Pd, H->Ed, H->n_leaf, H->n_types, H->cand_cap, H->n_rvis, H->n_rlev);
             if (L.total > kMaxSmemPerBlock) throw std::runtime_error("environment " + std::to_string(i) + " does not fit in shared memory");
             impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
             impl_->class_ppt[e.cls] = std::max(impl_->class_ppt[e.cls], (H->Pd + kGroupSizes[e.cls] - 1) / kGroupSizes[e.cls]);
+            if (impl_->class_ppt[e.cls] == 3) impl_->class_ppt[e.cls] = 4;
             d.scratch_off16 = (int)(scratch_bytes / 16);
-            scratch_bytes += ((size_t)H->list_cap * 4 + 15) & ~(size_t)15;
+            scratch_bytes += ((size_t)(H->list_cap + H->ilist_cap) * 4 + 15) & ~(size_t)15;
             if (scratch_bytes / 16 > 0x7fffffffull) throw std::runtime_error("neighbour-list scratch exceeds 32 GB");
         }
         impl_->class_envs[e.cls].push_back(i);
@@ -723,9 +736,10 @@ void Batch::finalize() {
         if (std::atoi(e))
             for (int c = 0; c < kNumClasses; c++)
                 if (!impl_->class_envs[c].empty())
-                    std::fprintf(stderr, "[mevo] class %d: %zu envs, max points %d edges %d leaves %d pairs %d items %d visits %d\n", c,
+                    std::fprintf(stderr, "[mevo] class %d (%d threads, %d points per thread): %zu envs, max points %d edges %d leaves %d pairs %d "
+                                 "items %d visits %d, shared memory %d B per CTA\n", c, kGroupSizes[c], impl_->class_ppt[c],
                                  impl_->class_envs[c].size(), impl_->class_max[c][0], impl_->class_max[c][1], impl_->class_max[c][2],
-                                 impl_->class_max[c][3], impl_->class_max[c][4], impl_->class_max[c][5]);
+                                 impl_->class_max[c][3], impl_->class_max[c][4], impl_->class_max[c][5], impl_->class_smem[c]);
     for (int c = 0; c < kFirstGroupClass; c++)
         std::stable_sort(impl_->class_envs[c].begin(), impl_->class_envs[c].end(),
                          [&](int a, int b) { return impl_->env_cost[a] > impl_->env_cost[b]; });

@@ -8,12 +8,14 @@
 // What bounds this path on B200 (ncu, profiles/r01h_step512_*): not HBM (the state is on chip) and not the FP64 pipe
 // (11 % busy) but a long chain of short dependent phases separated by CTA barriers, run by too few warps to hide their
 // latency.  The layout below is built around that:
-//   * shared memory holds only what is gathered across threads (positions, stage positions, velocities, contact forces,
-//     true velocities, per-edge forces, length_eq, boxes) plus compact tables (one u32 per edge, one 16-byte gather
-//     record per point, 8 bytes per leaf): a 20x20 robot needs ~100 KB instead of 187 KB, so TWO environments are
-//     resident per SM and one's serial phases (ordered rigid-cell pass, contact rounds) overlap the other's parallel ones;
-//     RK4 accumulators and stage velocities live in registers of the thread that owns the point, length_eq_goal stays in
-//     the state block in HBM (read once per substep, written once per launch);
+//   * shared memory holds only what is gathered across threads every stage (positions, stage positions, contact forces,
+//     per-edge forces, length_eq, boxes) plus compact tables (one u32 per edge, one 16-byte gather record per point, 8 bytes
+//     per leaf): a 20x20 robot needs ~90 KB instead of 187 KB, so TWO environments of 256 threads are resident per SM (four
+//     of 128 threads for 15x15, eight of 64 for 10x10) and one's serial phases (ordered rigid-cell pass, contact rounds)
+//     overlap the others' parallel ones.  What only its owner thread touches stays out of shared memory: velocities are
+//     read from / written to the state block in HBM once per substep and live in registers in between, like the RK4
+//     accumulators and stage velocities; true velocities (read by the contact resolver only) and length_eq_goal (read once
+//     per substep) stay in the state block too;
 //   * broad phase by temporal coherence: the all-pairs leaf table (23 k pairs on a 20x20 robot) is scanned once per
 //     launch -- and again only when points have moved more than half the margin since -- into a per-warp neighbour list
 //     of the pairs whose boxes are within kListMargin of each other; every substep tests only the listed pairs exactly.
@@ -38,16 +40,17 @@ constexpr int kGMiscInts = 96;
 // misc words: [0..7] self-collision counts per object (a-12), [8..10] rotating slots of cta_or, [12..13] largest point
 // displacement of a substep (high word of the double, by substep parity), [16..31] per-warp neighbour-list lengths
 // (-1: list overflowed, this warp scans its table range), [32..63] per-warp survivor counts (two round parities),
-// [64] candidate-dump cursor
-constexpr int kGmSelf = 0, kGmOr = 8, kGmDisp = 12, kGmList = 16, kGmSurv = 32, kGmDump = 64;
+// [64] candidate-dump cursor, [66..81] per-warp item-list lengths, [84..87] development counters (-DMEVO_PROF)
+constexpr int kGmSelf = 0, kGmOr = 8, kGmDisp = 12, kGmList = 16, kGmSurv = 32, kGmDump = 64, kGmIList = 66, kGmProf = 84;
 
 constexpr int kEidxBShift = 10, kEidxTypeShift10 = 20, kEidxRigidBit10 = 26;
 
-struct GHdr {                                 // first 256 bytes of the CTA's shared memory
+constexpr int kGHdrBytes = 320;
+struct GHdr {                                 // first kGHdrBytes of the CTA's shared memory
     int Pd, Ed, n_leaf, n_pairs, n_items, n_rlev, n_obj, seg_cap;
-    int lseg_cap, gx0, gy0, gw, gh, env, pad1, pad2;
-    int o_pos, o_spos, o_vel, o_cf, o_vt, o_ef, o_leq, o_aabb;
-    int o_csr, o_etab, o_eidx, o_lpt, o_claim, o_cand, o_surv, o_misc;
+    int lseg_cap, iseg_cap, gx0, gy0, gw, gh, env, pad0;
+    int o_pos, o_spos, o_cf, o_ef, o_leq, o_aabb, o_csr, o_etab;
+    int o_btab, o_eidx, o_lpt, o_rsched, o_rlev, o_cand, o_surv, o_misc;
     const int16_t* st_grid;
     const double4* st_aabb;
     const double2* st_pos;
@@ -56,36 +59,36 @@ struct GHdr {                                 // first 256 bytes of the CTA's sh
     const double2* g_last;                    // pos_last in HBM: read in the first substep of a launch only
     const unsigned int* pairs;
     const unsigned int* items;
-    const uint16_t* rlev;
-    const uint16_t* rvis;
     const ObjRec* objs;
     const double* ggoal;                      // length_eq_goal of this environment (state block)
-    unsigned int* list;                       // neighbour list scratch of this environment
+    unsigned int* list;                       // neighbour list scratch of this environment: tested pairs ...
+    unsigned int* ilist;                      // ... and always-candidate items
     double* gstate;                           // state block of this environment
     const double* gstate0;                    // its reset snapshot
 };
-static_assert(sizeof(GHdr) <= 256, "GHdr must fit its 256-byte slot");
+static_assert(sizeof(GHdr) <= kGHdrBytes, "GHdr must fit its slot");
 
 struct GLayout {
-    int o_pos, o_spos, o_vel, o_cf, o_vt, o_ef, o_leq, o_aabb, o_csr, o_etab, o_eidx, o_lpt, o_claim, o_cand, o_surv, o_misc, total;
+    int o_pos, o_spos, o_cf, o_ef, o_leq, o_aabb, o_csr, o_etab, o_btab, o_eidx, o_lpt, o_rsched, o_rlev, o_cand, o_surv, o_misc, total;
 };
 
-MEVO_HD GLayout g_layout(int Pd, int Ed, int n_leaf, int n_types, int cand_cap) {
+MEVO_HD GLayout g_layout(int Pd, int Ed, int n_leaf, int n_types, int cand_cap, int n_rvis, int n_rlev) {
     GLayout L;
-    int o = 256;
+    int o = kGHdrBytes;
     L.o_pos = o;   o += 16 * Pd;
     L.o_spos = o;  o += 16 * Pd;
-    L.o_vel = o;   o += 16 * Pd;
     L.o_cf = o;    o += 16 * Pd;
-    L.o_vt = o;    o += 16 * Pd;
-    L.o_ef = o;    o += 16 * (Ed + 1);              // [Ed] stays zero: empty gather slots point at it
+    L.o_ef = o;    o += 16 * (Ed + 1);              // [Ed] stays zero: empty gather slots point at it.  The first 4 * Pd bytes
+                                                    // double as the contact-claim words while contacts are applied (ef is dead then)
     L.o_leq = o;   o += align16(8 * Ed);
     L.o_aabb = o;  o += 32 * n_leaf;
     L.o_csr = o;   o += 16 * Pd;
-    L.o_etab = o;  o += 16 * n_types;
+    L.o_etab = o;  o += 16 * n_types;               // (spring constant, init_length_eq) per edge type
+    L.o_btab = o;  o += 32 * n_types;               // squared-length bands per edge type: Jacobi lo, hi; rigid lo, hi
     L.o_eidx = o;  o += align16(4 * Ed);
     L.o_lpt = o;   o += align16(8 * n_leaf);
-    L.o_claim = o; o += align16(4 * Pd);
+    L.o_rsched = o; o += align16(4 * n_rvis);       // packed edge word of every rigid-cell visit, level order
+    L.o_rlev = o;  o += align16(2 * (n_rlev + 3));  // level offsets into rsched (+ two padding entries for the prefetch)
     L.o_cand = o;  o += align16(4 * cand_cap);
     L.o_surv = o;  o += align16(4 * cand_cap);
     L.o_misc = o;  o += 4 * kGMiscInts;
@@ -114,6 +117,15 @@ __device__ __forceinline__ bool aabb_overlap_margin(const double4& a, const doub
     return !(a.x - m > b.z) & !(a.z + m < b.x) & !(a.y - m > b.w) & !(a.w + m < b.y);
 }
 
+// a point inside box b grown by m on every side (necessary for point_in_box after either has moved by <= m / 2)
+__device__ __forceinline__ bool point_in_box_margin(const double2 p, const double4& b, double m) {
+    return (p.x >= b.x - m) & (p.x <= b.z + m) & (p.y >= b.y - m) & (p.y <= b.w + m);
+}
+
+__device__ __forceinline__ unsigned leaf_corner(const uint2 lp, unsigned corner) {      // TL, TR, BR, BL point id of a leaf
+    return (((corner & 2u) ? lp.y : lp.x) >> ((corner & 1u) * 16)) & 0xffffu;
+}
+
 __device__ __forceinline__ double2 spring_force10(const double2* sp, uint32_t ix, double k, double& q, bool first_stage) {
     const double2 pa = sp[ix & 0x3ff], pb = sp[(ix >> kEidxBShift) & 0x3ff];
     const double dx = pa.x - pb.x, dy = pa.y - pb.y;
@@ -131,7 +143,20 @@ __device__ __forceinline__ double flip_if(double x, unsigned neg) {      // neg 
 }
 
 #ifdef MEVO_PROF
-__device__ unsigned long long g_g2prof[8];      // [0] collide [1] rk4 [2] constrain, cycles of thread 0 of every CTA
+// development only (-DMEVO_PROF): cycles of thread 0 of every CTA by phase
+// [0] boxes + list upkeep [1] broad phase + filter [2] resolve + contacts [3] RK4 [4] band test [5] Jacobi [6] rigid pass [7] true velocity
+__device__ unsigned long long g_g2prof[8];
+#define MEVO_GPROF(k)                                                                             \
+    do {                                                                                          \
+        if (threadIdx.x == 0) {                                                                   \
+            long long* _st = reinterpret_cast<long long*>(gsm_raw + reinterpret_cast<const GHdr*>(gsm_raw)->o_misc + 4 * kGmProf); \
+            const long long _n = clock64();                                                       \
+            atomicAdd(&g_g2prof[(int)_st[1]], (unsigned long long)(_n - _st[0]));                 \
+            _st[0] = _n; _st[1] = (k);                                                            \
+        }                                                                                         \
+    } while (0)
+#else
+#define MEVO_GPROF(k)
 #endif
 
 // =================================================================================== phase 1: collisions
@@ -147,17 +172,18 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
     const GHdr* H = reinterpret_cast<const GHdr*>(sm);
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const double2* pos = reinterpret_cast<const double2*>(sm + H->o_pos);
-    const double2* vt = reinterpret_cast<const double2*>(sm + H->o_vt);
+    const double2* vt = reinterpret_cast<const double2*>(H->gstate) + 3 * H->Pd;   // vel_true: state block (written by update_true_vel)
     double2* cf = reinterpret_cast<double2*>(sm + H->o_cf);
     double4* aabb = reinterpret_cast<double4*>(sm + H->o_aabb);
     const uint2* lpt = reinterpret_cast<const uint2*>(sm + H->o_lpt);
-    int* claim = reinterpret_cast<int*>(sm + H->o_claim);
+    int* claim = reinterpret_cast<int*>(sm + H->o_ef);        // aliases ef, which is dead between a substep's start and its RK4
     volatile int* misc = reinterpret_cast<volatile int*>(sm + H->o_misc);
     const int Pd = H->Pd, n_leaf = H->n_leaf, n_pairs = H->n_pairs, n_items = H->n_items, seg_cap = H->seg_cap;
     unsigned int* cand = reinterpret_cast<unsigned int*>(sm + H->o_cand) + warp * seg_cap;
     unsigned int* surv_all = reinterpret_cast<unsigned int*>(sm + H->o_surv);
     unsigned int* surv = surv_all + warp * seg_cap;
 
+    MEVO_GPROF(0);
     // ---- K2a: leaf boxes (a-4), zero collision_forces
     for (int l = t; l < n_leaf; l += G) {
         const uint2 lp = lpt[l];
@@ -171,7 +197,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
         minx = fmin(minx, q.x); maxx = fmax(maxx, q.x); miny = fmin(miny, q.y); maxy = fmax(maxy, q.y);
         aabb[l] = make_double4(minx, miny, maxx, maxy);
     }
-    for (int i = t; i < Pd; i += G) cf[i] = make_double2(0.0, 0.0);
+    for (int i = t; i < Pd; i += G) { cf[i] = make_double2(0.0, 0.0); claim[i] = 0x7fffffff; }
     if (t < 8) misc[kGmSelf + t] = 0;
     __syncthreads();
 
@@ -201,19 +227,40 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
             }
         }
         if (lane == 0) misc[kGmList + warp] = ok ? lcnt : -1;
+        // always-candidate items (non-shared corners of leaf pairs that share a point) whose corner is within the margin of
+        // the other leaf's box; this warp's chunks of the item table can never exceed its list segment
+        unsigned int* iseg = H->ilist + (size_t)warp * H->iseg_cap;
+        int icnt = 0;
+        for (int c = warp; c * 32 < n_items; c += 2 * NW) {              // two chunks in flight
+            const int i0 = c * 32 + lane, i1 = i0 + NW * 32;
+            const unsigned ic0 = __ldg(H->items + (i0 < n_items ? i0 : 0)), ic1 = __ldg(H->items + (i1 < n_items ? i1 : 0));
+            const unsigned q0 = leaf_corner(lpt[ic0 & kCodeLeafMask], (ic0 >> kItemCornerShift) & 3u);
+            const unsigned q1 = leaf_corner(lpt[ic1 & kCodeLeafMask], (ic1 >> kItemCornerShift) & 3u);
+            const bool h0 = (i0 < n_items) & point_in_box_margin(pos[q0], aabb[(ic0 >> 12) & kCodeLeafMask], kListMargin);
+            const bool h1 = (i1 < n_items) & point_in_box_margin(pos[q1], aabb[(ic1 >> 12) & kCodeLeafMask], kListMargin);
+            const unsigned m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+            if (h0) iseg[icnt + __popc(m0 & ((1u << lane) - 1u))] = ic0;
+            icnt += __popc(m0);
+            if (h1) iseg[icnt + __popc(m1 & ((1u << lane) - 1u))] = ic1;
+            icnt += __popc(m1);
+        }
+        if (lane == 0) misc[kGmIList + warp] = icnt;
         __syncwarp();                                                    // list entries are read by other lanes of this warp
     }
     const int lcnt = misc[kGmList + warp];
     const unsigned int* psrc = lcnt >= 0 ? lseg : pairs + p0;             // overflowed list: the table range itself, every substep
     const int pn = lcnt >= 0 ? lcnt : p1 - p0;
 
+    MEVO_GPROF(1);
     // ---- K2b + K3 in rounds: produce candidates into this warp's segment, filter their corners into survivors, resolve
     const int gw = H->gw;
     int pi = 0;                                   // cursor in psrc
     int sc = warp, sit = 0, max_cells = -1;       // terrain: leaf chunk (leaves sc * 32 + lane), cell iteration
     int cx0 = 0, cy0 = 0, wx = 1, n_cells = 0;
     double4 mybb = make_double4(0, 0, 0, 0);
-    int next_ic = warp;                           // always-candidate items: next 32-wide chunk of this warp
+    const unsigned int* iseg = H->ilist + (size_t)warp * H->iseg_cap;
+    const int icnt = misc[kGmIList + warp];
+    int ii = 0;                                   // cursor in this warp's item list
     int rc = 0;                                   // survivor round counter (uniform)
     int flags;
     do {
@@ -256,21 +303,23 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
                     max_cells = __reduce_max_sync(0xffffffffu, n_cells);
                     sit = 0;
                 }
-                while (sit < max_cells && cnt + 32 <= seg_cap) {
-                    const int it = sit++;
-                    bool hit = false;
-                    unsigned int code = 0;
-                    if (it < n_cells) {
-                        const int cx = cx0 + it % wx, cy = cy0 + it / wx;
-                        const int sl = __ldg(H->st_grid + cy * gw + cx);
-                        if (sl >= 0) {
-                            hit = aabb_overlap(mybb, ldg_d4(H->st_aabb + sl));
-                            code = (unsigned)(sc * 32 + lane) | ((unsigned)sl << 12) | kCodeStatic;
-                        }
+                while (sit < max_cells && cnt + 64 <= seg_cap) {           // two cells per lane in flight
+                    const int it0 = sit, it1 = sit + 1;
+                    sit += 2;
+                    int s0 = -1, s1 = -1;
+                    if (it0 < n_cells) s0 = __ldg(H->st_grid + (cy0 + it0 / wx) * gw + cx0 + it0 % wx);
+                    if (it1 < n_cells) s1 = __ldg(H->st_grid + (cy0 + it1 / wx) * gw + cx0 + it1 % wx);
+                    bool h0 = false, h1 = false;
+                    if (s0 >= 0) h0 = aabb_overlap(mybb, ldg_d4(H->st_aabb + s0));
+                    if (s1 >= 0) h1 = aabb_overlap(mybb, ldg_d4(H->st_aabb + s1));
+                    const unsigned m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+                    if (m0 | m1) {
+                        const unsigned me = (unsigned)(sc * 32 + lane) | kCodeStatic;
+                        if (h0) cand[cnt + __popc(m0 & ((1u << lane) - 1u))] = me | ((unsigned)s0 << 12);
+                        cnt += __popc(m0);
+                        if (h1) cand[cnt + __popc(m1 & ((1u << lane) - 1u))] = me | ((unsigned)s1 << 12);
+                        cnt += __popc(m1);
                     }
-                    const unsigned m = __ballot_sync(0xffffffffu, hit);
-                    if (hit) cand[cnt + __popc(m & ((1u << lane) - 1u))] = code;
-                    cnt += __popc(m);
                 }
                 if (sit < max_cells) break;                               // segment full: next round
                 sc += NW; max_cells = -1;
@@ -290,17 +339,15 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
         int next_cc = 0;
         do {
             int scnt = 0;
-            // non-shared corners of leaf pairs that share a point (always candidates), two chunks in flight
-            while (next_ic * 32 < n_items && scnt + 64 <= seg_cap) {
-                const int i0 = next_ic * 32 + lane, i1 = i0 + NW * 32;
-                next_ic += 2 * NW;
-                const unsigned ic0 = __ldg(H->items + (i0 < n_items ? i0 : 0)), ic1 = __ldg(H->items + (i1 < n_items ? i1 : 0));
-                const unsigned cr0 = (ic0 >> kItemCornerShift) & 3u, cr1 = (ic1 >> kItemCornerShift) & 3u;
-                const uint2 l0 = lpt[ic0 & kCodeLeafMask], l1 = lpt[ic1 & kCodeLeafMask];
-                const unsigned q0 = ((cr0 & 2u) ? l0.y : l0.x) >> ((cr0 & 1u) * 16) & 0xffffu;
-                const unsigned q1 = ((cr1 & 2u) ? l1.y : l1.x) >> ((cr1 & 1u) * 16) & 0xffffu;
-                const bool h0 = (i0 < n_items) & point_in_box(pos[q0], aabb[(ic0 >> 12) & kCodeLeafMask]);
-                const bool h1 = (i1 < n_items) & point_in_box(pos[q1], aabb[(ic1 >> 12) & kCodeLeafMask]);
+            // listed always-candidate items (see the list upkeep above), two chunks in flight
+            while (ii < icnt && scnt + 64 <= seg_cap) {
+                const int i0 = ii + lane, i1 = i0 + 32;
+                const unsigned ic0 = iseg[i0 < icnt ? i0 : ii], ic1 = iseg[i1 < icnt ? i1 : ii];
+                ii += 64;
+                const unsigned q0 = leaf_corner(lpt[ic0 & kCodeLeafMask], (ic0 >> kItemCornerShift) & 3u);
+                const unsigned q1 = leaf_corner(lpt[ic1 & kCodeLeafMask], (ic1 >> kItemCornerShift) & 3u);
+                const bool h0 = (i0 < icnt) & point_in_box(pos[q0], aabb[(ic0 >> 12) & kCodeLeafMask]);
+                const bool h1 = (i1 < icnt) & point_in_box(pos[q1], aabb[(ic1 >> 12) & kCodeLeafMask]);
                 const unsigned m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
                 if (m0 | m1) {
                     if (h0) surv[scnt + __popc(m0 & ((1u << lane) - 1u))] = ic0;
@@ -309,7 +356,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
                     scnt += __popc(m1);
                 }
             }
-            const bool items_done = next_ic * 32 >= n_items;
+            const bool items_done = ii >= icnt;
             if (items_done) {
                 // ... then the 8 corners of each candidate pair of this round (these pairs share no point)
                 while (next_cc * 32 < cnt * 8 && scnt + 32 <= seg_cap) {
@@ -326,16 +373,14 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
                         if (dir == 0) {
                             code = a | (b << 12) | (corner << kItemCornerShift) | (b_static ? kItemRefStatic : 0u) | same;
                             const double4 bb = b_static ? ldg_d4(H->st_aabb + b) : aabb[b];
-                            const uint2 la = lpt[a];
-                            hit = point_in_box(pos[((corner & 2u) ? la.y : la.x) >> ((corner & 1u) * 16) & 0xffffu], bb);
+                            hit = point_in_box(pos[leaf_corner(lpt[a], corner)], bb);
                         } else {
                             code = b | (a << 12) | (corner << kItemCornerShift) | (b_static ? kItemMainStatic : 0u) | same;
                             double2 pp;
                             if (b_static) {
                                 pp = __ldg(H->st_pos + __ldg(&H->st_leaf[b].pt[corner]));
                             } else {
-                                const uint2 lb = lpt[b];
-                                pp = pos[((corner & 2u) ? lb.y : lb.x) >> ((corner & 1u) * 16) & 0xffffu];
+                                pp = pos[leaf_corner(lpt[b], corner)];
                             }
                             hit = point_in_box(pp, aabb[a]);
                         }
@@ -354,6 +399,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
 #pragma unroll
             for (int w = 0; w < NW; w++) n_surv += scount[w];
             if (n_surv > 0) {
+                MEVO_GPROF(2);
                 // ---- K3b: resolve survivors, apply their contacts (a-5, a-6)
                 PointSrc src;
                 src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = H->st_pos;
@@ -392,6 +438,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
                         }
                     }
                 }
+                MEVO_GPROF(1);
             }
         } while (flags & 1);
     } while (flags & 2);
@@ -410,7 +457,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
 
 // =================================================================================== phase 2: actuators + RK4
 // PhysicsEngine::update_actuators + step_rk4 + get_pos_vel_slope (SURVEY 8a-7,8,9).  On return spos holds the new
-// positions (pos still holds the substep's start positions = pos_last) and vel the new velocities.
+// positions (pos still holds the substep's start positions = pos_last) and the state block the new velocities.
 template <int G, int MINB, int PPT>
 __device__ __noinline__ void g_rk4(unsigned fixmask) {
     constexpr int U = (G == 128) ? 4 : 3;            // edges per thread in flight: independent sqrt / div chains
@@ -419,7 +466,6 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
     const int t = threadIdx.x;
     const double2* pos = reinterpret_cast<const double2*>(sm + H->o_pos);
     double2* spos = reinterpret_cast<double2*>(sm + H->o_spos);
-    double2* vel = reinterpret_cast<double2*>(sm + H->o_vel);
     const double2* cf = reinterpret_cast<const double2*>(sm + H->o_cf);
     double2* ef = reinterpret_cast<double2*>(sm + H->o_ef);
     double* leq = reinterpret_cast<double*>(sm + H->o_leq);
@@ -428,9 +474,14 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
     const uint32_t* eidx = reinterpret_cast<const uint32_t*>(sm + H->o_eidx);
     const double* ggoal = H->ggoal;
     const int Pd = H->Pd, Ed = H->Ed;
-    double2 sv[PPT], ap[PPT], av[PPT];               // stage velocity and RK4 accumulators of this thread's points
+    MEVO_GPROF(3);
+    double2* gvel = reinterpret_cast<double2*>(H->gstate) + Pd;       // velocities: state block, touched by the owner thread only
+    double2 v0s[PPT], sv[PPT], ap[PPT], av[PPT];     // velocity, stage velocity and RK4 accumulators of this thread's points
 #pragma unroll
-    for (int k = 0; k < PPT; k++) { sv[k] = make_double2(0, 0); ap[k] = sv[k]; av[k] = sv[k]; }
+    for (int k = 0; k < PPT; k++) {
+        sv[k] = make_double2(0, 0); ap[k] = sv[k]; av[k] = sv[k];
+        v0s[k] = (t + k * G < Pd) ? gvel[t + k * G] : sv[k];         // in flight while the first spring pass runs
+    }
 
 #pragma unroll 1
     for (int s = 0; s < 4; s++) {
@@ -461,7 +512,7 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
         for (int k = 0; k < PPT; k++) {
             const int p = t + k * G;
             if (p < Pd) {
-                const double2 v = (s == 0) ? vel[p] : sv[k];
+                const double2 v = (s == 0) ? v0s[k] : sv[k];
                 double Fx = 0.0, Fy = 0.0;
                 {
                     // F -= f over the a sides in edge order, then F += f over the b sides (PhysicsEngine.cpp:530-531): the
@@ -497,7 +548,7 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
                 }
                 const double kpx = v.x * MEVO_DT, kpy = v.y * MEVO_DT;
                 const double kvx = Fx * MEVO_DT, kvy = Fy * MEVO_DT;
-                const double2 x0 = pos[p], v0 = vel[p];
+                const double2 x0 = pos[p], v0 = v0s[k];
                 if (s == 0) {
                     ap[k] = make_double2(kpx, kpy);
                     av[k] = make_double2(kvx, kvy);
@@ -515,7 +566,7 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
                     if ((fixmask >> k) & 1u) { dpx = 0.0; dpy = 0.0; dvx = 0.0; dvy = 0.0; }
                     // the new position goes to spos: pos keeps the substep's start position (= pos_last)
                     spos[p] = make_double2(x0.x + dpx, x0.y + dpy);
-                    vel[p] = make_double2(v0.x + dvx, v0.y + dvy);
+                    gvel[p] = make_double2(v0.x + dvx, v0.y + dvy);
                 }
             }
         }
@@ -535,7 +586,7 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     double2* pos = reinterpret_cast<double2*>(sm + H->o_pos);
     double2* spos = reinterpret_cast<double2*>(sm + H->o_spos);
-    double2* vt = reinterpret_cast<double2*>(sm + H->o_vt);
+    double2* vt = reinterpret_cast<double2*>(H->gstate) + 3 * H->Pd;               // vel_true: state block
     double2* ef = reinterpret_cast<double2*>(sm + H->o_ef);
     const uint4* csr = reinterpret_cast<const uint4*>(sm + H->o_csr);
     const double2* etab = reinterpret_cast<const double2*>(sm + H->o_etab);
@@ -543,6 +594,8 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
     volatile int* misc = reinterpret_cast<volatile int*>(sm + H->o_misc);
     const int Pd = H->Pd, Ed = H->Ed;
 
+    MEVO_GPROF(4);
+    const double4* btab = reinterpret_cast<const double4*>(sm + H->o_btab);
     int viol = 0;
     for (int base = 0; base < Ed; base += U * G) {
 #pragma unroll
@@ -553,14 +606,14 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
             const double2 pa = spos[ix & 0x3ff], pb = spos[(ix >> kEidxBShift) & 0x3ff];
             const double dx = pa.x - pb.x, dy = pa.y - pb.y;
             const double d2 = dx * dx + dy * dy;
-            const double l0 = etab[(ix >> kEidxTypeShift10) & 63].y;
-            const double l2 = l0 * l0;
-            if (valid && !(d2 > l2 * 0.5625001 && d2 < l2 * 1.5624999)) viol |= 1;
-            if (valid && ((ix >> kEidxRigidBit10) & 1u) && !(d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999)) viol |= 2;
+            const double4 bd = btab[(ix >> kEidxTypeShift10) & 63];      // l0^2 * {0.5625001, 1.5624999, 0.9409001, 1.0608999}
+            if (valid && !(d2 > bd.x && d2 < bd.y)) viol |= 1;
+            if (valid && ((ix >> kEidxRigidBit10) & 1u) && !(d2 > bd.z && d2 < bd.w)) viol |= 2;
         }
     }
     viol = cta_or(misc + kGmOr, viol, r);
     if (viol & 1) {
+        MEVO_GPROF(5);
         // Jacobi half (PhysicsEngine.cpp:613-671): corrections from the pre-correction positions, summed per point in edge order
         for (int e = t; e < Ed; e += G) {
             const uint32_t ix = eidx[e];
@@ -604,40 +657,58 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
         __syncthreads();
     }
     if (viol & 2) {
+        MEVO_GPROF(6);
         // ordered rigid-cell pass (PhysicsEngine.cpp:675-710), scheduled in point-disjoint levels that keep the reference's
         // order between visits sharing a point; the first warp walks the (narrow) levels with warp-level synchronisation
         if (warp == 0) {
-            const uint16_t* rlev = H->rlev;
-            const uint16_t* rvis = H->rvis;
+            // the schedule (packed edge word of every visit, level by level) sits in shared memory and the next level's words and
+            // band constants are fetched while the current level computes: what remains on the level-to-level chain is the
+            // position loads, the band test and, for a visit that moves its points, one sqrt -> divide sequence
+            const uint32_t* rsched = reinterpret_cast<const uint32_t*>(sm + H->o_rsched);
+            const uint16_t* rl = reinterpret_cast<const uint16_t*>(sm + H->o_rlev);
             const int n_rlev = H->n_rlev;
+            auto visit = [&](uint32_t ix, double l0, double lo, double hi) {
+                const int a = ix & 0x3ff, b = (ix >> kEidxBShift) & 0x3ff;
+                double2 pa = spos[a], pb = spos[b];
+                const double dx = pa.x - pb.x, dy = pa.y - pb.y;
+                const double d2 = dx * dx + dy * dy;
+                if (d2 > lo && d2 < hi) return;                                   // inside the guarded band: a no-op
+                const double dist = sqrt(d2);
+                const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
+                const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
+                double ox = dx * over_mag, oy = dy * over_mag;
+                double ux = dx * under_mag, uy = dy * under_mag;
+                const double stress = dist / l0;
+                if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
+                if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
+                const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
+                pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
+                spos[a] = pa; spos[b] = pb;
+            };
+            int beg = rl[0], end = rl[1];
+            bool have = beg + lane < end;
+            uint32_t ix = have ? rsched[beg + lane] : 0u;
+            double l0 = etab[(ix >> kEidxTypeShift10) & 63].y;
+            double4 bd = btab[(ix >> kEidxTypeShift10) & 63];
             for (int lv = 0; lv < n_rlev; lv++) {
-                const int i1 = __ldg(rlev + lv + 1);
-                for (int i = __ldg(rlev + lv) + lane; i < i1; i += 32) {
-                    const uint32_t ix = eidx[__ldg(rvis + i)];
-                    const int a = ix & 0x3ff, b = (ix >> kEidxBShift) & 0x3ff;
-                    double2 pa = spos[a], pb = spos[b];
-                    const double dx = pa.x - pb.x, dy = pa.y - pb.y;
-                    const double d2 = dx * dx + dy * dy;
-                    const double l0 = etab[(ix >> kEidxTypeShift10) & 63].y;
-                    const double l2 = l0 * l0;
-                    if (d2 > l2 * 0.9409001 && d2 < l2 * 1.0608999) continue;     // inside the guarded band: a no-op
-                    const double dist = sqrt(d2);
-                    const double over_mag = (dist - l0 * (1 + 0.03)) / (dist * 2);
-                    const double under_mag = (dist - l0 * (1 - 0.03)) / (dist * 2);
-                    double ox = dx * over_mag, oy = dy * over_mag;
-                    double ux = dx * under_mag, uy = dy * under_mag;
-                    const double stress = dist / l0;
-                    if (stress < (1 + 0.03)) { ox = 0.0; oy = 0.0; }
-                    if (stress > (1 - 0.03)) { ux = 0.0; uy = 0.0; }
-                    const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
-                    pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
-                    spos[a] = pa; spos[b] = pb;
+                const int nbeg = end, nend = rl[lv + 2];                           // rl is padded: the last levels read "empty"
+                const bool nhave = nbeg + lane < nend;
+                const uint32_t nix = nhave ? rsched[nbeg + lane] : 0u;
+                const double nl0 = etab[(nix >> kEidxTypeShift10) & 63].y;
+                const double4 nbd = btab[(nix >> kEidxTypeShift10) & 63];
+                if (have) visit(ix, l0, bd.z, bd.w);
+                for (int i = beg + lane + 32; i < end; i += 32) {                  // levels wider than a warp (rare)
+                    const uint32_t jx = rsched[i];
+                    const double4 jb = btab[(jx >> kEidxTypeShift10) & 63];
+                    visit(jx, etab[(jx >> kEidxTypeShift10) & 63].y, jb.z, jb.w);
                 }
                 __syncwarp();
+                beg = nbeg; end = nend; have = nhave; ix = nix; l0 = nl0; bd = nbd;
             }
         }
         __syncthreads();
     }
+    MEVO_GPROF(7);
     // PhysicsEngine::update_true_vel (:602-607) + largest displacement of this substep (neighbour-list validity)
     unsigned dmax = 0;
     if (t == 0) misc[kGmDisp + ((ss + 1) & 1)] = 0;
@@ -674,7 +745,7 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
     const DesignHeader* DH = reinterpret_cast<const DesignHeader*>(db);
     const int Pd = DH->Pd, Ed = DH->Ed, n_leaf = DH->n_leaf;
     double* gstate = prm.state + ed.state_off;
-    const GLayout L = g_layout(Pd, Ed, n_leaf, DH->n_types, DH->cand_cap);
+    const GLayout L = g_layout(Pd, Ed, n_leaf, DH->n_types, DH->cand_cap, DH->n_rvis, DH->n_rlev);
     unsigned fixmask = 0;                               // bit k: point t + k * G is fixed
 
     // ---------------------------------------------------------------- stage in (once per launch)
@@ -685,9 +756,10 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             H->n_rlev = DH->n_rlev; H->n_obj = DH->n_obj;
             H->seg_cap = DH->cand_cap / (G / 32);
             H->lseg_cap = DH->list_cap / (G / 32);
-            H->o_pos = L.o_pos; H->o_spos = L.o_spos; H->o_vel = L.o_vel; H->o_cf = L.o_cf; H->o_vt = L.o_vt; H->o_ef = L.o_ef;
-            H->o_leq = L.o_leq; H->o_aabb = L.o_aabb; H->o_csr = L.o_csr; H->o_etab = L.o_etab; H->o_eidx = L.o_eidx;
-            H->o_lpt = L.o_lpt; H->o_claim = L.o_claim; H->o_cand = L.o_cand; H->o_surv = L.o_surv; H->o_misc = L.o_misc;
+            H->iseg_cap = DH->ilist_cap / (G / 32);
+            H->o_pos = L.o_pos; H->o_spos = L.o_spos; H->o_cf = L.o_cf; H->o_ef = L.o_ef;
+            H->o_leq = L.o_leq; H->o_aabb = L.o_aabb; H->o_csr = L.o_csr; H->o_etab = L.o_etab; H->o_btab = L.o_btab; H->o_eidx = L.o_eidx;
+            H->o_lpt = L.o_lpt; H->o_rsched = L.o_rsched; H->o_rlev = L.o_rlev; H->o_cand = L.o_cand; H->o_surv = L.o_surv; H->o_misc = L.o_misc;
             if (ed.static_off != ~0ull) {
                 const uint8_t* sb = prm.statics + ed.static_off;
                 const StaticHeader* SHp = reinterpret_cast<const StaticHeader*>(sb);
@@ -704,27 +776,20 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             H->g_last = reinterpret_cast<const double2*>(gstate) + 2 * Pd;
             H->pairs = reinterpret_cast<const unsigned int*>(db + DH->o_pairs);
             H->items = reinterpret_cast<const unsigned int*>(db + DH->o_items);
-            H->rlev = reinterpret_cast<const uint16_t*>(db + DH->o_rlev);
-            H->rvis = reinterpret_cast<const uint16_t*>(db + DH->o_rvis);
             H->objs = reinterpret_cast<const ObjRec*>(db + DH->o_obj);
             H->ggoal = gstate + 8 * (size_t)Pd;
             H->list = prm.scratch + (size_t)ed.scratch_off16 * 4;
+            H->ilist = H->list + DH->list_cap;
             H->gstate = gstate;
             H->gstate0 = prm.state0 + ed.state_off;
             H->env = env;
         }
         const double2* g2 = reinterpret_cast<const double2*>(gstate);
         double2* pos = reinterpret_cast<double2*>(sm + L.o_pos);
-        double2* vel = reinterpret_cast<double2*>(sm + L.o_vel);
-        double2* vt = reinterpret_cast<double2*>(sm + L.o_vt);
         uint4* csr = reinterpret_cast<uint4*>(sm + L.o_csr);
-        int* claim = reinterpret_cast<int*>(sm + L.o_claim);
         const unsigned zero_ent = (unsigned)Ed << 1;
         for (int i = t; i < Pd; i += G) {
             pos[i] = g2[i];
-            vel[i] = g2[Pd + i];
-            vt[i] = g2[3 * Pd + i];
-            claim[i] = 0x7fffffff;
             uint4 rec = __ldg(reinterpret_cast<const uint4*>(db + DH->o_csr8) + i);
             unsigned* w = reinterpret_cast<unsigned*>(&rec);
 #pragma unroll
@@ -758,7 +823,22 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             }
         }
         double2* etab = reinterpret_cast<double2*>(sm + L.o_etab);
-        for (int i = t; i < DH->n_types; i += G) etab[i] = __ldg(reinterpret_cast<const double2*>(db + DH->o_etab) + i);
+        double4* btab = reinterpret_cast<double4*>(sm + L.o_btab);
+        for (int i = t; i < DH->n_types; i += G) {
+            const double2 kl = __ldg(reinterpret_cast<const double2*>(db + DH->o_etab) + i);
+            etab[i] = kl;
+            const double l2 = kl.y * kl.y;              // the limiters' guarded bands on squared lengths, as they are evaluated per edge
+            btab[i] = make_double4(l2 * 0.5625001, l2 * 1.5624999, l2 * 0.9409001, l2 * 1.0608999);
+        }
+        {   // rigid-cell visit schedule: packed edge word per visit, level offsets (padded with two copies of the end)
+            uint32_t* rsched = reinterpret_cast<uint32_t*>(sm + L.o_rsched);
+            uint16_t* rl = reinterpret_cast<uint16_t*>(sm + L.o_rlev);
+            const uint16_t* g_rvis = reinterpret_cast<const uint16_t*>(db + DH->o_rvis);
+            const uint16_t* g_rlev = reinterpret_cast<const uint16_t*>(db + DH->o_rlev);
+            for (int i = t; i < DH->n_rvis; i += G)
+                rsched[i] = __ldg(reinterpret_cast<const uint32_t*>(db + DH->o_eidx10) + __ldg(g_rvis + i));
+            for (int i = t; i < DH->n_rlev + 3; i += G) rl[i] = __ldg(g_rlev + min(i, DH->n_rlev));
+        }
         if (t == 0) reinterpret_cast<double2*>(sm + L.o_ef)[Ed] = make_double2(0.0, 0.0);
         uint2* lpt = reinterpret_cast<uint2*>(sm + L.o_lpt);
         for (int l = t; l < n_leaf; l += G) lpt[l] = __ldg(reinterpret_cast<const uint2*>(db + DH->o_lpt16) + l);
@@ -773,8 +853,10 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
     // (everything else the phases need is in the shared-memory header: the loop below keeps a dozen registers live across
     // the out-of-line calls)
 #ifdef MEVO_PROF
-    long long pt0 = clock64();
-    unsigned long long pacc[3] = {0, 0, 0};
+    if (threadIdx.x == 0) {
+        long long* st = reinterpret_cast<long long*>(sm + L.o_misc + 4 * kGmProf);
+        st[0] = clock64(); st[1] = 0;
+    }
 #endif
 
     for (int step = 0; step < prm.n_steps; step++) {
@@ -793,17 +875,8 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             const int cr = g_collide<G, MINB>(rebuild, r, dbg_row, dbg_n, prm.dbg_cand_cap, dbg_cf);
             r = cr >> 1;
             if (rebuild) D = 0.0;
-#ifdef MEVO_PROF
-            { const long long n = clock64(); pacc[0] += n - pt0; pt0 = n; }
-#endif
             g_rk4<G, MINB, PPT>(fixmask);
-#ifdef MEVO_PROF
-            { const long long n = clock64(); pacc[1] += n - pt0; pt0 = n; }
-#endif
             r = g_constrain<G, MINB, PPT>(fixmask, first_substep, r, ss);
-#ifdef MEVO_PROF
-            { const long long n = clock64(); pacc[2] += n - pt0; pt0 = n; }
-#endif
             {
                 const GHdr* H = reinterpret_cast<const GHdr*>(sm);
                 const volatile int* misc = reinterpret_cast<const volatile int*>(sm + H->o_misc);
@@ -815,11 +888,8 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
         }
         if (!unstable) completed_steps++;
     }
-#ifdef MEVO_PROF
-    if (threadIdx.x == 0) for (int q = 0; q < 3; q++) atomicAdd(&g_g2prof[q], pacc[q]);
-#endif
 
-    // ---------------------------------------------------------------- stage out (goals were written at stage in)
+    // ---------------------------------------------------------------- stage out (goals were written at stage in, velocities every substep)
     {
         const GHdr* H = reinterpret_cast<const GHdr*>(sm);
         const int tt = threadIdx.x, n_pts = H->Pd, e_id = H->env;
@@ -833,14 +903,10 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             }
         } else if (!first_substep) {
             const double2* pos = reinterpret_cast<const double2*>(sm + H->o_pos);
-            const double2* vel = reinterpret_cast<const double2*>(sm + H->o_vel);
-            const double2* vt = reinterpret_cast<const double2*>(sm + H->o_vt);
-            for (int i = tt; i < n_pts; i += G) {
+            for (int i = tt; i < n_pts; i += G) {          // vel and vel_true are in place already
                 const double2 x = pos[i];
                 o2[i] = x;
-                o2[n_pts + i] = vel[i];
                 o2[2 * n_pts + i] = x;                     // pos_last = pos after update_true_vel
-                o2[3 * n_pts + i] = vt[i];
             }
         }
         if (tt == 0) {

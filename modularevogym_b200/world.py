@@ -374,3 +374,22 @@ def obstacle_traverser_world(robot: np.ndarray, connections: Optional[np.ndarray
     w.add_from_array("ground", grid, 0, 0)
     w.add_from_array("robot", robot, 2, 4, connections)
     return w
+
+
+BRIDGE_WALKER_PILLARS = (0, 5, 10, 18, 29, 46, 58, 59)     # columns of FIXED voxels from the floor row up to the deck
+
+
+def bridge_walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """BridgeWalker-v0 (``evogym/envs/sim_files/BridgeWalker-v0.json`` + ``evogym/envs/walk.py:152-153``): one 60 x 5 object
+    ``new_object_2`` -- a FIXED floor row, FIXED pillars, and a two-voxel-thick SOFT deck hung between the pillars -- with the
+    robot at voxel (2, 5).  FIXED and SOFT voxels share one object, so the whole terrain is simulated (SURVEY 7 "dead work")."""
+    w = WorldSpec(width=60, height=5)
+    grid = np.zeros((5, 60), dtype=np.int64)          # row 0 = top
+    grid[4, :] = VOXEL_TYPES["FIXED"]
+    grid[0:2, :] = VOXEL_TYPES["SOFT"]
+    for c in BRIDGE_WALKER_PILLARS:
+        grid[:, c] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("new_object_2", grid, 0, 0)
+    w.add_from_array("robot", robot, 2, 5, connections)
+    return w
+
