@@ -13,13 +13,23 @@ from typing import List, Optional, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_ref", "libmevo_ref.so")
+LIB_PATH = os.path.join(_HERE, "_ref", "libmevo_ref.so")                # g++ -O2: the reference's Release default; parity uses this one
+LIB_PATH_O3 = os.path.join(_HERE, "_ref", "libmevo_ref_o3.so")          # g++ -O3 -march=x86-64-v3: CPU-baseline timing only
 
 _lib = None
 
 
-def available() -> bool:
-    return os.path.exists(LIB_PATH)
+def available(opt: str = "O2") -> bool:
+    return os.path.exists(LIB_PATH_O3 if opt == "O3" else LIB_PATH)
+
+
+def use_build(opt: str) -> None:
+    """Select the build this PROCESS loads (call before the first RefSim): "O2" (default) or "O3"."""
+    global _lib, LIB_PATH
+    if _lib is not None:
+        raise RuntimeError("the reference library is already loaded")
+    if opt == "O3":
+        LIB_PATH = LIB_PATH_O3
 
 
 def lib():
