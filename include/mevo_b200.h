@@ -120,6 +120,25 @@ int mevo_batch_step_substeps(mevo_batch* b, int n_steps, int n_substeps, int app
 /* enqueue only; pair with mevo_batch_sync */
 int mevo_batch_step_async(mevo_batch* b, int n_steps, int apply_actions);
 int mevo_batch_sync(mevo_batch* b);
+/* Allocation-free stepping.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * mevo_batch_step_async(b, n_steps, device_actions != NULL) on an already finalized batch, but the call itself allocates
+ * nothing -- no cudaMalloc / cudaFree, no stream or event creation, no allocating library routine: the size classes run back to
+ * back on the batch's stream and the group kernel's neighbour-list scratch is a file-scope `static __device__` array of
+ * MEVO_STATIC_SCRATCH_BYTES (32 MiB, about 1000 environments of 20x20 robots) that every GPU loading the library holds until
+ * the process exits.  A batch whose environments need more scratch than that is refused with MEVO_ERR and a message naming
+ * both sizes; so is a batch that has not been finalized (finalize allocates, this call never does).
+ *   device_actions     : caller's DEVICE buffer, values[env * stride + slot] (stride >= mevo_batch_action_stride);
+ *                        NULL = keep the edge goals as last set (apply_actions = 0)
+ *   device_unstable_out: caller's DEVICE buffer of n_envs bytes receiving the per-environment "unstable" flags;
+ *                        NULL = the batch's own buffer (mevo_batch_unstable_device_ptr)
+ * The state stays in the batch (mevo_env_get_state ...).  Enqueues on the batch's stream and does not sync.  All calls, of
+ * all batches on one GPU, share the one array, which keeps the last call's contents (nothing in it needs to start at zero:
+ * every launch rebuilds the lists it reads): calls that OVERLAP on one GPU -- two batches stepping concurrently through this
+ * entry point -- race on it; serialise them or use mevo_batch_step_async. */
+#define MEVO_STATIC_SCRATCH_BYTES (32u << 20)
+int mevo_batch_step_static_scratch(mevo_batch* b, int n_steps, const double* device_actions, int stride,
+                                   unsigned char* device_unstable_out);
 int mevo_batch_last_launches(const mevo_batch* b);            /* kernels launched by the last step call */
 /* on = 1: an environment whose step reports "unstable" is reverted to snapshot 0 (Sim::revert(0),
  * what the reference's envs do through reset() after the -3 reward, evogym/envs/walk.py:75-78) inside

@@ -61,6 +61,7 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_step": (_i, [_vp, _i, _i, _bp]),
     "mevo_batch_step_substeps": (_i, [_vp, _i, _i, _i, _bp]),
     "mevo_batch_step_async": (_i, [_vp, _i, _i]),
+    "mevo_batch_step_static_scratch": (_i, [_vp, _i, _vp, _i, _vp]),
     "mevo_batch_sync": (_i, [_vp]),
     "mevo_batch_last_launches": (_i, [_vp]),
     "mevo_env_get_time": (C.c_long, [_vp, _i]),
@@ -365,6 +366,11 @@ class Batch:
 
     def step_async(self, n_steps: int = 1, apply_actions: bool = True) -> None:
         _check(self.L.mevo_batch_step_async(self.h, int(n_steps), int(apply_actions)))
+
+    def step_static_scratch(self, n_steps: int, actions_device_ptr: int, stride: int, unstable_device_ptr: int = 0) -> None:
+        """allocation-free variant of ``step_async`` (``mevo_batch_step_static_scratch``): device action / flag buffers of the caller"""
+        _check(self.L.mevo_batch_step_static_scratch(self.h, int(n_steps), C.c_void_p(actions_device_ptr or None), int(stride),
+                                                     C.c_void_p(unstable_device_ptr or None)))
 
     def sync(self) -> None:
         _check(self.L.mevo_batch_sync(self.h))

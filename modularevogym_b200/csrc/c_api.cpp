@@ -276,6 +276,10 @@ int mevo_batch_step_async(mevo_batch* b, int n_steps, int apply_actions) {
     return guard([&] { b->impl.step_async(n_steps, apply_actions != 0, 30); return 0; });
 }
 
+int mevo_batch_step_static_scratch(mevo_batch* b, int n_steps, const double* device_actions, int stride, unsigned char* device_unstable_out) {
+    return guard([&] { b->impl.step_static_scratch(n_steps, device_actions, stride, device_unstable_out); return 0; });
+}
+
 int mevo_batch_sync(mevo_batch* b) {
     return guard([&] { b->impl.sync(); return 0; });
 }

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
@@ -154,6 +155,34 @@ void gstep_dispatch(int cls, int ppt, int variant, GAction what, const StepParam
     }
 }
 
+// ---- allocation-free stepping (Batch::step_static_scratch).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it).  The group kernel's neighbour-list scratch lives in this file-scope device array instead of the
+// cudaMalloc'ed block Batch::finalize sizes: kStaticScratchBytes (32 MiB, ~1000 environments of 20x20 robots) are held by
+// every GPU that loads the library until the process exits.  In HOST code the array's name is only a stand-in for the
+// symbol, not a device address; the address a kernel can use comes from cudaGetSymbolAddress, resolved once per device
+// with that device current.  All calls share the array and it keeps the last call's contents; nothing in it has to start
+// at zero (the kernel rebuilds every list it reads in the first substep of each launch, their lengths live in shared
+// memory), but two calls that overlap on one GPU would race on it.
+constexpr size_t kStaticScratchBytes = 32u << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+std::mutex g_static_scratch_mutex;
+unsigned int* g_static_scratch_ptr[kMaxDevices] = {};
+
+// device address of g_static_scratch on `device` (which must be current)
+unsigned int* static_scratch_address(int device) {
+    if (device < 0 || device >= kMaxDevices) throw std::runtime_error("static scratch: device index out of range");
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (!g_static_scratch_ptr[device]) {
+        void* ptr = nullptr;
+        CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) throw std::runtime_error("static scratch: cudaGetSymbolAddress returned a null address");
+        g_static_scratch_ptr[device] = static_cast<unsigned int*>(ptr);
+    }
+    return g_static_scratch_ptr[device];
+}
+
 __global__ void reset_kernel(double* state, const double* state0, const EnvDesc* envs, const uint8_t* design,
                              const int* env_ids, int n, int* sim_time, uint8_t* unstable) {
     // Environment::revert_to_snapshot(0) (Environment.cpp:247-263): pos, vel <- snapshot; pos_last <- pos;
@@ -186,6 +215,7 @@ struct Batch::Impl {
     int class_ppt[kNumClasses] = {};              // group kernel: points per thread of the class's build (1 or 2)
     int gvariant[kNumClasses] = {};               // group kernel: which register-budget build (gstep_dispatch) the class runs
     unsigned int* d_scratch = nullptr;            // group kernel: neighbour lists
+    size_t scratch_bytes = 0;                     // bytes of neighbour-list scratch this batch's environments address
     double* d_cf = nullptr;                       // test hook: collision_forces of the first substep
     int cta_sync = 1;
     int balance = 1;                              // warp kernel: environments per CTA chosen for equally full waves
@@ -763,6 +793,7 @@ void Batch::finalize() {
     cudaFree(impl_->d_scratch); impl_->d_scratch = nullptr;
     cudaFree(impl_->d_cf); impl_->d_cf = nullptr;
     CUDA_CHECK(cudaMalloc(&impl_->d_scratch, scratch_bytes + 16));
+    impl_->scratch_bytes = scratch_bytes;
     // dynamic shared-memory limits of the kernels this batch launches, on this batch's device
     for (int c = 0; c < kNumClasses; c++) {
         if (impl_->class_envs[c].empty()) continue;
@@ -1131,6 +1162,66 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
 void Batch::sync() {
     CUDA_CHECK(cudaSetDevice(device_));
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+// Sim::step for every environment like step_async, without allocating anything: no cudaMalloc / cudaFree, no stream or event
+// creation (the size classes run back to back on the batch's stream), neighbour lists in the file-scope g_static_scratch.
+// Inputs and outputs are the caller's: `dev_actions` (device, values[env * stride + slot]; nullptr keeps the edge goals as last
+// set) and `dev_unstable_out` (device, num_envs bytes; nullptr = the batch's own flag buffer).  The state stays in the batch.
+void Batch::step_static_scratch(int n_steps, const double* dev_actions, int stride, uint8_t* dev_unstable_out) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_)
+        throw std::runtime_error("step_static_scratch: call finalize first (finalize allocates; this entry point never does)");
+    if (n_steps < 1) throw std::runtime_error("step_static_scratch: n_steps must be >= 1");
+    if (impl_->scratch_bytes > kStaticScratchBytes)
+        throw std::runtime_error("step_static_scratch: this batch needs " + std::to_string(impl_->scratch_bytes) +
+                                 " bytes of neighbour-list scratch, the static array holds " + std::to_string(kStaticScratchBytes) +
+                                 " (MEVO_STATIC_SCRATCH_BYTES): use fewer / smaller environments per batch or mevo_batch_step_async");
+    if (dev_actions && stride < act_stride_)
+        throw std::runtime_error("step_static_scratch: stride smaller than the batch's action stride");
+    StepParams prm;
+    prm.design = d_design_;
+    prm.statics = d_static_;
+    prm.state = d_state_;
+    prm.act = dev_actions ? dev_actions : d_act_;
+    prm.act_stride = dev_actions ? stride : act_stride_;
+    prm.state0 = d_state0_;
+    prm.auto_reset = auto_reset_ ? 1 : 0;
+    prm.unstable_events = d_events_;
+    prm.envs = reinterpret_cast<const EnvDesc*>(d_envdesc_);
+    prm.n_steps = n_steps;
+    prm.n_substeps = 30;
+    prm.apply_actions = dev_actions ? 1 : 0;
+    prm.cta_sync = impl_->cta_sync;
+    prm.unstable = dev_unstable_out ? dev_unstable_out : d_unstable_;
+    prm.sim_time = d_time_;
+    prm.err = d_err_;
+    prm.dbg_cand = nullptr;
+    prm.dbg_cand_n = nullptr;
+    prm.dbg_cand_cap = 0;
+    prm.dbg_cf = nullptr;
+    prm.scratch = static_scratch_address(device_);          // NOT g_static_scratch itself: that name is a host-side stand-in
+    cudaStream_t st = (cudaStream_t)stream_;
+    stats_.launches = 0;
+    for (int c = kNumClasses - 1; c >= 0; c--) {
+        const int n = (int)impl_->class_envs[c].size();
+        if (n == 0) continue;
+        prm.class_envs = d_class_envs_ + impl_->class_off[c];
+        prm.n_class_envs = n;
+        switch (c) {
+            case 0:
+                if (impl_->wepc == 8) launch_wstep<MEVO_WCAPS_A, 8, 2>(prm, impl_->n_sm, impl_->balance != 0, st);
+                else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, impl_->n_sm, impl_->balance != 0, st);
+                else launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, impl_->n_sm, impl_->balance != 0, st);
+                break;
+            case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
+            case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c], impl_->gvariant[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
+        }
+        CUDA_CHECK(cudaGetLastError());
+        stats_.launches++;
+    }
+    for (auto& e : envs_) e.host_fresh = false;
 }
 
 int Batch::step(int n_steps, bool apply_actions, uint8_t* unstable_host, int n_substeps) {

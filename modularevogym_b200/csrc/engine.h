@@ -79,6 +79,8 @@ public:
     int step(int n_steps, bool apply_actions, uint8_t* unstable_host, int n_substeps = 30);
     void step_async(int n_steps, bool apply_actions, int n_substeps = 30);   // no host sync
     void sync();
+    // allocation-free variant of step_async (no counterpart in the reference; engine.cu: g_static_scratch)
+    void step_static_scratch(int n_steps, const double* dev_actions, int stride, uint8_t* dev_unstable_out);
     const uint8_t* unstable_device_ptr() const { return d_unstable_; }
     const int* time_device_ptr() const { return d_time_; }
 
