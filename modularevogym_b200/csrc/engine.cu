@@ -270,6 +270,12 @@ Batch::~Batch() {
                 std::fprintf(stderr, "[prof] group kernel, share of CTA cycles:");
                 for (int q = 0; q < 8; q++) std::fprintf(stderr, " %s %.3f", names[q], (double)gp[q] / tot);
                 std::fprintf(stderr, "\n");
+                unsigned long long gc[8];
+                if (cudaMemcpyFromSymbol(gc, g_g2cnt, sizeof(gc)) == cudaSuccess && gc[0]) {
+                    const double n = (double)gc[0];
+                    std::fprintf(stderr, "[prof] per CTA-substep: list rebuilds %.3f survivors %.2f contact batches %.3f contact rounds %.3f jacobi %.3f "
+                                 "rigid pass %.3f rigid moves %.2f\n", gc[1] / n, gc[2] / n, gc[3] / n, gc[4] / n, gc[5] / n, gc[6] / n, gc[7] / n);
+                }
             }
         }
     }
