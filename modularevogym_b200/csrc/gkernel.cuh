@@ -155,8 +155,15 @@ __device__ unsigned long long g_g2prof[8];
             _st[0] = _n; _st[1] = (k);                                                            \
         }                                                                                         \
     } while (0)
+// [0] substeps [1] list rebuilds [2] survivors [3] contact batches [4] contact rounds [5] substeps with Jacobi [6] substeps with
+// rigid pass [7] rigid visits that moved their points
+__device__ unsigned long long g_g2cnt[8];
+#define MEVO_GCOUNT(k, v) do { if (threadIdx.x == 0) atomicAdd(&g_g2cnt[k], (unsigned long long)(v)); } while (0)
+#define MEVO_GCOUNT_ANY(k, v) atomicAdd(&g_g2cnt[k], (unsigned long long)(v))
 #else
 #define MEVO_GPROF(k)
+#define MEVO_GCOUNT(k, v)
+#define MEVO_GCOUNT_ANY(k, v)
 #endif
 
 // =================================================================================== phase 1: collisions
@@ -184,6 +191,8 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
     unsigned int* surv = surv_all + warp * seg_cap;
 
     MEVO_GPROF(0);
+    MEVO_GCOUNT(0, 1);
+    MEVO_GCOUNT(1, rebuild);
     // ---- K2a: leaf boxes (a-4), zero collision_forces
     for (int l = t; l < n_leaf; l += G) {
         const uint2 lp = lpt[l];
@@ -400,6 +409,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
             for (int w = 0; w < NW; w++) n_surv += scount[w];
             if (n_surv > 0) {
                 MEVO_GPROF(2);
+                MEVO_GCOUNT(2, n_surv);
                 // ---- K3b: resolve survivors, apply their contacts (a-5, a-6)
                 PointSrc src;
                 src.dyn_pos = pos; src.dyn_vt = vt; src.st_pos = H->st_pos;
@@ -421,7 +431,9 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
                     }
                     // Contacts are applied in rounds: the lowest-numbered unapplied contact on each of its points goes
                     // first, so every point receives its contacts in list order -- the sums of a serial walk of the list.
+                    MEVO_GCOUNT(3, 1);
                     while (cta_or(misc + kGmOr, pending ? 1 : 0, r)) {
+                        MEVO_GCOUNT(4, 1);
                         if (pending) {
                             if (!c.p_static) atomicMin(&claim[c.p], gi);
                             if (!c.ab_static) { atomicMin(&claim[c.a], gi); atomicMin(&claim[c.b], gi); }
@@ -614,6 +626,7 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
     viol = cta_or(misc + kGmOr, viol, r);
     if (viol & 1) {
         MEVO_GPROF(5);
+        MEVO_GCOUNT(5, 1);
         // Jacobi half (PhysicsEngine.cpp:613-671): corrections from the pre-correction positions, summed per point in edge order
         for (int e = t; e < Ed; e += G) {
             const uint32_t ix = eidx[e];
@@ -658,6 +671,7 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
     }
     if (viol & 2) {
         MEVO_GPROF(6);
+        MEVO_GCOUNT(6, 1);
         // ordered rigid-cell pass (PhysicsEngine.cpp:675-710), scheduled in point-disjoint levels that keep the reference's
         // order between visits sharing a point; the first warp walks the (narrow) levels with warp-level synchronisation
         if (warp == 0) {
@@ -684,6 +698,7 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
                 const double cx = (ox + ux) * 0.5, cy = (oy + uy) * 0.5;
                 pa.x -= cx; pa.y -= cy; pb.x += cx; pb.y += cy;
                 spos[a] = pa; spos[b] = pb;
+                MEVO_GCOUNT_ANY(7, 1);
             };
             int beg = rl[0], end = rl[1];
             bool have = beg + lane < end;
