@@ -48,7 +48,9 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     deps = [os.path.join(CSRC, s) for s in LIB_SOURCES + LIB_HEADERS]
     if force or _stale(LIB_PATH, deps):
         extra = os.environ.get("MEVO_NVCC_EXTRA", "").split()          # development only (e.g. -DMEVO_PROF)
-        cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH] + \
+        # --exclude-libs,ALL: symbols of static archives (libstdc++.a where the toolchain links it statically, cudart_static) stay
+        # private to this library instead of mixing with another libstdc++ loaded in the process (numpy, torch)
+        cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-Xlinker", "--exclude-libs,ALL", "-o", LIB_PATH] + \
               [os.path.join(CSRC, s) for s in LIB_SOURCES]
         if verbose:
             print(" ".join(cmd))
@@ -67,7 +69,7 @@ def build_pymodule(force: bool = False, verbose: bool = False) -> str:
         cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden",
                "-I", pybind11.get_include(), "-I", sysconfig.get_paths()["include"],
                "-I", os.path.join(PKG_DIR, "..", "include"),
-               src, "-o", PYMOD_PATH, "-L", PKG_DIR, "-lmevo_b200", "-Wl,-rpath,$ORIGIN"]
+               src, "-o", PYMOD_PATH, "-L", PKG_DIR, "-lmevo_b200", "-Wl,-rpath,$ORIGIN", "-Wl,--exclude-libs,ALL"]
         if verbose:
             print(" ".join(cmd))
         subprocess.check_call(cmd)

@@ -46,6 +46,7 @@ def lib():
             "mref_create": (vp, [i, i]),
             "mref_destroy": (None, [vp]),
             "mref_add_object": (i, [vp, dp, i, i, dp, i, cp, d, d, i, i]),
+            "mref_add_object_from_file": (i, [vp, cp, cp, d, d, i, i]),
             "mref_num_points": (i, [vp]),
             "mref_num_edges": (i, [vp]),
             "mref_num_objects": (i, [vp]),
@@ -129,6 +130,13 @@ class RefSim:
         cn = np.ascontiguousarray(connections, dtype=np.float64).reshape(2, -1)
         ok = self.L.mref_add_object(self.h, _dp(g), g.shape[1], g.shape[0], _dp(cn), cn.shape[1],
                                     name.encode(), float(x), float(y), int(bool(is_robot)), int(self.quiet))
+        if ok:
+            self.object_names.append(name)
+        return bool(ok)
+
+    def add_object_from_file(self, path: str, name: str, x: float, y: float, is_robot: bool) -> bool:
+        """``Sim::read_robot_from_file`` / ``read_object_from_file``: the reference's own text loader (ObjectCreator.cpp:118-171)"""
+        ok = self.L.mref_add_object_from_file(self.h, str(path).encode(), name.encode(), float(x), float(y), int(bool(is_robot)), int(self.quiet))
         if ok:
             self.object_names.append(name)
         return bool(ok)

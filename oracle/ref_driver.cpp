@@ -126,6 +126,19 @@ int mref_add_object(void* h, const double* grid, int w, int hgt, const double* c
     return ok ? 1 : 0;
 }
 
+// Sim::read_object_from_file / read_robot_from_file (Sim.cpp:30-48 -> ObjectCreator.cpp:118-171): the reference's own text loader
+int mref_add_object_from_file(void* h, const char* file, const char* name, double x, double y, int is_robot, int quiet) {
+    bool ok;
+    if (quiet) {
+        SilenceStdout s;
+        ok = is_robot ? sim(h).read_robot_from_file(file, name, x, y) : sim(h).read_object_from_file(file, name, x, y);
+    } else {
+        ok = is_robot ? sim(h).read_robot_from_file(file, name, x, y) : sim(h).read_object_from_file(file, name, x, y);
+    }
+    if (ok) static_cast<RefSim*>(h)->names.push_back(name);
+    return ok ? 1 : 0;
+}
+
 int mref_num_points(void* h) { return env(h).get_num_points(); }
 int mref_num_edges(void* h) { return env(h).get_num_edges(); }
 int mref_num_objects(void* h) { return (int)env(h).get_objects()->size(); }
