@@ -164,6 +164,21 @@ int mevo_env_translate_object(mevo_batch* b, int env, const char* name, double d
 /* batched reset = Sim::revert(0) for the listed environments (goals are NOT reset, like the reference) */
 int mevo_batch_save_reset_state(mevo_batch* b);
 int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n);    /* env_ids NULL = all */
+/* Batched snapshot history: Environment::save_snapshot / revert_to_snapshot(t) / Sim::revert (Environment.cpp:239-263,
+ * Sim.cpp:126-133) for every environment at once, in a small fixed number of DEVICE-resident slots instead of the reference's
+ * unbounded per-step std::map (a batch of 65 536 environments cannot keep every step).  Slot 0 is the reset snapshot
+ * (mevo_batch_save_reset_state / mevo_batch_reset); slots 1 .. MEVO_SNAPSHOT_SLOTS - 1 are the caller's.  A snapshot holds pos,
+ * vel and the environment's time, like the reference's; revert restores pos, vel, sets pos_last = pos and vel_true = vel, sets
+ * the time to the snapshot's and leaves length_eq_goal alone ("goals are not reverted").  Reverting to an empty slot prints
+ * the reference's "Error: Could not revert simulation - no save found for time argument." and does nothing.
+ * mevo_batch_finalize drops all slots except 0 (the packing changes).  The pybind `Sim` keeps the reference's full per-step
+ * history for its single environment on the host. */
+#define MEVO_SNAPSHOT_SLOTS 8
+int mevo_batch_save_snapshot(mevo_batch* b, int slot);
+int mevo_batch_revert(mevo_batch* b, const int* env_ids, int n, int slot);     /* env_ids NULL = all environments */
+/* Sim::pos_at_time / vel_at_time of one environment from a slot: (P, 2) doubles each, global numbering, either may be NULL.
+ * Returns the time stored with the snapshot, -1 for an empty slot, < -1 on error. */
+long mevo_env_read_snapshot(mevo_batch* b, int env, int slot, double* pos, double* vel);
 /* centre of mass (mean of point positions) of object `obj` in every env: out = n_envs x 2 doubles (host) */
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out);
 /* What a rollout loop reads after mevo_batch_step_async, in one host round trip: the unstable flags of that step (n_envs bytes)

@@ -73,6 +73,9 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_env_translate_object": (_i, [_vp, _i, _cp, _d, _d]),
     "mevo_batch_save_reset_state": (_i, [_vp]),
     "mevo_batch_reset": (_i, [_vp, _ip, _i]),
+    "mevo_batch_save_snapshot": (_i, [_vp, _i]),
+    "mevo_batch_revert": (_i, [_vp, _ip, _i, _i]),
+    "mevo_env_read_snapshot": (C.c_long, [_vp, _i, _i, _dp, _dp]),
     "mevo_batch_object_com": (_i, [_vp, _i, _dp]),
     "mevo_batch_object_orientation": (_i, [_vp, _i, _dp]),
     "mevo_batch_object_orientation_device": (_i, [_vp, _i, _vp]),
@@ -417,6 +420,25 @@ class Batch:
         else:
             ids = np.ascontiguousarray(env_ids, dtype=np.int32)
             _check(self.L.mevo_batch_reset(self.h, _iptr(ids), ids.size))
+
+    def save_snapshot(self, slot: int) -> None:
+        _check(self.L.mevo_batch_save_snapshot(self.h, int(slot)))
+
+    def revert(self, slot: int, env_ids: Optional[Sequence[int]] = None) -> None:
+        if env_ids is None:
+            _check(self.L.mevo_batch_revert(self.h, None, 0, int(slot)))
+        else:
+            ids = np.ascontiguousarray(env_ids, dtype=np.int32)
+            _check(self.L.mevo_batch_revert(self.h, _iptr(ids), ids.size, int(slot)))
+
+    def read_snapshot(self, env: int, slot: int):
+        """(pos, vel, time) of environment ``env`` in snapshot ``slot``; ``None`` for an empty slot"""
+        P = self.num_points(env)
+        pos, vel = np.zeros((P, 2)), np.zeros((P, 2))
+        t = int(self.L.mevo_env_read_snapshot(self.h, int(env), int(slot), _dptr(pos), _dptr(vel)))
+        if t < -1:
+            raise MevoError(self.L.mevo_last_error().decode())
+        return None if t == -1 else (pos, vel, t)
 
     def object_com(self, obj: int, out: Optional[np.ndarray] = None) -> np.ndarray:
         if out is None:

@@ -329,6 +329,20 @@ int mevo_batch_reset(mevo_batch* b, const int* env_ids, int n) {
     });
 }
 
+int mevo_batch_save_snapshot(mevo_batch* b, int slot) {
+    return guard([&] { b->impl.save_snapshot(slot); return 0; });
+}
+
+int mevo_batch_revert(mevo_batch* b, const int* env_ids, int n, int slot) {
+    return guard([&] { b->impl.revert_envs(env_ids, n, slot); return 0; });
+}
+
+long mevo_env_read_snapshot(mevo_batch* b, int env, int slot, double* pos, double* vel) {
+    long t = MEVO_ERR;
+    const int rc = guard([&] { t = b->impl.read_snapshot(env, slot, pos, vel); return 0; });
+    return rc < 0 ? (long)MEVO_ERR - 1 : t;
+}
+
 int mevo_batch_object_com(mevo_batch* b, int obj, double* out) {
     return guard([&] { b->impl.object_com(obj, out); return 0; });
 }

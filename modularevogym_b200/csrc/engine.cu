@@ -201,6 +201,24 @@ __global__ void reset_kernel(double* state, const double* state0, const EnvDesc*
     if (threadIdx.x == 0) { sim_time[env] = 0; unstable[env] = 0; }
 }
 
+// Environment::revert_to_snapshot(t) (Environment.cpp:247-263) from a device-resident snapshot slot: pos, vel <- slot;
+// pos_last <- pos; vel_true <- vel; sim_time <- the slot's time; length_eq_goal is NOT touched.
+__global__ void revert_kernel(double* state, const double* slot, const int* slot_time, const EnvDesc* envs, const uint8_t* design,
+                              const int* env_ids, int n, int* sim_time, uint8_t* unstable) {
+    const int k = blockIdx.x;
+    if (k >= n) return;
+    const int env = env_ids ? env_ids[k] : k;
+    const EnvDesc ed = envs[env];
+    const int Pd = reinterpret_cast<const DesignHeader*>(design + ed.design_off)->Pd;
+    double2* s = reinterpret_cast<double2*>(state + ed.state_off);
+    const double2* s0 = reinterpret_cast<const double2*>(slot + ed.state_off);
+    for (int i = threadIdx.x; i < Pd; i += blockDim.x) {
+        const double2 p = s0[i], v = s0[Pd + i];
+        s[i] = p; s[Pd + i] = v; s[2 * Pd + i] = p; s[3 * Pd + i] = v;
+    }
+    if (threadIdx.x == 0) { sim_time[env] = slot_time[env]; unstable[env] = 0; }
+}
+
 }  // namespace
 
 struct Batch::Impl {
@@ -216,6 +234,11 @@ struct Batch::Impl {
     int gvariant[kNumClasses] = {};               // group kernel: which register-budget build (gstep_dispatch) the class runs
     unsigned int* d_scratch = nullptr;            // group kernel: neighbour lists
     size_t scratch_bytes = 0;                     // bytes of neighbour-list scratch this batch's environments address
+    // device-resident snapshot slots (Environment::save_snapshot / revert_to_snapshot, batched): a copy of the state buffer and of
+    // the per-environment times each, allocated on first use of the slot
+    static constexpr int kSlots = 8;
+    double* d_slot[kSlots] = {};
+    int* d_slot_time[kSlots] = {};
     double* d_cf = nullptr;                       // test hook: collision_forces of the first substep
     int cta_sync = 1;
     int balance = 1;                              // warp kernel: environments per CTA chosen for equally full waves
@@ -303,6 +326,7 @@ Batch::~Batch() {
     if (impl_) {
         cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); cudaFree(impl_->d_ids);
         cudaFree(impl_->d_scratch); cudaFree(impl_->d_cf);
+        for (int k = 0; k < Impl::kSlots; k++) { cudaFree(impl_->d_slot[k]); cudaFree(impl_->d_slot_time[k]); }
         for (int c = 0; c < kNumClasses; c++) {
             if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
             if (impl_->class_done[c]) cudaEventDestroy(impl_->class_done[c]);
@@ -798,6 +822,10 @@ void Batch::finalize() {
     CUDA_CHECK(cudaMalloc(&d_err_, sizeof(int) * n));
     cudaFree(impl_->d_scratch); impl_->d_scratch = nullptr;
     cudaFree(impl_->d_cf); impl_->d_cf = nullptr;
+    for (int k = 0; k < Impl::kSlots; k++) {        // snapshot slots hold the old packing: dropped
+        cudaFree(impl_->d_slot[k]); impl_->d_slot[k] = nullptr;
+        cudaFree(impl_->d_slot_time[k]); impl_->d_slot_time[k] = nullptr;
+    }
     CUDA_CHECK(cudaMalloc(&impl_->d_scratch, scratch_bytes + 16));
     impl_->scratch_bytes = scratch_bytes;
     // dynamic shared-memory limits of the kernels this batch launches, on this batch's device
@@ -1316,6 +1344,89 @@ void Batch::reset_all() {
                                                                 nullptr, num_envs(), d_time_, d_unstable_);
     CUDA_CHECK(cudaGetLastError());
     for (auto& e : envs_) e.host_fresh = false;
+}
+
+// ---- batched snapshot history (Environment::save_snapshot / revert_to_snapshot / Sim::revert, Environment.cpp:239-263,
+// Sim.cpp:126-133): slot 0 is the reset snapshot (save_reset_state / reset_*), slots 1 .. kSlots-1 are the caller's.
+
+void Batch::save_snapshot(int slot) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (slot == 0) { save_reset_state(); return; }
+    if (slot < 0 || slot >= Impl::kSlots) throw std::runtime_error("save_snapshot: slot out of range (0 .. 7)");
+    if (!impl_->d_slot[slot]) {
+        CUDA_CHECK(cudaMalloc(&impl_->d_slot[slot], sizeof(double) * (state_doubles_ + 2)));
+        CUDA_CHECK(cudaMalloc(&impl_->d_slot_time[slot], sizeof(int) * num_envs()));
+    }
+    cudaStream_t st = (cudaStream_t)stream_;
+    CUDA_CHECK(cudaMemcpyAsync(impl_->d_slot[slot], d_state_, sizeof(double) * state_doubles_, cudaMemcpyDeviceToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(impl_->d_slot_time[slot], d_time_, sizeof(int) * num_envs(), cudaMemcpyDeviceToDevice, st));
+}
+
+void Batch::revert_envs(const int* env_ids, int n, int slot) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (slot == 0) {
+        if (env_ids) reset_envs(env_ids, n); else reset_all();
+        return;
+    }
+    if (slot < 0 || slot >= Impl::kSlots) throw std::runtime_error("revert: slot out of range (0 .. 7)");
+    if (!impl_->d_slot[slot]) {
+        // the reference prints and does nothing when no snapshot exists for the time asked (Environment.cpp:249-252)
+        std::printf("Error: Could not revert simulation - no save found for time argument.\n");
+        return;
+    }
+    cudaStream_t st = (cudaStream_t)stream_;
+    const EnvDesc* ed = reinterpret_cast<const EnvDesc*>(d_envdesc_);
+    if (!env_ids) {
+        revert_kernel<<<num_envs(), 64, 0, st>>>(d_state_, impl_->d_slot[slot], impl_->d_slot_time[slot], ed, d_design_, nullptr, num_envs(),
+                                                 d_time_, d_unstable_);
+        CUDA_CHECK(cudaGetLastError());
+        for (auto& e : envs_) e.host_fresh = false;
+        return;
+    }
+    if (n <= 0) return;
+    for (int i = 0; i < n; i++)
+        if (env_ids[i] < 0 || env_ids[i] >= num_envs()) throw std::runtime_error("revert: environment id out of range");
+    if (n > impl_->ids_cap) {
+        cudaFree(impl_->d_ids); impl_->d_ids = nullptr; impl_->ids_cap = 0;
+        CUDA_CHECK(cudaMalloc(&impl_->d_ids, sizeof(int) * n));
+        impl_->ids_cap = n;
+    }
+    CUDA_CHECK(cudaMemcpyAsync(impl_->d_ids, env_ids, sizeof(int) * n, cudaMemcpyHostToDevice, st));
+    revert_kernel<<<n, 64, 0, st>>>(d_state_, impl_->d_slot[slot], impl_->d_slot_time[slot], ed, d_design_, impl_->d_ids, n, d_time_, d_unstable_);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaStreamSynchronize(st));          // env_ids is the caller's (pageable) memory
+    for (int i = 0; i < n; i++) envs_[env_ids[i]].host_fresh = false;
+}
+
+// Sim::pos_at_time / vel_at_time of one environment from a slot (global numbering; points of pruned all-FIXED objects never move
+// and read their construction positions, velocity 0).  Returns the slot's time for that environment, or -1 for an empty slot.
+long Batch::read_snapshot(int env, int slot, double* pos, double* vel) {
+    CUDA_CHECK(cudaSetDevice(device_));
+    if (!finalized_) finalize();
+    if (slot < 0 || slot >= Impl::kSlots) throw std::runtime_error("read_snapshot: slot out of range (0 .. 7)");
+    const double* src = slot == 0 ? d_state0_ : impl_->d_slot[slot];
+    if (!src) return -1;
+    download_state(env);                            // host mirror: static points
+    const EnvHost& e = envs_.at(env);
+    const int Pd = (int)e.dyn_points.size();
+    std::vector<double> s(4 * (size_t)Pd);
+    int t = 0;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (Pd) CUDA_CHECK(cudaMemcpyAsync(s.data(), src + e.state_off, sizeof(double) * s.size(), cudaMemcpyDeviceToHost, st));
+    if (slot != 0) CUDA_CHECK(cudaMemcpyAsync(&t, impl_->d_slot_time[slot] + env, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    if (pos) std::memcpy(pos, e.world.pos.data(), sizeof(double) * e.pos.size());
+    if (vel) std::fill(vel, vel + e.pos.size(), 0.0);
+    for (int k = 0; k < Pd; k++) {
+        const int g = e.dyn_points[k];
+        for (int c = 0; c < 2; c++) {
+            if (pos) pos[2 * g + c] = s[2 * k + c];
+            if (vel) vel[2 * g + c] = s[2 * Pd + 2 * k + c];
+        }
+    }
+    return t;
 }
 
 void Batch::object_com(int obj_index, double* out_host_2n) {

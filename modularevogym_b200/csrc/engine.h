@@ -97,6 +97,10 @@ public:
     void save_reset_state();
     void reset_envs(const int* env_ids, int n);     // Environment::revert_to_snapshot(0) semantics
     void reset_all();
+    // batched snapshot history: slot 0 = the reset snapshot, slots 1 .. 7 the caller's (device-resident copies)
+    void save_snapshot(int slot);                                   // Environment::save_snapshot of every environment
+    void revert_envs(const int* env_ids, int n, int slot);          // Environment::revert_to_snapshot; env_ids nullptr = all
+    long read_snapshot(int env, int slot, double* pos, double* vel); // Sim::pos_at_time / vel_at_time; returns the slot's time or -1
 
     // packed robot positions for the learner side: COM (x, y) of object `obj_index` per env
     void object_com(int obj_index, double* out_host_2n);
