@@ -118,8 +118,10 @@ void configure_wstep() {
 
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 void launch_wstep(StepParams prm, int n_sm, bool balance, cudaStream_t stream) {
-    constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
     prm.envs_per_cta = balance ? balanced_envs_per_cta(prm.n_class_envs, EPC, n_sm * MINB) : EPC;
+    // shared memory for the environments the CTA really takes: what is left of the SM's 228 KB serves as L1 for the static-terrain
+    // tables (grid, boxes, leaf records, points), which the collision phase reads through __ldg
+    const int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * prm.envs_per_cta;
     const int grid = (prm.n_class_envs + prm.envs_per_cta - 1) / prm.envs_per_cta;
     wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
 }
