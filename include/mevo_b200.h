@@ -56,6 +56,10 @@ int mevo_batch_add_object(mevo_batch* b, int env, const double* grid, int w, int
 /* Packs all environments into HBM (struct-of-arrays blobs) and uploads.  Called implicitly by the
  * first step.  May be called again after adding environments/objects; state is preserved. */
 int mevo_batch_finalize(mevo_batch* b);
+/* Number of finalize calls so far (explicit, implicit at the first step, or the re-pack that mevo_env_translate_object does when
+ * it moves an all-FIXED object).  Device pointers handed out and CUDA graphs captured in an earlier epoch are stale: a caller
+ * that caches them compares epochs (modularevogym_b200/vec_env.py re-captures its graph). */
+int mevo_batch_finalize_epoch(const mevo_batch* b);
 
 /* ---- queries --------------------------------------------------------------------------------- */
 int mevo_batch_num_envs(const mevo_batch* b);
@@ -241,6 +245,11 @@ int mevo_batch_task_apply_policy_device(mevo_batch* b, const void* device_action
 /* after mevo_batch_step*: reward (n_envs), done bytes (n_envs), observations (n_envs x stride, zero padded); any
  * output may be NULL.  reset_done = 1: environments that are done are reverted to snapshot 0 first and their
  * observation is the reset observation (vec-env semantics). */
+/* NOTE on unstable steps: Sim::step leaves the partially advanced state live and its getters read the last SAVED snapshot
+ * (Sim.cpp:105-115, history[sim_time]).  With reset_done = 1 (the vec-env semantics this layer is built for) an unstable
+ * environment is reverted and reports the reset observation, like the reference's worker.  With reset_done = 0 the observation
+ * of an unstable environment is computed from the live, partially advanced state -- reward and done are exact either way; a
+ * caller that needs the pre-step observation keeps it from the previous call or reverts a snapshot slot. */
 int mevo_batch_task_outputs(mevo_batch* b, double* reward, unsigned char* done, double* flat, int flat_stride, double* modular,
                             int modular_stride, double* other, int other_stride, int reset_done);
 int mevo_batch_task_outputs_device(mevo_batch* b, void* reward, unsigned char* done, void* flat, int flat_stride, void* modular,

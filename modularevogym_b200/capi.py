@@ -28,6 +28,7 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_begin_env": (_i, [_vp, _i, _i]),
     "mevo_batch_add_object": (_i, [_vp, _i, _dp, _i, _i, _dp, _i, _cp, _d, _d, _i]),
     "mevo_batch_finalize": (_i, [_vp]),
+    "mevo_batch_finalize_epoch": (_i, [_vp]),
     "mevo_batch_num_envs": (_i, [_vp]),
     "mevo_env_num_points": (_i, [_vp, _i]),
     "mevo_env_num_edges": (_i, [_vp, _i]),
@@ -273,6 +274,10 @@ class Batch:
 
     def finalize(self) -> None:
         _check(self.L.mevo_batch_finalize(self.h))
+
+    @property
+    def finalize_epoch(self) -> int:
+        return self.L.mevo_batch_finalize_epoch(self.h)
 
     # -- queries
     @property

@@ -138,6 +138,10 @@ int mevo_batch_finalize(mevo_batch* b) {
     return guard([&] { b->impl.finalize(); return 0; });
 }
 
+int mevo_batch_finalize_epoch(const mevo_batch* b) {
+    return b ? b->impl.finalize_epoch() : MEVO_ERR;
+}
+
 int mevo_batch_num_envs(const mevo_batch* b) { return b->impl.num_envs(); }
 int mevo_env_num_points(const mevo_batch* b, int env) { return guard([&] { return b->impl.world(env).num_points(); }); }
 int mevo_env_num_edges(const mevo_batch* b, int env) { return guard([&] { return b->impl.world(env).num_edges(); }); }

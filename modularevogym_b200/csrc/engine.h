@@ -49,6 +49,7 @@ public:
     int device() const { return device_; }
     int num_envs() const { return (int)envs_.size(); }
     bool finalized() const { return finalized_; }
+    int finalize_epoch() const { return finalize_epoch_; }      // bumped by every finalize(): device pointers and graphs of older epochs are stale
 
     int begin_env(int world_w, int world_h);
     bool add_object(int env, const double* grid, int w, int h, const double* conn, int k,

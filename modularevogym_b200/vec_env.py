@@ -92,6 +92,7 @@ class BatchedEvoGymEnv:
         # eager step, replayed afterwards; the policy output is copied into a persistent buffer the graph reads
         self.use_graph = use_graph
         self._graph = None
+        self._graph_epoch = -1
         self._graph_dtype = None
         self._actions = None
         self._eager_steps = 0
@@ -129,6 +130,8 @@ class BatchedEvoGymEnv:
         if a.shape != (self.num_envs, self.action_width):
             raise ValueError(f"actions must have shape {(self.num_envs, self.action_width)}, got {tuple(a.shape)}")
         cur = torch.cuda.current_stream(self.device)
+        if self._graph is not None and self.B.finalize_epoch != self._graph_epoch:
+            self._graph, self._eager_steps = None, 0            # the batch was re-packed (e.g. translate_object on terrain): re-capture
         if self.use_graph and self._graph is not None and a.dtype == self._graph_dtype:
             self._actions.copy_(a)
             self._stream.wait_stream(cur)
@@ -165,6 +168,7 @@ class BatchedEvoGymEnv:
             self._enqueue_step(self._actions.data_ptr(), self.action_width, like.dtype == torch.float32)
         finally:
             self._graph = self.B.capture_end()
+            self._graph_epoch = self.B.finalize_epoch
 
     def _wait(self):
         self.torch.cuda.current_stream(self.device).wait_stream(self._stream)
