@@ -23,7 +23,6 @@
 
 namespace mevo {
 
-constexpr int kMaxWarpsPerGroup = 16;    // group sizes 32 .. 512
 constexpr int kMaxDynObjects = 8;        // dynamic objects per environment (3-bit field in pair codes)
 constexpr int kMaxLeaves = 4095;         // 12-bit leaf ids in pair / candidate codes
 

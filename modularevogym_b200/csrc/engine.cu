@@ -136,7 +136,7 @@ void gstep_do(GAction what, const StepParams* prm, int smem, cudaStream_t stream
         gstep_kernel<G, MINB, PPT><<<prm->n_class_envs, G, smem, stream>>>(*prm);
 }
 
-void gstep_dispatch(int cls, int ppt, int variant, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
+void gstep_dispatch(int cls, int ppt, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
     const int g = kGroupSizes[cls];
     if (ppt > 2) {
         if (g == 64) gstep_do<64, 8, 4>(what, prm, smem, stream);
@@ -146,7 +146,6 @@ void gstep_dispatch(int cls, int ppt, int variant, GAction what, const StepParam
     } else if (ppt == 2) {
         if (g == 64) gstep_do<64, 8, 2>(what, prm, smem, stream);
         else if (g == 128) gstep_do<128, 4, 2>(what, prm, smem, stream);
-        else if (g == 256 && variant == 1) gstep_do<256, 3, 2>(what, prm, smem, stream);
         else if (g == 256) gstep_do<256, 2, 2>(what, prm, smem, stream);
         else gstep_do<512, 1, 2>(what, prm, smem, stream);
     } else {
@@ -233,7 +232,6 @@ struct Batch::Impl {
     bool use_warp_kernel = true;
     int wepc = 0;                                 // warp kernel: environments per CTA override (0 = default)
     int class_ppt[kNumClasses] = {};              // group kernel: points per thread of the class's build (1 or 2)
-    int gvariant[kNumClasses] = {};               // group kernel: which register-budget build (gstep_dispatch) the class runs
     unsigned int* d_scratch = nullptr;            // group kernel: neighbour lists
     size_t scratch_bytes = 0;                     // bytes of neighbour-list scratch this batch's environments address
     // device-resident snapshot slots (Environment::save_snapshot / revert_to_snapshot, batched): a copy of the state buffer and of
@@ -267,10 +265,6 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     cudaStream_t s;
     CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     stream_ = s;
-    // development: MEVO_GVARIANT = one digit per group class (64, 128, 256, 512 threads), 0 / 1 = the two register budgets
-    for (int c = kFirstGroupClass; c < kNumClasses; c++) impl_->gvariant[c] = 0;
-    if (const char* e = std::getenv("MEVO_GVARIANT"))
-        for (int c = kFirstGroupClass; c < kNumClasses && e[c - kFirstGroupClass]; c++) impl_->gvariant[c] = e[c - kFirstGroupClass] == '1';
     if (const char* e = std::getenv("MEVO_NO_WKERNEL")) impl_->use_warp_kernel = std::atoi(e) == 0;
     if (const char* e = std::getenv("MEVO_WEPC")) impl_->wepc = std::atoi(e);
     if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
@@ -839,7 +833,7 @@ void Batch::finalize() {
             else configure_wstep<MEVO_WCAPS_A, 16, 1>();
         } else if (c == 1) configure_wstep<MEVO_WCAPS_C, 12, 1>();
         else if (c == 2) configure_wstep<MEVO_WCAPS_B, 10, 1>();
-        else gstep_dispatch(c, impl_->class_ppt[c], impl_->gvariant[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
+        else gstep_dispatch(c, impl_->class_ppt[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
     }
     if (!d_events_) { CUDA_CHECK(cudaMalloc(&d_events_, sizeof(unsigned long long))); CUDA_CHECK(cudaMemset(d_events_, 0, sizeof(unsigned long long))); }
     d_act_ext_ = nullptr;
@@ -1183,7 +1177,7 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 break;
             case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            default: gstep_dispatch(c, impl_->class_ppt[c], impl_->gvariant[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
         }
         CUDA_CHECK(cudaGetLastError());
         stats_.launches++;
@@ -1252,7 +1246,7 @@ void Batch::step_static_scratch(int n_steps, const double* dev_actions, int stri
                 break;
             case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            default: gstep_dispatch(c, impl_->class_ppt[c], impl_->gvariant[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
         }
         CUDA_CHECK(cudaGetLastError());
         stats_.launches++;
