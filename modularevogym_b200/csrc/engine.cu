@@ -345,7 +345,9 @@ bool Batch::add_object(int env, const double* grid, int w, int h, const double* 
     EnvHost& e = envs_.at(env);
     if (finalized_) download_all();
     const int P_before = e.world.num_points(), E_before = e.world.num_edges();
+    const size_t objects_before = e.world.objects.size();
     if (!e.world.add_object(grid, w, h, conn, k, name, x, y, is_robot)) return false;
+    if (e.world.objects.size() == objects_before) return true;       // a grid without voxels: success, nothing added (like the reference)
     // extend the host mirror with the new object's rest state (Environment.cpp:44-109)
     const World& W = e.world;
     e.pos.insert(e.pos.end(), W.pos.begin() + 2 * P_before, W.pos.end());

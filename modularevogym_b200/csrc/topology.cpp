@@ -197,10 +197,9 @@ bool World::add_object(const double* grid, int w, int h, const double* conn, int
             std::printf("Error: Could not read in object - object must be connected.\n");
             return false;
         }
-        if (n_comp == 0) {
-            std::printf("Error: Could not read in object - object has no voxels.\n");
-            return false;
-        }
+        // a grid without voxels: the reference reports success and adds nothing (ObjectCreator.cpp:193-641 falls through all its
+        // loops, no SimObject is registered), so a caller sees `true` and an unchanged world
+        if (n_comp == 0) return true;
     }
     if (name_to_index.count(name)) {
         std::printf("Error Could not read in %s %s - duplicate name.\n", is_robot ? "robot" : "object", name.c_str());
