@@ -27,7 +27,7 @@ NVCC_FLAGS = [
 ]
 
 LIB_SOURCES = ["engine.cu", "task.cu", "render.cu", "c_api.cpp", "topology.cpp"]
-LIB_HEADERS = ["engine.h", "kernels.cuh", "wkernel.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
+LIB_HEADERS = ["engine.h", "kernels.cuh", "wkernel.cuh", "gkernel.cuh", "device_layout.h", "topology.h", os.path.join("..", "..", "include", "mevo_b200.h")]
 
 
 def _nvcc() -> str:

@@ -77,7 +77,8 @@ struct DesignHeader {        // 160 bytes
     int o_eidx10;                             // u32 per edge: a | b << 10 | type << 20 | rigid-cell << 26
     int o_lpt16;                              // 8 bytes per leaf: TL, TR, BR, BL point ids, u16 each
     int ilist_cap;                            // neighbour-list entries for the always-candidate items (follows the pair list)
-    int reserved[6];
+    int o_csrx;                               // 0, or (max_deg > 8: unshared duplicate side edges) a second 8-slot record per point
+    int reserved[5];
 };
 static_assert(sizeof(DesignHeader) == 160, "DesignHeader must be 160 bytes");
 

@@ -128,31 +128,40 @@ void launch_wstep(StepParams prm, int n_sm, bool balance, cudaStream_t stream) {
 
 // group kernel builds: (threads, CTAs per SM the register budget is set for, points per thread)
 enum class GAction { Configure, Launch };
-template <int G, int MINB, int PPT>
-void gstep_do(GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
+template <int G, int MINB, int PPT, bool XD>
+void gstep_do2(GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
     if (what == GAction::Configure)
-        CUDA_CHECK(cudaFuncSetAttribute(gstep_kernel<G, MINB, PPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_CHECK(cudaFuncSetAttribute(gstep_kernel<G, MINB, PPT, XD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     else
-        gstep_kernel<G, MINB, PPT><<<prm->n_class_envs, G, smem, stream>>>(*prm);
+        gstep_kernel<G, MINB, PPT, XD><<<prm->n_class_envs, G, smem, stream>>>(*prm);
+}
+template <int G, int MINB, int PPT>
+void gstep_do(bool xd, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
+    if (xd) gstep_do2<G, MINB, PPT, true>(what, prm, smem, stream);
+    else gstep_do2<G, MINB, PPT, false>(what, prm, smem, stream);
 }
 
-void gstep_dispatch(int cls, int ppt, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
+constexpr int kPptExtBit = 8;                 // class_ppt flag: a design of the class has gather slots 8..15 (DesignHeader::o_csrx)
+
+void gstep_dispatch(int cls, int ppt_x, GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
     const int g = kGroupSizes[cls];
+    const bool xd = (ppt_x & kPptExtBit) != 0;
+    const int ppt = ppt_x & ~kPptExtBit;
     if (ppt > 2) {
-        if (g == 64) gstep_do<64, 8, 4>(what, prm, smem, stream);
-        else if (g == 128) gstep_do<128, 4, 4>(what, prm, smem, stream);
-        else if (g == 256) gstep_do<256, 2, 4>(what, prm, smem, stream);
-        else gstep_do<512, 1, 4>(what, prm, smem, stream);
+        if (g == 64) gstep_do<64, 8, 4>(xd, what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 4, 4>(xd, what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 2, 4>(xd, what, prm, smem, stream);
+        else gstep_do<512, 1, 4>(xd, what, prm, smem, stream);
     } else if (ppt == 2) {
-        if (g == 64) gstep_do<64, 8, 2>(what, prm, smem, stream);
-        else if (g == 128) gstep_do<128, 4, 2>(what, prm, smem, stream);
-        else if (g == 256) gstep_do<256, 2, 2>(what, prm, smem, stream);
-        else gstep_do<512, 1, 2>(what, prm, smem, stream);
+        if (g == 64) gstep_do<64, 8, 2>(xd, what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 4, 2>(xd, what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 2, 2>(xd, what, prm, smem, stream);
+        else gstep_do<512, 1, 2>(xd, what, prm, smem, stream);
     } else {
-        if (g == 64) gstep_do<64, 8, 1>(what, prm, smem, stream);
-        else if (g == 128) gstep_do<128, 4, 1>(what, prm, smem, stream);
-        else if (g == 256) gstep_do<256, 2, 1>(what, prm, smem, stream);
-        else gstep_do<512, 1, 1>(what, prm, smem, stream);
+        if (g == 64) gstep_do<64, 8, 1>(xd, what, prm, smem, stream);
+        else if (g == 128) gstep_do<128, 4, 1>(xd, what, prm, smem, stream);
+        else if (g == 256) gstep_do<256, 2, 1>(xd, what, prm, smem, stream);
+        else gstep_do<512, 1, 1>(xd, what, prm, smem, stream);
     }
 }
 
@@ -231,7 +240,8 @@ struct Batch::Impl {
     std::vector<int> env_cost;                    // per env: estimated work of one substep
     bool use_warp_kernel = true;
     int wepc = 0;                                 // warp kernel: environments per CTA override (0 = default)
-    int class_ppt[kNumClasses] = {};              // group kernel: points per thread of the class's build (1 or 2)
+    int class_ppt[kNumClasses] = {};              // group kernel: points per thread of the class's build (1, 2 or 4)
+    int class_xd[kNumClasses] = {};               // kPptExtBit if a design of the class carries gather slots 8..15, else 0
     unsigned int* d_scratch = nullptr;            // group kernel: neighbour lists
     size_t scratch_bytes = 0;                     // bytes of neighbour-list scratch this batch's environments address
     // device-resident snapshot slots (Environment::save_snapshot / revert_to_snapshot, batched): a copy of the state buffer and of
@@ -474,10 +484,17 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.max_deg = max_deg;
     H.unit_mass = 1;
     for (int i = 0; i < Pd; i++) if (mass[i] != 1.0) H.unit_mass = 0;
-    // both kernels rely on what the reference's world builder guarantees (ObjectCreator.h:36-47: mass 1.0; a lattice point
-    // touches at most 4 sides + 4 diagonals)
+    // both kernels rely on what the reference's world builder guarantees (ObjectCreator.h:36-47: mass 1.0).  A lattice point
+    // touches at most 4 sides + 4 diagonals when neighbouring voxels are connected; between UNCONNECTED neighbours the side
+    // edge exists once per voxel, up to 4 more: those designs carry a second record per point (slots 8..15, group kernel only)
     if (!H.unit_mass) throw std::runtime_error("point masses other than 1.0 are not supported");
-    if (max_deg > 8) throw std::runtime_error("a point with more than 8 incident springs is not supported");
+    if (max_deg > 16) throw std::runtime_error("a point with more than 16 incident springs is not supported");
+    std::vector<uint16_t> csrx;
+    if (max_deg > 8) {
+        csrx.assign(8 * (size_t)Pd, 0xffff);
+        for (int i = 0; i < Pd; i++)
+            for (int j = 8; j < csro[i + 1] - csro[i]; j++) csrx[8 * (size_t)i + j - 8] = csre[csro[i] + j];
+    }
     // leaves, objects, pair table
     std::vector<LeafRec> leaves;
     std::vector<ObjRec> objrecs;
@@ -631,6 +648,8 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
         for (int q = 0; q < 4; q++) lpt16.push_back(lr.pt[q]);
     H.warp_ok = warp_ok ? 1 : 0;
     H.o_csr8 = dw.begin_section(); dw.put_array(csr8);
+    H.o_csrx = 0;
+    if (!csrx.empty()) { H.o_csrx = dw.begin_section(); dw.put_array(csrx); }
     H.o_eidx = dw.begin_section(); dw.put_array(eidx);
     H.o_etab = dw.begin_section(); dw.put_array(etab);
     H.o_pairs16 = dw.begin_section(); dw.put_array(pairs16);
@@ -714,6 +733,7 @@ void Batch::finalize() {
     impl_->env_cost.clear();
     size_t state_doubles = 0, scratch_bytes = 0;
     std::memset(impl_->class_ppt, 0, sizeof(impl_->class_ppt));
+    std::memset(impl_->class_xd, 0, sizeof(impl_->class_xd));
     act_stride_ = 1;
 
     auto intern = [](std::vector<uint8_t>& pool, std::unordered_map<uint64_t, std::vector<std::pair<size_t, size_t>>>& index,
@@ -780,6 +800,7 @@ void Batch::finalize() {
             impl_->class_smem[e.cls] = std::max(impl_->class_smem[e.cls], L.total);
             impl_->class_ppt[e.cls] = std::max(impl_->class_ppt[e.cls], (H->Pd + kGroupSizes[e.cls] - 1) / kGroupSizes[e.cls]);
             if (impl_->class_ppt[e.cls] == 3) impl_->class_ppt[e.cls] = 4;
+            if (H->o_csrx) impl_->class_xd[e.cls] = kPptExtBit;
             d.scratch_off16 = (int)(scratch_bytes / 16);
             scratch_bytes += ((size_t)(H->list_cap + H->ilist_cap) * 4 + 15) & ~(size_t)15;
             if (scratch_bytes / 16 > 0x7fffffffull) throw std::runtime_error("neighbour-list scratch exceeds 32 GB");
@@ -835,7 +856,7 @@ void Batch::finalize() {
             else configure_wstep<MEVO_WCAPS_A, 16, 1>();
         } else if (c == 1) configure_wstep<MEVO_WCAPS_C, 12, 1>();
         else if (c == 2) configure_wstep<MEVO_WCAPS_B, 10, 1>();
-        else gstep_dispatch(c, impl_->class_ppt[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
+        else gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
     }
     if (!d_events_) { CUDA_CHECK(cudaMalloc(&d_events_, sizeof(unsigned long long))); CUDA_CHECK(cudaMemset(d_events_, 0, sizeof(unsigned long long))); }
     d_act_ext_ = nullptr;
@@ -1179,7 +1200,7 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
                 break;
             case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            default: gstep_dispatch(c, impl_->class_ppt[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
         }
         CUDA_CHECK(cudaGetLastError());
         stats_.launches++;
@@ -1248,7 +1269,7 @@ void Batch::step_static_scratch(int n_steps, const double* dev_actions, int stri
                 break;
             case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
             case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            default: gstep_dispatch(c, impl_->class_ppt[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
         }
         CUDA_CHECK(cudaGetLastError());
         stats_.launches++;

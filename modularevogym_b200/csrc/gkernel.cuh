@@ -61,6 +61,7 @@ struct GHdr {                                 // first kGHdrBytes of the CTA's s
     const unsigned int* items;
     const ObjRec* objs;
     const double* ggoal;                      // length_eq_goal of this environment (state block)
+    const uint4* csrx;                        // nullptr, or gather slots 8..15 per point (design blob; 0xffff = empty)
     unsigned int* list;                       // neighbour list scratch of this environment: tested pairs ...
     unsigned int* ilist;                      // ... and always-candidate items
     double* gstate;                           // state block of this environment
@@ -140,6 +141,22 @@ __device__ __forceinline__ double2 spring_force10(const double2* sp, uint32_t ix
 
 __device__ __forceinline__ double flip_if(double x, unsigned neg) {      // neg ? -x : x, on the integer pipe (exact)
     return __hiloint2double(__double2hiint(x) ^ (int)(neg << 31), __double2loint(x));
+}
+
+// Gather slots 8..15 of point p (designs with unconnected neighbouring voxels: a side edge per voxel, up to 12 springs on
+// a point).  Continues the a-sides-then-b-sides list of the first record in the same order; read from the design blob.
+__device__ __noinline__ double2 g_gather_ext(const uint4* csrx, const double2* ef, int p, double2 acc) {
+    const uint4 rec = __ldg(csrx + p);
+    const unsigned w[4] = {rec.x, rec.y, rec.z, rec.w};
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const unsigned ent = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+        if (ent == 0xffffu) break;                                      // the list is dense: nothing follows an empty slot
+        const double2 c = ef[ent >> 1];
+        const unsigned neg = (ent & 1u) ^ 1u;
+        acc.x += flip_if(c.x, neg); acc.y += flip_if(c.y, neg);
+    }
+    return acc;
 }
 
 #ifdef MEVO_PROF
@@ -470,7 +487,7 @@ __device__ __noinline__ int g_collide(int rebuild, int r, unsigned int* dbg_row,
 // =================================================================================== phase 2: actuators + RK4
 // PhysicsEngine::update_actuators + step_rk4 + get_pos_vel_slope (SURVEY 8a-7,8,9).  On return spos holds the new
 // positions (pos still holds the substep's start positions = pos_last) and the state block the new velocities.
-template <int G, int MINB, int PPT>
+template <int G, int MINB, int PPT, bool XD>
 __device__ __noinline__ void g_rk4(unsigned fixmask) {
     constexpr int U = (G == 128) ? 4 : 3;            // edges per thread in flight: independent sqrt / div chains
     unsigned char* sm = gsm_raw;
@@ -545,6 +562,7 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
 #pragma unroll
                         for (int j = 0; j < 4; j++) { Fx += flip_if(g[j].x, sg[j]); Fy += flip_if(g[j].y, sg[j]); }
                     }
+                    if (XD && H->csrx) { const double2 a = g_gather_ext(H->csrx, ef, p, make_double2(Fx, Fy)); Fx = a.x; Fy = a.y; }
                 }
                 Fx += v.x * (-MEVO_VISCOUS_DRAG);
                 Fy += v.y * (-MEVO_VISCOUS_DRAG);
@@ -590,7 +608,7 @@ __device__ __noinline__ void g_rk4(unsigned fixmask) {
 // PhysicsEngine::resolve_edge_constraints + update_true_vel (SURVEY 8a-10,11) on the new positions in spos.  Band test on
 // squared lengths (no sqrt), guarded by 1e-7 so the decision never depends on the rounding of dist / L0: inside the band
 // every correction of the reference is exactly zero.  Returns r.
-template <int G, int MINB, int PPT>
+template <int G, int MINB, int PPT, bool XD>
 __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int r, int ss) {
     constexpr int U = (G == 128) ? 4 : 3;
     unsigned char* sm = gsm_raw;
@@ -664,6 +682,7 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
                     const unsigned neg = (ent & 1u) ^ 1u;
                     x.x += flip_if(c.x, neg); x.y += flip_if(c.y, neg);
                 }
+                if (XD && H->csrx) x = g_gather_ext(H->csrx, ef, p, x);
                 spos[p] = x;
             }
         }
@@ -749,7 +768,8 @@ __device__ __noinline__ int g_constrain(unsigned fixmask, int first_substep, int
 }
 
 // =================================================================================== the kernel
-template <int G, int MINB, int PPT>
+// XD: some design of the launch carries gather slots 8..15 (GHdr::csrx); false compiles the extension gather out
+template <int G, int MINB, int PPT, bool XD>
 __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
     static_assert(G % 32 == 0 && G >= 64 && G <= 512, "group size");
     unsigned char* sm = gsm_raw;
@@ -793,6 +813,7 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             H->items = reinterpret_cast<const unsigned int*>(db + DH->o_items);
             H->objs = reinterpret_cast<const ObjRec*>(db + DH->o_obj);
             H->ggoal = gstate + 8 * (size_t)Pd;
+            H->csrx = DH->o_csrx ? reinterpret_cast<const uint4*>(db + DH->o_csrx) : nullptr;
             H->list = prm.scratch + (size_t)ed.scratch_off16 * 4;
             H->ilist = H->list + DH->list_cap;
             H->gstate = gstate;
@@ -890,8 +911,8 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
             const int cr = g_collide<G, MINB>(rebuild, r, dbg_row, dbg_n, prm.dbg_cand_cap, dbg_cf);
             r = cr >> 1;
             if (rebuild) D = 0.0;
-            g_rk4<G, MINB, PPT>(fixmask);
-            r = g_constrain<G, MINB, PPT>(fixmask, first_substep, r, ss);
+            g_rk4<G, MINB, PPT, XD>(fixmask);
+            r = g_constrain<G, MINB, PPT, XD>(fixmask, first_substep, r, ss);
             {
                 const GHdr* H = reinterpret_cast<const GHdr*>(sm);
                 const volatile int* misc = reinterpret_cast<const volatile int*>(sm + H->o_misc);
