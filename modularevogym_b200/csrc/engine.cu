@@ -259,6 +259,17 @@ struct Batch::Impl {
     cudaEvent_t class_done[kNumClasses] = {};
     cudaEvent_t fork = nullptr;
     int concurrent_classes = 1;
+    // group classes: an env-step issued as `chunks` launches of consecutive substep ranges on `lanes` streams per class, each lane
+    // a contiguous share of the class.  A lane's next chunk starts as soon as its own previous chunk is done, so the SMs that the
+    // last, partly filled wave of one launch leaves idle run the other lanes' CTAs (1024 20x20 robots on 296 CTA slots are
+    // 3.46 waves: 13 % of the slots idle in a single launch).  MEVO_CHUNKS / MEVO_LANES; 1 / 1 = one launch per class.
+    int chunks = 4, lanes = 2;                    // most chunks considered; streams per class
+    double chunk_min_waves = 1.0;                 // chunk only when the class asks for more CTAs than fit at once (MEVO_CHUNK_MIN_WAVES) ...
+    double chunk_min_gain = 0.02;                 // ... and the estimated gain is at least this (MEVO_CHUNK_MIN_GAIN)
+    static constexpr int kMaxLanes = 4;
+    cudaStream_t lane_stream[kNumClasses][kMaxLanes] = {};
+    cudaEvent_t lane_done[kNumClasses][kMaxLanes] = {};
+    int class_slots[kNumClasses] = {};            // CTAs of the class's build that fit on the device at once
     int class_max[kNumClasses][6] = {};
     int* d_ids = nullptr;                         // reset_envs: environment ids on the device
     int ids_cap = 0;
@@ -280,6 +291,10 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     if (const char* e = std::getenv("MEVO_CTA_SYNC")) impl_->cta_sync = std::atoi(e);
     if (const char* e = std::getenv("MEVO_BALANCE")) impl_->balance = std::atoi(e);
     if (const char* e = std::getenv("MEVO_CONCURRENT_CLASSES")) impl_->concurrent_classes = std::atoi(e);
+    if (const char* e = std::getenv("MEVO_CHUNKS")) impl_->chunks = std::max(1, std::atoi(e));
+    if (const char* e = std::getenv("MEVO_CHUNK_MIN_WAVES")) impl_->chunk_min_waves = std::atof(e);
+    if (const char* e = std::getenv("MEVO_CHUNK_MIN_GAIN")) impl_->chunk_min_gain = std::atof(e);
+    if (const char* e = std::getenv("MEVO_LANES")) impl_->lanes = std::min((int)Impl::kMaxLanes, std::max(1, std::atoi(e)));
     CUDA_CHECK(cudaDeviceGetAttribute(&impl_->n_sm, cudaDevAttrMultiProcessorCount, device_));
 }
 
@@ -336,6 +351,10 @@ Batch::~Batch() {
         for (int c = 0; c < kNumClasses; c++) {
             if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
             if (impl_->class_done[c]) cudaEventDestroy(impl_->class_done[c]);
+            for (int l = 0; l < Impl::kMaxLanes; l++) {
+                if (impl_->lane_stream[c][l]) cudaStreamDestroy(impl_->lane_stream[c][l]);
+                if (impl_->lane_done[c][l]) cudaEventDestroy(impl_->lane_done[c][l]);
+            }
         }
         if (impl_->fork) cudaEventDestroy(impl_->fork);
     }
@@ -734,6 +753,7 @@ void Batch::finalize() {
     size_t state_doubles = 0, scratch_bytes = 0;
     std::memset(impl_->class_ppt, 0, sizeof(impl_->class_ppt));
     std::memset(impl_->class_xd, 0, sizeof(impl_->class_xd));
+    std::memset(impl_->class_slots, 0, sizeof(impl_->class_slots));
     act_stride_ = 1;
 
     auto intern = [](std::vector<uint8_t>& pool, std::unordered_map<uint64_t, std::vector<std::pair<size_t, size_t>>>& index,
@@ -856,7 +876,12 @@ void Batch::finalize() {
             else configure_wstep<MEVO_WCAPS_A, 16, 1>();
         } else if (c == 1) configure_wstep<MEVO_WCAPS_C, 12, 1>();
         else if (c == 2) configure_wstep<MEVO_WCAPS_B, 10, 1>();
-        else gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
+        else {
+            gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Configure, nullptr, impl_->class_smem[c], nullptr);
+            // resident CTAs: the register budget of the build (64 / 128 / 256 / 512 threads -> 8 / 4 / 2 / 1 per SM) or shared memory
+            const int by_regs = 512 / kGroupSizes[c], by_smem = (228 * 1024) / (impl_->class_smem[c] + 1024);
+            impl_->class_slots[c] = impl_->n_sm * std::max(1, std::min(by_regs, by_smem));
+        }
     }
     if (!d_events_) { CUDA_CHECK(cudaMalloc(&d_events_, sizeof(unsigned long long))); CUDA_CHECK(cudaMemset(d_events_, 0, sizeof(unsigned long long))); }
     d_act_ext_ = nullptr;
@@ -1168,18 +1193,57 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.dbg_cand_cap = cand_cap_;
     prm.dbg_cf = impl_->d_cf;
     prm.scratch = impl_->d_scratch;
+    prm.chunk_first = prm.chunk_last = 1;
     cudaStream_t main_st = (cudaStream_t)stream_;
     stats_.launches = 0;
     int n_used = 0;
-    for (int c = 0; c < kNumClasses; c++) n_used += impl_->class_envs[c].empty() ? 0 : 1;
-    const bool fork = n_used > 1 && impl_->concurrent_classes != 0;
+    int n_group = 0;
+    double waves = 0.0;                       // CTA demand of the group classes over what the device holds at once
+    for (int c = 0; c < kNumClasses; c++) {
+        const bool used = !impl_->class_envs[c].empty();
+        n_used += used ? 1 : 0;
+        if (used && c >= kFirstGroupClass) { n_group++; waves += (double)impl_->class_envs[c].size() / std::max(1, impl_->class_slots[c]); }
+    }
+    // chunked, laned launches (see Impl::chunks).  One launch leaves about 1 - waves / ceil(waves) of the CTA slots idle; with n
+    // chunks the figure is that of n * waves, and every extra launch costs its stage-in and a list build (~1.5 % of a step).
+    // The chunk count with the best estimate is taken, if it gains anything: 1024 robots of 20x20 (3.46 waves) run as 2 chunks
+    // (+10 %), the 8192-robot mix (15 waves) as one launch (chunked: -9 %).  Only a plain single env-step is chunked; the debug
+    // dumps describe "the first substep of the launch" and keep one launch
+    int n_chunks = 1;
+    if (n_steps == 1 && n_group >= 1 && !d_cand_ && !impl_->d_cf && impl_->chunks > 1) {
+        auto idle = [](double w) { return 1.0 - w / std::ceil(w - 1e-9); };
+        const bool forced = impl_->chunk_min_waves <= 0.0;                   // tests: exactly `chunks` chunks whatever the population
+        double best = impl_->chunk_min_gain;
+        for (int k = 2; k <= impl_->chunks && 2 * k <= n_substeps; k++) {
+            const double gain = idle(waves) - idle(waves * k) - 0.015 * (k - 1);
+            if (forced) n_chunks = k;
+            else if (waves > impl_->chunk_min_waves && gain > best) { best = gain; n_chunks = k; }
+        }
+    }
+    const bool laned = n_chunks > 1;
+    const bool fork = (n_used > 1 && impl_->concurrent_classes != 0) || laned;
     if (fork) {
         if (!impl_->fork) CUDA_CHECK(cudaEventCreateWithFlags(&impl_->fork, cudaEventDisableTiming));
         CUDA_CHECK(cudaEventRecord(impl_->fork, main_st));
     }
+    struct Lane { int c, off, n; cudaStream_t st; cudaEvent_t done; };
+    std::vector<Lane> lanes;
     for (int c = kNumClasses - 1; c >= 0; c--) {
         const int n = (int)impl_->class_envs[c].size();
         if (n == 0) continue;
+        if (laned && c >= kFirstGroupClass) {
+            const int L = std::max(1, std::min(impl_->lanes, n));
+            for (int l = 0; l < L; l++) {
+                if (!impl_->lane_stream[c][l]) {
+                    CUDA_CHECK(cudaStreamCreateWithFlags(&impl_->lane_stream[c][l], cudaStreamNonBlocking));
+                    CUDA_CHECK(cudaEventCreateWithFlags(&impl_->lane_done[c][l], cudaEventDisableTiming));
+                }
+                const int lo = (int)((long long)n * l / L), hi = (int)((long long)n * (l + 1) / L);
+                CUDA_CHECK(cudaStreamWaitEvent(impl_->lane_stream[c][l], impl_->fork, 0));
+                lanes.push_back({c, lo, hi - lo, impl_->lane_stream[c][l], impl_->lane_done[c][l]});
+            }
+            continue;
+        }
         cudaStream_t st = main_st;
         if (fork) {
             if (!impl_->class_stream[c]) {
@@ -1208,6 +1272,25 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
             CUDA_CHECK(cudaEventRecord(impl_->class_done[c], st));
             CUDA_CHECK(cudaStreamWaitEvent(main_st, impl_->class_done[c], 0));
         }
+    }
+    for (int k = 0; k < n_chunks && !lanes.empty(); k++) {
+        const int s0 = (int)((long long)n_substeps * k / n_chunks), s1 = (int)((long long)n_substeps * (k + 1) / n_chunks);
+        StepParams cp = prm;
+        cp.n_substeps = s1 - s0;
+        cp.chunk_first = k == 0;
+        cp.chunk_last = k == n_chunks - 1;
+        cp.apply_actions = (apply_actions && k == 0) ? 1 : 0;
+        for (const Lane& ln : lanes) {
+            cp.class_envs = d_class_envs_ + impl_->class_off[ln.c] + ln.off;
+            cp.n_class_envs = ln.n;
+            gstep_dispatch(ln.c, impl_->class_ppt[ln.c] | impl_->class_xd[ln.c], GAction::Launch, &cp, impl_->class_smem[ln.c], ln.st);
+            CUDA_CHECK(cudaGetLastError());
+            stats_.launches++;
+        }
+    }
+    for (const Lane& ln : lanes) {
+        CUDA_CHECK(cudaEventRecord(ln.done, ln.st));
+        CUDA_CHECK(cudaStreamWaitEvent(main_st, ln.done, 0));
     }
     for (auto& e : envs_) e.host_fresh = false;
 }
@@ -1253,6 +1336,7 @@ void Batch::step_static_scratch(int n_steps, const double* dev_actions, int stri
     prm.dbg_cand_n = nullptr;
     prm.dbg_cand_cap = 0;
     prm.dbg_cf = nullptr;
+    prm.chunk_first = prm.chunk_last = 1;
     prm.scratch = static_scratch_address(device_);          // NOT g_static_scratch itself: that name is a host-side stand-in
     cudaStream_t st = (cudaStream_t)stream_;
     stats_.launches = 0;

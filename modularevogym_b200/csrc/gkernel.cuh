@@ -775,6 +775,7 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
     unsigned char* sm = gsm_raw;
     const int t = threadIdx.x;
     const int env = prm.class_envs[blockIdx.x];
+    if (!prm.chunk_first && prm.unstable[env]) return;  // Sim::step aborted in an earlier chunk of this step (Sim.cpp:107-110)
     const EnvDesc ed = prm.envs[env];
     const uint8_t* db = prm.design + ed.design_off;
     const DesignHeader* DH = reinterpret_cast<const DesignHeader*>(db);
@@ -948,7 +949,7 @@ __global__ void __launch_bounds__(G, MINB) gstep_kernel(const StepParams prm) {
         if (tt == 0) {
             prm.unstable[e_id] = (uint8_t)unstable;
             if (unstable && prm.auto_reset) prm.sim_time[e_id] = 0;
-            else prm.sim_time[e_id] += completed_steps;
+            else if (prm.chunk_last) prm.sim_time[e_id] += completed_steps;
             if (unstable) atomicAdd(prm.unstable_events, 1ull);
         }
     }

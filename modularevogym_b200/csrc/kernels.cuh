@@ -47,6 +47,10 @@ struct StepParams {
     int dbg_cand_cap;
     double* dbg_cf;             // optional: collision_forces after the first substep's collision phase (state-block offsets)
     unsigned int* scratch;      // group kernel: neighbour lists (EnvDesc::scratch_off16)
+    // group kernel: an env-step may be issued as several launches of consecutive substep ranges ("chunks", Batch::step_async).
+    // chunk_first == 0: this launch continues a step -- an environment whose earlier chunk reported "unstable" is left alone;
+    // chunk_last == 0: more chunks follow -- the step is not counted yet
+    int chunk_first, chunk_last;
 };
 
 // PhysicsEngine.h:17-27
