@@ -112,18 +112,31 @@ template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, in
 void configure_wstep() {
     constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
     static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
-    CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB>,
+    CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, false>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, true>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 }
 
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 void launch_wstep(StepParams prm, int n_sm, bool balance, cudaStream_t stream) {
+    using Smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>;
+    if (prm.work) {
+        // one CTA of the full width per (CTA-group, chunk) item, drawn from a counter as the CTA starts (wkernel.cuh); the
+        // counters start at zero
+        prm.envs_per_cta = EPC;
+        const int groups = (prm.n_class_envs + EPC - 1) / EPC;
+        CUDA_CHECK(cudaMemsetAsync(prm.work, 0, sizeof(int) * (size_t)(1 + groups), stream));
+        const int grid = groups * prm.n_chunks;
+        wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, true><<<grid, 32 * EPC, Smem::kBytes * EPC, stream>>>(prm);
+        return;
+    }
     prm.envs_per_cta = balance ? balanced_envs_per_cta(prm.n_class_envs, EPC, n_sm * MINB) : EPC;
     // shared memory for the environments the CTA really takes: what is left of the SM's 228 KB serves as L1 for the static-terrain
     // tables (grid, boxes, leaf records, points), which the collision phase reads through __ldg
-    const int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * prm.envs_per_cta;
+    const int smem = Smem::kBytes * prm.envs_per_cta;
     const int grid = (prm.n_class_envs + prm.envs_per_cta - 1) / prm.envs_per_cta;
-    wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB><<<grid, 32 * EPC, smem, stream>>>(prm);
+    wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, false><<<grid, 32 * EPC, smem, stream>>>(prm);
 }
 
 // group kernel builds: (threads, CTAs per SM the register budget is set for, points per thread)
@@ -267,6 +280,9 @@ struct Batch::Impl {
     double chunk_min_waves = 1.0;                 // chunk only when the class asks for more CTAs than fit at once (MEVO_CHUNK_MIN_WAVES) ...
     double chunk_min_gain = 0.02;                 // ... and the estimated gain is at least this (MEVO_CHUNK_MIN_GAIN)
     static constexpr int kMaxLanes = 4;
+    int wchunks = 6;                              // warp classes: most chunks considered for the item form (MEVO_WCHUNKS)
+    int* d_work = nullptr;                        // its item counters, per warp class at work_off[c]
+    int work_off[kNumClasses] = {};
     cudaStream_t lane_stream[kNumClasses][kMaxLanes] = {};
     cudaEvent_t lane_done[kNumClasses][kMaxLanes] = {};
     int class_slots[kNumClasses] = {};            // CTAs of the class's build that fit on the device at once
@@ -294,6 +310,7 @@ Batch::Batch(int device) : device_(device), impl_(new Impl()) {
     if (const char* e = std::getenv("MEVO_CHUNKS")) impl_->chunks = std::max(1, std::atoi(e));
     if (const char* e = std::getenv("MEVO_CHUNK_MIN_WAVES")) impl_->chunk_min_waves = std::atof(e);
     if (const char* e = std::getenv("MEVO_CHUNK_MIN_GAIN")) impl_->chunk_min_gain = std::atof(e);
+    if (const char* e = std::getenv("MEVO_WCHUNKS")) impl_->wchunks = std::max(1, std::atoi(e));
     if (const char* e = std::getenv("MEVO_LANES")) impl_->lanes = std::min((int)Impl::kMaxLanes, std::max(1, std::atoi(e)));
     CUDA_CHECK(cudaDeviceGetAttribute(&impl_->n_sm, cudaDevAttrMultiProcessorCount, device_));
 }
@@ -346,7 +363,7 @@ Batch::~Batch() {
     cudaFree(d_cand_); cudaFree(d_cand_n_); cudaFree(d_events_);
     if (impl_) {
         cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); cudaFree(impl_->d_ids);
-        cudaFree(impl_->d_scratch); cudaFree(impl_->d_cf);
+        cudaFree(impl_->d_scratch); cudaFree(impl_->d_cf); cudaFree(impl_->d_work);
         for (int k = 0; k < Impl::kSlots; k++) { cudaFree(impl_->d_slot[k]); cudaFree(impl_->d_slot_time[k]); }
         for (int c = 0; c < kNumClasses; c++) {
             if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
@@ -867,6 +884,15 @@ void Batch::finalize() {
     }
     CUDA_CHECK(cudaMalloc(&impl_->d_scratch, scratch_bytes + 16));
     impl_->scratch_bytes = scratch_bytes;
+    {   // item counters of the chunked warp-kernel launches: 1 + one word per CTA-group, per warp class
+        int words = 0;
+        for (int c = 0; c < kFirstGroupClass; c++) {
+            impl_->work_off[c] = words;
+            words += 4 + (int)impl_->class_envs[c].size() / 4;           // groups are >= 4 environments wide
+        }
+        cudaFree(impl_->d_work); impl_->d_work = nullptr;
+        CUDA_CHECK(cudaMalloc(&impl_->d_work, sizeof(int) * (size_t)words));
+    }
     // dynamic shared-memory limits of the kernels this batch launches, on this batch's device
     for (int c = 0; c < kNumClasses; c++) {
         if (impl_->class_envs[c].empty()) continue;
@@ -1194,6 +1220,8 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     prm.dbg_cf = impl_->d_cf;
     prm.scratch = impl_->d_scratch;
     prm.chunk_first = prm.chunk_last = 1;
+    prm.work = nullptr;
+    prm.n_chunks = 1;
     cudaStream_t main_st = (cudaStream_t)stream_;
     stats_.launches = 0;
     int n_used = 0;
@@ -1210,9 +1238,10 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     // (+10 %), the 8192-robot mix (15 waves) as one launch (chunked: -9 %).  Only a plain single env-step is chunked; the debug
     // dumps describe "the first substep of the launch" and keep one launch
     int n_chunks = 1;
-    if (n_steps == 1 && n_group >= 1 && !d_cand_ && !impl_->d_cf && impl_->chunks > 1) {
-        auto idle = [](double w) { return 1.0 - w / std::ceil(w - 1e-9); };
-        const bool forced = impl_->chunk_min_waves <= 0.0;                   // tests: exactly `chunks` chunks whatever the population
+    auto idle = [](double w) { return 1.0 - w / std::ceil(w - 1e-9); };
+    const bool chunkable = n_steps == 1 && !d_cand_ && !impl_->d_cf;
+    const bool forced = impl_->chunk_min_waves <= 0.0;                       // tests: the largest chunk count whatever the population
+    if (chunkable && n_group >= 1 && impl_->chunks > 1) {
         double best = impl_->chunk_min_gain;
         for (int k = 2; k <= impl_->chunks && 2 * k <= n_substeps; k++) {
             const double gain = idle(waves) - idle(waves * k) - 0.015 * (k - 1);
@@ -1228,6 +1257,21 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
     }
     struct Lane { int c, off, n; cudaStream_t st; cudaEvent_t done; };
     std::vector<Lane> lanes;
+    auto launch_class = [&](int c, const StepParams& p, bool balance, cudaStream_t st) {
+        switch (c) {
+            case 0:
+                // default: one 16-warp CTA per SM (all warps of an SM in the same code region)
+                if (impl_->wepc == 8) launch_wstep<MEVO_WCAPS_A, 8, 2>(p, impl_->n_sm, balance, st);
+                else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(p, impl_->n_sm, balance, st);
+                else launch_wstep<MEVO_WCAPS_A, 16, 1>(p, impl_->n_sm, balance, st);
+                break;
+            case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(p, impl_->n_sm, balance, st); break;
+            case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(p, impl_->n_sm, balance, st); break;
+            default: gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Launch, &p, impl_->class_smem[c], st); break;
+        }
+        CUDA_CHECK(cudaGetLastError());
+        stats_.launches++;
+    };
     for (int c = kNumClasses - 1; c >= 0; c--) {
         const int n = (int)impl_->class_envs[c].size();
         if (n == 0) continue;
@@ -1255,19 +1299,24 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         }
         prm.class_envs = d_class_envs_ + impl_->class_off[c];
         prm.n_class_envs = n;
-        switch (c) {
-            case 0:
-                // default: one 16-warp CTA per SM (all warps of an SM in the same code region)
-                if (impl_->wepc == 8) launch_wstep<MEVO_WCAPS_A, 8, 2>(prm, impl_->n_sm, impl_->balance != 0, st);
-                else if (impl_->wepc == 4) launch_wstep<MEVO_WCAPS_A, 4, 4>(prm, impl_->n_sm, impl_->balance != 0, st);
-                else launch_wstep<MEVO_WCAPS_A, 16, 1>(prm, impl_->n_sm, impl_->balance != 0, st);
-                break;
-            case 1: launch_wstep<MEVO_WCAPS_C, 12, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            case 2: launch_wstep<MEVO_WCAPS_B, 10, 1>(prm, impl_->n_sm, impl_->balance != 0, st); break;
-            default: gstep_dispatch(c, impl_->class_ppt[c] | impl_->class_xd[c], GAction::Launch, &prm, impl_->class_smem[c], st); break;
+        prm.work = nullptr;
+        prm.n_chunks = 1;
+        if (c < kFirstGroupClass && chunkable && impl_->wchunks > 1) {
+            // warp classes: one CTA per (CTA-group, chunk) item where that fills the SMs better than one CTA per group
+            const int unit = c == 0 ? (impl_->wepc ? impl_->wepc : 16) : c == 1 ? 12 : 10;
+            const int slots = impl_->n_sm * (c == 0 && impl_->wepc ? 16 / impl_->wepc : 1);
+            const double w = (double)((n + unit - 1) / unit) / slots;
+            double best = impl_->chunk_min_gain;
+            for (int k = 2; k <= impl_->wchunks && 2 * k <= n_substeps; k++) {
+                const double gain = idle(w) - idle(w * k) - 0.012 * (k - 1);
+                if (forced) prm.n_chunks = k;
+                else if ((w > 1.0 || n_used > 1) && gain > best) { best = gain; prm.n_chunks = k; }     // alone and resident at once: nothing to fill
+            }
+            if (prm.n_chunks > 1) prm.work = impl_->d_work + impl_->work_off[c];
         }
-        CUDA_CHECK(cudaGetLastError());
-        stats_.launches++;
+        launch_class(c, prm, impl_->balance != 0, st);
+        prm.work = nullptr;
+        prm.n_chunks = 1;
         if (fork) {
             CUDA_CHECK(cudaEventRecord(impl_->class_done[c], st));
             CUDA_CHECK(cudaStreamWaitEvent(main_st, impl_->class_done[c], 0));
@@ -1283,9 +1332,7 @@ void Batch::step_async(int n_steps, bool apply_actions, int n_substeps) {
         for (const Lane& ln : lanes) {
             cp.class_envs = d_class_envs_ + impl_->class_off[ln.c] + ln.off;
             cp.n_class_envs = ln.n;
-            gstep_dispatch(ln.c, impl_->class_ppt[ln.c] | impl_->class_xd[ln.c], GAction::Launch, &cp, impl_->class_smem[ln.c], ln.st);
-            CUDA_CHECK(cudaGetLastError());
-            stats_.launches++;
+            launch_class(ln.c, cp, false, ln.st);
         }
     }
     for (const Lane& ln : lanes) {
@@ -1337,6 +1384,8 @@ void Batch::step_static_scratch(int n_steps, const double* dev_actions, int stri
     prm.dbg_cand_cap = 0;
     prm.dbg_cf = nullptr;
     prm.chunk_first = prm.chunk_last = 1;
+    prm.work = nullptr;
+    prm.n_chunks = 1;
     prm.scratch = static_scratch_address(device_);          // NOT g_static_scratch itself: that name is a host-side stand-in
     cudaStream_t st = (cudaStream_t)stream_;
     stats_.launches = 0;

@@ -51,6 +51,10 @@ struct StepParams {
     // chunk_first == 0: this launch continues a step -- an environment whose earlier chunk reported "unstable" is left alone;
     // chunk_last == 0: more chunks follow -- the step is not counted yet
     int chunk_first, chunk_last;
+    // warp kernel, item form (wkernel.cuh): work[0] = item counter, work[1 + g] = chunks CTA-group g has completed (zeroed by
+    // the host before the launch); the env-step is n_chunks chunks of n_substeps / n_chunks substeps.  nullptr: one item per CTA
+    int* work;
+    int n_chunks;
 };
 
 // PhysicsEngine.h:17-27

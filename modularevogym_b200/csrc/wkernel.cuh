@@ -642,21 +642,38 @@ __device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask,
 }
 
 // =================================================================================== the kernel
-template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
-__global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams prm) {
+// parameters of the work item a CTA is on (shared memory)
+struct WCtl {
+    int item;       // CTA-group: environments item * envs_per_cta ... of the class list, one per warp
+    int chunk;      // which chunk of the env-step
+    int nsub;       // substeps of the item
+    int first;      // the item starts an env-step (else it continues one: an environment whose earlier chunk aborted is left alone)
+    int last;       // it ends the step (the step is counted)
+    int apply;      // actions -> goals at stage in
+};
+
+template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB, bool ITEMS>
+__device__ __forceinline__ void wstep_item(const StepParams& prm, unsigned char* smem_raw, const volatile WCtl* ctl) {
     using S = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     const int grp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     // A CTA takes prm.envs_per_cta (<= EPC) consecutive entries of the class list; the host picks that number so that
     // the launch is a whole number of equally full waves.  Spare warps only keep the barrier count.
-    const int slot = blockIdx.x * prm.envs_per_cta + grp;
-    if (grp >= prm.envs_per_cta || slot >= prm.n_class_envs) {
+    const int slot = (ITEMS ? ctl->item : (int)blockIdx.x) * prm.envs_per_cta + grp;
+    if (grp >= prm.envs_per_cta || slot >= prm.n_class_envs) {                 // spare warps only keep the barrier count
         if (EPC > 1 && prm.cta_sync)
-            for (int i = prm.n_steps * prm.n_substeps; i > 0; i--) __syncthreads();
+            for (int i = prm.n_steps * (ITEMS ? ctl->nsub : prm.n_substeps); i > 0; i--) __syncthreads();
         return;
     }
     const int env = prm.class_envs[slot];
+    if (ITEMS) {
+        // an item that continues a step leaves an environment alone whose earlier chunk aborted the step (Sim.cpp:107-110)
+        if (!ctl->first && __ldcg(prm.unstable + env)) {
+            if (EPC > 1 && prm.cta_sync)
+                for (int i = prm.n_steps * ctl->nsub; i > 0; i--) __syncthreads();
+            return;
+        }
+    }
     unsigned char* sm = smem_raw + grp * S::kBytes;
     double* gstate;
     unsigned fixmask = 0;                               // bit k: point lane + 32 k is fixed
@@ -694,9 +711,9 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         double2* vt = reinterpret_cast<double2*>(sm + S::o_vt);
         uint4* csr = reinterpret_cast<uint4*>(sm + S::o_csr);
         for (int i = lane, k = 0; i < Pd; i += 32, k++) {
-            pos[i] = g2[i];
-            vel[i] = g2[Pd + i];
-            vt[i] = g2[3 * Pd + i];
+            pos[i] = __ldcg(g2 + i);                    // state: through L2 (a persistent CTA may hold stale L1 lines of it)
+            vel[i] = __ldcg(g2 + Pd + i);
+            vt[i] = __ldcg(g2 + 3 * Pd + i);
             {
                 // empty gather slots (0xffff) point at the all-zero entry of ef2 from here on
                 uint4 rec = __ldg(reinterpret_cast<const uint4*>(db + Hp->o_csr8) + i);
@@ -716,8 +733,8 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         const int16_t* eact = reinterpret_cast<const int16_t*>(db + Hp->o_eact);
         const double* act = prm.act + (size_t)env * prm.act_stride;
         for (int e = lane; e < Ed; e += 32) {
-            double g = ggoal[e];
-            if (prm.apply_actions) {
+            double g = __ldcg(ggoal + e);
+            if (ITEMS ? ctl->apply : prm.apply_actions) {
                 // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather
                 const int a0 = eact[2 * e], a1 = eact[2 * e + 1];
                 if (a0 >= 0) {
@@ -763,7 +780,7 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
     const bool dbg = prm.dbg_cand != nullptr || prm.dbg_cf != nullptr;
 
     for (int step = 0; step < prm.n_steps; step++) {
-        for (int sub = 0; sub < prm.n_substeps; sub++) {
+        for (int sub = 0; sub < (ITEMS ? ctl->nsub : prm.n_substeps); sub++) {
             // keeps the CTA's warps in the same code region: they share instruction-cache lines
             if (EPC > 1 && prm.cta_sync) __syncthreads();
             if (unstable) continue;                       // Sim::step aborted (Sim.cpp:107-110)
@@ -831,9 +848,55 @@ __global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams 
         if (lane == 0) {
             prm.unstable[env] = (uint8_t)unstable;
             if (unstable && prm.auto_reset) prm.sim_time[env] = 0;
-            else prm.sim_time[env] += completed_steps;
+            else if (ITEMS ? ctl->last : prm.chunk_last) prm.sim_time[env] += completed_steps;
             if (unstable) atomicAdd(prm.unstable_events, 1ull);
         }
+    }
+}
+
+// The kernel.  ITEMS == false: CTA b takes CTA-group b for a whole launch's worth (prm.n_substeps substeps, chunk flags of prm).
+// ITEMS == true: the grid has one CTA per (CTA-group, chunk) item -- chunks being consecutive substep ranges of ONE env-step --
+// and a CTA DRAWS its item from a counter when it starts: item i = chunk i / n_groups of group i % n_groups.  A chunk waits until
+// the group's previous chunk (drawn n_groups items earlier, by a CTA that is running or done -- so the wait cannot deadlock) has
+// published its state.  The hardware's CTA scheduler is the work queue: an SM takes the next item the moment a CTA retires.
+// With 4096 walkers on 148 SMs a single launch is 1.73 waves of 16-warp CTAs (or two waves of 14-warp CTAs); four chunks make
+// that 6.92 rounds of a quarter step.  The item's parameters sit in shared memory (WCtl): the body is at its register cap and
+// reads them where it needs them.  (A persistent loop around the body was measured 3 % slower: what the loop keeps live.)
+template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB, bool ITEMS>
+__global__ void __launch_bounds__(32 * EPC, MINB) wstep_kernel(const StepParams prm) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (!ITEMS) {
+        wstep_item<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, false>(prm, smem_raw, nullptr);
+        return;
+    }
+    __shared__ WCtl ctl;
+    if (threadIdx.x == 0) {
+        const int n_groups = (prm.n_class_envs + prm.envs_per_cta - 1) / prm.envs_per_cta;
+        const int i = atomicAdd(prm.work, 1);
+        const int k = i / n_groups, g = i - k * n_groups;
+        if (k > 0) {
+            const int* done = prm.work + 1 + g;
+            for (;;) {
+                int v;
+                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(done) : "memory");
+                if (v >= k) break;
+                __nanosleep(256);
+            }
+        }
+        const int s0 = prm.n_substeps * k / prm.n_chunks, s1 = prm.n_substeps * (k + 1) / prm.n_chunks;
+        ctl.item = g;
+        ctl.chunk = k;
+        ctl.nsub = s1 - s0;
+        ctl.first = k == 0;
+        ctl.last = k == prm.n_chunks - 1;
+        ctl.apply = prm.apply_actions && k == 0;
+    }
+    __syncthreads();
+    wstep_item<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, true>(prm, smem_raw, &ctl);
+    __syncthreads();                                           // every warp has staged out
+    if (threadIdx.x == 0) {
+        __threadfence();
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(prm.work + 1 + ctl.item), "r"(ctl.chunk + 1) : "memory");
     }
 }
 

@@ -1,5 +1,6 @@
-"""GPU: an env-step of the group classes issued as several launches of consecutive substep ranges on several streams per class
-(``Batch::step_async``: MEVO_CHUNKS x MEVO_LANES) leaves exactly what the single launch leaves: states bit for
+"""GPU: an env-step issued in chunks of consecutive substeps -- group classes: several launches on several streams per class
+(``Batch::step_async``: MEVO_CHUNKS x MEVO_LANES); warp classes: one CTA per (CTA-group, chunk) item drawn from
+a counter (MEVO_WCHUNKS) -- leaves exactly what the single launch leaves: states bit for
 bit, unstable flags, step counters, the reset of an environment whose step aborted in an early chunk (Sim.cpp:105-115)."""
 import numpy as np
 import pytest
@@ -13,11 +14,12 @@ N_STEPS = 4
 
 def _run(monkeypatch, chunks: int, lanes: int, auto_reset: bool):
     monkeypatch.setenv("MEVO_CHUNKS", str(chunks))
+    monkeypatch.setenv("MEVO_WCHUNKS", str(chunks + 1 if chunks > 1 else 1))
     monkeypatch.setenv("MEVO_LANES", str(lanes))
     monkeypatch.setenv("MEVO_CHUNK_MIN_WAVES", "0")          # chunk although these few environments fit the device at once
     B = capi.Batch(0)
     specs = [("obstacle20", i) for i in range(6)] + [("obstacle10", i) for i in range(8)] + [("bridge", i) for i in range(5)] + \
-            [("hetero", i) for i in range(24)]
+            [("hetero", i) for i in range(24)] + [("walker5x5", i) for i in range(40)] + [("pusher", i) for i in range(30)]
     for name, i in specs:
         B.add_world(workloads.world_for(name, i))
     B.finalize()
