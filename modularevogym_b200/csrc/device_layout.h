@@ -78,7 +78,10 @@ struct DesignHeader {        // 160 bytes
     int o_lpt16;                              // 8 bytes per leaf: TL, TR, BR, BL point ids, u16 each
     int ilist_cap;                            // neighbour-list entries for the always-candidate items (follows the pair list)
     int o_csrx;                               // 0, or (max_deg > 8: unshared duplicate side edges) a second 8-slot record per point
-    int reserved[5];
+    // warp kernel: tables in the exact form its shared memory holds them, staged in by bulk copies
+    int o_lpt8;                               // u32 per leaf: TL | TR << 8 | BR << 16 | BL << 24 point ids
+    unsigned int fixed_lo, fixed_hi;          // bit p: simulated point p (< 64) is fixed
+    int reserved[2];
 };
 static_assert(sizeof(DesignHeader) == 160, "DesignHeader must be 160 bytes");
 

@@ -682,6 +682,14 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     }
     for (const LeafRec& lr : leaves)
         for (int q = 0; q < 4; q++) lpt16.push_back(lr.pt[q]);
+    std::vector<uint32_t> lpt8;
+    H.fixed_lo = H.fixed_hi = 0;
+    if (warp_ok) {
+        for (const LeafRec& lr : leaves)
+            lpt8.push_back((uint32_t)lr.pt[0] | ((uint32_t)lr.pt[1] << 8) | ((uint32_t)lr.pt[2] << 16) | ((uint32_t)lr.pt[3] << 24));
+        for (int i = 0; i < Pd && i < 64; i++)
+            if (fixed[i]) (i < 32 ? H.fixed_lo : H.fixed_hi) |= 1u << (i & 31);
+    }
     H.warp_ok = warp_ok ? 1 : 0;
     H.o_csr8 = dw.begin_section(); dw.put_array(csr8);
     H.o_csrx = 0;
@@ -693,7 +701,9 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
     H.o_rord8 = dw.begin_section(); dw.put_array(rord8);
     H.o_eidx10 = dw.begin_section(); dw.put_array(eidx10);
     H.o_lpt16 = dw.begin_section(); dw.put_array(lpt16);
+    H.o_lpt8 = dw.begin_section(); dw.put_array(lpt8);
     H.total = dw.begin_section();
+    for (int q = 0; q < 16; q++) dw.put<uint8_t>(0);               // bulk copies round their size up to 16 bytes
     std::memcpy(design.data(), &H, sizeof(H));
 
     // ---- static blob

@@ -26,6 +26,34 @@
 
 namespace mevo {
 
+// ---- bulk copies global -> shared memory (the TMA unit's 1-D form) completing on an mbarrier
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// dst, src 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MBAR_DONE;\n"
+        "bra MBAR_WAIT;\n"
+        "MBAR_DONE:\n"
+        "}" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP>
 struct WarpSmem {
     static constexpr int kCandCap = 64;            // overlapping pairs per round (two 32-wide chunks)
@@ -634,7 +662,7 @@ __device__ __noinline__ void warp_constrain(unsigned char* sm, unsigned fixmask,
     for (int p = lane; p < Pd; p += 32) {                // PhysicsEngine::update_true_vel (:602-607)
         const double2 x = spos[p];
         // pos_last == pos at the start of every substep except possibly the first of a launch
-        const double2 l = first_substep ? H->g_last[p] : pos[p];
+        const double2 l = first_substep ? __ldcg(H->g_last + p) : pos[p];
         vt[p] = make_double2(div_const(x.x - l.x, MEVO_DT), div_const(x.y - l.y, MEVO_DT));
         pos[p] = x;
     }
@@ -678,20 +706,45 @@ __device__ __forceinline__ void wstep_item(const StepParams& prm, unsigned char*
     double* gstate;
     unsigned fixmask = 0;                               // bit k: point lane + 32 k is fixed
 
-    // ---------------------------------------------------------------- stage in (once per launch)
+    // ---------------------------------------------------------------- stage in (once per launch / item)
+    // The design blob holds the constant tables in the form shared memory wants them, the state block holds pos | vel | pos_last |
+    // vel_true | goals back to back: lane 0 hands every array to the bulk-copy engine (cp.async.bulk, one mbarrier per warp) and
+    // the warp waits once, instead of one dependent L2 round trip per table.  What is computed stays in lanes: actions -> goals.
     {
         const EnvDesc ed = prm.envs[env];
         const uint8_t* db = prm.design + ed.design_off;
         const DesignHeader* Hp = reinterpret_cast<const DesignHeader*>(db);
-        const int Pd = Hp->Pd, Ed = Hp->Ed, n_leaf = Hp->n_leaf;
-        const int n_pairs = Hp->n_pairs, n_items = Hp->n_items, n_vis = Hp->n_rvis;
+        const int4 h0 = __ldg(reinterpret_cast<const int4*>(Hp));              // Pd, Ed, n_leaf, n_obj
+        const int4 h1 = __ldg(reinterpret_cast<const int4*>(Hp) + 1);          // n_pairs, n_rlev, n_rvis, n_act
+        const int Pd = h0.x, Ed = h0.y, n_leaf = h0.z, n_obj = h0.w;
+        const int n_pairs = h1.x, n_vis = h1.z;
+        const int n_items = Hp->n_items, n_types = Hp->n_types;
         gstate = prm.state + ed.state_off;
         const double2* g2 = reinterpret_cast<const double2*>(gstate);
-        const LeafRec* g_leaf = reinterpret_cast<const LeafRec*>(db + Hp->o_leaf);
+        const uint32_t bar = smem_u32(sm + S::o_hdr + 88);
+        const int apply = ITEMS ? ctl->apply : prm.apply_actions;
         if (lane == 0) {
+            mbar_init(bar, 1);
+            asm volatile("fence.proxy.async;" ::: "memory");                   // the barrier, and what an earlier chunk's CTA
+                                                                               // released through the generic proxy
+            auto up16 = [](int n) { return (uint32_t)((n + 15) & ~15); };
+            const uint32_t b_pts = 16u * Pd, b_goal = up16(8 * Ed), b_eidx = up16(4 * Ed), b_etab = 16u * n_types;
+            const uint32_t b_lpt = up16(4 * n_leaf), b_pairs = up16(2 * n_pairs), b_items = up16(2 * n_items), b_rord = up16(n_vis);
+            mbar_expect_tx(bar, 4 * b_pts + b_goal + b_eidx + b_etab + b_lpt + b_pairs + b_items + b_rord);
+            bulk_g2s(smem_u32(sm + S::o_pos), g2, b_pts, bar);
+            bulk_g2s(smem_u32(sm + S::o_vel), g2 + Pd, b_pts, bar);
+            bulk_g2s(smem_u32(sm + S::o_vt), g2 + 3 * Pd, b_pts, bar);
+            bulk_g2s(smem_u32(sm + S::o_csr), db + Hp->o_csr8, b_pts, bar);
+            if (b_goal) bulk_g2s(smem_u32(sm + S::o_goal), gstate + 8 * (size_t)Pd, b_goal, bar);
+            if (b_eidx) bulk_g2s(smem_u32(sm + S::o_eidx), db + Hp->o_eidx, b_eidx, bar);
+            if (b_etab) bulk_g2s(smem_u32(sm + S::o_etab), db + Hp->o_etab, b_etab, bar);
+            if (b_lpt) bulk_g2s(smem_u32(sm + S::o_lpt), db + Hp->o_lpt8, b_lpt, bar);
+            if (b_pairs) bulk_g2s(smem_u32(sm + S::o_pairs), db + Hp->o_pairs16, b_pairs, bar);
+            if (b_items) bulk_g2s(smem_u32(sm + S::o_items), db + Hp->o_items16, b_items, bar);
+            if (b_rord) bulk_g2s(smem_u32(sm + S::o_rord), db + Hp->o_rord8, b_rord, bar);
             WarpHdr* H = reinterpret_cast<WarpHdr*>(sm + S::o_hdr);
             H->Pd = Pd; H->Ed = Ed; H->n_leaf = n_leaf; H->n_pairs = n_pairs; H->n_items = n_items; H->n_vis = n_vis;
-            H->g_leaf = g_leaf;
+            H->g_leaf = reinterpret_cast<const LeafRec*>(db + Hp->o_leaf);
             H->g_last = g2 + 2 * Pd;
             if (ed.static_off != ~0ull) {
                 const uint8_t* sb = prm.statics + ed.static_off;
@@ -705,71 +758,61 @@ __device__ __forceinline__ void wstep_item(const StepParams& prm, unsigned char*
                 H->gx0 = H->gy0 = H->gw = H->gh = 0;
                 H->st_grid = nullptr; H->st_aabb = nullptr; H->st_pos = nullptr; H->st_leaf = nullptr;
             }
+            reinterpret_cast<double2*>(sm + S::o_ef2)[S::kZero] = make_double2(0.0, 0.0);
         }
-        double2* pos = reinterpret_cast<double2*>(sm + S::o_pos);
-        double2* vel = reinterpret_cast<double2*>(sm + S::o_vel);
-        double2* vt = reinterpret_cast<double2*>(sm + S::o_vt);
-        uint4* csr = reinterpret_cast<uint4*>(sm + S::o_csr);
-        for (int i = lane, k = 0; i < Pd; i += 32, k++) {
-            pos[i] = __ldcg(g2 + i);                    // state: through L2 (a persistent CTA may hold stale L1 lines of it)
-            vel[i] = __ldcg(g2 + Pd + i);
-            vt[i] = __ldcg(g2 + 3 * Pd + i);
-            {
-                // empty gather slots (0xffff) point at the all-zero entry of ef2 from here on
-                uint4 rec = __ldg(reinterpret_cast<const uint4*>(db + Hp->o_csr8) + i);
-                unsigned* w = reinterpret_cast<unsigned*>(&rec);
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    if ((w[q] & 0xffffu) == 0xffffu) w[q] = (w[q] & 0xffff0000u) | (unsigned)S::kZero;
-                    if ((w[q] >> 16) == 0xffffu) w[q] = (w[q] & 0xffffu) | ((unsigned)S::kZero << 16);
-                }
-                csr[i] = rec;
-            }
-            if (__ldg(db + Hp->o_fixed + i)) fixmask |= 1u << k;
-        }
-        double* goal = reinterpret_cast<double*>(sm + S::o_goal);
-        uint32_t* eidx = reinterpret_cast<uint32_t*>(sm + S::o_eidx);
-        const double* ggoal = gstate + 8 * (size_t)Pd;
-        const int16_t* eact = reinterpret_cast<const int16_t*>(db + Hp->o_eact);
-        const double* act = prm.act + (size_t)env * prm.act_stride;
-        for (int e = lane; e < Ed; e += 32) {
-            double g = __ldcg(ggoal + e);
-            if (ITEMS ? ctl->apply : prm.apply_actions) {
-                // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather
-                const int a0 = eact[2 * e], a1 = eact[2 * e + 1];
-                if (a0 >= 0) {
-                    const double l0 = __ldg(reinterpret_cast<const double*>(db + Hp->o_el0) + e);
-                    double sum = 0.0 + act[a0];
-                    int cnt = 1;
-                    if (a1 >= 0) { sum += act[a1]; cnt = 2; }
-                    g = sum * (l0 / cnt);
-                }
-            }
-            goal[e] = g;
-            eidx[e] = __ldg(reinterpret_cast<const uint32_t*>(db + Hp->o_eidx) + e);
-        }
-        double2* etab = reinterpret_cast<double2*>(sm + S::o_etab);
-        if (lane < Hp->n_types) etab[lane] = __ldg(reinterpret_cast<const double2*>(db + Hp->o_etab) + lane);
-        if (lane == 0) reinterpret_cast<double2*>(sm + S::o_ef2)[S::kZero] = make_double2(0.0, 0.0);
-        uint32_t* lpt = reinterpret_cast<uint32_t*>(sm + S::o_lpt);
-        if (lane < n_leaf) {
-            const LeafRec r = g_leaf[lane];
-            lpt[lane] = (uint32_t)r.pt[0] | ((uint32_t)r.pt[1] << 8) | ((uint32_t)r.pt[2] << 16) | ((uint32_t)r.pt[3] << 24);
-        }
-        uint16_t* pairs = reinterpret_cast<uint16_t*>(sm + S::o_pairs);
-        uint16_t* items = reinterpret_cast<uint16_t*>(sm + S::o_items);
-        uint8_t* rord = reinterpret_cast<uint8_t*>(sm + S::o_rord);
-        for (int i = lane; i < n_pairs; i += 32) pairs[i] = __ldg(reinterpret_cast<const uint16_t*>(db + Hp->o_pairs16) + i);
-        for (int i = lane; i < n_items; i += 32) items[i] = __ldg(reinterpret_cast<const uint16_t*>(db + Hp->o_items16) + i);
-        for (int i = lane; i < n_vis; i += 32) rord[i] = __ldg(db + Hp->o_rord8 + i);
+        fixmask = ((Hp->fixed_lo >> lane) & 1u) | (((Hp->fixed_hi >> lane) & 1u) << 1);
         volatile int* misc = reinterpret_cast<volatile int*>(sm + S::o_misc);
         if (lane < 8) {
             int ns = 0x7fffffff;                        // never "unstable" unless a robot (PhysicsEngine.cpp:819-834)
-            if (lane < Hp->n_obj) {
+            if (lane < n_obj) {
                 const ObjRec orc = reinterpret_cast<const ObjRec*>(db + Hp->o_obj)[lane];
                 if (orc.is_robot) ns = orc.n_surface;
             }
             misc[8 + lane] = ns;
+        }
+        // K1: PhysicsEngine::update_actuator_goals (PhysicsEngine.cpp:38-97) as a per-edge gather, loads in flight under the copies
+        constexpr int kEPL = (ECAP + 31) / 32;
+        double gnew[kEPL];
+        unsigned gset = 0;
+        if (apply) {
+            const int16_t* eact = reinterpret_cast<const int16_t*>(db + Hp->o_eact);
+            const double* act = prm.act + (size_t)env * prm.act_stride;
+#pragma unroll
+            for (int q = 0; q < kEPL; q++) {
+                const int e = lane + 32 * q;
+                gnew[q] = 0.0;
+                if (e < Ed) {
+                    const int a0 = eact[2 * e], a1 = eact[2 * e + 1];
+                    if (a0 >= 0) {
+                        const double l0 = __ldg(reinterpret_cast<const double*>(db + Hp->o_el0) + e);
+                        double sum = 0.0 + act[a0];
+                        int cnt = 1;
+                        if (a1 >= 0) { sum += act[a1]; cnt = 2; }
+                        gnew[q] = sum * (l0 / cnt);
+                        gset |= 1u << q;
+                    }
+                }
+            }
+        }
+        __syncwarp();                                   // lane 0 has initialised the barrier
+        mbar_wait(bar, 0);
+        // empty gather slots (0xffff) point at the all-zero entry of ef2 from here on
+        uint4* csr = reinterpret_cast<uint4*>(sm + S::o_csr);
+        for (int i = lane; i < Pd; i += 32) {
+            uint4 rec = csr[i];
+            unsigned* w = reinterpret_cast<unsigned*>(&rec);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if ((w[q] & 0xffffu) == 0xffffu) w[q] = (w[q] & 0xffff0000u) | (unsigned)S::kZero;
+                if ((w[q] >> 16) == 0xffffu) w[q] = (w[q] & 0xffffu) | ((unsigned)S::kZero << 16);
+            }
+            csr[i] = rec;
+        }
+        if (apply) {
+            double* goal = reinterpret_cast<double*>(sm + S::o_goal);
+#pragma unroll
+            for (int q = 0; q < kEPL; q++)
+                if ((gset >> q) & 1u) goal[lane + 32 * q] = gnew[q];
         }
     }
     __syncwarp();
