@@ -415,9 +415,10 @@ def ncu_summary(kernel_key: str):
         return None
 
 
-KERNEL_OF = {"walker5x5": "wstep_kernel<40,112,24,192,256,112,16,1>", "pusher": "wstep_kernel<52,144,28,320,288,64,12,1>",
-             "thrower": "wstep_kernel<52,144,28,320,288,64,12,1>", "obstacle10": "gstep_kernel<64,8,2>", "obstacle20": "gstep_kernel<256,2,2>",
-             "climber20": "gstep_kernel<256,2,2>", "bridge": "gstep_kernel<256,2,2>", "hetero": "gstep_kernel<256,2,2>"}
+KERNEL_OF = {"walker5x5": "wstep_kernel<40,112,24,192,256,112,16,1,true>", "pusher": "wstep_kernel<52,144,28,320,288,64,12,1,true>",
+             "thrower": "wstep_kernel<52,144,28,320,288,64,12,1,true>", "obstacle10": "gstep_kernel<64,8,2,false>",
+             "obstacle20": "gstep_kernel<256,2,2,false>", "climber20": "gstep_kernel<256,2,2,false>", "bridge": "gstep_kernel<256,2,2,false>",
+             "hetero": "gstep_kernel<256,2,2,false>"}
 
 
 def short_config_run(torch, capi, dev, wl: str, n: int, rank: int, world: int, local: int, flush, with_cpu: bool, settle: int, K: int):
@@ -569,6 +570,9 @@ def main_ours(args) -> None:
             "traffic": ncu.get("dram_bytes_per_launch") if ncu and ncu.get("envs") == n else None,
             "kernel": "mevo::" + kernel + (" (largest class; the mix launches one kernel per size class)" if wl == "hetero" else ""),
             "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+            "launch_unit": ("one env-step (30 substeps) of this rank's environments; the engine may issue it as chunks of substeps -- warp "
+                            "classes: (CTA-group, chunk) items of ONE kernel launch, group classes: several launches on two streams (DESIGN 4, 10); "
+                            "`gpu_launches` counts the kernel launches"),
             "note": ("`achieved` is SURVEY 8d's streaming model (105 B/point + 32 B/edge per substep in the reference's numbering, FIXED "
                      "terrain included) / measured step time: an equivalent bandwidth, comparable across designs.  The engine keeps the "
                      "state in shared memory for all 30 substeps and never integrates all-FIXED terrain, so DRAM is nearly idle and the "
