@@ -731,10 +731,12 @@ __device__ __forceinline__ void wstep_item(const StepParams& prm, unsigned char*
             const uint32_t b_pts = 16u * Pd, b_goal = up16(8 * Ed), b_eidx = up16(4 * Ed), b_etab = 16u * n_types;
             const uint32_t b_lpt = up16(4 * n_leaf), b_pairs = up16(2 * n_pairs), b_items = up16(2 * n_items), b_rord = up16(n_vis);
             mbar_expect_tx(bar, 4 * b_pts + b_goal + b_eidx + b_etab + b_lpt + b_pairs + b_items + b_rord);
-            bulk_g2s(smem_u32(sm + S::o_pos), g2, b_pts, bar);
-            bulk_g2s(smem_u32(sm + S::o_vel), g2 + Pd, b_pts, bar);
-            bulk_g2s(smem_u32(sm + S::o_vt), g2 + 3 * Pd, b_pts, bar);
-            bulk_g2s(smem_u32(sm + S::o_csr), db + Hp->o_csr8, b_pts, bar);
+            if (b_pts) {                                 // (a world of all-FIXED pieces has nothing to simulate)
+                bulk_g2s(smem_u32(sm + S::o_pos), g2, b_pts, bar);
+                bulk_g2s(smem_u32(sm + S::o_vel), g2 + Pd, b_pts, bar);
+                bulk_g2s(smem_u32(sm + S::o_vt), g2 + 3 * Pd, b_pts, bar);
+                bulk_g2s(smem_u32(sm + S::o_csr), db + Hp->o_csr8, b_pts, bar);
+            }
             if (b_goal) bulk_g2s(smem_u32(sm + S::o_goal), gstate + 8 * (size_t)Pd, b_goal, bar);
             if (b_eidx) bulk_g2s(smem_u32(sm + S::o_eidx), db + Hp->o_eidx, b_eidx, bar);
             if (b_etab) bulk_g2s(smem_u32(sm + S::o_etab), db + Hp->o_etab, b_etab, bar);

@@ -94,3 +94,20 @@ def test_chunked_step_in_a_cuda_graph(monkeypatch):
     assert envs[0]._graph is not None and envs[0].B.last_launches > envs[1].B.last_launches
     for e in envs:
         e.close()
+
+
+def test_world_without_simulated_points_steps():
+    """a world of all-FIXED pieces (nothing to integrate: every copy of the stage-in has size zero) steps and counts time"""
+    from modularevogym_b200.world import WorldSpec
+    w = WorldSpec(width=12, height=6)
+    floor = np.full((1, 12), 5, dtype=np.int64)
+    w.add_from_array("floor", floor, 0, 0, np.stack((np.arange(11), np.arange(1, 12))).astype(np.int64))
+    B = capi.Batch(0)
+    B.add_world(w)
+    B.add_world(workloads.world_for("walker5x5", 0))
+    B.finalize()
+    for s in range(3):
+        n, flags = B.step(1, True)
+        assert n == 0 and not flags.any()
+    assert B.get_time(0) == 3 and B.get_time(1) == 3
+    B.close()
