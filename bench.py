@@ -526,6 +526,8 @@ def main_ours(args) -> None:
         gms = []
         for tensor in (com_dev, obs_dev):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            gather_env_rows(tensor, world * n)                                     # throw-away at THIS size (output allocation, NCCL buffers)
+            torch.cuda.synchronize()
             dist.barrier()
             e0.record()
             for _ in range(5):
