@@ -225,6 +225,8 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_OBSTACLE_TRAVERSER 4  /* WalkingBumpy2, evogym/envs/traverse.py:350-426 (ObstacleTraverser-v1): "other" observation =
                                            [vel com 2, orientation 1, get_floor_obs("robot", ["ground"], 5) 11]; the flat observation
                                            of this task holds [vel com, relative positions] only */
+#define MEVO_TASK_BRIDGE_WALKER 5       /* SoftBridge, evogym/envs/walk.py:122-232 (BridgeWalker-v0): Walker's reward, goal at x > 60 voxels;
+                                           "other" = [vel com 2, orientation 1]; flat = [vel com, orientation, relative positions] */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

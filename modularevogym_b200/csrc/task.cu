@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || p.task == 4) {                    // walk.py:70-84; traverse.py:20-26 (StairsBase.get_reward)
+    if (p.task == 0 || p.task == 4 || p.task == 5) {     // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3) {                            // climb.py:96-99
         reward = rf_y - ri_y;
@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     if ((p.task == 0 || p.task == 1) && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
     if (p.task == 3 && rf_y > 86 * kVoxel) { done = true; reward += 1.0; }        // climb.py:107-109
     if (p.task == 4 && rf_x > 59 * kVoxel) { done = true; reward += 2.0; }        // traverse.py:420-423
+    if (p.task == 5 && rf_x > 60 * kVoxel) { done = true; reward += 1.0; }        // walk.py:190-193
     int flags = (done ? 1 : 0) | (unstable ? 4 : 0);
     int ep = p.episode_len[env] + 1;
     if (p.max_episode_steps > 0 && ep >= p.max_episode_steps) {   // gym TimeLimit: truncated = not already done
@@ -352,7 +353,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 4) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 5) throw std::runtime_error("task_configure: unknown task id");
     if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -374,7 +375,8 @@ void Batch::task_build() {
     T.vox_idx.clear(); T.vox_mat.clear();
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
-    T.other_width = (T.task == 1 || T.task == 2) ? 6 : T.task == 4 ? 14 : 2;       // task 4: vel com 2 + orientation 1 + floor sight 11
+    // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
+    T.other_width = (T.task == 1 || T.task == 2) ? 6 : T.task == 4 ? 14 : T.task == 5 ? 3 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
@@ -511,6 +513,18 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     CUDA_CHECK(cudaGetLastError());
+    if (T.task == 5) {
+        // BridgeWalker-v0 (walk.py:161-165, base.py:656-657): column 2 of "other" and of the flat observation = get_ort_obs("robot")
+        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+        if (other) {
+            if (other_stride < 3) throw std::runtime_error("task_outputs: the 'other' observation of this task is 3 wide");
+            object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
+        }
+        if (flat) {
+            if (flat_stride < 3) throw std::runtime_error("task_outputs: the flat observation of this task is at least 3 wide");
+            object_orientation_strided_device(T.robot_obj, static_cast<char*>(flat) + 2 * el, flat_stride, is_f32);
+        }
+    }
     if (T.task == 4 && other) {
         // ObstacleTraverser-v1 (get_other_obs, base.py:706-714): [vel com, orientation, get_floor_obs("robot", ["ground"], 5)]
         if (other_stride < 14) throw std::runtime_error("task_outputs: the 'other' observation of this task is 14 wide");

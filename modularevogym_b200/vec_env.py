@@ -18,8 +18,8 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, climber_world, full_connectivity, obstacle_traverser_world, pusher_world, thrower_world,
-                    walker_world)
+from .world import (WorldSpec, bridge_walker_world, climber_world, full_connectivity, obstacle_traverser_world, pusher_world,
+                    thrower_world, walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
 # (evogym/envs/__init__.py:16-20,125-129,149-153))
@@ -29,6 +29,7 @@ TASKS = {
     "Thrower-v0": (2, thrower_world, "package", 300),
     "Climber-v0": (3, climber_world, None, 400),                              # evogym/envs/climb.py:38-112, __init__.py:187-191
     "ObstacleTraverser-v1": (4, obstacle_traverser_world, None, 1000),        # evogym/envs/traverse.py:350-426, __init__.py:76-80
+    "BridgeWalker-v0": (5, bridge_walker_world, None, 500),                   # evogym/envs/walk.py:122-232, __init__.py:22-26
 }
 
 

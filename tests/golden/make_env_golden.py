@@ -130,16 +130,20 @@ def main():
     warnings.filterwarnings("ignore")
     install_stubs()
 
-    from evogym.envs.walk import WalkingFlat
+    from evogym.envs.walk import SoftBridge, WalkingFlat
     from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
     from evogym.envs.climb import Climb0
     from evogym.envs.traverse import WalkingBumpy2
     from evogym import sample_robot
 
     tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
-             "climber": (Climb0, "Climber-v0"), "obstacle": (WalkingBumpy2, "ObstacleTraverser-v1")}
+             "climber": (Climb0, "Climber-v0"), "obstacle": (WalkingBumpy2, "ObstacleTraverser-v1"),
+             "bridgewalker": (SoftBridge, "BridgeWalker-v0")}
+    only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
+        if only and task not in only:
+            continue
         for seed in ((0, 1, 2) if task in ("walker", "pusher", "thrower") else (0,)):
             random.seed(100 + seed)
             np.random.seed(100 + seed)
@@ -187,6 +191,8 @@ def main():
             print(path, "reward sum", float(np.sum(rew)), "modular width", out["modular_obs"].shape[1],
                   "flat == modular rewards:", np.array_equal(out["reward"], out["modular_reward"]))
 
+    if only:
+        return
     # ---- terrain sight + orientation observations (base.py:258-372): ObstacleTraverser-v1 (floor, "ground"), CaveCrawler-v0
     # (floor + ceil, "terrain"), Climber-v2 (ceil, "pipe"); flat mode, the envs' own sight_dist
     from evogym.envs.traverse import WalkingBumpy2

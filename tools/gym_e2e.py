@@ -98,7 +98,7 @@ def main():
     # ---- the reference's smoke script (examples/modularevogym_test.py:1-37) on the fixture environments
     random.seed(0)
     np.random.seed(0)
-    for env_id in ("Walker-v0", "Pusher-v0", "Thrower-v0", "Climber-v0", "ObstacleTraverser-v1"):
+    for env_id in ("Walker-v0", "Pusher-v0", "Thrower-v0", "Climber-v0", "ObstacleTraverser-v1", "BridgeWalker-v0"):
         body, connections = sample_robot((5, 5))
         env = gym.make(env_id, body=body)
         env = gym.make(env_id, body=body, mode="modular", env_id=env_id)
