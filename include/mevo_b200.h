@@ -227,6 +227,13 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
                                            of this task holds [vel com, relative positions] only */
 #define MEVO_TASK_BRIDGE_WALKER 5       /* SoftBridge, evogym/envs/walk.py:122-232 (BridgeWalker-v0): Walker's reward, goal at x > 60 voxels;
                                            "other" = [vel com 2, orientation 1]; flat = [vel com, orientation, relative positions] */
+/* the other environments of traverse.py's StairsBase family: reward, "other" observation and flat observation as
+ * MEVO_TASK_OBSTACLE_TRAVERSER; goal column 79 / 69 / 74.  ObstacleTraverser-v0 and DownStepper-v0 also end the episode with
+ * reward - 3 when the robot lies on its back (orientation in (pi/2, 3pi/2), traverse.py:226-228, 325-327).  UpStepper-v0 has
+ * that rule (with a wider band) in flat mode only (traverse.py:124-129); this layer serves its modular mode, so it has none. */
+#define MEVO_TASK_OBSTACLE_TRAVERSER_V0 6   /* WalkingBumpy, traverse.py:251-347 */
+#define MEVO_TASK_UP_STEPPER 7              /* StepsUp, traverse.py:51-149 */
+#define MEVO_TASK_DOWN_STEPPER 8            /* StepsDown, traverse.py:152-248 */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -51,6 +51,8 @@ struct TaskEnvRec {                      // 32 bytes per environment
     int n_act;
 };
 
+constexpr double kPi = 3.14159265358979323846;       // math.pi
+
 struct TaskParams {
     const double* state;
     double* state_rw;
@@ -68,6 +70,11 @@ struct TaskParams {
     void* modular; int modular_stride;
     void* other; int other_stride;
     int n_envs, task, max_episode_steps, reset_done, other_width;
+    // stairs family (tasks 4, 6, 7, 8): goal column; orientation of the robot after this step (nullptr: no orientation rule) and at
+    // the last observation -- an unstable step saved no snapshot, the environment then reads the old one (Sim.cpp:105-115)
+    double goal_x;
+    const double* ort_now;
+    double* ort_prev;
 };
 
 struct ObjMeans { double ax, ay, bx, by, cx, cy, dx, dy; };
@@ -117,7 +124,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || p.task == 4 || p.task == 5) {     // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
+    if (p.task == 0 || p.task >= 4) {                    // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3) {                            // climb.py:96-99
         reward = rf_y - ri_y;
@@ -134,7 +141,12 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     if (unstable) reward -= 3.0;
     if ((p.task == 0 || p.task == 1) && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
     if (p.task == 3 && rf_y > 86 * kVoxel) { done = true; reward += 1.0; }        // climb.py:107-109
-    if (p.task == 4 && rf_x > 59 * kVoxel) { done = true; reward += 2.0; }        // traverse.py:420-423
+    if ((p.task == 4 || p.task >= 6) && rf_x > p.goal_x * kVoxel) { done = true; reward += 2.0; }   // traverse.py:120-123, 222-225, 321-324, 420-423
+    if (p.ort_now) {
+        // DownStepper-v0 / ObstacleTraverser-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327)
+        const double ort = unstable ? p.ort_prev[env] : p.ort_now[env];
+        if (ort > kPi / 2 && ort < 3 * kPi / 2) { done = true; reward -= 3.0; }
+    }
     if (p.task == 5 && rf_x > 60 * kVoxel) { done = true; reward += 1.0; }        // walk.py:190-193
     int flags = (done ? 1 : 0) | (unstable ? 4 : 0);
     int ep = p.episode_len[env] + 1;
@@ -308,13 +320,15 @@ struct Batch::Task {
     unsigned char* d_vox_mat = nullptr;
     short* d_act_vox = nullptr;
     double* d_prev = nullptr;
+    double* d_ort_now = nullptr;         // orientation rule of tasks 6, 8: after the step / at the last observation
+    double* d_ort_prev = nullptr;
     int* d_episode = nullptr;
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -353,7 +367,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 5) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 8) throw std::runtime_error("task_configure: unknown task id");
     if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -376,7 +390,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 1 || T.task == 2) ? 6 : T.task == 4 ? 14 : T.task == 5 ? 3 : 2;
+    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || T.task >= 6) ? 14 : T.task == 5 ? 3 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
@@ -431,7 +445,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, (T.task == 4 ? 2 : T.other_width) + 2 * r.r_count);
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || T.task >= 6) ? 2 : T.other_width) + 2 * r.r_count);
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -444,6 +458,9 @@ void Batch::task_build() {
     CUDA_CHECK(cudaMalloc(&T.d_prev, sizeof(double) * 4 * n));
     CUDA_CHECK(cudaMalloc(&T.d_episode, sizeof(int) * n));
     CUDA_CHECK(cudaMemset(T.d_prev, 0, sizeof(double) * 4 * n));
+    CUDA_CHECK(cudaMalloc(&T.d_ort_now, sizeof(double) * n));
+    CUDA_CHECK(cudaMalloc(&T.d_ort_prev, sizeof(double) * n));
+    CUDA_CHECK(cudaMemset(T.d_ort_prev, 0, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_episode, 0, sizeof(int) * n));
     T.epoch = finalize_epoch_;
 }
@@ -508,7 +525,14 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    p.other_width = T.task == 4 ? 2 : T.other_width;     // task 4: the kernel writes the velocity, the rest is filled below
+    const bool stairs = T.task == 4 || T.task >= 6;
+    p.other_width = stairs ? 2 : T.other_width;          // stairs family: the kernel writes the velocity, the rest is filled below
+    p.goal_x = T.task == 4 ? 59 : T.task == 6 ? 79 : T.task == 7 ? 69 : 74;
+    p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
+    if ((T.task == 6 || T.task == 8) && (reward || done)) {
+        object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
+        p.ort_now = T.d_ort_now;
+    }
     const int grid = (p.n_envs + 3) / 4;
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
@@ -525,8 +549,9 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
             object_orientation_strided_device(T.robot_obj, static_cast<char*>(flat) + 2 * el, flat_stride, is_f32);
         }
     }
-    if (T.task == 4 && other) {
-        // ObstacleTraverser-v1 (get_other_obs, base.py:706-714): [vel com, orientation, get_floor_obs("robot", ["ground"], 5)]
+    if (T.task == 6 || T.task == 8) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);   // of the (possibly reset) state
+    if (stairs && other) {
+        // ObstacleTraverser-v0 / -v1, UpStepper-v0, DownStepper-v0 (get_other_obs, base.py:706-714): [vel com, orientation, get_floor_obs("robot", ["ground"], 5)]
         if (other_stride < 14) throw std::runtime_error("task_outputs: the 'other' observation of this task is 14 wide");
         const size_t el = is_f32 ? sizeof(float) : sizeof(double);
         object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);

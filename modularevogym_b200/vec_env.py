@@ -18,8 +18,8 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, bridge_walker_world, climber_world, full_connectivity, obstacle_traverser_world, pusher_world,
-                    thrower_world, walker_world)
+from .world import (WorldSpec, bridge_walker_world, climber_world, down_stepper_world, full_connectivity, obstacle_traverser_v0_world,
+                    obstacle_traverser_world, pusher_world, thrower_world, up_stepper_world, walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
 # (evogym/envs/__init__.py:16-20,125-129,149-153))
@@ -30,6 +30,9 @@ TASKS = {
     "Climber-v0": (3, climber_world, None, 400),                              # evogym/envs/climb.py:38-112, __init__.py:187-191
     "ObstacleTraverser-v1": (4, obstacle_traverser_world, None, 1000),        # evogym/envs/traverse.py:350-426, __init__.py:76-80
     "BridgeWalker-v0": (5, bridge_walker_world, None, 500),                   # evogym/envs/walk.py:122-232, __init__.py:22-26
+    "ObstacleTraverser-v0": (6, obstacle_traverser_v0_world, None, 1000),     # traverse.py:251-347, __init__.py:70-74
+    "UpStepper-v0": (7, up_stepper_world, None, 600),                         # traverse.py:51-149, __init__.py:58-62
+    "DownStepper-v0": (8, down_stepper_world, None, 500),                     # traverse.py:152-248, __init__.py:64-68
 }
 
 
@@ -51,8 +54,8 @@ class BatchedEvoGymEnv:
         if env_id not in TASKS:
             raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
         task, builder, package, limit = TASKS[env_id]
-        if task == 4 and mode != "modular":
-            raise ValueError("ObstacleTraverser-v1 is available in modular mode only (its flat observation interleaves orientation "
+        if task in (4, 6, 7, 8) and mode != "modular":
+            raise ValueError(f"{env_id} is available in modular mode only (its flat observation interleaves orientation "
                              "and sight values with a per-robot number of positions)")
         self.env_id, self.mode, self.device_index = env_id, mode, device
         self.num_envs = len(bodies)

@@ -376,6 +376,52 @@ def obstacle_traverser_world(robot: np.ndarray, connections: Optional[np.ndarray
     return w
 
 
+# column heights of evogym/envs/sim_files/ObstacleTraverser-v0.json, 80 x 3
+OBSTACLE_TRAVERSER_V0_HEIGHTS = (1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 1, 1, 1, 1, 1, 2, 1, 1, 1, 1, 2, 2, 1, 1, 1, 1,
+                                 2, 1, 1, 2, 2, 1, 2, 1, 2, 1, 1, 2, 2, 1, 1, 2, 3, 2, 2, 1, 2, 3, 1, 2, 2, 3, 2, 1, 2, 2, 1, 1, 1, 2, 1, 1, 1, 1,
+                                 1, 1, 1)
+# one-voxel-thick stair treads of UpStepper-v0.json (70 x 9) / DownStepper-v0.json (75 x 10): tread y spans the columns
+# [b[y], b[y + 1]] (ascending) resp. [b[h - y], b[h - 1 - y]] read from the right (descending); neighbouring treads share a column
+UP_STEPPER_BREAKS = (0, 20, 29, 36, 42, 47, 51, 55, 61, 69)
+DOWN_STEPPER_BREAKS = (0, 20, 28, 35, 41, 47, 52, 57, 61, 65, 74)
+
+
+def obstacle_traverser_v0_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """ObstacleTraverser-v0 (``sim_files/ObstacleTraverser-v0.json`` + ``evogym/envs/traverse.py:256-257``): 80 x 3 bumpy fixed
+    ``ground``, the robot at voxel (2, 1)."""
+    w = WorldSpec(width=80, height=3)
+    grid = np.zeros((3, 80), dtype=np.int64)
+    for c, hgt in enumerate(OBSTACLE_TRAVERSER_V0_HEIGHTS):
+        grid[3 - hgt:, c] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("robot", robot, 2, 1, connections)
+    return w
+
+
+def up_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """UpStepper-v0 (``sim_files/UpStepper-v0.json`` + ``traverse.py:56-57``): nine ascending treads, the robot at voxel (1, 1)."""
+    b = UP_STEPPER_BREAKS
+    w = WorldSpec(width=70, height=9)
+    grid = np.zeros((9, 70), dtype=np.int64)
+    for y in range(9):
+        grid[8 - y, b[y]:b[y + 1] + 1] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
+def down_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """DownStepper-v0 (``sim_files/DownStepper-v0.json`` + ``traverse.py:157-158``): ten descending treads, the robot at voxel (1, 11)."""
+    b = DOWN_STEPPER_BREAKS
+    w = WorldSpec(width=75, height=10)
+    grid = np.zeros((10, 75), dtype=np.int64)
+    for k in range(10):                               # tread k from the left sits at height 9 - k
+        grid[k, b[k]:b[k + 1] + 1] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("robot", robot, 1, 11, connections)
+    return w
+
+
 BRIDGE_WALKER_PILLARS = (0, 5, 10, 18, 29, 46, 58, 59)     # columns of FIXED voxels from the floor row up to the deck
 
 

@@ -125,6 +125,22 @@ def install_stubs():
     sys.path.insert(0, REF)
 
 
+# DownStepper-v0 / ObstacleTraverser-v0 end the episode when the robot lies on its back (traverse.py:226-228, 325-327); random
+# rollouts of 12 steps never get there, so before step FLIP_STEP the robot is turned by pi about its centre of mass and lifted clear
+# of the ground (engine state only: the step's reward still starts from the last snapshot's centre of mass, which has the same x)
+FLIP_TASKS, FLIP_STEP = ("obstaclev0", "downstepper"), 6
+
+
+def flip_robot(env):
+    r = env._sim._r
+    pos, vel, last, vt = r.get_state()
+    info = r.object_info(list(r.object_names).index("robot"))
+    sl = slice(info["min_point"], info["max_point"] + 1)
+    c = pos[sl].mean(axis=0)
+    pos[sl] = 2.0 * c - pos[sl] + np.array([0.0, 0.6])
+    r.set_state(pos, np.zeros_like(vel), pos.copy(), np.zeros_like(vt))
+
+
 def main():
     import warnings
     warnings.filterwarnings("ignore")
@@ -133,12 +149,13 @@ def main():
     from evogym.envs.walk import SoftBridge, WalkingFlat
     from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
     from evogym.envs.climb import Climb0
-    from evogym.envs.traverse import WalkingBumpy2
+    from evogym.envs.traverse import StepsDown, StepsUp, WalkingBumpy, WalkingBumpy2
     from evogym import sample_robot
 
     tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
              "climber": (Climb0, "Climber-v0"), "obstacle": (WalkingBumpy2, "ObstacleTraverser-v1"),
-             "bridgewalker": (SoftBridge, "BridgeWalker-v0")}
+             "bridgewalker": (SoftBridge, "BridgeWalker-v0"), "obstaclev0": (WalkingBumpy, "ObstacleTraverser-v0"),
+             "upstepper": (StepsUp, "UpStepper-v0"), "downstepper": (StepsDown, "DownStepper-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
@@ -150,6 +167,8 @@ def main():
             body, conn = sample_robot((5, 5))
             rng = np.random.default_rng(500 + seed)
             out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": env_id}
+            if task in FLIP_TASKS:
+                out["flip_step"] = np.int32(FLIP_STEP)
             # ---- flat mode
             env = cls(body, conn, mode=None, env_id=env_id)
             n_act = env.get_actuator_indices("robot").size
@@ -158,6 +177,8 @@ def main():
             flat_obs, rew, done = [np.asarray(obs0, dtype=np.float64)], [], []
             pre = {k: [] for k in ("pos", "vel", "pos_last", "vel_true", "goal")}
             for t in range(n_steps):
+                if task in FLIP_TASKS and t == FLIP_STEP:
+                    flip_robot(env)
                 # engine state the step starts from (teacher forcing in the GPU test)
                 st = env._sim._r.get_state()
                 for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
@@ -178,6 +199,8 @@ def main():
             vox_acts = np.zeros((n_steps, body.size))
             for t in range(n_steps):
                 vox_acts[t, ~act_mask] = acts[t]
+                if task in FLIP_TASKS and t == FLIP_STEP:
+                    flip_robot(envm)
                 o, r, d, _ = envm.step(vox_acts[t].copy())
                 mod_obs.append(np.asarray(o["modular"], dtype=np.float64)); other_obs.append(np.asarray(o["other"], dtype=np.float64))
                 mrew.append(float(r)); mdone.append(bool(d))

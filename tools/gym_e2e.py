@@ -62,30 +62,34 @@ def main():
         env_id = str(g["env_id"])
         body, conn = g["body"], g["connections"]
         rec = {"fixture": os.path.basename(path), "env_id": env_id}
+        # fixtures that turn the robot over in the reference ENGINE before step `flip_step` (make_env_golden.py: the orientation rule
+        # of DownStepper-v0 / ObstacleTraverser-v0) are replayed up to that step: the pybind surface has no state setter
+        n_replay = int(g["flip_step"]) if "flip_step" in g else g["actions"].shape[0]
+        rec["steps"] = n_replay
         # ---- flat mode: gym.make through the registry (TimeLimit wrapper included), stored policy outputs replayed
         env = gym.make(env_id, body=body, connections=conn)
         assert isinstance(env.unwrapped._sim, simulator_cpp.Sim)
         o = env.reset()
         worst_r, worst_o = 0.0, rel_err(o, g["flat_obs"][0])
         dones = []
-        for t in range(g["actions"].shape[0]):
+        for t in range(n_replay):
             o, r, d, _ = env.step(g["actions"][t].copy())
             worst_r = max(worst_r, abs(float(r) - float(g["reward"][t])))
             worst_o = max(worst_o, rel_err(o, g["flat_obs"][t + 1]))
             dones.append(bool(d))
-        rec.update(flat_reward_err=worst_r, flat_obs_err=worst_o, flat_done_equal=dones == g["done"].astype(bool).tolist())
+        rec.update(flat_reward_err=worst_r, flat_obs_err=worst_o, flat_done_equal=dones == g["done"].astype(bool).tolist()[:n_replay])
         env.close()
         # ---- modular mode (ModularEvoGym's per-voxel observation / action layout)
         env = gym.make(env_id, body=body, connections=conn, mode="modular", env_id=env_id)
         o = env.reset()
         worst_r, worst_o = 0.0, max(rel_err(o["modular"], g["modular_obs"][0]), rel_err(o["other"], g["other_obs"][0]))
         dones = []
-        for t in range(g["voxel_actions"].shape[0]):
+        for t in range(n_replay):
             o, r, d, _ = env.step(g["voxel_actions"][t].copy())
             worst_r = max(worst_r, abs(float(r) - float(g["modular_reward"][t])))
             worst_o = max(worst_o, rel_err(o["modular"], g["modular_obs"][t + 1]), rel_err(o["other"], g["other_obs"][t + 1]))
             dones.append(bool(d))
-        rec.update(modular_reward_err=worst_r, modular_obs_err=worst_o, modular_done_equal=dones == g["modular_done"].astype(bool).tolist(),
+        rec.update(modular_reward_err=worst_r, modular_obs_err=worst_o, modular_done_equal=dones == g["modular_done"].astype(bool).tolist()[:n_replay],
                    masks_equal=bool(np.array_equal(env.unwrapped.act_mask, g["act_mask"]) and np.array_equal(env.unwrapped.obs_mask, g["obs_mask"])))
         env.close()
         good = (rec["flat_reward_err"] <= TOL_REWARD and rec["flat_obs_err"] <= TOL_OBS and rec["modular_reward_err"] <= TOL_REWARD and
@@ -98,7 +102,8 @@ def main():
     # ---- the reference's smoke script (examples/modularevogym_test.py:1-37) on the fixture environments
     random.seed(0)
     np.random.seed(0)
-    for env_id in ("Walker-v0", "Pusher-v0", "Thrower-v0", "Climber-v0", "ObstacleTraverser-v1", "BridgeWalker-v0"):
+    for env_id in ("Walker-v0", "Pusher-v0", "Thrower-v0", "Climber-v0", "ObstacleTraverser-v1", "BridgeWalker-v0", "ObstacleTraverser-v0", "UpStepper-v0",
+                   "DownStepper-v0"):
         body, connections = sample_robot((5, 5))
         env = gym.make(env_id, body=body)
         env = gym.make(env_id, body=body, mode="modular", env_id=env_id)
