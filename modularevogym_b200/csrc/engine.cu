@@ -106,16 +106,29 @@ int balanced_envs_per_cta(int n_envs, int epc, int slots) {
     return std::max(1, std::min(epc, per));
 }
 
-// Kernel attributes are per device: every Batch::finalize sets the dynamic shared-memory limit of the kernels its classes
-// use on its own device (several batches on several GPUs of one process each configure their own context).
+// Kernel attributes are per device AND shared by every batch of the process on that device: every Batch::finalize raises the
+// dynamic shared-memory limit of the kernels its classes use, on its own device, to what it needs -- never lowers it, or a batch
+// finalized later with smaller robots would make an earlier batch's launches fail ("invalid argument").
+template <class Kernel>
+void raise_dynamic_smem(Kernel kernel, int bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, int> limit;
+    int dev = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    int& cur = limit[{dev, reinterpret_cast<const void*>(kernel)}];
+    if (bytes > cur) {
+        CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        cur = bytes;
+    }
+}
+
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
 void configure_wstep() {
     constexpr int smem = WarpSmem<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP>::kBytes * EPC;
     static_assert(smem <= kMaxSmemPerBlock, "warp kernel CTA does not fit in shared memory");
-    CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, false>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CUDA_CHECK(cudaFuncSetAttribute(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, true>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    raise_dynamic_smem(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, false>, smem);
+    raise_dynamic_smem(wstep_kernel<PCAP, ECAP, LCAP, PAIRCAP, ITEMCAP, VISCAP, EPC, MINB, true>, smem);
 }
 
 template <int PCAP, int ECAP, int LCAP, int PAIRCAP, int ITEMCAP, int VISCAP, int EPC, int MINB>
@@ -144,7 +157,7 @@ enum class GAction { Configure, Launch };
 template <int G, int MINB, int PPT, bool XD>
 void gstep_do2(GAction what, const StepParams* prm, int smem, cudaStream_t stream) {
     if (what == GAction::Configure)
-        CUDA_CHECK(cudaFuncSetAttribute(gstep_kernel<G, MINB, PPT, XD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        raise_dynamic_smem(gstep_kernel<G, MINB, PPT, XD>, smem);
     else
         gstep_kernel<G, MINB, PPT, XD><<<prm->n_class_envs, G, smem, stream>>>(*prm);
 }

@@ -111,3 +111,41 @@ def test_world_without_simulated_points_steps():
         assert n == 0 and not flags.any()
     assert B.get_time(0) == 3 and B.get_time(1) == 3
     B.close()
+
+
+def test_two_batches_step_concurrently(monkeypatch):
+    """two batches of one GPU enqueue their steps back to back on their own streams: the item-drawing CTAs of one wait only for
+    CTAs that are already running, so sharing the SMs with another batch's kernels cannot stall them; results equal the batches
+    stepped one after the other"""
+    monkeypatch.setenv("MEVO_CHUNK_MIN_WAVES", "0")
+    monkeypatch.setenv("MEVO_WCHUNKS", "5")
+    monkeypatch.setenv("MEVO_CHUNKS", "3")
+
+    def make(offset):
+        B = capi.Batch(0)
+        for i in range(600):
+            B.add_world(workloads.world_for("walker5x5", offset + i))
+        for i in range(40):
+            B.add_world(workloads.world_for("obstacle10", offset + i))
+        B.finalize()
+        return B
+
+    acts = [workloads.clipped_actions(np.random.default_rng(20 + k), (6, 640, 128)) for k in range(2)]
+    ref = []
+    for k in range(2):                                  # one after the other
+        B = make(1000 * k)
+        for s in range(6):
+            B.set_actions(acts[k][s][:, :B.action_stride])
+            B.step(1, True)
+        ref.append([B.get_state(i)[0] for i in range(0, 640, 7)])
+        B.close()
+    Bs = [make(0), make(1000)]
+    for s in range(6):                                  # interleaved, no synchronisation between the two
+        for k in range(2):
+            Bs[k].set_actions(acts[k][s][:, :Bs[k].action_stride])
+            Bs[k].step_async(1, True)
+    for k in range(2):
+        Bs[k].sync()
+        got = [Bs[k].get_state(i)[0] for i in range(0, 640, 7)]
+        assert all(np.array_equal(a, b, equal_nan=True) for a, b in zip(got, ref[k]))
+        Bs[k].close()
