@@ -139,3 +139,45 @@ def test_batchsim_task_layer():
     assert abs(o["reward"][0] - g["reward"][0]) <= 1e-9 and o["done"][0] == 0
     assert rel_err(o["modular"][0], g["modular_obs"][1]) <= 1e-9 and rel_err(o["other"][0], g["other_obs"][1]) <= 1e-9
     assert B.object_orientation(0).shape == (1,)
+
+
+@pytest.mark.gpu
+def test_several_sims_of_different_sizes_step_alternately():
+    """a design loop keeps several `Sim`s alive in one process and steps them in turn: robots of different size classes (a later,
+    smaller one must not lower a kernel's shared-memory limit under an earlier, larger one); each equals the same Sim stepped alone"""
+    import random
+    from modularevogym_b200 import simulator_cpp as m
+    from modularevogym_b200.world import obstacle_traverser_world, sample_large_robot, walker_world
+
+    def build(k):
+        random.seed(900 + k)
+        side = (14, 9, 12, 7, 5)[k]
+        body, conn = sample_large_robot((side, side))
+        w = obstacle_traverser_world(body, conn) if k % 2 == 0 else walker_world(body, conn)
+        sim = m.Sim()
+        sim.init(w.width, w.height)
+        for o in w.load_order():
+            add = sim.read_robot_from_array if o.is_robot else sim.read_object_from_array
+            assert add(o.grid.astype(np.float64), o.connections.astype(np.float64), o.name, o.x, o.y)
+        return sim
+
+    def actions(sim, k, s):
+        idx = np.asarray(sim.get_indices_of_actuators("robot")).ravel()
+        rng = np.random.default_rng(100 * k + s)
+        return np.stack((idx.astype(np.float64), rng.uniform(0.6, 1.6, idx.size)), axis=1)
+
+    alone = []
+    for k in range(5):
+        sim = build(k)
+        for s in range(3):
+            sim.set_action("robot", actions(sim, k, s))
+            sim.step()
+        alone.append(np.asarray(sim.pos_at_time(sim.get_time())).copy())
+        del sim
+    sims = [build(k) for k in range(5)]
+    for s in range(3):
+        for k in range(5):
+            sims[k].set_action("robot", actions(sims[k], k, s))
+            sims[k].step()
+    for k in range(5):
+        assert np.array_equal(np.asarray(sims[k].pos_at_time(sims[k].get_time())), alone[k]), k
