@@ -234,6 +234,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_OBSTACLE_TRAVERSER_V0 6   /* WalkingBumpy, traverse.py:251-347 */
 #define MEVO_TASK_UP_STEPPER 7              /* StepsUp, traverse.py:51-149 */
 #define MEVO_TASK_DOWN_STEPPER 8            /* StepsDown, traverse.py:152-248 */
+#define MEVO_TASK_JUMPER 9                  /* StationaryJump, evogym/envs/jump.py:14-118 (Jumper-v0, the environment of examples/CuCo):
+                                               reward = 10 * rise - 5 * |drift| of the centre of mass, no goal;
+                                               "other" = [vel com 2, get_floor_obs("robot", ["ground"], 2) 5]; modular mode */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

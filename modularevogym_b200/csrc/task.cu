@@ -124,10 +124,12 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || p.task >= 4) {                    // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
+    if (p.task == 0 || (p.task >= 4 && p.task <= 8)) {   // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3) {                            // climb.py:96-99
         reward = rf_y - ri_y;
+    } else if (p.task == 9) {                            // jump.py:72-75
+        reward = (rf_y - ri_y) * 10 - fabs(rf_x - ri_x) * 5;
     } else if (p.task == 1) {                            // manipulate.py:38-58
         reward = (pf_x - pi_x) * 0.75;
         reward += (rf_x - ri_x) * 0.5;
@@ -141,7 +143,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     if (unstable) reward -= 3.0;
     if ((p.task == 0 || p.task == 1) && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
     if (p.task == 3 && rf_y > 86 * kVoxel) { done = true; reward += 1.0; }        // climb.py:107-109
-    if ((p.task == 4 || p.task >= 6) && rf_x > p.goal_x * kVoxel) { done = true; reward += 2.0; }   // traverse.py:120-123, 222-225, 321-324, 420-423
+    if ((p.task == 4 || (p.task >= 6 && p.task <= 8)) && rf_x > p.goal_x * kVoxel) { done = true; reward += 2.0; }   // traverse.py:120-123, 222-225, 321-324, 420-423
     if (p.ort_now) {
         // DownStepper-v0 / ObstacleTraverser-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327)
         const double ort = unstable ? p.ort_prev[env] : p.ort_now[env];
@@ -367,7 +369,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 8) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 9) throw std::runtime_error("task_configure: unknown task id");
     if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -390,7 +392,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || T.task >= 6) ? 14 : T.task == 5 ? 3 : 2;
+    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8)) ? 14 : T.task == 5 ? 3 : T.task == 9 ? 7 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
@@ -445,7 +447,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || T.task >= 6) ? 2 : T.other_width) + 2 * r.r_count);
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || T.task >= 6) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -525,8 +527,8 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    const bool stairs = T.task == 4 || T.task >= 6;
-    p.other_width = stairs ? 2 : T.other_width;          // stairs family: the kernel writes the velocity, the rest is filled below
+    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8);
+    p.other_width = (stairs || T.task == 9) ? 2 : T.other_width;          // stairs family: the kernel writes the velocity, the rest is filled below
     p.goal_x = T.task == 4 ? 59 : T.task == 6 ? 79 : T.task == 7 ? 69 : 74;
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     if ((T.task == 6 || T.task == 8) && (reward || done)) {
@@ -550,6 +552,12 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
         }
     }
     if (T.task == 6 || T.task == 8) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);   // of the (possibly reset) state
+    if (T.task == 9 && other) {
+        // Jumper-v0 (base.py:676-680): [vel com, get_floor_obs("robot", ["ground"], 2)]
+        if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");
+        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+        sight_obs_strided_device(T.robot_obj, {"ground"}, 2, 5.0, false, static_cast<char*>(other) + 2 * el, 5, other_stride, is_f32);
+    }
     if (stairs && other) {
         // ObstacleTraverser-v0 / -v1, UpStepper-v0, DownStepper-v0 (get_other_obs, base.py:706-714): [vel com, orientation, get_floor_obs("robot", ["ground"], 5)]
         if (other_stride < 14) throw std::runtime_error("task_outputs: the 'other' observation of this task is 14 wide");

@@ -422,6 +422,19 @@ def down_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = No
     return w
 
 
+def jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Jumper-v0 (``sim_files/Jumper-v0.json`` + ``evogym/envs/jump.py:19-20``): a 60-wide fixed floor between two 8-voxel walls,
+    the robot at voxel (32, 1)."""
+    w = WorldSpec(width=60, height=8)
+    grid = np.zeros((8, 60), dtype=np.int64)
+    grid[7, :] = VOXEL_TYPES["FIXED"]
+    grid[:, 0] = VOXEL_TYPES["FIXED"]
+    grid[:, 59] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("robot", robot, 32, 1, connections)
+    return w
+
+
 BRIDGE_WALKER_PILLARS = (0, 5, 10, 18, 29, 46, 58, 59)     # columns of FIXED voxels from the floor row up to the deck
 
 

@@ -150,12 +150,14 @@ def main():
     from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
     from evogym.envs.climb import Climb0
     from evogym.envs.traverse import StepsDown, StepsUp, WalkingBumpy, WalkingBumpy2
+    from evogym.envs.jump import StationaryJump
     from evogym import sample_robot
 
     tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
              "climber": (Climb0, "Climber-v0"), "obstacle": (WalkingBumpy2, "ObstacleTraverser-v1"),
              "bridgewalker": (SoftBridge, "BridgeWalker-v0"), "obstaclev0": (WalkingBumpy, "ObstacleTraverser-v0"),
-             "upstepper": (StepsUp, "UpStepper-v0"), "downstepper": (StepsDown, "DownStepper-v0")}
+             "upstepper": (StepsUp, "UpStepper-v0"), "downstepper": (StepsDown, "DownStepper-v0"),
+             "jumper": (StationaryJump, "Jumper-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():

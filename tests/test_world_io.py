@@ -76,7 +76,8 @@ def _same_world(a: W.WorldSpec, b: W.WorldSpec) -> bool:
 BUILDERS = [("Walker-v0", W.walker_world, (1, 1)), ("Pusher-v0", W.pusher_world, (1, 1)), ("Thrower-v0", W.thrower_world, (1, 1)),
             ("Climber-v0", W.climber_world, (1, 1)), ("ObstacleTraverser-v1", W.obstacle_traverser_world, (2, 4)),
             ("BridgeWalker-v0", W.bridge_walker_world, (2, 5)), ("ObstacleTraverser-v0", W.obstacle_traverser_v0_world, (2, 1)),
-            ("UpStepper-v0", W.up_stepper_world, (1, 1)), ("DownStepper-v0", W.down_stepper_world, (1, 11))]
+            ("UpStepper-v0", W.up_stepper_world, (1, 1)), ("DownStepper-v0", W.down_stepper_world, (1, 11)),
+            ("Jumper-v0", W.jumper_world, (32, 1))]
 
 
 @pytest.mark.parametrize("env_id,builder,at", BUILDERS)
