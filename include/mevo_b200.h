@@ -237,6 +237,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_JUMPER 9                  /* StationaryJump, evogym/envs/jump.py:14-118 (Jumper-v0, the environment of examples/CuCo):
                                                reward = 10 * rise - 5 * |drift| of the centre of mass, no goal;
                                                "other" = [vel com 2, get_floor_obs("robot", ["ground"], 2) 5]; modular mode */
+#define MEVO_TASK_HURDLER 10                /* VerticalBarrier, traverse.py:446-536 (Hurdler-v0): StairsBase reward and observation, no goal,
+                                               the orientation rule of MEVO_TASK_DOWN_STEPPER (traverse.py:514-516); modular mode */
+#define MEVO_TASK_CLIMBER_V1 11             /* Climb1, evogym/envs/climb.py:131-231 (Climber-v1): MEVO_TASK_CLIMBER with the goal at y > 65 voxels */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

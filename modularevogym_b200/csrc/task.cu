@@ -70,9 +70,10 @@ struct TaskParams {
     void* modular; int modular_stride;
     void* other; int other_stride;
     int n_envs, task, max_episode_steps, reset_done, other_width;
-    // stairs family (tasks 4, 6, 7, 8): goal column; orientation of the robot after this step (nullptr: no orientation rule) and at
+    // orientation rule (tasks 6, 8, 10): orientation of the robot after this step (nullptr: no orientation rule) and at
     // the last observation -- an unstable step saved no snapshot, the environment then reads the old one (Sim.cpp:105-115)
-    double goal_x;
+    int goal_axis;                       // 0: no goal, 1: robot com x, 2: robot com y beyond `goal` voxels ends the episode with `goal_bonus`
+    double goal, goal_bonus;
     const double* ort_now;
     double* ort_prev;
 };
@@ -124,9 +125,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || (p.task >= 4 && p.task <= 8)) {   // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
+    if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10) {   // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
-    } else if (p.task == 3) {                            // climb.py:96-99
+    } else if (p.task == 3 || p.task == 11) {            // climb.py:96-99, 190-193
         reward = rf_y - ri_y;
     } else if (p.task == 9) {                            // jump.py:72-75
         reward = (rf_y - ri_y) * 10 - fabs(rf_x - ri_x) * 5;
@@ -141,11 +142,11 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         reward = pf_x - pi_x + motion_penalty;
     }
     if (unstable) reward -= 3.0;
-    if ((p.task == 0 || p.task == 1) && rf_x > 99 * kVoxel) { done = true; reward += 1.0; }
-    if (p.task == 3 && rf_y > 86 * kVoxel) { done = true; reward += 1.0; }        // climb.py:107-109
-    if ((p.task == 4 || (p.task >= 6 && p.task <= 8)) && rf_x > p.goal_x * kVoxel) { done = true; reward += 2.0; }   // traverse.py:120-123, 222-225, 321-324, 420-423
+    // goal met (walk.py:79-82, 190-193; manipulate.py:390-393; climb.py:107-109, 201-203; traverse.py:120-123, 222-225, 321-324, 420-423)
+    if (p.goal_axis == 1 && rf_x > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
+    if (p.goal_axis == 2 && rf_y > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
     if (p.ort_now) {
-        // DownStepper-v0 / ObstacleTraverser-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327)
+        // DownStepper-v0 / ObstacleTraverser-v0 / Hurdler-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327, 514-516)
         const double ort = unstable ? p.ort_prev[env] : p.ort_now[env];
         if (ort > kPi / 2 && ort < 3 * kPi / 2) { done = true; reward -= 3.0; }
     }
@@ -369,7 +370,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 9) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 11) throw std::runtime_error("task_configure: unknown task id");
     if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -392,7 +393,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8)) ? 14 : T.task == 5 ? 3 : T.task == 9 ? 7 : 2;
+    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 : T.task == 9 ? 7 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
@@ -447,7 +448,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || T.task >= 6) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10)) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -527,11 +528,16 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8);
-    p.other_width = (stairs || T.task == 9) ? 2 : T.other_width;          // stairs family: the kernel writes the velocity, the rest is filled below
-    p.goal_x = T.task == 4 ? 59 : T.task == 6 ? 79 : T.task == 7 ? 69 : 74;
+    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10;
+    const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10;
+    p.other_width = (stairs || T.task == 9) ? 2 : T.other_width;          // sight tasks: the kernel writes the velocity, the rest is filled below
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11
+    static const int kGoalAxis[12] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2};
+    static const double kGoal[12] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65};
+    static const double kBonus[12] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1};
+    p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
-    if ((T.task == 6 || T.task == 8) && (reward || done)) {
+    if (ort_rule && (reward || done)) {
         object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
         p.ort_now = T.d_ort_now;
     }
@@ -551,7 +557,7 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
             object_orientation_strided_device(T.robot_obj, static_cast<char*>(flat) + 2 * el, flat_stride, is_f32);
         }
     }
-    if (T.task == 6 || T.task == 8) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);   // of the (possibly reset) state
+    if (ort_rule) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);   // of the (possibly reset) state
     if (T.task == 9 && other) {
         // Jumper-v0 (base.py:676-680): [vel com, get_floor_obs("robot", ["ground"], 2)]
         if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");

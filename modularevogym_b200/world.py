@@ -422,6 +422,46 @@ def down_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = No
     return w
 
 
+# column heights of evogym/envs/sim_files/Hurdler-v0.json, 70 x 6
+HURDLER_HEIGHTS = (1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 1, 1, 1, 1, 1, 1, 1, 3, 1, 1, 1, 1, 1, 1, 1, 2, 1, 1, 1, 1, 1, 1, 1, 3, 3, 1, 1, 1, 1, 1, 1, 1, 2,
+                   1, 1, 1, 1, 1, 1, 3, 1, 1, 1, 1, 1, 3, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 6)
+# rows of evogym/envs/sim_files/Climber-v1.json (7 x 70, top row first) as runs of (left wall, right wall, rows): F = FIXED,
+# S = SOFT; "==" = a full FIXED row (the cap and the floor of the pipe)
+CLIMBER_V1_WALLS = (("==", 1), ("FF", 4), ("SF", 5), ("FS", 4), ("FF", 2), ("SS", 3), ("FF", 4), ("SS", 2), ("FF", 3), ("SF", 3), ("FF", 1),
+                    ("FS", 2), ("SS", 1), ("FF", 2), ("SF", 2), ("FF", 1), ("FS", 1), ("SS", 1), ("SF", 1), ("FF", 2), ("FS", 2), ("SF", 2),
+                    ("FF", 3), ("FS", 3), ("FF", 2), ("SF", 2), ("FF", 2), ("FS", 1), ("FF", 7), ("==", 1))
+
+
+def hurdler_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Hurdler-v0 (``sim_files/Hurdler-v0.json`` + ``evogym/envs/traverse.py:451-452``): fixed ``ground`` with barriers of 2 - 3 voxels
+    and a 6-voxel end wall, the robot at voxel (2, 4)."""
+    w = WorldSpec(width=70, height=6)
+    grid = np.zeros((6, 70), dtype=np.int64)
+    for c, hgt in enumerate(HURDLER_HEIGHTS):
+        grid[6 - hgt:, c] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    w.add_from_array("robot", robot, 2, 4, connections)
+    return w
+
+
+def climber_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Climber-v1 (``sim_files/Climber-v1.json`` + ``evogym/envs/climb.py:139-140``): a 5-wide pipe whose walls alternate FIXED and
+    SOFT stretches -- one object, so the whole pipe is simulated --, the robot at voxel (1, 1)."""
+    w = WorldSpec(width=7, height=70)
+    grid = np.zeros((70, 7), dtype=np.int64)
+    t = {"F": VOXEL_TYPES["FIXED"], "S": VOXEL_TYPES["SOFT"]}
+    r = 0
+    for walls, n in CLIMBER_V1_WALLS:
+        if walls == "==":
+            grid[r:r + n, :] = VOXEL_TYPES["FIXED"]
+        else:
+            grid[r:r + n, 0], grid[r:r + n, 6] = t[walls[0]], t[walls[1]]
+        r += n
+    w.add_from_array("pipe", grid, 0, 0)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
 def jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
     """Jumper-v0 (``sim_files/Jumper-v0.json`` + ``evogym/envs/jump.py:19-20``): a 60-wide fixed floor between two 8-voxel walls,
     the robot at voxel (32, 1)."""

@@ -128,7 +128,7 @@ def install_stubs():
 # DownStepper-v0 / ObstacleTraverser-v0 end the episode when the robot lies on its back (traverse.py:226-228, 325-327); random
 # rollouts of 12 steps never get there, so before step FLIP_STEP the robot is turned by pi about its centre of mass and lifted clear
 # of the ground (engine state only: the step's reward still starts from the last snapshot's centre of mass, which has the same x)
-FLIP_TASKS, FLIP_STEP = ("obstaclev0", "downstepper"), 6
+FLIP_TASKS, FLIP_STEP = ("obstaclev0", "downstepper", "hurdler"), 6
 
 
 def flip_robot(env):
@@ -148,8 +148,8 @@ def main():
 
     from evogym.envs.walk import SoftBridge, WalkingFlat
     from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
-    from evogym.envs.climb import Climb0
-    from evogym.envs.traverse import StepsDown, StepsUp, WalkingBumpy, WalkingBumpy2
+    from evogym.envs.climb import Climb0, Climb1
+    from evogym.envs.traverse import StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
     from evogym import sample_robot
 
@@ -157,7 +157,7 @@ def main():
              "climber": (Climb0, "Climber-v0"), "obstacle": (WalkingBumpy2, "ObstacleTraverser-v1"),
              "bridgewalker": (SoftBridge, "BridgeWalker-v0"), "obstaclev0": (WalkingBumpy, "ObstacleTraverser-v0"),
              "upstepper": (StepsUp, "UpStepper-v0"), "downstepper": (StepsDown, "DownStepper-v0"),
-             "jumper": (StationaryJump, "Jumper-v0")}
+             "jumper": (StationaryJump, "Jumper-v0"), "hurdler": (VerticalBarrier, "Hurdler-v0"), "climberv1": (Climb1, "Climber-v1")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
