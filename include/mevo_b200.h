@@ -240,6 +240,10 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_HURDLER 10                /* VerticalBarrier, traverse.py:446-536 (Hurdler-v0): StairsBase reward and observation, no goal,
                                                the orientation rule of MEVO_TASK_DOWN_STEPPER (traverse.py:514-516); modular mode */
 #define MEVO_TASK_CLIMBER_V1 11             /* Climb1, evogym/envs/climb.py:131-231 (Climber-v1): MEVO_TASK_CLIMBER with the goal at y > 65 voxels */
+#define MEVO_TASK_CAVE_CRAWLER 12           /* Duck, evogym/envs/walk.py:235-345 (CaveCrawler-v0): Walker's reward, goal at x > 69 voxels;
+                                               "other" = [vel com 2, floor sight 11, ceiling sight 11] over "terrain"; modular mode */
+#define MEVO_TASK_CLIMBER_V2 13             /* Climb2, evogym/envs/climb.py:226-320 (Climber-v2): reward = rise + 0.2 * advance, no goal;
+                                               "other" = [vel com 2, orientation 1, ceiling sight 7 over "pipe"]; modular mode */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

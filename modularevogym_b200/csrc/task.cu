@@ -125,10 +125,12 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10) {   // walk.py:70-84, 180-183; traverse.py:20-26 (StairsBase.get_reward)
+    if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3 || p.task == 11) {            // climb.py:96-99, 190-193
         reward = rf_y - ri_y;
+    } else if (p.task == 13) {                           // climb.py:288-291
+        reward = (rf_y - ri_y) + (rf_x - ri_x) * 0.2;
     } else if (p.task == 9) {                            // jump.py:72-75
         reward = (rf_y - ri_y) * 10 - fabs(rf_x - ri_x) * 5;
     } else if (p.task == 1) {                            // manipulate.py:38-58
@@ -370,7 +372,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 11) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 13) throw std::runtime_error("task_configure: unknown task id");
     if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -393,7 +395,8 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 : T.task == 9 ? 7 : 2;
+    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+                    T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
@@ -448,7 +451,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10)) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task >= 12) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -530,11 +533,11 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10;
-    p.other_width = (stairs || T.task == 9) ? 2 : T.other_width;          // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11
-    static const int kGoalAxis[12] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2};
-    static const double kGoal[12] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65};
-    static const double kBonus[12] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1};
+    p.other_width = (stairs || T.task == 9 || T.task >= 12) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13
+    static const int kGoalAxis[14] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0};
+    static const double kGoal[14] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0};
+    static const double kBonus[14] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     if (ort_rule && (reward || done)) {
@@ -558,6 +561,20 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
         }
     }
     if (ort_rule) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);   // of the (possibly reset) state
+    if (T.task == 12 && other) {
+        // CaveCrawler-v0 (base.py:658-663): [vel com, get_floor_obs("robot", ["terrain"], 5), get_ceil_obs("robot", ["terrain"], 5)]
+        if (other_stride < 24) throw std::runtime_error("task_outputs: the 'other' observation of this task is 24 wide");
+        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+        sight_obs_strided_device(T.robot_obj, {"terrain"}, 5, 5.0, false, static_cast<char*>(other) + 2 * el, 11, other_stride, is_f32);
+        sight_obs_strided_device(T.robot_obj, {"terrain"}, 5, 5.0, true, static_cast<char*>(other) + 13 * el, 11, other_stride, is_f32);
+    }
+    if (T.task == 13 && other) {
+        // Climber-v2 (base.py:668-673): [vel com, get_ort_obs("robot"), get_ceil_obs("robot", ["pipe"], 3)]
+        if (other_stride < 10) throw std::runtime_error("task_outputs: the 'other' observation of this task is 10 wide");
+        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+        object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
+        sight_obs_strided_device(T.robot_obj, {"pipe"}, 3, 5.0, true, static_cast<char*>(other) + 3 * el, 7, other_stride, is_f32);
+    }
     if (T.task == 9 && other) {
         // Jumper-v0 (base.py:676-680): [vel com, get_floor_obs("robot", ["ground"], 2)]
         if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");

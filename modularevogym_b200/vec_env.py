@@ -18,7 +18,7 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, bridge_walker_world, climber_v1_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
+from .world import (WorldSpec, bridge_walker_world, cave_crawler_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
                     jumper_world, obstacle_traverser_v0_world,
                     obstacle_traverser_world, pusher_world, thrower_world, up_stepper_world, walker_world)
 
@@ -36,6 +36,8 @@ TASKS = {
     "DownStepper-v0": (8, down_stepper_world, None, 500),                     # traverse.py:152-248, __init__.py:64-68
     "Hurdler-v0": (10, hurdler_world, None, 1000),                            # traverse.py:446-536, __init__.py:82-86
     "Climber-v1": (11, climber_v1_world, None, 600),                          # climb.py:131-231, __init__.py:193-197
+    "CaveCrawler-v0": (12, cave_crawler_world, None, 1000),                   # walk.py:235-345, __init__.py:28-32
+    "Climber-v2": (13, climber_v2_world, None, 1000),                         # climb.py:226-320, __init__.py:199-203
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 
@@ -58,7 +60,7 @@ class BatchedEvoGymEnv:
         if env_id not in TASKS:
             raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
         task, builder, package, limit = TASKS[env_id]
-        if task in (4, 6, 7, 8, 9, 10) and mode != "modular":
+        if task in (4, 6, 7, 8, 9, 10, 12, 13) and mode != "modular":
             raise ValueError(f"{env_id} is available in modular mode only (its flat observation interleaves orientation "
                              "and sight values with a per-robot number of positions)")
         self.env_id, self.mode, self.device_index = env_id, mode, device

@@ -462,6 +462,93 @@ def climber_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None
     return w
 
 
+# terrain of evogym/envs/sim_files/CaveCrawler-v0.json (70 x 14, one object "terrain") and Climber-v2.json (27 x 42, "pipe"), top row
+# first: F = FIXED, S = SOFT, . = empty
+CAVE_CRAWLER_ROWS = (
+    "....................F.................................................",
+    "....................F.................................................",
+    "....................F.................................................",
+    "....................F.................................................",
+    "....................F................................................F",
+    "....................F................................................F",
+    "....................FF............FFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFF",
+    ".....................SSSSSSSSSSSSSS....SSSSSSSSSSSSSSS....FFF........F",
+    ".......................SSSSSSSSSS.........SSSSSSSSSS.......FF........F",
+    ".........................SSSSSS............................F.........F",
+    ".....................................................................F",
+    ".....................................................................F",
+    "..............................................SSSSS..................F",
+    "FFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFF",
+)
+CLIMBER_V2_ROWS = (
+    ".......FFFFFFFFFFFFFFFFFFFF",
+    "......FF..................F",
+    ".....FF...................F",
+    "....FF....................F",
+    "...FF.....................F",
+    "...F......................F",
+    "...F.......FFFFFFFFFFFFFFFF",
+    "..FF......FF...............",
+    "..F......FF................",
+    "..F.....FF.................",
+    "..F.....F..................",
+    ".FF.....F..................",
+    ".F......F..................",
+    ".F......F..................",
+    ".F.....FF..................",
+    ".F.....F...................",
+    ".F.....F...................",
+    ".F.....F...................",
+    "FF.....F...................",
+    "F......F...................",
+    "F......F...................",
+    "F......F...................",
+    "F.....FF...................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "F.....F....................",
+    "FFFFFFF....................",
+)
+
+
+def grid_from_rows(rows: Sequence[str]) -> np.ndarray:
+    code = {".": 0, "R": VOXEL_TYPES["RIGID"], "S": VOXEL_TYPES["SOFT"], "H": VOXEL_TYPES["H_ACT"], "V": VOXEL_TYPES["V_ACT"], "F": VOXEL_TYPES["FIXED"]}
+    return np.array([[code[ch] for ch in row] for row in rows], dtype=np.int64)
+
+
+def cave_crawler_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """CaveCrawler-v0 (``sim_files/CaveCrawler-v0.json`` + ``evogym/envs/walk.py:240-241``): a floor, a fixed ceiling with SOFT
+    stalactites, one object ``terrain`` (simulated: it has SOFT voxels); the robot at voxel (1, 2)."""
+    w = WorldSpec(width=70, height=14)
+    w.add_from_array("terrain", grid_from_rows(CAVE_CRAWLER_ROWS), 0, 0)
+    w.add_from_array("robot", robot, 1, 2, connections)
+    return w
+
+
+def climber_v2_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Climber-v2 (``sim_files/Climber-v2.json`` + ``evogym/envs/climb.py:233-234``): a fixed ``pipe`` that bends to the right at the
+    top; the robot at voxel (1, 1)."""
+    w = WorldSpec(width=27, height=42)
+    w.add_from_array("pipe", grid_from_rows(CLIMBER_V2_ROWS), 0, 0)
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
 def jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
     """Jumper-v0 (``sim_files/Jumper-v0.json`` + ``evogym/envs/jump.py:19-20``): a 60-wide fixed floor between two 8-voxel walls,
     the robot at voxel (32, 1)."""

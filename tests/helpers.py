@@ -35,7 +35,8 @@ class EnvGolden:
         self.env_id = str(self.z["env_id"])
         self.task = {"Walker-v0": 0, "Pusher-v0": 1, "Thrower-v0": 2, "Climber-v0": 3, "ObstacleTraverser-v1": 4,
                      "BridgeWalker-v0": 5, "ObstacleTraverser-v0": 6, "UpStepper-v0": 7, "DownStepper-v0": 8,
-                     "Jumper-v0": 9, "Hurdler-v0": 10, "Climber-v1": 11}[self.env_id]
+                     "Jumper-v0": 9, "Hurdler-v0": 10, "Climber-v1": 11, "CaveCrawler-v0": 12,
+                     "Climber-v2": 13}[self.env_id]
         self.package = "package" if self.task in (1, 2) else None
         self.n_steps = int(self.z["reward"].shape[0])
 
