@@ -149,3 +149,32 @@ def test_two_batches_step_concurrently(monkeypatch):
         got = [Bs[k].get_state(i)[0] for i in range(0, 640, 7)]
         assert all(np.array_equal(a, b, equal_nan=True) for a, b in zip(got, ref[k]))
         Bs[k].close()
+
+
+def test_build_step_close_cycles_leak_nothing(monkeypatch):
+    """design loops rebuild batches all the time: build -> step (item form, chunked lanes) -> close, repeated, leaves the free device
+    memory where it was (streams, events, item counters, scratch blocks, snapshot slots are all released)"""
+    import torch
+    monkeypatch.setenv("MEVO_CHUNK_MIN_WAVES", "0")
+    monkeypatch.setenv("MEVO_WCHUNKS", "3")
+    monkeypatch.setenv("MEVO_CHUNKS", "2")
+
+    def cycle(k):
+        B = capi.Batch(0)
+        for i in range(64):
+            B.add_world(workloads.world_for("walker5x5", 50 * k + i))
+        for i in range(12):
+            B.add_world(workloads.world_for("obstacle10", 50 * k + i))
+        B.finalize()
+        B.step(1, True)
+        B.save_snapshot(1)
+        B.close()
+
+    cycle(0)
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info(0)[0]
+    for k in range(1, 25):
+        cycle(k)
+    torch.cuda.synchronize()
+    free1 = torch.cuda.mem_get_info(0)[0]
+    assert free0 - free1 < 8 << 20, (free0, free1)
