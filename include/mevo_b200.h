@@ -53,6 +53,21 @@ int mevo_batch_begin_env(mevo_batch* b, int world_w, int world_h);
 int mevo_batch_add_object(mevo_batch* b, int env, const double* grid, int w, int h, const double* conn,
                           int k, const char* name, double x, double y, int is_robot);
 
+/* One call for what a design loop does per environment, n_envs times (env.update(body, connections), evogym/envs/walk.py:105-120:
+ * a new world from the environment's world file + the new robot): begin_env, the robot `robot_name` at voxel (rx, ry), then the
+ * n_terrain terrain objects -- the same for every environment, given in the order EvoSim loads them (robots first, the others
+ * alphabetical, evogym/sim.py:52-62; none of them may be a robot).  World size per environment: (world_w, world_h) grown to hold
+ * the robot, like EvoWorld.add_object does.
+ *   terrain_grids / terrain_conn : the objects' grids (h x w) and connection lists (2 x k) back to back; terrain_wh = w, h per object,
+ *   terrain_k = k per object, terrain_xy = x, y per object, terrain_names = the names separated by '\n'
+ *   robot_grids / robot_conn / robot_wh / robot_k : the same per environment
+ * Returns the id of the first new environment (ids are consecutive), MEVO_ERR when an object is refused (the message names the
+ * environment; environments added before it stay). */
+int mevo_batch_add_robot_envs(mevo_batch* b, int n_envs, int world_w, int world_h, int n_terrain, const double* terrain_grids,
+                              const int* terrain_wh, const double* terrain_conn, const int* terrain_k, const char* terrain_names,
+                              const double* terrain_xy, const double* robot_grids, const int* robot_wh, const double* robot_conn,
+                              const int* robot_k, const char* robot_name, double rx, double ry);
+
 /* Packs all environments into HBM (struct-of-arrays blobs) and uploads.  Called implicitly by the
  * first step.  May be called again after adding environments/objects; state is preserved. */
 int mevo_batch_finalize(mevo_batch* b);

@@ -27,6 +27,7 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_destroy": (None, [_vp]),
     "mevo_batch_begin_env": (_i, [_vp, _i, _i]),
     "mevo_batch_add_object": (_i, [_vp, _i, _dp, _i, _i, _dp, _i, _cp, _d, _d, _i]),
+    "mevo_batch_add_robot_envs": (_i, [_vp, _i, _i, _i, _i, _dp, _ip, _dp, _ip, _cp, _dp, _dp, _ip, _dp, _ip, _cp, _d, _d]),
     "mevo_batch_finalize": (_i, [_vp]),
     "mevo_batch_finalize_epoch": (_i, [_vp]),
     "mevo_batch_num_envs": (_i, [_vp]),
@@ -273,6 +274,26 @@ class Batch:
             if not self.add_object(env, o.grid, o.connections, o.name, o.x, o.y, o.is_robot):
                 raise ValueError(f"object {o.name} refused")
         return env
+
+    def add_robot_worlds(self, terrain, bodies, connections, robot_name: str, rx: int, ry: int) -> int:
+        """One call for ``[add_world(terrain + robot_i at (rx, ry)) for i ...]`` (``mevo_batch_add_robot_envs``): ``terrain`` is a
+        ``WorldSpec`` without robots, ``bodies`` / ``connections`` the robots' grids (row 0 = top) and (2, k) connection lists."""
+        objs = terrain.load_order()
+        if any(o.is_robot for o in objs):
+            raise ValueError("add_robot_worlds: the terrain must not contain robots")
+        f64 = lambda arrs: (np.concatenate([np.asarray(a, dtype=np.float64).ravel() for a in arrs]) if arrs else np.zeros(0))
+        i32 = lambda rows: np.ascontiguousarray(np.asarray(rows, dtype=np.int32).reshape(-1))
+        t_grids, t_conn = f64([o.grid for o in objs]), f64([np.asarray(o.connections).reshape(2, -1) for o in objs])
+        t_wh, t_k = i32([o.size for o in objs]), i32([np.asarray(o.connections).reshape(2, -1).shape[1] for o in objs])
+        t_xy = np.ascontiguousarray(np.asarray([(o.x, o.y) for o in objs], dtype=np.float64).reshape(-1))
+        bodies = [np.asarray(b) for b in bodies]
+        conns = [np.asarray(c).reshape(2, -1) for c in connections]
+        r_grids, r_conn = f64(bodies), f64(conns)
+        r_wh, r_k = i32([(b.shape[1], b.shape[0]) for b in bodies]), i32([c.shape[1] for c in conns])
+        names = "\n".join(o.name for o in objs).encode()
+        return _check(self.L.mevo_batch_add_robot_envs(self.h, len(bodies), int(terrain.width), int(terrain.height), len(objs), _dptr(t_grids),
+                                                       _iptr(t_wh), _dptr(t_conn), _iptr(t_k), names, _dptr(t_xy), _dptr(r_grids), _iptr(r_wh),
+                                                       _dptr(r_conn), _iptr(r_k), robot_name.encode(), float(rx), float(ry)))
 
     def finalize(self) -> None:
         _check(self.L.mevo_batch_finalize(self.h))

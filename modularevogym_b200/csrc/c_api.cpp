@@ -4,10 +4,14 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstring>
 #include <exception>
 #include <stdexcept>
+#include <mutex>
 #include <string>
+#include <thread>
+#include <vector>
 
 #include "engine.h"
 
@@ -131,6 +135,81 @@ int mevo_batch_add_object(mevo_batch* b, int env, const double* grid, int w, int
     return guard([&] {
         if (!grid || w <= 0 || h <= 0 || k < 0 || (k > 0 && !conn) || !name) throw std::invalid_argument("bad add_object arguments");
         return b->impl.add_object(env, grid, w, h, conn, k, name, x, y, is_robot != 0) ? 1 : 0;
+    });
+}
+
+int mevo_batch_add_robot_envs(mevo_batch* b, int n_envs, int world_w, int world_h, int n_terrain, const double* terrain_grids,
+                              const int* terrain_wh, const double* terrain_conn, const int* terrain_k, const char* terrain_names,
+                              const double* terrain_xy, const double* robot_grids, const int* robot_wh, const double* robot_conn,
+                              const int* robot_k, const char* robot_name, double rx, double ry) {
+    return guard([&] {
+        if (n_envs < 0 || n_terrain < 0 || !robot_grids || !robot_wh || !robot_k || !robot_name ||
+            (n_terrain > 0 && (!terrain_grids || !terrain_wh || !terrain_k || !terrain_names || !terrain_xy)))
+            throw std::invalid_argument("bad add_robot_envs arguments");
+        std::vector<std::string> names;
+        {
+            std::string all = n_terrain > 0 ? terrain_names : "";
+            size_t at = 0;
+            for (int t = 0; t < n_terrain; t++) {
+                const size_t nl = all.find('\n', at);
+                names.push_back(all.substr(at, nl == std::string::npos ? std::string::npos : nl - at));
+                if (names.back().empty()) throw std::invalid_argument("add_robot_envs: fewer terrain names than objects");
+                at = nl == std::string::npos ? all.size() : nl + 1;
+            }
+        }
+        // environments are independent host worlds: create them, then fill them on all host cores
+        std::vector<size_t> g_off(n_envs + 1, 0), c_off(n_envs + 1, 0);
+        for (int i = 0; i < n_envs; i++) {
+            const int w = robot_wh[2 * i], h = robot_wh[2 * i + 1], k = robot_k[i];
+            if (w <= 0 || h <= 0 || k < 0 || (k > 0 && !robot_conn)) throw std::invalid_argument("bad robot in add_robot_envs");
+            g_off[i + 1] = g_off[i] + (size_t)w * h;
+            c_off[i + 1] = c_off[i] + 2 * (size_t)k;
+        }
+        int first = -1;
+        for (int i = 0; i < n_envs; i++) {
+            const int env = b->impl.begin_env(std::max(world_w, (int)rx + robot_wh[2 * i]), std::max(world_h, (int)ry + robot_wh[2 * i + 1]));
+            if (first < 0) first = env;
+        }
+        std::mutex err_mu;
+        std::string err;
+        auto fill = [&](int lo, int hi) {
+            for (int i = lo; i < hi; i++) {
+                std::string why;
+                try {
+                    const int env = first + i;
+                    if (!b->impl.add_object(env, robot_grids + g_off[i], robot_wh[2 * i], robot_wh[2 * i + 1], robot_conn + c_off[i], robot_k[i],
+                                            robot_name, rx, ry, true))
+                        why = "add_robot_envs: the robot of environment " + std::to_string(i) + " was refused";
+                    const double* tg = terrain_grids;
+                    const double* tc = terrain_conn;
+                    for (int t = 0; t < n_terrain && why.empty(); t++) {
+                        const int tw = terrain_wh[2 * t], th = terrain_wh[2 * t + 1], tk = terrain_k[t];
+                        if (!b->impl.add_object(env, tg, tw, th, tc, tk, names[t], terrain_xy[2 * t], terrain_xy[2 * t + 1], false))
+                            why = "add_robot_envs: object " + names[t] + " of environment " + std::to_string(i) + " was refused";
+                        tg += (size_t)tw * th;
+                        tc += 2 * (size_t)tk;
+                    }
+                } catch (const std::exception& e) {
+                    why = e.what();
+                }
+                if (!why.empty()) {
+                    std::lock_guard<std::mutex> lock(err_mu);
+                    if (err.empty()) err = why;
+                    return;
+                }
+            }
+        };
+        const int n_thr = std::max(1, std::min({(int)std::thread::hardware_concurrency(), 16, n_envs / 64}));
+        if (n_thr <= 1) {
+            fill(0, n_envs);
+        } else {
+            std::vector<std::thread> pool;
+            for (int t = 0; t < n_thr; t++)
+                pool.emplace_back(fill, (int)((long long)n_envs * t / n_thr), (int)((long long)n_envs * (t + 1) / n_thr));
+            for (auto& th : pool) th.join();
+        }
+        if (!err.empty()) throw std::runtime_error(err);
+        return first < 0 ? b->impl.num_envs() : first;
     });
 }
 

@@ -416,7 +416,7 @@ bool Batch::add_object(int env, const double* grid, int w, int h, const double* 
     e.goal.insert(e.goal.end(), W.el0.begin() + E_before, W.el0.end());
     e.obj_force_dynamic.push_back(0);
     e.host_fresh = true;
-    finalized_ = false;
+    if (finalized_) finalized_ = false;       // (read-only when already false: mevo_batch_add_robot_envs fills environments from several threads)
     return true;
 }
 

@@ -8,6 +8,10 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <unordered_map>
 
 namespace mevo {
 
@@ -49,6 +53,35 @@ const int kSideMissingNeighbour[4] = {TOP, RIGHT, BOT, LEFT};
 const int kNdx[8] = {0, 0, -1, 1, -1, 1, -1, 1};
 const int kNdy[8] = {-1, 1, 0, 0, -1, -1, 1, 1};
 
+// ---- built-object cache.  Design loops and batched front ends add the same terrain object to thousands of worlds, each time after
+// a different robot: everything about the object except its global point / edge offsets is the same.  A successful build of an
+// object of >= kCacheMinCells cells that is not the first of its world (with offset 0 the "id 0 reads as unset" rule changes what
+// is shared, see the header comment) is kept, keyed by its complete input, and instantiated by shifting ids.
+constexpr int kCacheMinCells = 32;
+constexpr size_t kCacheMaxEntries = 128;
+
+struct ObjectTemplate {
+    int P0 = 0, E0 = 0;
+    std::vector<double> pos, el0, ek;
+    std::vector<uint8_t> fixed, on_surface;
+    std::vector<int> ea, eb;
+    VoxelObject obj;
+};
+
+std::mutex g_cache_mu;
+std::unordered_map<std::string, std::shared_ptr<const ObjectTemplate>> g_cache;
+
+std::string cache_key(const double* grid, int w, int h, const double* conn, int k, double x, double y, bool is_robot) {
+    std::string key;
+    key.reserve(64 + (size_t)w * h + 8 * (size_t)k);
+    auto put = [&](const void* p, size_t n) { key.append(static_cast<const char*>(p), n); };
+    const int hdr[4] = {w, h, k, is_robot ? 1 : 0};
+    put(hdr, sizeof(hdr)); put(&x, sizeof(x)); put(&y, sizeof(y));
+    for (int i = 0; i < w * h; i++) { const signed char c = (signed char)grid[i]; key.push_back((char)c); if ((double)c != grid[i]) return std::string(); }
+    for (int i = 0; i < 2 * k; i++) { const int v = (int)conn[i]; put(&v, sizeof(v)); if ((double)v != conn[i]) return std::string(); }
+    return key;
+}
+
 }  // namespace
 
 void World::init(int w, int h) {
@@ -84,6 +117,50 @@ bool World::add_object(const double* grid, int w, int h, const double* conn, int
                 return false;
             }
         }
+
+    auto mark_world_grid = [&]() {
+        for (int cy = 0; cy < h; cy++)
+            for (int cx = 0; cx < w; cx++)
+                if (grid[cell(cx, cy)] != 0)
+                    world_grid[(size_t)((int)(world_h - h + cy - y)) * world_w + (int)(cx + x)] = (int)grid[cell(cx, cy)];
+    };
+    const bool cacheable = n_cells >= kCacheMinCells && P0 > 0 && E0 > 0;
+    std::string key;
+    if (cacheable) {
+        key = cache_key(grid, w, h, conn, k, x, y, is_robot);
+        std::shared_ptr<const ObjectTemplate> t;
+        if (!key.empty()) {
+            std::lock_guard<std::mutex> lock(g_cache_mu);
+            auto it = g_cache.find(key);
+            if (it != g_cache.end()) t = it->second;
+        }
+        if (t) {
+            // a known-good build: what can still refuse it is the name (same message and order as below)
+            if (name_to_index.count(name)) {
+                std::printf("Error Could not read in %s %s - duplicate name.\n", is_robot ? "robot" : "object", name.c_str());
+                return false;
+            }
+            const int dp = P0 - t->P0, de = E0 - t->E0;
+            name_to_index[name] = (int)objects.size();
+            pos.insert(pos.end(), t->pos.begin(), t->pos.end());
+            mass.insert(mass.end(), t->fixed.size(), kMass);
+            fixed.insert(fixed.end(), t->fixed.begin(), t->fixed.end());
+            const size_t ne = t->ea.size();
+            ea.reserve(ea.size() + ne); eb.reserve(eb.size() + ne);
+            for (size_t i = 0; i < ne; i++) { ea.push_back(t->ea[i] + dp); eb.push_back(t->eb[i] + dp); }
+            el0.insert(el0.end(), t->el0.begin(), t->el0.end());
+            ek.insert(ek.end(), t->ek.begin(), t->ek.end());
+            on_surface.insert(on_surface.end(), t->on_surface.begin(), t->on_surface.end());
+            VoxelObject obj = t->obj;
+            obj.name = name;
+            obj.min_point += dp; obj.max_point += dp; obj.min_edge += de; obj.max_edge += de;
+            for (Boxel& b : obj.boxels)
+                for (int q = 0; q < 4; q++) { b.pt[q] += dp; b.ed[q] += de; }
+            mark_world_grid();
+            objects.push_back(std::move(obj));
+            return true;
+        }
+    }
 
     std::vector<Boxel> cells(n_cells);
     for (int i = 0; i < n_cells; i++) {
@@ -224,10 +301,7 @@ bool World::add_object(const double* grid, int w, int h, const double* conn, int
     obj.max_point = num_points() - 1;
     obj.max_edge = num_edges() - 1;
 
-    for (int cy = 0; cy < h; cy++)
-        for (int cx = 0; cx < w; cx++)
-            if (grid[cell(cx, cy)] != 0)
-                world_grid[(size_t)((int)(world_h - h + cy - y)) * world_w + (int)(cx + x)] = (int)grid[cell(cx, cy)];
+    mark_world_grid();
 
     obj.all_fixed = true;
     for (const Boxel& c : cells) {
@@ -254,6 +328,19 @@ bool World::add_object(const double* grid, int w, int h, const double* conn, int
             obj.actuator_grid_to_boxel[b.grid_index] = (int)j;
             obj.actuator_grid_index.push_back(b.grid_index);
         }
+    }
+    if (cacheable && !key.empty()) {
+        auto t = std::make_shared<ObjectTemplate>();
+        t->P0 = P0; t->E0 = E0;
+        t->pos.assign(pos.begin() + 2 * (size_t)P0, pos.end());
+        t->fixed.assign(fixed.begin() + P0, fixed.end());
+        t->ea.assign(ea.begin() + E0, ea.end()); t->eb.assign(eb.begin() + E0, eb.end());
+        t->el0.assign(el0.begin() + E0, el0.end()); t->ek.assign(ek.begin() + E0, ek.end());
+        t->on_surface.assign(on_surface.begin() + E0, on_surface.end());
+        t->obj = obj;
+        std::lock_guard<std::mutex> lock(g_cache_mu);
+        if (g_cache.size() >= kCacheMaxEntries) g_cache.clear();
+        g_cache.emplace(std::move(key), std::move(t));
     }
     objects.push_back(std::move(obj));
     return true;

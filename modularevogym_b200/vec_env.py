@@ -20,7 +20,7 @@ import numpy as np
 from . import capi
 from .world import (WorldSpec, bridge_walker_world, cave_crawler_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
                     jumper_world, obstacle_traverser_v0_world,
-                    obstacle_traverser_world, pusher_world, thrower_world, up_stepper_world, walker_world)
+                    obstacle_traverser_world, pusher_world, terrain_for, thrower_world, up_stepper_world, walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
 # (evogym/envs/__init__.py:16-20,125-129,149-153))
@@ -70,12 +70,22 @@ class BatchedEvoGymEnv:
         self.device = torch.device("cuda", device)
         self.dtype = {"float32": torch.float32, "float64": torch.float64}[out_dtype]
         self.B = capi.Batch(device)
-        for i, body in enumerate(self.bodies):
-            if worlds is not None:
+        if worlds is not None:
+            for i in range(self.num_envs):
                 self.B.add_world(worlds[i])
-            else:
-                cn = connections[i] if connections is not None and connections[i] is not None else full_connectivity(body)
-                self.B.add_world(builder(body, cn))
+        else:
+            conns = [connections[i] if connections is not None and connections[i] is not None else full_connectivity(b)
+                     for i, b in enumerate(self.bodies)]
+            # environments that share their terrain go in through one call (design loops rebuild the batch every episode); the
+            # terrain of Climber-v0 depends on the robot's width, so its environments are grouped by terrain
+            i = 0
+            while i < self.num_envs:
+                terrain, rx, ry = terrain_for(env_id, self.bodies[i])
+                j = i + 1
+                while j < self.num_envs and terrain_for(env_id, self.bodies[j])[0] is terrain:
+                    j += 1
+                self.B.add_robot_worlds(terrain, self.bodies[i:j], conns[i:j], "robot", rx, ry)
+                i = j
         self.B.finalize()
         self.B.set_auto_reset(False)            # the task kernel resets (it needs the flag and the pre-step centres of mass)
         self.B.task_configure(task, "robot", package, limit if max_episode_steps is None else max_episode_steps)
@@ -89,10 +99,10 @@ class BatchedEvoGymEnv:
         self._done = torch.zeros((n,), device=dev, dtype=torch.uint8)
         am = np.ones((n, d["max_voxels"]), dtype=np.int64)
         om = np.ones((n, d["max_voxels"]), dtype=np.int64)
-        for i in range(n):
-            t = self.B.task_env_tables(i)
-            nv = self.bodies[i].size
-            am[i, :nv], om[i, :nv] = t["act_mask"][:nv], t["obs_mask"][:nv]
+        for i, body in enumerate(self.bodies):          # get_act_mask / get_obs_mask (evogym/envs/base.py:530-560), as task_env_tables reports them
+            flat = body.ravel()
+            am[i, :flat.size] = ~((flat == 3) | (flat == 4))
+            om[i, :int(np.count_nonzero(flat))] = 0
         self.act_mask = torch.from_numpy(am).to(dev)
         self.obs_mask = torch.from_numpy(om).to(dev)
         self._stage = torch.ones((n, 1), device=dev, dtype=dt)

@@ -16,6 +16,7 @@ machine without the reference checkout; duck-typed ``evogym.EvoWorld`` instances
 """
 from __future__ import annotations
 
+import functools
 import json
 import random as _random
 from dataclasses import dataclass, field
@@ -34,18 +35,18 @@ def full_connectivity(structure: np.ndarray) -> np.ndarray:
     voxels visited in row-major order)."""
     s = np.asarray(structure)
     h, w = s.shape
-    out: List[Tuple[int, int]] = []
-    for r in range(h):
-        for c in range(w):
-            if s[r, c] == 0:
-                continue
-            if c + 1 < w and s[r, c + 1] != 0:
-                out.append((r * w + c, r * w + c + 1))
-            if r + 1 < h and s[r + 1, c] != 0:
-                out.append((r * w + c, (r + 1) * w + c))
-    if not out:
+    full = s != 0
+    idx = np.arange(h * w, dtype=np.int64).reshape(h, w)
+    right = np.zeros((h, w), dtype=bool)
+    down = np.zeros((h, w), dtype=bool)
+    right[:, :-1] = full[:, :-1] & full[:, 1:]
+    down[:-1, :] = full[:-1, :] & full[1:, :]
+    a = np.concatenate((idx[right], idx[down]))
+    if a.size == 0:
         return np.zeros((2, 0), dtype=np.int64)
-    return np.asarray(out, dtype=np.int64).T
+    b = np.concatenate((idx[right] + 1, idx[down] + w))
+    order = np.argsort(np.concatenate((2 * idx[right], 2 * idx[down] + 1)), kind="stable")       # per voxel: right, then lower
+    return np.stack((a[order], b[order]))
 
 
 def is_connected(structure: np.ndarray) -> bool:
@@ -235,13 +236,18 @@ class WorldSpec:
         if obj.x < 0 or obj.y < 0:
             raise ValueError(f"object {obj.name} position must be non-negative")
         w, h = obj.size
-        occ = self.occupancy()
+        for o in self.objects.values():                 # overlap with an existing object: compare the grids where the boxes meet
+            ow, oh = o.size
+            x0, x1 = max(obj.x, o.x), min(obj.x + w, o.x + ow)
+            y0, y1 = max(obj.y, o.y), min(obj.y + h, o.y + oh)
+            if x0 >= x1 or y0 >= y1:
+                continue
+            mine = obj.grid[h - (y1 - obj.y):h - (y0 - obj.y), x0 - obj.x:x1 - obj.x]          # row 0 = top
+            theirs = o.grid[oh - (y1 - o.y):oh - (y0 - o.y), x0 - o.x:x1 - o.x]
+            if ((mine != 0) & (theirs != 0)).any():
+                raise ValueError(f"cannot add object {obj.name}: overlaps an existing object")
         self.width = max(self.width, obj.x + w)
         self.height = max(self.height, obj.y + h)
-        for r in range(h):
-            for c in range(w):
-                if obj.grid[r, c] != 0 and (obj.x + c, obj.y + (h - 1 - r)) in occ:
-                    raise ValueError(f"cannot add object {obj.name}: overlaps an existing object")
         self.objects[obj.name] = obj
 
     def add_from_array(self, name: str, structure: np.ndarray, x: int, y: int,
@@ -253,9 +259,8 @@ class WorldSpec:
         if cn.size == 0:
             cn = np.zeros((2, 0), dtype=np.int64)
         flat = grid.ravel()
-        for v in cn.ravel():
-            if v < 0 or v >= flat.size or flat[v] == 0:
-                raise ValueError(f"could not load object {name}: connections contain invalid elements")
+        if cn.size and ((cn < 0).any() or (cn >= flat.size).any() or (flat[np.clip(cn, 0, flat.size - 1)] == 0).any()):
+            raise ValueError(f"could not load object {name}: connections contain invalid elements")
         self.add_object(ObjectSpec(name, grid, cn, int(x), int(y)))
 
     # ---- queries ------------------------------------------------------------------------
@@ -297,6 +302,20 @@ class WorldSpec:
         return w
 
 
+def _frozen(w: "WorldSpec") -> "WorldSpec":
+    """terrain built once per process and shared by every world a builder hands out: its arrays become read-only"""
+    for o in w.objects.values():
+        o.grid.setflags(write=False)
+        o.connections.setflags(write=False)
+    return w
+
+
+def _shared(terrain: "WorldSpec") -> "WorldSpec":
+    w = WorldSpec(width=terrain.width, height=terrain.height)
+    w.objects.update(terrain.objects)
+    return w
+
+
 def flat_ground_world(width: int = 100, name: str = "ground") -> WorldSpec:
     """``width`` x 1 strip of FIXED voxels at the bottom of the world: the terrain of Walker-v0
     (reference ``evogym/envs/sim_files/Walker-v0.json``: grid 100 x 1, one object ``ground``)."""
@@ -306,9 +325,15 @@ def flat_ground_world(width: int = 100, name: str = "ground") -> WorldSpec:
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _walker_terrain(width: int = 100) -> WorldSpec:
+    w = flat_ground_world(width)
+    return _frozen(w)
+
+
 def walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None, width: int = 100) -> WorldSpec:
     """Walker-v0: flat fixed ground + ``robot`` placed at voxel (1, 1) (``evogym/envs/walk.py:19-20``)."""
-    w = flat_ground_world(width)
+    w = _shared(_walker_terrain(width))
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
 
@@ -318,11 +343,17 @@ def _package() -> np.ndarray:
     return np.full((2, 3), VOXEL_TYPES["SOFT"], dtype=np.int64)
 
 
+@functools.lru_cache(maxsize=None)
+def _pusher_terrain() -> WorldSpec:
+    w = flat_ground_world(100)
+    w.add_from_array("package", _package(), 8, 1)
+    return _frozen(w)
+
+
 def pusher_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
     """Pusher-v0 (``evogym/envs/sim_files/Pusher-v0.json`` + ``evogym/envs/manipulate.py:323-324``): 100 x 1 fixed
     ground, the package at voxel (8, 1), the robot at (1, 1)."""
-    w = flat_ground_world(100)
-    w.add_from_array("package", _package(), 8, 1)
+    w = _shared(_pusher_terrain())
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
 
@@ -330,9 +361,8 @@ def pusher_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) ->
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
-def thrower_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """Thrower-v0 (``evogym/envs/sim_files/Thrower-v0.json`` + ``evogym/envs/manipulate.py:524-525``): 70 x 10 fixed
-    terrain (ground row + posts of rising height), the package at voxel (3, 7), the robot at (1, 1)."""
+@functools.lru_cache(maxsize=None)
+def _thrower_terrain() -> WorldSpec:
     w = WorldSpec(width=70, height=10)
     grid = np.zeros((10, 70), dtype=np.int64)
     grid[9, :] = VOXEL_TYPES["FIXED"]
@@ -340,8 +370,25 @@ def thrower_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -
         grid[9 - hgt:9, col] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
     w.add_from_array("package", _package(), 3, 7)
+    return _frozen(w)
+
+
+def thrower_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Thrower-v0 (``evogym/envs/sim_files/Thrower-v0.json`` + ``evogym/envs/manipulate.py:524-525``): 70 x 10 fixed
+    terrain (ground row + posts of rising height), the package at voxel (3, 7), the robot at (1, 1)."""
+    w = _shared(_thrower_terrain())
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
+
+
+@functools.lru_cache(maxsize=None)
+def _climber_terrain(width: int) -> WorldSpec:
+    w = WorldSpec(width=width, height=90)
+    grid = np.zeros((90, width), dtype=np.int64)
+    grid[:, 0] = grid[:, width - 1] = VOXEL_TYPES["FIXED"]
+    grid[0, :] = grid[89, :] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("pipe", grid, 0, 0)
+    return _frozen(w)
 
 
 def climber_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
@@ -350,11 +397,7 @@ def climber_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -
     robot (BASELINE configs[3] names Climber with 10x10 / 20x20 morphologies, which cannot exist in that pipe) the pipe is
     widened to the robot's width + 2 -- a synthetic Climber-style world, same wall contact on both sides."""
     width = max(7, int(np.asarray(robot).shape[1]) + 2)
-    w = WorldSpec(width=width, height=90)
-    grid = np.zeros((90, width), dtype=np.int64)
-    grid[:, 0] = grid[:, width - 1] = VOXEL_TYPES["FIXED"]
-    grid[0, :] = grid[89, :] = VOXEL_TYPES["FIXED"]
-    w.add_from_array("pipe", grid, 0, 0)
+    w = _shared(_climber_terrain(width))
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
 
@@ -364,14 +407,20 @@ OBSTACLE_TRAVERSER_V1_HEIGHTS = (3, 3, 4, 3, 4, 3, 3, 3, 2, 3, 2, 2, 3, 3, 2, 2,
                                  3, 4, 4, 4, 2, 3, 4, 5, 4, 3, 4, 3, 4, 3, 2, 2, 3, 4, 3, 2, 3, 10, 10)
 
 
-def obstacle_traverser_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """ObstacleTraverser-v1 (``evogym/envs/sim_files/ObstacleTraverser-v1.json`` + ``evogym/envs/traverse.py:355-356``): 60 x 10
-    bumpy fixed ``ground``, the robot at voxel (2, 4)."""
+@functools.lru_cache(maxsize=None)
+def _obstacle_traverser_terrain() -> WorldSpec:
     w = WorldSpec(width=60, height=10)
     grid = np.zeros((10, 60), dtype=np.int64)
     for c, hgt in enumerate(OBSTACLE_TRAVERSER_V1_HEIGHTS):
         grid[10 - hgt:, c] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def obstacle_traverser_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """ObstacleTraverser-v1 (``evogym/envs/sim_files/ObstacleTraverser-v1.json`` + ``evogym/envs/traverse.py:355-356``): 60 x 10
+    bumpy fixed ``ground``, the robot at voxel (2, 4)."""
+    w = _shared(_obstacle_traverser_terrain())
     w.add_from_array("robot", robot, 2, 4, connections)
     return w
 
@@ -386,38 +435,56 @@ UP_STEPPER_BREAKS = (0, 20, 29, 36, 42, 47, 51, 55, 61, 69)
 DOWN_STEPPER_BREAKS = (0, 20, 28, 35, 41, 47, 52, 57, 61, 65, 74)
 
 
-def obstacle_traverser_v0_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """ObstacleTraverser-v0 (``sim_files/ObstacleTraverser-v0.json`` + ``evogym/envs/traverse.py:256-257``): 80 x 3 bumpy fixed
-    ``ground``, the robot at voxel (2, 1)."""
+@functools.lru_cache(maxsize=None)
+def _obstacle_traverser_v0_terrain() -> WorldSpec:
     w = WorldSpec(width=80, height=3)
     grid = np.zeros((3, 80), dtype=np.int64)
     for c, hgt in enumerate(OBSTACLE_TRAVERSER_V0_HEIGHTS):
         grid[3 - hgt:, c] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def obstacle_traverser_v0_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """ObstacleTraverser-v0 (``sim_files/ObstacleTraverser-v0.json`` + ``evogym/envs/traverse.py:256-257``): 80 x 3 bumpy fixed
+    ``ground``, the robot at voxel (2, 1)."""
+    w = _shared(_obstacle_traverser_v0_terrain())
     w.add_from_array("robot", robot, 2, 1, connections)
     return w
 
 
-def up_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """UpStepper-v0 (``sim_files/UpStepper-v0.json`` + ``traverse.py:56-57``): nine ascending treads, the robot at voxel (1, 1)."""
+@functools.lru_cache(maxsize=None)
+def _up_stepper_terrain() -> WorldSpec:
     b = UP_STEPPER_BREAKS
     w = WorldSpec(width=70, height=9)
     grid = np.zeros((9, 70), dtype=np.int64)
     for y in range(9):
         grid[8 - y, b[y]:b[y + 1] + 1] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def up_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """UpStepper-v0 (``sim_files/UpStepper-v0.json`` + ``traverse.py:56-57``): nine ascending treads, the robot at voxel (1, 1)."""
+    w = _shared(_up_stepper_terrain())
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
 
 
-def down_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """DownStepper-v0 (``sim_files/DownStepper-v0.json`` + ``traverse.py:157-158``): ten descending treads, the robot at voxel (1, 11)."""
+@functools.lru_cache(maxsize=None)
+def _down_stepper_terrain() -> WorldSpec:
     b = DOWN_STEPPER_BREAKS
     w = WorldSpec(width=75, height=10)
     grid = np.zeros((10, 75), dtype=np.int64)
     for k in range(10):                               # tread k from the left sits at height 9 - k
         grid[k, b[k]:b[k + 1] + 1] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def down_stepper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """DownStepper-v0 (``sim_files/DownStepper-v0.json`` + ``traverse.py:157-158``): ten descending treads, the robot at voxel (1, 11)."""
+    w = _shared(_down_stepper_terrain())
     w.add_from_array("robot", robot, 1, 11, connections)
     return w
 
@@ -432,21 +499,26 @@ CLIMBER_V1_WALLS = (("==", 1), ("FF", 4), ("SF", 5), ("FS", 4), ("FF", 2), ("SS"
                     ("FF", 3), ("FS", 3), ("FF", 2), ("SF", 2), ("FF", 2), ("FS", 1), ("FF", 7), ("==", 1))
 
 
-def hurdler_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """Hurdler-v0 (``sim_files/Hurdler-v0.json`` + ``evogym/envs/traverse.py:451-452``): fixed ``ground`` with barriers of 2 - 3 voxels
-    and a 6-voxel end wall, the robot at voxel (2, 4)."""
+@functools.lru_cache(maxsize=None)
+def _hurdler_terrain() -> WorldSpec:
     w = WorldSpec(width=70, height=6)
     grid = np.zeros((6, 70), dtype=np.int64)
     for c, hgt in enumerate(HURDLER_HEIGHTS):
         grid[6 - hgt:, c] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def hurdler_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Hurdler-v0 (``sim_files/Hurdler-v0.json`` + ``evogym/envs/traverse.py:451-452``): fixed ``ground`` with barriers of 2 - 3 voxels
+    and a 6-voxel end wall, the robot at voxel (2, 4)."""
+    w = _shared(_hurdler_terrain())
     w.add_from_array("robot", robot, 2, 4, connections)
     return w
 
 
-def climber_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """Climber-v1 (``sim_files/Climber-v1.json`` + ``evogym/envs/climb.py:139-140``): a 5-wide pipe whose walls alternate FIXED and
-    SOFT stretches -- one object, so the whole pipe is simulated --, the robot at voxel (1, 1)."""
+@functools.lru_cache(maxsize=None)
+def _climber_v1_terrain() -> WorldSpec:
     w = WorldSpec(width=7, height=70)
     grid = np.zeros((70, 7), dtype=np.int64)
     t = {"F": VOXEL_TYPES["FIXED"], "S": VOXEL_TYPES["SOFT"]}
@@ -458,6 +530,13 @@ def climber_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None
             grid[r:r + n, 0], grid[r:r + n, 6] = t[walls[0]], t[walls[1]]
         r += n
     w.add_from_array("pipe", grid, 0, 0)
+    return _frozen(w)
+
+
+def climber_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Climber-v1 (``sim_files/Climber-v1.json`` + ``evogym/envs/climb.py:139-140``): a 5-wide pipe whose walls alternate FIXED and
+    SOFT stretches -- one object, so the whole pipe is simulated --, the robot at voxel (1, 1)."""
+    w = _shared(_climber_v1_terrain())
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
 
@@ -531,33 +610,51 @@ def grid_from_rows(rows: Sequence[str]) -> np.ndarray:
     return np.array([[code[ch] for ch in row] for row in rows], dtype=np.int64)
 
 
+@functools.lru_cache(maxsize=None)
+def _cave_crawler_terrain() -> WorldSpec:
+    w = WorldSpec(width=70, height=14)
+    w.add_from_array("terrain", grid_from_rows(CAVE_CRAWLER_ROWS), 0, 0)
+    return _frozen(w)
+
+
 def cave_crawler_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
     """CaveCrawler-v0 (``sim_files/CaveCrawler-v0.json`` + ``evogym/envs/walk.py:240-241``): a floor, a fixed ceiling with SOFT
     stalactites, one object ``terrain`` (simulated: it has SOFT voxels); the robot at voxel (1, 2)."""
-    w = WorldSpec(width=70, height=14)
-    w.add_from_array("terrain", grid_from_rows(CAVE_CRAWLER_ROWS), 0, 0)
+    w = _shared(_cave_crawler_terrain())
     w.add_from_array("robot", robot, 1, 2, connections)
     return w
+
+
+@functools.lru_cache(maxsize=None)
+def _climber_v2_terrain() -> WorldSpec:
+    w = WorldSpec(width=27, height=42)
+    w.add_from_array("pipe", grid_from_rows(CLIMBER_V2_ROWS), 0, 0)
+    return _frozen(w)
 
 
 def climber_v2_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
     """Climber-v2 (``sim_files/Climber-v2.json`` + ``evogym/envs/climb.py:233-234``): a fixed ``pipe`` that bends to the right at the
     top; the robot at voxel (1, 1)."""
-    w = WorldSpec(width=27, height=42)
-    w.add_from_array("pipe", grid_from_rows(CLIMBER_V2_ROWS), 0, 0)
+    w = _shared(_climber_v2_terrain())
     w.add_from_array("robot", robot, 1, 1, connections)
     return w
 
 
-def jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """Jumper-v0 (``sim_files/Jumper-v0.json`` + ``evogym/envs/jump.py:19-20``): a 60-wide fixed floor between two 8-voxel walls,
-    the robot at voxel (32, 1)."""
+@functools.lru_cache(maxsize=None)
+def _jumper_terrain() -> WorldSpec:
     w = WorldSpec(width=60, height=8)
     grid = np.zeros((8, 60), dtype=np.int64)
     grid[7, :] = VOXEL_TYPES["FIXED"]
     grid[:, 0] = VOXEL_TYPES["FIXED"]
     grid[:, 59] = VOXEL_TYPES["FIXED"]
     w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Jumper-v0 (``sim_files/Jumper-v0.json`` + ``evogym/envs/jump.py:19-20``): a 60-wide fixed floor between two 8-voxel walls,
+    the robot at voxel (32, 1)."""
+    w = _shared(_jumper_terrain())
     w.add_from_array("robot", robot, 32, 1, connections)
     return w
 
@@ -565,10 +662,8 @@ def jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) ->
 BRIDGE_WALKER_PILLARS = (0, 5, 10, 18, 29, 46, 58, 59)     # columns of FIXED voxels from the floor row up to the deck
 
 
-def bridge_walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
-    """BridgeWalker-v0 (``evogym/envs/sim_files/BridgeWalker-v0.json`` + ``evogym/envs/walk.py:152-153``): one 60 x 5 object
-    ``new_object_2`` -- a FIXED floor row, FIXED pillars, and a two-voxel-thick SOFT deck hung between the pillars -- with the
-    robot at voxel (2, 5).  FIXED and SOFT voxels share one object, so the whole terrain is simulated (SURVEY 7 "dead work")."""
+@functools.lru_cache(maxsize=None)
+def _bridge_walker_terrain() -> WorldSpec:
     w = WorldSpec(width=60, height=5)
     grid = np.zeros((5, 60), dtype=np.int64)          # row 0 = top
     grid[4, :] = VOXEL_TYPES["FIXED"]
@@ -576,6 +671,39 @@ def bridge_walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = N
     for c in BRIDGE_WALKER_PILLARS:
         grid[:, c] = VOXEL_TYPES["FIXED"]
     w.add_from_array("new_object_2", grid, 0, 0)
+    return _frozen(w)
+
+
+def bridge_walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """BridgeWalker-v0 (``evogym/envs/sim_files/BridgeWalker-v0.json`` + ``evogym/envs/walk.py:152-153``): one 60 x 5 object
+    ``new_object_2`` -- a FIXED floor row, FIXED pillars, and a two-voxel-thick SOFT deck hung between the pillars -- with the
+    robot at voxel (2, 5).  FIXED and SOFT voxels share one object, so the whole terrain is simulated (SURVEY 7 "dead work")."""
+    w = _shared(_bridge_walker_terrain())
     w.add_from_array("robot", robot, 2, 5, connections)
     return w
 
+
+
+# env id -> (terrain without the robot, built once per process; robot position).  Climber-v0's pipe depends on the robot's width.
+_TERRAINS = {
+    "Walker-v0": (lambda robot: _walker_terrain(100), (1, 1)),
+    "Pusher-v0": (lambda robot: _pusher_terrain(), (1, 1)),
+    "Thrower-v0": (lambda robot: _thrower_terrain(), (1, 1)),
+    "Climber-v0": (lambda robot: _climber_terrain(max(7, int(np.asarray(robot).shape[1]) + 2)), (1, 1)),
+    "Climber-v1": (lambda robot: _climber_v1_terrain(), (1, 1)),
+    "Climber-v2": (lambda robot: _climber_v2_terrain(), (1, 1)),
+    "ObstacleTraverser-v0": (lambda robot: _obstacle_traverser_v0_terrain(), (2, 1)),
+    "ObstacleTraverser-v1": (lambda robot: _obstacle_traverser_terrain(), (2, 4)),
+    "UpStepper-v0": (lambda robot: _up_stepper_terrain(), (1, 1)),
+    "DownStepper-v0": (lambda robot: _down_stepper_terrain(), (1, 11)),
+    "Hurdler-v0": (lambda robot: _hurdler_terrain(), (2, 4)),
+    "BridgeWalker-v0": (lambda robot: _bridge_walker_terrain(), (2, 5)),
+    "CaveCrawler-v0": (lambda robot: _cave_crawler_terrain(), (1, 2)),
+    "Jumper-v0": (lambda robot: _jumper_terrain(), (32, 1)),
+}
+
+
+def terrain_for(env_id: str, robot: np.ndarray) -> Tuple[WorldSpec, int, int]:
+    """(shared read-only terrain world, robot x, robot y) of a built-in environment: what its ``*_world`` builder puts around ``robot``"""
+    make, (rx, ry) = _TERRAINS[env_id]
+    return make(robot), rx, ry

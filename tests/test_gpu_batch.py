@@ -182,3 +182,46 @@ def test_fetch_step_results_equals_separate_reads():
     n_unstable = B.fetch_step_results_ptr(flags_b.ctypes.data, 0, com_b.ctypes.data)
     assert n_unstable == int(flags_a.sum()) and np.array_equal(flags_a, flags_b) and np.array_equal(com_a, com_b)
     A.close(); B.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("env_id", ["Walker-v0", "Pusher-v0", "Climber-v0", "ObstacleTraverser-v1", "BridgeWalker-v0", "CaveCrawler-v0"])
+def test_add_robot_envs_equals_add_world(env_id):
+    """mevo_batch_add_robot_envs (one call for a whole design-loop rebuild: shared terrain + one robot per environment) builds the
+    environments add_world builds from the per-environment WorldSpec: same topology arrays, same state after a step"""
+    import random
+    from modularevogym_b200 import capi
+    from modularevogym_b200.vec_env import TASKS
+    from modularevogym_b200.world import sample_large_robot, sample_robot, terrain_for
+    random.seed(31)
+    robots = [sample_robot((5, 5)) if k % 3 else sample_large_robot((4 + k % 4, 3 + k % 5)) for k in range(12)]
+    builder = TASKS[env_id][1]
+    A, B = capi.Batch(0), capi.Batch(0)
+    for body, conn in robots:
+        A.add_world(builder(body, conn))
+    i = 0
+    while i < len(robots):                               # grouped by terrain like the vec-env front (Climber-v0: pipe width)
+        terrain, rx, ry = terrain_for(env_id, robots[i][0])
+        j = i + 1
+        while j < len(robots) and terrain_for(env_id, robots[j][0])[0] is terrain:
+            j += 1
+        first = B.add_robot_worlds(terrain, [r for r, _ in robots[i:j]], [c for _, c in robots[i:j]], "robot", rx, ry)
+        assert first == i
+        i = j
+    A.finalize(); B.finalize()
+    assert A.num_envs == B.num_envs == len(robots)
+    acts = np.random.default_rng(3).uniform(0.6, 1.6, (len(robots), A.action_stride))
+    for X in (A, B):
+        X.set_actions(acts)
+        X.step(1, True)
+    for e in range(len(robots)):
+        ta, tb = A.topology(e), B.topology(e)
+        assert ta.keys() == tb.keys()
+        for k in ta:
+            assert np.array_equal(ta[k], tb[k]), (e, k)
+        assert A.num_objects(e) == B.num_objects(e)
+        for o in range(A.num_objects(e)):
+            assert A.object_info(e, o) == B.object_info(e, o)
+        for x, y in zip(A.get_state(e), B.get_state(e)):
+            assert np.array_equal(x, y), e
+    A.close(); B.close()

@@ -68,3 +68,41 @@ def test_random_world_matches_reference(seed, capfd):
         refused += not ok_ref
         same_world(hw, r, names)                # also after a refusal: the world must be untouched
     capfd.readouterr()                          # both print the reference's "Error: ..." lines on refusals
+
+
+def test_repeated_terrain_objects_match_reference(capfd):
+    """the builder keeps built objects of >= 32 cells that are not the first of their world and re-instantiates them with shifted
+    ids (csrc/topology.cpp, "built-object cache"): the same terrain and free objects after robots of different sizes -- different
+    point / edge offsets every time --, a duplicate name and an overlapping copy, all against the live reference"""
+    rng = np.random.default_rng(77)
+    W, H = 40, 16
+    ground = np.full((2, 40), 5.0)
+    ground[0, 5:9] = 0
+    ground_cn = []
+    for r_ in range(2):
+        for c in range(40):
+            if ground[r_, c] == 0:
+                continue
+            if c + 1 < 40 and ground[r_, c + 1]:
+                ground_cn.append((r_ * 40 + c, r_ * 40 + c + 1))
+            if r_ + 1 < 2 and ground[r_ + 1, c]:
+                ground_cn.append((r_ * 40 + c, (r_ + 1) * 40 + c))
+    ground_cn = np.asarray(ground_cn, dtype=np.float64).T
+    block, block_cn = random_object(np.random.default_rng(5), 6, 7, 0.1, 0.1)          # 42 cells, partial connectivity
+    for trial in range(8):
+        hw, r = capi.HostWorld(world_w=W, world_h=H), oref.RefSim(world_w=W, world_h=H)
+        names = []
+        h, w = int(rng.integers(2, 6)), int(rng.integers(2, 6))
+        robot, robot_cn = random_object(rng, h, w, 0.0, 0.0)
+        robot[0, 0] = 3.0
+        for grid, cn, name, x, y, is_robot in ((robot, robot_cn, "robot", 1, 2, True), (ground, ground_cn, "ground", 0, 0, False),
+                                               (block, block_cn, "block", 20, 3, False), (block, block_cn, "block", 30, 3, False),
+                                               (block, block_cn, "block2", 22, 4, False), (ground, ground_cn, "roof", 0, 12, False)):
+            n_before = r.num_objects
+            ok_ref = r.add_object(grid, cn, name, x, y, is_robot)
+            assert hw.add_object(grid, cn, name, x, y, is_robot) == ok_ref, (trial, name)
+            if r.num_objects > n_before:
+                names.append(name)
+            same_world(hw, r, names)
+        assert names == ["robot", "ground", "block", "roof"]
+    capfd.readouterr()
