@@ -305,7 +305,7 @@ struct Batch::Impl {
     int* d_com_ranges = nullptr;
     double* d_com_out = nullptr;
     int com_obj = -1;
-    std::vector<uint8_t> unstable_host;
+    uint8_t* unstable_host = nullptr;             // pinned staging buffer of the per-step flags (n bytes)
     std::vector<int> time_host;
     bool time_dirty = true;
 };
@@ -377,6 +377,7 @@ Batch::~Batch() {
     if (impl_) {
         cudaFree(impl_->d_com_ranges); cudaFree(impl_->d_com_out); cudaFree(impl_->d_ids);
         cudaFree(impl_->d_scratch); cudaFree(impl_->d_cf); cudaFree(impl_->d_work);
+        if (impl_->unstable_host) cudaFreeHost(impl_->unstable_host);
         for (int k = 0; k < Impl::kSlots; k++) { cudaFree(impl_->d_slot[k]); cudaFree(impl_->d_slot_time[k]); }
         for (int c = 0; c < kNumClasses; c++) {
             if (impl_->class_stream[c]) cudaStreamDestroy(impl_->class_stream[c]);
@@ -957,7 +958,10 @@ void Batch::finalize() {
         CUDA_CHECK(cudaMemset(d_unstable_, 0, n));
         CUDA_CHECK(cudaMemset(d_err_, 0, sizeof(int) * n));
     }
-    impl_->unstable_host.assign(n, 0);
+    if (impl_->unstable_host) cudaFreeHost(impl_->unstable_host);
+    impl_->unstable_host = nullptr;
+    CUDA_CHECK(cudaMallocHost(&impl_->unstable_host, (size_t)std::max(n, 1)));
+    std::memset(impl_->unstable_host, 0, (size_t)std::max(n, 1));
     impl_->time_host.assign(n, 0);
     impl_->com_obj = -1;
     if (cand_cap_ > 0) enable_candidate_dump(cand_cap_);
@@ -1436,11 +1440,11 @@ void Batch::step_static_scratch(int n_steps, const double* dev_actions, int stri
 int Batch::step(int n_steps, bool apply_actions, uint8_t* unstable_host, int n_substeps) {
     step_async(n_steps, apply_actions, n_substeps);
     const int n = num_envs();
-    CUDA_CHECK(cudaMemcpyAsync(impl_->unstable_host.data(), d_unstable_, n, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaMemcpyAsync(impl_->unstable_host, d_unstable_, n, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
     int count = 0;
     for (int i = 0; i < n; i++) count += impl_->unstable_host[i] ? 1 : 0;
-    if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host.data(), n);
+    if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host, n);
     return count;
 }
 
@@ -1622,11 +1626,11 @@ int Batch::fetch_step_results(uint8_t* unstable_host, int obj_index, double* com
         object_com_device(obj_index, nullptr);
         CUDA_CHECK(cudaMemcpyAsync(com_host_2n, impl_->d_com_out, sizeof(double) * 2 * n, cudaMemcpyDeviceToHost, st));
     }
-    CUDA_CHECK(cudaMemcpyAsync(impl_->unstable_host.data(), d_unstable_, n, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(impl_->unstable_host, d_unstable_, n, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     int count = 0;
     for (int i = 0; i < n; i++) count += impl_->unstable_host[i] ? 1 : 0;
-    if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host.data(), n);
+    if (unstable_host) std::memcpy(unstable_host, impl_->unstable_host, n);
     return count;
 }
 
