@@ -259,10 +259,13 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
                                                "other" = [vel com 2, floor sight 11, ceiling sight 11] over "terrain"; modular mode */
 #define MEVO_TASK_CLIMBER_V2 13             /* Climb2, evogym/envs/climb.py:226-320 (Climber-v2): reward = rise + 0.2 * advance, no goal;
                                                "other" = [vel com 2, orientation 1, ceiling sight 7 over "pipe"]; modular mode */
+#define MEVO_TASK_CARRIER 14                /* CarrySmallRect, manipulate.py:83-199 (Carrier-v0): reward = half the advance of package and robot,
+                                               10 x the package's fall below 3 voxels; goal at robot x > 99; observations as MEVO_TASK_PUSHER */
+#define MEVO_TASK_PUSHER_V1 15              /* PushSmallRectOnOppositeSide, manipulate.py:419-516 (Pusher-v1): MEVO_TASK_PUSHER with the goal at x > 69 */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */
-/* package: used by MEVO_TASK_PUSHER / MEVO_TASK_THROWER only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
+/* package: used by MEVO_TASK_PUSHER / _THROWER / _CARRIER / _PUSHER_V1 only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
 int mevo_batch_task_configure(mevo_batch* b, int task, const char* robot, const char* package, int max_episode_steps);
 /* dims[0..4] = flat observation width, modular observation width (9 x voxels), "other" observation width,
  * largest voxel count of a robot grid, action stride */

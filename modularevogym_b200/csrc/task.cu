@@ -133,7 +133,11 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         reward = (rf_y - ri_y) + (rf_x - ri_x) * 0.2;
     } else if (p.task == 9) {                            // jump.py:72-75
         reward = (rf_y - ri_y) * 10 - fabs(rf_x - ri_x) * 5;
-    } else if (p.task == 1) {                            // manipulate.py:38-58
+    } else if (p.task == 14) {                           // manipulate.py:111-127 (Carrier-v0, thresh_height 3 voxels)
+        reward = (pf_x - pi_x) * 0.5;
+        reward += (rf_x - ri_x) * 0.5;
+        if (pf_y < 3.0 * kVoxel) reward += 10 * (pf_y - pi_y);
+    } else if (p.task == 1 || p.task == 15) {            // manipulate.py:38-58 (Pusher-v0, Pusher-v1: thresh_height 0)
         reward = (pf_x - pi_x) * 0.75;
         reward += (rf_x - ri_x) * 0.5;
         reward += fabs(ri_x - pi_x) - fabs(rf_x - pf_x);
@@ -183,7 +187,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // ---- observations of the (possibly reset) state
     double oth[6];
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
-    if (p.task == 0 || p.task >= 3) {                    // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+    if (p.task == 0 || (p.task >= 3 && p.task <= 13)) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
         oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
@@ -372,12 +376,13 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 13) throw std::runtime_error("task_configure: unknown task id");
-    if ((task == 1 || task == 2) && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
+    if (task < 0 || task > 15) throw std::runtime_error("task_configure: unknown task id");
+    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15;
+    if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
     task_->robot = robot;
-    task_->package = (task == 1 || task == 2) ? package : std::string();
+    task_->package = needs_package ? package : std::string();
     task_->max_episode_steps = max_episode_steps;
     task_->epoch = -1;
 }
@@ -395,7 +400,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 1 || T.task == 2) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -451,7 +456,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task >= 12) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -533,11 +538,11 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10;
-    p.other_width = (stairs || T.task == 9 || T.task >= 12) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13
-    static const int kGoalAxis[14] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0};
-    static const double kGoal[14] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0};
-    static const double kBonus[14] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0};
+    p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15
+    static const int kGoalAxis[16] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1};
+    static const double kGoal[16] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69};
+    static const double kBonus[16] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     if (ort_rule && (reward || done)) {

@@ -18,7 +18,7 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, bridge_walker_world, cave_crawler_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
+from .world import (WorldSpec, bridge_walker_world, carrier_world, cave_crawler_world, pusher_v1_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
                     jumper_world, obstacle_traverser_v0_world,
                     obstacle_traverser_world, pusher_world, terrain_for, thrower_world, up_stepper_world, walker_world)
 
@@ -28,6 +28,8 @@ TASKS = {
     "Walker-v0": (0, walker_world, None, 500),
     "Pusher-v0": (1, pusher_world, "package", 500),
     "Thrower-v0": (2, thrower_world, "package", 300),
+    "Carrier-v0": (14, carrier_world, "package", 500),                        # manipulate.py:83-199, __init__.py:113-117
+    "Pusher-v1": (15, pusher_v1_world, "package", 600),                       # manipulate.py:419-516, __init__.py:131-135
     "Climber-v0": (3, climber_world, None, 400),                              # evogym/envs/climb.py:38-112, __init__.py:187-191
     "ObstacleTraverser-v1": (4, obstacle_traverser_world, None, 1000),        # evogym/envs/traverse.py:350-426, __init__.py:76-80
     "BridgeWalker-v0": (5, bridge_walker_world, None, 500),                   # evogym/envs/walk.py:122-232, __init__.py:22-26

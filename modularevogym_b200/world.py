@@ -358,6 +358,36 @@ def pusher_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) ->
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _carrier_terrain() -> WorldSpec:
+    w = flat_ground_world(100)
+    w.add_from_array("package", _package(), 3, 6)
+    return _frozen(w)
+
+
+def carrier_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Carrier-v0 (``sim_files/Carrier-v0.json`` + ``evogym/envs/manipulate.py:88-89``): 100 x 1 fixed ground, the SOFT package
+    hanging at voxel (3, 6) above the robot at (1, 1)."""
+    w = _shared(_carrier_terrain())
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
+@functools.lru_cache(maxsize=None)
+def _pusher_v1_terrain() -> WorldSpec:
+    w = flat_ground_world(100)
+    w.add_from_array("package", np.full((2, 3), VOXEL_TYPES["RIGID"], dtype=np.int64), 8, 1)
+    return _frozen(w)
+
+
+def pusher_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Pusher-v1 (``sim_files/Pusher-v1.json`` + ``manipulate.py:424-425``): 100 x 1 fixed ground, a RIGID package at voxel (8, 1),
+    the robot behind it at (13, 1): it has to get to the other side first."""
+    w = _shared(_pusher_v1_terrain())
+    w.add_from_array("robot", robot, 13, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -689,6 +719,8 @@ _TERRAINS = {
     "Walker-v0": (lambda robot: _walker_terrain(100), (1, 1)),
     "Pusher-v0": (lambda robot: _pusher_terrain(), (1, 1)),
     "Thrower-v0": (lambda robot: _thrower_terrain(), (1, 1)),
+    "Carrier-v0": (lambda robot: _carrier_terrain(), (1, 1)),
+    "Pusher-v1": (lambda robot: _pusher_v1_terrain(), (13, 1)),
     "Climber-v0": (lambda robot: _climber_terrain(max(7, int(np.asarray(robot).shape[1]) + 2)), (1, 1)),
     "Climber-v1": (lambda robot: _climber_v1_terrain(), (1, 1)),
     "Climber-v2": (lambda robot: _climber_v2_terrain(), (1, 1)),

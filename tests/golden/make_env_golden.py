@@ -147,7 +147,7 @@ def main():
     install_stubs()
 
     from evogym.envs.walk import Duck, SoftBridge, WalkingFlat
-    from evogym.envs.manipulate import PushSmallRect, ThrowSmallRect
+    from evogym.envs.manipulate import CarrySmallRect, PushSmallRect, PushSmallRectOnOppositeSide, ThrowSmallRect
     from evogym.envs.climb import Climb0, Climb1, Climb2
     from evogym.envs.traverse import StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
@@ -158,7 +158,8 @@ def main():
              "bridgewalker": (SoftBridge, "BridgeWalker-v0"), "obstaclev0": (WalkingBumpy, "ObstacleTraverser-v0"),
              "upstepper": (StepsUp, "UpStepper-v0"), "downstepper": (StepsDown, "DownStepper-v0"),
              "jumper": (StationaryJump, "Jumper-v0"), "hurdler": (VerticalBarrier, "Hurdler-v0"), "climberv1": (Climb1, "Climber-v1"),
-             "cavecrawler": (Duck, "CaveCrawler-v0"), "climberv2": (Climb2, "Climber-v2")}
+             "cavecrawler": (Duck, "CaveCrawler-v0"), "climberv2": (Climb2, "Climber-v2"),
+             "carrier": (CarrySmallRect, "Carrier-v0"), "pusherv1": (PushSmallRectOnOppositeSide, "Pusher-v1")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
