@@ -5,7 +5,7 @@
 // Sim::step, reference SimulatorCPP/Sim.cpp:105-115 -> Environment::step, Environment.cpp:166-205).  Same arithmetic,
 // statement for statement, as wstep_kernel (wkernel.cuh); the exactness contract is in kernels.cuh / DESIGN.md.
 //
-// What bounds this path on B200 (ncu, profiles/r01h_step512_*): not HBM (the state is on chip) and not the FP64 pipe
+// What bounds this path on B200 (ncu, profiles/r02k_gstep256_*; round 1: r01h_step512_*): not HBM (the state is on chip) and not the FP64 pipe
 // (11 % busy) but a long chain of short dependent phases separated by CTA barriers, run by too few warps to hide their
 // latency.  The layout below is built around that:
 //   * shared memory holds only what is gathered across threads every stage (positions, stage positions, contact forces,
@@ -27,7 +27,10 @@
 //     same sums as a serial walk) without one barrier per warp;
 //   * U edges per thread in flight in the spring / limiter passes (independent sqrt / div chains);
 //   * CTA-wide flags travel on barriers that exist anyway (cta_or: three rotating slots, one barrier per use): a
-//     contact-free substep of a robot inside its strain limits takes 12 barriers.
+//     contact-free substep of a robot inside its strain limits takes 12 barriers;
+//   * a launch may cover only a range of an env-step's substeps (StepParams::chunk_first / chunk_last): the host issues a step
+//     as several such launches on two streams per class where one launch would leave a partly filled last wave of CTAs
+//     (Batch::step_async).
 #pragma once
 
 #include "kernels.cuh"

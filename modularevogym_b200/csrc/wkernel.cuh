@@ -1,7 +1,7 @@
 // Warp-per-environment step kernel for small worlds (one 5x5-class robot, optionally a small free object):
 // the Walker-v0 / Pusher-v0 / Thrower-v0 configurations of BASELINE.json.
 //
-// Same arithmetic as step_kernel (kernels.cuh) -- the two agree bit for bit and tests run both -- but laid out
+// Same arithmetic as gstep_kernel (gkernel.cuh) -- the two agree bit for bit and tests run both -- but laid out
 // for what bounds this path on B200 (ncu: DRAM ~ 0, FP64 pipe < 20 %, issue slots < 40 %): each environment is one
 // long dependent chain (FP64 sqrt / div sequences, shared-memory round trips, ballots), shared memory allows 16 of
 // them per SM, the substep body is larger than the instruction cache, and with the barrier that keeps the warps in
@@ -19,7 +19,9 @@
 //     accumulates a contact's forces in registers,
 //   * division by a compile-time constant is three instructions and bit-identical (div_const, kernels.cuh),
 //   * one environment per warp, 16 warps = one CTA per SM; a CTA barrier every substep keeps them in the same code
-//     region so they share instruction-cache lines; the host sizes CTAs for equally full waves.
+//     region so they share instruction-cache lines; the host sizes CTAs for equally full waves, or issues the step as
+//     (CTA-group, chunk) work items that the CTAs draw from a counter (wstep_kernel below),
+//   * stage-in by the bulk-copy engine: the design blob holds the tables in the form shared memory wants them.
 #pragma once
 
 #include "kernels.cuh"
