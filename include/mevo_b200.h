@@ -262,6 +262,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_CARRIER 14                /* CarrySmallRect, manipulate.py:83-199 (Carrier-v0): reward = half the advance of package and robot,
                                                10 x the package's fall below 3 voxels; goal at robot x > 99; observations as MEVO_TASK_PUSHER */
 #define MEVO_TASK_PUSHER_V1 15              /* PushSmallRectOnOppositeSide, manipulate.py:419-516 (Pusher-v1): MEVO_TASK_PUSHER with the goal at x > 69 */
+#define MEVO_TASK_BALANCER 16               /* Balance, evogym/envs/balance.py:14-135 (Balancer-v0): reward = approach of the centre of mass to
+                                               (17, 5) voxels; "other" = [orientation]; flat = [orientation, relative positions] */
+#define MEVO_TASK_BALANCER_V1 17            /* BalanceJump, balance.py:138-259 (Balancer-v1): the same towards (17.5, 6) */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -133,6 +133,12 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         reward = (rf_y - ri_y) + (rf_x - ri_x) * 0.2;
     } else if (p.task == 9) {                            // jump.py:72-75
         reward = (rf_y - ri_y) * 10 - fabs(rf_x - ri_x) * 5;
+    } else if (p.task == 16) {                           // balance.py:47-53 (Balancer-v0)
+        reward = fabs(17 * kVoxel - ri_x) - fabs(17 * kVoxel - rf_x);
+        reward += (fabs(5.0 * kVoxel - ri_y) - fabs(5.0 * kVoxel - rf_y));
+    } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
+        reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
+        reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
     } else if (p.task == 14) {                           // manipulate.py:111-127 (Carrier-v0, thresh_height 3 voxels)
         reward = (pf_x - pi_x) * 0.5;
         reward += (rf_x - ri_x) * 0.5;
@@ -189,6 +195,8 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
     if (p.task == 0 || (p.task >= 3 && p.task <= 13)) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
+    } else if (p.task == 16 || p.task == 17) {           // Balancer: the orientation alone, written by the host's launch
+        oth[0] = 0.0; oth[1] = 0.0;
     } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
         oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
     }
@@ -376,7 +384,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 15) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 17) throw std::runtime_error("task_configure: unknown task id");
     const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
@@ -400,7 +408,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 16 || T.task == 17) ? 1 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -539,10 +547,10 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10;
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15
-    static const int kGoalAxis[16] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1};
-    static const double kGoal[16] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69};
-    static const double kBonus[16] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17
+    static const int kGoalAxis[18] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0};
+    static const double kGoal[18] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0};
+    static const double kBonus[18] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     if (ort_rule && (reward || done)) {
@@ -553,6 +561,11 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     CUDA_CHECK(cudaGetLastError());
+    if (T.task == 16 || T.task == 17) {
+        // Balancer-v0 / -v1 (balance.py:72-78, base.py:664-665): "other" = [orientation]; flat = [orientation, relative positions]
+        if (other) object_orientation_strided_device(T.robot_obj, other, other_stride, is_f32);
+        if (flat) object_orientation_strided_device(T.robot_obj, flat, flat_stride, is_f32);
+    }
     if (T.task == 5) {
         // BridgeWalker-v0 (walk.py:161-165, base.py:656-657): column 2 of "other" and of the flat observation = get_ort_obs("robot")
         const size_t el = is_f32 ? sizeof(float) : sizeof(double);

@@ -18,7 +18,7 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, bridge_walker_world, carrier_world, cave_crawler_world, pusher_v1_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
+from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_world, cave_crawler_world, pusher_v1_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
                     jumper_world, obstacle_traverser_v0_world,
                     obstacle_traverser_world, pusher_world, terrain_for, thrower_world, up_stepper_world, walker_world)
 
@@ -40,6 +40,8 @@ TASKS = {
     "Climber-v1": (11, climber_v1_world, None, 600),                          # climb.py:131-231, __init__.py:193-197
     "CaveCrawler-v0": (12, cave_crawler_world, None, 1000),                   # walk.py:235-345, __init__.py:28-32
     "Climber-v2": (13, climber_v2_world, None, 1000),                         # climb.py:226-320, __init__.py:199-203
+    "Balancer-v0": (16, balancer_world, None, 600),                           # balance.py:14-135, __init__.py:46-50
+    "Balancer-v1": (17, balancer_v1_world, None, 600),                        # balance.py:138-259, __init__.py:52-56
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 

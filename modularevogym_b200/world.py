@@ -388,6 +388,33 @@ def pusher_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None)
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _balancer_terrain(pole: int) -> WorldSpec:
+    w = WorldSpec(width=30, height=5)
+    grid = np.zeros((5, 30), dtype=np.int64)
+    grid[4, :] = VOXEL_TYPES["FIXED"]
+    grid[:, 0] = grid[:, 29] = VOXEL_TYPES["FIXED"]
+    grid[4 - pole:4, 17] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("ground", grid, 0, 0)
+    return _frozen(w)
+
+
+def balancer_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Balancer-v0 (``sim_files/Balancer-v0.json`` + ``evogym/envs/balance.py:19-20``): a walled 30 x 5 box with a 2-voxel pole
+    at column 17, the robot on top of it at voxel (15, 3)."""
+    w = _shared(_balancer_terrain(2))
+    w.add_from_array("robot", robot, 15, 3, connections)
+    return w
+
+
+def balancer_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Balancer-v1 (``sim_files/Balancer-v1.json`` + ``balance.py:143-144``): the same box with a 3-voxel pole, the robot on the floor
+    at voxel (10, 1): it has to jump onto the pole."""
+    w = _shared(_balancer_terrain(3))
+    w.add_from_array("robot", robot, 10, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -720,6 +747,8 @@ _TERRAINS = {
     "Pusher-v0": (lambda robot: _pusher_terrain(), (1, 1)),
     "Thrower-v0": (lambda robot: _thrower_terrain(), (1, 1)),
     "Carrier-v0": (lambda robot: _carrier_terrain(), (1, 1)),
+    "Balancer-v0": (lambda robot: _balancer_terrain(2), (15, 3)),
+    "Balancer-v1": (lambda robot: _balancer_terrain(3), (10, 1)),
     "Pusher-v1": (lambda robot: _pusher_v1_terrain(), (13, 1)),
     "Climber-v0": (lambda robot: _climber_terrain(max(7, int(np.asarray(robot).shape[1]) + 2)), (1, 1)),
     "Climber-v1": (lambda robot: _climber_v1_terrain(), (1, 1)),

@@ -151,6 +151,7 @@ def main():
     from evogym.envs.climb import Climb0, Climb1, Climb2
     from evogym.envs.traverse import StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
+    from evogym.envs.balance import Balance, BalanceJump
     from evogym import sample_robot
 
     tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
@@ -159,7 +160,8 @@ def main():
              "upstepper": (StepsUp, "UpStepper-v0"), "downstepper": (StepsDown, "DownStepper-v0"),
              "jumper": (StationaryJump, "Jumper-v0"), "hurdler": (VerticalBarrier, "Hurdler-v0"), "climberv1": (Climb1, "Climber-v1"),
              "cavecrawler": (Duck, "CaveCrawler-v0"), "climberv2": (Climb2, "Climber-v2"),
-             "carrier": (CarrySmallRect, "Carrier-v0"), "pusherv1": (PushSmallRectOnOppositeSide, "Pusher-v1")}
+             "carrier": (CarrySmallRect, "Carrier-v0"), "pusherv1": (PushSmallRectOnOppositeSide, "Pusher-v1"),
+             "balancer": (Balance, "Balancer-v0"), "balancerv1": (BalanceJump, "Balancer-v1")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
