@@ -18,9 +18,10 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_world, cave_crawler_world, pusher_v1_world, climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
-                    jumper_world, obstacle_traverser_v0_world,
-                    obstacle_traverser_world, pusher_world, terrain_for, thrower_world, up_stepper_world, walker_world)
+from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_world, cave_crawler_world,
+                    climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
+                    jumper_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
+                    terrain_for, thrower_world, up_stepper_world, walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
 # (evogym/envs/__init__.py:16-20,125-129,149-153))

@@ -1,3 +1,8 @@
+#!/usr/bin/env python
+"""cProfile of `BatchedEvoGymEnv.update` (design-loop rebuild) for 4096 Walker-v0 environments: where the host time goes.
+
+    python tools/prof_update.py
+"""
 import cProfile, pstats, random, sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
