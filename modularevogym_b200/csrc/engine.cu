@@ -49,7 +49,8 @@ int group_class_for(int Pd, int Ed) {
     // threads per environment.  MEVO_GCLASS = "p64,p128,p256" (development): largest point count that runs with 64 / 128 / 256
     // threads; MEVO_GROUP_SHIFT (development, tests) moves every environment up or down one class.  A class whose largest
     // environment has more points than threads runs a 2- or 4-points-per-thread build of the kernel.
-    int lim[3] = {128, 256, 512};          // measured on B200: few threads per environment, many environments per SM
+    int lim[3] = {128, 192, 512};          // measured on B200: few threads per environment, many environments per SM (the middle
+                                           // limit from a sweep on the heterogeneous mix: 256 -> 393 k, 160 ... 208 -> 399 ... 405 k env-steps/s)
     if (const char* g = std::getenv("MEVO_GCLASS")) std::sscanf(g, "%d,%d,%d", &lim[0], &lim[1], &lim[2]);
     const char* shift_env = std::getenv("MEVO_GROUP_SHIFT");       // read at every finalize: the tests move fixtures across classes
     const int shift = shift_env ? std::atoi(shift_env) : 0;
