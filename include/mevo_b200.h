@@ -265,6 +265,10 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_BALANCER 16               /* Balance, evogym/envs/balance.py:14-135 (Balancer-v0): reward = approach of the centre of mass to
                                                (17, 5) voxels; "other" = [orientation]; flat = [orientation, relative positions] */
 #define MEVO_TASK_BALANCER_V1 17            /* BalanceJump, balance.py:138-259 (Balancer-v1): the same towards (17.5, 6) */
+#define MEVO_TASK_GAP_JUMPER 18             /* Gaps, traverse.py:663-782 (GapJumper-v0): StairsBase reward and observation (floor sight over the five
+                                               platforms); a robot whose centre of mass drops below 4 voxels has fallen: reward - 3, done */
+#define MEVO_TASK_PLATFORM_JUMPER 19        /* FloatingPlatform, traverse.py:539-660 (PlatformJumper-v0): the same over seven platforms, fall below
+                                               0.4 m, and the orientation rule of MEVO_TASK_DOWN_STEPPER */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -74,6 +74,7 @@ struct TaskParams {
     // the last observation -- an unstable step saved no snapshot, the environment then reads the old one (Sim.cpp:105-115)
     int goal_axis;                       // 0: no goal, 1: robot com x, 2: robot com y beyond `goal` voxels ends the episode with `goal_bonus`
     double goal, goal_bonus;
+    double fall_y;                       // > 0: a robot whose centre of mass is below this height [m] has fallen off: reward - 3, done
     const double* ort_now;
     double* ort_prev;
 };
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
+    if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3 || p.task == 11) {            // climb.py:96-99, 190-193
         reward = rf_y - ri_y;
@@ -157,6 +158,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // goal met (walk.py:79-82, 190-193; manipulate.py:390-393; climb.py:107-109, 201-203; traverse.py:120-123, 222-225, 321-324, 420-423)
     if (p.goal_axis == 1 && rf_x > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
     if (p.goal_axis == 2 && rf_y > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
+    if (p.fall_y > 0 && rf_y < p.fall_y) { reward -= 3.0; done = true; }        // traverse.py:609-613, 734-738
     if (p.ort_now) {
         // DownStepper-v0 / ObstacleTraverser-v0 / Hurdler-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327, 514-516)
         const double ort = unstable ? p.ort_prev[env] : p.ort_now[env];
@@ -193,7 +195,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // ---- observations of the (possibly reset) state
     double oth[6];
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
-    if (p.task == 0 || (p.task >= 3 && p.task <= 13)) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task >= 18) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else if (p.task == 16 || p.task == 17) {           // Balancer: the orientation alone, written by the host's launch
         oth[0] = 0.0; oth[1] = 0.0;
@@ -384,7 +386,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 17) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 19) throw std::runtime_error("task_configure: unknown task id");
     const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
@@ -408,7 +410,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 16 || T.task == 17) ? 1 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 16 || T.task == 17) ? 1 : T.task >= 18 ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -464,7 +466,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13 || T.task >= 18) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -544,14 +546,15 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10;
-    const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10;
+    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task >= 18;
+    const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19;
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17
-    static const int kGoalAxis[18] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0};
-    static const double kGoal[18] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0};
-    static const double kBonus[18] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19
+    static const int kGoalAxis[20] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0};
+    static const double kGoal[20] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0};
+    static const double kBonus[20] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
+    p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     if (ort_rule && (reward || done)) {
         object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
@@ -604,7 +607,11 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
         if (other_stride < 14) throw std::runtime_error("task_outputs: the 'other' observation of this task is 14 wide");
         const size_t el = is_f32 ? sizeof(float) : sizeof(double);
         object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
-        sight_obs_strided_device(T.robot_obj, {"ground"}, 5, 5.0, false, static_cast<char*>(other) + 3 * el, 11, other_stride, is_f32);
+        static const std::vector<std::string> kGround = {"ground"};
+        static const std::vector<std::string> kGaps = {"platform_1", "platform_2", "platform_3", "platform_4", "platform_5"};
+        static const std::vector<std::string> kPlatforms = {"platform_1", "platform_2", "platform_3", "platform_4", "platform_5", "platform_6", "platform_7"};
+        const std::vector<std::string>& terrain = T.task == 18 ? kGaps : T.task == 19 ? kPlatforms : kGround;     // traverse.py:683, 562
+        sight_obs_strided_device(T.robot_obj, terrain, 5, 5.0, false, static_cast<char*>(other) + 3 * el, 11, other_stride, is_f32);
     }
     if (reset_done) for (auto& e : envs_) e.host_fresh = false;
 }

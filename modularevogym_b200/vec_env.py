@@ -19,7 +19,7 @@ import numpy as np
 
 from . import capi
 from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_world, cave_crawler_world,
-                    climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, hurdler_world,
+                    climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
                     jumper_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
 
@@ -43,6 +43,8 @@ TASKS = {
     "Climber-v2": (13, climber_v2_world, None, 1000),                         # climb.py:226-320, __init__.py:199-203
     "Balancer-v0": (16, balancer_world, None, 600),                           # balance.py:14-135, __init__.py:46-50
     "Balancer-v1": (17, balancer_v1_world, None, 600),                        # balance.py:138-259, __init__.py:52-56
+    "GapJumper-v0": (18, gap_jumper_world, None, 1000),                       # traverse.py:663-782, __init__.py:88-92
+    "PlatformJumper-v0": (19, platform_jumper_world, None, 1000),             # traverse.py:539-660, __init__.py:94-98
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 
@@ -65,7 +67,7 @@ class BatchedEvoGymEnv:
         if env_id not in TASKS:
             raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
         task, builder, package, limit = TASKS[env_id]
-        if task in (4, 6, 7, 8, 9, 10, 12, 13) and mode != "modular":
+        if task in (4, 6, 7, 8, 9, 10, 12, 13, 18, 19) and mode != "modular":
             raise ValueError(f"{env_id} is available in modular mode only (its flat observation interleaves orientation "
                              "and sight values with a per-robot number of positions)")
         self.env_id, self.mode, self.device_index = env_id, mode, device

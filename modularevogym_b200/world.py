@@ -415,6 +415,46 @@ def balancer_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = Non
     return w
 
 
+# (name, width, x, y) of the one-voxel-thick FIXED platforms of GapJumper-v0.json (80 x 6) and PlatformJumper-v0.json (91 x 9)
+GAP_JUMPER_PLATFORMS = (("platform_1", 20, 0, 5), ("platform_2", 10, 25, 5), ("platform_3", 10, 40, 5), ("platform_4", 10, 55, 5),
+                        ("platform_5", 10, 70, 5))
+PLATFORM_JUMPER_PLATFORMS = (("platform_1", 20, 0, 5), ("platform_2", 10, 21, 7), ("platform_3", 10, 33, 8), ("platform_4", 10, 46, 6),
+                             ("platform_5", 10, 57, 5), ("platform_6", 10, 70, 6), ("platform_7", 10, 81, 3))
+
+
+def _platform_terrain(width: int, height: int, platforms) -> WorldSpec:
+    w = WorldSpec(width=width, height=height)
+    for name, pw, x, y in platforms:
+        w.add_from_array(name, np.full((1, pw), VOXEL_TYPES["FIXED"], dtype=np.int64), x, y)
+    return _frozen(w)
+
+
+@functools.lru_cache(maxsize=None)
+def _gap_jumper_terrain() -> WorldSpec:
+    return _platform_terrain(80, 6, GAP_JUMPER_PLATFORMS)
+
+
+@functools.lru_cache(maxsize=None)
+def _platform_jumper_terrain() -> WorldSpec:
+    return _platform_terrain(91, 9, PLATFORM_JUMPER_PLATFORMS)
+
+
+def gap_jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """GapJumper-v0 (``sim_files/GapJumper-v0.json`` + ``evogym/envs/traverse.py:668-669``): five fixed platforms at one height with
+    gaps between them, the robot at voxel (1, 6)."""
+    w = _shared(_gap_jumper_terrain())
+    w.add_from_array("robot", robot, 1, 6, connections)
+    return w
+
+
+def platform_jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """PlatformJumper-v0 (``sim_files/PlatformJumper-v0.json`` + ``traverse.py:544-545``): seven fixed platforms at different
+    heights, the robot at voxel (1, 6)."""
+    w = _shared(_platform_jumper_terrain())
+    w.add_from_array("robot", robot, 1, 6, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -761,6 +801,8 @@ _TERRAINS = {
     "BridgeWalker-v0": (lambda robot: _bridge_walker_terrain(), (2, 5)),
     "CaveCrawler-v0": (lambda robot: _cave_crawler_terrain(), (1, 2)),
     "Jumper-v0": (lambda robot: _jumper_terrain(), (32, 1)),
+    "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
+    "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }
 
 

@@ -128,7 +128,22 @@ def install_stubs():
 # DownStepper-v0 / ObstacleTraverser-v0 end the episode when the robot lies on its back (traverse.py:226-228, 325-327); random
 # rollouts of 12 steps never get there, so before step FLIP_STEP the robot is turned by pi about its centre of mass and lifted clear
 # of the ground (engine state only: the step's reward still starts from the last snapshot's centre of mass, which has the same x)
-FLIP_TASKS, FLIP_STEP = ("obstaclev0", "downstepper", "hurdler"), 6
+FLIP_TASKS, FLIP_STEP = ("obstaclev0", "downstepper", "hurdler", "platformjumper"), 6
+
+
+# GapJumper-v0 ends the episode when the robot has fallen between the platforms (centre of mass below 4 voxels, traverse.py:734-738):
+# before step FLIP_STEP the robot is set down left of the first platform, just above the ground plane
+DROP_TASKS = ("gapjumper",)
+
+
+def drop_robot(env):
+    r = env._sim._r
+    pos, vel, last, vt = r.get_state()
+    info = r.object_info(list(r.object_names).index("robot"))
+    sl = slice(info["min_point"], info["max_point"] + 1)
+    low = pos[sl].min(axis=0)
+    pos[sl] += np.array([-1.0, 0.02]) - low
+    r.set_state(pos, np.zeros_like(vel), pos.copy(), np.zeros_like(vt))
 
 
 def flip_robot(env):
@@ -149,7 +164,7 @@ def main():
     from evogym.envs.walk import Duck, SoftBridge, WalkingFlat
     from evogym.envs.manipulate import CarrySmallRect, PushSmallRect, PushSmallRectOnOppositeSide, ThrowSmallRect
     from evogym.envs.climb import Climb0, Climb1, Climb2
-    from evogym.envs.traverse import StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
+    from evogym.envs.traverse import FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
     from evogym.envs.balance import Balance, BalanceJump
     from evogym import sample_robot
@@ -161,7 +176,8 @@ def main():
              "jumper": (StationaryJump, "Jumper-v0"), "hurdler": (VerticalBarrier, "Hurdler-v0"), "climberv1": (Climb1, "Climber-v1"),
              "cavecrawler": (Duck, "CaveCrawler-v0"), "climberv2": (Climb2, "Climber-v2"),
              "carrier": (CarrySmallRect, "Carrier-v0"), "pusherv1": (PushSmallRectOnOppositeSide, "Pusher-v1"),
-             "balancer": (Balance, "Balancer-v0"), "balancerv1": (BalanceJump, "Balancer-v1")}
+             "balancer": (Balance, "Balancer-v0"), "balancerv1": (BalanceJump, "Balancer-v1"),
+             "gapjumper": (Gaps, "GapJumper-v0"), "platformjumper": (FloatingPlatform, "PlatformJumper-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
@@ -173,7 +189,7 @@ def main():
             body, conn = sample_robot((5, 5))
             rng = np.random.default_rng(500 + seed)
             out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": env_id}
-            if task in FLIP_TASKS:
+            if task in FLIP_TASKS or task in DROP_TASKS:
                 out["flip_step"] = np.int32(FLIP_STEP)
             # ---- flat mode
             env = cls(body, conn, mode=None, env_id=env_id)
@@ -185,6 +201,8 @@ def main():
             for t in range(n_steps):
                 if task in FLIP_TASKS and t == FLIP_STEP:
                     flip_robot(env)
+                if task in DROP_TASKS and t == FLIP_STEP:
+                    drop_robot(env)
                 # engine state the step starts from (teacher forcing in the GPU test)
                 st = env._sim._r.get_state()
                 for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
@@ -207,6 +225,8 @@ def main():
                 vox_acts[t, ~act_mask] = acts[t]
                 if task in FLIP_TASKS and t == FLIP_STEP:
                     flip_robot(envm)
+                if task in DROP_TASKS and t == FLIP_STEP:
+                    drop_robot(envm)
                 o, r, d, _ = envm.step(vox_acts[t].copy())
                 mod_obs.append(np.asarray(o["modular"], dtype=np.float64)); other_obs.append(np.asarray(o["other"], dtype=np.float64))
                 mrew.append(float(r)); mdone.append(bool(d))
