@@ -140,6 +140,10 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
         reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
         reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
+    } else if (p.task == 20) {                           // manipulate.py:230-250 (Carrier-v1; its package term is overwritten there, :239-240)
+        reward = (fabs(40 * kVoxel - ri_x) - fabs(40 * kVoxel - rf_x));
+        const double thresh = pf_x > 20 * kVoxel ? 4.0 * kVoxel : 6.0 * kVoxel;
+        if (pf_y < thresh) reward += 10 * (pf_y - pi_y);
     } else if (p.task == 14) {                           // manipulate.py:111-127 (Carrier-v0, thresh_height 3 voxels)
         reward = (pf_x - pi_x) * 0.5;
         reward += (rf_x - ri_x) * 0.5;
@@ -195,7 +199,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // ---- observations of the (possibly reset) state
     double oth[6];
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
-    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task >= 18) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else if (p.task == 16 || p.task == 17) {           // Balancer: the orientation alone, written by the host's launch
         oth[0] = 0.0; oth[1] = 0.0;
@@ -386,8 +390,8 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 19) throw std::runtime_error("task_configure: unknown task id");
-    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15;
+    if (task < 0 || task > 20) throw std::runtime_error("task_configure: unknown task id");
+    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -410,7 +414,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 16 || T.task == 17) ? 1 : T.task >= 18 ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 16 || T.task == 17) ? 1 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -466,7 +470,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13 || T.task >= 18) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13 || T.task == 18 || T.task == 19) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -546,13 +550,13 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task >= 18;
+    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task == 18 || T.task == 19;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19;
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19
-    static const int kGoalAxis[20] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0};
-    static const double kGoal[20] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0};
-    static const double kBonus[20] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20
+    static const int kGoalAxis[21] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0};
+    static const double kGoal[21] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0};
+    static const double kBonus[21] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;

@@ -455,6 +455,31 @@ def platform_jumper_world(robot: np.ndarray, connections: Optional[np.ndarray] =
     return w
 
 
+# rows of the "ground" object of evogym/envs/sim_files/Carrier-v1.json (60 x 4, placed at voxel (0, 1)), top row first
+CARRIER_V1_ROWS = (
+    "................................................FF..........",
+    "FFFFFFFFFFFFFFFFFFFFFFFF........................FF..........",
+    ".......................FFFF.....................FF..........",
+    "..........................FFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFF",
+)
+
+
+@functools.lru_cache(maxsize=None)
+def _carrier_v1_terrain() -> WorldSpec:
+    w = WorldSpec(width=60, height=12)
+    w.add_from_array("ground", grid_from_rows(CARRIER_V1_ROWS), 0, 1)
+    w.add_from_array("package", np.full((2, 3), VOXEL_TYPES["RIGID"], dtype=np.int64), 3, 10)
+    return _frozen(w)
+
+
+def carrier_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Carrier-v1 (``sim_files/Carrier-v1.json`` + ``evogym/envs/manipulate.py:207-208``): a raised start shelf, two steps down and a
+    table post, a RIGID package at voxel (3, 10) above the robot at (1, 4)."""
+    w = _shared(_carrier_v1_terrain())
+    w.add_from_array("robot", robot, 1, 4, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -787,6 +812,7 @@ _TERRAINS = {
     "Pusher-v0": (lambda robot: _pusher_terrain(), (1, 1)),
     "Thrower-v0": (lambda robot: _thrower_terrain(), (1, 1)),
     "Carrier-v0": (lambda robot: _carrier_terrain(), (1, 1)),
+    "Carrier-v1": (lambda robot: _carrier_v1_terrain(), (1, 4)),
     "Balancer-v0": (lambda robot: _balancer_terrain(2), (15, 3)),
     "Balancer-v1": (lambda robot: _balancer_terrain(3), (10, 1)),
     "Pusher-v1": (lambda robot: _pusher_v1_terrain(), (13, 1)),

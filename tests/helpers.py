@@ -37,8 +37,9 @@ class EnvGolden:
                      "BridgeWalker-v0": 5, "ObstacleTraverser-v0": 6, "UpStepper-v0": 7, "DownStepper-v0": 8,
                      "Jumper-v0": 9, "Hurdler-v0": 10, "Climber-v1": 11, "CaveCrawler-v0": 12,
                      "Climber-v2": 13, "Carrier-v0": 14, "Pusher-v1": 15,
-                     "Balancer-v0": 16, "Balancer-v1": 17, "GapJumper-v0": 18, "PlatformJumper-v0": 19}[self.env_id]
-        self.package = "package" if self.task in (1, 2, 14, 15) else None
+                     "Balancer-v0": 16, "Balancer-v1": 17, "GapJumper-v0": 18, "PlatformJumper-v0": 19,
+                     "Carrier-v1": 20}[self.env_id]
+        self.package = "package" if self.task in (1, 2, 14, 15, 20) else None
         self.n_steps = int(self.z["reward"].shape[0])
 
     def __getitem__(self, k):
