@@ -272,10 +272,13 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_CARRIER_V1 20             /* CarrySmallRectToTable, manipulate.py:202-315 (Carrier-v1): reward = the robot's approach to x = 40 voxels
                                                (the package term is overwritten in the reference, :239-240, and so here) + 10 x the package's
                                                fall below 6 voxels (4 past x = 20); no goal; observations as MEVO_TASK_PUSHER */
+#define MEVO_TASK_LIFTER 21                 /* LiftSmallRect, manipulate.py:1207-1340 (Lifter-v0): reward = 10 x the package's rise + 10 x its approach
+                                               to x = 5.5 voxels + 20 x the robot's fall below 3 voxels; observations as MEVO_TASK_PUSHER followed
+                                               by the package's orientation (7 values) */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */
-/* package: used by MEVO_TASK_PUSHER / _THROWER / _CARRIER / _CARRIER_V1 / _PUSHER_V1 only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
+/* package: used by MEVO_TASK_PUSHER / _THROWER / _CARRIER / _CARRIER_V1 / _PUSHER_V1 / _LIFTER only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
 int mevo_batch_task_configure(mevo_batch* b, int task, const char* robot, const char* package, int max_episode_steps);
 /* dims[0..4] = flat observation width, modular observation width (9 x voxels), "other" observation width,
  * largest voxel count of a robot grid, action stride */

@@ -140,6 +140,11 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
         reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
         reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
+    } else if (p.task == 21) {                           // manipulate.py:1232-1250 (Lifter-v0)
+        reward = (pf_y - pi_y) * 10;
+        const double goal = 5.5 * kVoxel;
+        reward += (fabs(goal - pi_x) - fabs(goal - pf_x)) * 10;
+        if (rf_y < 3 * kVoxel) reward += 20 * (rf_y - ri_y);
     } else if (p.task == 20) {                           // manipulate.py:230-250 (Carrier-v1; its package term is overwritten there, :239-240)
         reward = (fabs(40 * kVoxel - ri_x) - fabs(40 * kVoxel - rf_x));
         const double thresh = pf_x > 20 * kVoxel ? 4.0 * kVoxel : 6.0 * kVoxel;
@@ -331,6 +336,7 @@ struct Batch::Task {
     int epoch = -1;                          // finalize epoch the tables were built for
     int flat_width = 0, modular_width = 0, other_width = 0, max_vox = 0;
     int robot_obj = -1;
+    int package_obj = -1;                // object index of the package (the same in every environment), -1: none
     std::vector<TaskEnvRec> rec;
     std::vector<short4> vox_idx;
     std::vector<unsigned char> vox_mat;
@@ -390,8 +396,8 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 20) throw std::runtime_error("task_configure: unknown task id");
-    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20;
+    if (task < 0 || task > 21) throw std::runtime_error("task_configure: unknown task id");
+    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20 || task == 21;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -414,9 +420,9 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 16 || T.task == 17) ? 1 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 16 || T.task == 17) ? 1 : T.task == 21 ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
-    T.robot_obj = -1;
+    T.robot_obj = -1; T.package_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
         const EnvHost& E = envs_[e];
@@ -433,6 +439,8 @@ void Batch::task_build() {
         if (!T.package.empty()) {
             const int po = E.world.find_object(T.package);
             if (po < 0) throw std::runtime_error("task: environment " + std::to_string(e) + " has no object named " + T.package);
+            if (T.package_obj < 0) T.package_obj = po;
+            else if (T.package_obj != po) throw std::runtime_error("task: the package must be the same object index in every environment");
             const VoxelObject& pk = E.world.objects[po];
             r.p_start = E.point_local[pk.min_point];
             r.p_count = pk.max_point - pk.min_point + 1;
@@ -553,10 +561,10 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task == 18 || T.task == 19;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19;
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20
-    static const int kGoalAxis[21] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0};
-    static const double kGoal[21] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0};
-    static const double kBonus[21] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21
+    static const int kGoalAxis[22] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0};
+    static const double kGoal[22] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0};
+    static const double kBonus[22] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
@@ -568,6 +576,18 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     CUDA_CHECK(cudaGetLastError());
+    if (T.task == 21) {
+        // Lifter-v0 (manipulate.py:1278-1283, base.py:684-685): column 6 of "other" and of the flat observation = get_ort_obs("package")
+        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+        if (other) {
+            if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");
+            object_orientation_strided_device(T.package_obj, static_cast<char*>(other) + 6 * el, other_stride, is_f32);
+        }
+        if (flat) {
+            if (flat_stride < 7) throw std::runtime_error("task_outputs: the flat observation of this task is at least 7 wide");
+            object_orientation_strided_device(T.package_obj, static_cast<char*>(flat) + 6 * el, flat_stride, is_f32);
+        }
+    }
     if (T.task == 16 || T.task == 17) {
         // Balancer-v0 / -v1 (balance.py:72-78, base.py:664-665): "other" = [orientation]; flat = [orientation, relative positions]
         if (other) object_orientation_strided_device(T.robot_obj, other, other_stride, is_f32);

@@ -20,7 +20,7 @@ import numpy as np
 from . import capi
 from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
                     climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
-                    jumper_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
+                    jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
@@ -31,6 +31,7 @@ TASKS = {
     "Thrower-v0": (2, thrower_world, "package", 300),
     "Carrier-v0": (14, carrier_world, "package", 500),                        # manipulate.py:83-199, __init__.py:113-117
     "Carrier-v1": (20, carrier_v1_world, "package", 1000),                    # manipulate.py:202-315, __init__.py:119-123
+    "Lifter-v0": (21, lifter_world, "package", 300),                          # manipulate.py:1207-1340, __init__.py:107-111
     "Pusher-v1": (15, pusher_v1_world, "package", 600),                       # manipulate.py:419-516, __init__.py:131-135
     "Climber-v0": (3, climber_world, None, 400),                              # evogym/envs/climb.py:38-112, __init__.py:187-191
     "ObstacleTraverser-v1": (4, obstacle_traverser_world, None, 1000),        # evogym/envs/traverse.py:350-426, __init__.py:76-80

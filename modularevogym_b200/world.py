@@ -480,6 +480,32 @@ def carrier_v1_world(robot: np.ndarray, connections: Optional[np.ndarray] = None
     return w
 
 
+# the "ground" object of evogym/envs/sim_files/Lifter-v0.json (11 x 5): a pit between two walled shelves
+LIFTER_ROWS = (
+    "F.........F",
+    "F.........F",
+    "FFFF...FFFF",
+    "...F...F...",
+    "...FFFFF...",
+)
+
+
+@functools.lru_cache(maxsize=None)
+def _lifter_terrain() -> WorldSpec:
+    w = WorldSpec(width=11, height=5)
+    w.add_from_array("ground", grid_from_rows(LIFTER_ROWS), 0, 0)
+    w.add_from_array("package", np.full((2, 1), VOXEL_TYPES["RIGID"], dtype=np.int64), 5, 1)
+    return _frozen(w)
+
+
+def lifter_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Lifter-v0 (``sim_files/Lifter-v0.json`` + ``evogym/envs/manipulate.py:1212-1213``): a RIGID 1 x 2 package at the bottom of a
+    pit, the robot above it at voxel (2, 3)."""
+    w = _shared(_lifter_terrain())
+    w.add_from_array("robot", robot, 2, 3, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -813,6 +839,7 @@ _TERRAINS = {
     "Thrower-v0": (lambda robot: _thrower_terrain(), (1, 1)),
     "Carrier-v0": (lambda robot: _carrier_terrain(), (1, 1)),
     "Carrier-v1": (lambda robot: _carrier_v1_terrain(), (1, 4)),
+    "Lifter-v0": (lambda robot: _lifter_terrain(), (2, 3)),
     "Balancer-v0": (lambda robot: _balancer_terrain(2), (15, 3)),
     "Balancer-v1": (lambda robot: _balancer_terrain(3), (10, 1)),
     "Pusher-v1": (lambda robot: _pusher_v1_terrain(), (13, 1)),

@@ -162,7 +162,7 @@ def main():
     install_stubs()
 
     from evogym.envs.walk import Duck, SoftBridge, WalkingFlat
-    from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, PushSmallRect, PushSmallRectOnOppositeSide, ThrowSmallRect
+    from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, LiftSmallRect, PushSmallRect, PushSmallRectOnOppositeSide, ThrowSmallRect
     from evogym.envs.climb import Climb0, Climb1, Climb2
     from evogym.envs.traverse import FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
@@ -178,7 +178,7 @@ def main():
              "carrier": (CarrySmallRect, "Carrier-v0"), "pusherv1": (PushSmallRectOnOppositeSide, "Pusher-v1"),
              "balancer": (Balance, "Balancer-v0"), "balancerv1": (BalanceJump, "Balancer-v1"),
              "gapjumper": (Gaps, "GapJumper-v0"), "platformjumper": (FloatingPlatform, "PlatformJumper-v0"),
-             "carrierv1": (CarrySmallRectToTable, "Carrier-v1")}
+             "carrierv1": (CarrySmallRectToTable, "Carrier-v1"), "lifter": (LiftSmallRect, "Lifter-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
