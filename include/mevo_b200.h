@@ -275,6 +275,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_LIFTER 21                 /* LiftSmallRect, manipulate.py:1207-1340 (Lifter-v0): reward = 10 x the package's rise + 10 x its approach
                                                to x = 5.5 voxels + 20 x the robot's fall below 3 voxels; observations as MEVO_TASK_PUSHER followed
                                                by the package's orientation (7 values) */
+#define MEVO_TASK_FLIPPER 22                /* Flipping, evogym/envs/flip.py:15-140 (Flipper-v0): reward = change of the robot's unwrapped orientation
+                                               (whole turns are counted per environment); done when the centre of mass passes x < 1 voxel;
+                                               "other" = [orientation]; flat = [orientation, relative positions] */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -77,6 +77,7 @@ struct TaskParams {
     double fall_y;                       // > 0: a robot whose centre of mass is below this height [m] has fallen off: reward - 3, done
     const double* ort_now;
     double* ort_prev;
+    int* flips;                          // Flipper-v0: whole turns so far (flip.py:34, 78-85)
 };
 
 struct ObjMeans { double ax, ay, bx, by, cx, cy, dx, dy; };
@@ -140,6 +141,15 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
         reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
         reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
+    } else if (p.task == 22) {                           // flip.py:78-90 (Flipper-v0): change of the unwrapped orientation
+        const double ort_1 = p.ort_prev[env], ort_2 = (unstable || !p.ort_now) ? ort_1 : p.ort_now[env];
+        int n = p.flips[env];
+        const double flattened_1 = n * 2 * kPi + ort_1;
+        if (ort_1 < kPi / 3 && ort_2 > 5 * kPi / 3) n -= 1;
+        if (ort_1 > 5 * kPi / 3 && ort_2 < kPi / 3) n += 1;
+        const double flattened_2 = n * 2 * kPi + ort_2;
+        reward = flattened_2 - flattened_1;
+        if (lane == 0) p.flips[env] = n;
     } else if (p.task == 21) {                           // manipulate.py:1232-1250 (Lifter-v0)
         reward = (pf_y - pi_y) * 10;
         const double goal = 5.5 * kVoxel;
@@ -167,8 +177,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // goal met (walk.py:79-82, 190-193; manipulate.py:390-393; climb.py:107-109, 201-203; traverse.py:120-123, 222-225, 321-324, 420-423)
     if (p.goal_axis == 1 && rf_x > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
     if (p.goal_axis == 2 && rf_y > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
+    if (p.task == 22 && rf_x < 1 * kVoxel) done = true;                          // flip.py:97-98: walked off the left end
     if (p.fall_y > 0 && rf_y < p.fall_y) { reward -= 3.0; done = true; }        // traverse.py:609-613, 734-738
-    if (p.ort_now) {
+    if (p.ort_now && p.task != 22) {
         // DownStepper-v0 / ObstacleTraverser-v0 / Hurdler-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327, 514-516)
         const double ort = unstable ? p.ort_prev[env] : p.ort_now[env];
         if (ort > kPi / 2 && ort < 3 * kPi / 2) { done = true; reward -= 3.0; }
@@ -189,7 +200,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
             pos[i] = q; vel[i] = v; pos[2 * te.Pd + i] = q; pos[3 * te.Pd + i] = v;
         }
         __syncwarp();
-        if (lane == 0) { p.sim_time[env] = 0; p.unstable[env] = 0; }
+        if (lane == 0) { p.sim_time[env] = 0; p.unstable[env] = 0; if (p.flips) p.flips[env] = 0; }
         ep = 0;
         R = object_means(pos, vel, te.r_start, te.r_count, lane);
         P = object_means(pos, vel, te.p_start, te.p_count, lane);
@@ -206,7 +217,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
     if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
-    } else if (p.task == 16 || p.task == 17) {           // Balancer: the orientation alone, written by the host's launch
+    } else if (p.task == 16 || p.task == 17 || p.task == 22) {   // Balancer, Flipper: the orientation alone, written by the host's launch
         oth[0] = 0.0; oth[1] = 0.0;
     } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
         oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
@@ -351,13 +362,14 @@ struct Batch::Task {
     double* d_prev = nullptr;
     double* d_ort_now = nullptr;         // orientation rule of tasks 6, 8: after the step / at the last observation
     double* d_ort_prev = nullptr;
+    int* d_flips = nullptr;              // Flipper-v0
     int* d_episode = nullptr;
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -396,7 +408,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 21) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 22) throw std::runtime_error("task_configure: unknown task id");
     const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20 || task == 21;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
@@ -420,7 +432,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 16 || T.task == 17) ? 1 : T.task == 21 ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 16 || T.task == 17 || T.task == 22) ? 1 : T.task == 21 ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1; T.package_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -494,6 +506,8 @@ void Batch::task_build() {
     CUDA_CHECK(cudaMalloc(&T.d_ort_now, sizeof(double) * n));
     CUDA_CHECK(cudaMalloc(&T.d_ort_prev, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_ort_prev, 0, sizeof(double) * n));
+    CUDA_CHECK(cudaMalloc(&T.d_flips, sizeof(int) * n));
+    CUDA_CHECK(cudaMemset(T.d_flips, 0, sizeof(int) * n));
     CUDA_CHECK(cudaMemset(T.d_episode, 0, sizeof(int) * n));
     T.epoch = finalize_epoch_;
 }
@@ -559,15 +573,15 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task == 18 || T.task == 19;
-    const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19;
+    const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19 || T.task == 22;   // (22: the reward needs both orientations)
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21
-    static const int kGoalAxis[22] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0};
-    static const double kGoal[22] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0};
-    static const double kBonus[22] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21  22
+    static const int kGoalAxis[23] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0};
+    static const double kGoal[23] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0,  0};
+    static const double kBonus[23] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
-    p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
+    p.ort_now = nullptr; p.ort_prev = T.d_ort_prev; p.flips = T.task == 22 ? T.d_flips : nullptr;
     if (ort_rule && (reward || done)) {
         object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
         p.ort_now = T.d_ort_now;
@@ -588,8 +602,8 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
             object_orientation_strided_device(T.package_obj, static_cast<char*>(flat) + 6 * el, flat_stride, is_f32);
         }
     }
-    if (T.task == 16 || T.task == 17) {
-        // Balancer-v0 / -v1 (balance.py:72-78, base.py:664-665): "other" = [orientation]; flat = [orientation, relative positions]
+    if (T.task == 16 || T.task == 17 || T.task == 22) {
+        // Flipper-v0 (flip.py:63-66) and Balancer-v0 / -v1 (balance.py:72-78, base.py:664-665): "other" = [orientation]; flat = [orientation, relative positions]
         if (other) object_orientation_strided_device(T.robot_obj, other, other_stride, is_f32);
         if (flat) object_orientation_strided_device(T.robot_obj, flat, flat_stride, is_f32);
     }
@@ -678,6 +692,7 @@ void Batch::task_reset_device(void* flat, int flat_stride, void* modular, int mo
     reset_all();
     Task& T = *task_;
     CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));   // -1: the outputs pass counts one
+    CUDA_CHECK(cudaMemsetAsync(T.d_flips, 0, sizeof(int) * num_envs(), (cudaStream_t)stream_));
     task_outputs_device(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, is_f32, false);
 }
 
@@ -686,6 +701,7 @@ void Batch::task_reset(double* flat, int flat_stride, double* modular, int modul
     reset_all();
     Task& T = *task_;
     CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));
+    CUDA_CHECK(cudaMemsetAsync(T.d_flips, 0, sizeof(int) * num_envs(), (cudaStream_t)stream_));
     task_outputs(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, false);
 }
 

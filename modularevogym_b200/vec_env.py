@@ -19,7 +19,7 @@ import numpy as np
 
 from . import capi
 from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
-                    climber_v1_world, climber_v2_world, climber_world, down_stepper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
+                    climber_v1_world, climber_v2_world, climber_world, down_stepper_world, flipper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
                     jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
 
@@ -47,6 +47,7 @@ TASKS = {
     "Balancer-v1": (17, balancer_v1_world, None, 600),                        # balance.py:138-259, __init__.py:52-56
     "GapJumper-v0": (18, gap_jumper_world, None, 1000),                       # traverse.py:663-782, __init__.py:88-92
     "PlatformJumper-v0": (19, platform_jumper_world, None, 1000),             # traverse.py:539-660, __init__.py:94-98
+    "Flipper-v0": (22, flipper_world, None, 600),                             # flip.py:15-140, __init__.py:40-44
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 

@@ -506,6 +506,21 @@ def lifter_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) ->
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _flipper_terrain() -> WorldSpec:
+    w = WorldSpec(width=70, height=1)
+    w.add_from_array("new_object_1", np.full((1, 70), VOXEL_TYPES["FIXED"], dtype=np.int64), 0, 0)
+    return _frozen(w)
+
+
+def flipper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Flipper-v0 (``sim_files/Flipper-v0.json`` + ``evogym/envs/flip.py:20-21``): a 70-wide fixed floor ``new_object_1``, the
+    robot at voxel (60, 1)."""
+    w = _shared(_flipper_terrain())
+    w.add_from_array("robot", robot, 60, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -854,6 +869,7 @@ _TERRAINS = {
     "BridgeWalker-v0": (lambda robot: _bridge_walker_terrain(), (2, 5)),
     "CaveCrawler-v0": (lambda robot: _cave_crawler_terrain(), (1, 2)),
     "Jumper-v0": (lambda robot: _jumper_terrain(), (32, 1)),
+    "Flipper-v0": (lambda robot: _flipper_terrain(), (60, 1)),
     "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
     "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }

@@ -146,6 +146,23 @@ def drop_robot(env):
     r.set_state(pos, np.zeros_like(vel), pos.copy(), np.zeros_like(vt))
 
 
+# Flipper-v0 counts whole turns when the orientation wraps between 0 and 2 pi (flip.py:78-85): before step FLIP_STEP the robot is
+# turned by +0.3 rad about its centre of mass (it sits at about -0.01 rad = 6.27 by then) and lifted clear of the floor
+TWIST_TASKS = ("flipper",)
+
+
+def twist_robot(env, angle=0.3):
+    r = env._sim._r
+    pos, vel, last, vt = r.get_state()
+    info = r.object_info(list(r.object_names).index("robot"))
+    sl = slice(info["min_point"], info["max_point"] + 1)
+    c = pos[sl].mean(axis=0)
+    d = pos[sl] - c
+    ca, sa = np.cos(angle), np.sin(angle)
+    pos[sl] = c + np.stack((ca * d[:, 0] - sa * d[:, 1], sa * d[:, 0] + ca * d[:, 1]), axis=1) + np.array([0.0, 0.12])
+    r.set_state(pos, np.zeros_like(vel), pos.copy(), np.zeros_like(vt))
+
+
 def flip_robot(env):
     r = env._sim._r
     pos, vel, last, vt = r.get_state()
@@ -167,6 +184,7 @@ def main():
     from evogym.envs.traverse import FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
     from evogym.envs.balance import Balance, BalanceJump
+    from evogym.envs.flip import Flipping
     from evogym import sample_robot
 
     tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
@@ -178,7 +196,8 @@ def main():
              "carrier": (CarrySmallRect, "Carrier-v0"), "pusherv1": (PushSmallRectOnOppositeSide, "Pusher-v1"),
              "balancer": (Balance, "Balancer-v0"), "balancerv1": (BalanceJump, "Balancer-v1"),
              "gapjumper": (Gaps, "GapJumper-v0"), "platformjumper": (FloatingPlatform, "PlatformJumper-v0"),
-             "carrierv1": (CarrySmallRectToTable, "Carrier-v1"), "lifter": (LiftSmallRect, "Lifter-v0")}
+             "carrierv1": (CarrySmallRectToTable, "Carrier-v1"), "lifter": (LiftSmallRect, "Lifter-v0"),
+             "flipper": (Flipping, "Flipper-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
@@ -190,7 +209,7 @@ def main():
             body, conn = sample_robot((5, 5))
             rng = np.random.default_rng(500 + seed)
             out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": env_id}
-            if task in FLIP_TASKS or task in DROP_TASKS:
+            if task in FLIP_TASKS or task in DROP_TASKS or task in TWIST_TASKS:
                 out["flip_step"] = np.int32(FLIP_STEP)
             # ---- flat mode
             env = cls(body, conn, mode=None, env_id=env_id)
@@ -204,6 +223,8 @@ def main():
                     flip_robot(env)
                 if task in DROP_TASKS and t == FLIP_STEP:
                     drop_robot(env)
+                if task in TWIST_TASKS and t == FLIP_STEP:
+                    twist_robot(env)
                 # engine state the step starts from (teacher forcing in the GPU test)
                 st = env._sim._r.get_state()
                 for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
@@ -228,6 +249,8 @@ def main():
                     flip_robot(envm)
                 if task in DROP_TASKS and t == FLIP_STEP:
                     drop_robot(envm)
+                if task in TWIST_TASKS and t == FLIP_STEP:
+                    twist_robot(envm)
                 o, r, d, _ = envm.step(vox_acts[t].copy())
                 mod_obs.append(np.asarray(o["modular"], dtype=np.float64)); other_obs.append(np.asarray(o["other"], dtype=np.float64))
                 mrew.append(float(r)); mdone.append(bool(d))
