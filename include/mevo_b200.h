@@ -278,10 +278,14 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_FLIPPER 22                /* Flipping, evogym/envs/flip.py:15-140 (Flipper-v0): reward = change of the robot's unwrapped orientation
                                                (whole turns are counted per environment); done when the centre of mass passes x < 1 voxel;
                                                "other" = [orientation]; flat = [orientation, relative positions] */
+#define MEVO_TASK_BEAM_TOPPLER 23           /* ToppleBeam, manipulate.py:887-1046 (BeamToppler-v0): `package` names the beam; reward from the beam's
+                                               approach, displacement and fall; done + 1 when the beam's centre of mass is left of 2 voxels;
+                                               "other" = [beam - robot com 2, vel com robot 2, vel com beam 2, beam orientation 1] */
+#define MEVO_TASK_BEAM_SLIDER 24            /* SlideBeam, manipulate.py:1049-1204 (BeamSlider-v0): the same observation, reward = approach + advance */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */
-/* package: used by MEVO_TASK_PUSHER / _THROWER / _CARRIER / _CARRIER_V1 / _PUSHER_V1 / _LIFTER only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
+/* package: used by MEVO_TASK_PUSHER / _THROWER / _CARRIER / _CARRIER_V1 / _PUSHER_V1 / _LIFTER / _BEAM_* only (NULL otherwise).  max_episode_steps: 0 = no limit (gym registration: Walker-v0 500). */
 int mevo_batch_task_configure(mevo_batch* b, int task, const char* robot, const char* package, int max_episode_steps);
 /* dims[0..4] = flat observation width, modular observation width (9 x voxels), "other" observation width,
  * largest voxel count of a robot grid, action stride */

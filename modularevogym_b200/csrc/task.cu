@@ -141,6 +141,14 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
         reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
         reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
+    } else if (p.task == 23) {                           // manipulate.py:926-945 (BeamToppler-v0; the "package" is the beam)
+        reward = fabs(pi_x - ri_x) - fabs(pf_x - rf_x);
+        reward += fabs(pf_x - pi_x) * 1.0;
+        reward += fabs(pf_y - pi_y) * 3.0;
+        reward += (pi_y - pf_y) * 10;
+    } else if (p.task == 24) {                           // manipulate.py:1088-1104 (BeamSlider-v0)
+        reward = fabs(pi_x - ri_x) - fabs(pf_x - rf_x);
+        reward += (pf_x - pi_x) * 1.0;
     } else if (p.task == 22) {                           // flip.py:78-90 (Flipper-v0): change of the unwrapped orientation
         const double ort_1 = p.ort_prev[env], ort_2 = (unstable || !p.ort_now) ? ort_1 : p.ort_now[env];
         int n = p.flips[env];
@@ -177,6 +185,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // goal met (walk.py:79-82, 190-193; manipulate.py:390-393; climb.py:107-109, 201-203; traverse.py:120-123, 222-225, 321-324, 420-423)
     if (p.goal_axis == 1 && rf_x > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
     if (p.goal_axis == 2 && rf_y > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
+    if ((p.task == 23 || p.task == 24) && pf_x < 2 * kVoxel) { reward += 1.0; done = true; }   // manipulate.py:942-944, 996-998 (task_complete)
     if (p.task == 22 && rf_x < 1 * kVoxel) done = true;                          // flip.py:97-98: walked off the left end
     if (p.fall_y > 0 && rf_y < p.fall_y) { reward -= 3.0; done = true; }        // traverse.py:609-613, 734-738
     if (p.ort_now && p.task != 22) {
@@ -219,6 +228,8 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else if (p.task == 16 || p.task == 17 || p.task == 22) {   // Balancer, Flipper: the orientation alone, written by the host's launch
         oth[0] = 0.0; oth[1] = 0.0;
+    } else if (p.task == 23 || p.task == 24) {           // get_obs_topple + vel com of robot and beam (base.py:644-650, 696-705); column 6: host
+        oth[0] = P.ax - R.ax; oth[1] = P.ay - R.ay; oth[2] = R.cx * kVoxel; oth[3] = R.cy * kVoxel; oth[4] = P.cx * kVoxel; oth[5] = P.cy * kVoxel;
     } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
         oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
     }
@@ -408,8 +419,8 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 22) throw std::runtime_error("task_configure: unknown task id");
-    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20 || task == 21;
+    if (task < 0 || task > 24) throw std::runtime_error("task_configure: unknown task id");
+    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20 || task == 21 || task == 23 || task == 24;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -432,7 +443,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 16 || T.task == 17 || T.task == 22) ? 1 : T.task == 21 ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 16 || T.task == 17 || T.task == 22) ? 1 : (T.task == 21 || T.task == 23 || T.task == 24) ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1; T.package_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -575,10 +586,10 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task == 18 || T.task == 19;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19 || T.task == 22;   // (22: the reward needs both orientations)
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21  22
-    static const int kGoalAxis[23] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0};
-    static const double kGoal[23] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0,  0};
-    static const double kBonus[23] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21  22  23  24
+    static const int kGoalAxis[25] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0};
+    static const double kGoal[25] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0,  0,  0,  0};
+    static const double kBonus[25] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev; p.flips = T.task == 22 ? T.d_flips : nullptr;
@@ -590,8 +601,9 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     CUDA_CHECK(cudaGetLastError());
-    if (T.task == 21) {
-        // Lifter-v0 (manipulate.py:1278-1283, base.py:684-685): column 6 of "other" and of the flat observation = get_ort_obs("package")
+    if (T.task == 21 || T.task == 23 || T.task == 24) {
+        // Lifter-v0 (manipulate.py:1278-1283, base.py:684-685), BeamToppler-v0 / BeamSlider-v0 (base.py:696-705): column 6 of "other" and of
+        // the flat observation = get_ort_obs of the package / beam
         const size_t el = is_f32 ? sizeof(float) : sizeof(double);
         if (other) {
             if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");

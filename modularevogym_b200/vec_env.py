@@ -18,7 +18,7 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, balancer_v1_world, balancer_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
+from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
                     climber_v1_world, climber_v2_world, climber_world, down_stepper_world, flipper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
                     jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
@@ -32,6 +32,8 @@ TASKS = {
     "Carrier-v0": (14, carrier_world, "package", 500),                        # manipulate.py:83-199, __init__.py:113-117
     "Carrier-v1": (20, carrier_v1_world, "package", 1000),                    # manipulate.py:202-315, __init__.py:119-123
     "Lifter-v0": (21, lifter_world, "package", 300),                          # manipulate.py:1207-1340, __init__.py:107-111
+    "BeamToppler-v0": (23, beam_toppler_world, "beam", 1000),                 # manipulate.py:887-1046, __init__.py:137-141
+    "BeamSlider-v0": (24, beam_slider_world, "beam", 1000),                   # manipulate.py:1049-1204, __init__.py:143-147
     "Pusher-v1": (15, pusher_v1_world, "package", 600),                       # manipulate.py:419-516, __init__.py:131-135
     "Climber-v0": (3, climber_world, None, 400),                              # evogym/envs/climb.py:38-112, __init__.py:187-191
     "ObstacleTraverser-v1": (4, obstacle_traverser_world, None, 1000),        # evogym/envs/traverse.py:350-426, __init__.py:76-80

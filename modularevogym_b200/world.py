@@ -521,6 +521,46 @@ def flipper_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -
     return w
 
 
+# (name, voxel type, w, h, x, y) of the objects of BeamToppler-v0.json / BeamSlider-v0.json (70 x 7) besides the 70 x 1 FIXED "ground"
+BEAM_TOPPLER_OBJECTS = (("beam", "RIGID", 10, 2, 29, 5), ("peg1", "FIXED", 5, 1, 27, 4), ("peg2", "FIXED", 5, 1, 36, 4))
+BEAM_SLIDER_OBJECTS = (("beam", "RIGID", 10, 2, 22, 5), ("peg1", "FIXED", 5, 1, 20, 4), ("peg2", "FIXED", 3, 1, 29, 4),
+                       ("peg3", "FIXED", 3, 1, 35, 4), ("peg4", "FIXED", 3, 1, 41, 4), ("peg5", "FIXED", 3, 1, 49, 4))
+
+
+def _beam_terrain(objects) -> WorldSpec:
+    w = WorldSpec(width=70, height=7)
+    w.add_from_array("ground", np.full((1, 70), VOXEL_TYPES["FIXED"], dtype=np.int64), 0, 0)
+    for name, kind, ow, oh, x, y in objects:
+        w.add_from_array(name, np.full((oh, ow), VOXEL_TYPES[kind], dtype=np.int64), x, y)
+    return _frozen(w)
+
+
+@functools.lru_cache(maxsize=None)
+def _beam_toppler_terrain() -> WorldSpec:
+    return _beam_terrain(BEAM_TOPPLER_OBJECTS)
+
+
+@functools.lru_cache(maxsize=None)
+def _beam_slider_terrain() -> WorldSpec:
+    return _beam_terrain(BEAM_SLIDER_OBJECTS)
+
+
+def beam_toppler_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """BeamToppler-v0 (``sim_files/BeamToppler-v0.json`` + ``evogym/envs/manipulate.py:892-893``): a RIGID 10 x 2 beam resting on two
+    fixed pegs, the robot at voxel (1, 1)."""
+    w = _shared(_beam_toppler_terrain())
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
+def beam_slider_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """BeamSlider-v0 (``sim_files/BeamSlider-v0.json`` + ``manipulate.py:1054-1055``): the beam on the first of a row of pegs, the
+    robot at voxel (1, 1)."""
+    w = _shared(_beam_slider_terrain())
+    w.add_from_array("robot", robot, 1, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -855,6 +895,8 @@ _TERRAINS = {
     "Carrier-v0": (lambda robot: _carrier_terrain(), (1, 1)),
     "Carrier-v1": (lambda robot: _carrier_v1_terrain(), (1, 4)),
     "Lifter-v0": (lambda robot: _lifter_terrain(), (2, 3)),
+    "BeamToppler-v0": (lambda robot: _beam_toppler_terrain(), (1, 1)),
+    "BeamSlider-v0": (lambda robot: _beam_slider_terrain(), (1, 1)),
     "Balancer-v0": (lambda robot: _balancer_terrain(2), (15, 3)),
     "Balancer-v1": (lambda robot: _balancer_terrain(3), (10, 1)),
     "Pusher-v1": (lambda robot: _pusher_v1_terrain(), (13, 1)),

@@ -179,7 +179,7 @@ def main():
     install_stubs()
 
     from evogym.envs.walk import Duck, SoftBridge, WalkingFlat
-    from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, LiftSmallRect, PushSmallRect, PushSmallRectOnOppositeSide, ThrowSmallRect
+    from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, LiftSmallRect, PushSmallRect, SlideBeam, ToppleBeam, PushSmallRectOnOppositeSide, ThrowSmallRect
     from evogym.envs.climb import Climb0, Climb1, Climb2
     from evogym.envs.traverse import FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
@@ -197,7 +197,7 @@ def main():
              "balancer": (Balance, "Balancer-v0"), "balancerv1": (BalanceJump, "Balancer-v1"),
              "gapjumper": (Gaps, "GapJumper-v0"), "platformjumper": (FloatingPlatform, "PlatformJumper-v0"),
              "carrierv1": (CarrySmallRectToTable, "Carrier-v1"), "lifter": (LiftSmallRect, "Lifter-v0"),
-             "flipper": (Flipping, "Flipper-v0")}
+             "flipper": (Flipping, "Flipper-v0"), "beamtoppler": (ToppleBeam, "BeamToppler-v0"), "beamslider": (SlideBeam, "BeamSlider-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():

@@ -83,7 +83,8 @@ BUILDERS = [("Walker-v0", W.walker_world, (1, 1)), ("Pusher-v0", W.pusher_world,
             ("Balancer-v0", W.balancer_world, (15, 3)), ("Balancer-v1", W.balancer_v1_world, (10, 1)),
             ("GapJumper-v0", W.gap_jumper_world, (1, 6)), ("PlatformJumper-v0", W.platform_jumper_world, (1, 6)),
             ("Carrier-v1", W.carrier_v1_world, (1, 4)), ("Lifter-v0", W.lifter_world, (2, 3)),
-            ("Flipper-v0", W.flipper_world, (60, 1))]
+            ("Flipper-v0", W.flipper_world, (60, 1)), ("BeamToppler-v0", W.beam_toppler_world, (1, 1)),
+            ("BeamSlider-v0", W.beam_slider_world, (1, 1))]
 
 
 @pytest.mark.parametrize("env_id,builder,at", BUILDERS)

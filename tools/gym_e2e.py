@@ -105,7 +105,8 @@ def main():
     for env_id in ("Walker-v0", "Pusher-v0", "Thrower-v0", "Climber-v0", "ObstacleTraverser-v1", "BridgeWalker-v0", "ObstacleTraverser-v0", "UpStepper-v0",
                    "DownStepper-v0", "Jumper-v0", "Hurdler-v0", "Climber-v1", "CaveCrawler-v0",
                    "Climber-v2", "Carrier-v0", "Pusher-v1", "Balancer-v0", "Balancer-v1", "GapJumper-v0",
-                   "PlatformJumper-v0", "Carrier-v1", "Lifter-v0", "Flipper-v0"):
+                   "PlatformJumper-v0", "Carrier-v1", "Lifter-v0", "Flipper-v0",
+                   "BeamToppler-v0", "BeamSlider-v0"):
         body, connections = sample_robot((5, 5))
         env = gym.make(env_id, body=body)
         env = gym.make(env_id, body=body, mode="modular", env_id=env_id)
