@@ -282,6 +282,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
                                                approach, displacement and fall; done + 1 when the beam's centre of mass is left of 2 voxels;
                                                "other" = [beam - robot com 2, vel com robot 2, vel com beam 2, beam orientation 1] */
 #define MEVO_TASK_BEAM_SLIDER 24            /* SlideBeam, manipulate.py:1049-1204 (BeamSlider-v0): the same observation, reward = approach + advance */
+#define MEVO_TASK_WINGSPAN 25               /* MaximizeXShape, evogym/envs/change_shape.py:287-385 (WingspanMazimizer-v0, the reference's spelling):
+                                               reward = growth of the robot's extent in x; "other" = [0, 0]; flat = relative positions only */
+#define MEVO_TASK_HEIGHT 26                 /* MaximizeYShape, change_shape.py:388-487 (HeightMaximizer-v0): the same in y */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -78,6 +78,8 @@ struct TaskParams {
     const double* ort_now;
     double* ort_prev;
     int* flips;                          // Flipper-v0: whole turns so far (flip.py:34, 78-85)
+    double* span_prev;                   // Wingspan / Height maximizer: the robot's extent at the last observation
+    int flat_prefix;                     // values in front of the relative positions in the flat observation
 };
 
 struct ObjMeans { double ax, ay, bx, by, cx, cy, dx, dy; };
@@ -104,6 +106,22 @@ __device__ __forceinline__ ObjMeans object_means(const double2* pos, const doubl
         m.ax /= n; m.ay /= n; m.bx /= n; m.by /= n; m.cx /= n; m.cy /= n; m.dx /= n; m.dy /= n;
     }
     return m;
+}
+
+// extent of one object along x (axis 0) or y (axis 1) in the units BenchmarkBase.object_pos_at_time returns
+__device__ __forceinline__ double object_span(const double2* pos, int start, int count, int lane, int axis) {
+    double lo = 1e300, hi = -1e300;
+    for (int i = lane; i < count; i += 32) {
+        const double2 q = pos[start + i];
+        const double v = ((axis ? q.y : q.x) / kVoxel) * kVoxel;
+        lo = fmin(lo, v); hi = fmax(hi, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    return hi - lo;
 }
 
 template <typename OutT>
@@ -141,6 +159,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
         reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
         reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
+    } else if (p.task == 25 || p.task == 26) {           // change_shape.py:354-367, 456-469: growth of the robot's extent in x / y
+        const double span = object_span(pos, te.r_start, te.r_count, lane, p.task == 26);
+        reward = (unstable ? p.span_prev[env] : span) - p.span_prev[env];
     } else if (p.task == 23) {                           // manipulate.py:926-945 (BeamToppler-v0; the "package" is the beam)
         reward = fabs(pi_x - ri_x) - fabs(pf_x - rf_x);
         reward += fabs(pf_x - pi_x) * 1.0;
@@ -214,6 +235,10 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         R = object_means(pos, vel, te.r_start, te.r_count, lane);
         P = object_means(pos, vel, te.p_start, te.p_count, lane);
     }
+    if (p.span_prev) {                                   // of the (possibly reset) state
+        const double span = object_span(pos, te.r_start, te.r_count, lane, p.task == 26);
+        if (lane == 0) p.span_prev[env] = span;
+    }
     if (lane == 0) {
         p.episode_len[env] = ep;
         p.prev[4 * env] = R.ax; p.prev[4 * env + 1] = R.ay; p.prev[4 * env + 2] = P.ax; p.prev[4 * env + 3] = P.ay;
@@ -226,7 +251,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
     if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
-    } else if (p.task == 16 || p.task == 17 || p.task == 22) {   // Balancer, Flipper: the orientation alone, written by the host's launch
+    } else if (p.task == 16 || p.task == 17 || p.task == 22 || p.task == 25 || p.task == 26) {   // Balancer, Flipper: the orientation alone, written by the host's launch; ShapeChange: [0, 0] (base.py:666-667)
         oth[0] = 0.0; oth[1] = 0.0;
     } else if (p.task == 23 || p.task == 24) {           // get_obs_topple + vel com of robot and beam (base.py:644-650, 696-705); column 6: host
         oth[0] = P.ax - R.ax; oth[1] = P.ay - R.ay; oth[2] = R.cx * kVoxel; oth[3] = R.cy * kVoxel; oth[4] = P.cx * kVoxel; oth[5] = P.cy * kVoxel;
@@ -241,14 +266,15 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     }
     if (p.flat) {                                        // walk.py:58-61 / manipulate.py:363-367
         OutT* row = reinterpret_cast<OutT*>(p.flat) + (size_t)env * p.flat_stride;
-        if (lane < ow && lane < p.flat_stride) row[lane] = (OutT)oth[lane < 6 ? lane : 0];
+        const int fp = p.flat_prefix;
+        if (lane < fp && lane < p.flat_stride) row[lane] = (OutT)oth[lane < 6 ? lane : 0];
         const int n = te.r_count;
         for (int i = lane; i < n; i += 32) {             // get_relative_pos_obs (base.py:228-240 * VOXEL_SIZE)
             const double2 q = pos[te.r_start + i];
-            if (ow + i < p.flat_stride) row[ow + i] = (OutT)((q.x / kVoxel - R.bx) * kVoxel);
-            if (ow + n + i < p.flat_stride) row[ow + n + i] = (OutT)((q.y / kVoxel - R.by) * kVoxel);
+            if (fp + i < p.flat_stride) row[fp + i] = (OutT)((q.x / kVoxel - R.bx) * kVoxel);
+            if (fp + n + i < p.flat_stride) row[fp + n + i] = (OutT)((q.y / kVoxel - R.by) * kVoxel);
         }
-        for (int i = ow + 2 * n + lane; i < p.flat_stride; i += 32) row[i] = (OutT)0;
+        for (int i = fp + 2 * n + lane; i < p.flat_stride; i += 32) row[i] = (OutT)0;
     }
     if (p.modular) {                                     // base.py:480-506: 9 values per voxel, non-empty voxels first
         OutT* row = reinterpret_cast<OutT*>(p.modular) + (size_t)env * p.modular_stride;
@@ -374,13 +400,14 @@ struct Batch::Task {
     double* d_ort_now = nullptr;         // orientation rule of tasks 6, 8: after the step / at the last observation
     double* d_ort_prev = nullptr;
     int* d_flips = nullptr;              // Flipper-v0
+    double* d_span_prev = nullptr;       // Wingspan / Height maximizer
     int* d_episode = nullptr;
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -419,7 +446,7 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 24) throw std::runtime_error("task_configure: unknown task id");
+    if (task < 0 || task > 26) throw std::runtime_error("task_configure: unknown task id");
     const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20 || task == 21 || task == 23 || task == 24;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
@@ -443,7 +470,7 @@ void Batch::task_build() {
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
     // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 16 || T.task == 17 || T.task == 22) ? 1 : (T.task == 21 || T.task == 23 || T.task == 24) ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
+    T.other_width = (T.task == 25 || T.task == 26) ? 2 : (T.task == 16 || T.task == 17 || T.task == 22) ? 1 : (T.task == 21 || T.task == 23 || T.task == 24) ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
                     T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
     T.robot_obj = -1; T.package_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
@@ -501,7 +528,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13 || T.task == 18 || T.task == 19) ? 2 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13 || T.task == 18 || T.task == 19) ? 2 : (T.task == 25 || T.task == 26) ? 0 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -519,6 +546,8 @@ void Batch::task_build() {
     CUDA_CHECK(cudaMemset(T.d_ort_prev, 0, sizeof(double) * n));
     CUDA_CHECK(cudaMalloc(&T.d_flips, sizeof(int) * n));
     CUDA_CHECK(cudaMemset(T.d_flips, 0, sizeof(int) * n));
+    CUDA_CHECK(cudaMalloc(&T.d_span_prev, sizeof(double) * n));
+    CUDA_CHECK(cudaMemset(T.d_span_prev, 0, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_episode, 0, sizeof(int) * n));
     T.epoch = finalize_epoch_;
 }
@@ -586,13 +615,15 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task == 18 || T.task == 19;
     const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19 || T.task == 22;   // (22: the reward needs both orientations)
     p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21  22  23  24
-    static const int kGoalAxis[25] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0};
-    static const double kGoal[25] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0,  0,  0,  0};
-    static const double kBonus[25] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0};
+    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21  22  23  24  25  26
+    static const int kGoalAxis[27] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0};
+    static const double kGoal[27] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0};
+    static const double kBonus[27] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0};
     p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
     p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev; p.flips = T.task == 22 ? T.d_flips : nullptr;
+    p.span_prev = (T.task == 25 || T.task == 26) ? T.d_span_prev : nullptr;
+    p.flat_prefix = (T.task == 25 || T.task == 26) ? 0 : p.other_width;
     if (ort_rule && (reward || done)) {
         object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
         p.ort_now = T.d_ort_now;

@@ -20,7 +20,7 @@ import numpy as np
 from . import capi
 from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
                     climber_v1_world, climber_v2_world, climber_world, down_stepper_world, flipper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
-                    jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world,
+                    jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world, shape_change_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
 
 # env id -> (task id of the C ABI, world builder, package object, gym registration's max_episode_steps
@@ -50,6 +50,8 @@ TASKS = {
     "GapJumper-v0": (18, gap_jumper_world, None, 1000),                       # traverse.py:663-782, __init__.py:88-92
     "PlatformJumper-v0": (19, platform_jumper_world, None, 1000),             # traverse.py:539-660, __init__.py:94-98
     "Flipper-v0": (22, flipper_world, None, 600),                             # flip.py:15-140, __init__.py:40-44
+    "WingspanMazimizer-v0": (25, shape_change_world, None, 600),              # change_shape.py:287-385, __init__.py:174-178 (sic)
+    "HeightMaximizer-v0": (26, shape_change_world, None, 500),                # change_shape.py:388-487, __init__.py:180-184
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 

@@ -561,6 +561,24 @@ def beam_slider_world(robot: np.ndarray, connections: Optional[np.ndarray] = Non
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _shape_change_terrain() -> WorldSpec:
+    w = WorldSpec(width=20, height=10)
+    grid = np.zeros((10, 20), dtype=np.int64)
+    grid[9, :] = VOXEL_TYPES["FIXED"]
+    grid[:, 0:2] = grid[:, 18:20] = VOXEL_TYPES["FIXED"]
+    w.add_from_array("new_object_4", grid, 0, 0)
+    return _frozen(w)
+
+
+def shape_change_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """The ShapeChange environments (``sim_files/ShapeChange.json`` + ``evogym/envs/change_shape.py:292-293``): a walled 20 x 10 box
+    ``new_object_4``, the robot at voxel (7, 1)."""
+    w = _shared(_shape_change_terrain())
+    w.add_from_array("robot", robot, 7, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -912,6 +930,8 @@ _TERRAINS = {
     "CaveCrawler-v0": (lambda robot: _cave_crawler_terrain(), (1, 2)),
     "Jumper-v0": (lambda robot: _jumper_terrain(), (32, 1)),
     "Flipper-v0": (lambda robot: _flipper_terrain(), (60, 1)),
+    "WingspanMazimizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
+    "HeightMaximizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
     "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }
