@@ -375,6 +375,69 @@ __global__ void policy_actions_kernel(const InT* a, int in_stride, int per_voxel
     act[idx] = out;
 }
 
+// ---- what distinguishes the tasks on the HOST side (the reward formulas are in task_outputs_kernel, by task id) ----------------------
+struct SightPart { const char* terrain; int dist; bool ceil; int col; };      // terrain: object names separated by ','; nullptr: none
+struct TaskDesc {
+    const char* env;                 // the reference's environment id (documentation)
+    int goal_axis;                   // 0: no goal, 1: robot com x, 2: robot com y beyond `goal` voxels ends the episode with `bonus`
+    double goal, bonus;
+    bool ort_rule;                   // a robot on its back ends the episode with -3 (traverse.py:226-228, 325-327, 514-516, 615-617)
+    double fall_y;                   // > 0: a centre of mass below this height [m] ends the episode with -3
+    bool package;                    // the task has a second object (package / beam)
+    int other_width;                 // width of the "other" observation
+    int kernel_width;                // ... of which the task kernel writes the first values itself; the rest comes from the launches below
+    int flat_prefix;                 // values in front of the relative positions in the flat observation
+    int ort_col;                     // column of an orientation value in "other" (-1: none) ...
+    bool ort_of_package;             // ... of the package instead of the robot ...
+    bool ort_in_flat;                // ... also at the same column of the flat observation
+    SightPart sight[2];              // floor / ceiling sight blocks of "other"
+};
+constexpr const char* kPlatforms5 = "platform_1,platform_2,platform_3,platform_4,platform_5";
+constexpr const char* kPlatforms7 = "platform_1,platform_2,platform_3,platform_4,platform_5,platform_6,platform_7";
+#define MEVO_NO_SIGHT {{nullptr, 0, false, 0}, {nullptr, 0, false, 0}}
+#define MEVO_FLOOR5(names) {{names, 5, false, 3}, {nullptr, 0, false, 0}}
+const TaskDesc kTasks[] = {
+    /*  0 */ {"Walker-v0", 1, 99, 1, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
+    /*  1 */ {"Pusher-v0", 1, 99, 1, false, 0, true, 6, 6, 6, -1, false, false, MEVO_NO_SIGHT},
+    /*  2 */ {"Thrower-v0", 0, 0, 0, false, 0, true, 6, 6, 6, -1, false, false, MEVO_NO_SIGHT},
+    /*  3 */ {"Climber-v0", 2, 86, 1, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
+    /*  4 */ {"ObstacleTraverser-v1", 1, 59, 2, false, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
+    /*  5 */ {"BridgeWalker-v0", 1, 60, 1, false, 0, false, 3, 3, 3, 2, false, true, MEVO_NO_SIGHT},
+    /*  6 */ {"ObstacleTraverser-v0", 1, 79, 2, true, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
+    /*  7 */ {"UpStepper-v0", 1, 69, 2, false, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
+    /*  8 */ {"DownStepper-v0", 1, 74, 2, true, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
+    /*  9 */ {"Jumper-v0", 0, 0, 0, false, 0, false, 7, 2, 2, -1, false, false, {{"ground", 2, false, 2}, {nullptr, 0, false, 0}}},
+    /* 10 */ {"Hurdler-v0", 0, 0, 0, true, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
+    /* 11 */ {"Climber-v1", 2, 65, 1, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
+    /* 12 */ {"CaveCrawler-v0", 1, 69, 1, false, 0, false, 24, 2, 2, -1, false, false, {{"terrain", 5, false, 2}, {"terrain", 5, true, 13}}},
+    /* 13 */ {"Climber-v2", 0, 0, 0, false, 0, false, 10, 2, 2, 2, false, false, {{"pipe", 3, true, 3}, {nullptr, 0, false, 0}}},
+    /* 14 */ {"Carrier-v0", 1, 99, 1, false, 0, true, 6, 6, 6, -1, false, false, MEVO_NO_SIGHT},
+    /* 15 */ {"Pusher-v1", 1, 69, 1, false, 0, true, 6, 6, 6, -1, false, false, MEVO_NO_SIGHT},
+    /* 16 */ {"Balancer-v0", 0, 0, 0, false, 0, false, 1, 1, 1, 0, false, true, MEVO_NO_SIGHT},
+    /* 17 */ {"Balancer-v1", 0, 0, 0, false, 0, false, 1, 1, 1, 0, false, true, MEVO_NO_SIGHT},
+    /* 18 */ {"GapJumper-v0", 0, 0, 0, false, 4 * kVoxel, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5(kPlatforms5)},
+    /* 19 */ {"PlatformJumper-v0", 0, 0, 0, true, 0.4, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5(kPlatforms7)},
+    /* 20 */ {"Carrier-v1", 0, 0, 0, false, 0, true, 6, 6, 6, -1, false, false, MEVO_NO_SIGHT},
+    /* 21 */ {"Lifter-v0", 0, 0, 0, false, 0, true, 7, 7, 7, 6, true, true, MEVO_NO_SIGHT},
+    /* 22 */ {"Flipper-v0", 0, 0, 0, false, 0, false, 1, 1, 1, 0, false, true, MEVO_NO_SIGHT},
+    /* 23 */ {"BeamToppler-v0", 0, 0, 0, false, 0, true, 7, 7, 7, 6, true, true, MEVO_NO_SIGHT},
+    /* 24 */ {"BeamSlider-v0", 0, 0, 0, false, 0, true, 7, 7, 7, 6, true, true, MEVO_NO_SIGHT},
+    /* 25 */ {"WingspanMazimizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
+    /* 26 */ {"HeightMaximizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
+};
+constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
+constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskHeight = 26;
+
+std::vector<std::string> split_names(const char* names) {
+    std::vector<std::string> out;
+    std::string cur;
+    for (const char* c = names; ; c++) {
+        if (*c == ',' || *c == 0) { out.push_back(cur); cur.clear(); if (*c == 0) break; }
+        else cur.push_back(*c);
+    }
+    return out;
+}
+
 }  // namespace
 
 struct Batch::Task {
@@ -446,8 +509,8 @@ int modular_corner_index(const std::vector<int>& body, int h, int w, std::vector
 }
 
 void Batch::task_configure(int task, const std::string& robot, const std::string& package, int max_episode_steps) {
-    if (task < 0 || task > 26) throw std::runtime_error("task_configure: unknown task id");
-    const bool needs_package = task == 1 || task == 2 || task == 14 || task == 15 || task == 20 || task == 21 || task == 23 || task == 24;
+    if (task < 0 || task >= kNumTasks) throw std::runtime_error("task_configure: unknown task id");
+    const bool needs_package = kTasks[task].package;
     if (needs_package && package.empty()) throw std::runtime_error("task_configure: this task needs a package object");
     if (!task_) task_ = new Task();
     task_->task = task;
@@ -469,9 +532,8 @@ void Batch::task_build() {
     T.vox_idx.clear(); T.vox_mat.clear();
     T.act_vox.assign((size_t)n * std::max(1, act_stride_), 0);
     T.index_array.assign(n, {}); T.act_mask.assign(n, {}); T.obs_mask.assign(n, {}); T.corner_size.assign(n, 0);
-    // task 4: vel com 2 + orientation 1 + floor sight 11; task 5: vel com 2 + orientation 1
-    T.other_width = (T.task == 25 || T.task == 26) ? 2 : (T.task == 16 || T.task == 17 || T.task == 22) ? 1 : (T.task == 21 || T.task == 23 || T.task == 24) ? 7 : (T.task == 18 || T.task == 19) ? 14 : (T.task == 1 || T.task == 2 || T.task >= 14) ? 6 : (T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10) ? 14 : T.task == 5 ? 3 :
-                    T.task == 9 ? 7 : T.task == 12 ? 24 : T.task == 13 ? 10 : 2;
+    const TaskDesc& D = kTasks[T.task];
+    T.other_width = D.other_width;
     T.robot_obj = -1; T.package_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
     for (int e = 0; e < n; e++) {
@@ -528,7 +590,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, ((T.task == 4 || (T.task >= 6 && T.task <= 10) || T.task == 12 || T.task == 13 || T.task == 18 || T.task == 19) ? 2 : (T.task == 25 || T.task == 26) ? 0 : T.other_width) + 2 * r.r_count);   // sight tasks: [vel com, positions]
+        T.flat_width = std::max(T.flat_width, D.flat_prefix + 2 * r.r_count);
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -612,19 +674,19 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;
-    const bool stairs = T.task == 4 || (T.task >= 6 && T.task <= 8) || T.task == 10 || T.task == 18 || T.task == 19;
-    const bool ort_rule = T.task == 6 || T.task == 8 || T.task == 10 || T.task == 19 || T.task == 22;   // (22: the reward needs both orientations)
-    p.other_width = (stairs || T.task == 9 || T.task == 12 || T.task == 13) ? 2 : T.other_width;   // sight tasks: the kernel writes the velocity, the rest is filled below
-    //                         task:  0   1   2   3   4   5   6   7   8   9  10  11  12  13  14  15  16  17  18  19  20  21  22  23  24  25  26
-    static const int kGoalAxis[27] = {1,  1,  0,  2,  1,  1,  1,  1,  1,  0,  0,  2,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0};
-    static const double kGoal[27] = {99, 99,  0, 86, 59, 60, 79, 69, 74,  0,  0, 65, 69,  0, 99, 69,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0};
-    static const double kBonus[27] = {1,  1,  0,  1,  2,  1,  2,  2,  2,  0,  0,  1,  1,  0,  1,  1,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0,  0};
-    p.goal_axis = kGoalAxis[T.task]; p.goal = kGoal[T.task]; p.goal_bonus = kBonus[T.task];
-    p.fall_y = T.task == 18 ? 4 * kVoxel : T.task == 19 ? 0.4 : 0.0;            // GapJumper-v0, PlatformJumper-v0
-    p.ort_now = nullptr; p.ort_prev = T.d_ort_prev; p.flips = T.task == 22 ? T.d_flips : nullptr;
-    p.span_prev = (T.task == 25 || T.task == 26) ? T.d_span_prev : nullptr;
-    p.flat_prefix = (T.task == 25 || T.task == 26) ? 0 : p.other_width;
-    if (ort_rule && (reward || done)) {
+    const TaskDesc& D = kTasks[T.task];
+    const bool ort_pair = D.ort_rule || T.task == kTaskFlipper;        // the kernel needs the orientation after the step and at the last observation
+    p.other_width = D.kernel_width;
+    p.flat_prefix = D.flat_prefix;
+    p.goal_axis = D.goal_axis; p.goal = D.goal; p.goal_bonus = D.bonus;
+    p.fall_y = D.fall_y;
+    p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
+    p.flips = T.task == kTaskFlipper ? T.d_flips : nullptr;
+    p.span_prev = (T.task == kTaskWingspan || T.task == kTaskHeight) ? T.d_span_prev : nullptr;
+    if (other && other_stride < D.other_width)
+        throw std::runtime_error("task_outputs: the 'other' observation of this task is " + std::to_string(D.other_width) + " wide");
+    if (flat && flat_stride < D.flat_prefix) throw std::runtime_error("task_outputs: the flat observation is narrower than its fixed part");
+    if (ort_pair && (reward || done)) {
         object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
         p.ort_now = T.d_ort_now;
     }
@@ -632,68 +694,19 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     if (is_f32) task_outputs_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     else task_outputs_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(p);
     CUDA_CHECK(cudaGetLastError());
-    if (T.task == 21 || T.task == 23 || T.task == 24) {
-        // Lifter-v0 (manipulate.py:1278-1283, base.py:684-685), BeamToppler-v0 / BeamSlider-v0 (base.py:696-705): column 6 of "other" and of
-        // the flat observation = get_ort_obs of the package / beam
-        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
-        if (other) {
-            if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");
-            object_orientation_strided_device(T.package_obj, static_cast<char*>(other) + 6 * el, other_stride, is_f32);
-        }
-        if (flat) {
-            if (flat_stride < 7) throw std::runtime_error("task_outputs: the flat observation of this task is at least 7 wide");
-            object_orientation_strided_device(T.package_obj, static_cast<char*>(flat) + 6 * el, flat_stride, is_f32);
-        }
+    // what the kernel left open in "other" (and the flat observation), on the (possibly reset) state: get_ort_obs (base.py:258-267),
+    // get_floor_obs / get_ceil_obs (base.py:269-372) as get_other_obs lays them out (base.py:652-744)
+    const size_t el = is_f32 ? sizeof(float) : sizeof(double);
+    if (D.ort_col >= 0) {
+        const int obj = D.ort_of_package ? T.package_obj : T.robot_obj;
+        if (other) object_orientation_strided_device(obj, static_cast<char*>(other) + D.ort_col * el, other_stride, is_f32);
+        if (flat && D.ort_in_flat) object_orientation_strided_device(obj, static_cast<char*>(flat) + D.ort_col * el, flat_stride, is_f32);
     }
-    if (T.task == 16 || T.task == 17 || T.task == 22) {
-        // Flipper-v0 (flip.py:63-66) and Balancer-v0 / -v1 (balance.py:72-78, base.py:664-665): "other" = [orientation]; flat = [orientation, relative positions]
-        if (other) object_orientation_strided_device(T.robot_obj, other, other_stride, is_f32);
-        if (flat) object_orientation_strided_device(T.robot_obj, flat, flat_stride, is_f32);
-    }
-    if (T.task == 5) {
-        // BridgeWalker-v0 (walk.py:161-165, base.py:656-657): column 2 of "other" and of the flat observation = get_ort_obs("robot")
-        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
-        if (other) {
-            if (other_stride < 3) throw std::runtime_error("task_outputs: the 'other' observation of this task is 3 wide");
-            object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
-        }
-        if (flat) {
-            if (flat_stride < 3) throw std::runtime_error("task_outputs: the flat observation of this task is at least 3 wide");
-            object_orientation_strided_device(T.robot_obj, static_cast<char*>(flat) + 2 * el, flat_stride, is_f32);
-        }
-    }
-    if (ort_rule) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);   // of the (possibly reset) state
-    if (T.task == 12 && other) {
-        // CaveCrawler-v0 (base.py:658-663): [vel com, get_floor_obs("robot", ["terrain"], 5), get_ceil_obs("robot", ["terrain"], 5)]
-        if (other_stride < 24) throw std::runtime_error("task_outputs: the 'other' observation of this task is 24 wide");
-        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
-        sight_obs_strided_device(T.robot_obj, {"terrain"}, 5, 5.0, false, static_cast<char*>(other) + 2 * el, 11, other_stride, is_f32);
-        sight_obs_strided_device(T.robot_obj, {"terrain"}, 5, 5.0, true, static_cast<char*>(other) + 13 * el, 11, other_stride, is_f32);
-    }
-    if (T.task == 13 && other) {
-        // Climber-v2 (base.py:668-673): [vel com, get_ort_obs("robot"), get_ceil_obs("robot", ["pipe"], 3)]
-        if (other_stride < 10) throw std::runtime_error("task_outputs: the 'other' observation of this task is 10 wide");
-        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
-        object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
-        sight_obs_strided_device(T.robot_obj, {"pipe"}, 3, 5.0, true, static_cast<char*>(other) + 3 * el, 7, other_stride, is_f32);
-    }
-    if (T.task == 9 && other) {
-        // Jumper-v0 (base.py:676-680): [vel com, get_floor_obs("robot", ["ground"], 2)]
-        if (other_stride < 7) throw std::runtime_error("task_outputs: the 'other' observation of this task is 7 wide");
-        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
-        sight_obs_strided_device(T.robot_obj, {"ground"}, 2, 5.0, false, static_cast<char*>(other) + 2 * el, 5, other_stride, is_f32);
-    }
-    if (stairs && other) {
-        // ObstacleTraverser-v0 / -v1, UpStepper-v0, DownStepper-v0 (get_other_obs, base.py:706-714): [vel com, orientation, get_floor_obs("robot", ["ground"], 5)]
-        if (other_stride < 14) throw std::runtime_error("task_outputs: the 'other' observation of this task is 14 wide");
-        const size_t el = is_f32 ? sizeof(float) : sizeof(double);
-        object_orientation_strided_device(T.robot_obj, static_cast<char*>(other) + 2 * el, other_stride, is_f32);
-        static const std::vector<std::string> kGround = {"ground"};
-        static const std::vector<std::string> kGaps = {"platform_1", "platform_2", "platform_3", "platform_4", "platform_5"};
-        static const std::vector<std::string> kPlatforms = {"platform_1", "platform_2", "platform_3", "platform_4", "platform_5", "platform_6", "platform_7"};
-        const std::vector<std::string>& terrain = T.task == 18 ? kGaps : T.task == 19 ? kPlatforms : kGround;     // traverse.py:683, 562
-        sight_obs_strided_device(T.robot_obj, terrain, 5, 5.0, false, static_cast<char*>(other) + 3 * el, 11, other_stride, is_f32);
-    }
+    if (ort_pair) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);
+    for (const SightPart& sp : D.sight)
+        if (sp.terrain && other)
+            sight_obs_strided_device(T.robot_obj, split_names(sp.terrain), sp.dist, 5.0, sp.ceil, static_cast<char*>(other) + sp.col * el,
+                                     2 * sp.dist + 1, other_stride, is_f32);
     if (reset_done) for (auto& e : envs_) e.host_fresh = false;
 }
 
