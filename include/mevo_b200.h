@@ -285,6 +285,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_WINGSPAN 25               /* MaximizeXShape, evogym/envs/change_shape.py:287-385 (WingspanMazimizer-v0, the reference's spelling):
                                                reward = growth of the robot's extent in x; "other" = [0, 0]; flat = relative positions only */
 #define MEVO_TASK_HEIGHT 26                 /* MaximizeYShape, change_shape.py:388-487 (HeightMaximizer-v0): the same in y */
+#define MEVO_TASK_AREA_MAX 27               /* MaximizeShape, change_shape.py:85-183 (AreaMaximizer-v0): reward = 10 x growth of the signed area of the
+                                               robot's convex hull, computed by the reference's own gift wrapping (one lane per environment) */
+#define MEVO_TASK_AREA_MIN 28               /* MinimizeShape, change_shape.py:186-284 (AreaMinimizer-v0): 10 x its shrinkage */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -124,6 +124,34 @@ __device__ __forceinline__ double object_span(const double2* pos, int start, int
     return hi - lo;
 }
 
+// Signed area of the convex hull of one object's points as ShapeBase computes it (evogym/envs/change_shape.py:45-82): the gift
+// wrapping there is restated statement for statement -- start at the first point of smallest x, `>=` in the turn test, the running
+// `endpoint` scan in point order, the shoelace sum in hull order without an absolute value -- because its sign and its choice among
+// collinear points follow from exactly that order.  Sequential by nature: one lane per environment.
+__device__ double hull_area_signed(const double2* pos, int start, int count) {
+    auto pt = [&](int j) { const double2 q = pos[start + j]; return make_double2((q.x / kVoxel) * kVoxel, (q.y / kVoxel) * kVoxel); };
+    if (count <= 0) return 0.0;
+    int first = 0;
+    double min_x = pt(0).x;
+    for (int j = 1; j < count; j++) { const double x = pt(j).x; if (x < min_x) { min_x = x; first = j; } }
+    const double2 p0 = pt(first);
+    double2 on_hull = p0;
+    double area = 0.0;
+    for (int i = 0; i < count; i++) {                    // (the reference's list has `count` slots)
+        double2 endpoint = pt(0);
+        for (int j = 1; j < count; j++) {
+            const double2 sj = pt(j);
+            // CCW(p1 = S[j], p2 = P[i], p3 = endpoint)
+            const bool ccw = (endpoint.y - sj.y) * (on_hull.x - sj.x) >= (on_hull.y - sj.y) * (endpoint.x - sj.x);
+            if ((endpoint.x == on_hull.x && endpoint.y == on_hull.y) || !ccw) endpoint = sj;
+        }
+        area += (on_hull.x * endpoint.y - endpoint.x * on_hull.y);
+        on_hull = endpoint;
+        if (endpoint.x == p0.x && endpoint.y == p0.y) break;
+    }
+    return 0.5 * area;
+}
+
 template <typename OutT>
 __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -159,6 +187,12 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     } else if (p.task == 17) {                           // balance.py:171-177 (Balancer-v1)
         reward = fabs(17.5 * kVoxel - ri_x) - fabs(17.5 * kVoxel - rf_x);
         reward += (fabs(6 * kVoxel - ri_y) - fabs(6 * kVoxel - rf_y));
+    } else if (p.task == 27 || p.task == 28) {           // change_shape.py:152-164, 253-265: growth / shrinkage of the convex hull's area
+        double area = 0.0;
+        if (lane == 0) area = hull_area_signed(pos, te.r_start, te.r_count);
+        area = __shfl_sync(0xffffffffu, area, 0);
+        const double area_final = unstable ? p.span_prev[env] : area;
+        reward = p.task == 27 ? (area_final - p.span_prev[env]) * 10 : (p.span_prev[env] - area_final) * 10;
     } else if (p.task == 25 || p.task == 26) {           // change_shape.py:354-367, 456-469: growth of the robot's extent in x / y
         const double span = object_span(pos, te.r_start, te.r_count, lane, p.task == 26);
         reward = (unstable ? p.span_prev[env] : span) - p.span_prev[env];
@@ -235,9 +269,13 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         R = object_means(pos, vel, te.r_start, te.r_count, lane);
         P = object_means(pos, vel, te.p_start, te.p_count, lane);
     }
-    if (p.span_prev) {                                   // of the (possibly reset) state
-        const double span = object_span(pos, te.r_start, te.r_count, lane, p.task == 26);
-        if (lane == 0) p.span_prev[env] = span;
+    if (p.span_prev) {                                   // the shape measure of the (possibly reset) state
+        if (p.task >= 27) {
+            if (lane == 0) p.span_prev[env] = hull_area_signed(pos, te.r_start, te.r_count);
+        } else {
+            const double span = object_span(pos, te.r_start, te.r_count, lane, p.task == 26);
+            if (lane == 0) p.span_prev[env] = span;
+        }
     }
     if (lane == 0) {
         p.episode_len[env] = ep;
@@ -251,7 +289,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
     if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
-    } else if (p.task == 16 || p.task == 17 || p.task == 22 || p.task == 25 || p.task == 26) {   // Balancer, Flipper: the orientation alone, written by the host's launch; ShapeChange: [0, 0] (base.py:666-667)
+    } else if (p.task == 16 || p.task == 17 || p.task == 22 || p.task >= 25) {   // Balancer, Flipper: the orientation alone, written by the host's launch; ShapeChange: [0, 0] (base.py:666-667)
         oth[0] = 0.0; oth[1] = 0.0;
     } else if (p.task == 23 || p.task == 24) {           // get_obs_topple + vel com of robot and beam (base.py:644-650, 696-705); column 6: host
         oth[0] = P.ax - R.ax; oth[1] = P.ay - R.ay; oth[2] = R.cx * kVoxel; oth[3] = R.cy * kVoxel; oth[4] = P.cx * kVoxel; oth[5] = P.cy * kVoxel;
@@ -424,9 +462,11 @@ const TaskDesc kTasks[] = {
     /* 24 */ {"BeamSlider-v0", 0, 0, 0, false, 0, true, 7, 7, 7, 6, true, true, MEVO_NO_SIGHT},
     /* 25 */ {"WingspanMazimizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
     /* 26 */ {"HeightMaximizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
+    /* 27 */ {"AreaMaximizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
+    /* 28 */ {"AreaMinimizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
 };
 constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
-constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskHeight = 26;
+constexpr int kTaskFlipper = 22, kTaskWingspan = 25;
 
 std::vector<std::string> split_names(const char* names) {
     std::vector<std::string> out;
@@ -682,7 +722,7 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.fall_y = D.fall_y;
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     p.flips = T.task == kTaskFlipper ? T.d_flips : nullptr;
-    p.span_prev = (T.task == kTaskWingspan || T.task == kTaskHeight) ? T.d_span_prev : nullptr;
+    p.span_prev = T.task >= kTaskWingspan ? T.d_span_prev : nullptr;          // the ShapeChange tasks (25 ... 28)
     if (other && other_stride < D.other_width)
         throw std::runtime_error("task_outputs: the 'other' observation of this task is " + std::to_string(D.other_width) + " wide");
     if (flat && flat_stride < D.flat_prefix) throw std::runtime_error("task_outputs: the flat observation is narrower than its fixed part");

@@ -52,6 +52,8 @@ TASKS = {
     "Flipper-v0": (22, flipper_world, None, 600),                             # flip.py:15-140, __init__.py:40-44
     "WingspanMazimizer-v0": (25, shape_change_world, None, 600),              # change_shape.py:287-385, __init__.py:174-178 (sic)
     "HeightMaximizer-v0": (26, shape_change_world, None, 500),                # change_shape.py:388-487, __init__.py:180-184
+    "AreaMaximizer-v0": (27, shape_change_world, None, 600),                  # change_shape.py:85-183, __init__.py:162-166
+    "AreaMinimizer-v0": (28, shape_change_world, None, 600),                  # change_shape.py:186-284, __init__.py:168-172
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 

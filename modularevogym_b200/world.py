@@ -932,6 +932,8 @@ _TERRAINS = {
     "Flipper-v0": (lambda robot: _flipper_terrain(), (60, 1)),
     "WingspanMazimizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "HeightMaximizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
+    "AreaMaximizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
+    "AreaMinimizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
     "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }

@@ -185,7 +185,7 @@ def main():
     from evogym.envs.jump import StationaryJump
     from evogym.envs.balance import Balance, BalanceJump
     from evogym.envs.flip import Flipping
-    from evogym.envs.change_shape import MaximizeXShape, MaximizeYShape
+    from evogym.envs.change_shape import MaximizeShape, MaximizeXShape, MaximizeYShape, MinimizeShape
     from evogym import sample_robot
 
     tasks = {"walker": (WalkingFlat, "Walker-v0"), "pusher": (PushSmallRect, "Pusher-v0"), "thrower": (ThrowSmallRect, "Thrower-v0"),
@@ -199,7 +199,8 @@ def main():
              "gapjumper": (Gaps, "GapJumper-v0"), "platformjumper": (FloatingPlatform, "PlatformJumper-v0"),
              "carrierv1": (CarrySmallRectToTable, "Carrier-v1"), "lifter": (LiftSmallRect, "Lifter-v0"),
              "flipper": (Flipping, "Flipper-v0"), "beamtoppler": (ToppleBeam, "BeamToppler-v0"), "beamslider": (SlideBeam, "BeamSlider-v0"),
-             "wingspan": (MaximizeXShape, "WingspanMazimizer-v0"), "height": (MaximizeYShape, "HeightMaximizer-v0")}
+             "wingspan": (MaximizeXShape, "WingspanMazimizer-v0"), "height": (MaximizeYShape, "HeightMaximizer-v0"),
+             "areamax": (MaximizeShape, "AreaMaximizer-v0"), "areamin": (MinimizeShape, "AreaMinimizer-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
