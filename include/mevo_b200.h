@@ -288,6 +288,9 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_AREA_MAX 27               /* MaximizeShape, change_shape.py:85-183 (AreaMaximizer-v0): reward = 10 x growth of the signed area of the
                                                robot's convex hull, computed by the reference's own gift wrapping (one lane per environment) */
 #define MEVO_TASK_AREA_MIN 28               /* MinimizeShape, change_shape.py:186-284 (AreaMinimizer-v0): 10 x its shrinkage */
+#define MEVO_TASK_BIDIRECTIONAL_WALKER 29   /* BiWalk, multi_goal.py:91-205 (BidirectionalWalker-v0): walk to a list of x positions in turn; the reward is the
+                                               approach to the current goal (+1 after the last), the flat observation ends with [goal index, x goal,
+                                               x goal - com x].  The reference has no modular mode for it; goal lists: mevo_batch_task_set_goals */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */
@@ -322,6 +325,19 @@ int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* 
                           int other_stride);
 int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
                                  int other_stride, int is_f32);
+
+/* BidirectionalWalker-v0 (evogym/envs/multi_goal.py:91-205, task 29): each environment walks to a list of x positions in turn
+ * (WalkToX, multi_goal.py:62-88).  The reference draws a new list in __init__ and in every reset() from Python's global `random`
+ * (set_random_goals(20, 50, 100), multi_goal.py:115-129).  Here every environment gets a list when the task tables are built and a
+ * new one whenever mevo_batch_task_outputs(reset_done = 1) restarts its episode, drawn on the device by the same rule from a
+ * counter-based generator (identically distributed lists, not Python's stream); mevo_batch_task_reset keeps the lists and returns
+ * to their first goal, so a host that wants its own lists (or Python's stream) sets them before it resets.
+ *   set_goals: `goals` holds `stride` ints per environment, the first counts[i] (1 ... 61) are that environment's x goals in voxels
+ *   draw_goals: new lists for all environments from `seed` (also the seed of later device draws)
+ *   get_goals: list of one environment (at most `cap` values), its length and the index of the current goal */
+int mevo_batch_task_set_goals(mevo_batch* b, int env_first, int n_envs, const int* counts, const int* goals, int stride);
+int mevo_batch_task_draw_goals(mevo_batch* b, unsigned long long seed);
+int mevo_batch_task_get_goals(mevo_batch* b, int env, int* count, int* current, int* goals, int cap);
 
 /* ---- headless rasteriser ------------------------------------------------------------------------------- */
 /* Interface::render (SimulatorCPP/Interface.cpp:55-135: background, voxel grid lines, one quad per voxel coloured by cell

@@ -95,6 +95,9 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_task_outputs": (_i, [_vp, _dp, _bp, _dp, _i, _dp, _i, _dp, _i, _i]),
     "mevo_batch_task_outputs_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i]),
     "mevo_batch_task_reset": (_i, [_vp, _dp, _i, _dp, _i, _dp, _i]),
+    "mevo_batch_task_set_goals": (_i, [_vp, _i, _i, _ip, _ip, _i]),
+    "mevo_batch_task_draw_goals": (_i, [_vp, C.c_ulonglong]),
+    "mevo_batch_task_get_goals": (_i, [_vp, _i, _ip, _ip, _ip, _i]),
     "mevo_batch_task_reset_device": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i]),
     "mevo_env_render": (_i, [_vp, _i, _d, _d, _d, _d, _i, _i, _i, _bp]),
     "mevo_env_render_device": (_i, [_vp, _i, _d, _d, _d, _d, _i, _i, _i, _vp]),
@@ -119,7 +122,7 @@ MEVO_TASK_HURDLER, MEVO_TASK_CLIMBER_V1, MEVO_TASK_CAVE_CRAWLER, MEVO_TASK_CLIMB
 MEVO_TASK_CARRIER, MEVO_TASK_PUSHER_V1, MEVO_TASK_BALANCER, MEVO_TASK_BALANCER_V1 = 14, 15, 16, 17
 MEVO_TASK_GAP_JUMPER, MEVO_TASK_PLATFORM_JUMPER, MEVO_TASK_CARRIER_V1, MEVO_TASK_LIFTER, MEVO_TASK_FLIPPER = 18, 19, 20, 21, 22
 MEVO_TASK_BEAM_TOPPLER, MEVO_TASK_BEAM_SLIDER, MEVO_TASK_WINGSPAN, MEVO_TASK_HEIGHT = 23, 24, 25, 26
-MEVO_TASK_AREA_MAX, MEVO_TASK_AREA_MIN = 27, 28
+MEVO_TASK_AREA_MAX, MEVO_TASK_AREA_MIN, MEVO_TASK_BIDIRECTIONAL_WALKER = 27, 28, 29
 MEVO_DONE, MEVO_DONE_TRUNCATED, MEVO_DONE_UNSTABLE = 1, 2, 4      # done byte bits (include/mevo_b200.h)
 
 _lib = None
@@ -553,6 +556,26 @@ class Batch:
         vp = lambda p: C.c_void_p(p) if p else None
         _check(self.L.mevo_batch_task_reset_device(self.h, vp(flat_ptr), int(flat_stride), vp(modular_ptr), int(modular_stride),
                                                    vp(other_ptr), int(other_stride), int(is_f32)))
+
+    def task_set_goals(self, goals, env_first: int = 0) -> None:
+        """BidirectionalWalker-v0: ``goals`` is one sequence of x positions (voxels) per environment, starting at ``env_first``
+        (the arguments of the reference's ``WalkToX`` goals, multi_goal.py:62-71); the current goal of those environments is the first."""
+        counts = np.asarray([len(g) for g in goals], dtype=np.int32)
+        stride = max(1, int(counts.max()) if counts.size else 1)
+        table = np.zeros((len(goals), stride), dtype=np.int32)
+        for i, g in enumerate(goals):
+            table[i, :len(g)] = np.asarray(g, dtype=np.int32)
+        _check(self.L.mevo_batch_task_set_goals(self.h, int(env_first), len(goals), _iptr(counts), _iptr(table), stride))
+
+    def task_draw_goals(self, seed: int) -> None:
+        """new goal lists for all environments, drawn on the device (set_random_goals(20, 50, 100), multi_goal.py:115-129)"""
+        _check(self.L.mevo_batch_task_draw_goals(self.h, int(seed) & 0xFFFFFFFFFFFFFFFF))
+
+    def task_get_goals(self, env: int) -> dict:
+        count, current = C.c_int(0), C.c_int(0)
+        buf = np.zeros(64, dtype=np.int32)
+        _check(self.L.mevo_batch_task_get_goals(self.h, int(env), C.byref(count), C.byref(current), _iptr(buf), 64))
+        return {"goals": buf[:count.value].copy(), "current": current.value}
 
     def render(self, env: int, cam_pos, cam_size, resolution, hide_background=False, hide_grid=False, hide_edges=False,
                hide_boxels=False) -> np.ndarray:

@@ -589,6 +589,30 @@ int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, voi
     });
 }
 
+int mevo_batch_task_set_goals(mevo_batch* b, int env_first, int n_envs, const int* counts, const int* goals, int stride) {
+    return guard([&] {
+        if (n_envs > 0 && (!counts || !goals)) throw std::runtime_error("mevo_batch_task_set_goals: null argument");
+        b->impl.task_set_goals(env_first, n_envs, counts, goals, stride);
+        return 0;
+    });
+}
+
+int mevo_batch_task_draw_goals(mevo_batch* b, unsigned long long seed) {
+    return guard([&] {
+        b->impl.task_draw_goals(seed);
+        return 0;
+    });
+}
+
+int mevo_batch_task_get_goals(mevo_batch* b, int env, int* count, int* current, int* goals, int cap) {
+    return guard([&] {
+        if (!count || !current || (cap > 0 && !goals)) throw std::runtime_error("mevo_batch_task_get_goals: null argument");
+        const int r = b->impl.task_get_goals(env, goals, cap);
+        *count = r & 0xffff; *current = r >> 16;
+        return 0;
+    });
+}
+
 int mevo_env_render(mevo_batch* b, int env, double cam_x, double cam_y, double cam_w, double cam_h, int res_w, int res_h, int flags,
                     unsigned char* out) {
     return guard([&] {

@@ -134,6 +134,10 @@ public:
                       double* other, int other_stride, bool reset_done);
     void task_reset_device(void* flat, int flat_stride, void* modular, int modular_stride, void* other, int other_stride, bool is_f32);
     void task_reset(double* flat, int flat_stride, double* modular, int modular_stride, double* other, int other_stride);
+    // BidirectionalWalker-v0 (multi_goal.py:91-205): per-environment goal lists -- from the host, or drawn on the device
+    void task_set_goals(int env_first, int n_envs, const int* counts, const int* goals, int stride);
+    void task_draw_goals(unsigned long long seed);
+    int task_get_goals(int env, int* out, int cap);      // returns count | current << 16
 
     // get_floor_obs / get_ceil_obs (evogym/envs/base.py:269-372) of object `obj_index` against the named terrain objects
     void sight_obs_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,

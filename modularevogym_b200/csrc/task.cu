@@ -80,7 +80,36 @@ struct TaskParams {
     int* flips;                          // Flipper-v0: whole turns so far (flip.py:34, 78-85)
     double* span_prev;                   // Wingspan / Height maximizer: the robot's extent at the last observation
     int flat_prefix;                     // values in front of the relative positions in the flat observation
+    // BidirectionalWalker-v0 (multi_goal.py:21-205): per environment kGoalStride ints -- [0] number of goals, [1] index of the current
+    // goal, [2] lists drawn on the device so far, [3 ...] the goals' x positions in voxels
+    int* goals;
+    unsigned long long goal_seed;
 };
+
+constexpr int kGoalStride = 64, kMaxGoals = kGoalStride - 3;
+
+// BiWalk.set_random_goals(20, 50, 100) (multi_goal.py:115-129) for an episode the DEVICE starts (the vec-env's reset of a finished
+// episode): positions uniform in [20, 50) until the path from voxel 35 through them is at least 100 voxels long.  The reference
+// draws from Python's global, unseeded `random`; here a counter-based generator keyed on (seed, environment, list number) gives
+// identically distributed lists -- hosts that want Python's stream hand their own lists over with mevo_batch_task_set_goals.
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long& x) {
+    unsigned long long z = (x += 0x9e3779b97f4a7c15ull);
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+__device__ void draw_goals(int* g, int env, unsigned long long seed) {
+    unsigned long long x = seed ^ (0xd1342543de82ef95ull * (unsigned long long)(env + 1)) ^ (0x2545f4914f6cdd1dull * (unsigned long long)(g[2] + 1));
+    g[2] += 1;
+    int curr = 35, dist = 0, n = 0;
+    while (dist < 100 && n < kMaxGoals) {
+        const int next = 20 + (int)__umul64hi(splitmix64(x), 30ull);
+        dist += abs(curr - next);
+        curr = next;
+        g[3 + n++] = next;
+    }
+    g[0] = n; g[1] = 0;
+}
 
 struct ObjMeans { double ax, ay, bx, by, cx, cy, dx, dy; };
 
@@ -173,7 +202,27 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
 
     double reward;
     bool done = unstable;
-    if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
+    int goal_shown = 0;                                  // BidirectionalWalker-v0: the goal index the observation reports
+    bool goals_done = false;
+    if (p.task == 29) {                                  // multi_goal.py:41-58, 73-84 (GoalBase.get_reward over WalkToX.evaluate)
+        int* g = p.goals + (size_t)env * kGoalStride;
+        const int count = g[0];
+        int cur = g[1];
+        goal_shown = cur < count ? cur : count - 1;      // BiWalk.step builds the observation BEFORE get_reward moves on (:143-157)
+        reward = 0;
+        if (p.reward || p.done) {
+            bool reached = true;
+            while (reached && cur != count) {
+                const double gx = g[3 + cur] * 0.1;
+                reward = fabs(gx - ri_x) - fabs(gx - rf_x);
+                reached = fabs(gx - rf_x) < 2 * 0.1;     // within two voxels: on to the next goal, evaluated on the same step
+                if (reached) cur += 1;
+            }
+            goals_done = cur == count;
+            __syncwarp();
+            if (lane == 0) g[1] = cur;
+        }
+    } else if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3 || p.task == 11) {            // climb.py:96-99, 190-193
         reward = rf_y - ri_y;
@@ -237,6 +286,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         reward = pf_x - pi_x + motion_penalty;
     }
     if (unstable) reward -= 3.0;
+    if (goals_done) { done = true; reward += 1.0; }      // multi_goal.py:171-173
     // goal met (walk.py:79-82, 190-193; manipulate.py:390-393; climb.py:107-109, 201-203; traverse.py:120-123, 222-225, 321-324, 420-423)
     if (p.goal_axis == 1 && rf_x > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
     if (p.goal_axis == 2 && rf_y > p.goal * kVoxel) { done = true; reward += p.goal_bonus; }
@@ -250,6 +300,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     }
     if (p.task == 5 && rf_x > 60 * kVoxel) { done = true; reward += 1.0; }        // walk.py:190-193
     int flags = (done ? 1 : 0) | (unstable ? 4 : 0);
+    bool was_reset = false;
     int ep = p.episode_len[env] + 1;
     if (p.max_episode_steps > 0 && ep >= p.max_episode_steps) {   // gym TimeLimit: truncated = not already done
         if (!done) flags |= 2;
@@ -265,6 +316,12 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         }
         __syncwarp();
         if (lane == 0) { p.sim_time[env] = 0; p.unstable[env] = 0; if (p.flips) p.flips[env] = 0; }
+        if (p.task == 29) {                              // BiWalk.reset (multi_goal.py:178-184): first goal of a new list
+            if (lane == 0) draw_goals(p.goals + (size_t)env * kGoalStride, env, p.goal_seed);
+            __syncwarp();
+            goal_shown = 0;
+        }
+        was_reset = true;
         ep = 0;
         R = object_means(pos, vel, te.r_start, te.r_count, lane);
         P = object_means(pos, vel, te.p_start, te.p_count, lane);
@@ -289,6 +346,8 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
     if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
+    } else if (p.task == 29) {                           // get_vel_com_obs, as Walker-v0
+        oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;
     } else if (p.task == 16 || p.task == 17 || p.task == 22 || p.task >= 25) {   // Balancer, Flipper: the orientation alone, written by the host's launch; ShapeChange: [0, 0] (base.py:666-667)
         oth[0] = 0.0; oth[1] = 0.0;
     } else if (p.task == 23 || p.task == 24) {           // get_obs_topple + vel com of robot and beam (base.py:644-650, 696-705); column 6: host
@@ -312,7 +371,15 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
             if (fp + i < p.flat_stride) row[fp + i] = (OutT)((q.x / kVoxel - R.bx) * kVoxel);
             if (fp + n + i < p.flat_stride) row[fp + n + i] = (OutT)((q.y / kVoxel - R.by) * kVoxel);
         }
-        for (int i = fp + 2 * n + lane; i < p.flat_stride; i += 32) row[i] = (OutT)0;
+        int tail = 0;
+        if (p.task == 29) {                              // [current_goal, x_goal, x_goal - com x] (multi_goal.py:86-88, 146-157)
+            tail = 3;
+            const double gx = p.goals[(size_t)env * kGoalStride + 3 + goal_shown] * 0.1;
+            const double com_x = (unstable && !was_reset) ? ri_x : R.ax;
+            const double v = lane == 0 ? (double)goal_shown : lane == 1 ? gx : gx - com_x;
+            if (lane < 3 && fp + 2 * n + lane < p.flat_stride) row[fp + 2 * n + lane] = (OutT)v;
+        }
+        for (int i = fp + 2 * n + tail + lane; i < p.flat_stride; i += 32) row[i] = (OutT)0;
     }
     if (p.modular) {                                     // base.py:480-506: 9 values per voxel, non-empty voxels first
         OutT* row = reinterpret_cast<OutT*>(p.modular) + (size_t)env * p.modular_stride;
@@ -395,6 +462,11 @@ __global__ void __launch_bounds__(128) sight_kernel(const double* state, const E
     for (int c = n_cols + lane; c < stride; c += 32) row[c] = (OutT)0;
 }
 
+__global__ void draw_goals_kernel(int* goals, int n_envs, unsigned long long seed) {
+    const int env = blockIdx.x * blockDim.x + threadIdx.x;
+    if (env < n_envs) draw_goals(goals + (size_t)env * kGoalStride, env, seed);
+}
+
 template <typename InT>
 __global__ void policy_actions_kernel(const InT* a, int in_stride, int per_voxel, const TaskEnvRec* tenv, const short* act_vox,
                                       double* act, int act_stride, int n_envs) {
@@ -464,9 +536,10 @@ const TaskDesc kTasks[] = {
     /* 26 */ {"HeightMaximizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
     /* 27 */ {"AreaMaximizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
     /* 28 */ {"AreaMinimizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
+    /* 29 */ {"BidirectionalWalker-v0", 0, 0, 0, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
 };
 constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
-constexpr int kTaskFlipper = 22, kTaskWingspan = 25;
+constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29;
 
 std::vector<std::string> split_names(const char* names) {
     std::vector<std::string> out;
@@ -504,13 +577,15 @@ struct Batch::Task {
     double* d_ort_prev = nullptr;
     int* d_flips = nullptr;              // Flipper-v0
     double* d_span_prev = nullptr;       // Wingspan / Height maximizer
+    int* d_goals = nullptr;              // BidirectionalWalker-v0: kGoalStride ints per environment (TaskParams::goals)
+    unsigned long long goal_seed = 0x6a09e667f3bcc909ull;
     int* d_episode = nullptr;
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -630,7 +705,7 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, D.flat_prefix + 2 * r.r_count);
+        T.flat_width = std::max(T.flat_width, D.flat_prefix + 2 * r.r_count + (T.task == kTaskBiWalk ? 3 : 0));
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -651,7 +726,61 @@ void Batch::task_build() {
     CUDA_CHECK(cudaMalloc(&T.d_span_prev, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_span_prev, 0, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_episode, 0, sizeof(int) * n));
+    if (T.task == kTaskBiWalk) {                         // every environment starts with a drawn list (BiWalk.__init__, multi_goal.py:108)
+        CUDA_CHECK(cudaMalloc(&T.d_goals, sizeof(int) * kGoalStride * n));
+        CUDA_CHECK(cudaMemset(T.d_goals, 0, sizeof(int) * kGoalStride * n));
+        draw_goals_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(T.d_goals, n, T.goal_seed);
+        CUDA_CHECK(cudaGetLastError());
+    }
     T.epoch = finalize_epoch_;
+}
+
+// BidirectionalWalker-v0: the goal lists.  `goals` holds `stride` ints per environment of which the first counts[i] are used
+// (x positions in voxels, the argument of WalkToX, multi_goal.py:64-71); the current-goal index of those environments returns to 0.
+void Batch::task_set_goals(int env_first, int n_envs, const int* counts, const int* goals, int stride) {
+    task_build();
+    Task& T = *task_;
+    if (T.task != kTaskBiWalk) throw std::runtime_error("task_set_goals: the configured task has no goal list");
+    if (env_first < 0 || n_envs < 0 || env_first + n_envs > num_envs()) throw std::runtime_error("task_set_goals: environment range out of bounds");
+    std::vector<int> host((size_t)n_envs * kGoalStride, 0);
+    for (int i = 0; i < n_envs; i++) {
+        if (counts[i] < 1) throw std::runtime_error("task_set_goals: an environment needs at least one goal (multi_goal.py:28-29)");
+        if (counts[i] > kMaxGoals || counts[i] > stride)
+            throw std::runtime_error("task_set_goals: at most " + std::to_string(kMaxGoals) + " goals per environment");
+        host[(size_t)i * kGoalStride] = counts[i];
+        for (int k = 0; k < counts[i]; k++) host[(size_t)i * kGoalStride + 3 + k] = goals[(size_t)i * stride + k];
+    }
+    if (n_envs == 0) return;
+    cudaStream_t s = (cudaStream_t)stream_;
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    // the per-environment draw counters ([2]) are kept: read, merge, write back
+    std::vector<int> cur((size_t)n_envs * kGoalStride);
+    CUDA_CHECK(cudaMemcpy(cur.data(), T.d_goals + (size_t)env_first * kGoalStride, sizeof(int) * cur.size(), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n_envs; i++) host[(size_t)i * kGoalStride + 2] = cur[(size_t)i * kGoalStride + 2];
+    CUDA_CHECK(cudaMemcpy(T.d_goals + (size_t)env_first * kGoalStride, host.data(), sizeof(int) * host.size(), cudaMemcpyHostToDevice));
+}
+
+// New lists for every environment, drawn on the device from `seed` (and the seed later resets of finished episodes draw from).
+void Batch::task_draw_goals(unsigned long long seed) {
+    task_build();
+    Task& T = *task_;
+    if (T.task != kTaskBiWalk) throw std::runtime_error("task_draw_goals: the configured task has no goal list");
+    T.goal_seed = seed;
+    draw_goals_kernel<<<(num_envs() + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(T.d_goals, num_envs(), seed);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+// (count, current index, goals ...) of one environment, for hosts and tests
+int Batch::task_get_goals(int env, int* out, int cap) {
+    task_build();
+    Task& T = *task_;
+    if (T.task != kTaskBiWalk) throw std::runtime_error("task_get_goals: the configured task has no goal list");
+    if (env < 0 || env >= num_envs()) throw std::runtime_error("task_get_goals: environment out of range");
+    int host[kGoalStride];
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    CUDA_CHECK(cudaMemcpy(host, T.d_goals + (size_t)env * kGoalStride, sizeof(host), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < host[0] && k < cap; k++) out[k] = host[3 + k];
+    return host[0] | (host[1] << 16);
 }
 
 void Batch::task_dims(int* dims) {
@@ -722,7 +851,8 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.fall_y = D.fall_y;
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
     p.flips = T.task == kTaskFlipper ? T.d_flips : nullptr;
-    p.span_prev = T.task >= kTaskWingspan ? T.d_span_prev : nullptr;          // the ShapeChange tasks (25 ... 28)
+    p.span_prev = T.task >= kTaskWingspan && T.task <= kTaskAreaMin ? T.d_span_prev : nullptr;
+    p.goals = T.d_goals; p.goal_seed = T.goal_seed;          // the ShapeChange tasks (25 ... 28)
     if (other && other_stride < D.other_width)
         throw std::runtime_error("task_outputs: the 'other' observation of this task is " + std::to_string(D.other_width) + " wide");
     if (flat && flat_stride < D.flat_prefix) throw std::runtime_error("task_outputs: the flat observation is narrower than its fixed part");
@@ -769,7 +899,8 @@ void Batch::task_outputs(double* reward, unsigned char* done, double* flat, int 
     double* d_mod = reinterpret_cast<double*>(base + b_rew + b_flat);
     double* d_oth = reinterpret_cast<double*>(base + b_rew + b_flat + b_mod);
     unsigned char* d_done = reinterpret_cast<unsigned char*>(base + b_rew + b_flat + b_mod + b_oth);
-    task_outputs_device(d_rew, d_done, flat ? d_flat : nullptr, flat_stride, modular ? d_mod : nullptr, modular_stride,
+    // (no reward and no done flags wanted: the reset observation -- the kernel then leaves the tasks' episode state alone)
+    task_outputs_device(reward ? d_rew : nullptr, done ? d_done : nullptr, flat ? d_flat : nullptr, flat_stride, modular ? d_mod : nullptr, modular_stride,
                         other ? d_oth : nullptr, other_stride, false, reset_done);
     cudaStream_t s = (cudaStream_t)stream_;
     if (reward) CUDA_CHECK(cudaMemcpyAsync(reward, d_rew, b_rew, cudaMemcpyDeviceToHost, s));
@@ -789,6 +920,8 @@ void Batch::task_reset_device(void* flat, int flat_stride, void* modular, int mo
     Task& T = *task_;
     CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));   // -1: the outputs pass counts one
     CUDA_CHECK(cudaMemsetAsync(T.d_flips, 0, sizeof(int) * num_envs(), (cudaStream_t)stream_));
+    if (T.d_goals)                                       // current goal <- 0; the lists stay (new ones: task_set_goals / task_draw_goals first)
+        CUDA_CHECK(cudaMemset2DAsync(T.d_goals + 1, sizeof(int) * kGoalStride, 0, sizeof(int), num_envs(), (cudaStream_t)stream_));
     task_outputs_device(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, is_f32, false);
 }
 
@@ -798,6 +931,8 @@ void Batch::task_reset(double* flat, int flat_stride, double* modular, int modul
     Task& T = *task_;
     CUDA_CHECK(cudaMemsetAsync(T.d_episode, 0xff, sizeof(int) * num_envs(), (cudaStream_t)stream_));
     CUDA_CHECK(cudaMemsetAsync(T.d_flips, 0, sizeof(int) * num_envs(), (cudaStream_t)stream_));
+    if (T.d_goals)                                       // current goal <- 0; the lists stay (new ones: task_set_goals / task_draw_goals first)
+        CUDA_CHECK(cudaMemset2DAsync(T.d_goals + 1, sizeof(int) * kGoalStride, 0, sizeof(int), num_envs(), (cudaStream_t)stream_));
     task_outputs(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, false);
 }
 

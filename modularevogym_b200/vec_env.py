@@ -13,12 +13,13 @@ output tensors only; all compute is in ``libmevo_b200.so`` through the C ABI (``
 """
 from __future__ import annotations
 
+import random
 from typing import Dict, Optional, Sequence, Tuple
 
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
+from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bidirectional_walker_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
                     climber_v1_world, climber_v2_world, climber_world, down_stepper_world, flipper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
                     jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world, shape_change_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
@@ -54,8 +55,22 @@ TASKS = {
     "HeightMaximizer-v0": (26, shape_change_world, None, 500),                # change_shape.py:388-487, __init__.py:180-184
     "AreaMaximizer-v0": (27, shape_change_world, None, 600),                  # change_shape.py:85-183, __init__.py:162-166
     "AreaMinimizer-v0": (28, shape_change_world, None, 600),                  # change_shape.py:186-284, __init__.py:168-172
+    "BidirectionalWalker-v0": (29, bidirectional_walker_world, None, 1000),   # multi_goal.py:91-205, __init__.py:206-210 (flat mode only)
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
+
+
+def random_goals(lower_bound: int = 20, upper_bound: int = 50, goal_dist: int = 100, start: int = 35, limit: int = 61) -> list:
+    """The x goals of one BidirectionalWalker-v0 episode, drawn as ``BiWalk.set_random_goals`` does (multi_goal.py:115-129): uniform
+    positions until the path through them is ``goal_dist`` voxels long (``limit``: the device table's capacity, never reached in
+    practice -- the mean hop is ten voxels)."""
+    goals, curr, dist = [], start, 0
+    while dist < goal_dist and len(goals) < limit:
+        nxt = random.randrange(lower_bound, upper_bound)
+        dist += abs(curr - nxt)
+        curr = nxt
+        goals.append(nxt)
+    return goals
 
 
 class BatchedEvoGymEnv:
@@ -79,6 +94,8 @@ class BatchedEvoGymEnv:
         if task in (4, 6, 7, 8, 9, 10, 12, 13, 18, 19) and mode != "modular":
             raise ValueError(f"{env_id} is available in modular mode only (its flat observation interleaves orientation "
                              "and sight values with a per-robot number of positions)")
+        if task == 29 and mode == "modular":
+            raise ValueError(f"{env_id} has no modular mode in the reference (evogym/envs/multi_goal.py:93); pass mode=None")
         self.env_id, self.mode, self.device_index = env_id, mode, device
         self.num_envs = len(bodies)
         self.bodies = [np.asarray(b) for b in bodies]
@@ -149,6 +166,9 @@ class BatchedEvoGymEnv:
     def reset(self):
         """``venv.reset()``: every environment to snapshot 0; returns the observation (tensors owned by the env, overwritten
         by the next ``step``)."""
+        if self.env_id == "BidirectionalWalker-v0":
+            # BiWalk.reset draws new goals from Python's global `random` (multi_goal.py:115-129, 183-184): the same calls, here
+            self.B.task_set_goals([random_goals() for _ in range(self.num_envs)])
         f, fs, m, ms, o, os_ = self._ptrs()
         self.B.task_reset_device(f, fs, m, ms, o, os_, self.dtype == self.torch.float32)
         self._wait()

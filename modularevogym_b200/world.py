@@ -579,6 +579,21 @@ def shape_change_world(robot: np.ndarray, connections: Optional[np.ndarray] = No
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _bidirectional_walker_terrain() -> WorldSpec:
+    w = WorldSpec(width=70, height=1)
+    w.add_from_array("new_object_1", np.full((1, 70), VOXEL_TYPES["FIXED"], dtype=np.int64), 0, 0)
+    return _frozen(w)
+
+
+def bidirectional_walker_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """BidirectionalWalker-v0 (``sim_files/BidirectionalWalker-v0.json`` + ``evogym/envs/multi_goal.py:96-97``): a flat strip of 70
+    fixed voxels ``new_object_1``, the robot in its middle at voxel (33, 1)."""
+    w = _shared(_bidirectional_walker_terrain())
+    w.add_from_array("robot", robot, 33, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -934,6 +949,7 @@ _TERRAINS = {
     "HeightMaximizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "AreaMaximizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "AreaMinimizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
+    "BidirectionalWalker-v0": (lambda robot: _bidirectional_walker_terrain(), (33, 1)),
     "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
     "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }

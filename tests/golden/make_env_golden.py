@@ -267,6 +267,47 @@ def main():
             print(path, "reward sum", float(np.sum(rew)), "modular width", out["modular_obs"].shape[1],
                   "flat == modular rewards:", np.array_equal(out["reward"], out["modular_reward"]))
 
+    # ---- BidirectionalWalker-v0 (multi_goal.py:91-205): flat mode only (the reference has no modular mode for it).  Three goal lists:
+    # the environment's own random draw; a list whose first goals lie within two voxels of the start, so that get_reward walks
+    # through several goals in one step (multi_goal.py:50-53); and a list the robot exhausts on the first step (done, +1)
+    if not only or "biwalk" in only:
+        from evogym.envs.multi_goal import BiWalk, WalkToX
+        for tag, forced in (("random", None), ("near", [36, 35, 34, 22, 48]), ("all", [35, 36])):
+            random.seed(100)
+            np.random.seed(100)
+            body, conn = sample_robot((5, 5))
+            rng = np.random.default_rng(500)
+            env = BiWalk(body, conn)
+            random.seed(4242)
+            obs0 = env.reset()                          # draws a new list
+            if forced is not None:
+                env.init_reward_goals([WalkToX(g) for g in forced])
+                env.current_goal = 0
+                obs0 = np.concatenate((obs0[:-3], np.array([0]), env.goals[0].get_obs({"robot_com_pos_final": env.object_pos_at_time(env.get_time(), "robot")})))
+            goals = [g.x_goal for g in env.goals]
+            n_act = env.get_actuator_indices("robot").size
+            acts = rng.uniform(-1.0, 1.0, size=(n_steps, n_act))
+            flat_obs, rew, done, cur = [np.asarray(obs0, dtype=np.float64)], [], [], []
+            pre = {k: [] for k in ("pos", "vel", "pos_last", "vel_true", "goal")}
+            for t in range(n_steps):
+                st = env._sim._r.get_state()
+                for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
+                    pre[k].append(v.copy())
+                pre["goal"].append(env._sim._r.edges()["goal"].copy())
+                o, r, d, _ = env.step(acts[t].copy())
+                flat_obs.append(np.asarray(o, dtype=np.float64)); rew.append(float(r)); done.append(bool(d)); cur.append(env.current_goal)
+                if d:
+                    break
+            from modularevogym_b200.world import WorldSpec
+            out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": "BidirectionalWalker-v0",
+                   "world_json": json.dumps(WorldSpec.from_evoworld(env.world).to_dict()), "goals": np.asarray(goals, dtype=np.int32),
+                   "current_goal": np.asarray(cur, dtype=np.int32), "actions": acts[:len(rew)], "flat_obs": np.stack(flat_obs),
+                   "reward": np.asarray(rew), "done": np.asarray(done),
+                   "actuator_indices": env.get_actuator_indices("robot").astype(np.int32)}
+            out.update({"pre_" + k: np.stack(v) for k, v in pre.items()})
+            path = os.path.join(HERE, f"biwalk_{tag}.npz")
+            np.savez_compressed(path, **out)
+            print(path, "goals", goals, "current", cur, "reward", rew[:3], "done", done[-1])
     if only:
         return
     # ---- terrain sight + orientation observations (base.py:258-372): ObstacleTraverser-v1 (floor, "ground"), CaveCrawler-v0

@@ -14,10 +14,10 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def golden_names() -> List[str]:
-    """engine fixtures (make_golden.py); env_* / sight_* are the task-layer fixtures (make_env_golden.py), worlds_* the world-file
+    """engine fixtures (make_golden.py); env_* / sight_* / biwalk_* are the task-layer fixtures (make_env_golden.py), worlds_* the world-file
     topologies (make_world_golden.py)"""
     names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith(("env_", "sight_", "worlds_", "adv_"))]
+    return [n for n in names if not n.startswith(("env_", "sight_", "worlds_", "adv_", "biwalk_"))]
 
 
 def env_golden_names() -> List[str]:
