@@ -99,6 +99,31 @@ def main():
         log.append(rec)
         print(json.dumps(rec), flush=True)
 
+    # ---- BidirectionalWalker-v0 (flat mode only in the reference): the fixture's goal list is put in place of the one reset() drew
+    from evogym.envs.multi_goal import WalkToX
+    for path in sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "biwalk_*.npz"))):
+        with np.load(path) as z:
+            g = {k: z[k] for k in z.files}
+        env = gym.make("BidirectionalWalker-v0", body=g["body"], connections=g["connections"])
+        assert isinstance(env.unwrapped._sim, simulator_cpp.Sim)
+        o = env.reset()
+        env.unwrapped.init_reward_goals([WalkToX(int(x)) for x in g["goals"]])
+        env.unwrapped.current_goal = 0
+        worst_r, worst_o, dones, currents = 0.0, rel_err(o[:-3], g["flat_obs"][0][:-3]), [], []
+        for t in range(g["reward"].shape[0]):
+            o, r, d, _ = env.step(g["actions"][t].copy())
+            worst_r = max(worst_r, abs(float(r) - float(g["reward"][t])))
+            worst_o = max(worst_o, rel_err(o, g["flat_obs"][t + 1]))
+            dones.append(bool(d)); currents.append(int(env.unwrapped.current_goal))
+        env.close()
+        rec = {"fixture": os.path.basename(path), "env_id": "BidirectionalWalker-v0", "steps": len(dones), "flat_reward_err": worst_r,
+               "flat_obs_err": worst_o, "flat_done_equal": dones == g["done"].astype(bool).tolist(),
+               "goal_index_equal": currents == g["current_goal"].tolist()}
+        rec["ok"] = bool(worst_r <= TOL_REWARD and worst_o <= TOL_OBS and rec["flat_done_equal"] and rec["goal_index_equal"])
+        ok &= rec["ok"]
+        log.append(rec)
+        print(json.dumps(rec), flush=True)
+
     # ---- the reference's smoke script (examples/modularevogym_test.py:1-37) on the fixture environments
     random.seed(0)
     np.random.seed(0)
