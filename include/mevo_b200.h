@@ -291,6 +291,8 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_BIDIRECTIONAL_WALKER 29   /* BiWalk, multi_goal.py:91-205 (BidirectionalWalker-v0): walk to a list of x positions in turn; the reward is the
                                                approach to the current goal (+1 after the last), the flat observation ends with [goal index, x goal,
                                                x goal - com x].  The reference has no modular mode for it; goal lists: mevo_batch_task_set_goals */
+#define MEVO_TASK_TRAVERSER 30               /* BlockSoup, traverse.py:784-911 (Traverser-v0): x progress across a pit filled with 27 loose rigid blocks;
+                                               com x beyond voxel 59 ends the episode with + 2; "other" as task 18 with the pit and all blocks as terrain */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

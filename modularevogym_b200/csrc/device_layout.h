@@ -23,7 +23,8 @@
 
 namespace mevo {
 
-constexpr int kMaxDynObjects = 8;        // dynamic objects per environment (3-bit field in pair codes)
+constexpr int kMaxDynObjects = 8;        // robots per environment (self-collision counters), and dynamic objects the warp kernels take
+constexpr int kMaxPairObjects = 64;      // dynamic objects per environment (6-bit object field of the pair codes, kCodeObjShift)
 constexpr int kMaxLeaves = 4095;         // 12-bit leaf ids in pair / candidate codes
 
 struct alignas(16) LeafRec {  // 32 bytes; one surface boxel

@@ -563,7 +563,12 @@ void Batch::pack_env(int env_id, std::vector<uint8_t>& design, std::vector<uint8
         r.leaf_count = (uint16_t)(leaves.size() - r.leaf_start);
         objrecs.push_back(r);
     }
-    if ((int)objrecs.size() > kMaxDynObjects) throw std::runtime_error("too many dynamic objects in one environment (max 8)");
+    // Per-object device state is the self-collision counter of ROBOTS only (PhysicsEngine.cpp:856-863): robots, which load first
+    // (evogym/sim.py:52-62), must sit in the first kMaxDynObjects slots; other simulated objects (the 27 blocks of Traverser-v0)
+    // only need their slot to fit the pair code's object field.  More than kMaxDynObjects objects run on the group kernels.
+    if ((int)objrecs.size() > kMaxPairObjects) throw std::runtime_error("too many dynamic objects in one environment (max 64)");
+    for (size_t i = kMaxDynObjects; i < objrecs.size(); i++)
+        if (objrecs[i].is_robot) throw std::runtime_error("too many robots in one environment (max 8, loaded before the other objects)");
     if ((int)leaves.size() > kMaxLeaves) throw std::runtime_error("too many surface voxels in one environment (max 4095)");
     // Leaf pairs inside one object that share a point ALWAYS have overlapping boxes (both boxes contain
     // the shared point), so they are candidates in every substep: they are not tested; their non-shared

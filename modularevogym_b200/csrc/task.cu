@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
             __syncwarp();
             if (lane == 0) g[1] = cur;
         }
-    } else if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
+    } else if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19 || p.task == 30) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3 || p.task == 11) {            // climb.py:96-99, 190-193
         reward = rf_y - ri_y;
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // ---- observations of the (possibly reset) state
     double oth[6];
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
-    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19 || p.task == 30) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else if (p.task == 29) {                           // get_vel_com_obs, as Walker-v0
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;
@@ -504,6 +504,8 @@ struct TaskDesc {
 };
 constexpr const char* kPlatforms5 = "platform_1,platform_2,platform_3,platform_4,platform_5";
 constexpr const char* kPlatforms7 = "platform_1,platform_2,platform_3,platform_4,platform_5,platform_6,platform_7";
+// BlockSoup.terrain_list (traverse.py:815-823): the pit and the 27 loose blocks in it
+constexpr const char* kBlockSoup = "ground,block_0,block_1,block_2,block_3,block_4,block_5,block_6,block_7,block_8,block_9,block_10,block_11,block_12,block_13,block_14,block_15,block_16,block_17,block_18,block_19,block_20,block_21,block_22,block_23,block_24,block_25,block_26";
 #define MEVO_NO_SIGHT {{nullptr, 0, false, 0}, {nullptr, 0, false, 0}}
 #define MEVO_FLOOR5(names) {{names, 5, false, 3}, {nullptr, 0, false, 0}}
 const TaskDesc kTasks[] = {
@@ -537,6 +539,7 @@ const TaskDesc kTasks[] = {
     /* 27 */ {"AreaMaximizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
     /* 28 */ {"AreaMinimizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
     /* 29 */ {"BidirectionalWalker-v0", 0, 0, 0, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
+    /* 30 */ {"Traverser-v0", 1, 59, 2, false, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5(kBlockSoup)},
 };
 constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
 constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29;
@@ -985,17 +988,25 @@ void Batch::sight_obs_strided_device(int obj_index, const std::vector<std::strin
             r.o_count = ob.max_point - ob.min_point + 1;
             if (r.o_start < 0) throw std::runtime_error("sight_obs: the observed object is static");
             std::vector<double> stat;
+            std::vector<std::pair<int, int>> dyn;                  // simulated terrain objects: (first point, count) in the state
             for (const std::string& t : terrain) {
                 const int ti = E.world.find_object(t);
                 if (ti < 0) continue;                              // the reference would raise on an unknown name; envs never pass one
                 const VoxelObject& tb = E.world.objects[ti];
                 const int l0 = E.point_local[tb.min_point];
                 if (l0 >= 0) {
-                    if (r.n_dyn >= 3) throw std::runtime_error("sight_obs: more than 3 simulated terrain objects");
-                    r.dyn_start[r.n_dyn] = l0; r.dyn_count[r.n_dyn] = tb.max_point - tb.min_point + 1; r.n_dyn++;
+                    dyn.emplace_back(l0, tb.max_point - tb.min_point + 1);
                 } else {
                     for (int p = tb.min_point; p <= tb.max_point; p++) { stat.push_back(E.pos[2 * p]); stat.push_back(E.pos[2 * p + 1]); }
                 }
+            }
+            // the kernel takes a maximum / minimum over all terrain points, so neighbouring ranges are one range (the 27 blocks of
+            // Traverser-v0 follow each other in the state)
+            std::sort(dyn.begin(), dyn.end());
+            for (const auto& d : dyn) {
+                if (r.n_dyn > 0 && r.dyn_start[r.n_dyn - 1] + r.dyn_count[r.n_dyn - 1] == d.first) { r.dyn_count[r.n_dyn - 1] += d.second; continue; }
+                if (r.n_dyn >= 3) throw std::runtime_error("sight_obs: more than 3 separate ranges of simulated terrain points");
+                r.dyn_start[r.n_dyn] = d.first; r.dyn_count[r.n_dyn] = d.second; r.n_dyn++;
             }
             int off = -1;
             for (const auto& sv : seen) if (sv.first == stat) { off = sv.second; break; }

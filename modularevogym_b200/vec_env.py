@@ -19,7 +19,7 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bidirectional_walker_world, bridge_walker_world, carrier_v1_world, carrier_world, cave_crawler_world,
+from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bidirectional_walker_world, bridge_walker_world, traverser_world, carrier_v1_world, carrier_world, cave_crawler_world,
                     climber_v1_world, climber_v2_world, climber_world, down_stepper_world, flipper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
                     jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world, shape_change_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
@@ -56,6 +56,7 @@ TASKS = {
     "AreaMaximizer-v0": (27, shape_change_world, None, 600),                  # change_shape.py:85-183, __init__.py:162-166
     "AreaMinimizer-v0": (28, shape_change_world, None, 600),                  # change_shape.py:186-284, __init__.py:168-172
     "BidirectionalWalker-v0": (29, bidirectional_walker_world, None, 1000),   # multi_goal.py:91-205, __init__.py:206-210 (flat mode only)
+    "Traverser-v0": (30, traverser_world, None, 600),                         # traverse.py:784-911, __init__.py:100-104
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 
@@ -91,7 +92,7 @@ class BatchedEvoGymEnv:
         if env_id not in TASKS:
             raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
         task, builder, package, limit = TASKS[env_id]
-        if task in (4, 6, 7, 8, 9, 10, 12, 13, 18, 19) and mode != "modular":
+        if task in (4, 6, 7, 8, 9, 10, 12, 13, 18, 19, 30) and mode != "modular":
             raise ValueError(f"{env_id} is available in modular mode only (its flat observation interleaves orientation "
                              "and sight values with a per-robot number of positions)")
         if task == 29 and mode == "modular":

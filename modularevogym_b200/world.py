@@ -594,6 +594,36 @@ def bidirectional_walker_world(robot: np.ndarray, connections: Optional[np.ndarr
     return w
 
 
+# BlockSoup.blocks (evogym/envs/traverse.py:792-813): (x, y, edge length) of the loose rigid blocks in the pit
+TRAVERSER_BLOCKS = ((20, 1, 3), (24, 1, 3), (27, 1, 2), (31, 1, 3), (34, 1, 3), (38, 1, 2), (41, 1, 3), (45, 1, 3),
+                    (21, 4, 3), (24, 4, 2), (26, 4, 1), (29, 4, 2), (31, 4, 3), (34, 4, 2), (36, 4, 2), (40, 4, 3), (43, 4, 2), (46, 4, 3)) + \
+                   tuple((x, 7, 2) for x in range(20, 45, 3))
+
+
+@functools.lru_cache(maxsize=None)
+def _traverser_terrain() -> WorldSpec:
+    w = WorldSpec(width=60, height=9)
+    grid = np.zeros((9, 60), dtype=np.int64)
+    fixed = VOXEL_TYPES["FIXED"]
+    grid[8 - 8, 0:20] = fixed                    # start ledge (y = 8)
+    grid[:, 19] = fixed                          # left wall of the pit
+    grid[8 - 0, 19:50] = fixed                   # pit floor (y = 0)
+    grid[8 - 6:, 49] = fixed                     # right wall, up to y = 6
+    grid[8 - 6, 49:60] = fixed                   # exit ledge (y = 6)
+    w.add_from_array("ground", grid, 0, 0)
+    for k, (x, y, size) in enumerate(TRAVERSER_BLOCKS):
+        w.add_from_array(f"block_{k}", np.full((size, size), VOXEL_TYPES["RIGID"], dtype=np.int64), x, y)
+    return _frozen(w)
+
+
+def traverser_world(robot: np.ndarray, connections: Optional[np.ndarray] = None) -> WorldSpec:
+    """Traverser-v0 (``sim_files/Traverser-v0.json`` + ``rigid_{1,2,3}x{1,2,3}.json`` + ``evogym/envs/traverse.py:788-823``): a pit
+    between two ledges, filled with 27 loose rigid blocks ``block_0 ... block_26``; the robot on the start ledge at voxel (1, 9)."""
+    w = _shared(_traverser_terrain())
+    w.add_from_array("robot", robot, 1, 9, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -950,6 +980,7 @@ _TERRAINS = {
     "AreaMaximizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "AreaMinimizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "BidirectionalWalker-v0": (lambda robot: _bidirectional_walker_terrain(), (33, 1)),
+    "Traverser-v0": (lambda robot: _traverser_terrain(), (1, 9)),
     "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
     "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }

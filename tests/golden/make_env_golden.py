@@ -50,7 +50,13 @@ def install_stubs():
             self._range = {}
 
         def _add(self, grid, conn, name, x, y, robot):
-            ok = self._r.add_object(np.asarray(grid, dtype=np.float64), np.asarray(conn, dtype=np.float64), name, x, y, robot)
+            # evogym/sim.py:83-84 hands np.empty((2, 1)) -- uninitialised memory -- over for an object without connections (the 1 x 1
+            # block of Traverser-v0); whatever it holds, the reference then reads cell indices out of it.  Pass no connection instead.
+            conn = np.asarray(conn, dtype=np.float64).reshape(2, -1)
+            n_cells = np.asarray(grid).size
+            valid = np.isfinite(conn).all(axis=0) & (conn >= 0).all(axis=0) & (conn < n_cells).all(axis=0)
+            conn = np.ascontiguousarray(conn[:, valid])
+            ok = self._r.add_object(np.asarray(grid, dtype=np.float64), conn, name, x, y, robot)
             if ok:
                 info = self._r.object_info(self._r.num_objects - 1)
                 self._range[name] = (info["min_point"], info["max_point"])
@@ -181,7 +187,7 @@ def main():
     from evogym.envs.walk import Duck, SoftBridge, WalkingFlat
     from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, LiftSmallRect, PushSmallRect, SlideBeam, ToppleBeam, PushSmallRectOnOppositeSide, ThrowSmallRect
     from evogym.envs.climb import Climb0, Climb1, Climb2
-    from evogym.envs.traverse import FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
+    from evogym.envs.traverse import BlockSoup, FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
     from evogym.envs.balance import Balance, BalanceJump
     from evogym.envs.flip import Flipping
@@ -200,7 +206,8 @@ def main():
              "carrierv1": (CarrySmallRectToTable, "Carrier-v1"), "lifter": (LiftSmallRect, "Lifter-v0"),
              "flipper": (Flipping, "Flipper-v0"), "beamtoppler": (ToppleBeam, "BeamToppler-v0"), "beamslider": (SlideBeam, "BeamSlider-v0"),
              "wingspan": (MaximizeXShape, "WingspanMazimizer-v0"), "height": (MaximizeYShape, "HeightMaximizer-v0"),
-             "areamax": (MaximizeShape, "AreaMaximizer-v0"), "areamin": (MinimizeShape, "AreaMinimizer-v0")}
+             "areamax": (MaximizeShape, "AreaMaximizer-v0"), "areamin": (MinimizeShape, "AreaMinimizer-v0"),
+             "traverser": (BlockSoup, "Traverser-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():

@@ -235,6 +235,10 @@ def cases():
     out.append(("squash_s14", world_with_robot("Walker-v0", r, c, 1, 1), 14, perturb_squash))
     r, c = seeded_robot(15)
     out.append(("collapse_s15", world_with_robot("Walker-v0", r, c, 1, 1), 15, perturb_collapse))
+    # Traverser-v0: 28 simulated objects (the robot and 27 loose rigid blocks that settle onto each other during the rollout)
+    from modularevogym_b200.world import traverser_world
+    r, c = seeded_robot(16)
+    out.append(("blocksoup_s16", traverser_world(r, c), 16, None))
     return out
 
 
@@ -243,7 +247,7 @@ def main():
     for name, world, seed, perturb in cases():
         if only and name not in only:
             continue
-        big = world.objects["robot"].grid.size > 64
+        big = world.objects["robot"].grid.size > 64 or len(world.objects) > 8
         fx = record(name, world, seed, perturb, n_sub=30 if big else N_SUB, n_steps=4 if big else N_STEPS)
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **fx)
 

@@ -40,7 +40,7 @@ class EnvGolden:
                      "Balancer-v0": 16, "Balancer-v1": 17, "GapJumper-v0": 18, "PlatformJumper-v0": 19,
                      "Carrier-v1": 20, "Lifter-v0": 21, "Flipper-v0": 22,
                      "BeamToppler-v0": 23, "BeamSlider-v0": 24, "WingspanMazimizer-v0": 25, "HeightMaximizer-v0": 26,
-                     "AreaMaximizer-v0": 27, "AreaMinimizer-v0": 28}[self.env_id]
+                     "AreaMaximizer-v0": 27, "AreaMinimizer-v0": 28, "Traverser-v0": 30}[self.env_id]
         self.package = "package" if self.task in (1, 2, 14, 15, 20, 21) else "beam" if self.task in (23, 24) else None
         self.n_steps = int(self.z["reward"].shape[0])
 

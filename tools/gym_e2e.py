@@ -132,7 +132,7 @@ def main():
                    "Climber-v2", "Carrier-v0", "Pusher-v1", "Balancer-v0", "Balancer-v1", "GapJumper-v0",
                    "PlatformJumper-v0", "Carrier-v1", "Lifter-v0", "Flipper-v0",
                    "BeamToppler-v0", "BeamSlider-v0", "WingspanMazimizer-v0", "HeightMaximizer-v0",
-                   "AreaMaximizer-v0", "AreaMinimizer-v0"):
+                   "AreaMaximizer-v0", "AreaMinimizer-v0", "Traverser-v0"):
         body, connections = sample_robot((5, 5))
         env = gym.make(env_id, body=body)
         env = gym.make(env_id, body=body, mode="modular", env_id=env_id)
