@@ -293,6 +293,8 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
                                                x goal - com x].  The reference has no modular mode for it; goal lists: mevo_batch_task_set_goals */
 #define MEVO_TASK_TRAVERSER 30               /* BlockSoup, traverse.py:784-911 (Traverser-v0): x progress across a pit filled with 27 loose rigid blocks;
                                                com x beyond voxel 59 ends the episode with + 2; "other" as task 18 with the pit and all blocks as terrain */
+#define MEVO_TASK_CATCHER 31                 /* CatchSmallRect, manipulate.py:630-886 (Catcher-v0): a package tumbles down from two pegs; reward = approach of
+                                               robot and package in x + 10 x the package's fall below 5 voxels; observations laid out as task 23's */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

@@ -250,6 +250,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         reward += fabs(pf_x - pi_x) * 1.0;
         reward += fabs(pf_y - pi_y) * 3.0;
         reward += (pi_y - pf_y) * 10;
+    } else if (p.task == 31) {                           // manipulate.py:737-753 (Catcher-v0, thresh_height 5 voxels)
+        reward = fabs(ri_x - pi_x) - fabs(rf_x - pf_x);
+        if (pf_y < 5.0 * kVoxel) reward += 10 * (pf_y - pi_y);
     } else if (p.task == 24) {                           // manipulate.py:1088-1104 (BeamSlider-v0)
         reward = fabs(pi_x - ri_x) - fabs(pf_x - rf_x);
         reward += (pf_x - pi_x) * 1.0;
@@ -348,9 +351,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else if (p.task == 29) {                           // get_vel_com_obs, as Walker-v0
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;
-    } else if (p.task == 16 || p.task == 17 || p.task == 22 || p.task >= 25) {   // Balancer, Flipper: the orientation alone, written by the host's launch; ShapeChange: [0, 0] (base.py:666-667)
+    } else if (p.task == 16 || p.task == 17 || p.task == 22 || (p.task >= 25 && p.task <= 28)) {   // Balancer, Flipper: the orientation alone, written by the host's launch; ShapeChange: [0, 0] (base.py:666-667)
         oth[0] = 0.0; oth[1] = 0.0;
-    } else if (p.task == 23 || p.task == 24) {           // get_obs_topple + vel com of robot and beam (base.py:644-650, 696-705); column 6: host
+    } else if (p.task == 23 || p.task == 24 || p.task == 31) {   // get_obs_topple / get_obs_catch (manipulate.py:726-735) + vel com of robot and beam (base.py:644-650, 696-705); column 6: host
         oth[0] = P.ax - R.ax; oth[1] = P.ay - R.ay; oth[2] = R.cx * kVoxel; oth[3] = R.cy * kVoxel; oth[4] = P.cx * kVoxel; oth[5] = P.cy * kVoxel;
     } else {                                             // PackageBase.get_obs (manipulate.py:22-36)
         oth[0] = R.dx; oth[1] = R.dy; oth[2] = P.ax - R.ax; oth[3] = P.ay - R.ay; oth[4] = P.dx; oth[5] = P.dy;
@@ -540,6 +543,7 @@ const TaskDesc kTasks[] = {
     /* 28 */ {"AreaMinimizer-v0", 0, 0, 0, false, 0, false, 2, 2, 0, -1, false, false, MEVO_NO_SIGHT},
     /* 29 */ {"BidirectionalWalker-v0", 0, 0, 0, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
     /* 30 */ {"Traverser-v0", 1, 59, 2, false, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5(kBlockSoup)},
+    /* 31 */ {"Catcher-v0", 0, 0, 0, false, 0, true, 7, 7, 7, 6, true, true, MEVO_NO_SIGHT},
 };
 constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
 constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29;

@@ -19,7 +19,7 @@ from typing import Dict, Optional, Sequence, Tuple
 import numpy as np
 
 from . import capi
-from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bidirectional_walker_world, bridge_walker_world, traverser_world, carrier_v1_world, carrier_world, cave_crawler_world,
+from .world import (WorldSpec, balancer_v1_world, balancer_world, beam_slider_world, beam_toppler_world, bidirectional_walker_world, bridge_walker_world, catcher_world, traverser_world, carrier_v1_world, carrier_world, cave_crawler_world,
                     climber_v1_world, climber_v2_world, climber_world, down_stepper_world, flipper_world, full_connectivity, gap_jumper_world, hurdler_world, platform_jumper_world,
                     jumper_world, lifter_world, obstacle_traverser_v0_world, obstacle_traverser_world, pusher_v1_world, pusher_world, shape_change_world,
                     terrain_for, thrower_world, up_stepper_world, walker_world)
@@ -57,6 +57,9 @@ TASKS = {
     "AreaMinimizer-v0": (28, shape_change_world, None, 600),                  # change_shape.py:186-284, __init__.py:168-172
     "BidirectionalWalker-v0": (29, bidirectional_walker_world, None, 1000),   # multi_goal.py:91-205, __init__.py:206-210 (flat mode only)
     "Traverser-v0": (30, traverser_world, None, 600),                         # traverse.py:784-911, __init__.py:100-104
+    # Catcher-v0: the reference re-draws the package's launch position at EVERY reset (it rebuilds its world); here it is drawn per
+    # environment when the batch is built (construction, update()) -- episodes restarted on the device keep their environment's draw
+    "Catcher-v0": (31, catcher_world, "package", 400),                        # manipulate.py:630-886, __init__.py:155-159
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
 
@@ -112,11 +115,12 @@ class BatchedEvoGymEnv:
                      for i, b in enumerate(self.bodies)]
             # environments that share their terrain go in through one call (design loops rebuild the batch every episode); the
             # terrain of Climber-v0 depends on the robot's width, so its environments are grouped by terrain
+            placed = [terrain_for(env_id, b) for b in self.bodies]      # once per environment: Catcher-v0's terrain is a random draw
             i = 0
             while i < self.num_envs:
-                terrain, rx, ry = terrain_for(env_id, self.bodies[i])
+                terrain, rx, ry = placed[i]
                 j = i + 1
-                while j < self.num_envs and terrain_for(env_id, self.bodies[j])[0] is terrain:
+                while j < self.num_envs and placed[j][0] is terrain:
                     j += 1
                 self.B.add_robot_worlds(terrain, self.bodies[i:j], conns[i:j], "robot", rx, ry)
                 i = j

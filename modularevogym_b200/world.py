@@ -624,6 +624,37 @@ def traverser_world(robot: np.ndarray, connections: Optional[np.ndarray] = None)
     return w
 
 
+@functools.lru_cache(maxsize=None)
+def _catcher_terrain(offsetx: int, offsety: int) -> WorldSpec:
+    w = flat_ground_world(100)
+    w.add_from_array("package", _package(), 21 + offsetx, 41 + offsety)
+    peg = np.full((1, 5), VOXEL_TYPES["FIXED"], dtype=np.int64)
+    w.add_from_array("peg1", peg, 17 + offsetx, 39 + offsety)
+    w.add_from_array("peg2", peg, 19 + offsetx, 25 + offsety)
+    return _frozen(w)
+
+
+def catcher_offsets() -> Tuple[int, int]:
+    """where CatchSmallRect.random_init hangs the package and its two pegs (``evogym/envs/manipulate.py:652-653``): the reference's
+    own two calls of Python's global ``random``"""
+    offsetx = _random.randint(-6, 4)
+    offsety = _random.randint(0, 5)
+    return offsetx, offsety
+
+
+def catcher_world(robot: np.ndarray, connections: Optional[np.ndarray] = None, offsetx: Optional[int] = None,
+                  offsety: Optional[int] = None) -> WorldSpec:
+    """Catcher-v0 (``sim_files/Walker-v0.json`` + ``package.json`` + ``peg.json`` + ``evogym/envs/manipulate.py:646-671``): flat
+    ground, the robot at voxel (22, 1), high above it a package resting on the end of one fixed peg with a second peg below -- the
+    package tips off and tumbles down.  The whole arrangement is shifted by a random offset (drawn here like the reference draws
+    it when none is given)."""
+    if offsetx is None or offsety is None:
+        offsetx, offsety = catcher_offsets()
+    w = _shared(_catcher_terrain(int(offsetx), int(offsety)))
+    w.add_from_array("robot", robot, 22, 1, connections)
+    return w
+
+
 THROWER_POSTS = {10: 2, 14: 3, 18: 4, 23: 6, 28: 7, 39: 9, 69: 9}     # column -> voxels above the ground row
 
 
@@ -981,6 +1012,7 @@ _TERRAINS = {
     "AreaMinimizer-v0": (lambda robot: _shape_change_terrain(), (7, 1)),
     "BidirectionalWalker-v0": (lambda robot: _bidirectional_walker_terrain(), (33, 1)),
     "Traverser-v0": (lambda robot: _traverser_terrain(), (1, 9)),
+    "Catcher-v0": (lambda robot: _catcher_terrain(*catcher_offsets()), (22, 1)),      # a new draw per environment
     "GapJumper-v0": (lambda robot: _gap_jumper_terrain(), (1, 6)),
     "PlatformJumper-v0": (lambda robot: _platform_jumper_terrain(), (1, 6)),
 }

@@ -142,6 +142,24 @@ FLIP_TASKS, FLIP_STEP = ("obstaclev0", "downstepper", "hurdler", "platformjumper
 DROP_TASKS = ("gapjumper",)
 
 
+# Catcher-v0 rewards the package's fall only below 5 voxels (manipulate.py:750-751), which the tumbling package reaches long after
+# 12 steps: before step FLIP_STEP the package is set down beside the robot, just above the ground
+LOWER_TASKS = ("catcher",)
+
+
+def lower_package(env):
+    r = env._sim._r
+    pos, vel, last, vt = r.get_state()
+    names = list(r.object_names)
+    ri, pi = r.object_info(names.index("robot")), r.object_info(names.index("package"))
+    rs, ps = slice(ri["min_point"], ri["max_point"] + 1), slice(pi["min_point"], pi["max_point"] + 1)
+    target = np.array([pos[rs][:, 0].max() + 0.3, 0.12])
+    pos[ps] += target - pos[ps].min(axis=0)
+    vel[ps] = 0.0
+    vt[ps] = 0.0
+    r.set_state(pos, vel, pos.copy(), vt)
+
+
 def drop_robot(env):
     r = env._sim._r
     pos, vel, last, vt = r.get_state()
@@ -185,7 +203,7 @@ def main():
     install_stubs()
 
     from evogym.envs.walk import Duck, SoftBridge, WalkingFlat
-    from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, LiftSmallRect, PushSmallRect, SlideBeam, ToppleBeam, PushSmallRectOnOppositeSide, ThrowSmallRect
+    from evogym.envs.manipulate import CarrySmallRect, CarrySmallRectToTable, CatchSmallRect, LiftSmallRect, PushSmallRect, SlideBeam, ToppleBeam, PushSmallRectOnOppositeSide, ThrowSmallRect
     from evogym.envs.climb import Climb0, Climb1, Climb2
     from evogym.envs.traverse import BlockSoup, FloatingPlatform, Gaps, StepsDown, StepsUp, VerticalBarrier, WalkingBumpy, WalkingBumpy2
     from evogym.envs.jump import StationaryJump
@@ -207,7 +225,7 @@ def main():
              "flipper": (Flipping, "Flipper-v0"), "beamtoppler": (ToppleBeam, "BeamToppler-v0"), "beamslider": (SlideBeam, "BeamSlider-v0"),
              "wingspan": (MaximizeXShape, "WingspanMazimizer-v0"), "height": (MaximizeYShape, "HeightMaximizer-v0"),
              "areamax": (MaximizeShape, "AreaMaximizer-v0"), "areamin": (MinimizeShape, "AreaMinimizer-v0"),
-             "traverser": (BlockSoup, "Traverser-v0")}
+             "traverser": (BlockSoup, "Traverser-v0"), "catcher": (CatchSmallRect, "Catcher-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
@@ -219,12 +237,14 @@ def main():
             body, conn = sample_robot((5, 5))
             rng = np.random.default_rng(500 + seed)
             out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": env_id}
-            if task in FLIP_TASKS or task in DROP_TASKS or task in TWIST_TASKS:
+            if task in FLIP_TASKS or task in DROP_TASKS or task in TWIST_TASKS or task in LOWER_TASKS:
                 out["flip_step"] = np.int32(FLIP_STEP)
             # ---- flat mode
             env = cls(body, conn, mode=None, env_id=env_id)
             n_act = env.get_actuator_indices("robot").size
             acts = rng.uniform(-1.0, 1.0, size=(n_steps, n_act))       # policy outputs; BenchmarkBase.step adds 1, base clips
+            if task == "catcher":                       # CatchSmallRect.reset re-draws the package's launch position (manipulate.py:815):
+                random.seed(1234)                       # the same draw for the flat and the modular environment
             obs0 = env.reset()
             flat_obs, rew, done = [np.asarray(obs0, dtype=np.float64)], [], []
             pre = {k: [] for k in ("pos", "vel", "pos_last", "vel_true", "goal")}
@@ -235,6 +255,8 @@ def main():
                     drop_robot(env)
                 if task in TWIST_TASKS and t == FLIP_STEP:
                     twist_robot(env)
+                if task in LOWER_TASKS and t == FLIP_STEP:
+                    lower_package(env)
                 # engine state the step starts from (teacher forcing in the GPU test)
                 st = env._sim._r.get_state()
                 for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
@@ -244,13 +266,19 @@ def main():
                 flat_obs.append(np.asarray(o, dtype=np.float64)); rew.append(float(r)); done.append(bool(d))
             from modularevogym_b200.world import WorldSpec
             out["world_json"] = json.dumps(WorldSpec.from_evoworld(env.world).to_dict())
+            if task == "catcher":
+                out["catch_offset"] = np.asarray([env.offsetx, env.offsety], dtype=np.int32)
             out.update({"pre_" + k: np.stack(v) for k, v in pre.items()})
             out.update(actions=acts, flat_obs=np.stack(flat_obs), reward=np.asarray(rew), done=np.asarray(done),
                        actuator_indices=env.get_actuator_indices("robot").astype(np.int32))
             # ---- modular mode, same policy outputs scattered over the voxel grid
             envm = cls(body, conn, mode="modular", env_id=env_id)
             act_mask = envm.act_mask.astype(bool)
+            if task == "catcher":
+                random.seed(1234)
             m0 = envm.reset()
+            if task == "catcher":
+                assert (envm.offsetx, envm.offsety) == (env.offsetx, env.offsety)
             mod_obs, other_obs, mrew, mdone = [np.asarray(m0["modular"], dtype=np.float64)], [np.asarray(m0["other"], dtype=np.float64)], [], []
             vox_acts = np.zeros((n_steps, body.size))
             for t in range(n_steps):
@@ -261,6 +289,8 @@ def main():
                     drop_robot(envm)
                 if task in TWIST_TASKS and t == FLIP_STEP:
                     twist_robot(envm)
+                if task in LOWER_TASKS and t == FLIP_STEP:
+                    lower_package(envm)
                 o, r, d, _ = envm.step(vox_acts[t].copy())
                 mod_obs.append(np.asarray(o["modular"], dtype=np.float64)); other_obs.append(np.asarray(o["other"], dtype=np.float64))
                 mrew.append(float(r)); mdone.append(bool(d))

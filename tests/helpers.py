@@ -40,8 +40,8 @@ class EnvGolden:
                      "Balancer-v0": 16, "Balancer-v1": 17, "GapJumper-v0": 18, "PlatformJumper-v0": 19,
                      "Carrier-v1": 20, "Lifter-v0": 21, "Flipper-v0": 22,
                      "BeamToppler-v0": 23, "BeamSlider-v0": 24, "WingspanMazimizer-v0": 25, "HeightMaximizer-v0": 26,
-                     "AreaMaximizer-v0": 27, "AreaMinimizer-v0": 28, "Traverser-v0": 30}[self.env_id]
-        self.package = "package" if self.task in (1, 2, 14, 15, 20, 21) else "beam" if self.task in (23, 24) else None
+                     "AreaMaximizer-v0": 27, "AreaMinimizer-v0": 28, "Traverser-v0": 30, "Catcher-v0": 31}[self.env_id]
+        self.package = "package" if self.task in (1, 2, 14, 15, 20, 21, 31) else "beam" if self.task in (23, 24) else None
         self.n_steps = int(self.z["reward"].shape[0])
 
     def __getitem__(self, k):
