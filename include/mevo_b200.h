@@ -239,13 +239,15 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
 #define MEVO_TASK_CLIMBER 3             /* Climb0, evogym/envs/climb.py:38-112 (Climber-v0): reward = rise of the centre of mass */
 #define MEVO_TASK_OBSTACLE_TRAVERSER 4  /* WalkingBumpy2, evogym/envs/traverse.py:350-426 (ObstacleTraverser-v1): "other" observation =
                                            [vel com 2, orientation 1, get_floor_obs("robot", ["ground"], 5) 11]; the flat observation
-                                           of this task holds [vel com, relative positions] only */
+                                           = [vel com, orientation, relative positions, floor sight] (traverse.py:396-401): in the flat rows
+                                           of all sighted tasks the sight blocks follow each environment's own relative positions */
 #define MEVO_TASK_BRIDGE_WALKER 5       /* SoftBridge, evogym/envs/walk.py:122-232 (BridgeWalker-v0): Walker's reward, goal at x > 60 voxels;
                                            "other" = [vel com 2, orientation 1]; flat = [vel com, orientation, relative positions] */
 /* the other environments of traverse.py's StairsBase family: reward, "other" observation and flat observation as
  * MEVO_TASK_OBSTACLE_TRAVERSER; goal column 79 / 69 / 74.  ObstacleTraverser-v0 and DownStepper-v0 also end the episode with
  * reward - 3 when the robot lies on its back (orientation in (pi/2, 3pi/2), traverse.py:226-228, 325-327).  UpStepper-v0 has
- * that rule (with a wider band) in flat mode only (traverse.py:124-129); this layer serves its modular mode, so it has none. */
+ * that rule (with a wider band) in flat mode only (traverse.py:124-129): MEVO_TASK_UP_STEPPER is the modular-mode environment
+ * (no such rule), MEVO_TASK_UP_STEPPER_FLAT the flat-mode one. */
 #define MEVO_TASK_OBSTACLE_TRAVERSER_V0 6   /* WalkingBumpy, traverse.py:251-347 */
 #define MEVO_TASK_UP_STEPPER 7              /* StepsUp, traverse.py:51-149 */
 #define MEVO_TASK_DOWN_STEPPER 8            /* StepsDown, traverse.py:152-248 */
@@ -295,6 +297,8 @@ int mevo_batch_object_obs_device(mevo_batch* b, int obj, double* device_out, int
                                                com x beyond voxel 59 ends the episode with + 2; "other" as task 18 with the pit and all blocks as terrain */
 #define MEVO_TASK_CATCHER 31                 /* CatchSmallRect, manipulate.py:630-886 (Catcher-v0): a package tumbles down from two pegs; reward = approach of
                                                robot and package in x + 10 x the package's fall below 5 voxels; observations laid out as task 23's */
+#define MEVO_TASK_UP_STEPPER_FLAT 32         /* StepsUp with mode=None, traverse.py:51-149: as task 7 plus "orientation in (pi/2 - pi/12, 3pi/2 + pi/12)
+                                               ends the episode with - 3" (traverse.py:124-129) */
 #define MEVO_DONE 1            /* done byte, bit 0: episode over (goal, unstable or step limit) */
 #define MEVO_DONE_TRUNCATED 2  /* bit 1: over only because of max_episode_steps (gym TimeLimit.truncated) */
 #define MEVO_DONE_UNSTABLE 4   /* bit 2: Sim::step reported an unstable simulation (reward already carries the -3) */

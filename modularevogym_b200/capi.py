@@ -122,7 +122,7 @@ MEVO_TASK_HURDLER, MEVO_TASK_CLIMBER_V1, MEVO_TASK_CAVE_CRAWLER, MEVO_TASK_CLIMB
 MEVO_TASK_CARRIER, MEVO_TASK_PUSHER_V1, MEVO_TASK_BALANCER, MEVO_TASK_BALANCER_V1 = 14, 15, 16, 17
 MEVO_TASK_GAP_JUMPER, MEVO_TASK_PLATFORM_JUMPER, MEVO_TASK_CARRIER_V1, MEVO_TASK_LIFTER, MEVO_TASK_FLIPPER = 18, 19, 20, 21, 22
 MEVO_TASK_BEAM_TOPPLER, MEVO_TASK_BEAM_SLIDER, MEVO_TASK_WINGSPAN, MEVO_TASK_HEIGHT = 23, 24, 25, 26
-MEVO_TASK_AREA_MAX, MEVO_TASK_AREA_MIN, MEVO_TASK_BIDIRECTIONAL_WALKER, MEVO_TASK_TRAVERSER, MEVO_TASK_CATCHER = 27, 28, 29, 30, 31
+MEVO_TASK_AREA_MAX, MEVO_TASK_AREA_MIN, MEVO_TASK_BIDIRECTIONAL_WALKER, MEVO_TASK_TRAVERSER, MEVO_TASK_CATCHER, MEVO_TASK_UP_STEPPER_FLAT = 27, 28, 29, 30, 31, 32
 MEVO_DONE, MEVO_DONE_TRUNCATED, MEVO_DONE_UNSTABLE = 1, 2, 4      # done byte bits (include/mevo_b200.h)
 
 _lib = None

@@ -144,7 +144,7 @@ public:
                           void* out, int stride, bool is_f32);                       // async on stream()
     // as above into a column block of a wider row: `width` columns written (zero padded), rows `row_stride` elements apart
     void sight_obs_strided_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
-                                  void* out, int width, int row_stride, bool is_f32);
+                                  void* out, int width, int row_stride, bool is_f32, const int* env_off = nullptr);   // env_off: device, + elements per env
     void sight_obs(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
                    double* out_host, int stride);
 

@@ -77,6 +77,7 @@ struct TaskParams {
     double fall_y;                       // > 0: a robot whose centre of mass is below this height [m] has fallen off: reward - 3, done
     const double* ort_now;
     double* ort_prev;
+    double ort_band;
     int* flips;                          // Flipper-v0: whole turns so far (flip.py:34, 78-85)
     double* span_prev;                   // Wingspan / Height maximizer: the robot's extent at the last observation
     int flat_prefix;                     // values in front of the relative positions in the flat observation
@@ -222,7 +223,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
             __syncwarp();
             if (lane == 0) g[1] = cur;
         }
-    } else if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19 || p.task == 30) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
+    } else if (p.task == 0 || (p.task >= 4 && p.task <= 8) || p.task == 10 || p.task == 12 || p.task == 18 || p.task == 19 || p.task == 30 || p.task == 32) {   // walk.py:70-84, 180-183, 295-298; traverse.py:20-26 (StairsBase.get_reward)
         reward = rf_x - ri_x;
     } else if (p.task == 3 || p.task == 11) {            // climb.py:96-99, 190-193
         reward = rf_y - ri_y;
@@ -299,7 +300,8 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     if (p.ort_now && p.task != 22) {
         // DownStepper-v0 / ObstacleTraverser-v0 / Hurdler-v0: a robot on its back ends the episode (traverse.py:226-228, 325-327, 514-516)
         const double ort = unstable ? p.ort_prev[env] : p.ort_now[env];
-        if (ort > kPi / 2 && ort < 3 * kPi / 2) { done = true; reward -= 3.0; }
+        // (UpStepper-v0 in flat mode: the band is pi / 12 wider on both sides, traverse.py:124-129)
+        if (ort > kPi / 2 - p.ort_band && ort < 3 * kPi / 2 + p.ort_band) { done = true; reward -= 3.0; }
     }
     if (p.task == 5 && rf_x > 60 * kVoxel) { done = true; reward += 1.0; }        // walk.py:190-193
     int flags = (done ? 1 : 0) | (unstable ? 4 : 0);
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     // ---- observations of the (possibly reset) state
     double oth[6];
     oth[2] = oth[3] = oth[4] = oth[5] = 0.0;
-    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19 || p.task == 30) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
+    if (p.task == 0 || (p.task >= 3 && p.task <= 13) || p.task == 18 || p.task == 19 || p.task == 30 || p.task == 32) {  // get_vel_com_obs (base.py:214-226 * VOXEL_SIZE, base.py:405-409)
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;  // task 4: orientation and floor sight follow in columns 2.. (host launches)
     } else if (p.task == 29) {                           // get_vel_com_obs, as Walker-v0
         oth[0] = R.cx * kVoxel; oth[1] = R.cy * kVoxel;
@@ -421,7 +423,7 @@ struct SightEnvRec {                     // 48 bytes per environment
 template <typename OutT>
 __global__ void __launch_bounds__(128) sight_kernel(const double* state, const EnvDesc* envs, const SightEnvRec* rec, const double2* st_pts,
                                                     int n_envs, int sight_dist, double sight_range, int ceil, OutT* out, int stride,
-                                                    int row_stride) {
+                                                    int row_stride, const int* env_off) {
     const int env = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (env >= n_envs) return;
@@ -434,7 +436,7 @@ __global__ void __launch_bounds__(128) sight_kernel(const double* state, const E
     if (r.o_count > 0) { cx /= r.o_count; cy /= r.o_count; }
     const double x_lo = cx - (sight_dist + 0.5), x_hi = cx + (sight_dist + 0.5);
     const int n_cols = 2 * sight_dist + 1;
-    OutT* row = out + (size_t)env * row_stride;
+    OutT* row = out + (size_t)env * row_stride + (env_off ? env_off[env] : 0);   // env_off: the block's column depends on the robot (flat rows)
     for (int c = 0; c < n_cols && c < stride; c++) {
         const int i = c - sight_dist;
         const double c_lo = cx + (i - 0.5), c_hi = cx + (i + 0.5);
@@ -544,9 +546,10 @@ const TaskDesc kTasks[] = {
     /* 29 */ {"BidirectionalWalker-v0", 0, 0, 0, false, 0, false, 2, 2, 2, -1, false, false, MEVO_NO_SIGHT},
     /* 30 */ {"Traverser-v0", 1, 59, 2, false, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5(kBlockSoup)},
     /* 31 */ {"Catcher-v0", 0, 0, 0, false, 0, true, 7, 7, 7, 6, true, true, MEVO_NO_SIGHT},
+    /* 32 */ {"UpStepper-v0 (flat mode)", 1, 69, 2, true, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
 };
 constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
-constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29;
+constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29, kTaskUpStepperFlat = 32;
 
 std::vector<std::string> split_names(const char* names) {
     std::vector<std::string> out;
@@ -584,15 +587,17 @@ struct Batch::Task {
     double* d_ort_prev = nullptr;
     int* d_flips = nullptr;              // Flipper-v0
     double* d_span_prev = nullptr;       // Wingspan / Height maximizer
+    int* d_flat_tail = nullptr;          // sighted tasks: 2 x robot points per environment = how far the sight blocks move right in the flat row
+    int flat_fixed = 0;                  // values in front of the relative positions in the flat row
     int* d_goals = nullptr;              // BidirectionalWalker-v0: kGoalStride ints per environment (TaskParams::goals)
     unsigned long long goal_seed = 0x6a09e667f3bcc909ull;
     int* d_episode = nullptr;
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_flat_tail); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_flat_tail = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -658,6 +663,12 @@ void Batch::task_build() {
     T.other_width = D.other_width;
     T.robot_obj = -1; T.package_obj = -1;
     T.flat_width = T.other_width; T.modular_width = 0; T.max_vox = 0;
+    // Flat rows of the sighted environments (traverse.py:96-102, 396-401, walk.py:282-287, climb.py:272-277, jump.py:60-64): the
+    // values of "other" with the relative positions inserted in front of the first sight block
+    int first_sight = -1;
+    for (const SightPart& sp : D.sight) if (sp.terrain && (first_sight < 0 || sp.col < first_sight)) first_sight = sp.col;
+    T.flat_fixed = first_sight >= 0 ? first_sight : D.flat_prefix;
+    std::vector<int> flat_tail(n, 0);
     for (int e = 0; e < n; e++) {
         const EnvHost& E = envs_[e];
         const int ro = E.world.find_object(T.robot);
@@ -712,7 +723,9 @@ void Batch::task_build() {
         T.obs_mask[e].assign(w * h, 1);
         std::fill(T.obs_mask[e].begin(), T.obs_mask[e].begin() + n_full, 0);
         r.n_act = std::min(k, E.n_act);
-        T.flat_width = std::max(T.flat_width, D.flat_prefix + 2 * r.r_count + (T.task == kTaskBiWalk ? 3 : 0));
+        T.flat_width = std::max(T.flat_width, first_sight >= 0 ? D.other_width + 2 * r.r_count
+                                                                 : D.flat_prefix + 2 * r.r_count + (T.task == kTaskBiWalk ? 3 : 0));
+        flat_tail[e] = 2 * r.r_count;
         T.modular_width = std::max(T.modular_width, 9 * w * h);
         T.max_vox = std::max(T.max_vox, w * h);
     }
@@ -721,6 +734,7 @@ void Batch::task_build() {
         CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&d), sizeof(Elem) * std::max<size_t>(1, v.size())));
         if (!v.empty()) CUDA_CHECK(cudaMemcpy(d, v.data(), sizeof(Elem) * v.size(), cudaMemcpyHostToDevice));
     };
+    up(T.d_flat_tail, flat_tail);
     up(T.d_rec, T.rec); up(T.d_vox_idx, T.vox_idx); up(T.d_vox_mat, T.vox_mat); up(T.d_act_vox, T.act_vox);
     CUDA_CHECK(cudaMalloc(&T.d_prev, sizeof(double) * 4 * n));
     CUDA_CHECK(cudaMalloc(&T.d_episode, sizeof(int) * n));
@@ -853,16 +867,20 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     const TaskDesc& D = kTasks[T.task];
     const bool ort_pair = D.ort_rule || T.task == kTaskFlipper;        // the kernel needs the orientation after the step and at the last observation
     p.other_width = D.kernel_width;
-    p.flat_prefix = D.flat_prefix;
+    p.flat_prefix = T.flat_fixed;
     p.goal_axis = D.goal_axis; p.goal = D.goal; p.goal_bonus = D.bonus;
     p.fall_y = D.fall_y;
     p.ort_now = nullptr; p.ort_prev = T.d_ort_prev;
+    p.ort_band = T.task == kTaskUpStepperFlat ? kPi / 12 : 0.0;
     p.flips = T.task == kTaskFlipper ? T.d_flips : nullptr;
     p.span_prev = T.task >= kTaskWingspan && T.task <= kTaskAreaMin ? T.d_span_prev : nullptr;
     p.goals = T.d_goals; p.goal_seed = T.goal_seed;          // the ShapeChange tasks (25 ... 28)
     if (other && other_stride < D.other_width)
         throw std::runtime_error("task_outputs: the 'other' observation of this task is " + std::to_string(D.other_width) + " wide");
-    if (flat && flat_stride < D.flat_prefix) throw std::runtime_error("task_outputs: the flat observation is narrower than its fixed part");
+    const bool sighted = D.sight[0].terrain || D.sight[1].terrain;
+    if (flat && flat_stride < (sighted ? T.flat_width : T.flat_fixed))
+        throw std::runtime_error(sighted ? "task_outputs: the flat observation of this task is " + std::to_string(T.flat_width) + " wide (mevo_batch_task_dims)"
+                                         : std::string("task_outputs: the flat observation is narrower than its fixed part"));
     if (ort_pair && (reward || done)) {
         object_orientation_strided_device(T.robot_obj, T.d_ort_now, 1, false);
         p.ort_now = T.d_ort_now;
@@ -877,13 +895,17 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     if (D.ort_col >= 0) {
         const int obj = D.ort_of_package ? T.package_obj : T.robot_obj;
         if (other) object_orientation_strided_device(obj, static_cast<char*>(other) + D.ort_col * el, other_stride, is_f32);
-        if (flat && D.ort_in_flat) object_orientation_strided_device(obj, static_cast<char*>(flat) + D.ort_col * el, flat_stride, is_f32);
+        if (flat && (D.ort_in_flat || (sighted && D.ort_col < T.flat_fixed))) object_orientation_strided_device(obj, static_cast<char*>(flat) + D.ort_col * el, flat_stride, is_f32);
     }
     if (ort_pair) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);
-    for (const SightPart& sp : D.sight)
+    for (const SightPart& sp : D.sight) {
         if (sp.terrain && other)
             sight_obs_strided_device(T.robot_obj, split_names(sp.terrain), sp.dist, 5.0, sp.ceil, static_cast<char*>(other) + sp.col * el,
                                      2 * sp.dist + 1, other_stride, is_f32);
+        if (sp.terrain && flat)                          // same block, behind this environment's relative positions
+            sight_obs_strided_device(T.robot_obj, split_names(sp.terrain), sp.dist, 5.0, sp.ceil, static_cast<char*>(flat) + sp.col * el,
+                                     2 * sp.dist + 1, flat_stride, is_f32, T.d_flat_tail);
+    }
     if (reset_done) for (auto& e : envs_) e.host_fresh = false;
 }
 
@@ -966,7 +988,7 @@ void Batch::sight_obs_device(int obj_index, const std::vector<std::string>& terr
 }
 
 void Batch::sight_obs_strided_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
-                                     void* out, int stride, int row_stride, bool is_f32) {
+                                     void* out, int stride, int row_stride, bool is_f32, const int* env_off) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     if (sight_dist < 0 || sight_dist > 1000) throw std::runtime_error("sight_obs: bad sight_dist");
@@ -1030,10 +1052,10 @@ void Batch::sight_obs_strided_device(int obj_index, const std::vector<std::strin
     const int grid = (n + 3) / 4;
     if (is_f32)
         sight_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
-                                                                    sight_dist, sight_range, ceil ? 1 : 0, static_cast<float*>(out), stride, row_stride);
+                                                                    sight_dist, sight_range, ceil ? 1 : 0, static_cast<float*>(out), stride, row_stride, env_off);
     else
         sight_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
-                                                                     sight_dist, sight_range, ceil ? 1 : 0, static_cast<double*>(out), stride, row_stride);
+                                                                     sight_dist, sight_range, ceil ? 1 : 0, static_cast<double*>(out), stride, row_stride, env_off);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -95,9 +95,8 @@ class BatchedEvoGymEnv:
         if env_id not in TASKS:
             raise ValueError(f"Environment not support: {env_id}")          # the reference's message (base.py:744)
         task, builder, package, limit = TASKS[env_id]
-        if task in (4, 6, 7, 8, 9, 10, 12, 13, 18, 19, 30) and mode != "modular":
-            raise ValueError(f"{env_id} is available in modular mode only (its flat observation interleaves orientation "
-                             "and sight values with a per-robot number of positions)")
+        if task == 7 and mode != "modular":
+            task = 32           # UpStepper-v0 ends the episode of a tilted robot in flat mode only (traverse.py:124-129): MEVO_TASK_UP_STEPPER_FLAT
         if task == 29 and mode == "modular":
             raise ValueError(f"{env_id} has no modular mode in the reference (evogym/envs/multi_goal.py:93); pass mode=None")
         self.env_id, self.mode, self.device_index = env_id, mode, device

@@ -172,7 +172,10 @@ def drop_robot(env):
 
 # Flipper-v0 counts whole turns when the orientation wraps between 0 and 2 pi (flip.py:78-85): before step FLIP_STEP the robot is
 # turned by +0.3 rad about its centre of mass (it sits at about -0.01 rad = 6.27 by then) and lifted clear of the floor
-TWIST_TASKS = ("flipper",)
+# UpStepper-v0 ends the episode of a tilted robot in FLAT mode only, and in a band pi / 12 wider than the other environments'
+# (traverse.py:124-129): its robot is turned by 1.4 rad -- inside (pi/2 - pi/12, pi/2) -- so the flat rollout ends there, the modular one goes on
+TWIST_TASKS = ("flipper", "upstepper")
+TWIST_ANGLE = {"flipper": 0.3, "upstepper": 1.4}
 
 
 def twist_robot(env, angle=0.3):
@@ -254,7 +257,7 @@ def main():
                 if task in DROP_TASKS and t == FLIP_STEP:
                     drop_robot(env)
                 if task in TWIST_TASKS and t == FLIP_STEP:
-                    twist_robot(env)
+                    twist_robot(env, TWIST_ANGLE[task])
                 if task in LOWER_TASKS and t == FLIP_STEP:
                     lower_package(env)
                 # engine state the step starts from (teacher forcing in the GPU test)
@@ -288,7 +291,7 @@ def main():
                 if task in DROP_TASKS and t == FLIP_STEP:
                     drop_robot(envm)
                 if task in TWIST_TASKS and t == FLIP_STEP:
-                    twist_robot(envm)
+                    twist_robot(envm, TWIST_ANGLE[task])
                 if task in LOWER_TASKS and t == FLIP_STEP:
                     lower_package(envm)
                 o, r, d, _ = envm.step(vox_acts[t].copy())
