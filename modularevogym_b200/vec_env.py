@@ -57,8 +57,9 @@ TASKS = {
     "AreaMinimizer-v0": (28, shape_change_world, None, 600),                  # change_shape.py:186-284, __init__.py:168-172
     "BidirectionalWalker-v0": (29, bidirectional_walker_world, None, 1000),   # multi_goal.py:91-205, __init__.py:206-210 (flat mode only)
     "Traverser-v0": (30, traverser_world, None, 600),                         # traverse.py:784-911, __init__.py:100-104
-    # Catcher-v0: the reference re-draws the package's launch position at EVERY reset (it rebuilds its world); here it is drawn per
-    # environment when the batch is built (construction, update()) -- episodes restarted on the device keep their environment's draw
+    # Catcher-v0: the reference re-draws the package's launch position at EVERY reset (it rebuilds its world and its simulator,
+    # manipulate.py:815).  Here it is drawn per environment whenever the batch is built -- construction, update() and reset(), which
+    # rebuilds the batch like the reference does -- while episodes restarted on the device keep their environment's draw
     "Catcher-v0": (31, catcher_world, "package", 400),                        # manipulate.py:630-886, __init__.py:155-159
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
@@ -102,6 +103,7 @@ class BatchedEvoGymEnv:
         self.env_id, self.mode, self.device_index = env_id, mode, device
         self.num_envs = len(bodies)
         self.bodies = [np.asarray(b) for b in bodies]
+        self._connections, self._own_worlds = connections, worlds is not None
         self.torch = torch
         self.device = torch.device("cuda", device)
         self.dtype = {"float32": torch.float32, "float64": torch.float64}[out_dtype]
@@ -167,9 +169,12 @@ class BatchedEvoGymEnv:
         return self._flat.data_ptr(), self._flat.shape[1], 0, 0, 0, 0
 
     # -- VecEnv surface
-    def reset(self):
+    def reset(self, rebuild: bool = True):
         """``venv.reset()``: every environment to snapshot 0; returns the observation (tensors owned by the env, overwritten
-        by the next ``step``)."""
+        by the next ``step``).  ``rebuild`` matters for Catcher-v0 only (see ``TASKS``)."""
+        if self.env_id == "Catcher-v0" and not self._own_worlds and rebuild:
+            self.close()                        # CatchSmallRect.reset: a new draw, a new world, a new simulator
+            self.__init__(bodies=self.bodies, connections=self._connections, **self._ctor)
         if self.env_id == "BidirectionalWalker-v0":
             # BiWalk.reset draws new goals from Python's global `random` (multi_goal.py:115-129, 183-184): the same calls, here
             self.B.task_set_goals([random_goals() for _ in range(self.num_envs)])
@@ -243,7 +248,7 @@ class BatchedEvoGymEnv:
         the batch is rebuilt (worlds are packed on all host cores) and the reset observation of the new robots is returned."""
         self.close()
         self.__init__(bodies=bodies, connections=connections, **self._ctor)
-        return self.reset()
+        return self.reset(rebuild=False)        # (Catcher-v0: update() draws once, manipulate.py:843-851)
 
 
 def make_vec_envs(env_name: str, robot_structures: Sequence, device: int = 0, mode: Optional[str] = "modular",
