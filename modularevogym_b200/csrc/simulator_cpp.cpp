@@ -405,6 +405,25 @@ public:
         out["flat"] = d[0]; out["modular"] = d[1]; out["other"] = d[2]; out["max_voxels"] = d[3]; out["action_stride"] = d[4];
         return out;
     }
+    // BidirectionalWalker-v0: goal lists (one sequence of x positions in voxels per environment, starting at env_first)
+    void task_set_goals(const std::vector<std::vector<int>>& goals, int env_first) {
+        size_t stride = 1;
+        for (const auto& g : goals) stride = std::max(stride, g.size());
+        std::vector<int> counts(goals.size()), table(goals.size() * stride, 0);
+        for (size_t i = 0; i < goals.size(); i++) {
+            counts[i] = (int)goals[i].size();
+            std::copy(goals[i].begin(), goals[i].end(), table.begin() + i * stride);
+        }
+        chk(mevo_batch_task_set_goals(b_, env_first, (int)goals.size(), counts.data(), table.data(), (int)stride));
+    }
+    void task_draw_goals(unsigned long long seed) { chk(mevo_batch_task_draw_goals(b_, seed)); }
+    py::dict task_get_goals(int env) {
+        int count = 0, current = 0, buf[64];
+        chk(mevo_batch_task_get_goals(b_, env, &count, &current, buf, 64));
+        py::dict out;
+        out["goals"] = std::vector<int>(buf, buf + count); out["current"] = current;
+        return out;
+    }
     py::dict task_env_tables(int env) {
         int d[5];
         chk(mevo_batch_task_dims(b_, d));
@@ -546,6 +565,9 @@ PYBIND11_MODULE(simulator_cpp, m) {
         .def("task_apply_policy_device", &BatchSim::task_apply_policy_device)
         .def("task_outputs", &BatchSim::task_outputs, py::arg("reset_done") = true)
         .def("task_outputs_device", &BatchSim::task_outputs_device)
+        .def("task_set_goals", &BatchSim::task_set_goals, py::arg("goals"), py::arg("env_first") = 0)
+        .def("task_draw_goals", &BatchSim::task_draw_goals)
+        .def("task_get_goals", &BatchSim::task_get_goals)
         .def("task_reset", &BatchSim::task_reset)
         .def("task_reset_device", &BatchSim::task_reset_device)
         .def_property_readonly("cuda_stream", &BatchSim::cuda_stream)

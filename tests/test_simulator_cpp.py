@@ -142,6 +142,39 @@ def test_batchsim_task_layer():
 
 
 @pytest.mark.gpu
+def test_batchsim_goal_lists():
+    """BatchSim's BidirectionalWalker-v0 goal lists (mevo_batch_task_set_goals / _draw_goals / _get_goals): first step of the
+    reference rollout whose first three goals are reached at once"""
+    import json
+    import os
+    from helpers import GOLDEN_DIR
+    from modularevogym_b200 import simulator_cpp as m
+    from modularevogym_b200.world import WorldSpec
+    with np.load(os.path.join(GOLDEN_DIR, "biwalk_near.npz")) as z:
+        g = {k: z[k] for k in z.files}
+    world = WorldSpec.from_dict(json.loads(str(g["world_json"])))
+    B = m.BatchSim(0)
+    e = B.begin_env(world.width, world.height)
+    for o in world.load_order():
+        assert B.add_object(e, o.grid.astype(np.float64), o.connections.astype(np.float64), o.name, o.x, o.y, o.is_robot)
+    B.finalize()
+    B.task_configure(29, "robot", None, 1000)
+    drawn = B.task_get_goals(0)
+    assert drawn["current"] == 0 and len(drawn["goals"]) >= 4 and all(20 <= x < 50 for x in drawn["goals"])
+    B.task_set_goals([g["goals"].tolist()])
+    assert B.task_get_goals(0)["goals"] == g["goals"].tolist()
+    r = B.task_reset()
+    assert rel_err(r["flat"][0], g["flat_obs"][0]) <= 1e-12
+    B.task_apply_policy(g["actions"][0][None, :], False)
+    assert not B.step(1).any()
+    o = B.task_outputs(False)
+    assert abs(o["reward"][0] - g["reward"][0]) <= 1e-9 and rel_err(o["flat"][0], g["flat_obs"][1]) <= 1e-9
+    assert B.task_get_goals(0)["current"] == int(g["current_goal"][0]) == 3
+    B.task_draw_goals(5)
+    assert B.task_get_goals(0)["goals"] != g["goals"].tolist()
+
+
+@pytest.mark.gpu
 def test_several_sims_of_different_sizes_step_alternately():
     """a design loop keeps several `Sim`s alive in one process and steps them in turn: robots of different size classes (a later,
     smaller one must not lower a kernel's shared-memory limit under an earlier, larger one); each equals the same Sim stepped alone"""
