@@ -84,7 +84,9 @@ BUILDERS = [("Walker-v0", W.walker_world, (1, 1)), ("Pusher-v0", W.pusher_world,
             ("GapJumper-v0", W.gap_jumper_world, (1, 6)), ("PlatformJumper-v0", W.platform_jumper_world, (1, 6)),
             ("Carrier-v1", W.carrier_v1_world, (1, 4)), ("Lifter-v0", W.lifter_world, (2, 3)),
             ("Flipper-v0", W.flipper_world, (60, 1)), ("BeamToppler-v0", W.beam_toppler_world, (1, 1)),
-            ("BeamSlider-v0", W.beam_slider_world, (1, 1)), ("ShapeChange", W.shape_change_world, (7, 1))]
+            ("BeamSlider-v0", W.beam_slider_world, (1, 1)), ("ShapeChange", W.shape_change_world, (7, 1)),
+            ("BidirectionalWalker-v0", W.bidirectional_walker_world, (33, 1))]
+# (Traverser-v0 and Catcher-v0 add objects in their environments' code: pinned against the environments' own worlds in test_task_layer.py)
 
 
 @pytest.mark.parametrize("env_id,builder,at", BUILDERS)
