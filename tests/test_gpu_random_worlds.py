@@ -28,13 +28,18 @@ def random_world(seed: int):
     assert probe.add_object(floor, cn, "floor", 0, 0, False)
     spec.add_from_array("floor", floor.astype(np.int64), 0, 0, cn.astype(np.int64))
     robots = []
-    for k in range(int(rng.integers(2, 6))):
+    # every fourth world: 9 ... 14 small objects -- more simulated objects than the warp kernels' eight (group kernels, 6-bit object
+    # field of the pair codes); at most four of them robots (robots own the eight self-collision counters)
+    many = seed % 4 == 3
+    for k in range(int(rng.integers(9, 15)) if many else int(rng.integers(2, 6))):
         for _try in range(20):
-            h, w = int(rng.integers(1, 7)), int(rng.integers(1, 7))
+            h, w = (int(rng.integers(1, 4)), int(rng.integers(1, 4))) if many else (int(rng.integers(1, 7)), int(rng.integers(1, 7)))
             grid, c = random_object(rng, h, w, p_empty=float(rng.choice([0.0, 0.2, 0.4])), p_drop=float(rng.choice([0.0, 0.0, 0.2])))
+            if many and k >= 4:
+                grid = np.where((grid == 3) | (grid == 4), 2, grid)
             if not grid.any():
                 continue
-            x, y = int(rng.integers(0, W - w + 1)), int(rng.integers(1, 5))
+            x, y = int(rng.integers(0, W - w + 1)), int(rng.integers(1, 12 if many else 5))
             is_robot = bool(((grid == 3) | (grid == 4)).any())
             name = f"{'robot' if is_robot else 'thing'}{k}"
             n0 = probe.num_objects
@@ -72,6 +77,7 @@ def test_random_worlds_teacher_forced(kernel, monkeypatch):
     # gather record, DesignHeader::o_csrx)
     deg = [np.bincount(np.concatenate((r.edges()["a"], r.edges()["b"]))).max() for r in refs]
     assert max(deg) > 8, deg
+    assert max(sum(1 for o in range(B.num_objects(i)) if not static_objs[i][o]) for i in range(n)) > 8
     rngs = [np.random.default_rng(90 + i) for i in range(n)]
     live = [True] * n
     exact = total = contacts = 0
