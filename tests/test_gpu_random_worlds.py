@@ -122,3 +122,25 @@ def test_random_worlds_teacher_forced(kernel, monkeypatch):
                 live[i] = False
     print(f"\n[random worlds, {kernel}] {sum(d > 8 for d in deg)} of {n} worlds with a point of more than 8 springs (max {max(deg)}); {total} substeps, {exact} bit-identical, {contacts} with contacts, worst rel err pos/vel/vel_true/cf {worst}")
     B.close()
+
+
+def test_object_limits_are_refused_with_a_message():
+    """nine robots (eight self-collision counters) and 65 simulated objects (6-bit object field) are refused when the batch is packed"""
+    def world(n_objects, n_robots):
+        w = WorldSpec(width=3 * n_objects + 2, height=6)
+        w.add_from_array("floor", np.full((1, 3 * n_objects + 2), 5, dtype=np.int64), 0, 0)
+        for k in range(n_objects):
+            w.add_from_array(f"{'robot' if k < n_robots else 'thing'}{k:02d}", np.array([[3 if k < n_robots else 2]], dtype=np.int64), 1 + 3 * k, 2)
+        return w
+    for n_objects, n_robots, msg in ((9, 9, "robots"), (65, 2, "dynamic objects")):
+        B = capi.Batch(0)
+        B.add_world(world(n_objects, n_robots))
+        with pytest.raises(capi.MevoError, match=msg):
+            B.finalize()
+        B.close()
+    B = capi.Batch(0)                       # 8 robots + 56 things: accepted, and steps
+    B.add_world(world(64, 8))
+    B.finalize()
+    n_unstable, flags = B.step(2, apply_actions=False)
+    assert n_unstable == 0 and not flags.any()
+    B.close()
