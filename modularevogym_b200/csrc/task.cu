@@ -408,6 +408,8 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
     }
 }
 
+constexpr int kSightCols = 64;            // sight blocks up to this many columns (sight_dist <= 31) are computed in one pass
+
 struct SightEnvRec {                     // 48 bytes per environment
     int o_start, o_count;                // observed object: dynamic-local point range
     int Pd;
@@ -437,32 +439,73 @@ __global__ void __launch_bounds__(128) sight_kernel(const double* state, const E
     const double x_lo = cx - (sight_dist + 0.5), x_hi = cx + (sight_dist + 0.5);
     const int n_cols = 2 * sight_dist + 1;
     OutT* row = out + (size_t)env * row_stride + (env_off ? env_off[env] : 0);   // env_off: the block's column depends on the robot (flat rows)
-    for (int c = 0; c < n_cols && c < stride; c++) {
-        const int i = c - sight_dist;
-        const double c_lo = cx + (i - 0.5), c_hi = cx + (i + 0.5);
-        double best = 0.0;
-        bool any = false;
+    if (n_cols <= kSightCols) {
+        // ONE pass over the terrain points.  The columns are the open intervals (cx + i - 0.5, cx + i + 0.5): neighbours share their
+        // end point, so a point lies in at most one of them -- found from the rounded offset and confirmed (against its two neighbours
+        // too: x - cx rounds) with the reference's own comparisons.  Per column the highest (floor) / lowest (ceiling) y is kept as an
+        // order-preserving integer key in shared memory; a maximum does not depend on the visiting order, so the result is the
+        // column-by-column scan's, bit for bit.
+        __shared__ unsigned long long s_key[4][kSightCols];
+        unsigned long long* key = s_key[(threadIdx.x >> 5) & 3];
+        const unsigned long long none = ceil ? ~0ull : 0ull;
+        for (int c = lane; c < n_cols; c += 32) key[c] = none;
+        __syncwarp();
         auto visit = [&](double2 q) {
             const double x = q.x / kVoxel, y = q.y / kVoxel;
             if (!(x > x_lo) || !(x < x_hi)) return;
             if (ceil ? !(y > cy) : !(y < cy)) return;
-            if (!(x > c_lo) || !(x < c_hi)) return;
-            if (!any) { best = y; any = true; }
-            else best = ceil ? fmin(best, y) : fmax(best, y);
+            const int g = (int)floor(x - cx + 0.5);
+            for (int i = g - 1; i <= g + 1; i++) {
+                if (i < -sight_dist || i > sight_dist) continue;
+                const double c_lo = cx + (i - 0.5), c_hi = cx + (i + 0.5);
+                if (!(x > c_lo) || !(x < c_hi)) continue;
+                const long long b = __double_as_longlong(y);
+                const unsigned long long k = b < 0 ? ~(unsigned long long)b : (unsigned long long)b | 0x8000000000000000ull;
+                if (ceil) atomicMin(&key[i + sight_dist], k); else atomicMax(&key[i + sight_dist], k);
+                break;
+            }
         };
         for (int k = lane; k < r.st_count; k += 32) visit(st_pts[r.st_off + k]);
         for (int s = 0; s < r.n_dyn; s++)
             for (int k = lane; k < r.dyn_count[s]; k += 32) visit(pos[r.dyn_start[s] + k]);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-            const bool oa = __shfl_xor_sync(0xffffffffu, any ? 1 : 0, o) != 0;
-            if (oa) { best = any ? (ceil ? fmin(best, ob) : fmax(best, ob)) : ob; any = true; }
+        __syncwarp();
+        for (int c = lane; c < n_cols && c < stride; c += 32) {
+            const unsigned long long k = key[c];
+            const bool any = k != none;
+            const double best = __longlong_as_double((k & 0x8000000000000000ull) ? (long long)(k & 0x7fffffffffffffffull) : (long long)~k);
+            double elev = any ? best : (ceil ? (0.0 + sight_range) + cy : (0.0 - sight_range) + cy);
+            elev = ceil ? elev - cy : cy - elev;
+            elev = fmin(fmax(elev, 0.0), sight_range);
+            row[c] = (OutT)(elev * kVoxel);
         }
-        double elev = any ? best : (ceil ? (0.0 + sight_range) + cy : (0.0 - sight_range) + cy);
-        elev = ceil ? elev - cy : cy - elev;
-        elev = fmin(fmax(elev, 0.0), sight_range);
-        if (lane == 0) row[c] = (OutT)(elev * kVoxel);
+    } else {                                             // wider than any environment of the reference looks: column by column
+        for (int c = 0; c < n_cols && c < stride; c++) {
+            const int i = c - sight_dist;
+            const double c_lo = cx + (i - 0.5), c_hi = cx + (i + 0.5);
+            double best = 0.0;
+            bool any = false;
+            auto visit = [&](double2 q) {
+                const double x = q.x / kVoxel, y = q.y / kVoxel;
+                if (!(x > x_lo) || !(x < x_hi)) return;
+                if (ceil ? !(y > cy) : !(y < cy)) return;
+                if (!(x > c_lo) || !(x < c_hi)) return;
+                if (!any) { best = y; any = true; }
+                else best = ceil ? fmin(best, y) : fmax(best, y);
+            };
+            for (int k = lane; k < r.st_count; k += 32) visit(st_pts[r.st_off + k]);
+            for (int s = 0; s < r.n_dyn; s++)
+                for (int k = lane; k < r.dyn_count[s]; k += 32) visit(pos[r.dyn_start[s] + k]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+                const bool oa = __shfl_xor_sync(0xffffffffu, any ? 1 : 0, o) != 0;
+                if (oa) { best = any ? (ceil ? fmin(best, ob) : fmax(best, ob)) : ob; any = true; }
+            }
+            double elev = any ? best : (ceil ? (0.0 + sight_range) + cy : (0.0 - sight_range) + cy);
+            elev = ceil ? elev - cy : cy - elev;
+            elev = fmin(fmax(elev, 0.0), sight_range);
+            if (lane == 0) row[c] = (OutT)(elev * kVoxel);
+        }
     }
     for (int c = n_cols + lane; c < stride; c += 32) row[c] = (OutT)0;
 }
