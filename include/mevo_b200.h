@@ -334,6 +334,12 @@ int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* 
 int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
                                  int other_stride, int is_f32);
 
+/* Optional second form of the done byte: `device_planes` points to 3 * n_envs bytes on the device; every later
+ * mevo_batch_task_outputs[_device] call that writes `done` also writes done / truncated / unstable as 0 or 1 into the three planes
+ * (the layout of a bool tensor of shape (3, n): what SubprocVecEnv's `done` array and the TimeLimit / unstable infos are).  The
+ * buffer belongs to the caller and must outlive the calls; NULL switches the planes off.  Cleared by mevo_batch_task_configure. */
+int mevo_batch_task_bind_flag_planes(mevo_batch* b, void* device_planes);
+
 /* BidirectionalWalker-v0 (evogym/envs/multi_goal.py:91-205, task 29): each environment walks to a list of x positions in turn
  * (WalkToX, multi_goal.py:62-88).  The reference draws a new list in __init__ and in every reset() from Python's global `random`
  * (set_random_goals(20, 50, 100), multi_goal.py:115-129).  Here every environment gets a list when the task tables are built and a

@@ -95,6 +95,7 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_task_outputs": (_i, [_vp, _dp, _bp, _dp, _i, _dp, _i, _dp, _i, _i]),
     "mevo_batch_task_outputs_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i]),
     "mevo_batch_task_reset": (_i, [_vp, _dp, _i, _dp, _i, _dp, _i]),
+    "mevo_batch_task_bind_flag_planes": (_i, [_vp, _vp]),
     "mevo_batch_task_set_goals": (_i, [_vp, _i, _i, _ip, _ip, _i]),
     "mevo_batch_task_draw_goals": (_i, [_vp, C.c_ulonglong]),
     "mevo_batch_task_get_goals": (_i, [_vp, _i, _ip, _ip, _ip, _i]),
@@ -556,6 +557,11 @@ class Batch:
         vp = lambda p: C.c_void_p(p) if p else None
         _check(self.L.mevo_batch_task_reset_device(self.h, vp(flat_ptr), int(flat_stride), vp(modular_ptr), int(modular_stride),
                                                    vp(other_ptr), int(other_stride), int(is_f32)))
+
+    def task_bind_flag_planes(self, device_ptr: int) -> None:
+        """``device_ptr``: 3 * n bytes (a ``torch.bool`` tensor of shape (3, n)) that every later task_outputs call fills with done /
+        truncated / unstable as 0 / 1; 0 switches it off"""
+        _check(self.L.mevo_batch_task_bind_flag_planes(self.h, C.c_void_p(device_ptr) if device_ptr else None))
 
     def task_set_goals(self, goals, env_first: int = 0) -> None:
         """BidirectionalWalker-v0: ``goals`` is one sequence of x positions (voxels) per environment, starting at ``env_first``

@@ -589,6 +589,13 @@ int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, voi
     });
 }
 
+int mevo_batch_task_bind_flag_planes(mevo_batch* b, void* device_planes) {
+    return guard([&] {
+        b->impl.task_bind_flag_planes(device_planes);
+        return 0;
+    });
+}
+
 int mevo_batch_task_set_goals(mevo_batch* b, int env_first, int n_envs, const int* counts, const int* goals, int stride) {
     return guard([&] {
         if (n_envs > 0 && (!counts || !goals)) throw std::runtime_error("mevo_batch_task_set_goals: null argument");

@@ -66,6 +66,7 @@ struct TaskParams {
     unsigned char* unstable;             // flags of the last step launch (cleared for environments reset here)
     int* sim_time;
     void* reward; unsigned char* done;
+    unsigned char* flag_planes;          // optional: 3 x n_envs bytes (0 / 1) -- done, truncated, unstable -- next to the bit field in `done`
     void* flat; int flat_stride;
     void* modular; int modular_stride;
     void* other; int other_stride;
@@ -344,6 +345,9 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         p.prev[4 * env] = R.ax; p.prev[4 * env + 1] = R.ay; p.prev[4 * env + 2] = P.ax; p.prev[4 * env + 3] = P.ay;
         if (p.reward) reinterpret_cast<OutT*>(p.reward)[env] = (OutT)reward;
         if (p.done) p.done[env] = (unsigned char)flags;
+        if (p.flag_planes && p.done) {
+            p.flag_planes[env] = flags & 1; p.flag_planes[p.n_envs + env] = (flags >> 1) & 1; p.flag_planes[2 * p.n_envs + env] = (flags >> 2) & 1;
+        }
     }
 
     // ---- observations of the (possibly reset) state
@@ -630,6 +634,7 @@ struct Batch::Task {
     double* d_ort_prev = nullptr;
     int* d_flips = nullptr;              // Flipper-v0
     double* d_span_prev = nullptr;       // Wingspan / Height maximizer
+    unsigned char* d_flag_planes = nullptr;      // caller's buffer (mevo_batch_task_bind_flag_planes), not owned
     int* d_flat_tail = nullptr;          // sighted tasks: 2 x robot points per environment = how far the sight blocks move right in the flat row
     int flat_fixed = 0;                  // values in front of the relative positions in the flat row
     int* d_goals = nullptr;              // BidirectionalWalker-v0: kGoalStride ints per environment (TaskParams::goals)
@@ -688,6 +693,7 @@ void Batch::task_configure(int task, const std::string& robot, const std::string
     task_->package = needs_package ? package : std::string();
     task_->max_episode_steps = max_episode_steps;
     task_->epoch = -1;
+    task_->d_flag_planes = nullptr;
 }
 
 void Batch::task_build() {
@@ -834,6 +840,13 @@ void Batch::task_draw_goals(unsigned long long seed) {
     CUDA_CHECK(cudaGetLastError());
 }
 
+// The done byte of task_outputs as three byte planes of 0 / 1 (done, truncated, unstable; n_envs bytes each) in a device buffer of the
+// caller -- what a torch.bool tensor of shape (3, n) is -- so that a vec-env front needs no kernels of its own to split the bit field.
+void Batch::task_bind_flag_planes(void* device_planes) {
+    if (!task_) throw std::runtime_error("task layer used before mevo_batch_task_configure");
+    task_->d_flag_planes = static_cast<unsigned char*>(device_planes);
+}
+
 // (count, current index, goals ...) of one environment, for hosts and tests
 int Batch::task_get_goals(int env, int* out, int cap) {
     task_build();
@@ -903,7 +916,7 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.envs = reinterpret_cast<const EnvDesc*>(d_envdesc_);
     p.tenv = T.d_rec; p.vox_idx = T.d_vox_idx; p.vox_mat = T.d_vox_mat;
     p.prev = T.d_prev; p.episode_len = T.d_episode; p.unstable = d_unstable_; p.sim_time = d_time_;
-    p.reward = reward; p.done = done;
+    p.reward = reward; p.done = done; p.flag_planes = T.d_flag_planes;
     p.flat = flat; p.flat_stride = flat_stride; p.modular = modular; p.modular_stride = modular_stride;
     p.other = other; p.other_stride = other_stride;
     p.n_envs = num_envs(); p.task = T.task; p.max_episode_steps = T.max_episode_steps; p.reset_done = reset_done ? 1 : 0;

@@ -136,6 +136,9 @@ class BatchedEvoGymEnv:
         self._other = torch.zeros((n, d["other"]), device=dev, dtype=dt)
         self._reward = torch.zeros((n, 1), device=dev, dtype=dt)
         self._done = torch.zeros((n,), device=dev, dtype=torch.uint8)
+        # done / truncated / unstable as bool rows, written by the task kernel next to the bit field (no kernels here to split it)
+        self._flags = torch.zeros((3, n), device=dev, dtype=torch.bool)
+        self.B.task_bind_flag_planes(self._flags.data_ptr())
         am = np.ones((n, d["max_voxels"]), dtype=np.int64)
         om = np.ones((n, d["max_voxels"]), dtype=np.int64)
         for i, body in enumerate(self.bodies):          # get_act_mask / get_obs_mask (evogym/envs/base.py:530-560), as task_env_tables reports them
@@ -186,7 +189,8 @@ class BatchedEvoGymEnv:
     def step(self, actions):
         """``actions``: (n, voxels) in modular mode, (n, actuators) otherwise -- raw policy outputs (the environment adds 1 and
         clips to [0.6, 1.6] like ``BenchmarkBase.step``); a CUDA tensor (float32 / float64) or anything ``torch.as_tensor`` takes.
-        Returns ``obs, reward (n, 1), done (n,) bool, infos`` with ``infos = {'truncated': ..., 'unstable': ...}`` tensors."""
+        Returns ``obs, reward (n, 1), done (n,) bool, infos`` with ``infos = {'truncated': ..., 'unstable': ...}`` tensors (all
+        owned by the env and overwritten by the next ``step``, like the observation)."""
         torch = self.torch
         a = torch.as_tensor(actions)
         if a.dtype not in (torch.float32, torch.float64):
@@ -212,9 +216,8 @@ class BatchedEvoGymEnv:
                 self._enqueue_step(a.data_ptr(), a.shape[1], a.dtype == torch.float32)
                 self._eager_steps += 1
         self._wait()
-        done = (self._done & 1).bool()
-        infos = {"truncated": (self._done & 2).bool(), "unstable": (self._done & 4).bool()}
-        return self._obs(), self._reward, done, infos
+        infos = {"truncated": self._flags[1], "unstable": self._flags[2]}
+        return self._obs(), self._reward, self._flags[0], infos
 
     def _enqueue_step(self, act_ptr: int, act_stride: int, act_f32: bool) -> None:
         self.B.task_apply_policy_device(act_ptr, act_stride, self.mode == "modular", act_f32)

@@ -3,7 +3,7 @@
 actuator targets -> 30 substeps -> reward / done / modular observation (float32) + reset of finished environments, three
 launches per env-step on one stream, no host round trip.  CUDA events on the engine's stream.
 
-    python tools/bench_vec_env.py [env_id:n_envs ...]
+    python tools/bench_vec_env.py [--warmup=W] [--steps=K] [env_id:n_envs ...]
 """
 import json
 import os
@@ -18,7 +18,8 @@ def main():
     import torch
     from modularevogym_b200.vec_env import BatchedEvoGymEnv
     from modularevogym_b200.world import sample_robot
-    specs = sys.argv[1:] or ["Walker-v0:4096", "Pusher-v0:4096", "Thrower-v0:4096", "Climber-v0:4096", "ObstacleTraverser-v1:4096"]
+    opts = dict(a[2:].split("=") for a in sys.argv[1:] if a.startswith("--"))
+    specs = [a for a in sys.argv[1:] if not a.startswith("--")] or ["Walker-v0:4096", "Pusher-v0:4096", "Thrower-v0:4096", "Climber-v0:4096", "ObstacleTraverser-v1:4096"]
     for spec in specs:
         env_id, n = spec.split(":")
         n = int(n)
@@ -29,14 +30,16 @@ def main():
             bodies.append(b); conns.append(c)
         env = BatchedEvoGymEnv(env_id, bodies, conns, device=0, mode="modular")
         env.reset()
-        K, W = 100, 5
+        K, W = int(opts.get("steps", 100)), int(opts.get("warmup", 50))
         g = torch.Generator(device="cuda").manual_seed(0)
         acts = torch.rand((K + W, n, env.action_width), device="cuda", generator=g) * 2 - 1
         stream = env._stream
         n_done = 0
         print("built", env_id, n, file=sys.stderr, flush=True)
-        for s in range(W):
-            env.step(acts[s])
+        for s in range(W):                      # the warm-up runs the loop's own consumer of `done` too: its first use loads torch's
+            _, _, done, _ = env.step(acts[s])   # reduction kernels, which does not belong in the timed region
+            n_done = n_done + done.sum()
+        n_done = 0
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         import time
