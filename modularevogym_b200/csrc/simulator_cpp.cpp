@@ -416,6 +416,7 @@ public:
         }
         chk(mevo_batch_task_set_goals(b_, env_first, (int)goals.size(), counts.data(), table.data(), (int)stride));
     }
+    void task_bind_flag_planes(std::uintptr_t device_planes) { chk(mevo_batch_task_bind_flag_planes(b_, reinterpret_cast<void*>(device_planes))); }
     void task_draw_goals(unsigned long long seed) { chk(mevo_batch_task_draw_goals(b_, seed)); }
     py::dict task_get_goals(int env) {
         int count = 0, current = 0, buf[64];
@@ -566,6 +567,7 @@ PYBIND11_MODULE(simulator_cpp, m) {
         .def("task_outputs", &BatchSim::task_outputs, py::arg("reset_done") = true)
         .def("task_outputs_device", &BatchSim::task_outputs_device)
         .def("task_set_goals", &BatchSim::task_set_goals, py::arg("goals"), py::arg("env_first") = 0)
+        .def("task_bind_flag_planes", &BatchSim::task_bind_flag_planes)
         .def("task_draw_goals", &BatchSim::task_draw_goals)
         .def("task_get_goals", &BatchSim::task_get_goals)
         .def("task_reset", &BatchSim::task_reset)
