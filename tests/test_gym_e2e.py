@@ -26,4 +26,4 @@ def test_reference_gym_envs_run_on_this_engine():
     lines = [json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")]
     assert lines[-1]["summary"] == "ok"
     assert lines[-1]["fixtures"] >= 40
-    assert sum(1 for l in lines if "smoke" in l) == 31
+    assert sum(1 for l in lines if "smoke" in l) == 32

@@ -160,6 +160,24 @@ def main():
         log.append(rec)
         print(json.dumps(rec), flush=True)
 
+    # BidirectionalWalker-v0 has neither a modular mode nor update(): the same rollout in flat mode
+    body, connections = sample_robot((5, 5))
+    env = gym.make("BidirectionalWalker-v0", body=body, connections=connections)
+    ob = env.reset()
+    steps, ret = 0, 0.0
+    while True:
+        ob, reward, done, info = env.step(np.random.uniform(low=-1.0, high=1.0, size=env.action_space.shape[0]))
+        steps += 1
+        ret += float(reward)
+        if done:
+            break
+    env.close()
+    rec = {"smoke": "BidirectionalWalker-v0", "steps_until_done": steps, "return": ret, "finite": bool(np.isfinite(ret) and np.isfinite(ob).all()),
+           "truncated": bool(info.get("TimeLimit.truncated", False)), "mode": "flat"}
+    ok &= rec["finite"]
+    log.append(rec)
+    print(json.dumps(rec), flush=True)
+
     summary = {"summary": "ok" if ok else "MISMATCH", "fixtures": sum(1 for r in log if "fixture" in r), "tolerance": {"reward": TOL_REWARD, "obs": TOL_OBS}}
     print(json.dumps(summary), flush=True)
     if args.out:
