@@ -319,11 +319,13 @@ int mevo_batch_task_apply_policy_device(mevo_batch* b, const void* device_action
 /* after mevo_batch_step*: reward (n_envs), done bytes (n_envs), observations (n_envs x stride, zero padded); any
  * output may be NULL.  reset_done = 1: environments that are done are reverted to snapshot 0 first and their
  * observation is the reset observation (vec-env semantics). */
-/* NOTE on unstable steps: Sim::step leaves the partially advanced state live and its getters read the last SAVED snapshot
- * (Sim.cpp:105-115, history[sim_time]).  With reset_done = 1 (the vec-env semantics this layer is built for) an unstable
- * environment is reverted and reports the reset observation, like the reference's worker.  With reset_done = 0 the observation
- * of an unstable environment is computed from the live, partially advanced state -- reward and done are exact either way; a
- * caller that needs the pre-step observation keeps it from the previous call or reverts a snapshot slot. */
+/* NOTE on unstable steps: Sim::step leaves the partially advanced state live, saves no snapshot and does not advance time; the
+ * environment's getters read the last SAVED snapshot (Sim.cpp:105-115, history[sim_time]).  The task layer keeps that snapshot's
+ * positions and velocities per environment (written by every call for the environments whose step went through, or that it reset):
+ * reward, done, the observation returned for an unstable step and the "before" values of the steps after it are the reference's
+ * also with reset_done = 0, while the live state (mevo_env_get_state, the next mevo_batch_step) stays partially advanced as in
+ * the reference.  With reset_done = 1 an unstable environment is reverted and reports the reset observation, like the
+ * reference's vec-env worker. */
 int mevo_batch_task_outputs(mevo_batch* b, double* reward, unsigned char* done, double* flat, int flat_stride, double* modular,
                             int modular_stride, double* other, int other_stride, int reset_done);
 int mevo_batch_task_outputs_device(mevo_batch* b, void* reward, unsigned char* done, void* flat, int flat_stride, void* modular,

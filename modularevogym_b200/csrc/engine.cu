@@ -1671,17 +1671,17 @@ void Batch::object_com_device(int obj_index, double* out_device_2n) {
     CUDA_CHECK(cudaGetLastError());
 }
 
-void Batch::object_orientation_strided_device(int obj_index, void* out, int row_stride, bool is_f32) {
+void Batch::object_orientation_strided_device(int obj_index, void* out, int row_stride, bool is_f32, const double* state_like) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     const int n = num_envs();
     bind_object_ranges(obj_index);
     const EnvDesc* ed = reinterpret_cast<const EnvDesc*>(d_envdesc_);
     if (is_f32)
-        orientation_kernel<float><<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, ed, impl_->d_com_ranges, n,
+        orientation_kernel<float><<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(state_like ? state_like : d_state_, d_state0_, ed, impl_->d_com_ranges, n,
                                                                                  static_cast<float*>(out), row_stride);
     else
-        orientation_kernel<double><<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(d_state_, d_state0_, ed, impl_->d_com_ranges, n,
+        orientation_kernel<double><<<(n + 3) / 4, 128, 0, (cudaStream_t)stream_>>>(state_like ? state_like : d_state_, d_state0_, ed, impl_->d_com_ranges, n,
                                                                                   static_cast<double*>(out), row_stride);
     CUDA_CHECK(cudaGetLastError());
 }

@@ -111,7 +111,8 @@ public:
     // Environment::object_orientation_at_time of object `obj_index` per env: current state against snapshot 0
     void object_orientation(int obj_index, double* out_host_n);
     void object_orientation_device(int obj_index, double* out_device_n);   // async on stream()
-    void object_orientation_strided_device(int obj_index, void* out, int row_stride, bool is_f32);   // out[env * row_stride]
+    // out[env * row_stride]; state_like: a device buffer laid out like the state (the task layer's saved snapshot), nullptr = the live state
+    void object_orientation_strided_device(int obj_index, void* out, int row_stride, bool is_f32, const double* state_like = nullptr);
     // Walker-style observation rows [vel com (2), relative x (n), relative y (n), zero padding] (evogym/envs/walk.py:58-61)
     int object_obs_width(int obj_index) const;                       // 2 + 2 * (largest point count of the object)
     void object_obs_device(int obj_index, double* out_device, int stride);   // async on stream()
@@ -145,7 +146,8 @@ public:
                           void* out, int stride, bool is_f32);                       // async on stream()
     // as above into a column block of a wider row: `width` columns written (zero padded), rows `row_stride` elements apart
     void sight_obs_strided_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
-                                  void* out, int width, int row_stride, bool is_f32, const int* env_off = nullptr);   // env_off: device, + elements per env
+                                  void* out, int width, int row_stride, bool is_f32, const int* env_off = nullptr,   // env_off: device, + elements per env
+                                  const double* state_like = nullptr);
     void sight_obs(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
                    double* out_host, int stride);
 

@@ -57,6 +57,7 @@ struct TaskParams {
     const double* state;
     double* state_rw;
     const double* state0;
+    double* saved;                       // the state of the last SAVED snapshot (Sim.cpp:105-115: history[sim_time]), same layout as `state`
     const EnvDesc* envs;
     const TaskEnvRec* tenv;
     const short4* vox_idx;               // per modular row: TL, TR, BL, BR point index inside the robot, -1 = empty voxel
@@ -332,11 +333,23 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         R = object_means(pos, vel, te.r_start, te.r_count, lane);
         P = object_means(pos, vel, te.p_start, te.p_count, lane);
     }
-    if (p.span_prev) {                                   // the shape measure of the (possibly reset) state
+    // What the environment reads from here on is the last SAVED snapshot.  A step that went through (or a reset) has saved one:
+    // the live positions and velocities.  An unstable step has not (Sim.cpp:105-115): the live state is partially advanced, the
+    // reference's getters -- observation, and the next step's "before" values -- still see the snapshot of the step before.
+    double2* opos = reinterpret_cast<double2*>(p.saved + soff);
+    double2* ovel = opos + te.Pd;
+    if (!unstable || was_reset) {
+        for (int i = lane; i < 2 * te.Pd; i += 32) opos[i] = pos[i];
+        __syncwarp();
+    } else {
+        R = object_means(opos, ovel, te.r_start, te.r_count, lane);
+        P = object_means(opos, ovel, te.p_start, te.p_count, lane);
+    }
+    if (p.span_prev) {                                   // the shape measure of that snapshot
         if (p.task >= 27) {
-            if (lane == 0) p.span_prev[env] = hull_area_signed(pos, te.r_start, te.r_count);
+            if (lane == 0) p.span_prev[env] = hull_area_signed(opos, te.r_start, te.r_count);
         } else {
-            const double span = object_span(pos, te.r_start, te.r_count, lane, p.task == 26);
+            const double span = object_span(opos, te.r_start, te.r_count, lane, p.task == 26);
             if (lane == 0) p.span_prev[env] = span;
         }
     }
@@ -376,7 +389,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         if (lane < fp && lane < p.flat_stride) row[lane] = (OutT)oth[lane < 6 ? lane : 0];
         const int n = te.r_count;
         for (int i = lane; i < n; i += 32) {             // get_relative_pos_obs (base.py:228-240 * VOXEL_SIZE)
-            const double2 q = pos[te.r_start + i];
+            const double2 q = opos[te.r_start + i];
             if (fp + i < p.flat_stride) row[fp + i] = (OutT)((q.x / kVoxel - R.bx) * kVoxel);
             if (fp + n + i < p.flat_stride) row[fp + n + i] = (OutT)((q.y / kVoxel - R.by) * kVoxel);
         }
@@ -403,7 +416,7 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
                 } else if (id.x >= 0) {
                     const int k = c & 3;
                     const int pt = k == 0 ? id.x : k == 1 ? id.y : k == 2 ? id.z : id.w;
-                    const double2 q = pos[te.r_start + pt];
+                    const double2 q = opos[te.r_start + pt];
                     v = c < 4 ? (q.x / kVoxel - R.bx) * kVoxel : (q.y / kVoxel - R.by) * kVoxel;
                 }
             }
@@ -634,6 +647,7 @@ struct Batch::Task {
     double* d_ort_prev = nullptr;
     int* d_flips = nullptr;              // Flipper-v0
     double* d_span_prev = nullptr;       // Wingspan / Height maximizer
+    double* d_saved = nullptr;           // positions and velocities of the last saved snapshot of every environment (layout of the state)
     unsigned char* d_flag_planes = nullptr;      // caller's buffer (mevo_batch_task_bind_flag_planes), not owned
     int* d_flat_tail = nullptr;          // sighted tasks: 2 x robot points per environment = how far the sight blocks move right in the flat row
     int flat_fixed = 0;                  // values in front of the relative positions in the flat row
@@ -643,9 +657,9 @@ struct Batch::Task {
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_flat_tail); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_flat_tail); cudaFree(d_saved); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_flat_tail = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_flat_tail = nullptr; d_saved = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -785,6 +799,8 @@ void Batch::task_build() {
     };
     up(T.d_flat_tail, flat_tail);
     up(T.d_rec, T.rec); up(T.d_vox_idx, T.vox_idx); up(T.d_vox_mat, T.vox_mat); up(T.d_act_vox, T.act_vox);
+    CUDA_CHECK(cudaMalloc(&T.d_saved, sizeof(double) * (state_doubles_ + 2)));
+    CUDA_CHECK(cudaMemcpy(T.d_saved, d_state_, sizeof(double) * state_doubles_, cudaMemcpyDeviceToDevice));
     CUDA_CHECK(cudaMalloc(&T.d_prev, sizeof(double) * 4 * n));
     CUDA_CHECK(cudaMalloc(&T.d_episode, sizeof(int) * n));
     CUDA_CHECK(cudaMemset(T.d_prev, 0, sizeof(double) * 4 * n));
@@ -912,7 +928,7 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     task_build();
     Task& T = *task_;
     TaskParams p;
-    p.state = d_state_; p.state_rw = d_state_; p.state0 = d_state0_;
+    p.state = d_state_; p.state_rw = d_state_; p.state0 = d_state0_; p.saved = T.d_saved;
     p.envs = reinterpret_cast<const EnvDesc*>(d_envdesc_);
     p.tenv = T.d_rec; p.vox_idx = T.d_vox_idx; p.vox_mat = T.d_vox_mat;
     p.prev = T.d_prev; p.episode_len = T.d_episode; p.unstable = d_unstable_; p.sim_time = d_time_;
@@ -950,17 +966,17 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     const size_t el = is_f32 ? sizeof(float) : sizeof(double);
     if (D.ort_col >= 0) {
         const int obj = D.ort_of_package ? T.package_obj : T.robot_obj;
-        if (other) object_orientation_strided_device(obj, static_cast<char*>(other) + D.ort_col * el, other_stride, is_f32);
-        if (flat && (D.ort_in_flat || (sighted && D.ort_col < T.flat_fixed))) object_orientation_strided_device(obj, static_cast<char*>(flat) + D.ort_col * el, flat_stride, is_f32);
+        if (other) object_orientation_strided_device(obj, static_cast<char*>(other) + D.ort_col * el, other_stride, is_f32, T.d_saved);
+        if (flat && (D.ort_in_flat || (sighted && D.ort_col < T.flat_fixed))) object_orientation_strided_device(obj, static_cast<char*>(flat) + D.ort_col * el, flat_stride, is_f32, T.d_saved);
     }
-    if (ort_pair) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false);
+    if (ort_pair) object_orientation_strided_device(T.robot_obj, T.d_ort_prev, 1, false, T.d_saved);
     for (const SightPart& sp : D.sight) {
         if (sp.terrain && other)
             sight_obs_strided_device(T.robot_obj, split_names(sp.terrain), sp.dist, 5.0, sp.ceil, static_cast<char*>(other) + sp.col * el,
-                                     2 * sp.dist + 1, other_stride, is_f32);
+                                     2 * sp.dist + 1, other_stride, is_f32, nullptr, T.d_saved);
         if (sp.terrain && flat)                          // same block, behind this environment's relative positions
             sight_obs_strided_device(T.robot_obj, split_names(sp.terrain), sp.dist, 5.0, sp.ceil, static_cast<char*>(flat) + sp.col * el,
-                                     2 * sp.dist + 1, flat_stride, is_f32, T.d_flat_tail);
+                                     2 * sp.dist + 1, flat_stride, is_f32, T.d_flat_tail, T.d_saved);
     }
     if (reset_done) for (auto& e : envs_) e.host_fresh = false;
 }
@@ -1044,7 +1060,7 @@ void Batch::sight_obs_device(int obj_index, const std::vector<std::string>& terr
 }
 
 void Batch::sight_obs_strided_device(int obj_index, const std::vector<std::string>& terrain, int sight_dist, double sight_range, bool ceil,
-                                     void* out, int stride, int row_stride, bool is_f32, const int* env_off) {
+                                     void* out, int stride, int row_stride, bool is_f32, const int* env_off, const double* state_like) {
     CUDA_CHECK(cudaSetDevice(device_));
     if (!finalized_) finalize();
     if (sight_dist < 0 || sight_dist > 1000) throw std::runtime_error("sight_obs: bad sight_dist");
@@ -1107,10 +1123,10 @@ void Batch::sight_obs_strided_device(int obj_index, const std::vector<std::strin
     }
     const int grid = (n + 3) / 4;
     if (is_f32)
-        sight_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
+        sight_kernel<float><<<grid, 128, 0, (cudaStream_t)stream_>>>(state_like ? state_like : d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
                                                                     sight_dist, sight_range, ceil ? 1 : 0, static_cast<float*>(out), stride, row_stride, env_off);
     else
-        sight_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
+        sight_kernel<double><<<grid, 128, 0, (cudaStream_t)stream_>>>(state_like ? state_like : d_state_, reinterpret_cast<const EnvDesc*>(d_envdesc_), S.d_rec, S.d_pts, n,
                                                                      sight_dist, sight_range, ceil ? 1 : 0, static_cast<double*>(out), stride, row_stride, env_off);
     CUDA_CHECK(cudaGetLastError());
 }

@@ -160,6 +160,22 @@ def lower_package(env):
     r.set_state(pos, vel, pos.copy(), vt)
 
 
+# An unstable step saves no snapshot (Sim.cpp:105-115): the environment then reads the snapshot of the step before -- for the
+# observation it returns and for the "before" values of the steps that follow.  Before step FLIP_STEP the robot is crushed to 4 % of
+# its size about its centre of mass (engine state only), which the engine reports as unstable; the rollout goes on without a reset.
+CRUSH_TASKS = ("walkercrush",)
+
+
+def crush_robot(env):
+    r = env._sim._r
+    pos, vel, last, vt = r.get_state()
+    info = r.object_info(list(r.object_names).index("robot"))
+    sl = slice(info["min_point"], info["max_point"] + 1)
+    c = pos[sl].mean(axis=0)
+    pos[sl] = c + 0.04 * (pos[sl] - c)
+    r.set_state(pos, vel, pos.copy(), vt)
+
+
 def drop_robot(env):
     r = env._sim._r
     pos, vel, last, vt = r.get_state()
@@ -228,7 +244,8 @@ def main():
              "flipper": (Flipping, "Flipper-v0"), "beamtoppler": (ToppleBeam, "BeamToppler-v0"), "beamslider": (SlideBeam, "BeamSlider-v0"),
              "wingspan": (MaximizeXShape, "WingspanMazimizer-v0"), "height": (MaximizeYShape, "HeightMaximizer-v0"),
              "areamax": (MaximizeShape, "AreaMaximizer-v0"), "areamin": (MinimizeShape, "AreaMinimizer-v0"),
-             "traverser": (BlockSoup, "Traverser-v0"), "catcher": (CatchSmallRect, "Catcher-v0")}
+             "traverser": (BlockSoup, "Traverser-v0"), "catcher": (CatchSmallRect, "Catcher-v0"),
+             "walkercrush": (WalkingFlat, "Walker-v0")}
     only = [a for a in sys.argv[1:] if not a.startswith("-")]          # e.g. `make_env_golden.py bridgewalker`: only these tasks
     n_steps = 12
     for task, (cls, env_id) in tasks.items():
@@ -240,7 +257,7 @@ def main():
             body, conn = sample_robot((5, 5))
             rng = np.random.default_rng(500 + seed)
             out = {"body": body.astype(np.int32), "connections": np.asarray(conn, dtype=np.int32), "env_id": env_id}
-            if task in FLIP_TASKS or task in DROP_TASKS or task in TWIST_TASKS or task in LOWER_TASKS:
+            if task in FLIP_TASKS or task in DROP_TASKS or task in TWIST_TASKS or task in LOWER_TASKS or task in CRUSH_TASKS:
                 out["flip_step"] = np.int32(FLIP_STEP)
             # ---- flat mode
             env = cls(body, conn, mode=None, env_id=env_id)
@@ -260,6 +277,8 @@ def main():
                     twist_robot(env, TWIST_ANGLE[task])
                 if task in LOWER_TASKS and t == FLIP_STEP:
                     lower_package(env)
+                if task in CRUSH_TASKS and t == FLIP_STEP:
+                    crush_robot(env)
                 # engine state the step starts from (teacher forcing in the GPU test)
                 st = env._sim._r.get_state()
                 for k, v in zip(("pos", "vel", "pos_last", "vel_true"), st):
@@ -294,6 +313,8 @@ def main():
                     twist_robot(envm, TWIST_ANGLE[task])
                 if task in LOWER_TASKS and t == FLIP_STEP:
                     lower_package(envm)
+                if task in CRUSH_TASKS and t == FLIP_STEP:
+                    crush_robot(envm)
                 o, r, d, _ = envm.step(vox_acts[t].copy())
                 mod_obs.append(np.asarray(o["modular"], dtype=np.float64)); other_obs.append(np.asarray(o["other"], dtype=np.float64))
                 mrew.append(float(r)); mdone.append(bool(d))

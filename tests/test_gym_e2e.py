@@ -25,5 +25,5 @@ def test_reference_gym_envs_run_on_this_engine():
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     lines = [json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")]
     assert lines[-1]["summary"] == "ok"
-    assert lines[-1]["fixtures"] >= 40
+    assert lines[-1]["fixtures"] >= 41
     assert sum(1 for l in lines if "smoke" in l) == 32
