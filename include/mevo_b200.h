@@ -336,6 +336,14 @@ int mevo_batch_task_reset(mevo_batch* b, double* flat, int flat_stride, double* 
 int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, void* modular, int modular_stride, void* other,
                                  int other_stride, int is_f32);
 
+/* Catcher-v0 (task 31): CatchSmallRect.reset re-draws where the package is launched from and rebuilds its world
+ * (manipulate.py:646-671, 815).  Environments are BUILT with one draw each (the host's); when mevo_batch_task_outputs(reset_done = 1)
+ * restarts an episode it gives the environment the launch position -- the two static pegs and the package's snapshot-0 points -- of
+ * a uniformly drawn environment of the batch, i.e. one of the batch's own draws.  out[env] (n_envs ints) = the environment whose
+ * launch position `env` runs now.  Host-side views of `env`'s world (the static rows of mevo_env_get_state, mevo_env_render) keep
+ * showing the pegs where it was built; mevo_batch_task_reset returns every environment to its own. */
+int mevo_batch_task_launch_sources(mevo_batch* b, int* out);
+
 /* Optional second form of the done byte: `device_planes` points to 3 * n_envs bytes on the device; every later
  * mevo_batch_task_outputs[_device] call that writes `done` also writes done / truncated / unstable as 0 or 1 into the three planes
  * (the layout of a bool tensor of shape (3, n): what SubprocVecEnv's `done` array and the TimeLimit / unstable infos are).  The

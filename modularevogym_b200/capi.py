@@ -96,6 +96,7 @@ SIGNATURES: Dict[str, tuple] = {
     "mevo_batch_task_outputs_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i]),
     "mevo_batch_task_reset": (_i, [_vp, _dp, _i, _dp, _i, _dp, _i]),
     "mevo_batch_task_bind_flag_planes": (_i, [_vp, _vp]),
+    "mevo_batch_task_launch_sources": (_i, [_vp, _ip]),
     "mevo_batch_task_set_goals": (_i, [_vp, _i, _i, _ip, _ip, _i]),
     "mevo_batch_task_draw_goals": (_i, [_vp, C.c_ulonglong]),
     "mevo_batch_task_get_goals": (_i, [_vp, _i, _ip, _ip, _ip, _i]),
@@ -557,6 +558,12 @@ class Batch:
         vp = lambda p: C.c_void_p(p) if p else None
         _check(self.L.mevo_batch_task_reset_device(self.h, vp(flat_ptr), int(flat_stride), vp(modular_ptr), int(modular_stride),
                                                    vp(other_ptr), int(other_stride), int(is_f32)))
+
+    def task_launch_sources(self) -> np.ndarray:
+        """Catcher-v0: per environment, the environment whose launch position (pegs, package start) it runs now"""
+        out = np.zeros(self.num_envs, dtype=np.int32)
+        _check(self.L.mevo_batch_task_launch_sources(self.h, _iptr(out)))
+        return out
 
     def task_bind_flag_planes(self, device_ptr: int) -> None:
         """``device_ptr``: 3 * n bytes (a ``torch.bool`` tensor of shape (3, n)) that every later task_outputs call fills with done /

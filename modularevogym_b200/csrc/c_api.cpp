@@ -589,6 +589,14 @@ int mevo_batch_task_reset_device(mevo_batch* b, void* flat, int flat_stride, voi
     });
 }
 
+int mevo_batch_task_launch_sources(mevo_batch* b, int* out) {
+    return guard([&] {
+        if (!out) throw std::runtime_error("mevo_batch_task_launch_sources: null argument");
+        b->impl.task_launch_sources(out);
+        return 0;
+    });
+}
+
 int mevo_batch_task_bind_flag_planes(mevo_batch* b, void* device_planes) {
     return guard([&] {
         b->impl.task_bind_flag_planes(device_planes);

@@ -136,6 +136,7 @@ public:
     void task_reset_device(void* flat, int flat_stride, void* modular, int modular_stride, void* other, int other_stride, bool is_f32);
     void task_reset(double* flat, int flat_stride, double* modular, int modular_stride, double* other, int other_stride);
     // BidirectionalWalker-v0 (multi_goal.py:91-205): per-environment goal lists -- from the host, or drawn on the device
+    void task_launch_sources(int* out);                 // Catcher-v0: whose launch position each environment runs now (n ints)
     void task_bind_flag_planes(void* device_planes);    // 3 x n bytes: done, truncated, unstable as 0 / 1 (nullptr: off)
     void task_set_goals(int env_first, int n_envs, const int* counts, const int* goals, int stride);
     void task_draw_goals(unsigned long long seed);

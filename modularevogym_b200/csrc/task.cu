@@ -20,6 +20,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -87,6 +88,13 @@ struct TaskParams {
     // goal, [2] lists drawn on the device so far, [3 ...] the goals' x positions in voxels
     int* goals;
     unsigned long long goal_seed;
+    // Catcher-v0 (manipulate.py:815: every reset re-draws where the package is launched from): an episode restarted on the device
+    // takes over the launch position -- static geometry (the two pegs) and the package's snapshot-0 points -- of a uniformly drawn
+    // environment of the batch, i.e. one of the batch's own draws of the reference's random.randint pair
+    EnvDesc* envs_rw;                    // nullptr: off
+    const unsigned long long* static0;   // static_off of every environment as built
+    int* draws;                          // per environment: resamples so far
+    int* source;                         // per environment: whose launch position it runs now
 };
 
 constexpr int kGoalStride = 64, kMaxGoals = kGoalStride - 3;
@@ -323,6 +331,25 @@ __global__ void __launch_bounds__(128) task_outputs_kernel(TaskParams p) {
         }
         __syncwarp();
         if (lane == 0) { p.sim_time[env] = 0; p.unstable[env] = 0; if (p.flips) p.flips[env] = 0; }
+        if (p.envs_rw) {                                 // Catcher-v0: the launch position of a drawn environment (see TaskParams)
+            int j = 0;
+            if (lane == 0) {
+                unsigned long long x = p.goal_seed ^ (0xd1342543de82ef95ull * (unsigned long long)(env + 1)) ^
+                                       (0x2545f4914f6cdd1dull * (unsigned long long)(p.draws[env] + 1));
+                p.draws[env] += 1;
+                j = (int)__umul64hi(splitmix64(x), (unsigned long long)p.n_envs);
+                p.envs_rw[env].static_off = p.static0[j];
+                p.source[env] = j;
+            }
+            j = __shfl_sync(0xffffffffu, j, 0);
+            const TaskEnvRec tj = p.tenv[j];
+            const double2* sj = reinterpret_cast<const double2*>(p.state0 + p.envs[j].state_off);
+            for (int i = lane; i < te.p_count && i < tj.p_count; i += 32) {
+                const double2 q = sj[tj.p_start + i], v = sj[tj.Pd + tj.p_start + i];
+                pos[te.p_start + i] = q; vel[te.p_start + i] = v; pos[2 * te.Pd + te.p_start + i] = q; pos[3 * te.Pd + te.p_start + i] = v;
+            }
+            __syncwarp();
+        }
         if (p.task == 29) {                              // BiWalk.reset (multi_goal.py:178-184): first goal of a new list
             if (lane == 0) draw_goals(p.goals + (size_t)env * kGoalStride, env, p.goal_seed);
             __syncwarp();
@@ -527,6 +554,11 @@ __global__ void __launch_bounds__(128) sight_kernel(const double* state, const E
     for (int c = n_cols + lane; c < stride; c += 32) row[c] = (OutT)0;
 }
 
+__global__ void source_identity_kernel(int* source, int n_envs) {
+    const int env = blockIdx.x * blockDim.x + threadIdx.x;
+    if (env < n_envs) source[env] = env;
+}
+
 __global__ void draw_goals_kernel(int* goals, int n_envs, unsigned long long seed) {
     const int env = blockIdx.x * blockDim.x + threadIdx.x;
     if (env < n_envs) draw_goals(goals + (size_t)env * kGoalStride, env, seed);
@@ -609,7 +641,7 @@ const TaskDesc kTasks[] = {
     /* 32 */ {"UpStepper-v0 (flat mode)", 1, 69, 2, true, 0, false, 14, 2, 2, 2, false, false, MEVO_FLOOR5("ground")},
 };
 constexpr int kNumTasks = (int)(sizeof(kTasks) / sizeof(kTasks[0]));
-constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29, kTaskUpStepperFlat = 32;
+constexpr int kTaskFlipper = 22, kTaskWingspan = 25, kTaskAreaMin = 28, kTaskBiWalk = 29, kTaskCatcher = 31, kTaskUpStepperFlat = 32;
 
 std::vector<std::string> split_names(const char* names) {
     std::vector<std::string> out;
@@ -647,6 +679,8 @@ struct Batch::Task {
     double* d_ort_prev = nullptr;
     int* d_flips = nullptr;              // Flipper-v0
     double* d_span_prev = nullptr;       // Wingspan / Height maximizer
+    int* d_source = nullptr;             // Catcher-v0: environment whose launch position each environment runs now
+    unsigned long long* d_static0 = nullptr;     // Catcher-v0: static_off of every environment as built
     double* d_saved = nullptr;           // positions and velocities of the last saved snapshot of every environment (layout of the state)
     unsigned char* d_flag_planes = nullptr;      // caller's buffer (mevo_batch_task_bind_flag_planes), not owned
     int* d_flat_tail = nullptr;          // sighted tasks: 2 x robot points per environment = how far the sight blocks move right in the flat row
@@ -657,9 +691,9 @@ struct Batch::Task {
     void* d_scratch = nullptr;               // host-facing outputs staged here
     size_t scratch_bytes = 0;
     void free_device() {
-        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_flat_tail); cudaFree(d_saved); cudaFree(d_episode);
+        cudaFree(d_rec); cudaFree(d_vox_idx); cudaFree(d_vox_mat); cudaFree(d_act_vox); cudaFree(d_prev); cudaFree(d_ort_now); cudaFree(d_ort_prev); cudaFree(d_flips); cudaFree(d_span_prev); cudaFree(d_goals); cudaFree(d_flat_tail); cudaFree(d_saved); cudaFree(d_static0); cudaFree(d_source); cudaFree(d_episode);
         cudaFree(d_scratch);
-        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_flat_tail = nullptr; d_saved = nullptr; d_episode = nullptr;
+        d_rec = nullptr; d_vox_idx = nullptr; d_vox_mat = nullptr; d_act_vox = nullptr; d_prev = nullptr; d_ort_now = nullptr; d_ort_prev = nullptr; d_flips = nullptr; d_span_prev = nullptr; d_goals = nullptr; d_flat_tail = nullptr; d_saved = nullptr; d_static0 = nullptr; d_source = nullptr; d_episode = nullptr;
         d_scratch = nullptr; scratch_bytes = 0;
     }
 };
@@ -812,6 +846,18 @@ void Batch::task_build() {
     CUDA_CHECK(cudaMalloc(&T.d_span_prev, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_span_prev, 0, sizeof(double) * n));
     CUDA_CHECK(cudaMemset(T.d_episode, 0, sizeof(int) * n));
+    if (T.task == kTaskCatcher) {                        // the launch positions the batch was built with
+        std::vector<EnvDesc> desc(n);
+        CUDA_CHECK(cudaMemcpy(desc.data(), d_envdesc_, sizeof(EnvDesc) * n, cudaMemcpyDeviceToHost));
+        std::vector<unsigned long long> off(n);
+        for (int e = 0; e < n; e++) off[e] = desc[e].static_off;
+        CUDA_CHECK(cudaMalloc(&T.d_static0, sizeof(unsigned long long) * n));
+        CUDA_CHECK(cudaMemcpy(T.d_static0, off.data(), sizeof(unsigned long long) * n, cudaMemcpyHostToDevice));
+        std::vector<int> self(n);
+        for (int e = 0; e < n; e++) self[e] = e;
+        CUDA_CHECK(cudaMalloc(&T.d_source, sizeof(int) * n));
+        CUDA_CHECK(cudaMemcpy(T.d_source, self.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    }
     if (T.task == kTaskBiWalk) {                         // every environment starts with a drawn list (BiWalk.__init__, multi_goal.py:108)
         CUDA_CHECK(cudaMalloc(&T.d_goals, sizeof(int) * kGoalStride * n));
         CUDA_CHECK(cudaMemset(T.d_goals, 0, sizeof(int) * kGoalStride * n));
@@ -861,6 +907,17 @@ void Batch::task_draw_goals(unsigned long long seed) {
 void Batch::task_bind_flag_planes(void* device_planes) {
     if (!task_) throw std::runtime_error("task layer used before mevo_batch_task_configure");
     task_->d_flag_planes = static_cast<unsigned char*>(device_planes);
+}
+
+// Catcher-v0: out[env] = the environment whose launch position (pegs, package start) `env` runs now -- itself until the task kernel
+// restarts its episode.  The host-side world of `env` (mevo_env_get_state's rows of static points, the rasteriser) keeps showing the
+// pegs where the environment was BUILT; the simulation uses those of out[env].
+void Batch::task_launch_sources(int* out) {
+    task_build();
+    Task& T = *task_;
+    if (!T.d_source) throw std::runtime_error("task_launch_sources: the configured task does not re-draw launch positions");
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    CUDA_CHECK(cudaMemcpy(out, T.d_source, sizeof(int) * num_envs(), cudaMemcpyDeviceToHost));
 }
 
 // (count, current index, goals ...) of one environment, for hosts and tests
@@ -946,7 +1003,9 @@ void Batch::task_outputs_device(void* reward, unsigned char* done, void* flat, i
     p.ort_band = T.task == kTaskUpStepperFlat ? kPi / 12 : 0.0;
     p.flips = T.task == kTaskFlipper ? T.d_flips : nullptr;
     p.span_prev = T.task >= kTaskWingspan && T.task <= kTaskAreaMin ? T.d_span_prev : nullptr;
-    p.goals = T.d_goals; p.goal_seed = T.goal_seed;          // the ShapeChange tasks (25 ... 28)
+    p.goals = T.d_goals; p.goal_seed = T.goal_seed;
+    const bool resample = T.task == kTaskCatcher && T.d_static0 && reset_done;
+    p.envs_rw = resample ? reinterpret_cast<EnvDesc*>(d_envdesc_) : nullptr; p.static0 = T.d_static0; p.draws = T.d_flips; p.source = T.d_source;          // the ShapeChange tasks (25 ... 28)
     if (other && other_stride < D.other_width)
         throw std::runtime_error("task_outputs: the 'other' observation of this task is " + std::to_string(D.other_width) + " wide");
     const bool sighted = D.sight[0].terrain || D.sight[1].terrain;
@@ -1023,6 +1082,11 @@ void Batch::task_reset_device(void* flat, int flat_stride, void* modular, int mo
     CUDA_CHECK(cudaMemsetAsync(T.d_flips, 0, sizeof(int) * num_envs(), (cudaStream_t)stream_));
     if (T.d_goals)                                       // current goal <- 0; the lists stay (new ones: task_set_goals / task_draw_goals first)
         CUDA_CHECK(cudaMemset2DAsync(T.d_goals + 1, sizeof(int) * kGoalStride, 0, sizeof(int), num_envs(), (cudaStream_t)stream_));
+    if (T.d_static0)                                     // Catcher-v0: snapshot 0 is the launch position the environment was built with
+        CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(d_envdesc_) + offsetof(EnvDesc, static_off), sizeof(EnvDesc), T.d_static0,
+                                     sizeof(unsigned long long), sizeof(unsigned long long), num_envs(), cudaMemcpyDeviceToDevice,
+                                     (cudaStream_t)stream_));
+    if (T.d_source) source_identity_kernel<<<(num_envs() + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(T.d_source, num_envs());
     task_outputs_device(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, is_f32, false);
 }
 
@@ -1034,6 +1098,11 @@ void Batch::task_reset(double* flat, int flat_stride, double* modular, int modul
     CUDA_CHECK(cudaMemsetAsync(T.d_flips, 0, sizeof(int) * num_envs(), (cudaStream_t)stream_));
     if (T.d_goals)                                       // current goal <- 0; the lists stay (new ones: task_set_goals / task_draw_goals first)
         CUDA_CHECK(cudaMemset2DAsync(T.d_goals + 1, sizeof(int) * kGoalStride, 0, sizeof(int), num_envs(), (cudaStream_t)stream_));
+    if (T.d_static0)                                     // Catcher-v0: snapshot 0 is the launch position the environment was built with
+        CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(d_envdesc_) + offsetof(EnvDesc, static_off), sizeof(EnvDesc), T.d_static0,
+                                     sizeof(unsigned long long), sizeof(unsigned long long), num_envs(), cudaMemcpyDeviceToDevice,
+                                     (cudaStream_t)stream_));
+    if (T.d_source) source_identity_kernel<<<(num_envs() + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(T.d_source, num_envs());
     task_outputs(nullptr, nullptr, flat, flat_stride, modular, modular_stride, other, other_stride, false);
 }
 

@@ -59,7 +59,8 @@ TASKS = {
     "Traverser-v0": (30, traverser_world, None, 600),                         # traverse.py:784-911, __init__.py:100-104
     # Catcher-v0: the reference re-draws the package's launch position at EVERY reset (it rebuilds its world and its simulator,
     # manipulate.py:815).  Here it is drawn per environment whenever the batch is built -- construction, update() and reset(), which
-    # rebuilds the batch like the reference does -- while episodes restarted on the device keep their environment's draw
+    # rebuilds the batch like the reference does -- and an episode restarted on the device takes over the launch position of a
+    # uniformly drawn environment of the batch: one of the batch's own draws (mevo_batch_task_launch_sources)
     "Catcher-v0": (31, catcher_world, "package", 400),                        # manipulate.py:630-886, __init__.py:155-159
     "Jumper-v0": (9, jumper_world, None, 500),                                # evogym/envs/jump.py:14-118, __init__.py:34-38
 }
