@@ -4,7 +4,7 @@ Host-side mirror of what the reference assembles per rollout worker out of proce
 (``examples/transformer_ppo/envs.py:29-77`` ``make_env`` / ``make_vec_envs``: ``gym.make(env_id, body=..., mode='modular')``
 -> ``TimeLimit`` -> ``SubprocVecEnv`` (``examples/modular_envs/wrappers/subproc_vec_env.py``: reset on done, return the reset
 observation) -> ``VecPyTorch`` (``envs.py:126-159``: numpy -> float32 torch tensors on the device, reward ``(n, 1)``)),
-for the environments the benchmark configurations name (Walker-v0, Pusher-v0, Thrower-v0, Climber-v0, ObstacleTraverser-v1).
+for all 32 environment ids the reference registers (``TASKS``), in ModularEvoGym's modular mode and in EvoGym's flat mode.
 
 One env-step of all environments = three launches on one CUDA stream and no host round trip:
 policy output -> actuator targets (``policy_actions_kernel``), 30 substeps (``wstep_kernel`` / ``step_kernel``),
@@ -84,7 +84,8 @@ class BatchedEvoGymEnv:
 
     ``mode='modular'`` (ModularEvoGym, ``evogym/envs/base.py:746-753``): observations are a dict ``modular`` (n, 9 * voxels),
     ``other`` (n, 2 | 6), ``act_mask`` / ``obs_mask`` (n, voxels), ``stage`` (n, 1); actions are one value per voxel.
-    ``mode=None`` (EvoGym): the flat observation (n, width) and one action value per actuator.
+    ``mode=None`` (EvoGym): the flat observation (n, width) and one action value per actuator; robots with fewer points than the
+    widest one have their row zero-padded at the end (sight blocks and goal values follow each robot's OWN relative positions).
     ``worlds`` overrides the built-in terrain (a ``WorldSpec`` per environment that already contains the robot)."""
 
     def __init__(self, env_id: str, bodies: Sequence[np.ndarray], connections: Optional[Sequence[Optional[np.ndarray]]] = None,
